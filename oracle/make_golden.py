@@ -1,0 +1,165 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (under
+oracle/reference_shim.py) and the oracle restatement on the same seeded inputs,
+asserting they agree, and saving the reference's outputs.
+
+Run in the build container (needs /root/reference):  python -m oracle.make_golden
+TEST INFRASTRUCTURE ONLY.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import oracle, reference_shim  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, 'tests', 'golden')
+
+
+def seeded(shape, seed, scale=1.0):
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale
+
+
+def rel(a, b):
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def grads_err(ours, theirs):
+    """Worst per-tensor relative L2 error.  Conv biases that feed an
+    InstanceNorm have an analytically ZERO gradient (the norm removes the
+    mean), so what autograd reports for them is rounding noise (~1e-9): errors
+    are measured relative to max(|tensor|, 1e-3 * the largest tensor norm)."""
+    floor = 1e-3 * max(float(g.norm()) for g in theirs.values())
+    return max(float((ours[k] - theirs[k]).norm()) / max(float(theirs[k].norm()), floor) for k in theirs)
+
+
+def summarize_grads(grads):
+    """Per-tensor L2 norm, sum and the first 16 entries (full tensors are 6.7 MB)."""
+    out = {}
+    for k, g in grads.items():
+        flat = g.reshape(-1)
+        out['gnorm/' + k] = np.float64(flat.double().norm().item())
+        out['gsum/' + k] = np.float64(flat.double().sum().item())
+        out['ghead/' + k] = flat[:16].numpy().copy()
+        if flat.numel() <= 4096:
+            out['gfull/' + k] = g.numpy().copy()
+    return out
+
+
+def ref_closure_losses(ref_loss_net, sw, cw):
+    style = ref_loss_net.get_total_current_style_loss(weight=sw)
+    content = ref_loss_net.get_total_current_content_loss(weight=cw)
+    per_node = torch.stack([n[0].loss for n in ref_loss_net.style_losses] +
+                           [n[0].loss for n in ref_loss_net.content_losses] +
+                           [n[0].loss for n in ref_loss_net.feature_losses])
+    return style, content, per_node
+
+
+def gatys_case(ref, name, h, w, sw=100_000.0, cw=1.0):
+    vw = oracle.make_vgg_weights(1)
+    content = seeded((1, 3, h, w), 10)
+    style = seeded((1, 3, h, w), 11)
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12)
+    # reference: StyleNetwork + the closure body of train_gatys (network.py:438-454)
+    net = ref.StyleNetwork(style, content)
+    x = x0.clone().requires_grad_(True)
+    net(x, content)
+    s, c, per_node = ref_closure_losses(net, sw, cw)
+    total = s + c
+    total.backward()
+    # oracle
+    targets = oracle.style_targets(style, vw)
+    o_total, o_grad, o_losses = oracle.gatys_closure(x0, content, targets, vw, sw, cw)
+    errs = dict(total=abs(o_total.item() - total.item()) / abs(total.item()),
+                grad=rel(o_grad, x.grad), losses=rel(o_losses, per_node.detach()))
+    print(name, 'oracle-vs-reference', errs)
+    assert errs['total'] < 1e-5 and errs['grad'] < 1e-4 and errs['losses'] < 1e-5, errs
+    taps = oracle.vgg_taps(x0, vw)
+    np.savez_compressed(
+        os.path.join(GOLDEN, name + '.npz'),
+        h=h, w=w, sw=sw, cw=cw, total=np.float64(total.item()),
+        losses=per_node.detach().numpy(), grad=x.grad.numpy(),
+        tap_norms=np.array([t.double().norm().item() for t in taps]),
+        gram_norms=np.array([oracle.gram_matrix(t).double().norm().item() for t in taps]),
+        style_target_gram0=targets[0].numpy())
+
+
+def load_params(module, params):
+    sd = module.state_dict()
+    assert set(sd.keys()) == set(params.keys()), set(sd.keys()) ^ set(params.keys())
+    module.load_state_dict({k: v.clone() for k, v in params.items()})
+
+
+def fast_case(ref, name, b, s, sw=100_000.0, cw=1.0):
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(2, 3)
+    style = seeded((1, 3, s, s), 21)
+    batch = seeded((b, 3, s, s), 22)
+    net = ref.ImageTransformNet(style, b)
+    load_params(net, params)
+    loss_net = ref.StyleNetwork(style, torch.rand([1, 3, s, s]))
+    # closure body of static_train (network.py:690-731)
+    out = net(batch)
+    loss_net(out, content_image=batch)
+    st, ct, per_node = ref_closure_losses(loss_net, sw, cw)
+    total = st + ct + net.get_total_variation_regularization_loss(out)
+    total.backward()
+    rgrads = {k: p.grad.detach() for k, p in net.named_parameters()}
+    targets = oracle.style_targets(style, vw)
+    o_total, o_grads, o_out, o_losses = oracle.fast_st_closure(batch, params, targets, vw, sw, cw)
+    errs = dict(total=abs(o_total.item() - total.item()) / abs(total.item()), out=rel(o_out, out.detach()),
+                grads=grads_err(o_grads, rgrads))
+    print(name, 'oracle-vs-reference', errs)
+    assert errs['total'] < 1e-5 and errs['out'] < 1e-5 and errs['grads'] < 1e-4, errs
+    np.savez_compressed(os.path.join(GOLDEN, name + '.npz'), b=b, s=s, sw=sw, cw=cw,
+                        total=np.float64(total.item()), losses=per_node.detach().numpy(),
+                        out=out.detach().numpy(), **summarize_grads(rgrads))
+
+
+def video_case(ref, name, b, s, sw=100_000.0, cw=1.0, tw=0.8):
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(3, 6)
+    style = seeded((1, 3, s, s), 31)
+    batch = seeded((b, 3, s, s), 32)
+    old_content = batch + 0.05 * seeded((b, 3, s, s), 33)
+    old_stylized = seeded((b, 3, s, s), 34)
+    net = ref.VideoTransformNet(style, b)
+    load_params(net, params)
+    loss_net = ref.StyleNetwork(style, torch.rand([1, 3, s, s]))
+    # closure body of video_train (network.py:984-1037)
+    out = net(torch.cat([batch, old_stylized], dim=1))
+    loss_net(out, content_image=batch)
+    st, ct, per_node = ref_closure_losses(loss_net, sw, cw)
+    temporal = net.get_temporal_loss(old_content, old_stylized, batch, out, temporal_weight=tw)
+    total = st + ct + net.get_total_variation_regularization_loss(out) + temporal
+    total.backward()
+    rgrads = {k: p.grad.detach() for k, p in net.named_parameters()}
+    targets = oracle.style_targets(style, vw)
+    o_total, o_grads, o_out, _ = oracle.video_closure(batch, old_content, old_stylized, params,
+                                                      targets, vw, sw, cw, tw)
+    errs = dict(total=abs(o_total.item() - total.item()) / abs(total.item()), out=rel(o_out, out.detach()),
+                grads=grads_err(o_grads, rgrads))
+    print(name, 'oracle-vs-reference', errs)
+    assert errs['total'] < 1e-5 and errs['out'] < 1e-5 and errs['grads'] < 1e-4, errs
+    np.savez_compressed(os.path.join(GOLDEN, name + '.npz'), b=b, s=s, sw=sw, cw=cw, tw=tw,
+                        total=np.float64(total.item()), temporal=np.float64(temporal.item()),
+                        losses=per_node.detach().numpy(), out=out.detach().numpy(),
+                        **summarize_grads(rgrads))
+
+
+def main():
+    assert reference_shim.available(), 'needs /root/reference'
+    os.makedirs(GOLDEN, exist_ok=True)
+    torch.manual_seed(0)
+    ref = reference_shim.load_reference(vgg_seed=1)
+    gatys_case(ref, 'gatys_64x64', 64, 64)
+    gatys_case(ref, 'gatys_40x56', 40, 56)       # ragged: not a multiple of the 8x16 tile
+    fast_case(ref, 'fast_st_b2_32', 2, 32)
+    video_case(ref, 'video_st_b2_32', 2, 32)
+    print('golden fixtures written to', GOLDEN)
+
+
+if __name__ == '__main__':
+    main()

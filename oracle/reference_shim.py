@@ -1,0 +1,109 @@
+"""Import the UNMODIFIED reference (``/root/reference/stransfer``) in the build
+container.  TEST INFRASTRUCTURE ONLY -- used by ``oracle/make_golden.py`` and
+``tests/test_oracle_vs_reference.py`` (skipped when /root/reference is absent).
+
+Shims, none of them on the numeric path:
+  1. stub modules for tensorboardX / imageio / matplotlib / colored_traceback;
+  2. ``nn.Conv2d(padding_mode='reflection')`` -> ``'zeros'``: that string is not
+     a valid mode; under the reference's pinned torch 1.1.0 it silently fell
+     through to zero padding, under torch 2.x it raises;
+  3. ``torchvision.models.vgg19(pretrained=True)`` -> random-init VGG-19 whose
+     five executed convs carry ``oracle.make_vgg_weights(seed)`` (no network).
+"""
+import os
+import sys
+import types
+
+import torch
+import torch.nn as nn
+
+REFERENCE_ROOT = os.environ.get('STRANSFER_REFERENCE_ROOT', '/root/reference')
+
+
+def available():
+    return os.path.isdir(os.path.join(REFERENCE_ROOT, 'stransfer'))
+
+
+def _stub_modules():
+    tbx = types.ModuleType('tensorboardX')
+
+    class SummaryWriter:
+        def __init__(self, *a, **k): pass
+        def add_scalar(self, *a, **k): pass
+        def add_image(self, *a, **k): pass
+    tbx.SummaryWriter = SummaryWriter
+    sys.modules.setdefault('tensorboardX', tbx)
+
+    imageio = types.ModuleType('imageio')
+    core = types.ModuleType('imageio.core')
+    fmt = types.ModuleType('imageio.core.format')
+
+    class Format:
+        class Reader: pass
+    fmt.Format = Format
+    core.format = fmt
+    imageio.core = core
+    sys.modules.setdefault('imageio', imageio)
+    sys.modules.setdefault('imageio.core', core)
+    sys.modules.setdefault('imageio.core.format', fmt)
+
+    mpl = types.ModuleType('matplotlib')
+    plt = types.ModuleType('matplotlib.pyplot')
+    mpl.pyplot = plt
+    sys.modules.setdefault('matplotlib', mpl)
+    sys.modules.setdefault('matplotlib.pyplot', plt)
+
+    ct = types.ModuleType('colored_traceback')
+    ct.add_hook = lambda *a, **k: None
+    sys.modules.setdefault('colored_traceback', ct)
+
+
+_ORIG_CONV_INIT = nn.Conv2d.__init__
+
+
+def _conv_init(self, *a, **k):
+    if k.get('padding_mode') == 'reflection':
+        k['padding_mode'] = 'zeros'
+    _ORIG_CONV_INIT(self, *a, **k)
+
+
+def load_reference(vgg_seed=1, workdir='/tmp/stransfer_ref_cwd'):
+    """Returns the reference's ``stransfer.network`` module (CPU)."""
+    import warnings
+    import torchvision
+    from oracle import oracle
+
+    _stub_modules()
+    nn.Conv2d.__init__ = _conv_init
+
+    def vgg19(pretrained=False, **kw):
+        m = torchvision.models.vgg.vgg19(weights=None)
+        with torch.no_grad():
+            for idx, (w, b) in zip(oracle.VGG_FEATURE_IDX, oracle.make_vgg_weights(vgg_seed)):
+                m.features[idx].weight.copy_(w)
+                m.features[idx].bias.copy_(b)
+        return m
+    torchvision.models.vgg19 = vgg19
+
+    os.makedirs(workdir, exist_ok=True)      # the import creates ./runs/runtime.log
+    cwd = os.getcwd()
+    os.chdir(workdir)
+    # the repo root holds a drop-in package that is ALSO called `stransfer`;
+    # make sure the reference's copy is the one imported here.
+    for name in [n for n in sys.modules if n == 'stransfer' or n.startswith('stransfer.')]:
+        del sys.modules[name]
+    sys.path.insert(0, REFERENCE_ROOT)
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            import stransfer.network as ref_network
+    finally:
+        sys.path.remove(REFERENCE_ROOT)
+        os.chdir(cwd)
+    assert ref_network.__file__.startswith(REFERENCE_ROOT), ref_network.__file__
+    mods = {n: m for n, m in sys.modules.items() if n == 'stransfer' or n.startswith('stransfer.')}
+    for n in mods:                           # leave no alias behind for the drop-in package
+        del sys.modules[n]
+    ref_network._shim_modules = mods
+    torch.set_default_dtype(torch.float32)
+    return ref_network
