@@ -1,0 +1,130 @@
+/* libstransfer_b200.so -- C ABI of the B200 (sm_100a) kernels behind
+ * tupini07/StyleTransfer's `stransfer.network` hot path.
+ *
+ * The reference has no FFI of its own: every numeric op is a stock torch call.
+ * Each entry point below replaces the torch call(s) cited beside it
+ * (file:line into /root/reference/stransfer/network.py); INTEGRATION.md shows
+ * the ctypes binding + torch.autograd.Function a maintainer would add there.
+ *
+ * Conventions
+ *  - every function returns 0 on success or a negative ST_ERR_* code;
+ *    st_last_error() returns a thread-local message for the last failure.
+ *  - all data pointers are DEVICE pointers owned by the caller; nothing is
+ *    allocated inside; scratch comes from a caller-provided workspace whose
+ *    size the matching *_workspace_bytes() query returns.
+ *  - every launch is stream-ordered on `stream` (a cudaStream_t); no hidden
+ *    synchronisation, so the calls can be captured in a CUDA graph.
+ *  - activations use the "split-bf16 NHWC" format: channels-last, two bf16
+ *    planes hi = bf16(x), lo = bf16(x - hi).  A NULL lo plane selects plain
+ *    bf16 (1 tensor-core pass per product instead of 3).  Channel counts are
+ *    multiples of 8 (images are padded 3/6 -> 8 with zeros).
+ *  - scalars that come from autograd (loss weights = grad_output entries) are
+ *    passed as device pointers (`gw`) so that no host sync is needed.
+ */
+#ifndef STRANSFER_B200_H
+#define STRANSFER_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ST_OK 0
+#define ST_ERR_INVALID (-1)
+#define ST_ERR_CUDA (-2)
+#define ST_ERR_UNSUPPORTED (-3)
+
+/* build info: compute capability the kernels were compiled for (100) */
+int st_arch(void);
+const char* st_last_error(void);
+/* 0 = auto (tcgen05 where eligible), 1 = force the generic mma.sync conv (testing) */
+int st_set_conv_path(int path);
+
+/* ---- layout / packing ------------------------------------------------- */
+/* img_utils/torch.cat boundary: NCHW fp32 (optionally two tensors concatenated on
+ * channels, network.py:984-986) -> split-bf16 NHWC with Cpad channels. */
+int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo,
+                    int N, int C1, int C2, int H, int W, int Cpad, void* stream);
+int st_nhwc_to_nchw(const void* hi, const void* lo, float* out,
+                    int N, int C, int H, int W, int Cpad, void* stream);
+/* nn.Conv2d.weight [Cout][Cin][ks][ks] fp32 -> packed [rows_pad][ks*ks][cols_pad] split-bf16.
+ * mode 0 forward; 1 backward-data (gather form, any stride); 2 backward-data as a
+ * forward conv with flipped taps (stride 1). */
+int st_pack_conv_weight(const float* w, void* hi, void* lo, int Cout, int Cin, int ks,
+                        int rows_pad, int cols_pad, int mode, void* stream);
+
+/* ---- convolution ------------------------------------------------------ */
+/* nn.Conv2d forward (network.py:246-275 VGG, :468-481, :525-609 transform net) and
+ * its autograd backward-data.  y = conv(x, w) [+bias] ; y *= (mask > 0) ; y += add ;
+ * out = y ; relu_out = relu(y).  `up`=1 reads x through a nearest x2 upsample
+ * (nn.Upsample network.py:580-594).  `transposed`=1 evaluates the backward-data
+ * gather (weights packed with mode 1).  w_img_rows != 0 selects per-image weights
+ * (rows n*w_img_rows.. of the packed matrix): used for the Gram backward dF = F*D.
+ * out_nchw (optional) receives the first Cnchw channels as NCHW fp32. */
+int st_conv2d(const void* x_hi, const void* x_lo, int N, int H, int W, int Cin, int up,
+              const void* w_hi, const void* w_lo, int w_rows_total, int w_img_rows,
+              int ks, int stride, int pad, int transposed,
+              int Ho, int Wo, int Cout_pad, int Cbias,
+              const float* bias, const void* mask, const void* add_hi, const void* add_lo,
+              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo,
+              float* out_nchw, int Cnchw, void* stream);
+
+/* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]) */
+size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks);
+int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy,
+                    const void* x_hi, const void* x_lo, int N, int H, int W, int CinPad, int up,
+                    int Ho, int Wo, int ks, int stride, int pad, int Cout, int Cin,
+                    float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- VGG pieces -------------------------------------------------------- */
+/* nn.ReLU + nn.MaxPool2d(2,2) of VGG pieces 2 and 5 (network.py:257-314) */
+int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo,
+                           int N, int H, int W, int C, void* stream);
+/* backward: gx = route(gy) * relu'(x) + add */
+int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
+                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo,
+                           int N, int H, int W, int C, void* stream);
+
+/* ---- losses ------------------------------------------------------------ */
+/* StyleLoss.gram_matrix (network.py:92-108): G[b] = F_b^T F_b / (C*H*W), fp32 [B][C][C] */
+size_t st_gram_workspace_bytes(int B, int HW, int C);
+int st_gram_fwd(const void* f_hi, const void* f_lo, int B, int HW, int C, float* G,
+                void* workspace, size_t workspace_bytes, void* stream);
+/* StyleLoss.forward (network.py:110-123): loss = mean((G - T)^2), T [C][C] broadcast;
+ * diff = G - T is kept for the backward.  ws: >= 4096 floats */
+int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* ws, void* stream);
+/* backward seed: D = (*gw) * 4/(B*C^2*C*HW) * diff, packed split-bf16 [B*C][C];
+ * dF = F * D is then st_conv2d(ks=1, w_img_rows=C). */
+int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* gw, void* d_hi, void* d_lo, void* stream);
+/* ContentLoss (network.py:155-164) / FeatureReconstructionLoss (network.py:186-201):
+ * relu=1 compares relu(x) with relu(t); feature_form=1 returns mse^2/numel. */
+int st_mse_fwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel,
+               int relu, int feature_form, float* loss, float* ws, void* stream);
+/* g (+)= scale * (*gw) * (mul ? *mul : 1) * (f(x) - f(t)) * f'(x) */
+int st_mse_bwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel,
+               int relu, float scale, const float* gw, const float* mul, int accumulate,
+               void* g_hi, void* g_lo, void* stream);
+/* total variation (network.py:621-641) on NCHW fp32; ws >= 2048 floats */
+int st_tv_fwd(const float* x, int N, int C, int H, int W, float factor, float* loss, float* ws, void* stream);
+int st_tv_bwd(const float* x, int N, int C, int H, int W, float factor, const float* gw, float* g, void* stream);
+/* temporal loss (network.py:885-903) on NCHW fp32: out3 = {loss, ||cs-os||, ||cc-oc||}; ws >= 2048 floats */
+int st_temporal_fwd(const float* old_content, const float* old_stylized, const float* cur_content,
+                    const float* cur_stylized, size_t numel, float tw, float* out3, float* ws, void* stream);
+int st_temporal_bwd(const float* old_stylized, const float* cur_stylized, size_t numel, float tw,
+                    const float* stats3, const float* gw, float* g, void* stream);
+
+/* ---- InstanceNorm2d(affine) (network.py:474, :483, :531-600) ------------- */
+size_t st_instnorm_workspace_bytes(int N, int C);
+/* y = gamma*(x-mean)*rstd+beta, optional fused ReLU, optional x2 nearest upsample on write
+ * (the nn.Upsample that follows, network.py:580, :592); mean/rstd [N][C] are saved for backward */
+int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
+                    void* y_hi, void* y_lo, float* mean, float* rstd,
+                    int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
+int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
+                    const float* mean, const float* rstd, const float* gamma, const float* beta,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta,
+                    int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,203 @@
+// extern "C" entry points of libstransfer_b200.so (see include/stransfer_b200.h).
+#include "common.cuh"
+#include "../../include/stransfer_b200.h"
+#include <stdarg.h>
+#include <stdio.h>
+
+static thread_local char g_err[512] = "";
+void st_set_error(const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+static int g_conv_path = 0;
+
+// internal kernels (other translation units)
+bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
+int conv_tc_run(const bf16*, const bf16*, int, int, int, int, const bf16*, const bf16*, int, int, int, int,
+                const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, cudaStream_t);
+int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int,
+                 int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*,
+                 bf16*, bf16*, bf16*, bf16*, float*, int, cudaStream_t);
+size_t contract_workspace_bytes(int N, int Ho, int Wo, int Cdy, int Ktot, int groups);
+int contract_run(const bf16*, const bf16*, int, const bf16*, const bf16*, int, int, int, int, int, int, int, int, int, int,
+                 int, int, int, float, float*, void*, size_t, cudaStream_t);
+int ew_nchw_to_nhwc(const float*, const float*, bf16*, bf16*, int, int, int, int, int, int, cudaStream_t);
+int ew_nhwc_to_nchw(const bf16*, const bf16*, float*, int, int, int, int, int, cudaStream_t);
+int ew_pack_weight(const float*, bf16*, bf16*, int, int, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_fwd(const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_bwd(const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
+int ew_mse_fwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, int, float*, float*, cudaStream_t);
+int ew_mse_bwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, float, const float*, const float*, int, bf16*, bf16*, cudaStream_t);
+int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, cudaStream_t);
+int ew_style_seed(const float*, int, int, float, const float*, bf16*, bf16*, cudaStream_t);
+int ew_channel_sum(const bf16*, const bf16*, int, int, int, float*, float*, cudaStream_t);
+size_t in_workspace_floats(int N, int C);
+int in_forward(const bf16*, const bf16*, const float*, const float*, float, bf16*, bf16*, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
+int in_backward(const bf16*, const bf16*, const bf16*, const bf16*, const float*, const float*, const float*, const float*,
+                bf16*, bf16*, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
+int tv_forward(const float*, size_t, int, int, float, float*, float*, cudaStream_t);
+int tv_backward(const float*, size_t, int, int, float, const float*, float*, cudaStream_t);
+int temporal_forward(const float*, const float*, const float*, const float*, size_t, float, float*, float*, cudaStream_t);
+int temporal_backward(const float*, const float*, size_t, float, const float*, const float*, float*, cudaStream_t);
+
+#define BF(p) static_cast<bf16*>(p)
+#define CBF(p) static_cast<const bf16*>(p)
+#define STRM(s) static_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int st_arch(void) { return 100; }
+const char* st_last_error(void) { return g_err; }
+int st_set_conv_path(int path) { g_conv_path = path; return ST_OK; }
+
+int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int N, int C1, int C2, int H, int W, int Cpad, void* stream) {
+    ST_CHECK_ARG(a && hi && N > 0 && H > 0 && W > 0, "st_nchw_to_nhwc: null pointer or empty shape");
+    ST_CHECK_ARG(Cpad % 8 == 0 && C1 + C2 <= Cpad && (C2 == 0 || b), "st_nchw_to_nhwc: Cpad must be a multiple of 8 and >= C1+C2");
+    return ew_nchw_to_nhwc(a, b, BF(hi), BF(lo), N, C1, C2, H, W, Cpad, STRM(stream));
+}
+int st_nhwc_to_nchw(const void* hi, const void* lo, float* out, int N, int C, int H, int W, int Cpad, void* stream) {
+    ST_CHECK_ARG(hi && out && N > 0 && H > 0 && W > 0, "st_nhwc_to_nchw: null pointer or empty shape");
+    ST_CHECK_ARG(Cpad % 8 == 0 && C <= Cpad, "st_nhwc_to_nchw: Cpad must be a multiple of 8 and >= C");
+    return ew_nhwc_to_nchw(CBF(hi), CBF(lo), out, N, C, H, W, Cpad, STRM(stream));
+}
+int st_pack_conv_weight(const float* w, void* hi, void* lo, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, void* stream) {
+    ST_CHECK_ARG(w && hi, "st_pack_conv_weight: null pointer");
+    ST_CHECK_ARG(mode >= 0 && mode <= 2 && cols_pad % 8 == 0, "st_pack_conv_weight: bad mode or cols_pad %% 8 != 0");
+    const int rows = mode == 0 ? Cout : Cin, cols = mode == 0 ? Cin : Cout;
+    ST_CHECK_ARG(rows_pad >= rows && cols_pad >= cols, "st_pack_conv_weight: padded sizes smaller than the weight");
+    return ew_pack_weight(w, BF(hi), BF(lo), Cout, Cin, ks, rows_pad, cols_pad, mode, STRM(stream));
+}
+
+int st_conv2d(const void* x_hi, const void* x_lo, int N, int H, int W, int Cin, int up,
+              const void* w_hi, const void* w_lo, int w_rows_total, int w_img_rows,
+              int ks, int stride, int pad, int transposed, int Ho, int Wo, int Cout_pad, int Cbias,
+              const float* bias, const void* mask, const void* add_hi, const void* add_lo,
+              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, float* out_nchw, int Cnchw, void* stream) {
+    ST_CHECK_ARG(x_hi && w_hi, "st_conv2d: null input or weight");
+    ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0, "st_conv2d: empty shape");
+    ST_CHECK_ARG(Cin % 8 == 0 && Cout_pad % 8 == 0, "st_conv2d: channel counts must be multiples of 8 (got %d, %d)", Cin, Cout_pad);
+    ST_CHECK_ARG(ks >= 1 && ks <= 11 && (ks & 1) && stride >= 1, "st_conv2d: unsupported kernel size/stride");
+    ST_CHECK_ARG(out_hi || relu_hi || out_nchw, "st_conv2d: no output requested");
+    ST_CHECK_ARG(!(add_lo && !add_hi), "st_conv2d: add_lo without add_hi");
+    const bool tc = g_conv_path == 0 && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && !out_nchw &&
+                    w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad);
+    if (tc)
+        return conv_tc_run(CBF(x_hi), CBF(x_lo), N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_rows_total, w_img_rows, ks, Cout_pad,
+                           bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), STRM(stream));
+    if (w_img_rows != 0) {
+        // per-image weights on the generic path: one launch per image
+        for (int n = 0; n < N; ++n) {
+            const size_t xin = static_cast<size_t>(n) * H * W * Cin, xo = static_cast<size_t>(n) * Ho * Wo * Cout_pad;
+            const size_t wo = static_cast<size_t>(n) * w_img_rows * ks * ks * Cin;
+            int rc = conv_gen_run(CBF(x_hi) + xin, x_lo ? CBF(x_lo) + xin : nullptr, 1, H, W, Cin, up,
+                                  CBF(w_hi) + wo, w_lo ? CBF(w_lo) + wo : nullptr, ks, stride, pad, transposed, Ho, Wo, Cout_pad, Cout_pad, Cbias,
+                                  bias, mask ? CBF(mask) + xo : nullptr, add_hi ? CBF(add_hi) + xo : nullptr, add_lo ? CBF(add_lo) + xo : nullptr,
+                                  out_hi ? BF(out_hi) + xo : nullptr, out_lo ? BF(out_lo) + xo : nullptr,
+                                  relu_hi ? BF(relu_hi) + xo : nullptr, relu_lo ? BF(relu_lo) + xo : nullptr,
+                                  out_nchw ? out_nchw + static_cast<size_t>(n) * Cnchw * Ho * Wo : nullptr, Cnchw, STRM(stream));
+            if (rc) return rc;
+        }
+        return ST_OK;
+    }
+    return conv_gen_run(CBF(x_hi), CBF(x_lo), N, H, W, Cin, up, CBF(w_hi), CBF(w_lo), ks, stride, pad, transposed,
+                        Ho, Wo, Cout_pad, Cout_pad, Cbias, bias, CBF(mask), CBF(add_hi), CBF(add_lo),
+                        BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_nchw, Cnchw, STRM(stream));
+}
+
+size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {
+    size_t a = contract_workspace_bytes(N, Ho, Wo, Cdy, ks * ks * CinPad, 1);
+    size_t b = static_cast<size_t>(1024) * Cdy * sizeof(float);
+    return a > b ? a : b;
+}
+int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy, const void* x_hi, const void* x_lo,
+                    int N, int H, int W, int CinPad, int up, int Ho, int Wo, int ks, int stride, int pad,
+                    int Cout, int Cin, float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream) {
+    ST_CHECK_ARG(dy_hi && x_hi && dw && workspace, "st_conv2d_wgrad: null pointer");
+    ST_CHECK_ARG(Cdy % 8 == 0 && CinPad % 8 == 0 && Cout <= Cdy && Cin <= CinPad, "st_conv2d_wgrad: bad channel counts");
+    ST_CHECK_ARG(workspace_bytes >= st_conv2d_wgrad_workspace_bytes(N, Ho, Wo, Cdy, CinPad, ks), "st_conv2d_wgrad: workspace too small");
+    int rc = contract_run(CBF(dy_hi), CBF(dy_lo), Cdy, CBF(x_hi), CBF(x_lo), N, H, W, CinPad, up, Ho, Wo, ks, stride, pad,
+                          0, Cout, Cin, 1.f, dw, workspace, workspace_bytes, STRM(stream));
+    if (rc) return rc;
+    if (db) {
+        ST_CHECK_ARG(Cdy <= 256, "st_conv2d_wgrad: bias gradient supports up to 256 channels");
+        rc = ew_channel_sum(CBF(dy_hi), CBF(dy_lo), N * Ho * Wo, Cdy, Cout, db, static_cast<float*>(workspace), STRM(stream));
+    }
+    return rc;
+}
+
+int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, int N, int H, int W, int C, void* stream) {
+    ST_CHECK_ARG(x_hi && y_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_fwd: null pointer or C %% 8 != 0");
+    return ew_relu_maxpool_fwd(CBF(x_hi), CBF(x_lo), BF(y_hi), BF(y_lo), N, H, W, C, STRM(stream));
+}
+int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
+                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int N, int H, int W, int C, void* stream) {
+    ST_CHECK_ARG(x_hi && gy_hi && gx_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_bwd: null pointer or C %% 8 != 0");
+    return ew_relu_maxpool_bwd(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), N, H, W, C, STRM(stream));
+}
+
+size_t st_gram_workspace_bytes(int B, int HW, int C) { return contract_workspace_bytes(B, HW, 1, C, C, B); }
+int st_gram_fwd(const void* f_hi, const void* f_lo, int B, int HW, int C, float* G, void* workspace, size_t workspace_bytes, void* stream) {
+    ST_CHECK_ARG(f_hi && G && workspace && B > 0 && HW > 0, "st_gram_fwd: null pointer or empty shape");
+    ST_CHECK_ARG(C % 8 == 0, "st_gram_fwd: C %% 8 != 0");
+    const float scale = 1.0f / (static_cast<float>(C) * static_cast<float>(HW));
+    return contract_run(CBF(f_hi), CBF(f_lo), C, CBF(f_hi), CBF(f_lo), B, HW, 1, C, 0, HW, 1, 1, 1, 0,
+                        1, C, C, scale, G, workspace, workspace_bytes, STRM(stream));
+}
+int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* ws, void* stream) {
+    ST_CHECK_ARG(G && T && diff && loss && ws, "st_style_mse_fwd: null pointer");
+    return ew_style_fwd(G, T, B, C, diff, loss, ws, STRM(stream));
+}
+int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* gw, void* d_hi, void* d_lo, void* stream) {
+    ST_CHECK_ARG(diff && gw && d_hi, "st_style_mse_bwd_seed: null pointer");
+    // d/dF of mean_{b,i,j}(G-T)^2 with G = F^T F/(C*HW): 4/(B*C^2) * 1/(C*HW) * F (G-T)   
+    const double scale = 4.0 / (static_cast<double>(B) * C * C) / (static_cast<double>(C) * HW);
+    return ew_style_seed(diff, B, C, static_cast<float>(scale), gw, BF(d_hi), BF(d_lo), STRM(stream));
+}
+int st_mse_fwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel, int relu, int feature_form,
+               float* loss, float* ws, void* stream) {
+    ST_CHECK_ARG(x_hi && t_hi && loss && ws && numel % 8 == 0 && numel > 0, "st_mse_fwd: null pointer or numel %% 8 != 0");
+    return ew_mse_fwd(CBF(x_hi), CBF(x_lo), CBF(t_hi), CBF(t_lo), numel, relu, feature_form, loss, ws, STRM(stream));
+}
+int st_mse_bwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel, int relu, float scale,
+               const float* gw, const float* mul, int accumulate, void* g_hi, void* g_lo, void* stream) {
+    ST_CHECK_ARG(x_hi && t_hi && gw && g_hi && numel % 8 == 0 && numel > 0, "st_mse_bwd: null pointer or numel %% 8 != 0");
+    return ew_mse_bwd(CBF(x_hi), CBF(x_lo), CBF(t_hi), CBF(t_lo), numel, relu, scale, gw, mul, accumulate, BF(g_hi), BF(g_lo), STRM(stream));
+}
+int st_tv_fwd(const float* x, int N, int C, int H, int W, float factor, float* loss, float* ws, void* stream) {
+    ST_CHECK_ARG(x && loss && ws && N > 0 && C > 0 && H > 0 && W > 0, "st_tv_fwd: null pointer or empty shape");
+    return tv_forward(x, static_cast<size_t>(N) * C * H * W, H, W, factor, loss, ws, STRM(stream));
+}
+int st_tv_bwd(const float* x, int N, int C, int H, int W, float factor, const float* gw, float* g, void* stream) {
+    ST_CHECK_ARG(x && gw && g && N > 0 && C > 0 && H > 0 && W > 0, "st_tv_bwd: null pointer or empty shape");
+    return tv_backward(x, static_cast<size_t>(N) * C * H * W, H, W, factor, gw, g, STRM(stream));
+}
+int st_temporal_fwd(const float* oc, const float* os, const float* cc, const float* cs, size_t numel, float tw,
+                    float* out3, float* ws, void* stream) {
+    ST_CHECK_ARG(oc && os && cc && cs && out3 && ws && numel > 0, "st_temporal_fwd: null pointer or empty shape");
+    return temporal_forward(oc, os, cc, cs, numel, tw, out3, ws, STRM(stream));
+}
+int st_temporal_bwd(const float* os, const float* cs, size_t numel, float tw, const float* stats3, const float* gw, float* g, void* stream) {
+    ST_CHECK_ARG(os && cs && stats3 && gw && g && numel > 0, "st_temporal_bwd: null pointer or empty shape");
+    return temporal_backward(os, cs, numel, tw, stats3, gw, g, STRM(stream));
+}
+
+size_t st_instnorm_workspace_bytes(int N, int C) { return (in_workspace_floats(N, C) + 2 * static_cast<size_t>(N) * C) * sizeof(float); }
+static bool in_channels_ok(int C) { return C >= 8 && C <= 256 && (C & (C - 1)) == 0; }
+int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
+                    void* y_hi, void* y_lo, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
+                    void* workspace, void* stream) {
+    ST_CHECK_ARG(x_hi && gamma && beta && y_hi && mean && rstd && workspace, "st_instnorm_fwd: null pointer");
+    ST_CHECK_ARG(in_channels_ok(C), "st_instnorm_fwd: C must be a power of two in [8,256] (got %d)", C);
+    return in_forward(CBF(x_hi), CBF(x_lo), gamma, beta, eps, BF(y_hi), BF(y_lo), mean, rstd, N, H, W, C, relu, up,
+                      static_cast<float*>(workspace), STRM(stream));
+}
+int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
+                    const float* mean, const float* rstd, const float* gamma, const float* beta,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int up,
+                    void* workspace, void* stream) {
+    ST_CHECK_ARG(x_hi && gy_hi && mean && rstd && gamma && beta && dx_hi && dgamma && dbeta && workspace, "st_instnorm_bwd: null pointer");
+    ST_CHECK_ARG(in_channels_ok(C), "st_instnorm_bwd: C must be a power of two in [8,256] (got %d)", C);
+    return in_backward(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), mean, rstd, gamma, beta, BF(dx_hi), BF(dx_lo),
+                       dgamma, dbeta, N, H, W, C, relu, up, static_cast<float*>(workspace), STRM(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,98 @@
+// Shared device helpers for the stransfer sm_100a kernels.
+//
+// Data format used by every kernel ("split-bf16 NHWC"): an activation tensor is
+// stored channels-last as TWO bf16 planes, hi = bf16(x) and lo = bf16(x - hi).
+// hi + lo carries ~16 mantissa bits, and a product a*b is evaluated on the bf16
+// tensor cores as a_hi*b_hi + a_lo*b_hi + a_hi*b_lo with fp32 accumulation
+// (the "bf16x3" scheme).  A NULL lo plane means plain bf16 (one MMA per
+// product).  Why: DESIGN.md section "Precision" (single-pass bf16 gives a 3e-2 error
+// on the Gatys input gradient; the north-star tolerance is 1e-3).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda.h>
+#include <stdint.h>
+
+typedef __nv_bfloat16 bf16;
+
+// ----- error plumbing (host) -------------------------------------------------
+void st_set_error(const char* fmt, ...);
+#define ST_OK 0
+#define ST_ERR_INVALID (-1)
+#define ST_ERR_CUDA (-2)
+#define ST_ERR_UNSUPPORTED (-3)
+#define ST_CHECK_ARG(cond, ...)                                   \
+    do { if (!(cond)) { st_set_error(__VA_ARGS__); return ST_ERR_INVALID; } } while (0)
+#define ST_CHECK_LAUNCH(name)                                                       \
+    do { cudaError_t e_ = cudaGetLastError();                                       \
+         if (e_ != cudaSuccess) { st_set_error("%s: %s", name, cudaGetErrorString(e_)); \
+                                  return ST_ERR_CUDA; } } while (0)
+
+// ----- split-bf16 -------------------------------------------------------------
+__device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
+    hi = __float2bfloat16_rn(v);
+    lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+__device__ __forceinline__ float join_bf16(bf16 hi, bf16 lo) {
+    return __bfloat162float(hi) + __bfloat162float(lo);
+}
+// pack two floats into a bf16x2 word (a = low half)
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ float bf16lo_to_f(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16hi_to_f(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+// split 2 floats -> (hi word, lo word)
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = pack_bf16x2(a, b);
+    lo = pack_bf16x2(a - bf16lo_to_f(hi), b - bf16hi_to_f(hi));
+}
+
+// 8 channels (one 16-byte vector per plane) <-> 8 floats
+__device__ __forceinline__ void load8(const bf16* hi, const bf16* lo, size_t off, float (&v)[8]) {
+    uint4 h = *reinterpret_cast<const uint4*>(hi + off);
+    uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { v[2 * i] = bf16lo_to_f(hw[i]); v[2 * i + 1] = bf16hi_to_f(hw[i]); }
+    if (lo) {
+        uint4 l = *reinterpret_cast<const uint4*>(lo + off);
+        uint32_t lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { v[2 * i] += bf16lo_to_f(lw[i]); v[2 * i + 1] += bf16hi_to_f(lw[i]); }
+    }
+}
+__device__ __forceinline__ void store8(bf16* hi, bf16* lo, size_t off, const float (&v)[8]) {
+    uint32_t hw[4], lw[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) split2(v[2 * i], v[2 * i + 1], hw[i], lw[i]);
+    *reinterpret_cast<uint4*>(hi + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+    if (lo) *reinterpret_cast<uint4*>(lo + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+}
+
+// ----- reductions ---------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// block-wide sum; result valid in thread 0.  `sm` must hold >= 32 floats.
+__device__ __forceinline__ float block_sum(float v, float* sm) {
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        v = lane < nw ? sm[lane] : 0.f;
+        v = warp_sum(v);
+    }
+    return v;
+}
+
+static inline int st_num_sms() {
+    static int n = 0;
+    if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+    return n;
+}

@@ -1,0 +1,359 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution for sm_100a (stride 1, 3x3 pad 1
+// or 1x1), NHWC split-bf16 activations.  This one kernel serves
+//   * conv forward of the VGG prefix and of the transform net's 3x3 layers
+//     (reference: nn.Conv2d call sites network.py:246-275, :468-481, :582-599),
+//   * their backward-data (dgrad = the same conv with flipped/transposed weights,
+//     ReLU mask and the loss gradient of the tap fused into the epilogue),
+//   * the Gram backward dF = F * D (a 1x1 conv with per-image weights D,
+//     reference: autograd of network.py:92-123).
+//
+// GEMM view: M = 128 output pixels (an 8 x 16 patch), N = BN output channels,
+// K = taps * Cin.  A single TMA box load of a (8+2) x 16 pixel x 64 channel halo
+// patch per horizontal tap s feeds the three vertical taps r: tap r starts
+// r*16 rows = r*2048 bytes into the box, which keeps the 1024-byte alignment the
+// 128B swizzle needs.  Zero padding comes from TMA out-of-bounds fill.
+//
+// Warp roles (192 threads, persistent, one CTA per SM):
+//   warp 0  TMA producer      warp 1  tcgen05.mma issuer (+ TMEM alloc)
+//   warps 2-5  epilogue: tcgen05.ld -> bias / mask / add -> split-bf16 stores
+// Pipelines: A ring (halo boxes), B ring (weight tiles), 2 TMEM accumulators.
+#include "common.cuh"
+#include "ptx.cuh"
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <string.h>
+
+namespace {
+
+constexpr int TILE_H = 8, TILE_W = 16, BLOCK_M = 128, KCH = 64;
+constexpr int NUM_THREADS = 192;
+
+struct ConvTcParams {
+    int N, H, W, Cin, Cout;
+    int tiles_h, tiles_w, n_blocks, work;
+    int w_img_rows;                 // weight-row offset per image (0: shared weights)
+    int has_a_lo, has_w_lo;
+    const float* bias;              // [Cout] or null
+    const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
+    const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
+    const bf16* add_lo;
+    bf16* out_hi; bf16* out_lo;     // result (pre-activation)
+    bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
+};
+
+template <int KS, int BN> struct Cfg {
+    static constexpr int A_ROWS = (TILE_H + KS - 1) * TILE_W;
+    static constexpr int A_PLANE = A_ROWS * 128;            // bytes (64 bf16 per row)
+    static constexpr int B_PLANE = BN * 128;
+    static constexpr int NA = 2;
+    static constexpr int NB = (BN == 128) ? 4 : 6;
+    static constexpr int A_BYTES = NA * 2 * A_PLANE;
+    static constexpr int B_BYTES = NB * 2 * B_PLANE;
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int SMEM = 1024 + A_BYTES + B_BYTES + BAR_BYTES;   // 1024 slack for alignment
+    static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : 256;
+};
+
+template <int KS, int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
+               const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
+               const ConvTcParams p) {
+    using C = Cfg<KS, BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + C::A_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::A_BYTES + C::B_BYTES);
+    uint64_t* a_full = bars;                 // [NA]
+    uint64_t* a_empty = a_full + C::NA;      // [NA]
+    uint64_t* b_full = a_empty + C::NA;      // [NB]
+    uint64_t* b_empty = b_full + C::NB;      // [NB]
+    uint64_t* t_full = b_empty + C::NB;      // [2]
+    uint64_t* t_empty = t_full + 2;          // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int pad = KS / 2;
+    const int kchunks = p.Cin / KCH;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmW_hi);
+        if (p.has_a_lo) ptx::prefetch_tmap(&tmA_lo);
+        if (p.has_w_lo) ptx::prefetch_tmap(&tmW_lo);
+        for (int i = 0; i < C::NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
+        for (int i = 0; i < C::NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], 4); }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int a = 0, b = 0; uint32_t aph = 0, bph = 0;
+            const uint32_t a_tx = (p.has_a_lo ? 2 : 1) * C::A_PLANE;
+            const uint32_t b_tx = (p.has_w_lo ? 2 : 1) * C::B_PLANE;
+            for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x) {
+                const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
+                const int tw = t % p.tiles_w; t /= p.tiles_w;
+                const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+                const int h0 = th * TILE_H, w0 = tw * TILE_W;
+                const int wrow = n * p.w_img_rows + nb * BN;
+                for (int c = 0; c < kchunks; ++c) {
+                    for (int s = 0; s < KS; ++s) {
+                        ptx::mbar_wait(&a_empty[a], aph ^ 1);
+                        ptx::mbar_expect_tx(&a_full[a], a_tx);
+                        uint8_t* dst = sA + a * 2 * C::A_PLANE;
+                        ptx::tma_load_4d(dst, &tmA_hi, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
+                        if (p.has_a_lo) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
+                        if (++a == C::NA) { a = 0; aph ^= 1; }
+                        for (int r = 0; r < KS; ++r) {
+                            ptx::mbar_wait(&b_empty[b], bph ^ 1);
+                            ptx::mbar_expect_tx(&b_full[b], b_tx);
+                            uint8_t* bd = sB + b * 2 * C::B_PLANE;
+                            ptx::tma_load_3d(bd, &tmW_hi, &b_full[b], c * KCH, r * KS + s, wrow);
+                            if (p.has_w_lo) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
+                            if (++b == C::NB) { b = 0; bph ^= 1; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_M, BN);
+            int a = 0, b = 0; uint32_t aph = 0, bph = 0;
+            int it = 0;
+            for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
+                const int acc = it & 1;
+                ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                uint32_t accumulate = 0;
+                for (int c = 0; c < kchunks; ++c) {
+                    for (int s = 0; s < KS; ++s) {
+                        ptx::mbar_wait(&a_full[a], aph);
+                        ptx::tc_fence_after();
+                        const uint32_t a_base = ptx::smem_u32(sA + a * 2 * C::A_PLANE);
+                        for (int r = 0; r < KS; ++r) {
+                            ptx::mbar_wait(&b_full[b], bph);
+                            ptx::tc_fence_after();
+                            const uint32_t b_base = ptx::smem_u32(sB + b * 2 * C::B_PLANE);
+                            const uint32_t a_tap = a_base + r * TILE_W * 128;
+#pragma unroll
+                            for (int k = 0; k < KCH / 16; ++k) {
+                                const uint64_t ah = ptx::umma_desc_k_sw128(a_tap + k * 32);
+                                const uint64_t bh = ptx::umma_desc_k_sw128(b_base + k * 32);
+                                ptx::mma_bf16_ss(d_tmem, ah, bh, idesc, accumulate);
+                                accumulate = 1;
+                                if (p.has_a_lo)
+                                    ptx::mma_bf16_ss(d_tmem, ptx::umma_desc_k_sw128(a_tap + C::A_PLANE + k * 32), bh, idesc, 1);
+                                if (p.has_w_lo)
+                                    ptx::mma_bf16_ss(d_tmem, ah, ptx::umma_desc_k_sw128(b_base + C::B_PLANE + k * 32), idesc, 1);
+                            }
+                            ptx::tc_commit(&b_empty[b]);
+                            if (++b == C::NB) { b = 0; bph ^= 1; }
+                        }
+                        ptx::tc_commit(&a_empty[a]);
+                        if (++a == C::NA) { a = 0; aph ^= 1; }
+                    }
+                }
+                ptx::tc_commit(&t_full[acc]);
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5) =====================
+        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        const int m = q * 32 + lane;                  // accumulator row = pixel within the patch
+        int it = 0;
+        for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
+            const int acc = it & 1;
+            const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
+            const int tw = t % p.tiles_w; t /= p.tiles_w;
+            const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+            const int h = th * TILE_H + m / TILE_W, w = tw * TILE_W + m % TILE_W;
+            const bool valid = (h < p.H) && (w < p.W);
+            const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
+            ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
+            ptx::tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int j = 0; j < BN / 16; ++j) {
+                uint32_t r[16];
+                ptx::tmem_ld16(taddr + j * 16, r);
+                ptx::tmem_ld_wait();
+                if (valid) {
+                    const int ch = nb * BN + j * 16;
+                    const size_t off = pix * p.Cout + ch;
+#pragma unroll
+                    for (int half = 0; half < 2; ++half) {
+                        float v[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[half * 8 + i]);
+                        const size_t o = off + half * 8;
+                        if (p.bias) {
+                            const float4 b0 = *reinterpret_cast<const float4*>(p.bias + ch + half * 8);
+                            const float4 b1 = *reinterpret_cast<const float4*>(p.bias + ch + half * 8 + 4);
+                            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+                            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+                        }
+                        if (p.mask) {
+                            float mk[8];
+                            load8(p.mask, nullptr, o, mk);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] = mk[i] > 0.f ? v[i] : 0.f;
+                        }
+                        if (p.add_hi) {
+                            float ad[8];
+                            load8(p.add_hi, p.add_lo, o, ad);
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] += ad[i];
+                        }
+                        if (p.out_hi) store8(p.out_hi, p.out_lo, o, v);
+                        if (p.relu_hi) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+                            store8(p.relu_hi, p.relu_lo, o, v);
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------
+// host: tensor maps
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+struct MapKey {
+    const void* ptr; uint64_t d[4]; uint32_t box[4]; int rank;
+    bool operator==(const MapKey& o) const { return memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+    size_t operator()(const MapKey& k) const {
+        const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+        size_t h = 1469598103934665603ull;
+        for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ w[i]) * 1099511628211ull;
+        return h;
+    }
+};
+std::mutex g_map_mu;
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+
+// bf16 tensor, dims innermost first, contiguous; 128B swizzle, zero OOB fill.
+int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box) {
+    MapKey key; memset(&key, 0, sizeof(key));
+    key.ptr = ptr; key.rank = rank;
+    for (int i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.box[i] = box[i]; }
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    auto itf = g_maps.find(key);
+    if (itf != g_maps.end()) { *out = itf->second; return ST_OK; }
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { st_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)"); return ST_ERR_CUDA; }
+    cuuint64_t gd[4], gs[3]; cuuint32_t bx[4], es[4];
+    uint64_t stride = 2;
+    for (int i = 0; i < rank; ++i) {
+        gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1;
+        stride *= dims[i];
+        if (i < rank - 1) gs[i] = stride;
+    }
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gd, gs, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { st_set_error("cuTensorMapEncodeTiled failed: %d", (int)r); return ST_ERR_CUDA; }
+    if (g_maps.size() > 8192) g_maps.clear();
+    g_maps.emplace(key, *out);
+    return ST_OK;
+}
+
+template <int KS, int BN>
+int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
+           const ConvTcParams& p, cudaStream_t stream) {
+    using C = Cfg<KS, BN>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { st_set_error("conv_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
+        attr_set = true;
+    }
+    int grid = p.work < st_num_sms() ? p.work : st_num_sms();
+    conv_tc_kernel<KS, BN><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
+    ST_CHECK_LAUNCH("conv_tc_kernel");
+    return ST_OK;
+}
+
+}  // namespace
+
+// Eligibility of the tcgen05 path (the generic kernel covers everything else).
+bool conv_tc_eligible(int ks, int stride, int Cin, int Cout) {
+    return (ks == 3 || ks == 1) && stride == 1 && Cin % 64 == 0 && (Cout % 128 == 0 || Cout == 64 || Cout == 32);
+}
+
+int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int N, int H, int W, int Cin,
+                const bf16* w_hi, const bf16* w_lo, int w_rows_total, int w_img_rows, int ks, int Cout,
+                const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
+                bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, cudaStream_t stream) {
+    const int BN = (Cout % 128 == 0) ? 128 : Cout;
+    const int taps = ks * ks;
+    ConvTcParams p;
+    p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
+    p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
+    p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
+    p.w_img_rows = w_img_rows; p.has_a_lo = x_lo != nullptr; p.has_w_lo = w_lo != nullptr;
+    p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
+    p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
+
+    CUtensorMap ah, al, wh, wl;
+    uint64_t ad[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint32_t ab[4] = {KCH, TILE_W, (uint32_t)(TILE_H + ks - 1), 1};
+    uint64_t wd[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total};
+    uint32_t wb[3] = {KCH, 1, (uint32_t)BN};
+    int rc;
+    if ((rc = make_map(&ah, x_hi, 4, ad, ab))) return rc;
+    if ((rc = make_map(&wh, w_hi, 3, wd, wb))) return rc;
+    al = ah; wl = wh;
+    if (x_lo && (rc = make_map(&al, x_lo, 4, ad, ab))) return rc;
+    if (w_lo && (rc = make_map(&wl, w_lo, 3, wd, wb))) return rc;
+
+    if (ks == 3) {
+        if (BN == 128) return launch<3, 128>(ah, al, wh, wl, p, stream);
+        if (BN == 64) return launch<3, 64>(ah, al, wh, wl, p, stream);
+        if (BN == 32) return launch<3, 32>(ah, al, wh, wl, p, stream);
+    } else {
+        if (BN == 128) return launch<1, 128>(ah, al, wh, wl, p, stream);
+        if (BN == 64) return launch<1, 64>(ah, al, wh, wl, p, stream);
+        if (BN == 32) return launch<1, 32>(ah, al, wh, wl, p, stream);
+    }
+    st_set_error("conv_tc: unsupported tile configuration ks=%d BN=%d", ks, BN);
+    return ST_ERR_UNSUPPORTED;
+}

@@ -1,0 +1,330 @@
+// Bandwidth kernels of the VGG loss network: layout conversion, weight packing,
+// fused ReLU+maxpool forward/backward, MSE losses and their gradients, the style
+// (Gram) MSE and its gradient seed.  All are coalesced 128-bit accesses over the
+// split-bf16 NHWC format; reductions are two-stage and deterministic.
+// Reference call sites: nn.ReLU/nn.MaxPool2d inside the VGG pieces
+// (network.py:257-314), F.mse_loss (network.py:118, :163, :193).
+#include "common.cuh"
+
+namespace {
+
+// ---------------------------------------------------------------------------
+// NCHW fp32 (one or two sources, channel-concatenated: network.py:984-986) ->
+// NHWC split-bf16 with the channel count padded to Cpad (zeros).
+// One thread per pixel; reads are coalesced along W per channel plane.
+// ---------------------------------------------------------------------------
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                    bf16* __restrict__ hi, bf16* __restrict__ lo,
+                                    int N, int C1, int C2, int HW, int Cpad) {
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * HW) return;
+    const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
+    for (int c0 = 0; c0 < Cpad; c0 += 8) {
+        float v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = c0 + i;
+            float x = 0.f;
+            if (c < C1) x = a[(static_cast<size_t>(n) * C1 + c) * HW + px];
+            else if (c < C1 + C2) x = b[(static_cast<size_t>(n) * C2 + (c - C1)) * HW + px];
+            v[i] = x;
+        }
+        store8(hi, lo, idx * Cpad + c0, v);
+    }
+}
+
+// NHWC split-bf16 (Cpad channels stored) -> NCHW fp32 (first C channels)
+__global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __restrict__ lo,
+                                    float* __restrict__ out, int N, int C, int HW, int Cpad) {
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * HW) return;
+    const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
+    for (int c0 = 0; c0 < C; c0 += 8) {
+        float v[8];
+        load8(hi, lo, idx * Cpad + c0, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (c0 + i < C) out[(static_cast<size_t>(n) * C + c0 + i) * HW + px] = v[i];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Weight packing: PyTorch [Cout][Cin][ks][ks] fp32 -> [rows_pad][taps][cols_pad]
+// split-bf16, K-major.   mode 0: rows=co, cols=ci, tap=(r,s)          (forward)
+//                        mode 1: rows=ci, cols=co, tap=(r,s)          (dgrad, gather form)
+//                        mode 2: rows=ci, cols=co, tap=(ks-1-r,ks-1-s) (dgrad as a forward conv)
+// ---------------------------------------------------------------------------
+__global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict__ hi, bf16* __restrict__ lo,
+                                   int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode) {
+    const int taps = ks * ks;
+    const int total = rows_pad * taps * cols_pad;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    int q = idx; const int col = q % cols_pad; q /= cols_pad; const int tap = q % taps; const int row = q / taps;
+    int r = tap / ks, s = tap % ks;
+    int co, ci;
+    if (mode == 0) { co = row; ci = col; } else { ci = row; co = col; }
+    if (mode == 2) { r = ks - 1 - r; s = ks - 1 - s; }
+    float v = 0.f;
+    if (co < Cout && ci < Cin) v = w[((static_cast<size_t>(co) * Cin + ci) * ks + r) * ks + s];
+    bf16 h, l; split_bf16(v, h, l);
+    hi[idx] = h;
+    if (lo) lo[idx] = l;
+}
+
+// ---------------------------------------------------------------------------
+// ReLU + MaxPool2d(2,2) forward (VGG pieces 2 and 5): y = max over the window of relu(x)
+// ---------------------------------------------------------------------------
+__global__ void relu_maxpool_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                        bf16* __restrict__ yh, bf16* __restrict__ yl,
+                                        int N, int H, int W, int C) {
+    const int Ho = H / 2, Wo = W / 2, Cv = C / 8;
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
+    size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wo; q /= Wo; const int oh = q % Ho; const int n = q / Ho;
+    float m[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m[i] = 0.f;                 // relu folded into the max
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        const size_t off = ((static_cast<size_t>(n) * H + oh * 2 + (d >> 1)) * W + ow * 2 + (d & 1)) * C + cv * 8;
+        float v[8]; load8(xh, xl, off, v);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], v[i]);
+    }
+    store8(yh, yl, ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8, m);
+}
+
+// Backward of the above, fused with the loss gradient of the tap:
+//   g_x = (x is the first maximum of relu(x) in its window and x > 0) ? g_y : 0   (+ add)
+// One thread per (window, 8 channels); windows are enumerated over ceil(H/2) x ceil(W/2)
+// so that odd borders (which max_pool2d drops) still receive `add`.
+__global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                        const bf16* __restrict__ gyh, const bf16* __restrict__ gyl,
+                                        const bf16* __restrict__ addh, const bf16* __restrict__ addl,
+                                        bf16* __restrict__ gxh, bf16* __restrict__ gxl,
+                                        int N, int H, int W, int C) {
+    const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, Cv = C / 8;
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
+    size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wc; q /= Wc; const int oh = q % Hc; const int n = q / Hc;
+    const bool pooled = oh < Ho && ow < Wo;
+    float x[4][8]; bool inb[4];
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        const int h = oh * 2 + (d >> 1), w = ow * 2 + (d & 1);
+        inb[d] = h < H && w < W;
+        if (inb[d]) load8(xh, xl, ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8, x[d]);
+    }
+    float g[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = 0.f;
+    if (pooled) load8(gyh, gyl, ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8, g);
+    int arg[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float best = -1.f, bx = 0.f; int a = -1;
+        if (pooled) {
+#pragma unroll
+            for (int d = 0; d < 4; ++d) { const float v = fmaxf(x[d][i], 0.f); if (v > best) { best = v; a = d; bx = x[d][i]; } }
+            if (!(bx > 0.f)) a = -1;                         // relu'(x) = 0
+        }
+        arg[i] = a;
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (!inb[d]) continue;
+        const int h = oh * 2 + (d >> 1), w = ow * 2 + (d & 1);
+        const size_t off = ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = (arg[i] == d) ? g[i] : 0.f;
+        if (addh) {
+            float a[8]; load8(addh, addl, off, a);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] += a[i];
+        }
+        store8(gxh, gxl, off, o);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// MSE forward: partial[b] = sum over this block's slice of (f(x) - f(t))^2,
+// f = identity or relu (FeatureReconstructionLoss sits on ReLU_4, network.py:230-232)
+// ---------------------------------------------------------------------------
+__global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                   const bf16* __restrict__ th, const bf16* __restrict__ tl,
+                                   size_t nvec, int relu, float* __restrict__ partial) {
+    __shared__ float sm[32];
+    float s = 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        float a[8], b[8];
+        load8(xh, xl, i * 8, a); load8(th, tl, i * 8, b);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float d = relu ? (fmaxf(a[k], 0.f) - fmaxf(b[k], 0.f)) : (a[k] - b[k]);
+            s += d * d;
+        }
+    }
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// out[0] = scale * sum(partial[0..n)) ; optionally squared first (feature loss: mse^2 / numel)
+__global__ void sum_partials_kernel(const float* __restrict__ partial, int n, float scale, int square,
+                                    float post_scale, float* __restrict__ out) {
+    __shared__ float sm[32];
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) { s *= scale; if (square) s = s * s * post_scale; out[0] = s; }
+}
+
+// MSE backward: g = coef * (f(x) - f(t)) * f'(x),  coef = scale * (*gw) * (mul ? *mul : 1)
+__global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                               const bf16* __restrict__ th, const bf16* __restrict__ tl,
+                               size_t nvec, int relu, float scale, const float* __restrict__ gw,
+                               const float* __restrict__ mul, int accumulate,
+                               bf16* __restrict__ gh, bf16* __restrict__ gl) {
+    const float coef = scale * gw[0] * (mul ? mul[0] : 1.f);
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        float a[8], b[8], o[8];
+        load8(xh, xl, i * 8, a); load8(th, tl, i * 8, b);
+        if (accumulate) load8(gh, gl, i * 8, o);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float d = relu ? ((a[k] > 0.f) ? (a[k] - fmaxf(b[k], 0.f)) * coef : 0.f) : (a[k] - b[k]) * coef;
+            o[k] = accumulate ? o[k] + d : d;
+        }
+        store8(gh, gl, i * 8, o);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Style loss on the (small) Gram matrices: diff = G - T (T broadcast over the batch),
+// partial sums of diff^2 per block.   network.py:110-123
+// ---------------------------------------------------------------------------
+__global__ void style_diff_kernel(const float* __restrict__ G, const float* __restrict__ T, int CC, int total,
+                                  float* __restrict__ diff, float* __restrict__ partial) {
+    __shared__ float sm[32];
+    float s = 0.f;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const float d = G[i] - T[i % CC];
+        diff[i] = d;
+        s += d * d;
+    }
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+
+// D = (*gw) * scale * diff, packed split-bf16 [B*C rows][C] (the per-image "weights" of the
+// 1x1 conv that evaluates dF = F * D on the tensor cores)
+__global__ void style_seed_kernel(const float* __restrict__ diff, int total, float scale, const float* __restrict__ gw,
+                                  bf16* __restrict__ dh, bf16* __restrict__ dl) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    bf16 h, l; split_bf16(diff[i] * scale * gw[0], h, l);
+    dh[i] = h;
+    if (dl) dl[i] = l;
+}
+
+// per-channel sum over pixels (conv bias gradient): partial[blk][C], then finish
+__global__ void channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                           int P, int C, int rows_per_block, float* __restrict__ partial) {
+    // blockDim.x = C (<= 256); each thread owns one channel, rows are coalesced across threads
+    const int c = threadIdx.x;
+    const int p0 = blockIdx.x * rows_per_block, p1 = min(P, p0 + rows_per_block);
+    float s = 0.f;
+    for (int p = p0; p < p1; ++p) {
+        const size_t o = static_cast<size_t>(p) * C + c;
+        float v = __bfloat162float(xh[o]);
+        if (xl) v += __bfloat162float(xl[o]);
+        s += v;
+    }
+    partial[static_cast<size_t>(blockIdx.x) * C + c] = s;
+}
+__global__ void channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, float* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= Cout) return;
+    float s = 0.f;
+    for (int b = 0; b < nblk; ++b) s += partial[static_cast<size_t>(b) * C + c];
+    out[c] = s;
+}
+
+inline int grid_for(size_t n, int block, int cap_mult = 8) {
+    size_t g = (n + block - 1) / block;
+    size_t cap = static_cast<size_t>(st_num_sms()) * cap_mult;
+    return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+int ew_nchw_to_nhwc(const float* a, const float* b, bf16* hi, bf16* lo, int N, int C1, int C2, int H, int W, int Cpad, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * H * W;
+    nchw_to_nhwc_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, hi, lo, N, C1, C2, H * W, Cpad);
+    ST_CHECK_LAUNCH("nchw_to_nhwc_kernel"); return ST_OK;
+}
+int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * H * W;
+    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad);
+    ST_CHECK_LAUNCH("nhwc_to_nchw_kernel"); return ST_OK;
+}
+int ew_pack_weight(const float* w, bf16* hi, bf16* lo, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, cudaStream_t st) {
+    const int total = rows_pad * ks * ks * cols_pad;
+    pack_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, hi, lo, Cout, Cin, ks, rows_pad, cols_pad, mode);
+    ST_CHECK_LAUNCH("pack_weight_kernel"); return ST_OK;
+}
+int ew_relu_maxpool_fwd(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, int N, int H, int W, int C, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * (H / 2) * (W / 2) * (C / 8);
+    if (n == 0) return ST_OK;
+    relu_maxpool_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, N, H, W, C);
+    ST_CHECK_LAUNCH("relu_maxpool_fwd_kernel"); return ST_OK;
+}
+int ew_relu_maxpool_bwd(const bf16* xh, const bf16* xl, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
+                        bf16* gxh, bf16* gxl, int N, int H, int W, int C, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+    relu_maxpool_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C);
+    ST_CHECK_LAUNCH("relu_maxpool_bwd_kernel"); return ST_OK;
+}
+// workspace: >= 4096 floats
+int ew_mse_fwd(const bf16* xh, const bf16* xl, const bf16* th, const bf16* tl, size_t n, int relu, int feature_form,
+               float* loss_out, float* ws, cudaStream_t st) {
+    const size_t nvec = n / 8;
+    int grid = grid_for(nvec, 256, 4); if (grid > 4096) grid = 4096;
+    mse_partial_kernel<<<grid, 256, 0, st>>>(xh, xl, th, tl, nvec, relu, ws);
+    ST_CHECK_LAUNCH("mse_partial_kernel");
+    // feature_form: (mse)^2 / numel   network.py:193-199
+    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(n), feature_form, 1.0f / static_cast<float>(n), loss_out);
+    ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
+}
+int ew_mse_bwd(const bf16* xh, const bf16* xl, const bf16* th, const bf16* tl, size_t n, int relu, float scale,
+               const float* gw, const float* mul, int accumulate, bf16* gh, bf16* gl, cudaStream_t st) {
+    const size_t nvec = n / 8;
+    mse_bwd_kernel<<<grid_for(nvec, 256), 256, 0, st>>>(xh, xl, th, tl, nvec, relu, scale, gw, mul, accumulate, gh, gl);
+    ST_CHECK_LAUNCH("mse_bwd_kernel"); return ST_OK;
+}
+int ew_style_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss_out, float* ws, cudaStream_t st) {
+    const int total = B * C * C;
+    int grid = grid_for(total, 256, 2); if (grid > 4096) grid = 4096;
+    style_diff_kernel<<<grid, 256, 0, st>>>(G, T, C * C, total, diff, ws);
+    ST_CHECK_LAUNCH("style_diff_kernel");
+    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(total), 0, 1.f, loss_out);
+    ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
+}
+int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw, bf16* dh, bf16* dl, cudaStream_t st) {
+    const int total = B * C * C;
+    style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl);
+    ST_CHECK_LAUNCH("style_seed_kernel"); return ST_OK;
+}
+// ws: >= nblk*C floats with nblk = min(1024, ceil(P/64))
+int ew_channel_sum(const bf16* xh, const bf16* xl, int P, int C, int Cout, float* out, float* ws, cudaStream_t st) {
+    int nblk = (P + 63) / 64; if (nblk > 1024) nblk = 1024;
+    const int rows = (P + nblk - 1) / nblk;
+    nblk = (P + rows - 1) / rows;
+    channel_sum_partial_kernel<<<nblk, C, 0, st>>>(xh, xl, P, C, rows, ws);
+    ST_CHECK_LAUNCH("channel_sum_partial_kernel");
+    channel_sum_finish_kernel<<<(Cout + 127) / 128, 128, 0, st>>>(ws, nblk, C, Cout, out);
+    ST_CHECK_LAUNCH("channel_sum_finish_kernel"); return ST_OK;
+}

@@ -1,0 +1,357 @@
+// InstanceNorm2d(affine) forward/backward with fused ReLU and fused nearest x2
+// upsample-on-write (network.py:474, :483, :531-600), the total-variation loss
+// (network.py:621-641) and the temporal loss (network.py:885-903).
+// HBM-bound kernels: 128-bit accesses, channels-last so a warp reads contiguous
+// memory, per-(n,c) statistics reduced in two deterministic stages.
+#include "common.cuh"
+
+namespace {
+
+constexpr int IN_THREADS = 256;
+
+// stage 1: per (image, pixel split) partial sums of a[c] and b[c] over the split's pixels.
+// MODE 0 (forward stats): a = x, b = x*x
+// MODE 1 (backward stats): a = dy_eff, b = dy_eff * xhat, with
+//        dy_eff = (relu ? dy * (gamma*xhat+beta > 0) : dy), dy summed over the 2x2
+//        upsampled positions when up != 0.
+template <int MODE>
+__global__ void __launch_bounds__(IN_THREADS)
+in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                const bf16* __restrict__ gh, const bf16* __restrict__ gl,
+                const float* __restrict__ mean, const float* __restrict__ rstd,
+                const float* __restrict__ gamma, const float* __restrict__ beta,
+                int HW, int W, int C, int splits, int chunk, int relu, int up,
+                float* __restrict__ partial /* [N][splits][2][C] */) {
+    extern __shared__ float sm[];                 // [lanes][2][C]
+    const int n = blockIdx.x / splits, sp = blockIdx.x % splits;
+    const int Cv = C / 8, lanes = IN_THREADS / Cv;
+    const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
+    const int p0 = sp * chunk, p1 = min(HW, p0 + chunk);
+    float sa[8], sb[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { sa[i] = 0.f; sb[i] = 0.f; }
+    float mu[8], rs[8], ga[8], be[8];
+    if (MODE == 1) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            mu[i] = mean[n * C + cv * 8 + i]; rs[i] = rstd[n * C + cv * 8 + i];
+            ga[i] = gamma[cv * 8 + i]; be[i] = beta[cv * 8 + i];
+        }
+    }
+    if (pl < lanes) {
+        for (int p = p0 + pl; p < p1; p += lanes) {
+            float x[8];
+            load8(xh, xl, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
+            if (MODE == 0) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { sa[i] += x[i]; sb[i] += x[i] * x[i]; }
+            } else {
+                float g[8];
+                if (!up) {
+                    load8(gh, gl, (static_cast<size_t>(n) * HW + p) * C + cv * 8, g);
+                } else {
+                    const int h = p / W, w = p - h * W, W2 = W * 2;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) g[i] = 0.f;
+#pragma unroll
+                    for (int d = 0; d < 4; ++d) {
+                        float t[8];
+                        load8(gh, gl, ((static_cast<size_t>(n) * HW * 4) + static_cast<size_t>(h * 2 + (d >> 1)) * W2 + w * 2 + (d & 1)) * C + cv * 8, t);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) g[i] += t[i];
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float xhat = (x[i] - mu[i]) * rs[i];
+                    const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g[i];
+                    sa[i] += ge; sb[i] += ge * xhat;
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            sm[(pl * 2 + 0) * C + cv * 8 + i] = sa[i];
+            sm[(pl * 2 + 1) * C + cv * 8 + i] = sb[i];
+        }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * C; j += IN_THREADS) {
+        float s = 0.f;
+        for (int l = 0; l < lanes; ++l) s += sm[l * 2 * C + j];
+        partial[(static_cast<size_t>(blockIdx.x)) * 2 * C + j] = s;
+    }
+}
+
+// forward finalize: mean / rstd per (n,c)    (biased variance, eps inside the sqrt)
+__global__ void in_finalize_fwd_kernel(const float* __restrict__ partial, int NC, int C, int splits, int HW, float eps,
+                                       float* __restrict__ mean, float* __restrict__ rstd) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= NC) return;
+    const int n = i / C, c = i % C;
+    double s = 0.0, q = 0.0;
+    for (int sp = 0; sp < splits; ++sp) {
+        s += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + c];
+        q += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + C + c];
+    }
+    const double m = s / HW;
+    double var = q / HW - m * m; if (var < 0.0) var = 0.0;
+    mean[i] = static_cast<float>(m);
+    rstd[i] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+}
+
+// backward finalize: s1 = sum dy_eff, s2 = sum dy_eff*xhat per (n,c); dgamma/dbeta = sums over n
+__global__ void in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int splits,
+                                       float* __restrict__ s1, float* __restrict__ s2,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float dg = 0.f, db = 0.f;
+    for (int n = 0; n < N; ++n) {
+        float a = 0.f, b = 0.f;
+        for (int sp = 0; sp < splits; ++sp) {
+            a += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + c];
+            b += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + C + c];
+        }
+        s1[n * C + c] = a; s2[n * C + c] = b;
+        db += a; dg += b;
+    }
+    dgamma[c] = dg; dbeta[c] = db;
+}
+
+// forward apply: y = gamma * (x - mean) * rstd + beta  (+ReLU) (+ x2 nearest upsample on write)
+__global__ void in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                    bf16* __restrict__ yh, bf16* __restrict__ yl,
+                                    int N, int H, int W, int C, int relu, int up) {
+    const int Cv = C / 8;
+    const size_t total = static_cast<size_t>(N) * H * W * Cv;
+    for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+         idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int cv = idx % Cv; const size_t pix = idx / Cv;
+        const int n = pix / (static_cast<size_t>(H) * W);
+        float x[8];
+        load8(xh, xl, pix * C + cv * 8, x);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = cv * 8 + i;
+            float y = gamma[c] * (x[i] - mean[n * C + c]) * rstd[n * C + c] + beta[c];
+            x[i] = relu ? fmaxf(y, 0.f) : y;
+        }
+        if (!up) {
+            store8(yh, yl, pix * C + cv * 8, x);
+        } else {
+            const int p = pix - static_cast<size_t>(n) * H * W; const int h = p / W, w = p - h * W;
+#pragma unroll
+            for (int d = 0; d < 4; ++d)
+                store8(yh, yl, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, x);
+        }
+    }
+}
+
+// backward apply: dx = gamma*rstd/HW * (HW*dy_eff - s1 - xhat*s2)
+__global__ void in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                    const bf16* __restrict__ gh, const bf16* __restrict__ gl,
+                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                    const float* __restrict__ s1, const float* __restrict__ s2,
+                                    bf16* __restrict__ dxh, bf16* __restrict__ dxl,
+                                    int N, int H, int W, int C, int relu, int up) {
+    const int Cv = C / 8, HW = H * W;
+    const float inv_hw = 1.0f / HW;
+    const size_t total = static_cast<size_t>(N) * HW * Cv;
+    for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
+         idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int cv = idx % Cv; const size_t pix = idx / Cv;
+        const int n = pix / HW;
+        float x[8], g[8];
+        load8(xh, xl, pix * C + cv * 8, x);
+        if (!up) {
+            load8(gh, gl, pix * C + cv * 8, g);
+        } else {
+            const int p = pix - static_cast<size_t>(n) * HW; const int h = p / W, w = p - h * W;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = 0.f;
+#pragma unroll
+            for (int d = 0; d < 4; ++d) {
+                float t[8];
+                load8(gh, gl, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, t);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) g[i] += t[i];
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = cv * 8 + i;
+            const float rs = rstd[n * C + c];
+            const float xhat = (x[i] - mean[n * C + c]) * rs;
+            const float ge = (relu && !(gamma[c] * xhat + beta[c] > 0.f)) ? 0.f : g[i];
+            x[i] = gamma[c] * rs * (ge - inv_hw * (s1[n * C + c] + xhat * s2[n * C + c]));
+        }
+        store8(dxh, dxl, pix * C + cv * 8, x);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Total variation on an NCHW fp32 image batch: partial sums of |dx| + |dy|
+// ---------------------------------------------------------------------------
+__global__ void tv_partial_kernel(const float* __restrict__ x, size_t total, int H, int W, float* __restrict__ partial) {
+    __shared__ float sm[32];
+    float s = 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int w = i % W; const int h = (i / W) % H;
+        const float v = x[i];
+        if (w + 1 < W) s += fabsf(v - x[i + 1]);
+        if (h + 1 < H) s += fabsf(v - x[i + W]);
+    }
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+__device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0.f) ? -1.f : 0.f); }
+// g = coef * d/dx TV,  coef = factor * (*gw)
+__global__ void tv_bwd_kernel(const float* __restrict__ x, size_t total, int H, int W, float factor,
+                              const float* __restrict__ gw, float* __restrict__ g) {
+    const float coef = factor * gw[0];
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int w = i % W; const int h = (i / W) % H;
+        const float v = x[i];
+        float d = 0.f;
+        if (w + 1 < W) d += sgn(v - x[i + 1]);
+        if (w > 0) d -= sgn(x[i - 1] - v);
+        if (h + 1 < H) d += sgn(v - x[i + W]);
+        if (h > 0) d -= sgn(x[i - W] - v);
+        g[i] = coef * d;
+    }
+}
+__global__ void finish_scalar_kernel(const float* __restrict__ partial, int n, float scale, float* __restrict__ out) {
+    __shared__ float sm[32];
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
+    s = block_sum(s, sm);
+    if (threadIdx.x == 0) out[0] = s * scale;
+}
+
+// ---------------------------------------------------------------------------
+// Temporal loss: tw * ||cs - os|| / (||cc - oc|| + 1)     (fp32 NCHW tensors)
+// ---------------------------------------------------------------------------
+__global__ void temporal_partial_kernel(const float* __restrict__ oc, const float* __restrict__ os,
+                                        const float* __restrict__ cc, const float* __restrict__ cs,
+                                        size_t total, float* __restrict__ partial /* [grid][2] */) {
+    __shared__ float sm[32];
+    float a = 0.f, b = 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const float ds = cs[i] - os[i], dc = cc[i] - oc[i];
+        a += ds * ds; b += dc * dc;
+    }
+    a = block_sum(a, sm);
+    b = block_sum(b, sm);
+    if (threadIdx.x == 0) { partial[blockIdx.x * 2] = a; partial[blockIdx.x * 2 + 1] = b; }
+}
+// out[0] = loss, out[1] = ||ds||, out[2] = ||dc||
+__global__ void temporal_finish_kernel(const float* __restrict__ partial, int n, float tw, float* __restrict__ out) {
+    __shared__ float sm[32];
+    float a = 0.f, b = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { a += partial[i * 2]; b += partial[i * 2 + 1]; }
+    a = block_sum(a, sm);
+    b = block_sum(b, sm);
+    if (threadIdx.x == 0) {
+        const float ns = sqrtf(a), nc = sqrtf(b);
+        out[0] = tw * ns / (nc + 1.f); out[1] = ns; out[2] = nc;
+    }
+}
+// g = (*gw) * tw / ((nc + 1) * ns) * (cs - os)   (0 when ns == 0, as torch's norm backward)
+__global__ void temporal_bwd_kernel(const float* __restrict__ os, const float* __restrict__ cs, size_t total, float tw,
+                                    const float* __restrict__ stats, const float* __restrict__ gw, float* __restrict__ g) {
+    const float ns = stats[1], nc = stats[2];
+    const float coef = ns > 0.f ? gw[0] * tw / ((nc + 1.f) * ns) : 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        g[i] = coef * (cs[i] - os[i]);
+}
+
+inline int in_splits(int N, int HW) {
+    int splits = (3 * st_num_sms() + N - 1) / N;
+    const int maxs = (HW + 255) / 256;
+    if (splits > maxs) splits = maxs;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+    return splits;
+}
+inline int ew_grid(size_t n, int block) {
+    size_t g = (n + block - 1) / block; size_t cap = static_cast<size_t>(st_num_sms()) * 8;
+    return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+
+size_t in_workspace_floats(int N, int C) { return static_cast<size_t>(N) * 64 * 2 * C; }
+
+int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* beta, float eps,
+               bf16* yh, bf16* yl, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
+               float* ws, cudaStream_t st) {
+    const int HW = H * W, splits = in_splits(N, HW);
+    const int chunk = (HW + splits - 1) / splits;
+    const int lanes = IN_THREADS / (C / 8);
+    in_stats_kernel<0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, 0, ws);
+    ST_CHECK_LAUNCH("in_stats_kernel<0>");
+    in_finalize_fwd_kernel<<<(N * C + 127) / 128, 128, 0, st>>>(ws, N * C, C, splits, HW, eps, mean, rstd);
+    ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
+    in_apply_fwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
+        xh, xl, mean, rstd, gamma, beta, yh, yl, N, H, W, C, relu, up);
+    ST_CHECK_LAUNCH("in_apply_fwd_kernel");
+    return ST_OK;
+}
+
+int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
+                const float* mean, const float* rstd, const float* gamma, const float* beta,
+                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int up,
+                float* ws, cudaStream_t st) {
+    const int HW = H * W, splits = in_splits(N, HW);
+    const int chunk = (HW + splits - 1) / splits;
+    const int lanes = IN_THREADS / (C / 8);
+    float* s1 = ws + static_cast<size_t>(N) * splits * 2 * C;
+    float* s2 = s1 + static_cast<size_t>(N) * C;
+    in_stats_kernel<1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+        xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, up, ws);
+    ST_CHECK_LAUNCH("in_stats_kernel<1>");
+    in_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
+    ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
+    in_apply_bwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
+        xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, N, H, W, C, relu, up);
+    ST_CHECK_LAUNCH("in_apply_bwd_kernel");
+    return ST_OK;
+}
+
+int tv_forward(const float* x, size_t total, int H, int W, float factor, float* loss, float* ws, cudaStream_t st) {
+    int grid = ew_grid(total, 256); if (grid > 2048) grid = 2048;
+    tv_partial_kernel<<<grid, 256, 0, st>>>(x, total, H, W, ws);
+    ST_CHECK_LAUNCH("tv_partial_kernel");
+    finish_scalar_kernel<<<1, 256, 0, st>>>(ws, grid, factor, loss);
+    ST_CHECK_LAUNCH("finish_scalar_kernel");
+    return ST_OK;
+}
+int tv_backward(const float* x, size_t total, int H, int W, float factor, const float* gw, float* g, cudaStream_t st) {
+    tv_bwd_kernel<<<ew_grid(total, 256), 256, 0, st>>>(x, total, H, W, factor, gw, g);
+    ST_CHECK_LAUNCH("tv_bwd_kernel");
+    return ST_OK;
+}
+int temporal_forward(const float* oc, const float* os, const float* cc, const float* cs, size_t total, float tw,
+                     float* out3, float* ws, cudaStream_t st) {
+    int grid = ew_grid(total, 256); if (grid > 1024) grid = 1024;
+    temporal_partial_kernel<<<grid, 256, 0, st>>>(oc, os, cc, cs, total, ws);
+    ST_CHECK_LAUNCH("temporal_partial_kernel");
+    temporal_finish_kernel<<<1, 256, 0, st>>>(ws, grid, tw, out3);
+    ST_CHECK_LAUNCH("temporal_finish_kernel");
+    return ST_OK;
+}
+int temporal_backward(const float* os, const float* cs, size_t total, float tw, const float* stats, const float* gw,
+                      float* g, cudaStream_t st) {
+    temporal_bwd_kernel<<<ew_grid(total, 256), 256, 0, st>>>(os, cs, total, tw, stats, gw, g);
+    ST_CHECK_LAUNCH("temporal_bwd_kernel");
+    return ST_OK;
+}
