@@ -1,0 +1,82 @@
+"""ctypes binding of libstransfer_b200.so (include/stransfer_b200.h).
+
+There is deliberately NO fallback: if the library is missing or a call fails the
+product path raises.  ``lib()`` loads (and, if the sources changed, rebuilds) the
+in-tree shared object.
+"""
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_size_t, c_void_p
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, 'libstransfer_b200.so')
+
+_P, _I, _F, _Z = c_void_p, c_int, c_float, c_size_t
+
+# name -> (restype, argtypes); mirrors include/stransfer_b200.h one to one
+SIGNATURES = {
+    'st_arch': (_I, []),
+    'st_last_error': (c_char_p, []),
+    'st_set_conv_path': (_I, [_I]),
+    'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    'st_nhwc_to_nchw': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    'st_pack_conv_weight': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    'st_conv2d': (_I, [_P, _P, _I, _I, _I, _I, _I,          # x, N H W Cin up
+                       _P, _P, _I, _I,                      # w, rows_total, img_rows
+                       _I, _I, _I, _I,                      # ks stride pad transposed
+                       _I, _I, _I, _I,                      # Ho Wo Cout_pad Cbias
+                       _P, _P, _P, _P,                      # bias mask add_hi add_lo
+                       _P, _P, _P, _P,                      # out_hi out_lo relu_hi relu_lo
+                       _P, _I, _P]),                        # out_nchw Cnchw stream
+    'st_conv2d_wgrad_workspace_bytes': (_Z, [_I, _I, _I, _I, _I, _I]),
+    'st_conv2d_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
+                             _P, _P, _P, _Z, _P]),
+    'st_relu_maxpool2x2_fwd': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    'st_relu_maxpool2x2_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    'st_gram_workspace_bytes': (_Z, [_I, _I, _I]),
+    'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _P, _P, _Z, _P]),
+    'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P]),
+    'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
+    'st_mse_fwd': (_I, [_P, _P, _P, _P, _Z, _I, _I, _P, _P, _P]),
+    'st_mse_bwd': (_I, [_P, _P, _P, _P, _Z, _I, _F, _P, _P, _I, _P, _P, _P]),
+    'st_tv_fwd': (_I, [_P, _I, _I, _I, _I, _F, _P, _P, _P]),
+    'st_tv_bwd': (_I, [_P, _I, _I, _I, _I, _F, _P, _P, _P]),
+    'st_temporal_fwd': (_I, [_P, _P, _P, _P, _Z, _F, _P, _P, _P]),
+    'st_temporal_bwd': (_I, [_P, _P, _Z, _F, _P, _P, _P, _P]),
+    'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
+    'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+}
+
+_lib = None
+
+
+class StransferError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load the shared object (building it first when stale/missing)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    from . import build as _build
+    if not _build.up_to_date():
+        _build.build()
+    if not os.path.exists(LIB_PATH):
+        raise StransferError(f'{LIB_PATH} is missing: run `python -m styletransfer_b200.build`')
+    handle = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(handle, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    if handle.st_arch() != 100:
+        raise StransferError('libstransfer_b200.so was not built for sm_100a')
+    _lib = handle
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().st_last_error().decode(errors='replace')
+        raise StransferError(f'{what} failed (code {rc}): {msg}')

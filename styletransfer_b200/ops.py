@@ -1,0 +1,282 @@
+"""Thin Python wrappers over the C ABI: device buffers in the split-bf16 NHWC
+format and one function per entry point.  PyTorch is used for memory and streams
+only; every numeric op below is a kernel of libstransfer_b200.so.
+"""
+import torch
+
+from . import _lib
+
+# 'bf16x3': hi+lo planes, 3 tensor-core passes per product (parity grade, default)
+# 'bf16'  : hi plane only, 1 pass (fast, ~3e-2 error on the Gatys gradient)
+PRECISION = 'bf16x3'
+
+
+def set_precision(mode):
+    global PRECISION
+    assert mode in ('bf16x3', 'bf16')
+    PRECISION = mode
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(t, what):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise _lib.StransferError(f'{what}: expected a CUDA tensor (there is no CPU fallback)')
+
+
+def pad8(c):
+    return (c + 7) // 8 * 8
+
+
+class Split:
+    """NHWC activation stored as bf16 hi (+ lo) planes in one allocation."""
+    __slots__ = ('buf', 'N', 'H', 'W', 'C', 'hi', 'lo')
+
+    def __init__(self, N, H, W, C, device, lo=None, zero=False):
+        lo = (PRECISION == 'bf16x3') if lo is None else lo
+        alloc = torch.zeros if zero else torch.empty
+        self.buf = alloc((2 if lo else 1, N, H, W, C), dtype=torch.bfloat16, device=device)
+        self.N, self.H, self.W, self.C = N, H, W, C
+        self.hi = self.buf[0].data_ptr()
+        self.lo = self.buf[1].data_ptr() if lo else None
+
+    @property
+    def shape(self):
+        return (self.N, self.H, self.W, self.C)
+
+    def float(self):
+        """fp32 NHWC view of the value (hi + lo) -- for tests/debugging."""
+        v = self.buf[0].float()
+        return v + self.buf[1].float() if self.buf.shape[0] == 2 else v
+
+    def like(self):
+        return Split(self.N, self.H, self.W, self.C, self.buf.device, lo=self.lo is not None)
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def from_nchw(x, x2=None, cpad=None):
+    """NCHW fp32 -> Split (channel-concat of x and x2, padded with zeros to cpad)."""
+    _require_cuda(x, 'from_nchw')
+    x = x.contiguous().float()
+    N, C1, H, W = x.shape
+    C2 = 0
+    if x2 is not None:
+        x2 = x2.contiguous().float()
+        C2 = x2.shape[1]
+    cpad = cpad or pad8(C1 + C2)
+    out = Split(N, H, W, cpad, x.device)
+    _lib.check(_lib.lib().st_nchw_to_nhwc(x.data_ptr(), _p(x2), out.hi, out.lo, N, C1, C2, H, W, cpad, _stream()),
+               'st_nchw_to_nhwc')
+    return out
+
+
+def to_nchw(s, C=None):
+    C = C or s.C
+    out = torch.empty((s.N, C, s.H, s.W), dtype=torch.float32, device=s.buf.device)
+    _lib.check(_lib.lib().st_nhwc_to_nchw(s.hi, s.lo, out.data_ptr(), s.N, C, s.H, s.W, s.C, _stream()), 'st_nhwc_to_nchw')
+    return out
+
+
+class PackedWeight:
+    """nn.Conv2d weight packed for one of the conv modes (see st_pack_conv_weight)."""
+    __slots__ = ('buf', 'hi', 'lo', 'rows', 'cols', 'ks', 'mode', 'cout', 'cin')
+
+    def __init__(self, w, mode, rows_pad=None, cols_pad=None):
+        _require_cuda(w, 'PackedWeight')
+        w = w.detach().contiguous().float()
+        cout, cin, ks, _ = w.shape
+        rows, cols = (cout, cin) if mode == 0 else (cin, cout)
+        self.rows, self.cols = rows_pad or pad8(rows), cols_pad or pad8(cols)
+        self.ks, self.mode, self.cout, self.cin = ks, mode, cout, cin
+        lo = PRECISION == 'bf16x3'
+        self.buf = torch.empty((2 if lo else 1, self.rows, ks * ks, self.cols), dtype=torch.bfloat16, device=w.device)
+        self.hi = self.buf[0].data_ptr()
+        self.lo = self.buf[1].data_ptr() if lo else None
+        _lib.check(_lib.lib().st_pack_conv_weight(w.data_ptr(), self.hi, self.lo, cout, cin, ks, self.rows, self.cols,
+                                                  mode, _stream()), 'st_pack_conv_weight')
+
+
+def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
+           mask=None, add=None, want_out=True, want_relu=False, out_nchw_channels=0, w_img_rows=0, w_ptrs=None):
+    """Generic entry to st_conv2d.  `w` is a PackedWeight (or None with w_ptrs =
+    (hi, lo, rows_total, ks, cols) for the per-image Gram-backward weights).
+    Returns (out Split|None, relu Split|None, out_nchw Tensor|None)."""
+    if w is not None:
+        w_hi, w_lo, rows_total, ks, cols = w.hi, w.lo, w.rows, w.ks, w.cols
+        cout_pad = w.rows
+    else:
+        w_hi, w_lo, rows_total, ks, cols = w_ptrs
+        cout_pad = w_img_rows
+    assert cols == x.C, f'weight expects {cols} input channels, activation has {x.C}'
+    pad = ks // 2 if pad is None else pad
+    Hl, Wl = x.H << up, x.W << up
+    if out_hw is not None:
+        Ho, Wo = out_hw
+    elif transposed:
+        Ho, Wo = x.H * stride, x.W * stride
+    else:
+        Ho, Wo = (Hl + 2 * pad - ks) // stride + 1, (Wl + 2 * pad - ks) // stride + 1
+    dev = x.buf.device
+    out = Split(x.N, Ho, Wo, cout_pad, dev) if want_out else None
+    relu = Split(x.N, Ho, Wo, cout_pad, dev) if want_relu else None
+    nchw = torch.empty((x.N, out_nchw_channels, Ho, Wo), dtype=torch.float32, device=dev) if out_nchw_channels else None
+    for t in (mask, add):
+        assert t is None or t.shape == (x.N, Ho, Wo, cout_pad), 'mask/add shape mismatch'
+    cbias = 0 if bias is None else bias.numel()
+    _lib.check(_lib.lib().st_conv2d(
+        x.hi, x.lo, x.N, x.H, x.W, x.C, up, w_hi, w_lo, rows_total, w_img_rows, ks, stride, pad, transposed,
+        Ho, Wo, cout_pad, cbias, _p(bias), mask.hi if mask else None,
+        add.hi if add else None, add.lo if add else None,
+        out.hi if out else None, out.lo if out else None, relu.hi if relu else None, relu.lo if relu else None,
+        _p(nchw), out_nchw_channels, _stream()), 'st_conv2d')
+    return out, relu, nchw
+
+
+_ws_cache = {}
+
+
+def workspace(nbytes, device, tag='ws'):
+    """Grow-only scratch buffer per (device, tag, stream)."""
+    key = (device, tag, _stream())
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 16), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def conv2d_wgrad(dy, x, ks, stride, pad, up, cout, cin, want_bias=True):
+    L = _lib.lib()
+    dev = x.buf.device
+    nbytes = L.st_conv2d_wgrad_workspace_bytes(dy.N, dy.H, dy.W, dy.C, x.C, ks)
+    ws = workspace(nbytes, dev)
+    dw = torch.empty((cout, cin, ks, ks), dtype=torch.float32, device=dev)
+    db = torch.empty((cout,), dtype=torch.float32, device=dev) if want_bias else None
+    _lib.check(L.st_conv2d_wgrad(dy.hi, dy.lo, dy.C, x.hi, x.lo, x.N, x.H, x.W, x.C, up, dy.H, dy.W, ks, stride, pad,
+                                 cout, cin, dw.data_ptr(), _p(db), ws.data_ptr(), ws.numel(), _stream()), 'st_conv2d_wgrad')
+    return dw, db
+
+
+def relu_maxpool_fwd(x):
+    y = Split(x.N, x.H // 2, x.W // 2, x.C, x.buf.device)
+    _lib.check(_lib.lib().st_relu_maxpool2x2_fwd(x.hi, x.lo, y.hi, y.lo, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_fwd')
+    return y
+
+
+def relu_maxpool_bwd(x, gy, add=None):
+    gx = x.like()
+    _lib.check(_lib.lib().st_relu_maxpool2x2_bwd(x.hi, x.lo, gy.hi, gy.lo, add.hi if add else None, add.lo if add else None,
+                                                 gx.hi, gx.lo, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_bwd')
+    return gx
+
+
+def gram(f):
+    """[B][C][C] fp32 Gram matrices, already divided by C*H*W (network.py:92-108)."""
+    L = _lib.lib()
+    dev = f.buf.device
+    HW = f.H * f.W
+    nbytes = L.st_gram_workspace_bytes(f.N, HW, f.C)
+    ws = workspace(nbytes, dev)
+    G = torch.empty((f.N, f.C, f.C), dtype=torch.float32, device=dev)
+    _lib.check(L.st_gram_fwd(f.hi, f.lo, f.N, HW, f.C, G.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), 'st_gram_fwd')
+    return G
+
+
+def style_mse_fwd(G, T, loss_out):
+    """loss_out: 1-element fp32 view that receives mean((G-T)^2); returns diff."""
+    B, C, _ = G.shape
+    diff = torch.empty_like(G)
+    ws = workspace(4096 * 4, G.device, 'small')
+    _lib.check(_lib.lib().st_style_mse_fwd(G.data_ptr(), T.data_ptr(), B, C, diff.data_ptr(), loss_out.data_ptr(),
+                                           ws.data_ptr(), _stream()), 'st_style_mse_fwd')
+    return diff
+
+
+def style_seed(diff, HW, gw):
+    """Packed per-image weights D = gw * 4/(B C^2 C HW) * diff for the dF = F*D conv."""
+    B, C, _ = diff.shape
+    lo = PRECISION == 'bf16x3'
+    buf = torch.empty((2 if lo else 1, B * C, C), dtype=torch.bfloat16, device=diff.device)
+    hi, lo_p = buf[0].data_ptr(), (buf[1].data_ptr() if lo else None)
+    _lib.check(_lib.lib().st_style_mse_bwd_seed(diff.data_ptr(), B, C, HW, gw.data_ptr(), hi, lo_p, _stream()),
+               'st_style_mse_bwd_seed')
+    return buf, (hi, lo_p, B * C, 1, C)
+
+
+def mse_fwd(x, t, loss_out, relu=False, feature_form=False):
+    ws = workspace(4096 * 4, x.buf.device, 'small')
+    n = x.buf[0].numel()
+    _lib.check(_lib.lib().st_mse_fwd(x.hi, x.lo, t.hi, t.lo, n, int(relu), int(feature_form), loss_out.data_ptr(),
+                                     ws.data_ptr(), _stream()), 'st_mse_fwd')
+
+
+def mse_bwd(x, t, gw, scale, out=None, relu=False, mul=None):
+    acc = out is not None
+    out = out or x.like()
+    n = x.buf[0].numel()
+    _lib.check(_lib.lib().st_mse_bwd(x.hi, x.lo, t.hi, t.lo, n, int(relu), float(scale), gw.data_ptr(), _p(mul), int(acc),
+                                     out.hi, out.lo, _stream()), 'st_mse_bwd')
+    return out
+
+
+def instnorm_fwd(x, gamma, beta, relu=False, up=False, eps=1e-5):
+    L = _lib.lib()
+    dev = x.buf.device
+    ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
+    y = Split(x.N, x.H << int(up), x.W << int(up), x.C, dev)
+    stats = torch.empty((2, x.N, x.C), dtype=torch.float32, device=dev)
+    _lib.check(L.st_instnorm_fwd(x.hi, x.lo, gamma.data_ptr(), beta.data_ptr(), eps, y.hi, y.lo,
+                                 stats[0].data_ptr(), stats[1].data_ptr(), x.N, x.H, x.W, x.C, int(relu), int(up),
+                                 ws.data_ptr(), _stream()), 'st_instnorm_fwd')
+    return y, stats
+
+
+def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False):
+    L = _lib.lib()
+    dev = x.buf.device
+    ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
+    dx = x.like()
+    dgamma = torch.empty_like(gamma)
+    dbeta = torch.empty_like(beta)
+    _lib.check(L.st_instnorm_bwd(x.hi, x.lo, gy.hi, gy.lo, stats[0].data_ptr(), stats[1].data_ptr(),
+                                 gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(),
+                                 x.N, x.H, x.W, x.C, int(relu), int(up), ws.data_ptr(), _stream()), 'st_instnorm_bwd')
+    return dx, dgamma, dbeta
+
+
+def tv_fwd(x, factor):
+    _require_cuda(x, 'tv_fwd')
+    N, C, H, W = x.shape
+    loss = torch.empty((), dtype=torch.float32, device=x.device)
+    ws = workspace(4096 * 4, x.device, 'small')
+    _lib.check(_lib.lib().st_tv_fwd(x.data_ptr(), N, C, H, W, float(factor), loss.data_ptr(), ws.data_ptr(), _stream()), 'st_tv_fwd')
+    return loss
+
+
+def tv_bwd(x, factor, gw):
+    N, C, H, W = x.shape
+    g = torch.empty_like(x)
+    _lib.check(_lib.lib().st_tv_bwd(x.data_ptr(), N, C, H, W, float(factor), gw.data_ptr(), g.data_ptr(), _stream()), 'st_tv_bwd')
+    return g
+
+
+def temporal_fwd(old_content, old_stylized, cur_content, cur_stylized, tw):
+    _require_cuda(cur_stylized, 'temporal_fwd')
+    out3 = torch.empty((3,), dtype=torch.float32, device=cur_stylized.device)
+    ws = workspace(4096 * 4, cur_stylized.device, 'small')
+    _lib.check(_lib.lib().st_temporal_fwd(old_content.data_ptr(), old_stylized.data_ptr(), cur_content.data_ptr(),
+                                          cur_stylized.data_ptr(), cur_stylized.numel(), float(tw), out3.data_ptr(),
+                                          ws.data_ptr(), _stream()), 'st_temporal_fwd')
+    return out3
+
+
+def temporal_bwd(old_stylized, cur_stylized, tw, stats3, gw):
+    g = torch.empty_like(cur_stylized)
+    _lib.check(_lib.lib().st_temporal_bwd(old_stylized.data_ptr(), cur_stylized.data_ptr(), cur_stylized.numel(), float(tw),
+                                          stats3.data_ptr(), gw.data_ptr(), g.data_ptr(), _stream()), 'st_temporal_bwd')
+    return g

@@ -1,0 +1,107 @@
+"""Single-pass VGG-19 loss network on the B200 kernels.
+
+Replaces the seven (+2) prefix passes that StyleNetwork.forward runs per call
+(reference network.py:366-401 -> run_through_pieces :316-340) by ONE forward that
+emits the five pre-ReLU taps, and autograd's backward through the replicated
+prefixes by ONE fused backward-data chain to the image.  VGG weights are frozen
+(no wgrad).  Losses come back as a length-7 tensor
+[style x5, content, feature] whose gradient weights (grad_output) are read on the
+device, so no host synchronisation happens anywhere in forward or backward.
+"""
+import torch
+
+from . import ops
+
+# (cin, cout, pool_before): conv1_1, conv1_2, conv2_1, conv2_2, conv3_1 = Conv2d_1..5
+PREFIX = [(3, 64, False), (64, 64, False), (64, 128, True), (128, 128, False), (128, 256, True)]
+CONTENT_TAP = 3
+N_LOSSES = 7
+
+
+class VGGPrefix:
+    """Packed weights of the five executed convs."""
+
+    def __init__(self, weights):
+        assert len(weights) == 5
+        self.device = weights[0][0].device
+        self.fwd, self.bwd, self.bias = [], [], []
+        for i, (w, b) in enumerate(weights):
+            ops._require_cuda(w, 'VGGPrefix')
+            cin_pad = 8 if i == 0 else w.shape[1]
+            self.fwd.append(ops.PackedWeight(w, 0, cols_pad=cin_pad))
+            # backward-data: conv1_1 goes through the gather form (3 output channels, padded to 8),
+            # the others run as forward convs with flipped taps on the tcgen05 kernel
+            self.bwd.append(ops.PackedWeight(w, 1 if i == 0 else 2, rows_pad=cin_pad))
+            self.bias.append(b.detach().contiguous().float())
+
+    def taps(self, x, upto=5, keep_all=True):
+        """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto."""
+        h = ops.from_nchw(x, cpad=8)
+        taps = []
+        for i in range(upto):
+            pool_next = i + 1 < 5 and PREFIX[i + 1][2]
+            last = i + 1 == upto
+            # a tap feeds either relu+maxpool (separate kernel) or a conv that wants relu(tap)
+            want_relu = not last and not pool_next
+            tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=True, want_relu=want_relu)
+            taps.append(tap)
+            if last:
+                break
+            h = ops.relu_maxpool_fwd(tap) if pool_next else relu
+        return taps
+
+
+class _VGGLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, net, style_targets, content_target, with_feature):
+        taps = net.taps(x)
+        losses = torch.zeros(N_LOSSES, dtype=torch.float32, device=x.device)
+        diffs = []
+        for i, tap in enumerate(taps):
+            G = ops.gram(tap)
+            diffs.append(ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1]))
+        ops.mse_fwd(taps[CONTENT_TAP], content_target, losses[5:6])
+        feat_mse = None
+        if with_feature:
+            feat_mse = torch.empty(1, dtype=torch.float32, device=x.device)
+            ops.mse_fwd(taps[CONTENT_TAP], content_target, feat_mse, relu=True)
+            ops.mse_fwd(taps[CONTENT_TAP], content_target, losses[6:7], relu=True, feature_form=True)
+        ctx.net, ctx.taps, ctx.diffs = net, taps, diffs
+        ctx.content_target, ctx.feat_mse = content_target, feat_mse
+        ctx.in_shape = x.shape
+        return losses
+
+    @staticmethod
+    def backward(ctx, gl):
+        net, taps, diffs = ctx.net, ctx.taps, ctx.diffs
+        gl = gl.contiguous().float()
+        # dF_l = F_l * D_l  (Gram backward, per-image 1x1 conv on the tensor cores)
+        def style_grad(i, add=None):
+            tap = taps[i]
+            _buf, wp = ops.style_seed(diffs[i], tap.H * tap.W, gl[i:i + 1])
+            out, _, _ = ops.conv2d(tap, None, w_ptrs=wp, w_img_rows=tap.C, add=add)
+            return out
+
+        t4 = taps[CONTENT_TAP]
+        numel4 = t4.buf[0].numel()
+        cgrad = ops.mse_bwd(t4, ctx.content_target, gl[5:6], 2.0 / numel4)
+        if ctx.feat_mse is not None:
+            # d/dx [mse^2/numel] = 2*mse/numel * 2/numel * (relu x - relu t) * (x > 0)
+            ops.mse_bwd(t4, ctx.content_target, gl[6:7], 4.0 / (float(numel4) * float(numel4)), out=cgrad,
+                        relu=True, mul=ctx.feat_mse)
+        g5 = style_grad(4)
+        gp2, _, _ = ops.conv2d(g5, net.bwd[4])                                   # -> grad of pool2 output
+        g4 = ops.relu_maxpool_bwd(t4, gp2, add=style_grad(3, add=cgrad))         # -> grad of tap4
+        g3, _, _ = ops.conv2d(g4, net.bwd[3], mask=taps[2], add=style_grad(2))   # relu'(tap3) fused
+        gp1, _, _ = ops.conv2d(g3, net.bwd[2])
+        g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1))
+        g1, _, _ = ops.conv2d(g2, net.bwd[1], mask=taps[0], add=style_grad(0))
+        _, _, gx = ops.conv2d(g1, net.bwd[0], transposed=1, want_out=False, out_nchw_channels=ctx.in_shape[1])
+        ctx.taps = ctx.diffs = None
+        return gx, None, None, None, None
+
+
+def vgg_losses(x, net, style_targets, content_target, with_feature=True):
+    """losses[0:5] style nodes, [5] content node, [6] feature node (0 when skipped)."""
+    ops._require_cuda(x, 'vgg_losses')
+    return _VGGLossFn.apply(x.contiguous().float(), net, style_targets, content_target, with_feature)
