@@ -1,0 +1,151 @@
+"""CPU-only tests: the oracle against the committed golden vectors (= outputs of the
+unmodified reference), the C-ABI library's exported symbols, and host-side logic."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle, reference_shim
+from oracle.make_golden import grads_err, seeded
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + '.npz'))
+
+
+@pytest.mark.parametrize('name', ['gatys_64x64', 'gatys_40x56'])
+def test_oracle_gatys_vs_golden(golden_dir, name):
+    g = _load(golden_dir, name)
+    h, w = int(g['h']), int(g['w'])
+    vw = oracle.make_vgg_weights(1)
+    content, style = seeded((1, 3, h, w), 10), seeded((1, 3, h, w), 11)
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12)
+    targets = oracle.style_targets(style, vw)
+    total, grad, losses = oracle.gatys_closure(x0, content, targets, vw, float(g['sw']), float(g['cw']))
+    assert abs(total.item() - float(g['total'])) / float(g['total']) < 1e-5
+    assert np.allclose(losses.numpy(), g['losses'], rtol=1e-4, atol=0)
+    assert float((grad - torch.from_numpy(g['grad'])).norm() / torch.from_numpy(g['grad']).norm()) < 1e-4
+    assert np.allclose(targets[0].numpy(), g['style_target_gram0'], rtol=1e-4, atol=1e-7)
+
+
+def _check_grad_summary(g, grads):
+    floor = 1e-3 * max(float(g['gnorm/' + k]) for k in grads)
+    for k, v in grads.items():
+        n = float(g['gnorm/' + k])
+        assert abs(float(v.double().norm()) - n) <= 1e-3 * max(n, floor), k
+        head = torch.from_numpy(g['ghead/' + k])
+        assert float((v.reshape(-1)[:16] - head).norm()) <= 1e-3 * max(float(head.norm()), floor), k
+
+
+def test_oracle_fast_st_vs_golden(golden_dir):
+    g = _load(golden_dir, 'fast_st_b2_32')
+    b, s = int(g['b']), int(g['s'])
+    vw, params = oracle.make_vgg_weights(1), oracle.make_transform_params(2, 3)
+    style, batch = seeded((1, 3, s, s), 21), seeded((b, 3, s, s), 22)
+    total, grads, out, losses = oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw)
+    assert abs(total.item() - float(g['total'])) / float(g['total']) < 1e-5
+    assert np.allclose(out.numpy(), g['out'], rtol=1e-4, atol=1e-5)
+    _check_grad_summary(g, grads)
+
+
+def test_oracle_video_vs_golden(golden_dir):
+    g = _load(golden_dir, 'video_st_b2_32')
+    b, s = int(g['b']), int(g['s'])
+    vw, params = oracle.make_vgg_weights(1), oracle.make_transform_params(3, 6)
+    style, batch = seeded((1, 3, s, s), 31), seeded((b, 3, s, s), 32)
+    old_content, old_stylized = batch + 0.05 * seeded((b, 3, s, s), 33), seeded((b, 3, s, s), 34)
+    total, grads, out, _ = oracle.video_closure(batch, old_content, old_stylized, params,
+                                                oracle.style_targets(style, vw), vw, temporal_weight=float(g['tw']))
+    assert abs(total.item() - float(g['total'])) / float(g['total']) < 1e-5
+    assert np.allclose(out.numpy(), g['out'], rtol=1e-4, atol=1e-5)
+    _check_grad_summary(g, grads)
+
+
+@pytest.mark.skipif(not reference_shim.available(), reason='/root/reference not present (GPU box)')
+def test_oracle_vs_live_reference_single_pass_equivalence():
+    """F4: the reference's 7+2 prefix passes equal the oracle's single pass."""
+    ref = reference_shim.load_reference(vgg_seed=1)
+    vw = oracle.make_vgg_weights(1)
+    content, style = seeded((1, 3, 24, 40), 1), seeded((1, 3, 24, 40), 2)
+    net = ref.StyleNetwork(style, content)
+    x = (content + 0.2 * seeded((1, 3, 24, 40), 3)).requires_grad_(True)
+    net(x, content)
+    total = net.get_total_current_style_loss(weight=1e5) + net.get_total_current_content_loss(weight=1)
+    total.backward()
+    o_total, o_grad, _ = oracle.gatys_closure(x.detach(), content, oracle.style_targets(style, vw), vw)
+    assert abs(o_total.item() - total.item()) / total.item() < 1e-5
+    assert float((o_grad - x.grad).norm() / x.grad.norm()) < 1e-4
+    pieces = [[n for n, _ in p.named_children()] for p in net.net_pieces]
+    assert pieces[:6] == [['Conv2d_1'], ['ReLU_1', 'Conv2d_2'], ['ReLU_2', 'MaxPool2d_2', 'Conv2d_3'],
+                          ['ReLU_3', 'Conv2d_4'], ['ReLU_4'], ['MaxPool2d_4', 'Conv2d_5']]
+
+
+# ---------------------------------------------------------------------------
+# the C-ABI library: loads, exports every declared symbol (no compute without a GPU)
+# ---------------------------------------------------------------------------
+def _declared_symbols():
+    text = open(os.path.join(ROOT, 'include', 'stransfer_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(st_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from styletransfer_b200 import _lib, build
+    build.build()
+    handle = ctypes.CDLL(_lib.LIB_PATH)
+    declared = _declared_symbols()
+    assert len(declared) >= 24
+    for name in declared:
+        assert hasattr(handle, name), name
+    assert sorted(_lib.SIGNATURES) == declared          # the ctypes table mirrors the header 1:1
+    L = _lib.lib()
+    assert L.st_arch() == 100
+    # argument validation happens before any CUDA call
+    assert L.st_conv2d(None, None, 1, 8, 8, 8, 0, None, None, 8, 0, 3, 1, 1, 0, 8, 8, 8, 0,
+                       None, None, None, None, None, None, None, None, None, 0, None) == -1
+    assert b'null' in L.st_last_error()
+    assert L.st_instnorm_workspace_bytes(4, 128) > 0
+    assert L.st_gram_workspace_bytes(1, 512 * 512, 64) > 0
+
+
+def test_sass_has_blackwell_tensor_and_tma_instructions():
+    """The hot conv kernel must be tcgen05/TMA code, not a recompiled legacy path."""
+    import shutil
+    import subprocess
+    from styletransfer_b200 import _lib, build
+    build.build()
+    cuobjdump = shutil.which('cuobjdump') or '/usr/local/cuda/bin/cuobjdump'
+    if not os.path.exists(cuobjdump):
+        pytest.skip('cuobjdump not available')
+    sass = subprocess.run([cuobjdump, '-sass', _lib.LIB_PATH], capture_output=True, text=True).stdout
+    for mnemonic in ('UTCHMMA', 'UTMALDG', 'LDTM'):
+        assert mnemonic in sass, mnemonic
+
+
+# ---------------------------------------------------------------------------
+# host logic
+# ---------------------------------------------------------------------------
+def test_product_path_refuses_cpu_tensors():
+    from styletransfer_b200 import network
+    from styletransfer_b200._lib import StransferError
+    with pytest.raises(StransferError):
+        network.StyleNetwork(torch.zeros(1, 3, 16, 16))
+    with pytest.raises(StransferError):
+        network.StyleLoss(torch.zeros(1, 8, 4, 4))
+
+
+def test_latest_weights_lookup(tmp_path, monkeypatch):
+    from styletransfer_b200 import constants, network
+    monkeypatch.setattr(constants, 'PROJECT_ROOT_PATH', str(tmp_path))
+    os.makedirs(tmp_path / 'data' / 'models')
+    with pytest.raises(AssertionError):
+        network._load_latest_model_weigths('fast_st', 'wave.jpg')
+    for e in (1, 9, 10):
+        torch.save({'epoch': torch.tensor(e)}, tmp_path / 'data' / 'models' / f'fast_st_wave.jpg_epoch{e}.pth')
+    # lexicographic rule of the reference (network.py:65-67): epoch9 sorts last
+    assert int(network._load_latest_model_weigths('fast_st', 'wave.jpg')['epoch']) == 9

@@ -1,0 +1,158 @@
+"""Parity of the Gatys hot path (StyleNetwork forward+backward to the image) against
+the committed golden vectors (outputs of the UNMODIFIED reference, see
+oracle/make_golden.py) and against the CPU oracle on fresh seeded inputs.
+
+North-star tolerances: per-layer features and Gram matrices <= 1e-2
+relative L2; total loss and input gradient <= 1e-3 relative; PSNR >= 40 dB after
+100 L-BFGS steps."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle
+from tests.util import nhwc, rel_l2, seeded
+
+pytestmark = pytest.mark.gpu
+TOL_FEATURE, TOL_LOSS_GRAD = 1e-2, 1e-3
+
+
+@pytest.fixture(scope='module')
+def net_mod():
+    from styletransfer_b200 import network, ops
+    ops.set_precision('bf16x3')
+    return network
+
+
+def _vgg_cuda():
+    return [(w.cuda(), b.cuda()) for w, b in oracle.make_vgg_weights(1)]
+
+
+def _closure(network, content, style, x0, sw, cw):
+    net = network.StyleNetwork(style, content, vgg_weights=_vgg_cuda())
+    x = x0.clone().requires_grad_(True)
+    net(x, content)
+    total = net.get_total_current_style_loss(weight=sw) + net.get_total_current_content_loss(weight=cw)
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses])
+    return net, total.detach(), x.grad.detach(), per_node.detach()
+
+
+@pytest.mark.parametrize('name', ['gatys_64x64', 'gatys_40x56'])
+def test_closure_matches_reference_golden(net_mod, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name + '.npz'))
+    h, w = int(g['h']), int(g['w'])
+    content = seeded((1, 3, h, w), 10, device='cuda')
+    style = seeded((1, 3, h, w), 11, device='cuda')
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12, device='cuda')
+    net, total, grad, per_node = _closure(net_mod, content, style, x0, float(g['sw']), float(g['cw']))
+    assert abs(float(total) - float(g['total'])) / abs(float(g['total'])) < TOL_LOSS_GRAD
+    assert rel_l2(per_node, torch.from_numpy(g['losses'])) < TOL_LOSS_GRAD
+    assert rel_l2(grad, torch.from_numpy(g['grad'])) < TOL_LOSS_GRAD
+    assert rel_l2(net.style_losses[0][0].target, torch.from_numpy(g['style_target_gram0'])) < TOL_FEATURE
+
+
+def test_features_and_grams_match_oracle(net_mod):
+    from styletransfer_b200 import ops, vgg_loss
+    vw = oracle.make_vgg_weights(1)
+    x = seeded((2, 3, 48, 80), 70)
+    taps_ref = oracle.vgg_taps(x, vw)
+    prefix = vgg_loss.VGGPrefix(_vgg_cuda())
+    taps = prefix.taps(x.cuda())
+    for t, r in zip(taps, taps_ref):
+        assert rel_l2(nhwc(t), r) < TOL_FEATURE
+        assert rel_l2(ops.gram(t), oracle.gram_matrix(r)) < TOL_FEATURE
+
+
+def test_run_through_pieces_and_modules(net_mod):
+    vw = oracle.make_vgg_weights(1)
+    style, content = seeded((1, 3, 32, 32), 71), seeded((1, 3, 32, 32), 72)
+    net = net_mod.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
+    taps = oracle.vgg_taps(content, vw)
+    for piece, ref in [(0, taps[0]), (1, taps[1]), (2, taps[2]), (3, taps[3]), (4, torch.relu(taps[3])), (5, taps[4])]:
+        assert rel_l2(net.run_through_pieces(content.cuda(), piece), ref) < TOL_FEATURE
+    with pytest.raises(NotImplementedError):
+        net.run_through_pieces(content.cuda())
+    # stand-alone loss modules with autograd (network.py:79-201)
+    f = seeded((2, 64, 12, 20), 73)
+    tgt = seeded((1, 64, 12, 20), 74)
+    fr = f.clone().requires_grad_(True)
+    lref = oracle.style_loss(fr, oracle.gram_matrix(tgt))
+    lref.backward()
+    sl = net_mod.StyleLoss(tgt.cuda())
+    fc = f.cuda().requires_grad_(True)
+    assert sl(fc) is fc
+    sl.loss.backward()
+    assert abs(float(sl.loss) - float(lref)) / float(lref) < TOL_LOSS_GRAD
+    assert rel_l2(fc.grad, fr.grad) < TOL_LOSS_GRAD
+    for cls, fn in [(net_mod.ContentLoss, oracle.content_loss), (net_mod.FeatureReconstructionLoss, oracle.feature_loss)]:
+        fr = f.clone().requires_grad_(True)
+        tgt2 = seeded((2, 64, 12, 20), 75)
+        lref = fn(fr, tgt2)
+        lref.backward()
+        m = cls(tgt2.cuda())
+        fc = f.cuda().requires_grad_(True)
+        m(fc)
+        m.loss.backward()
+        assert abs(float(m.loss) - float(lref)) / float(lref) < TOL_LOSS_GRAD
+        assert rel_l2(fc.grad, fr.grad) < TOL_LOSS_GRAD
+
+
+def test_feature_loss_gradient_path(net_mod):
+    """static_test uses the feature node (network.py:788-791); check its value + gradient."""
+    vw = oracle.make_vgg_weights(1)
+    content, style = seeded((1, 3, 32, 48), 76), seeded((1, 3, 32, 48), 77)
+    x0 = seeded((1, 3, 32, 48), 78)
+    xr = x0.clone().requires_grad_(True)
+    losses, _ = oracle.loss_network(xr, content, oracle.style_targets(style, vw), vw)
+    (1e5 * losses[:5].sum() + 1e9 * losses[6]).backward()
+    net = net_mod.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
+    x = x0.cuda().requires_grad_(True)
+    net(x, content.cuda())
+    tot = net.get_total_current_style_loss(1e5) + net.get_total_current_feature_loss(1e9)
+    tot.backward()
+    assert rel_l2(net.feature_losses[0][0].loss, losses[6]) < TOL_LOSS_GRAD
+    assert rel_l2(x.grad, xr.grad) < TOL_LOSS_GRAD
+
+
+def test_lbfgs_100_steps_psnr(net_mod):
+    """100 L-BFGS steps (train_gatys, network.py:411-458) vs the same loop on the CPU oracle."""
+    vw = oracle.make_vgg_weights(1)
+    s = 32
+    content, style = seeded((1, 3, s, s), 80), seeded((1, 3, s, s), 81)
+    targets = oracle.style_targets(style, vw)
+    xr = content.clone().requires_grad_(True)
+    opt = torch.optim.LBFGS([xr])
+    for _ in range(100):
+        def closure():
+            opt.zero_grad()
+            losses, _ = oracle.loss_network(xr, content, targets, vw)
+            total = 1e5 * losses[:5].sum() + losses[5]
+            total.backward()
+            return total
+        opt.step(closure)
+    net = net_mod.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
+    out = net.train_gatys(style.cuda(), content.cuda(), steps=100)
+    mse = float(((out.detach().cpu() - xr.detach()) ** 2).mean())
+    peak = float(xr.detach().max() - xr.detach().min())
+    psnr = 10 * math.log10(peak * peak / max(mse, 1e-30))
+    assert psnr >= 40.0, psnr
+
+
+def test_full_size_properties(net_mod):
+    """512x512 (BASELINE configs[1]): size-independent properties -- the loss of the
+    content image against itself has zero content term, the gradient is finite, and
+    two evaluations are bit-identical (deterministic reductions)."""
+    content, style = seeded((1, 3, 512, 512), 90, device='cuda'), seeded((1, 3, 512, 512), 91, device='cuda')
+    net, total, grad, per_node = _closure(net_mod, content, style, content, 1e5, 1.0)
+    assert float(per_node[5]) == 0.0
+    assert torch.isfinite(grad).all() and float(grad.abs().max()) > 0
+    _, total2, grad2, _ = _closure(net_mod, content, style, content, 1e5, 1.0)
+    assert float(total) == float(total2) and torch.equal(grad, grad2)
+    # linearity of backward in the loss weights: grad(2*sw, 2*cw) == 2*grad(sw, cw)
+    x0 = content + 0.1 * style
+    _, _, g1, _ = _closure(net_mod, content, style, x0, 1e5, 1.0)
+    _, _, g2, _ = _closure(net_mod, content, style, x0, 2e5, 2.0)
+    assert rel_l2(g2, 2 * g1) < 1e-4

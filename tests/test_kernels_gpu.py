@@ -1,0 +1,222 @@
+"""Per-kernel parity: each C-ABI entry point against a plain PyTorch fp32 op on the
+same GPU (TF32 off).  Tolerances: split-bf16 storage carries ~16 mantissa bits, so
+rel-L2 <= 1e-4 on single ops in bf16x3 mode (north star: features/Grams <= 1e-2)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from tests.util import fp32_reference_mode, nhwc, rel_l2, seeded
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+@pytest.fixture(scope='module')
+def ops():
+    fp32_reference_mode()
+    from styletransfer_b200 import _lib, ops as o
+    _lib.lib()
+    o.set_precision('bf16x3')
+    return o
+
+
+def test_layout_roundtrip(ops):
+    x = seeded((2, 3, 20, 36), 1, device='cuda')
+    s = ops.from_nchw(x)
+    assert s.shape == (2, 20, 36, 8)
+    assert rel_l2(nhwc(s, 3), x) < 1e-5
+    assert float(nhwc(s)[:, 3:].abs().max()) == 0.0
+    assert rel_l2(ops.to_nchw(s, 3), x) < 1e-5
+    a, b = seeded((1, 3, 8, 8), 2, device='cuda'), seeded((1, 3, 8, 8), 3, device='cuda')
+    s2 = ops.from_nchw(a, b)                      # channel concat (video net input)
+    assert rel_l2(nhwc(s2, 6), torch.cat([a, b], 1)) < 1e-5
+
+
+def _conv_case(ops, N, H, W, cin, cout, ks, stride, path, relu=True, up=0, seed=0):
+    from styletransfer_b200 import _lib
+    _lib.lib().st_set_conv_path(path)
+    try:
+        x = seeded((N, cin, H, W), seed + 1, device='cuda')
+        w = seeded((cout, cin, ks, ks), seed + 2, 1.0 / (cin * ks * ks) ** 0.5, device='cuda')
+        b = seeded((cout,), seed + 3, 0.1, device='cuda')
+        xs = ops.from_nchw(x)
+        pw = ops.PackedWeight(w, 0, cols_pad=xs.C)
+        out, rl, _ = ops.conv2d(xs, pw, b, stride=stride, up=up, want_relu=relu)
+        xin = F.interpolate(x, scale_factor=2, mode='nearest') if up else x
+        ref = F.conv2d(xin, w, b, stride=stride, padding=ks // 2)
+        e = rel_l2(nhwc(out, cout), ref)
+        er = rel_l2(nhwc(rl, cout), F.relu(ref)) if relu else 0.0
+        return max(e, er)
+    finally:
+        _lib.lib().st_set_conv_path(0)
+
+
+@pytest.mark.parametrize('cin,cout,ks,stride,up', [
+    (3, 64, 3, 1, 0), (3, 32, 9, 1, 0), (6, 32, 9, 1, 0), (32, 64, 3, 2, 0), (64, 128, 3, 2, 0),
+    (32, 3, 9, 1, 0), (128, 64, 3, 1, 1), (64, 32, 3, 1, 1), (64, 64, 3, 1, 0)])
+def test_conv_generic(ops, cin, cout, ks, stride, up):
+    assert _conv_case(ops, 2, 20, 28, cin, cout, ks, stride, path=1, up=up) < TOL
+
+
+@pytest.mark.parametrize('cin,cout,H,W', [
+    (64, 64, 16, 32), (64, 64, 20, 36), (64, 128, 24, 40), (128, 128, 8, 16),
+    (128, 256, 12, 20), (128, 64, 16, 16), (64, 32, 16, 48), (128, 128, 33, 17)])
+def test_conv_tcgen05_3x3(ops, cin, cout, H, W):
+    assert _conv_case(ops, 2, H, W, cin, cout, 3, 1, path=0) < TOL
+
+
+def test_conv_tcgen05_many_tiles(ops):
+    # more work items than SMs: exercises the persistent loop, both TMEM accumulators
+    # and every pipeline phase wrap
+    assert _conv_case(ops, 3, 96, 160, 64, 64, 3, 1, path=0) < TOL
+    assert _conv_case(ops, 1, 64, 128, 128, 256, 3, 1, path=0) < TOL
+
+
+def test_conv_tcgen05_plain_bf16(ops):
+    ops.set_precision('bf16')
+    try:
+        assert _conv_case(ops, 1, 16, 32, 64, 64, 3, 1, path=0) < 1e-2
+    finally:
+        ops.set_precision('bf16x3')
+
+
+@pytest.mark.parametrize('cin,cout,ks,stride,path', [
+    (64, 64, 3, 1, 0), (128, 256, 3, 1, 0), (64, 128, 3, 1, 0), (3, 64, 3, 1, 1),
+    (32, 64, 3, 2, 1), (64, 128, 3, 2, 1), (32, 3, 9, 1, 1), (3, 32, 9, 1, 1)])
+def test_conv_dgrad(ops, cin, cout, ks, stride, path):
+    """backward-data with the fused epilogue: gx = dgrad(gy) * (tap > 0) + add"""
+    N, H, W = 2, 16, 32
+    Ho, Wo = (H + 2 * (ks // 2) - ks) // stride + 1, (W + 2 * (ks // 2) - ks) // stride + 1
+    w = seeded((cout, cin, ks, ks), 5, 1.0 / (cin * ks * ks) ** 0.5, device='cuda')
+    gy = seeded((N, cout, Ho, Wo), 6, device='cuda')
+    x = seeded((N, cin, H, W), 7, device='cuda').requires_grad_(True)
+    F.conv2d(x, w, None, stride=stride, padding=ks // 2).backward(gy)
+    gys = ops.from_nchw(gy)
+    cin_pad = ops.pad8(cin)
+    if path == 0:
+        pw = ops.PackedWeight(w, 2, rows_pad=cin_pad, cols_pad=gys.C)
+        tap = seeded((N, cin, H, W), 8, device='cuda')
+        add = seeded((N, cin, H, W), 9, device='cuda')
+        out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=ops.from_nchw(add))
+        ref = x.grad * (tap > 0) + add
+        assert rel_l2(nhwc(out, cin), ref) < TOL
+    else:
+        pw = ops.PackedWeight(w, 1, rows_pad=cin_pad, cols_pad=gys.C)
+        out, _, nchw = ops.conv2d(gys, pw, stride=stride, transposed=1, out_hw=(H, W), out_nchw_channels=cin)
+        assert rel_l2(nhwc(out, cin), x.grad) < TOL
+        assert rel_l2(nchw, x.grad) < TOL
+
+
+@pytest.mark.parametrize('cin,cout,ks,stride,up', [
+    (128, 128, 3, 1, 0), (3, 32, 9, 1, 0), (32, 64, 3, 2, 0), (128, 64, 3, 1, 1), (32, 3, 9, 1, 0)])
+def test_conv_wgrad(ops, cin, cout, ks, stride, up):
+    N, H, W = 2, 12, 20
+    x = seeded((N, cin, H, W), 11, device='cuda')
+    w = seeded((cout, cin, ks, ks), 12, 0.05, device='cuda').requires_grad_(True)
+    b = torch.zeros(cout, device='cuda', requires_grad=True)
+    xin = F.interpolate(x, scale_factor=2, mode='nearest') if up else x
+    y = F.conv2d(xin, w, b, stride=stride, padding=ks // 2)
+    gy = seeded(tuple(y.shape), 13, device='cuda')
+    y.backward(gy)
+    dw, db = ops.conv2d_wgrad(ops.from_nchw(gy), ops.from_nchw(x), ks, stride, ks // 2, up, cout, cin)
+    assert rel_l2(dw, w.grad) < TOL
+    assert rel_l2(db, b.grad) < TOL
+
+
+@pytest.mark.parametrize('H,W', [(16, 32), (15, 21)])
+def test_relu_maxpool(ops, H, W):
+    x = seeded((2, 64, H, W), 21, device='cuda').requires_grad_(True)
+    y = F.max_pool2d(F.relu(x), 2, 2)
+    gy = seeded(tuple(y.shape), 22, device='cuda')
+    y.backward(gy)
+    xs = ops.from_nchw(x.detach())
+    ys = ops.relu_maxpool_fwd(xs)
+    # the pooled value is rounded to split-bf16 twice (input and output)
+    assert rel_l2(nhwc(ys), y) < 1e-5
+    add = seeded((2, 64, H, W), 23, device='cuda')
+    gx = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=ops.from_nchw(add))
+    assert rel_l2(nhwc(gx), x.grad + add) < 1e-5
+
+
+@pytest.mark.parametrize('B,C,H,W', [(1, 64, 32, 32), (2, 128, 20, 12), (3, 256, 9, 7), (1, 64, 128, 128)])
+def test_gram_and_style_loss(ops, B, C, H, W):
+    f = seeded((B, C, H, W), 31, device='cuda').requires_grad_(True)
+    T = seeded((1, C, C), 32, 0.01, device='cuda')
+    G = torch.bmm(f.view(B, C, -1), f.view(B, C, -1).transpose(1, 2)) / (C * H * W)
+    loss = F.mse_loss(G, T.expand_as(G))
+    loss.backward()
+    fs = ops.from_nchw(f.detach())
+    Gk = ops.gram(fs)
+    assert rel_l2(Gk, G) < TOL
+    lk = torch.zeros(1, device='cuda')
+    diff = ops.style_mse_fwd(Gk, T, lk)
+    assert abs(float(lk) - float(loss)) / float(loss) < 1e-4
+    gw = torch.tensor([1.0], device='cuda')
+    _buf, wp = ops.style_seed(diff, H * W, gw)
+    dF, _, _ = ops.conv2d(fs, None, w_ptrs=wp, w_img_rows=C)
+    assert rel_l2(nhwc(dF), f.grad) < 2e-4
+
+
+def test_mse(ops):
+    x = seeded((2, 128, 10, 12), 41, device='cuda').requires_grad_(True)
+    t = seeded((2, 128, 10, 12), 42, device='cuda')
+    loss = F.mse_loss(x, t)
+    loss.backward()
+    xs, ts = ops.from_nchw(x.detach()), ops.from_nchw(t)
+    lk = torch.zeros(1, device='cuda')
+    ops.mse_fwd(xs, ts, lk)
+    assert abs(float(lk) - float(loss)) / float(loss) < 1e-5
+    g = ops.mse_bwd(xs, ts, torch.tensor([3.0], device='cuda'), 2.0 / x.numel())
+    assert rel_l2(nhwc(g), 3.0 * x.grad) < 1e-5
+    # FeatureReconstructionLoss form on relu'd maps (network.py:186-201)
+    x2 = x.detach().clone().requires_grad_(True)
+    l2 = F.mse_loss(F.relu(x2), F.relu(t)).pow(2) / x2.numel()
+    l2.backward()
+    ops.mse_fwd(xs, ts, lk, relu=True, feature_form=True)
+    assert abs(float(lk) - float(l2)) / float(l2) < 1e-4
+    mse = torch.zeros(1, device='cuda')
+    ops.mse_fwd(xs, ts, mse, relu=True)
+    n = float(x.numel())
+    g2 = ops.mse_bwd(xs, ts, torch.tensor([1.0], device='cuda'), 4.0 / (n * n), relu=True, mul=mse)
+    assert rel_l2(nhwc(g2), x2.grad) < 1e-4
+
+
+@pytest.mark.parametrize('C,H,W,relu,up', [(32, 16, 24, True, False), (128, 8, 8, False, True),
+                                           (64, 12, 20, True, True), (128, 7, 9, False, False)])
+def test_instance_norm(ops, C, H, W, relu, up):
+    N = 3
+    x = seeded((N, C, H, W), 51, device='cuda').requires_grad_(True)
+    gamma = (1 + 0.1 * seeded((C,), 52, device='cuda')).requires_grad_(True)
+    beta = (0.1 * seeded((C,), 53, device='cuda')).requires_grad_(True)
+    y = F.instance_norm(x, None, None, gamma, beta, True, 0.0, 1e-5)
+    if relu:
+        y = F.relu(y)
+    if up:
+        y = F.interpolate(y, scale_factor=2, mode='nearest')
+    gy = seeded(tuple(y.shape), 54, device='cuda')
+    y.backward(gy)
+    xs = ops.from_nchw(x.detach())
+    ys, stats = ops.instnorm_fwd(xs, gamma.detach(), beta.detach(), relu=relu, up=up)
+    assert rel_l2(nhwc(ys), y) < 1e-4
+    dx, dg, db = ops.instnorm_bwd(xs, ops.from_nchw(gy), stats, gamma.detach(), beta.detach(), relu=relu, up=up)
+    assert rel_l2(nhwc(dx), x.grad) < 2e-4
+    assert rel_l2(dg, gamma.grad) < 2e-4
+    assert rel_l2(db, beta.grad) < 2e-4
+
+
+def test_tv_and_temporal(ops):
+    x = seeded((2, 3, 17, 23), 61, device='cuda').requires_grad_(True)
+    tv = 1e-6 * ((x[:, :, :, :-1] - x[:, :, :, 1:]).abs().sum() + (x[:, :, :-1, :] - x[:, :, 1:, :]).abs().sum())
+    tv.backward()
+    lk = ops.tv_fwd(x.detach(), 1e-6)
+    assert abs(float(lk) - float(tv)) / float(tv) < 1e-5
+    g = ops.tv_bwd(x.detach(), 1e-6, torch.tensor([2.0], device='cuda'))
+    assert rel_l2(g, 2.0 * x.grad) < 1e-6
+    oc, os_, cc = (seeded((2, 3, 17, 23), s, device='cuda') for s in (62, 63, 64))
+    cs = seeded((2, 3, 17, 23), 65, device='cuda').requires_grad_(True)
+    tl = ((cs - os_).norm() / ((cc - oc).norm() + 1)) * 0.8
+    tl.backward()
+    out3 = ops.temporal_fwd(oc, os_, cc, cs.detach(), 0.8)
+    assert abs(float(out3[0]) - float(tl)) / float(tl) < 1e-5
+    g = ops.temporal_bwd(os_, cs.detach(), 0.8, out3, torch.tensor([1.0], device='cuda'))
+    assert rel_l2(g, cs.grad) < 1e-5
