@@ -38,6 +38,8 @@ int st_arch(void);
 const char* st_last_error(void);
 /* 0 = auto (tcgen05 where eligible), 1 = force the generic mma.sync conv (testing) */
 int st_set_conv_path(int path);
+/* number of kernels this library has launched so far in this process */
+long long st_launch_count(void);
 
 /* ---- layout / packing ------------------------------------------------- */
 /* img_utils/torch.cat boundary: NCHW fp32 (optionally two tensors concatenated on

@@ -9,6 +9,7 @@ void st_set_error(const char* fmt, ...) {
     va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
 }
 static int g_conv_path = 0;
+long long g_st_launches = 0;
 
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
@@ -48,6 +49,7 @@ extern "C" {
 int st_arch(void) { return 100; }
 const char* st_last_error(void) { return g_err; }
 int st_set_conv_path(int path) { g_conv_path = path; return ST_OK; }
+long long st_launch_count(void) { return g_st_launches; }
 
 int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int N, int C1, int C2, int H, int W, int Cpad, void* stream) {
     ST_CHECK_ARG(a && hi && N > 0 && H > 0 && W > 0, "st_nchw_to_nhwc: null pointer or empty shape");

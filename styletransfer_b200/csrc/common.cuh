@@ -23,8 +23,9 @@ void st_set_error(const char* fmt, ...);
 #define ST_ERR_UNSUPPORTED (-3)
 #define ST_CHECK_ARG(cond, ...)                                   \
     do { if (!(cond)) { st_set_error(__VA_ARGS__); return ST_ERR_INVALID; } } while (0)
+extern long long g_st_launches;      // kernels launched by this library (st_launch_count)
 #define ST_CHECK_LAUNCH(name)                                                       \
-    do { cudaError_t e_ = cudaGetLastError();                                       \
+    do { ++g_st_launches; cudaError_t e_ = cudaGetLastError();                                       \
          if (e_ != cudaSuccess) { st_set_error("%s: %s", name, cudaGetErrorString(e_)); \
                                   return ST_ERR_CUDA; } } while (0)
 

@@ -13,7 +13,7 @@ import pytest
 import torch
 
 from oracle import oracle
-from tests.util import nhwc, rel_l2, seeded
+from tests.util import nhwc, record, rel_l2, seeded
 
 pytestmark = pytest.mark.gpu
 TOL_FEATURE, TOL_LOSS_GRAD = 1e-2, 1e-3
@@ -50,7 +50,8 @@ def test_closure_matches_reference_golden(net_mod, golden_dir, name):
     net, total, grad, per_node = _closure(net_mod, content, style, x0, float(g['sw']), float(g['cw']))
     assert abs(float(total) - float(g['total'])) / abs(float(g['total'])) < TOL_LOSS_GRAD
     assert rel_l2(per_node, torch.from_numpy(g['losses'])) < TOL_LOSS_GRAD
-    assert rel_l2(grad, torch.from_numpy(g['grad'])) < TOL_LOSS_GRAD
+    assert record(name + '/grad_rel_l2', rel_l2(grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
+    record(name + '/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total'])))
     assert rel_l2(net.style_losses[0][0].target, torch.from_numpy(g['style_target_gram0'])) < TOL_FEATURE
 
 
@@ -62,8 +63,8 @@ def test_features_and_grams_match_oracle(net_mod):
     prefix = vgg_loss.VGGPrefix(_vgg_cuda())
     taps = prefix.taps(x.cuda())
     for t, r in zip(taps, taps_ref):
-        assert rel_l2(nhwc(t), r) < TOL_FEATURE
-        assert rel_l2(ops.gram(t), oracle.gram_matrix(r)) < TOL_FEATURE
+        assert record('tap_rel_l2', rel_l2(nhwc(t), r)) < TOL_FEATURE
+        assert record('gram_rel_l2', rel_l2(ops.gram(t), oracle.gram_matrix(r))) < TOL_FEATURE
 
 
 def test_run_through_pieces_and_modules(net_mod):
@@ -114,7 +115,7 @@ def test_feature_loss_gradient_path(net_mod):
     tot = net.get_total_current_style_loss(1e5) + net.get_total_current_feature_loss(1e9)
     tot.backward()
     assert rel_l2(net.feature_losses[0][0].loss, losses[6]) < TOL_LOSS_GRAD
-    assert rel_l2(x.grad, xr.grad) < TOL_LOSS_GRAD
+    assert record('feature_path/grad_rel_l2', rel_l2(x.grad, xr.grad)) < TOL_LOSS_GRAD
 
 
 def test_lbfgs_100_steps_psnr(net_mod):
@@ -138,6 +139,7 @@ def test_lbfgs_100_steps_psnr(net_mod):
     mse = float(((out.detach().cpu() - xr.detach()) ** 2).mean())
     peak = float(xr.detach().max() - xr.detach().min())
     psnr = 10 * math.log10(peak * peak / max(mse, 1e-30))
+    record('lbfgs100/psnr_db', psnr)
     assert psnr >= 40.0, psnr
 
 

@@ -142,6 +142,7 @@ def test_relu_maxpool(ops, H, W):
 def test_gram_and_style_loss(ops, B, C, H, W):
     f = seeded((B, C, H, W), 31, device='cuda').requires_grad_(True)
     T = seeded((1, C, C), 32, 0.01, device='cuda')
+    T = 0.5 * (T + T.transpose(1, 2))            # Gram targets are symmetric (the backward relies on it)
     G = torch.bmm(f.view(B, C, -1), f.view(B, C, -1).transpose(1, 2)) / (C * H * W)
     loss = F.mse_loss(G, T.expand_as(G))
     loss.backward()

@@ -22,3 +22,19 @@ def fp32_reference_mode():
     """Make torch's own GPU ops a trustworthy fp32 reference (no TF32)."""
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
+
+
+def record(name, value):
+    """Append a measured error to gpurun_out/parity.jsonl (evidence of the margins;
+    travels back from the GPU box).  Never fails a test."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = os.path.join(root, 'gpurun_out')
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, 'parity.jsonl'), 'a') as f:
+            f.write(json.dumps({'name': name, 'value': float(value)}) + '\n')
+    except OSError:
+        pass
+    return value
