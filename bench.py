@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""Benchmark of the stransfer.network hot path on B200 (contract: see the task brief).
+
+Headline metric (BASELINE.json, configs[1]): Gatys VGG-19 forward+backward closures per
+second at 512x512, one content/style pair per GPU (N GPUs = N independent pairs, no
+collective, weak scaling).  A "step" is one closure of train_gatys
+(reference network.py:438-454): zero_grad -> StyleNetwork.forward -> 1e5*style + content
+-> backward to the image.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SIZE = 512
+STYLE_WEIGHT, CONTENT_WEIGHT = 100_000.0, 1.0
+# algorithmic work of one closure at SxS, batch 1
+GF_PREFIX_FWD = 224_640 * SIZE * SIZE / 1e9          # 58.89 GF @512
+GF_GRAM = 40_960 * SIZE * SIZE / 1e9                 # 10.74 GF @512 (fwd; bwd the same)
+GF_CLOSURE = 2 * GF_PREFIX_FWD + 2 * GF_GRAM         # 139.25 GF @512
+
+
+def seeded(shape, seed):
+    return torch.randn(*shape, generator=torch.Generator().manual_seed(seed))
+
+
+def peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(hbm=p['hbm_gbs'], tf_burst=p['bf16_tflops'], tf_sustained=p['bf16_tflops_sustained'], src='measured')
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src='fallback')
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
+                                       '--format=csv,noheader,nounits', '-lms', '100'], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f:
+            parts = [x.strip() for x in line.split(',')]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), parts[2:6]):
+                if val.lower().startswith('active'):
+                    reasons.add(name)
+        self.f.close()
+        os.unlink(self.f.name)
+        return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def cpu_reference_closure_rate(budget_s, max_steps, warmup=1):
+    """The reference's CPU path (as-executed port, oracle.gatys_closure_as_executed) on the
+    host cores: closures/s at 512x512 on a bounded number of closures."""
+    from oracle import oracle
+    torch.set_num_threads(os.cpu_count() or 1)
+    vw = oracle.make_vgg_weights(1)
+    content, style = seeded((1, 3, SIZE, SIZE), 100), seeded((1, 3, SIZE, SIZE), 101)
+    targets = oracle.style_targets(style, vw)
+    x = content.clone()
+    t0 = time.perf_counter()
+    for _ in range(warmup):
+        oracle.gatys_closure_as_executed(x, content, targets, vw, STYLE_WEIGHT, CONTENT_WEIGHT)
+    per = (time.perf_counter() - t0) / max(warmup, 1)
+    n = int(max(1, min(max_steps, budget_s / max(per, 1e-3))))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        oracle.gatys_closure_as_executed(x, content, targets, vw, STYLE_WEIGHT, CONTENT_WEIGHT)
+    dt = time.perf_counter() - t0
+    return n / dt, n, torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    rate, n, cores = cpu_reference_closure_rate(budget_s=150.0, max_steps=args.steps, warmup=min(args.warmup, 2) or 1)
+    sample = (f'{n} closures of the 512x512 Gatys closure, as executed by the reference (7+2 VGG prefix passes, '
+              f'VGG wgrad), fp32 torch CPU port of network.py:438-454 (the Python reference cannot travel to the GPU box)')
+    line = {'impl': 'reference', 'metric': 'gatys_vgg19_fwd_bwd_closures_per_s_512', 'value': rate, 'unit': 'it/s',
+            'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1000.0 / rate,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'gatys_st 512x512 single pair, closure fwd+bwd (configs[1])', 'size': SIZE,
+                       'timed_closures': n},
+            'cpu_baseline': {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': rate, 'unit': 'it/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line))
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device -- the product path has no CPU fallback')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    from styletransfer_b200 import _lib, network, ops
+    L = _lib.lib()
+    ops.set_precision(args.precision)
+
+    # one independent content/style pair per rank (BASELINE configs[1]: no communication)
+    content = seeded((1, 3, SIZE, SIZE), 100 + 10 * rank).to(dev)
+    style = seeded((1, 3, SIZE, SIZE), 101 + 10 * rank).to(dev)
+    net = network.StyleNetwork(style, content, vgg_weights=network.load_vgg19_prefix_weights(seed=1))
+    net.compute_feature_loss = False           # train_gatys never reads the feature node
+    x = content.clone().requires_grad_(True)
+
+    def closure():
+        x.grad = None
+        net(x, content)
+        total = (net.get_total_current_style_loss(weight=STYLE_WEIGHT) +
+                 net.get_total_current_content_loss(weight=CONTENT_WEIGHT))
+        total.backward()
+        return total
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t)
+        return ms
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    for _ in range(max(args.warmup, 3)):
+        closure()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    n0 = L.st_launch_count()
+    ms = timed(closure, args.steps)
+    launches = L.st_launch_count() - n0
+    clocks = sampler.stop() if sampler else None
+
+    # ---- end to end: host image in pinned memory -> closure -> loss back on the host ----
+    host_img = content.detach().cpu().pin_memory()
+    host_loss = torch.zeros(1).pin_memory()
+
+    def e2e_step():
+        with torch.no_grad():
+            x.copy_(host_img, non_blocking=True)
+        host_loss.copy_(closure().detach().reshape(1), non_blocking=False)
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+
+    # ---- roofline of the dominant kernel: CUDA events around every tcgen05 conv launch ----
+    records = []
+    real_conv2d = ops.conv2d
+
+    def traced_conv2d(xs, w, *a, **k):
+        ks = w.ks if w is not None else k['w_ptrs'][3]
+        cin = xs.C
+        cout = w.rows if w is not None else k['w_img_rows']
+        tc = ks in (1, 3) and k.get('stride', 1) == 1 and not k.get('up') and not k.get('transposed') and cin % 64 == 0
+        if not tc:
+            return real_conv2d(xs, w, *a, **k)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = real_conv2d(xs, w, *a, **k)
+        e1.record()
+        records.append((ks, cin, cout, 2.0 * xs.N * xs.H * xs.W * cin * cout * ks * ks, e0, e1))
+        return out
+    ops.conv2d = traced_conv2d
+    torch.cuda.synchronize()
+    for _ in range(args.steps):
+        closure()
+    torch.cuda.synchronize()
+    ops.conv2d = real_conv2d
+    groups = {}
+    for ks, cin, cout, fl, e0, e1 in records:
+        g = groups.setdefault(f'conv_tc_kernel<{ks}x{ks}> {cin}->{cout}', [0.0, 0.0, 0])
+        g[0] += fl; g[1] += e0.elapsed_time(e1); g[2] += 1
+    pk = peaks()
+    fl3 = sum(g[0] for k, g in groups.items() if '<3x3>' in k)
+    ms3 = sum(g[1] for k, g in groups.items() if '<3x3>' in k)
+    n3 = sum(g[2] for k, g in groups.items() if '<3x3>' in k)
+    passes = 3 if args.precision == 'bf16x3' else 1
+    achieved = fl3 / (ms3 * 1e-3) / 1e12 if ms3 > 0 else 0.0
+    roofline = {'bound': 'tensor', 'kernel': 'conv_tc_kernel<3x3> (8 launches per closure: 4 fwd + 4 dgrad)',
+                'achieved': achieved, 'peak': pk['tf_sustained'], 'unit': 'TFLOP/s', 'frac': achieved / pk['tf_sustained'],
+                'peak_source': pk['src'] + ' bf16_tflops_sustained', 'traffic': None,
+                'avg_launch_ms': ms3 / max(n3, 1), 'algorithmic_gflop_per_launch': fl3 / max(n3, 1) / 1e9,
+                'mma_passes_per_product': passes, 'issued_frac': achieved * passes / pk['tf_sustained'],
+                'share_of_step': (ms3 / args.steps) / (ms / args.steps)}
+    per_kernel = {k: {'tflops': g[0] / (g[1] * 1e-3) / 1e12, 'ms_per_launch': g[1] / g[2], 'launches_per_step': g[2] / args.steps}
+                  for k, g in sorted(groups.items())}
+
+    if rank != 0:
+        return
+    value = world * args.steps / (ms * 1e-3)
+    e2e_value = world * args.steps / (ms_e2e * 1e-3)
+    line = {'metric': 'gatys_vgg19_fwd_bwd_closures_per_s_512', 'value': value, 'unit': 'it/s', 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'bf16x3 (split-bf16 operands, 3 tcgen05 passes, fp32 accumulate)' if passes == 3 else 'bf16',
+            'data': 'synthetic',
+            'config': {'workload': 'gatys_st 512x512 single pair per GPU, closure fwd+bwd (BASELINE configs[1])',
+                       'size': SIZE, 'pairs': world, 'parallelism': f'{world} independent pairs, no collective',
+                       'l2': 'working set ~1.5 GB per closure >> 126 MB L2 (no flush needed)',
+                       'algorithmic_gflop_per_step': GF_CLOSURE},
+            'tflops_algorithmic': value / world * GF_CLOSURE / 1e3,
+            'e2e': {'value': e2e_value, 'unit': 'it/s', 'h2d_bytes_per_step': host_img.numel() * 4, 'd2h_bytes_per_step': 4,
+                    'ms_per_step': ms_e2e / args.steps},
+            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'kernels': per_kernel}
+    if world == 1 and not args.no_cpu_baseline:
+        rate, n, cores = cpu_reference_closure_rate(budget_s=20.0, max_steps=8, warmup=1)
+        line['cpu_baseline'] = {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port',
+                                'sample': f'{n} closures at 512x512 of the as-executed reference closure '
+                                          f'(oracle.gatys_closure_as_executed, torch fp32 CPU)'}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--precision', default='bf16x3', choices=['bf16x3', 'bf16'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local_rank = int(os.environ.get('LOCAL_RANK', 0))
+    if args.impl == 'reference':
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == '__main__':
+    main()

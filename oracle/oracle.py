@@ -241,3 +241,26 @@ def video_closure(batch, old_content, old_stylized, params, targets, vgg_w,
              temporal_loss(old_content, old_stylized, batch, out, temporal_weight))
     total.backward()
     return total.detach(), {k: v.grad.detach() for k, v in ps.items()}, out.detach(), losses.detach()
+
+
+def gatys_closure_as_executed(x, content_image, targets, weights,
+                              style_weight=100_000.0, content_weight=1.0):
+    """The closure of train_gatys exactly AS THE REFERENCE EXECUTES IT: every loss
+    node re-runs the VGG prefix from the image (network.py:378-398: content +
+    feature node on the input and on the content image, then five style nodes =
+    7 + 2 prefix passes), and the VGG weights carry requires_grad so
+    autograd also computes their (unused) gradients.  Numerically equal
+    to gatys_closure; used as the timed CPU baseline."""
+    ws = [(w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)) for w, b in weights]
+    x = x.detach().clone().requires_grad_(True)
+    node_losses = []
+    # content node (piece 3) and feature node (piece 4): targets reset from content_image
+    ctarget = vgg_taps(content_image, ws, upto=CONTENT_TAP + 1)[CONTENT_TAP].detach()
+    closs = content_loss(vgg_taps(x, ws, upto=CONTENT_TAP + 1)[CONTENT_TAP], ctarget)
+    ftarget = F.relu(vgg_taps(content_image, ws, upto=FEATURE_TAP + 1)[FEATURE_TAP]).detach()
+    floss = feature_loss(F.relu(vgg_taps(x, ws, upto=FEATURE_TAP + 1)[FEATURE_TAP]), ftarget)
+    for i in range(5):
+        node_losses.append(style_loss(vgg_taps(x, ws, upto=i + 1)[i], targets[i]))
+    total = style_weight * torch.stack(node_losses).sum() + content_weight * closs
+    total.backward()
+    return total.detach(), x.grad.detach(), torch.stack(node_losses + [closs, floss]).detach()
