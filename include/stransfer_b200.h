@@ -16,8 +16,12 @@
  *    synchronisation, so the calls can be captured in a CUDA graph.
  *  - activations use the "split-bf16 NHWC" format: channels-last, two bf16
  *    planes hi = bf16(x), lo = bf16(x - hi).  A NULL lo plane selects plain
- *    bf16 (1 tensor-core pass per product instead of 3).  Channel counts are
- *    multiples of 8 (images are padded 3/6 -> 8 with zeros).
+ *    bf16 (1 tensor-core pass per product instead of 3).  Where a `planes`
+ *    argument is 3 a THIRD plane bf16(x - hi - lo) lives one plane stride after
+ *    lo (at lo + (lo - hi)): ~24 mantissa bits, 6 tensor-core passes per
+ *    product.  Forward activations need it: ReLU masks / max-pool argmaxes flip
+ *    on 1e-5 errors and each flip costs a whole gradient entry.
+ *    Channel counts are multiples of 8 (images are padded 3/6 -> 8 with zeros).
  *  - scalars that come from autograd (loss weights = grad_output entries) are
  *    passed as device pointers (`gw`) so that no host sync is needed.
  */
@@ -44,14 +48,14 @@ long long st_launch_count(void);
 /* ---- layout / packing ------------------------------------------------- */
 /* img_utils/torch.cat boundary: NCHW fp32 (optionally two tensors concatenated on
  * channels, network.py:984-986) -> split-bf16 NHWC with Cpad channels. */
-int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo,
+int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int planes,
                     int N, int C1, int C2, int H, int W, int Cpad, void* stream);
-int st_nhwc_to_nchw(const void* hi, const void* lo, float* out,
+int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, float* out,
                     int N, int C, int H, int W, int Cpad, void* stream);
 /* nn.Conv2d.weight [Cout][Cin][ks][ks] fp32 -> packed [rows_pad][ks*ks][cols_pad] split-bf16.
  * mode 0 forward; 1 backward-data (gather form, any stride); 2 backward-data as a
  * forward conv with flipped taps (stride 1). */
-int st_pack_conv_weight(const float* w, void* hi, void* lo, int Cout, int Cin, int ks,
+int st_pack_conv_weight(const float* w, void* hi, void* lo, int planes, int Cout, int Cin, int ks,
                         int rows_pad, int cols_pad, int mode, void* stream);
 
 /* ---- convolution ------------------------------------------------------ */
@@ -61,13 +65,15 @@ int st_pack_conv_weight(const float* w, void* hi, void* lo, int Cout, int Cin, i
  * (nn.Upsample network.py:580-594).  `transposed`=1 evaluates the backward-data
  * gather (weights packed with mode 1).  w_img_rows != 0 selects per-image weights
  * (rows n*w_img_rows.. of the packed matrix): used for the Gram backward dF = F*D.
- * out_nchw (optional) receives the first Cnchw channels as NCHW fp32. */
-int st_conv2d(const void* x_hi, const void* x_lo, int N, int H, int W, int Cin, int up,
-              const void* w_hi, const void* w_lo, int w_rows_total, int w_img_rows,
+ * out_nchw (optional) receives the first Cnchw channels as NCHW fp32.
+ * x_planes / w_planes / out_planes: 1..3 (see the conventions above); `add`, `out` and
+ * `relu_out` all carry out_planes planes; `mask` is read from its hi plane only. */
+int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
+              const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows,
               int ks, int stride, int pad, int transposed,
               int Ho, int Wo, int Cout_pad, int Cbias,
               const float* bias, const void* mask, const void* add_hi, const void* add_lo,
-              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo,
+              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes,
               float* out_nchw, int Cnchw, void* stream);
 
 /* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]) */
@@ -79,11 +85,11 @@ int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy,
 
 /* ---- VGG pieces -------------------------------------------------------- */
 /* nn.ReLU + nn.MaxPool2d(2,2) of VGG pieces 2 and 5 (network.py:257-314) */
-int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo,
+int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, int planes,
                            int N, int H, int W, int C, void* stream);
 /* backward: gx = route(gy) * relu'(x) + add */
 int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
-                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo,
+                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int x_planes,
                            int N, int H, int W, int C, void* stream);
 
 /* ---- losses ------------------------------------------------------------ */
@@ -119,11 +125,11 @@ size_t st_instnorm_workspace_bytes(int N, int C);
 /* y = gamma*(x-mean)*rstd+beta, optional fused ReLU, optional x2 nearest upsample on write
  * (the nn.Upsample that follows, network.py:580, :592); mean/rstd [N][C] are saved for backward */
 int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
-                    void* y_hi, void* y_lo, float* mean, float* rstd,
+                    void* y_hi, void* y_lo, int planes, float* mean, float* rstd,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                     const float* mean, const float* rstd, const float* gamma, const float* beta,
-                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int x_planes,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 
 #ifdef __cplusplus

@@ -19,21 +19,21 @@ SIGNATURES = {
     'st_last_error': (c_char_p, []),
     'st_set_conv_path': (_I, [_I]),
     'st_launch_count': (ctypes.c_longlong, []),
-    'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
-    'st_nhwc_to_nchw': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
-    'st_pack_conv_weight': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
-    'st_conv2d': (_I, [_P, _P, _I, _I, _I, _I, _I,          # x, N H W Cin up
-                       _P, _P, _I, _I,                      # w, rows_total, img_rows
+    'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
+    'st_nhwc_to_nchw': (_I, [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P]),
+    'st_pack_conv_weight': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
+    'st_conv2d': (_I, [_P, _P, _I, _I, _I, _I, _I, _I,      # x, planes, N H W Cin up
+                       _P, _P, _I, _I, _I,                  # w, planes, rows_total, img_rows
                        _I, _I, _I, _I,                      # ks stride pad transposed
                        _I, _I, _I, _I,                      # Ho Wo Cout_pad Cbias
                        _P, _P, _P, _P,                      # bias mask add_hi add_lo
-                       _P, _P, _P, _P,                      # out_hi out_lo relu_hi relu_lo
+                       _P, _P, _P, _P, _I,                  # out_hi out_lo relu_hi relu_lo out_planes
                        _P, _I, _P]),                        # out_nchw Cnchw stream
     'st_conv2d_wgrad_workspace_bytes': (_Z, [_I, _I, _I, _I, _I, _I]),
     'st_conv2d_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                              _P, _P, _P, _Z, _P]),
-    'st_relu_maxpool2x2_fwd': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
-    'st_relu_maxpool2x2_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    'st_relu_maxpool2x2_fwd': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    'st_relu_maxpool2x2_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_gram_workspace_bytes': (_Z, [_I, _I, _I]),
     'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _P, _P, _Z, _P]),
     'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P]),
@@ -45,8 +45,8 @@ SIGNATURES = {
     'st_temporal_fwd': (_I, [_P, _P, _P, _P, _Z, _F, _P, _P, _P]),
     'st_temporal_bwd': (_I, [_P, _P, _Z, _F, _P, _P, _P, _P]),
     'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
-    'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
-    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
 }
 
 _lib = None

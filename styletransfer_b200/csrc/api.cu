@@ -13,28 +13,28 @@ long long g_st_launches = 0;
 
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
-int conv_tc_run(const bf16*, const bf16*, int, int, int, int, const bf16*, const bf16*, int, int, int, int,
-                const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, cudaStream_t);
-int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int,
+int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
+                const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, cudaStream_t);
+int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*,
-                 bf16*, bf16*, bf16*, bf16*, float*, int, cudaStream_t);
+                 bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
 size_t contract_workspace_bytes(int N, int Ho, int Wo, int Cdy, int Ktot, int groups);
 int contract_run(const bf16*, const bf16*, int, const bf16*, const bf16*, int, int, int, int, int, int, int, int, int, int,
                  int, int, int, float, float*, void*, size_t, cudaStream_t);
-int ew_nchw_to_nhwc(const float*, const float*, bf16*, bf16*, int, int, int, int, int, int, cudaStream_t);
-int ew_nhwc_to_nchw(const bf16*, const bf16*, float*, int, int, int, int, int, cudaStream_t);
-int ew_pack_weight(const float*, bf16*, bf16*, int, int, int, int, int, int, cudaStream_t);
-int ew_relu_maxpool_fwd(const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
-int ew_relu_maxpool_bwd(const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
+int ew_nchw_to_nhwc(const float*, const float*, bf16*, bf16*, int, int, int, int, int, int, int, cudaStream_t);
+int ew_nhwc_to_nchw(const bf16*, const bf16*, int, float*, int, int, int, int, int, cudaStream_t);
+int ew_pack_weight(const float*, bf16*, bf16*, int, int, int, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_fwd(const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_bwd(const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int ew_mse_fwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, int, float*, float*, cudaStream_t);
 int ew_mse_bwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, float, const float*, const float*, int, bf16*, bf16*, cudaStream_t);
 int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, cudaStream_t);
 int ew_style_seed(const float*, int, int, float, const float*, bf16*, bf16*, cudaStream_t);
 int ew_channel_sum(const bf16*, const bf16*, int, int, int, float*, float*, cudaStream_t);
 size_t in_workspace_floats(int N, int C);
-int in_forward(const bf16*, const bf16*, const float*, const float*, float, bf16*, bf16*, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
+int in_forward(const bf16*, const bf16*, const float*, const float*, float, bf16*, bf16*, int, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
 int in_backward(const bf16*, const bf16*, const bf16*, const bf16*, const float*, const float*, const float*, const float*,
-                bf16*, bf16*, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
+                bf16*, bf16*, float*, float*, int, int, int, int, int, int, int, float*, cudaStream_t);
 int tv_forward(const float*, size_t, int, int, float, float*, float*, cudaStream_t);
 int tv_backward(const float*, size_t, int, int, float, const float*, float*, cudaStream_t);
 int temporal_forward(const float*, const float*, const float*, const float*, size_t, float, float*, float*, cudaStream_t);
@@ -51,29 +51,29 @@ const char* st_last_error(void) { return g_err; }
 int st_set_conv_path(int path) { g_conv_path = path; return ST_OK; }
 long long st_launch_count(void) { return g_st_launches; }
 
-int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int N, int C1, int C2, int H, int W, int Cpad, void* stream) {
+int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int planes, int N, int C1, int C2, int H, int W, int Cpad, void* stream) {
     ST_CHECK_ARG(a && hi && N > 0 && H > 0 && W > 0, "st_nchw_to_nhwc: null pointer or empty shape");
     ST_CHECK_ARG(Cpad % 8 == 0 && C1 + C2 <= Cpad && (C2 == 0 || b), "st_nchw_to_nhwc: Cpad must be a multiple of 8 and >= C1+C2");
-    return ew_nchw_to_nhwc(a, b, BF(hi), BF(lo), N, C1, C2, H, W, Cpad, STRM(stream));
+    return ew_nchw_to_nhwc(a, b, BF(hi), BF(lo), lo ? planes : 1, N, C1, C2, H, W, Cpad, STRM(stream));
 }
-int st_nhwc_to_nchw(const void* hi, const void* lo, float* out, int N, int C, int H, int W, int Cpad, void* stream) {
+int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, float* out, int N, int C, int H, int W, int Cpad, void* stream) {
     ST_CHECK_ARG(hi && out && N > 0 && H > 0 && W > 0, "st_nhwc_to_nchw: null pointer or empty shape");
     ST_CHECK_ARG(Cpad % 8 == 0 && C <= Cpad, "st_nhwc_to_nchw: Cpad must be a multiple of 8 and >= C");
-    return ew_nhwc_to_nchw(CBF(hi), CBF(lo), out, N, C, H, W, Cpad, STRM(stream));
+    return ew_nhwc_to_nchw(CBF(hi), CBF(lo), lo ? planes : 1, out, N, C, H, W, Cpad, STRM(stream));
 }
-int st_pack_conv_weight(const float* w, void* hi, void* lo, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, void* stream) {
+int st_pack_conv_weight(const float* w, void* hi, void* lo, int planes, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, void* stream) {
     ST_CHECK_ARG(w && hi, "st_pack_conv_weight: null pointer");
     ST_CHECK_ARG(mode >= 0 && mode <= 2 && cols_pad % 8 == 0, "st_pack_conv_weight: bad mode or cols_pad %% 8 != 0");
     const int rows = mode == 0 ? Cout : Cin, cols = mode == 0 ? Cin : Cout;
     ST_CHECK_ARG(rows_pad >= rows && cols_pad >= cols, "st_pack_conv_weight: padded sizes smaller than the weight");
-    return ew_pack_weight(w, BF(hi), BF(lo), Cout, Cin, ks, rows_pad, cols_pad, mode, STRM(stream));
+    return ew_pack_weight(w, BF(hi), BF(lo), lo ? planes : 1, Cout, Cin, ks, rows_pad, cols_pad, mode, STRM(stream));
 }
 
-int st_conv2d(const void* x_hi, const void* x_lo, int N, int H, int W, int Cin, int up,
-              const void* w_hi, const void* w_lo, int w_rows_total, int w_img_rows,
+int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
+              const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows,
               int ks, int stride, int pad, int transposed, int Ho, int Wo, int Cout_pad, int Cbias,
               const float* bias, const void* mask, const void* add_hi, const void* add_lo,
-              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, float* out_nchw, int Cnchw, void* stream) {
+              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes, float* out_nchw, int Cnchw, void* stream) {
     ST_CHECK_ARG(x_hi && w_hi, "st_conv2d: null input or weight");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0, "st_conv2d: empty shape");
     ST_CHECK_ARG(Cin % 8 == 0 && Cout_pad % 8 == 0, "st_conv2d: channel counts must be multiples of 8 (got %d, %d)", Cin, Cout_pad);
@@ -83,26 +83,26 @@ int st_conv2d(const void* x_hi, const void* x_lo, int N, int H, int W, int Cin, 
     const bool tc = g_conv_path == 0 && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && !out_nchw &&
                     w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad);
     if (tc)
-        return conv_tc_run(CBF(x_hi), CBF(x_lo), N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_rows_total, w_img_rows, ks, Cout_pad,
-                           bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), STRM(stream));
+        return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
+                           bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, STRM(stream));
     if (w_img_rows != 0) {
         // per-image weights on the generic path: one launch per image
         for (int n = 0; n < N; ++n) {
             const size_t xin = static_cast<size_t>(n) * H * W * Cin, xo = static_cast<size_t>(n) * Ho * Wo * Cout_pad;
             const size_t wo = static_cast<size_t>(n) * w_img_rows * ks * ks * Cin;
-            int rc = conv_gen_run(CBF(x_hi) + xin, x_lo ? CBF(x_lo) + xin : nullptr, 1, H, W, Cin, up,
-                                  CBF(w_hi) + wo, w_lo ? CBF(w_lo) + wo : nullptr, ks, stride, pad, transposed, Ho, Wo, Cout_pad, Cout_pad, Cbias,
+            int rc = conv_gen_run(CBF(x_hi) + xin, x_lo ? CBF(x_lo) + xin : nullptr, x_planes >= 3 ? 2 : x_planes, 1, H, W, Cin, up,
+                                  CBF(w_hi) + wo, w_lo ? CBF(w_lo) + wo : nullptr, w_planes >= 3 ? 2 : w_planes, ks, stride, pad, transposed, Ho, Wo, Cout_pad, Cout_pad, Cbias,
                                   bias, mask ? CBF(mask) + xo : nullptr, add_hi ? CBF(add_hi) + xo : nullptr, add_lo ? CBF(add_lo) + xo : nullptr,
                                   out_hi ? BF(out_hi) + xo : nullptr, out_lo ? BF(out_lo) + xo : nullptr,
-                                  relu_hi ? BF(relu_hi) + xo : nullptr, relu_lo ? BF(relu_lo) + xo : nullptr,
+                                  relu_hi ? BF(relu_hi) + xo : nullptr, relu_lo ? BF(relu_lo) + xo : nullptr, out_planes >= 3 ? 2 : out_planes,
                                   out_nchw ? out_nchw + static_cast<size_t>(n) * Cnchw * Ho * Wo : nullptr, Cnchw, STRM(stream));
             if (rc) return rc;
         }
         return ST_OK;
     }
-    return conv_gen_run(CBF(x_hi), CBF(x_lo), N, H, W, Cin, up, CBF(w_hi), CBF(w_lo), ks, stride, pad, transposed,
+    return conv_gen_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, up, CBF(w_hi), CBF(w_lo), w_planes, ks, stride, pad, transposed,
                         Ho, Wo, Cout_pad, Cout_pad, Cbias, bias, CBF(mask), CBF(add_hi), CBF(add_lo),
-                        BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_nchw, Cnchw, STRM(stream));
+                        BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw, STRM(stream));
 }
 
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {
@@ -126,14 +126,14 @@ int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy, const void* x
     return rc;
 }
 
-int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, int N, int H, int W, int C, void* stream) {
+int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, int planes, int N, int H, int W, int C, void* stream) {
     ST_CHECK_ARG(x_hi && y_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_fwd: null pointer or C %% 8 != 0");
-    return ew_relu_maxpool_fwd(CBF(x_hi), CBF(x_lo), BF(y_hi), BF(y_lo), N, H, W, C, STRM(stream));
+    return ew_relu_maxpool_fwd(CBF(x_hi), CBF(x_lo), BF(y_hi), BF(y_lo), x_lo ? planes : 1, N, H, W, C, STRM(stream));
 }
 int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
-                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int N, int H, int W, int C, void* stream) {
+                           const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int x_planes, int N, int H, int W, int C, void* stream) {
     ST_CHECK_ARG(x_hi && gy_hi && gx_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_bwd: null pointer or C %% 8 != 0");
-    return ew_relu_maxpool_bwd(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), N, H, W, C, STRM(stream));
+    return ew_relu_maxpool_bwd(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), x_lo ? x_planes : 1, N, H, W, C, STRM(stream));
 }
 
 size_t st_gram_workspace_bytes(int B, int HW, int C) { return contract_workspace_bytes(B, HW, 1, C, C, B); }
@@ -185,21 +185,21 @@ int st_temporal_bwd(const float* os, const float* cs, size_t numel, float tw, co
 size_t st_instnorm_workspace_bytes(int N, int C) { return (in_workspace_floats(N, C) + 2 * static_cast<size_t>(N) * C) * sizeof(float); }
 static bool in_channels_ok(int C) { return C >= 8 && C <= 256 && (C & (C - 1)) == 0; }
 int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
-                    void* y_hi, void* y_lo, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
+                    void* y_hi, void* y_lo, int planes, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
                     void* workspace, void* stream) {
     ST_CHECK_ARG(x_hi && gamma && beta && y_hi && mean && rstd && workspace, "st_instnorm_fwd: null pointer");
     ST_CHECK_ARG(in_channels_ok(C), "st_instnorm_fwd: C must be a power of two in [8,256] (got %d)", C);
-    return in_forward(CBF(x_hi), CBF(x_lo), gamma, beta, eps, BF(y_hi), BF(y_lo), mean, rstd, N, H, W, C, relu, up,
+    return in_forward(CBF(x_hi), CBF(x_lo), gamma, beta, eps, BF(y_hi), BF(y_lo), x_lo ? planes : 1, mean, rstd, N, H, W, C, relu, up,
                       static_cast<float*>(workspace), STRM(stream));
 }
 int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                     const float* mean, const float* rstd, const float* gamma, const float* beta,
-                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int up,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int x_planes, int N, int H, int W, int C, int relu, int up,
                     void* workspace, void* stream) {
     ST_CHECK_ARG(x_hi && gy_hi && mean && rstd && gamma && beta && dx_hi && dgamma && dbeta && workspace, "st_instnorm_bwd: null pointer");
     ST_CHECK_ARG(in_channels_ok(C), "st_instnorm_bwd: C must be a power of two in [8,256] (got %d)", C);
     return in_backward(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), mean, rstd, gamma, beta, BF(dx_hi), BF(dx_lo),
-                       dgamma, dbeta, N, H, W, C, relu, up, static_cast<float*>(workspace), STRM(stream));
+                       dgamma, dbeta, x_lo ? x_planes : 1, N, H, W, C, relu, up, static_cast<float*>(workspace), STRM(stream));
 }
 
 }  // extern "C"

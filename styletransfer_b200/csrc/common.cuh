@@ -71,6 +71,48 @@ __device__ __forceinline__ void store8(bf16* hi, bf16* lo, size_t off, const flo
     if (lo) *reinterpret_cast<uint4*>(lo + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
 }
 
+// ----- three-plane variants ("bf16x6"): hi + mid + lo carries ~24 mantissa bits.  The
+// third plane of a tensor always sits one plane stride after the second:
+//     p2 = lo + (lo - hi).
+__device__ __forceinline__ const bf16* third_plane(const bf16* hi, const bf16* lo, int planes) {
+    return (planes >= 3 && lo) ? lo + (lo - hi) : nullptr;
+}
+__device__ __forceinline__ bf16* third_plane(bf16* hi, bf16* lo, int planes) {
+    return (planes >= 3 && lo) ? lo + (lo - hi) : nullptr;
+}
+__device__ __forceinline__ void load8p(const bf16* hi, const bf16* lo, int planes, size_t off, float (&v)[8]) {
+    load8(hi, planes >= 2 ? lo : nullptr, off, v);
+    const bf16* p2 = third_plane(hi, lo, planes);
+    if (p2) {
+        uint4 l = *reinterpret_cast<const uint4*>(p2 + off);
+        uint32_t lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { v[2 * i] += bf16lo_to_f(lw[i]); v[2 * i + 1] += bf16hi_to_f(lw[i]); }
+    }
+}
+__device__ __forceinline__ void store8p(bf16* hi, bf16* lo, int planes, size_t off, const float (&v)[8]) {
+    uint32_t hw[4], mw[4], lw[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float a = v[2 * i], b = v[2 * i + 1];
+        hw[i] = pack_bf16x2(a, b);
+        const float ra = a - bf16lo_to_f(hw[i]), rb = b - bf16hi_to_f(hw[i]);
+        mw[i] = pack_bf16x2(ra, rb);
+        lw[i] = pack_bf16x2(ra - bf16lo_to_f(mw[i]), rb - bf16hi_to_f(mw[i]));
+    }
+    *reinterpret_cast<uint4*>(hi + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+    if (planes >= 2 && lo) *reinterpret_cast<uint4*>(lo + off) = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+    bf16* p2 = third_plane(hi, lo, planes);
+    if (p2) *reinterpret_cast<uint4*>(p2 + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+}
+// 2 values -> up to three bf16x2 words
+__device__ __forceinline__ void split2p(float a, float b, uint32_t& h, uint32_t& m, uint32_t& l) {
+    h = pack_bf16x2(a, b);
+    const float ra = a - bf16lo_to_f(h), rb = b - bf16hi_to_f(h);
+    m = pack_bf16x2(ra, rb);
+    l = pack_bf16x2(ra - bf16lo_to_f(m), rb - bf16hi_to_f(m));
+}
+
 // ----- reductions ---------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -14,6 +14,7 @@ constexpr int BM = 64, BK = 32, LDS = 40;   // LDS: padded smem row (bf16) -> co
 
 struct GenParams {
     const bf16* x_hi; const bf16* x_lo;
+    int x_planes, w_planes, out_planes;   // 1..3 bf16 planes (third plane: common.cuh)
     int N, H, W, Cin;          // stored input tensor
     int up;                    // 1: input is read through a nearest x2 upsample (K6)
     const bf16* w_hi; const bf16* w_lo;
@@ -42,11 +43,13 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 
 template <int BN>
 __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
-    __shared__ __align__(16) bf16 As[2][BM][LDS];
-    __shared__ __align__(16) bf16 Bs[2][BN][LDS];
+    __shared__ __align__(16) bf16 As[3][BM][LDS];
+    __shared__ __align__(16) bf16 Bs[3][BN][LDS];
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-    const bool a_lo = p.x_lo != nullptr, w_lo = p.w_lo != nullptr;
+    const int ap = p.x_planes, wp = p.w_planes, maxord = max(ap, wp) - 1;
+    const bf16* x_p2 = third_plane(p.x_hi, p.x_lo, ap);
+    const bf16* w_p2 = third_plane(p.w_hi, p.w_lo, wp);
     const int Hl = p.H << p.up, Wl = p.W << p.up;
 
     // the two A rows this thread gathers
@@ -72,7 +75,7 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
         if (kvalid) { tap = k / p.Cin; ci = k - tap * p.Cin; r = tap / p.ks; s = tap - r * p.ks; }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-            uint4 vh = make_uint4(0, 0, 0, 0), vl = make_uint4(0, 0, 0, 0);
+            uint4 vh = make_uint4(0, 0, 0, 0), vl = make_uint4(0, 0, 0, 0), v2 = make_uint4(0, 0, 0, 0);
             if (kvalid && pv[i]) {
                 int ih, iw; bool ok;
                 if (!p.transposed) {
@@ -88,44 +91,50 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
                 if (ok) {
                     const size_t off = ((static_cast<size_t>(pn[i]) * p.H + ih) * p.W + iw) * p.Cin + ci;
                     vh = *reinterpret_cast<const uint4*>(p.x_hi + off);
-                    if (a_lo) vl = *reinterpret_cast<const uint4*>(p.x_lo + off);
+                    if (ap > 1) vl = *reinterpret_cast<const uint4*>(p.x_lo + off);
+                    if (x_p2) v2 = *reinterpret_cast<const uint4*>(x_p2 + off);
                 }
             }
             const int row = (t >> 2) + i * 32;
             *reinterpret_cast<uint4*>(&As[0][row][kv]) = vh;
             *reinterpret_cast<uint4*>(&As[1][row][kv]) = vl;
+            *reinterpret_cast<uint4*>(&As[2][row][kv]) = v2;
         }
         // ---- load B ----
         for (int idx = t; idx < BN * 4; idx += 128) {
             const int row = idx >> 2, kb = (idx & 3) * 8;
-            uint4 vh = make_uint4(0, 0, 0, 0), vl = make_uint4(0, 0, 0, 0);
+            uint4 vh = make_uint4(0, 0, 0, 0), vl = make_uint4(0, 0, 0, 0), v2 = make_uint4(0, 0, 0, 0);
             if (n0 + row < p.Cout_pad && k0 + kb < p.Ktot) {
                 const size_t off = static_cast<size_t>(n0 + row) * p.Ktot + k0 + kb;
                 vh = *reinterpret_cast<const uint4*>(p.w_hi + off);
-                if (w_lo) vl = *reinterpret_cast<const uint4*>(p.w_lo + off);
+                if (wp > 1) vl = *reinterpret_cast<const uint4*>(p.w_lo + off);
+                if (w_p2) v2 = *reinterpret_cast<const uint4*>(w_p2 + off);
             }
             *reinterpret_cast<uint4*>(&Bs[0][row][kb]) = vh;
             *reinterpret_cast<uint4*>(&Bs[1][row][kb]) = vl;
+            *reinterpret_cast<uint4*>(&Bs[2][row][kb]) = v2;
         }
         __syncthreads();
         // ---- MMA ----
 #pragma unroll
         for (int kk = 0; kk < BK; kk += 16) {
-            uint32_t ah[4], al[4];
+            uint32_t af[3][4];
             const int arow = warp * 16 + (lane & 15), acol = kk + (lane >> 4) * 8;
-            ldmatrix_x4(static_cast<uint32_t>(__cvta_generic_to_shared(&As[0][arow][acol])), ah[0], ah[1], ah[2], ah[3]);
-            if (a_lo) ldmatrix_x4(static_cast<uint32_t>(__cvta_generic_to_shared(&As[1][arow][acol])), al[0], al[1], al[2], al[3]);
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                if (i < ap) ldmatrix_x4(static_cast<uint32_t>(__cvta_generic_to_shared(&As[i][arow][acol])), af[i][0], af[i][1], af[i][2], af[i][3]);
 #pragma unroll
             for (int j = 0; j < BN / 8; ++j) {
                 const int brow = j * 8 + (lane & 7), bcol = kk + ((lane >> 3) & 1) * 8;
-                uint32_t bh0, bh1;
-                ldmatrix_x2(static_cast<uint32_t>(__cvta_generic_to_shared(&Bs[0][brow][bcol])), bh0, bh1);
-                mma16816(acc[j], ah, bh0, bh1);
-                if (a_lo) mma16816(acc[j], al, bh0, bh1);
-                if (w_lo) {
-                    uint32_t bl0, bl1;
-                    ldmatrix_x2(static_cast<uint32_t>(__cvta_generic_to_shared(&Bs[1][brow][bcol])), bl0, bl1);
-                    mma16816(acc[j], ah, bl0, bl1);
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    if (q >= wp) break;
+                    uint32_t b0, b1;
+                    ldmatrix_x2(static_cast<uint32_t>(__cvta_generic_to_shared(&Bs[q][brow][bcol])), b0, b1);
+                    // plane pairs (i, q) with i + q <= maxord: 1, 3 or 6 passes per product
+#pragma unroll
+                    for (int i = 0; i < 3; ++i)
+                        if (i < ap && i + q <= maxord) mma16816(acc[j], af[i], b0, b1);
                 }
             }
         }
@@ -156,17 +165,23 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
                     if (p.add_lo) {
                         const uint32_t b = *reinterpret_cast<const uint32_t*>(p.add_lo + o);
                         v0 += bf16lo_to_f(b); v1 += bf16hi_to_f(b);
+                        const bf16* a2 = third_plane(p.add_hi, p.add_lo, p.out_planes);   // add carries the output's planes
+                        if (a2) { const uint32_t c = *reinterpret_cast<const uint32_t*>(a2 + o); v0 += bf16lo_to_f(c); v1 += bf16hi_to_f(c); }
                     }
                 }
                 if (p.out_hi) {
-                    uint32_t h, l; split2(v0, v1, h, l);
+                    uint32_t h, m, l; split2p(v0, v1, h, m, l);
                     *reinterpret_cast<uint32_t*>(p.out_hi + o) = h;
-                    if (p.out_lo) *reinterpret_cast<uint32_t*>(p.out_lo + o) = l;
+                    if (p.out_lo && p.out_planes > 1) *reinterpret_cast<uint32_t*>(p.out_lo + o) = m;
+                    bf16* o2 = third_plane(p.out_hi, p.out_lo, p.out_planes);
+                    if (o2) *reinterpret_cast<uint32_t*>(o2 + o) = l;
                 }
                 if (p.relu_hi) {
-                    uint32_t h, l; split2(fmaxf(v0, 0.f), fmaxf(v1, 0.f), h, l);
+                    uint32_t h, m, l; split2p(fmaxf(v0, 0.f), fmaxf(v1, 0.f), h, m, l);
                     *reinterpret_cast<uint32_t*>(p.relu_hi + o) = h;
-                    if (p.relu_lo) *reinterpret_cast<uint32_t*>(p.relu_lo + o) = l;
+                    if (p.relu_lo && p.out_planes > 1) *reinterpret_cast<uint32_t*>(p.relu_lo + o) = m;
+                    bf16* o2 = third_plane(p.relu_hi, p.relu_lo, p.out_planes);
+                    if (o2) *reinterpret_cast<uint32_t*>(o2 + o) = l;
                 }
             }
             if (p.out_nchw) {
@@ -181,13 +196,14 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
 
 }  // namespace
 
-int conv_gen_run(const bf16* x_hi, const bf16* x_lo, int N, int H, int W, int Cin, int up,
-                 const bf16* w_hi, const bf16* w_lo, int ks, int stride, int pad, int transposed,
+int conv_gen_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
+                 const bf16* w_hi, const bf16* w_lo, int w_planes, int ks, int stride, int pad, int transposed,
                  int Ho, int Wo, int Cout_pad, int Cstore, int Cbias,
                  const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
-                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo,
+                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes,
                  float* out_nchw, int Cnchw, cudaStream_t stream) {
     GenParams p;
+    p.x_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1; p.w_planes = w_lo ? (w_planes >= 3 ? 3 : 2) : 1; p.out_planes = out_planes;
     p.x_hi = x_hi; p.x_lo = x_lo; p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.up = up;
     p.w_hi = w_hi; p.w_lo = w_lo; p.Ktot = ks * ks * Cin;
     p.ks = ks; p.stride = stride; p.pad = pad; p.transposed = transposed;

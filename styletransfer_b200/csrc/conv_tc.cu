@@ -33,7 +33,9 @@ struct ConvTcParams {
     int N, H, W, Cin, Cout;
     int tiles_h, tiles_w, n_blocks, work;
     int w_img_rows;                 // weight-row offset per image (0: shared weights)
-    int has_a_lo, has_w_lo;
+    int w_rows_total;               // rows of one weight plane
+    int a_planes, w_planes, out_planes;   // 1, 2 or 3 bf16 planes per tensor (see common.cuh)
+    int nb;                               // B-ring depth (fits the shared-memory budget)
     const float* bias;              // [Cout] or null
     const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
     const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
@@ -47,11 +49,13 @@ template <int KS, int BN> struct Cfg {
     static constexpr int A_PLANE = A_ROWS * 128;            // bytes (64 bf16 per row)
     static constexpr int B_PLANE = BN * 128;
     static constexpr int NA = 2;
-    static constexpr int NB = (BN == 128) ? 4 : 6;
-    static constexpr int A_BYTES = NA * 2 * A_PLANE;
-    static constexpr int B_BYTES = NB * 2 * B_PLANE;
+    static constexpr int NB_MAX = 8;
     static constexpr int BAR_BYTES = 256;
-    static constexpr int SMEM = 1024 + A_BYTES + B_BYTES + BAR_BYTES;   // 1024 slack for alignment
+    static constexpr int SMEM_MAX = 232448;                            // 227 KB opt-in limit
+    // bytes for given plane counts and ring depth (1024 slack for alignment)
+    static constexpr int smem(int a_planes, int w_planes, int nb) {
+        return 1024 + NA * a_planes * A_PLANE + nb * w_planes * B_PLANE + BAR_BYTES;
+    }
     static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : 256;
 };
 
@@ -63,14 +67,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
     using C = Cfg<KS, BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int NB = p.nb;
+    const int a_slot = p.a_planes * C::A_PLANE, b_slot = p.w_planes * C::B_PLANE;
     uint8_t* sA = smem;
-    uint8_t* sB = smem + C::A_BYTES;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::A_BYTES + C::B_BYTES);
+    uint8_t* sB = smem + C::NA * a_slot;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + NB * b_slot);
     uint64_t* a_full = bars;                 // [NA]
     uint64_t* a_empty = a_full + C::NA;      // [NA]
     uint64_t* b_full = a_empty + C::NA;      // [NB]
-    uint64_t* b_empty = b_full + C::NB;      // [NB]
-    uint64_t* t_full = b_empty + C::NB;      // [2]
+    uint64_t* b_empty = b_full + NB;         // [NB]
+    uint64_t* t_full = b_empty + NB;         // [2]
     uint64_t* t_empty = t_full + 2;          // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
@@ -80,10 +86,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmW_hi);
-        if (p.has_a_lo) ptx::prefetch_tmap(&tmA_lo);
-        if (p.has_w_lo) ptx::prefetch_tmap(&tmW_lo);
+        if (p.a_planes > 1) ptx::prefetch_tmap(&tmA_lo);
+        if (p.w_planes > 1) ptx::prefetch_tmap(&tmW_lo);
         for (int i = 0; i < C::NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
-        for (int i = 0; i < C::NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
+        for (int i = 0; i < NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], 4); }
         ptx::fence_barrier_init();
     }
@@ -97,8 +103,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         // ===================== TMA producer =====================
         if (lane == 0) {
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
-            const uint32_t a_tx = (p.has_a_lo ? 2 : 1) * C::A_PLANE;
-            const uint32_t b_tx = (p.has_w_lo ? 2 : 1) * C::B_PLANE;
+            const uint32_t a_tx = a_slot, b_tx = b_slot;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x) {
                 const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
                 const int tw = t % p.tiles_w; t /= p.tiles_w;
@@ -109,17 +114,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                     for (int s = 0; s < KS; ++s) {
                         ptx::mbar_wait(&a_empty[a], aph ^ 1);
                         ptx::mbar_expect_tx(&a_full[a], a_tx);
-                        uint8_t* dst = sA + a * 2 * C::A_PLANE;
+                        uint8_t* dst = sA + a * a_slot;
+                        // the planes of one tensor are equally spaced, so one tensor map per tensor
+                        // with the plane index as 5th coordinate would also do; two maps keep rank 4
                         ptx::tma_load_4d(dst, &tmA_hi, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
-                        if (p.has_a_lo) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
+                        if (p.a_planes > 1) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
+                        if (p.a_planes > 2) ptx::tma_load_4d(dst + 2 * C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n + p.N);
                         if (++a == C::NA) { a = 0; aph ^= 1; }
                         for (int r = 0; r < KS; ++r) {
                             ptx::mbar_wait(&b_empty[b], bph ^ 1);
                             ptx::mbar_expect_tx(&b_full[b], b_tx);
-                            uint8_t* bd = sB + b * 2 * C::B_PLANE;
+                            uint8_t* bd = sB + b * b_slot;
                             ptx::tma_load_3d(bd, &tmW_hi, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (p.has_w_lo) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (++b == C::NB) { b = 0; bph ^= 1; }
+                            if (p.w_planes > 1) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
+                            if (p.w_planes > 2) ptx::tma_load_3d(bd + 2 * C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow + p.w_rows_total);
+                            if (++b == NB) { b = 0; bph ^= 1; }
                         }
                     }
                 }
@@ -129,6 +138,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         // ===================== MMA issuer =====================
         if (lane == 0) {
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_M, BN);
+            const int maxord = max(p.a_planes, p.w_planes) - 1;
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
             int it = 0;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
@@ -141,25 +151,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                     for (int s = 0; s < KS; ++s) {
                         ptx::mbar_wait(&a_full[a], aph);
                         ptx::tc_fence_after();
-                        const uint32_t a_base = ptx::smem_u32(sA + a * 2 * C::A_PLANE);
+                        const uint32_t a_base = ptx::smem_u32(sA + a * a_slot);
                         for (int r = 0; r < KS; ++r) {
                             ptx::mbar_wait(&b_full[b], bph);
                             ptx::tc_fence_after();
-                            const uint32_t b_base = ptx::smem_u32(sB + b * 2 * C::B_PLANE);
+                            const uint32_t b_base = ptx::smem_u32(sB + b * b_slot);
                             const uint32_t a_tap = a_base + r * TILE_W * 128;
 #pragma unroll
                             for (int k = 0; k < KCH / 16; ++k) {
-                                const uint64_t ah = ptx::umma_desc_k_sw128(a_tap + k * 32);
-                                const uint64_t bh = ptx::umma_desc_k_sw128(b_base + k * 32);
-                                ptx::mma_bf16_ss(d_tmem, ah, bh, idesc, accumulate);
-                                accumulate = 1;
-                                if (p.has_a_lo)
-                                    ptx::mma_bf16_ss(d_tmem, ptx::umma_desc_k_sw128(a_tap + C::A_PLANE + k * 32), bh, idesc, 1);
-                                if (p.has_w_lo)
-                                    ptx::mma_bf16_ss(d_tmem, ah, ptx::umma_desc_k_sw128(b_base + C::B_PLANE + k * 32), idesc, 1);
+                                // a*w = sum over plane pairs (i, j) with i + j <= maxord: 1, 3 or 6 passes
+                                for (int i = 0; i < p.a_planes; ++i) {
+                                    const uint64_t ad = ptx::umma_desc_k_sw128(a_tap + i * C::A_PLANE + k * 32);
+                                    for (int j = 0; j < p.w_planes && i + j <= maxord; ++j) {
+                                        ptx::mma_bf16_ss(d_tmem, ad, ptx::umma_desc_k_sw128(b_base + j * C::B_PLANE + k * 32), idesc, accumulate);
+                                        accumulate = 1;
+                                    }
+                                }
                             }
                             ptx::tc_commit(&b_empty[b]);
-                            if (++b == C::NB) { b = 0; bph ^= 1; }
+                            if (++b == NB) { b = 0; bph ^= 1; }
                         }
                         ptx::tc_commit(&a_empty[a]);
                         if (++a == C::NA) { a = 0; aph ^= 1; }
@@ -212,15 +222,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                         }
                         if (p.add_hi) {
                             float ad[8];
-                            load8(p.add_hi, p.add_lo, o, ad);
+                            load8p(p.add_hi, p.add_lo, p.add_lo ? p.out_planes : 1, o, ad);   // add carries the output's planes
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] += ad[i];
                         }
-                        if (p.out_hi) store8(p.out_hi, p.out_lo, o, v);
+                        if (p.out_hi) store8p(p.out_hi, p.out_lo, p.out_planes, o, v);
                         if (p.relu_hi) {
 #pragma unroll
                             for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-                            store8(p.relu_hi, p.relu_lo, o, v);
+                            store8p(p.relu_hi, p.relu_lo, p.out_planes, o, v);
                         }
                     }
                 }
@@ -298,16 +308,21 @@ int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, 
 
 template <int KS, int BN>
 int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
-           const ConvTcParams& p, cudaStream_t stream) {
+           ConvTcParams p, cudaStream_t stream) {
     using C = Cfg<KS, BN>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_MAX);
         if (e != cudaSuccess) { st_set_error("conv_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
+    // deepest weight ring that fits next to the two activation slots
+    int nb = C::NB_MAX;
+    while (nb > 1 && C::smem(p.a_planes, p.w_planes, nb) > C::SMEM_MAX) --nb;
+    if (C::smem(p.a_planes, p.w_planes, nb) > C::SMEM_MAX) { st_set_error("conv_tc: tile does not fit shared memory"); return ST_ERR_UNSUPPORTED; }
+    p.nb = nb;
     int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tc_kernel<KS, BN><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
+    conv_tc_kernel<KS, BN><<<grid, NUM_THREADS, C::smem(p.a_planes, p.w_planes, nb), stream>>>(ah, al, wh, wl, p);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
 }
@@ -319,31 +334,37 @@ bool conv_tc_eligible(int ks, int stride, int Cin, int Cout) {
     return (ks == 3 || ks == 1) && stride == 1 && Cin % 64 == 0 && (Cout % 128 == 0 || Cout == 64 || Cout == 32);
 }
 
-int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int N, int H, int W, int Cin,
-                const bf16* w_hi, const bf16* w_lo, int w_rows_total, int w_img_rows, int ks, int Cout,
+int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin,
+                const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout,
                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
-                bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, cudaStream_t stream) {
+                bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, cudaStream_t stream) {
     const int BN = (Cout % 128 == 0) ? 128 : Cout;
     const int taps = ks * ks;
     ConvTcParams p;
     p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
     p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
     p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
-    p.w_img_rows = w_img_rows; p.has_a_lo = x_lo != nullptr; p.has_w_lo = w_lo != nullptr;
+    p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
+    p.a_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1;
+    p.w_planes = w_lo ? (w_planes >= 3 ? 3 : 2) : 1;
+    p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
 
+    // the third plane follows the second at the same stride: the "lo" map simply spans both
     CUtensorMap ah, al, wh, wl;
     uint64_t ad[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t ad2[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N * (p.a_planes == 3 ? 2 : 1)};
     uint32_t ab[4] = {KCH, TILE_W, (uint32_t)(TILE_H + ks - 1), 1};
     uint64_t wd[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total};
+    uint64_t wd2[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total * (p.w_planes == 3 ? 2 : 1)};
     uint32_t wb[3] = {KCH, 1, (uint32_t)BN};
     int rc;
     if ((rc = make_map(&ah, x_hi, 4, ad, ab))) return rc;
     if ((rc = make_map(&wh, w_hi, 3, wd, wb))) return rc;
     al = ah; wl = wh;
-    if (x_lo && (rc = make_map(&al, x_lo, 4, ad, ab))) return rc;
-    if (w_lo && (rc = make_map(&wl, w_lo, 3, wd, wb))) return rc;
+    if (x_lo && (rc = make_map(&al, x_lo, 4, ad2, ab))) return rc;
+    if (w_lo && (rc = make_map(&wl, w_lo, 3, wd2, wb))) return rc;
 
     if (ks == 3) {
         if (BN == 128) return launch<3, 128>(ah, al, wh, wl, p, stream);

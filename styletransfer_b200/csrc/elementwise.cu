@@ -15,7 +15,7 @@ namespace {
 // ---------------------------------------------------------------------------
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                     bf16* __restrict__ hi, bf16* __restrict__ lo,
-                                    int N, int C1, int C2, int HW, int Cpad) {
+                                    int N, int C1, int C2, int HW, int Cpad, int planes) {
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * HW) return;
     const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
@@ -29,19 +29,19 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __
             else if (c < C1 + C2) x = b[(static_cast<size_t>(n) * C2 + (c - C1)) * HW + px];
             v[i] = x;
         }
-        store8(hi, lo, idx * Cpad + c0, v);
+        store8p(hi, lo, planes, idx * Cpad + c0, v);
     }
 }
 
 // NHWC split-bf16 (Cpad channels stored) -> NCHW fp32 (first C channels)
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __restrict__ lo,
-                                    float* __restrict__ out, int N, int C, int HW, int Cpad) {
+                                    float* __restrict__ out, int N, int C, int HW, int Cpad, int planes) {
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * HW) return;
     const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
     for (int c0 = 0; c0 < C; c0 += 8) {
         float v[8];
-        load8(hi, lo, idx * Cpad + c0, v);
+        load8p(hi, lo, planes, idx * Cpad + c0, v);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
             if (c0 + i < C) out[(static_cast<size_t>(n) * C + c0 + i) * HW + px] = v[i];
@@ -55,7 +55,7 @@ __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __r
 //                        mode 2: rows=ci, cols=co, tap=(ks-1-r,ks-1-s) (dgrad as a forward conv)
 // ---------------------------------------------------------------------------
 __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict__ hi, bf16* __restrict__ lo,
-                                   int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode) {
+                                   int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, int planes) {
     const int taps = ks * ks;
     const int total = rows_pad * taps * cols_pad;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -69,7 +69,9 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict
     if (co < Cout && ci < Cin) v = w[((static_cast<size_t>(co) * Cin + ci) * ks + r) * ks + s];
     bf16 h, l; split_bf16(v, h, l);
     hi[idx] = h;
-    if (lo) lo[idx] = l;
+    if (lo && planes > 1) lo[idx] = l;
+    bf16* p2 = third_plane(hi, lo, planes);
+    if (p2) p2[idx] = __float2bfloat16_rn(v - __bfloat162float(h) - __bfloat162float(l));
 }
 
 // ---------------------------------------------------------------------------
@@ -77,7 +79,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict
 // ---------------------------------------------------------------------------
 __global__ void relu_maxpool_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                                         bf16* __restrict__ yh, bf16* __restrict__ yl,
-                                        int N, int H, int W, int C) {
+                                        int N, int H, int W, int C, int planes) {
     const int Ho = H / 2, Wo = W / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
@@ -88,11 +90,11 @@ __global__ void relu_maxpool_fwd_kernel(const bf16* __restrict__ xh, const bf16*
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
         const size_t off = ((static_cast<size_t>(n) * H + oh * 2 + (d >> 1)) * W + ow * 2 + (d & 1)) * C + cv * 8;
-        float v[8]; load8(xh, xl, off, v);
+        float v[8]; load8p(xh, xl, planes, off, v);
 #pragma unroll
         for (int i = 0; i < 8; ++i) m[i] = fmaxf(m[i], v[i]);
     }
-    store8(yh, yl, ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8, m);
+    store8p(yh, yl, planes, ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8, m);
 }
 
 // Backward of the above, fused with the loss gradient of the tap:
@@ -103,7 +105,7 @@ __global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16*
                                         const bf16* __restrict__ gyh, const bf16* __restrict__ gyl,
                                         const bf16* __restrict__ addh, const bf16* __restrict__ addl,
                                         bf16* __restrict__ gxh, bf16* __restrict__ gxl,
-                                        int N, int H, int W, int C) {
+                                        int N, int H, int W, int C, int x_planes) {
     const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
@@ -114,7 +116,7 @@ __global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16*
     for (int d = 0; d < 4; ++d) {
         const int h = oh * 2 + (d >> 1), w = ow * 2 + (d & 1);
         inb[d] = h < H && w < W;
-        if (inb[d]) load8(xh, xl, ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8, x[d]);
+        if (inb[d]) load8p(xh, xl, x_planes, ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8, x[d]);
     }
     float g[8];
 #pragma unroll
@@ -261,31 +263,31 @@ inline int grid_for(size_t n, int block, int cap_mult = 8) {
 
 }  // namespace
 
-int ew_nchw_to_nhwc(const float* a, const float* b, bf16* hi, bf16* lo, int N, int C1, int C2, int H, int W, int Cpad, cudaStream_t st) {
+int ew_nchw_to_nhwc(const float* a, const float* b, bf16* hi, bf16* lo, int planes, int N, int C1, int C2, int H, int W, int Cpad, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * H * W;
-    nchw_to_nhwc_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, hi, lo, N, C1, C2, H * W, Cpad);
+    nchw_to_nhwc_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, hi, lo, N, C1, C2, H * W, Cpad, planes);
     ST_CHECK_LAUNCH("nchw_to_nhwc_kernel"); return ST_OK;
 }
-int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
+int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, int planes, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * H * W;
-    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad);
+    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad, planes);
     ST_CHECK_LAUNCH("nhwc_to_nchw_kernel"); return ST_OK;
 }
-int ew_pack_weight(const float* w, bf16* hi, bf16* lo, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, cudaStream_t st) {
+int ew_pack_weight(const float* w, bf16* hi, bf16* lo, int planes, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, cudaStream_t st) {
     const int total = rows_pad * ks * ks * cols_pad;
-    pack_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, hi, lo, Cout, Cin, ks, rows_pad, cols_pad, mode);
+    pack_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, hi, lo, Cout, Cin, ks, rows_pad, cols_pad, mode, planes);
     ST_CHECK_LAUNCH("pack_weight_kernel"); return ST_OK;
 }
-int ew_relu_maxpool_fwd(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, int N, int H, int W, int C, cudaStream_t st) {
+int ew_relu_maxpool_fwd(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, int planes, int N, int H, int W, int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * (H / 2) * (W / 2) * (C / 8);
     if (n == 0) return ST_OK;
-    relu_maxpool_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, N, H, W, C);
+    relu_maxpool_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, N, H, W, C, planes);
     ST_CHECK_LAUNCH("relu_maxpool_fwd_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_bwd(const bf16* xh, const bf16* xl, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
-                        bf16* gxh, bf16* gxl, int N, int H, int W, int C, cudaStream_t st) {
+                        bf16* gxh, bf16* gxl, int x_planes, int N, int H, int W, int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
-    relu_maxpool_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C);
+    relu_maxpool_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C, x_planes);
     ST_CHECK_LAUNCH("relu_maxpool_bwd_kernel"); return ST_OK;
 }
 // workspace: >= 4096 floats

@@ -20,7 +20,7 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                 const bf16* __restrict__ gh, const bf16* __restrict__ gl,
                 const float* __restrict__ mean, const float* __restrict__ rstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
-                int HW, int W, int C, int splits, int chunk, int relu, int up,
+                int HW, int W, int C, int splits, int chunk, int relu, int up, int x_planes,
                 float* __restrict__ partial /* [N][splits][2][C] */) {
     extern __shared__ float sm[];                 // [lanes][2][C]
     const int n = blockIdx.x / splits, sp = blockIdx.x % splits;
@@ -41,7 +41,7 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
     if (pl < lanes) {
         for (int p = p0 + pl; p < p1; p += lanes) {
             float x[8];
-            load8(xh, xl, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
+            load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
             if (MODE == 0) {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { sa[i] += x[i]; sb[i] += x[i] * x[i]; }
@@ -124,7 +124,7 @@ __global__ void in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __r
                                     const float* __restrict__ mean, const float* __restrict__ rstd,
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     bf16* __restrict__ yh, bf16* __restrict__ yl,
-                                    int N, int H, int W, int C, int relu, int up) {
+                                    int N, int H, int W, int C, int relu, int up, int planes) {
     const int Cv = C / 8;
     const size_t total = static_cast<size_t>(N) * H * W * Cv;
     for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
@@ -132,7 +132,7 @@ __global__ void in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __r
         const int cv = idx % Cv; const size_t pix = idx / Cv;
         const int n = pix / (static_cast<size_t>(H) * W);
         float x[8];
-        load8(xh, xl, pix * C + cv * 8, x);
+        load8p(xh, xl, planes, pix * C + cv * 8, x);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int c = cv * 8 + i;
@@ -140,12 +140,12 @@ __global__ void in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __r
             x[i] = relu ? fmaxf(y, 0.f) : y;
         }
         if (!up) {
-            store8(yh, yl, pix * C + cv * 8, x);
+            store8p(yh, yl, planes, pix * C + cv * 8, x);
         } else {
             const int p = pix - static_cast<size_t>(n) * H * W; const int h = p / W, w = p - h * W;
 #pragma unroll
             for (int d = 0; d < 4; ++d)
-                store8(yh, yl, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, x);
+                store8p(yh, yl, planes, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, x);
         }
     }
 }
@@ -157,7 +157,7 @@ __global__ void in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __r
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const float* __restrict__ s1, const float* __restrict__ s2,
                                     bf16* __restrict__ dxh, bf16* __restrict__ dxl,
-                                    int N, int H, int W, int C, int relu, int up) {
+                                    int N, int H, int W, int C, int relu, int up, int x_planes) {
     const int Cv = C / 8, HW = H * W;
     const float inv_hw = 1.0f / HW;
     const size_t total = static_cast<size_t>(N) * HW * Cv;
@@ -166,7 +166,7 @@ __global__ void in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __r
         const int cv = idx % Cv; const size_t pix = idx / Cv;
         const int n = pix / HW;
         float x[8], g[8];
-        load8(xh, xl, pix * C + cv * 8, x);
+        load8p(xh, xl, x_planes, pix * C + cv * 8, x);
         if (!up) {
             load8(gh, gl, pix * C + cv * 8, g);
         } else {
@@ -291,25 +291,25 @@ inline int ew_grid(size_t n, int block) {
 size_t in_workspace_floats(int N, int C) { return static_cast<size_t>(N) * 64 * 2 * C; }
 
 int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* beta, float eps,
-               bf16* yh, bf16* yl, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
+               bf16* yh, bf16* yl, int planes, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
                float* ws, cudaStream_t st) {
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
     const int lanes = IN_THREADS / (C / 8);
     in_stats_kernel<0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, 0, ws);
+        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, 0, planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
     in_finalize_fwd_kernel<<<(N * C + 127) / 128, 128, 0, st>>>(ws, N * C, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
     in_apply_fwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
-        xh, xl, mean, rstd, gamma, beta, yh, yl, N, H, W, C, relu, up);
+        xh, xl, mean, rstd, gamma, beta, yh, yl, N, H, W, C, relu, up, planes);
     ST_CHECK_LAUNCH("in_apply_fwd_kernel");
     return ST_OK;
 }
 
 int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
                 const float* mean, const float* rstd, const float* gamma, const float* beta,
-                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, int N, int H, int W, int C, int relu, int up,
+                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, int x_planes, int N, int H, int W, int C, int relu, int up,
                 float* ws, cudaStream_t st) {
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
@@ -317,12 +317,12 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
     float* s1 = ws + static_cast<size_t>(N) * splits * 2 * C;
     float* s2 = s1 + static_cast<size_t>(N) * C;
     in_stats_kernel<1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-        xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, up, ws);
+        xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, up, x_planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
     in_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
     in_apply_bwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
-        xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, N, H, W, C, relu, up);
+        xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, N, H, W, C, relu, up, x_planes);
     ST_CHECK_LAUNCH("in_apply_bwd_kernel");
     return ST_OK;
 }

@@ -248,12 +248,13 @@ class StyleNetwork(nn.Module):
 
     @staticmethod
     def _relu_split(tap):
+        """relu of a Split (the ReLU_4 feature target).  Off the hot path (targets only)."""
         out = tap.like()
-        v = tap.float().clamp_(min=0)
-        hi = v.to(torch.bfloat16)
-        out.buf[0].copy_(hi)
-        if out.lo is not None:
-            out.buf[1].copy_((v - hi.float()).to(torch.bfloat16))
+        rest = tap.float().clamp_(min=0)
+        for p in range(out.planes):
+            plane = rest.to(torch.bfloat16)
+            out.buf[p].copy_(plane)
+            rest = rest - plane.float()
         return out
 
     @staticmethod

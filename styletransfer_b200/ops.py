@@ -6,15 +6,28 @@ import torch
 
 from . import _lib
 
-# 'bf16x3': hi+lo planes, 3 tensor-core passes per product (parity grade, default)
-# 'bf16'  : hi plane only, 1 pass (fast, ~3e-2 error on the Gatys gradient)
-PRECISION = 'bf16x3'
+# precision mode -> (planes of forward activations/weights, planes of gradients)
+#  'bf16x6': forward 3 planes / 6 tensor-core passes per product, backward 2 planes / 3 passes.
+#            Parity grade (default): forward values are fp32-accurate, so ReLU masks and
+#            max-pool argmaxes agree with the reference (each flip costs a whole gradient entry).
+#  'bf16x3': 2 planes / 3 passes everywhere (loss 1e-5, gradient ~2e-3 at >= 128^2 images)
+#  'bf16'  : 1 plane / 1 pass (fast, ~3e-2 error on the Gatys gradient)
+_MODES = {'bf16x6': (3, 2), 'bf16x3': (2, 2), 'bf16': (1, 1)}
+PRECISION = 'bf16x6'
 
 
 def set_precision(mode):
     global PRECISION
-    assert mode in ('bf16x3', 'bf16')
+    assert mode in _MODES
     PRECISION = mode
+
+
+def fwd_planes():
+    return _MODES[PRECISION][0]
+
+
+def bwd_planes():
+    return _MODES[PRECISION][1]
 
 
 def _stream():
@@ -32,15 +45,15 @@ def pad8(c):
 
 class Split:
     """NHWC activation stored as bf16 hi (+ lo) planes in one allocation."""
-    __slots__ = ('buf', 'N', 'H', 'W', 'C', 'hi', 'lo')
+    __slots__ = ('buf', 'N', 'H', 'W', 'C', 'hi', 'lo', 'planes')
 
-    def __init__(self, N, H, W, C, device, lo=None, zero=False):
-        lo = (PRECISION == 'bf16x3') if lo is None else lo
+    def __init__(self, N, H, W, C, device, planes=None, zero=False):
+        planes = fwd_planes() if planes is None else planes
         alloc = torch.zeros if zero else torch.empty
-        self.buf = alloc((2 if lo else 1, N, H, W, C), dtype=torch.bfloat16, device=device)
-        self.N, self.H, self.W, self.C = N, H, W, C
+        self.buf = alloc((planes, N, H, W, C), dtype=torch.bfloat16, device=device)
+        self.N, self.H, self.W, self.C, self.planes = N, H, W, C, planes
         self.hi = self.buf[0].data_ptr()
-        self.lo = self.buf[1].data_ptr() if lo else None
+        self.lo = self.buf[1].data_ptr() if planes > 1 else None   # plane 3 sits at lo + (lo - hi)
 
     @property
     def shape(self):
@@ -49,17 +62,22 @@ class Split:
     def float(self):
         """fp32 NHWC view of the value (hi + lo) -- for tests/debugging."""
         v = self.buf[0].float()
-        return v + self.buf[1].float() if self.buf.shape[0] == 2 else v
+        for p in range(1, self.planes):
+            v = v + self.buf[p].float()
+        return v
 
     def like(self):
-        return Split(self.N, self.H, self.W, self.C, self.buf.device, lo=self.lo is not None)
+        return Split(self.N, self.H, self.W, self.C, self.buf.device, planes=self.planes)
+
+    def grad_like(self):
+        return Split(self.N, self.H, self.W, self.C, self.buf.device, planes=bwd_planes())
 
 
 def _p(t):
     return None if t is None else t.data_ptr()
 
 
-def from_nchw(x, x2=None, cpad=None):
+def from_nchw(x, x2=None, cpad=None, planes=None):
     """NCHW fp32 -> Split (channel-concat of x and x2, padded with zeros to cpad)."""
     _require_cuda(x, 'from_nchw')
     x = x.contiguous().float()
@@ -69,8 +87,8 @@ def from_nchw(x, x2=None, cpad=None):
         x2 = x2.contiguous().float()
         C2 = x2.shape[1]
     cpad = cpad or pad8(C1 + C2)
-    out = Split(N, H, W, cpad, x.device)
-    _lib.check(_lib.lib().st_nchw_to_nhwc(x.data_ptr(), _p(x2), out.hi, out.lo, N, C1, C2, H, W, cpad, _stream()),
+    out = Split(N, H, W, cpad, x.device, planes=planes)
+    _lib.check(_lib.lib().st_nchw_to_nhwc(x.data_ptr(), _p(x2), out.hi, out.lo, out.planes, N, C1, C2, H, W, cpad, _stream()),
                'st_nchw_to_nhwc')
     return out
 
@@ -78,26 +96,27 @@ def from_nchw(x, x2=None, cpad=None):
 def to_nchw(s, C=None):
     C = C or s.C
     out = torch.empty((s.N, C, s.H, s.W), dtype=torch.float32, device=s.buf.device)
-    _lib.check(_lib.lib().st_nhwc_to_nchw(s.hi, s.lo, out.data_ptr(), s.N, C, s.H, s.W, s.C, _stream()), 'st_nhwc_to_nchw')
+    _lib.check(_lib.lib().st_nhwc_to_nchw(s.hi, s.lo, s.planes, out.data_ptr(), s.N, C, s.H, s.W, s.C, _stream()), 'st_nhwc_to_nchw')
     return out
 
 
 class PackedWeight:
     """nn.Conv2d weight packed for one of the conv modes (see st_pack_conv_weight)."""
-    __slots__ = ('buf', 'hi', 'lo', 'rows', 'cols', 'ks', 'mode', 'cout', 'cin')
+    __slots__ = ('buf', 'hi', 'lo', 'rows', 'cols', 'ks', 'mode', 'cout', 'cin', 'planes')
 
-    def __init__(self, w, mode, rows_pad=None, cols_pad=None):
+    def __init__(self, w, mode, rows_pad=None, cols_pad=None, planes=None):
         _require_cuda(w, 'PackedWeight')
         w = w.detach().contiguous().float()
         cout, cin, ks, _ = w.shape
         rows, cols = (cout, cin) if mode == 0 else (cin, cout)
         self.rows, self.cols = rows_pad or pad8(rows), cols_pad or pad8(cols)
         self.ks, self.mode, self.cout, self.cin = ks, mode, cout, cin
-        lo = PRECISION == 'bf16x3'
-        self.buf = torch.empty((2 if lo else 1, self.rows, ks * ks, self.cols), dtype=torch.bfloat16, device=w.device)
+        # forward weights carry the forward precision, backward-data weights the gradient precision
+        self.planes = planes or (fwd_planes() if mode == 0 else bwd_planes())
+        self.buf = torch.empty((self.planes, self.rows, ks * ks, self.cols), dtype=torch.bfloat16, device=w.device)
         self.hi = self.buf[0].data_ptr()
-        self.lo = self.buf[1].data_ptr() if lo else None
-        _lib.check(_lib.lib().st_pack_conv_weight(w.data_ptr(), self.hi, self.lo, cout, cin, ks, self.rows, self.cols,
+        self.lo = self.buf[1].data_ptr() if self.planes > 1 else None
+        _lib.check(_lib.lib().st_pack_conv_weight(w.data_ptr(), self.hi, self.lo, self.planes, cout, cin, ks, self.rows, self.cols,
                                                   mode, _stream()), 'st_pack_conv_weight')
 
 
@@ -108,10 +127,14 @@ def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
     Returns (out Split|None, relu Split|None, out_nchw Tensor|None)."""
     if w is not None:
         w_hi, w_lo, rows_total, ks, cols = w.hi, w.lo, w.rows, w.ks, w.cols
-        cout_pad = w.rows
+        cout_pad, w_planes, forward = w.rows, w.planes, w.mode == 0
     else:
         w_hi, w_lo, rows_total, ks, cols = w_ptrs
-        cout_pad = w_img_rows
+        cout_pad, w_planes, forward = w_img_rows, (2 if w_lo else 1), False
+    # forward convs run at the forward precision; backward convs read at most the
+    # gradient precision from their (possibly 3-plane) operands
+    out_planes = fwd_planes() if forward else bwd_planes()
+    x_planes = x.planes if forward else min(x.planes, bwd_planes())
     assert cols == x.C, f'weight expects {cols} input channels, activation has {x.C}'
     pad = ks // 2 if pad is None else pad
     Hl, Wl = x.H << up, x.W << up
@@ -122,18 +145,18 @@ def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
     else:
         Ho, Wo = (Hl + 2 * pad - ks) // stride + 1, (Wl + 2 * pad - ks) // stride + 1
     dev = x.buf.device
-    out = Split(x.N, Ho, Wo, cout_pad, dev) if want_out else None
-    relu = Split(x.N, Ho, Wo, cout_pad, dev) if want_relu else None
+    out = Split(x.N, Ho, Wo, cout_pad, dev, planes=out_planes) if want_out else None
+    relu = Split(x.N, Ho, Wo, cout_pad, dev, planes=out_planes) if want_relu else None
     nchw = torch.empty((x.N, out_nchw_channels, Ho, Wo), dtype=torch.float32, device=dev) if out_nchw_channels else None
     for t in (mask, add):
         assert t is None or t.shape == (x.N, Ho, Wo, cout_pad), 'mask/add shape mismatch'
     cbias = 0 if bias is None else bias.numel()
     _lib.check(_lib.lib().st_conv2d(
-        x.hi, x.lo, x.N, x.H, x.W, x.C, up, w_hi, w_lo, rows_total, w_img_rows, ks, stride, pad, transposed,
+        x.hi, x.lo if x_planes > 1 else None, x_planes, x.N, x.H, x.W, x.C, up, w_hi, w_lo, w_planes, rows_total, w_img_rows, ks, stride, pad, transposed,
         Ho, Wo, cout_pad, cbias, _p(bias), mask.hi if mask else None,
         add.hi if add else None, add.lo if add else None,
         out.hi if out else None, out.lo if out else None, relu.hi if relu else None, relu.lo if relu else None,
-        _p(nchw), out_nchw_channels, _stream()), 'st_conv2d')
+        out_planes, _p(nchw), out_nchw_channels, _stream()), 'st_conv2d')
     return out, relu, nchw
 
 
@@ -163,15 +186,15 @@ def conv2d_wgrad(dy, x, ks, stride, pad, up, cout, cin, want_bias=True):
 
 
 def relu_maxpool_fwd(x):
-    y = Split(x.N, x.H // 2, x.W // 2, x.C, x.buf.device)
-    _lib.check(_lib.lib().st_relu_maxpool2x2_fwd(x.hi, x.lo, y.hi, y.lo, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_fwd')
+    y = Split(x.N, x.H // 2, x.W // 2, x.C, x.buf.device, planes=x.planes)
+    _lib.check(_lib.lib().st_relu_maxpool2x2_fwd(x.hi, x.lo, y.hi, y.lo, x.planes, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_fwd')
     return y
 
 
 def relu_maxpool_bwd(x, gy, add=None):
-    gx = x.like()
+    gx = x.grad_like()
     _lib.check(_lib.lib().st_relu_maxpool2x2_bwd(x.hi, x.lo, gy.hi, gy.lo, add.hi if add else None, add.lo if add else None,
-                                                 gx.hi, gx.lo, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_bwd')
+                                                 gx.hi, gx.lo, x.planes, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_bwd')
     return gx
 
 
@@ -200,7 +223,7 @@ def style_mse_fwd(G, T, loss_out):
 def style_seed(diff, HW, gw):
     """Packed per-image weights D = gw * 4/(B C^2 C HW) * diff for the dF = F*D conv."""
     B, C, _ = diff.shape
-    lo = PRECISION == 'bf16x3'
+    lo = bwd_planes() > 1
     buf = torch.empty((2 if lo else 1, B * C, C), dtype=torch.bfloat16, device=diff.device)
     hi, lo_p = buf[0].data_ptr(), (buf[1].data_ptr() if lo else None)
     _lib.check(_lib.lib().st_style_mse_bwd_seed(diff.data_ptr(), B, C, HW, gw.data_ptr(), hi, lo_p, _stream()),
@@ -217,7 +240,7 @@ def mse_fwd(x, t, loss_out, relu=False, feature_form=False):
 
 def mse_bwd(x, t, gw, scale, out=None, relu=False, mul=None):
     acc = out is not None
-    out = out or x.like()
+    out = out or x.grad_like()
     n = x.buf[0].numel()
     _lib.check(_lib.lib().st_mse_bwd(x.hi, x.lo, t.hi, t.lo, n, int(relu), float(scale), gw.data_ptr(), _p(mul), int(acc),
                                      out.hi, out.lo, _stream()), 'st_mse_bwd')
@@ -228,9 +251,9 @@ def instnorm_fwd(x, gamma, beta, relu=False, up=False, eps=1e-5):
     L = _lib.lib()
     dev = x.buf.device
     ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
-    y = Split(x.N, x.H << int(up), x.W << int(up), x.C, dev)
+    y = Split(x.N, x.H << int(up), x.W << int(up), x.C, dev, planes=x.planes)
     stats = torch.empty((2, x.N, x.C), dtype=torch.float32, device=dev)
-    _lib.check(L.st_instnorm_fwd(x.hi, x.lo, gamma.data_ptr(), beta.data_ptr(), eps, y.hi, y.lo,
+    _lib.check(L.st_instnorm_fwd(x.hi, x.lo, gamma.data_ptr(), beta.data_ptr(), eps, y.hi, y.lo, x.planes,
                                  stats[0].data_ptr(), stats[1].data_ptr(), x.N, x.H, x.W, x.C, int(relu), int(up),
                                  ws.data_ptr(), _stream()), 'st_instnorm_fwd')
     return y, stats
@@ -240,11 +263,11 @@ def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False):
     L = _lib.lib()
     dev = x.buf.device
     ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
-    dx = x.like()
+    dx = x.grad_like()
     dgamma = torch.empty_like(gamma)
     dbeta = torch.empty_like(beta)
     _lib.check(L.st_instnorm_bwd(x.hi, x.lo, gy.hi, gy.lo, stats[0].data_ptr(), stats[1].data_ptr(),
-                                 gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(),
+                                 gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(), x.planes,
                                  x.N, x.H, x.W, x.C, int(relu), int(up), ws.data_ptr(), _stream()), 'st_instnorm_bwd')
     return dx, dgamma, dbeta
 

@@ -106,8 +106,8 @@ def test_library_exports_every_declared_symbol():
     L = _lib.lib()
     assert L.st_arch() == 100
     # argument validation happens before any CUDA call
-    assert L.st_conv2d(None, None, 1, 8, 8, 8, 0, None, None, 8, 0, 3, 1, 1, 0, 8, 8, 8, 0,
-                       None, None, None, None, None, None, None, None, None, 0, None) == -1
+    assert L.st_conv2d(None, None, 1, 1, 8, 8, 8, 0, None, None, 1, 8, 0, 3, 1, 1, 0, 8, 8, 8, 0,
+                       None, None, None, None, None, None, None, None, 1, None, 0, None) == -1
     assert b'null' in L.st_last_error()
     assert L.st_instnorm_workspace_bytes(4, 128) > 0
     assert L.st_gram_workspace_bytes(1, 512 * 512, 64) > 0

@@ -22,7 +22,7 @@ TOL_FEATURE, TOL_LOSS_GRAD = 1e-2, 1e-3
 @pytest.fixture(scope='module')
 def net_mod():
     from styletransfer_b200 import network, ops
-    ops.set_precision('bf16x3')
+    ops.set_precision('bf16x6')
     return network
 
 
