@@ -14,7 +14,7 @@ import torch.nn as nn
 import torch.optim as optim
 from tqdm import tqdm
 
-from . import c_logging, constants, ops, vgg_loss
+from . import c_logging, constants, ops, transform, vgg_loss
 from ._lib import StransferError
 
 LOGGER = c_logging.get_logger()
@@ -362,3 +362,396 @@ class StyleNetwork(nn.Module):
             optimizer.step(closure)
         self.compute_feature_loss = True
         return input_image
+
+
+# --------------------------------------------------------------------------
+# transform-net building blocks (reference network.py:461-611)
+# --------------------------------------------------------------------------
+class _ConvFn(torch.autograd.Function):
+    """Stand-alone nn.Conv2d replacement (NCHW fp32 boundary) on the conv kernels."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride):
+        xs = ops.from_nchw(x, cpad=ops.pad8(x.shape[1]))
+        pw = ops.PackedWeight(weight, 0, cols_pad=xs.C)
+        _, _, y = ops.conv2d(xs, pw, bias, stride=stride, want_out=False, out_nchw_channels=weight.shape[0])
+        ctx.xs, ctx.weight, ctx.stride, ctx.cin = xs, weight, stride, x.shape[1]
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xs, w, stride = ctx.xs, ctx.weight, ctx.stride
+        cout, cin, k, _ = w.shape
+        g = ops.from_nchw(gy.contiguous().float(), cpad=ops.pad8(cout), planes=ops.bwd_planes())
+        dw, db = ops.conv2d_wgrad(g, xs, k, stride, k // 2, 0, cout, cin)
+        gx = None
+        if ctx.needs_input_grad[0]:
+            pw = ops.PackedWeight(w, 1, rows_pad=xs.C, cols_pad=g.C)
+            _, _, gx = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xs.H, xs.W), want_out=False,
+                                  out_nchw_channels=cin)
+        return gx, dw, db, None
+
+
+class Conv2d(nn.Module):
+    """Parameter container + stand-alone forward with nn.Conv2d's names, shapes and default
+    init (kaiming-uniform a=sqrt(5)); zero padding of k//2 (the reference's effective
+    arithmetic).  Inside ImageTransformNet the fused path is used instead."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=None, padding_mode='zeros'):
+        super().__init__()
+        import math
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.kernel_size, self.stride = kernel_size, stride
+        self.padding = kernel_size // 2 if padding is None else padding
+        assert self.padding == kernel_size // 2, 'the kernels implement "same" padding (k // 2)'
+        self.padding_mode = 'zeros'          # 'reflection' ran as zeros in the reference (torch 1.1.0)
+        self.weight = nn.Parameter(torch.empty(out_channels, in_channels, kernel_size, kernel_size))
+        self.bias = nn.Parameter(torch.empty(out_channels))
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        bound = 1.0 / math.sqrt(in_channels * kernel_size * kernel_size)
+        nn.init.uniform_(self.bias, -bound, bound)
+
+    def forward(self, x):
+        ops._require_cuda(x, 'Conv2d.forward')
+        return _ConvFn.apply(x.contiguous().float(), self.weight, self.bias, self.stride)
+
+
+class _InstanceNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        xs = ops.from_nchw(x)
+        ys, stats = ops.instnorm_fwd(xs, gamma, beta, eps=eps)
+        ctx.xs, ctx.stats, ctx.gamma, ctx.beta, ctx.C = xs, stats, gamma, beta, x.shape[1]
+        return ops.to_nchw(ys, x.shape[1])
+
+    @staticmethod
+    def backward(ctx, gy):
+        g = ops.from_nchw(gy.contiguous().float(), planes=ops.bwd_planes())
+        dx, dg, db = ops.instnorm_bwd(ctx.xs, g, ctx.stats, ctx.gamma, ctx.beta)
+        return ops.to_nchw(dx, ctx.C), dg, db, None
+
+
+class InstanceNorm2d(nn.Module):
+    """nn.InstanceNorm2d(affine=True, track_running_stats=False) (network.py:474, :483)."""
+
+    def __init__(self, num_features, eps=1e-5, affine=True):
+        super().__init__()
+        assert affine, 'the reference only uses affine instance norms'
+        self.num_features, self.eps = num_features, eps
+        self.weight = nn.Parameter(torch.ones(num_features))
+        self.bias = nn.Parameter(torch.zeros(num_features))
+
+    def forward(self, x):
+        ops._require_cuda(x, 'InstanceNorm2d.forward')
+        return _InstanceNormFn.apply(x.contiguous().float(), self.weight, self.bias, self.eps)
+
+
+class ResidualBlock(nn.Module):
+    """network.py:461-506: conv -> IN -> ReLU -> conv -> (+= x) -> IN, no trailing ReLU."""
+
+    def __init__(self, in_channels, out_channels, kernel_size=3, stride=1):
+        super().__init__()
+        self.conv1 = Conv2d(in_channels, out_channels, kernel_size, stride)
+        self.insn1 = InstanceNorm2d(out_channels, affine=True)
+        self.relu = nn.ReLU()
+        self.conv2 = Conv2d(out_channels, out_channels, kernel_size, stride)
+        self.insn2 = InstanceNorm2d(out_channels, affine=True)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        residual = x
+        out = self.relu(self.insn1(self.conv1(x)))
+        out = self.conv2(out)
+        out = out + residual
+        return self.insn2(out)
+
+
+# --------------------------------------------------------------------------
+# total-variation / temporal losses as autograd functions (network.py:621-641, :885-903)
+# --------------------------------------------------------------------------
+class _TVFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, factor):
+        ctx.x, ctx.factor = x, factor
+        return ops.tv_fwd(x, factor)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.tv_bwd(ctx.x, ctx.factor, g.reshape(1).contiguous().float()), None
+
+
+class _TemporalFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, old_content, old_stylized, cur_content, cur_stylized, tw):
+        out3 = ops.temporal_fwd(old_content, old_stylized, cur_content, cur_stylized, tw)
+        ctx.os, ctx.cs, ctx.tw, ctx.out3 = old_stylized, cur_stylized, tw, out3
+        return out3[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        gs = ops.temporal_bwd(ctx.os, ctx.cs, ctx.tw, ctx.out3, g.reshape(1).contiguous().float())
+        return None, None, None, gs, None
+
+
+# --------------------------------------------------------------------------
+# ImageTransformNet (reference network.py:509-832)
+# --------------------------------------------------------------------------
+class ImageTransformNet(nn.Sequential):
+    """network.py:509-832.  Same 23 modules / 62 state-dict tensors as the reference; the
+    forward runs the fused split-bf16 pipeline of ``transform.TransformNetFn``."""
+
+    def __init__(self, style_image: torch.Tensor, batch_size=4):
+        super().__init__(
+            Conv2d(3, 32, 9, 1), InstanceNorm2d(32, affine=True), nn.ReLU(),
+            Conv2d(32, 64, 3, 2), InstanceNorm2d(64, affine=True), nn.ReLU(),
+            Conv2d(64, 128, 3, 2), InstanceNorm2d(128, affine=True), nn.ReLU(),
+            ResidualBlock(128, 128, 3), ResidualBlock(128, 128, 3), ResidualBlock(128, 128, 3),
+            ResidualBlock(128, 128, 3), ResidualBlock(128, 128, 3),
+            nn.Upsample(mode='nearest', scale_factor=2),
+            Conv2d(128, 64, 3, 1), InstanceNorm2d(64, affine=True), nn.ReLU(),
+            nn.Upsample(mode='nearest', scale_factor=2),
+            Conv2d(64, 32, 3, 1), InstanceNorm2d(32, affine=True), nn.ReLU(),
+            Conv2d(32, 3, 9, 1),
+        )
+        assert isinstance(style_image, torch.Tensor), 'Style image need to be already loaded'
+        self.style_image = style_image
+        self.batch_size = batch_size
+        self._pack_cache = transform._PackCache()
+
+    def forward(self, input: torch.Tensor) -> torch.Tensor:
+        ops._require_cuda(input, type(self).__name__ + '.forward')
+        sd = dict(self.named_parameters())
+        params = [sd[n] for n in transform.PARAM_NAMES]
+        return transform.TransformNetFn.apply(input.contiguous().float(), self._pack_cache, *params)
+
+    def get_total_variation_regularization_loss(self, transformed_image: torch.Tensor,
+                                                regularization_factor=1e-6) -> torch.Tensor:
+        """network.py:621-641"""
+        ops._require_cuda(transformed_image, 'get_total_variation_regularization_loss')
+        return _TVFn.apply(transformed_image.contiguous().float(), float(regularization_factor))
+
+    def get_optimizer(self, optimizer=optim.Adam):
+        """network.py:643-649"""
+        return optimizer(self.parameters())
+
+    # -- the closure body of static_train (network.py:690-731), factored out so that the
+    #    benchmark and the parity tests run exactly what the training loop runs
+    def closure_loss(self, batch, loss_network, style_weight=100_000, content_weight=1):
+        transformed_image = self(batch)
+        loss_network(transformed_image, content_image=batch)
+        style_loss = loss_network.get_total_current_style_loss(weight=style_weight)
+        content_loss = loss_network.get_total_current_content_loss(weight=content_weight)
+        regularization_loss = self.get_total_variation_regularization_loss(transformed_image)
+        return style_loss + content_loss + regularization_loss, transformed_image
+
+    def static_train(self, style_name='nsp', epochs=50, style_weight=100_000, content_weight=1,
+                     train_loader=None, test_loader=None, max_iterations=None):
+        """network.py:651-770.  ``train_loader`` / ``test_loader`` (extra, optional) replace the
+        COCO loaders -- the dataset download is host glue outside the hot path."""
+        from . import dataset
+        tb_writer = get_tensorboard_writer(f'runs/fast-image-style-transfer-still-image_{style_name}')
+        loss_network = StyleNetwork(self.style_image, torch.rand([1, 3, 256, 256]).to(constants.DEVICE))
+        loss_network.compute_feature_loss = False        # the training closure never reads it
+        optimizer = self.get_optimizer(optimizer=optim.Adam)
+        LOGGER.info('Training network with "%s" optimizer', type(optimizer))
+        iteration = 0
+        if train_loader is None:
+            test_loader, train_loader = dataset.get_coco_loader(test_split=0.10, test_limit=20,
+                                                                batch_size=self.batch_size)
+        for epoch in range(epochs):
+            LOGGER.info('Starting epoch %d', epoch)
+            epoch_checkpoint_name = os.path.join(constants.PROJECT_ROOT_PATH,
+                                                 f'data/models/fast_st_{style_name}_epoch{epoch}.pth')
+            if os.path.isfile(epoch_checkpoint_name):
+                self.load_state_dict(adaptive_torch_load(epoch_checkpoint_name))
+                continue
+            for batch in tqdm(train_loader):
+                batch = batch.squeeze(1).to(constants.DEVICE)
+
+                def closure():
+                    optimizer.zero_grad()
+                    total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight)
+                    total_loss.backward()
+                    return total_loss
+
+                if iteration % 20 == 0:
+                    total_loss = closure()
+                    tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
+                    LOGGER.info('Batch Loss: %.8f', total_loss)
+                if iteration % 150 == 0 and test_loader is not None:
+                    average_test_loss = self.static_test(test_loader, loss_network)
+                    tb_writer.add_scalar('data/fst_test_loss', average_test_loss, iteration)
+                iteration += 1
+                optimizer.step(closure)
+                if max_iterations is not None and iteration >= max_iterations:
+                    return
+            os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
+            torch.save(self.state_dict(), epoch_checkpoint_name)
+
+    def static_test(self, test_loader, loss_network, style_weight=100_000, feature_weight=1):
+        """network.py:772-796"""
+        total_test_loss = []
+        prev = loss_network.compute_feature_loss
+        loss_network.compute_feature_loss = True
+        with torch.no_grad():
+            for test_batch in test_loader:
+                test_batch = test_batch.squeeze(1).to(constants.DEVICE)
+                transformed_image = torch.clamp(self(test_batch), min=0, max=255)
+                loss_network(transformed_image, content_image=test_batch)
+                style_loss = style_weight * loss_network.get_total_current_style_loss()
+                feature_loss = feature_weight * loss_network.get_total_current_feature_loss()
+                total_test_loss.append((style_loss + feature_loss).item())
+        loss_network.compute_feature_loss = prev
+        average_test_loss = torch.mean(torch.Tensor(total_test_loss))
+        LOGGER.info('Average test loss: %.8f', average_test_loss)
+        return average_test_loss
+
+    def process_image(self, image_path: str, style_name='nsp', out_dir='results/') -> None:
+        """network.py:798-832"""
+        from . import img_utils
+        self.load_state_dict(_load_latest_model_weigths(model_name='fast_st', style_name=style_name))
+        input_image = img_utils.image_loader(os.path.join(constants.PROJECT_ROOT_PATH, image_path))
+        with torch.no_grad():
+            transformed_image = self(input_image)
+        out_dir = os.path.join(constants.PROJECT_ROOT_PATH, out_dir)
+        os.makedirs(out_dir, exist_ok=True)
+        out_file = os.path.join(out_dir, f'converted_fast_st_{style_name}.png')
+        img_utils.imshow(transformed_image, path=out_file)
+
+
+# --------------------------------------------------------------------------
+# VideoTransformNet (reference network.py:835-1158)
+# --------------------------------------------------------------------------
+class VideoTransformNet(ImageTransformNet):
+    """network.py:835-1158: 6-channel first conv (frame_t ++ stylised_{t-1}), optional warm
+    start from a fast_st state dict, temporal loss."""
+
+    def __init__(self, style_image: torch.Tensor, batch_size=4, fast_transfer_dict=None):
+        super().__init__(style_image, batch_size)
+        self[0] = Conv2d(6, 32, 9, 1)
+        if fast_transfer_dict is not None:
+            if isinstance(fast_transfer_dict, str):
+                fast_transfer_dict = adaptive_torch_load(fast_transfer_dict)
+            del fast_transfer_dict['0.weight']
+            del fast_transfer_dict['0.bias']
+            m_sd = self.state_dict().copy()
+            m_sd.update(fast_transfer_dict)
+            self.load_state_dict(m_sd)
+            self.has_external_weights = True
+        else:
+            self.has_external_weights = False
+
+    def get_temporal_loss(self, old_content, old_stylized, current_content, current_stylized,
+                          temporal_weight=1) -> torch.Tensor:
+        """network.py:885-903: tw * ||cur_sty - old_sty|| / (||cur_con - old_con|| + 1); the
+        gradient flows into ``current_stylized`` only."""
+        ops._require_cuda(current_stylized, 'get_temporal_loss')
+        c = lambda t: t.detach().contiguous().float()
+        return _TemporalFn.apply(c(old_content), c(old_stylized), c(current_content),
+                                 current_stylized.contiguous().float(), float(temporal_weight))
+
+    def closure_loss_video(self, batch, old_images, loss_network, temporal_weight=0.8,
+                           style_weight=100_000, content_weight=1):
+        """Closure body of video_train (network.py:984-1037); updates ``old_images`` in place."""
+        old_content_images, old_styled_images = old_images
+        batch_with_old_content = torch.cat([batch, old_styled_images], dim=1)
+        transformed_image = self(batch_with_old_content)
+        loss_network(transformed_image, content_image=batch)
+        style_loss = loss_network.get_total_current_style_loss(weight=style_weight)
+        content_loss = loss_network.get_total_current_content_loss(weight=content_weight)
+        regularization_loss = self.get_total_variation_regularization_loss(transformed_image)
+        temporal_loss = self.get_temporal_loss(old_content_images, old_styled_images, batch, transformed_image,
+                                               temporal_weight=temporal_weight)
+        total_loss = style_loss + content_loss + regularization_loss + temporal_loss
+        old_images[0] = batch.detach()
+        old_images[1] = transformed_image.detach()
+        return total_loss, transformed_image
+
+    def video_train(self, style_name='nsp', epochs=50, temporal_weight=0.8, style_weight=100_000,
+                    feature_weight=1, content_weight=1, video_loader=None, max_iterations=None) -> None:
+        """network.py:905-1069.  ``video_loader`` (extra, optional): an iterable of clips, each an
+        iterable of frame batches [B,3,H,W] (replaces VideoDataset + iterate_on_video_batches)."""
+        from . import dataset
+        tb_writer = get_tensorboard_writer(f'runs/video-style-transfer_{style_name}')
+        style_loss_network = StyleNetwork(self.style_image, torch.rand([1, 3, 256, 256]).to(constants.DEVICE))
+        style_loss_network.compute_feature_loss = False
+        optimizer = self.get_optimizer(optimizer=optim.Adam)
+        LOGGER.info('Training video network with "%s" optimizer', type(optimizer))
+        iteration = 0
+        if video_loader is None:
+            video_loader = dataset.VideoDataset(batch_size=self.batch_size)
+        for epoch in range(epochs):
+            if epoch == 0 and self.has_external_weights:
+                LOGGER.info('Freezing weights imported from fast transfer network for the first epoch')
+                for name, param in self.named_parameters():
+                    if not name.startswith('0.'):
+                        param.requires_grad = False
+            if epoch == 1 and self.has_external_weights:
+                LOGGER.info('Unfreezing all weights')
+                for param in self.parameters():
+                    param.requires_grad = True
+            epoch_checkpoint_name = os.path.join(constants.PROJECT_ROOT_PATH,
+                                                 f'data/models/video_st_{style_name}_epoch{epoch}.pth')
+            if os.path.isfile(epoch_checkpoint_name):
+                self.load_state_dict(adaptive_torch_load(epoch_checkpoint_name))
+                continue
+            LOGGER.info('Starting epoch %d', epoch)
+            for video_batch in video_loader:
+                old_images = None
+                for batch in dataset.iterate_on_video_batches(video_batch):
+                    batch = batch.to(constants.DEVICE)
+                    if old_images is None:
+                        old_images = [batch, batch]
+                    # the closure reads the previous frame's images as they were BEFORE this
+                    # iteration (network.py:980-986 binds them outside the closure)
+                    frozen = [old_images[0], old_images[1]]
+
+                    def closure():
+                        optimizer.zero_grad()
+                        state = [frozen[0], frozen[1]]
+                        total_loss, _ = self.closure_loss_video(batch, state, style_loss_network, temporal_weight,
+                                                                style_weight, content_weight)
+                        old_images[0], old_images[1] = state
+                        total_loss.backward()
+                        return total_loss
+
+                    if iteration % 20 == 0:
+                        total_loss = closure()
+                        tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
+                        LOGGER.info('Epoch: %d\tBatch Loss: %.4f', epoch, total_loss)
+                    iteration += 1
+                    optimizer.step(closure)
+                    if max_iterations is not None and iteration >= max_iterations:
+                        return
+            os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
+            torch.save(self.state_dict(), epoch_checkpoint_name)
+
+    def process_video(self, video_path: str, style_name='nsp', working_dir='workdir/', out_dir='results/',
+                      fps=24.0, frames=None):
+        """network.py:1071-1158.  The recurrent per-frame forward is the hot path; decoding the
+        input video and muxing the mp4 need imageio (not in this image): ``frames`` (extra,
+        optional) supplies an iterable of [1,3,H,W] tensors and the stylised frames are written
+        as PNGs into ``working_dir``."""
+        from . import dataset, img_utils
+        working_dir = os.path.join(constants.PROJECT_ROOT_PATH, working_dir)
+        self.load_state_dict(_load_latest_model_weigths(model_name='video_st', style_name=style_name))
+        if frames is None:
+            frames = dataset.iterate_on_video_batches([dataset.open_video(os.path.join(constants.PROJECT_ROOT_PATH, video_path))])
+        shutil.rmtree(working_dir, ignore_errors=True)
+        os.makedirs(working_dir, exist_ok=True)
+        old_image = None
+        LOGGER.info('Starting to process video into stylized frames')
+        outputs = []
+        with torch.no_grad():
+            for i, video_frame in enumerate(frames):
+                video_frame = video_frame.to(constants.DEVICE)
+                if old_image is None:
+                    old_image = video_frame
+                transformed_image = self(torch.cat([video_frame, old_image], dim=1))
+                old_image = transformed_image.detach()
+                outputs.append(transformed_image)
+                img_utils.imshow(transformed_image[0], path=f'{working_dir}{i}.png')
+                if i % 50 == 0:
+                    LOGGER.info('.. processing, currently frame %d', i)
+        LOGGER.info('All frames have been stylized.')
+        dataset.write_video(working_dir, os.path.join(constants.PROJECT_ROOT_PATH, out_dir), f'video_st_{style_name}.mp4', fps)
+        return outputs

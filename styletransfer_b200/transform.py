@@ -1,0 +1,196 @@
+"""Fused forward/backward of the Johnson transform net on the B200 kernels.
+
+One ``torch.autograd.Function`` evaluates the whole ``nn.Sequential`` of the
+reference's ``ImageTransformNet`` / ``VideoTransformNet`` (network.py:521-611,
+:850-855; ``ResidualBlock`` :461-506) in the split-bf16 NHWC format, so that the
+23 modules exchange no NCHW fp32 tensors: conv (tcgen05 for the 3x3 stride-1
+layers, the gather kernel for 9x9 / stride-2) -> InstanceNorm(+ReLU)(+x2 nearest
+upsample on write) -> ... .  The backward runs backward-data and backward-weight
+of every conv and the InstanceNorm backward (dx, dgamma, dbeta) and returns the
+gradient of all 62 parameter tensors plus the input gradient.
+
+Zero padding is the reference arithmetic (``padding_mode='reflection'`` fell
+through to zeros under the pinned torch 1.1.0).
+"""
+import torch
+
+from . import ops
+
+# (state-dict prefix, kind, cin, cout, k, stride) -- nn.Sequential positions of network.py:521-611
+LAYERS = [
+    ('0', 'conv', 3, 32, 9, 1), ('1', 'in', 32), ('2', 'relu'),
+    ('3', 'conv', 32, 64, 3, 2), ('4', 'in', 64), ('5', 'relu'),
+    ('6', 'conv', 64, 128, 3, 2), ('7', 'in', 128), ('8', 'relu'),
+    ('9', 'res', 128), ('10', 'res', 128), ('11', 'res', 128), ('12', 'res', 128), ('13', 'res', 128),
+    ('14', 'up'), ('15', 'conv', 128, 64, 3, 1), ('16', 'in', 64), ('17', 'relu'),
+    ('18', 'up'), ('19', 'conv', 64, 32, 3, 1), ('20', 'in', 32), ('21', 'relu'),
+    ('22', 'conv', 32, 3, 9, 1),
+]
+
+
+def param_names():
+    """The 62 state-dict keys in module order (weights then bias per module)."""
+    names = []
+    for spec in LAYERS:
+        name, kind = spec[0], spec[1]
+        if kind in ('conv', 'in'):
+            names += [name + '.weight', name + '.bias']
+        elif kind == 'res':
+            for sub in ('conv1', 'insn1', 'conv2', 'insn2'):
+                names += [f'{name}.{sub}.weight', f'{name}.{sub}.bias']
+    return names
+
+
+PARAM_NAMES = param_names()
+
+
+def plan():
+    """Flatten LAYERS into fused stages:
+       ('conv', wname, k, stride, residual_from) and ('in', name, relu, up)."""
+    stages = []
+    specs = list(LAYERS)
+    i = 0
+
+    def norm_flags(j):
+        """relu / up flags of the modules that follow position j (an InstanceNorm)."""
+        relu = up = False
+        k = j + 1
+        while k < len(specs) and specs[k][1] in ('relu', 'up'):
+            relu |= specs[k][1] == 'relu'
+            up |= specs[k][1] == 'up'
+            k += 1
+        return relu, up, k
+
+    while i < len(specs):
+        spec = specs[i]
+        name, kind = spec[0], spec[1]
+        if kind == 'conv':
+            stages.append(('conv', name, spec[4], spec[5], False))
+            i += 1
+        elif kind == 'in':
+            relu, up, nxt = norm_flags(i)
+            stages.append(('in', name, relu, up))
+            i = nxt
+        elif kind == 'res':
+            stages.append(('mark',))                                  # residual = x
+            stages.append(('conv', name + '.conv1', 3, 1, False))
+            stages.append(('in', name + '.insn1', True, False))
+            stages.append(('conv', name + '.conv2', 3, 1, True))      # out += residual (epilogue add)
+            relu, up, nxt = norm_flags(i)                             # an Upsample may follow the last block
+            stages.append(('in', name + '.insn2', False, up))
+            i = nxt
+        else:
+            raise AssertionError(f'unexpected module order at {name}')
+    return stages
+
+
+PLAN = plan()
+
+
+class _PackCache:
+    """Packed (split-bf16, K-major) copies of the conv weights, refreshed when the fp32
+    master weight changes (optimizer step bumps ``_version``)."""
+
+    def __init__(self):
+        self.entries = {}
+
+    def get(self, name, w, mode, **kw):
+        key = (name, mode, ops.PRECISION)
+        tag = (w.data_ptr(), w._version, tuple(w.shape))
+        hit = self.entries.get(key)
+        if hit is None or hit[0] != tag:
+            hit = (tag, ops.PackedWeight(w, mode, **kw))
+            self.entries[key] = hit
+        return hit[1]
+
+
+class TransformNetFn(torch.autograd.Function):
+    """y = net(x).  args: x NCHW fp32 [N, Cin, H, W], cache, then the 62 parameters in
+    PARAM_NAMES order."""
+
+    @staticmethod
+    def forward(ctx, x, cache, *params):
+        p = dict(zip(PARAM_NAMES, params))
+        N, cin, H, W = x.shape
+        h = ops.from_nchw(x, cpad=ops.pad8(cin))
+        saved = []          # per stage: what backward needs
+        residual = None
+        out_nchw = None
+        n_conv = sum(1 for s in PLAN if s[0] == 'conv')
+        seen = 0
+        for st in PLAN:
+            if st[0] == 'mark':
+                residual = h
+                saved.append(None)
+            elif st[0] == 'conv':
+                _, name, k, stride, add_res = st
+                seen += 1
+                w, b = p[name + '.weight'], p[name + '.bias']
+                pw = cache.get(name, w, 0, cols_pad=h.C)
+                last = seen == n_conv
+                if last:
+                    _, _, out_nchw = ops.conv2d(h, pw, b, stride=stride, want_out=False, out_nchw_channels=w.shape[0])
+                    saved.append(h)
+                else:
+                    y, _, _ = ops.conv2d(h, pw, b, stride=stride, add=residual if add_res else None)
+                    saved.append(h)
+                    h = y
+            else:
+                _, name, relu, up = st
+                y, stats = ops.instnorm_fwd(h, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
+                saved.append((h, stats))
+                h = y
+        ctx.saved, ctx.cache, ctx.params, ctx.in_shape = saved, cache, params, x.shape
+        return out_nchw
+
+    @staticmethod
+    def backward(ctx, gy):
+        p = dict(zip(PARAM_NAMES, ctx.params))
+        need = dict(zip(PARAM_NAMES, ctx.needs_input_grad[2:]))
+        grads = {}
+        cache = ctx.cache
+        N, cin, H, W = ctx.in_shape
+        g = ops.from_nchw(gy.contiguous().float(), cpad=8, planes=ops.bwd_planes())
+        res_grad = None      # gradient flowing into the residual branch of the current block
+        first_conv = next(i for i, s in enumerate(PLAN) if s[0] == 'conv')
+        for idx in range(len(PLAN) - 1, -1, -1):
+            st = PLAN[idx]
+            if st[0] == 'mark':
+                # g is the gradient wrt conv1's input; the residual branch was added by conv1's dgrad epilogue
+                res_grad = None
+            elif st[0] == 'conv':
+                _, name, k, stride, add_res = st
+                xin = ctx.saved[idx]
+                w = p[name + '.weight']
+                cout, cin_w = w.shape[0], w.shape[1]
+                if need[name + '.weight'] or need[name + '.bias']:
+                    dw, db = ops.conv2d_wgrad(g, xin, k, stride, k // 2, 0, cout, cin_w)
+                    grads[name + '.weight'], grads[name + '.bias'] = dw, db
+                if add_res:
+                    res_grad = g                    # d(out)/d(residual) = identity
+                if idx == first_conv:
+                    if ctx.needs_input_grad[0]:
+                        pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C)
+                        _, _, gx = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xin.H, xin.W),
+                                              want_out=False, out_nchw_channels=cin)
+                        grads['__input__'] = gx
+                    break
+                tc = k == 3 and stride == 1
+                # the conv after a residual 'mark' (conv1) adds the block's residual gradient
+                add = res_grad if (PLAN[idx - 1][0] == 'mark') else None
+                if tc:
+                    pw = cache.get(name, w, 2, rows_pad=xin.C, cols_pad=g.C)
+                    g, _, _ = ops.conv2d(g, pw, add=add)
+                else:
+                    pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C)
+                    g, _, _ = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xin.H, xin.W), add=add)
+            else:
+                _, name, relu, up = st
+                xin, stats = ctx.saved[idx]
+                g, dgam, dbet = ops.instnorm_bwd(xin, g, stats, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
+                grads[name + '.weight'], grads[name + '.bias'] = dgam, dbet
+        ctx.saved = None
+        out = [grads.get('__input__'), None]
+        for n in PARAM_NAMES:
+            out.append(grads.get(n) if need[n] else None)
+        return tuple(out)
