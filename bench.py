@@ -103,6 +103,92 @@ def cpu_reference_closure_rate(budget_s, max_steps, warmup=1):
     return n / dt, n, torch.get_num_threads()
 
 
+FAST_B, FAST_S = 16, 256
+GF_FAST_PER_IMG = 106.6          # SURVEY.md section 8a row a13 (single-pass, no VGG wgrad)
+
+
+def cpu_reference_fast_st_rate(budget_s=25.0, b=2):
+    """fast_st training closure (oracle.fast_st_closure, torch fp32 CPU) on a bounded sample:
+    images per second at 256x256."""
+    from oracle import oracle
+    torch.set_num_threads(os.cpu_count() or 1)
+    vw, params = oracle.make_vgg_weights(1), oracle.make_transform_params(2, 3)
+    style, batch = seeded((1, 3, FAST_S, FAST_S), 201), seeded((b, 3, FAST_S, FAST_S), 202)
+    targets = oracle.style_targets(style, vw)
+    t0 = time.perf_counter()
+    oracle.fast_st_closure(batch, params, targets, vw)
+    per = time.perf_counter() - t0
+    n = int(max(1, min(4, budget_s / max(per, 1e-3) - 1)))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        oracle.fast_st_closure(batch, params, targets, vw)
+    dt = time.perf_counter() - t0
+    return n * b / dt, n, b, torch.get_num_threads()
+
+
+def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
+    """Secondary metric (BASELINE configs[2]): fast_st training images/s at 256x256, global
+    batch 16 sharded over the ranks (strong scaling), one step = the static_train closure
+    (network.py:690-731) + flat-bucket all-reduce + Adam step (network.py:765)."""
+    from oracle import oracle
+    from styletransfer_b200 import dist as st_dist, network
+    per = FAST_B // world
+    style = seeded((1, 3, FAST_S, FAST_S), 201).to(dev)
+    net = network.ImageTransformNet(style, per).to(dev)
+    net.load_state_dict({k: v.clone() for k, v in oracle.make_transform_params(2, 3).items()})
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, FAST_S, FAST_S]).to(dev),
+                                    vgg_weights=network.load_vgg19_prefix_weights(seed=1))
+    loss_net.compute_feature_loss = False
+    opt = net.get_optimizer()
+    bucket = st_dist.GradBucket(net.parameters())
+    global_batch = seeded((FAST_B, 3, FAST_S, FAST_S), 202)
+    batch = global_batch[rank * per:(rank + 1) * per].to(dev)
+    last = [None]
+
+    def closure():
+        bucket.rebind()
+        bucket.zero()
+        total, _ = net.closure_loss(batch, loss_net, tv_scale=float(world))
+        total.backward()
+        bucket.all_reduce()
+        last[0] = total.detach()
+        return total
+
+    def step():
+        opt.step(closure)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    n0 = L.st_launch_count()
+    ms = timed(step, args.steps)
+    launches = L.st_launch_count() - n0
+    host_batch = batch.detach().cpu().pin_memory()
+    host_loss = torch.zeros(1).pin_memory()
+
+    def e2e_step():
+        batch.copy_(host_batch, non_blocking=True)
+        step()
+        host_loss.copy_(last[0].reshape(1), non_blocking=False)
+    for _ in range(2):
+        e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+    value = FAST_B * args.steps / (ms * 1e-3)
+    out = {'metric': 'fast_st_train_images_per_s_256', 'value': value, 'unit': 'img/s', 'ms_per_step': ms / args.steps,
+           'scaling': 'strong', 'global_batch': FAST_B, 'per_gpu_batch': per,
+           'config': {'workload': 'fast_st train 256x256, global batch 16, closure + all-reduce + Adam (BASELINE configs[2])',
+                      'parallelism': f'dp{world}', 'allreduce_bytes': bucket.nbytes() if world > 1 else 0},
+           'tflops_algorithmic': value * GF_FAST_PER_IMG / 1e3, 'algorithmic_gflop_per_image': GF_FAST_PER_IMG,
+           'e2e': {'value': FAST_B * args.steps / (ms_e2e * 1e-3), 'unit': 'img/s',
+                   'h2d_bytes_per_step': host_batch.numel() * 4 * world, 'd2h_bytes_per_step': 4 * world,
+                   'ms_per_step': ms_e2e / args.steps},
+           'gpu_launches': int(launches), 'loss_after': float(last[0])}
+    if with_cpu:
+        rate, n, b, cores = cpu_reference_fast_st_rate()
+        out['cpu_baseline'] = {'value': rate, 'unit': 'img/s', 'cores': cores, 'kind': 'port',
+                               'sample': f'{n} closures of batch {b} at 256x256 (oracle.fast_st_closure, torch fp32 CPU, no Adam step)'}
+    return out
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -231,7 +317,16 @@ def run_ours(args, rank, world, local_rank):
     per_kernel = {k: {'tflops': g[0] / (g[1] * 1e-3) / 1e12, 'ms_per_launch': g[1] / g[2], 'launches_per_step': g[2] / args.steps}
                   for k, g in sorted(groups.items())}
 
+    # free the Gatys working set, then the secondary fast_st training metric (all ranks take part)
+    del net
+    torch.cuda.empty_cache()
+    fast = None
+    if not args.no_fast_st:
+        fast = run_fast_st(args, rank, world, dev, L, timed, with_cpu=(rank == 0 and world == 1 and not args.no_cpu_baseline))
     if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
         return
     value = world * args.steps / (ms * 1e-3)
     e2e_value = world * args.steps / (ms_e2e * 1e-3)
@@ -249,6 +344,8 @@ def run_ours(args, rank, world, local_rank):
             'e2e': {'value': e2e_value, 'unit': 'it/s', 'h2d_bytes_per_step': host_img.numel() * 4, 'd2h_bytes_per_step': 4,
                     'ms_per_step': ms_e2e / args.steps},
             'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'kernels': per_kernel}
+    if fast is not None:
+        line['fast_st'] = fast
     if world == 1 and not args.no_cpu_baseline:
         rate, n, cores = cpu_reference_closure_rate(budget_s=20.0, max_steps=8, warmup=1)
         line['cpu_baseline'] = {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port',
@@ -256,6 +353,7 @@ def run_ours(args, rank, world, local_rank):
                                           f'(oracle.gatys_closure_as_executed, torch fp32 CPU)'}
     print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
@@ -267,6 +365,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--precision', default='bf16x6', choices=['bf16x6', 'bf16x3', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-fast-st', action='store_true', help='skip the secondary fast_st training metric')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))

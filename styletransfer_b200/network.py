@@ -14,7 +14,7 @@ import torch.nn as nn
 import torch.optim as optim
 from tqdm import tqdm
 
-from . import c_logging, constants, ops, transform, vgg_loss
+from . import c_logging, constants, dist as st_dist, ops, transform, vgg_loss
 from ._lib import StransferError
 
 LOGGER = c_logging.get_logger()
@@ -535,12 +535,16 @@ class ImageTransformNet(nn.Sequential):
 
     # -- the closure body of static_train (network.py:690-731), factored out so that the
     #    benchmark and the parity tests run exactly what the training loop runs
-    def closure_loss(self, batch, loss_network, style_weight=100_000, content_weight=1):
+    def closure_loss(self, batch, loss_network, style_weight=100_000, content_weight=1, tv_scale=1.0):
+        """``tv_scale``: world size under data parallelism (dist.tv_scale()): the TV term is a
+        sum over the batch while the other terms are means, see dist.py."""
         transformed_image = self(batch)
         loss_network(transformed_image, content_image=batch)
         style_loss = loss_network.get_total_current_style_loss(weight=style_weight)
         content_loss = loss_network.get_total_current_content_loss(weight=content_weight)
         regularization_loss = self.get_total_variation_regularization_loss(transformed_image)
+        if tv_scale != 1.0:
+            regularization_loss = regularization_loss * tv_scale
         return style_loss + content_loss + regularization_loss, transformed_image
 
     def static_train(self, style_name='nsp', epochs=50, style_weight=100_000, content_weight=1,
@@ -553,6 +557,10 @@ class ImageTransformNet(nn.Sequential):
         loss_network.compute_feature_loss = False        # the training closure never reads it
         optimizer = self.get_optimizer(optimizer=optim.Adam)
         LOGGER.info('Training network with "%s" optimizer', type(optimizer))
+        # data parallel (launched under torchrun): loader batches are GLOBAL batches, sharded
+        # over the ranks; one flat-bucket all-reduce per closure (dist.py)
+        world = st_dist.world_size()
+        bucket = st_dist.GradBucket(self.parameters()) if world > 1 else None
         iteration = 0
         if train_loader is None:
             test_loader, train_loader = dataset.get_coco_loader(test_split=0.10, test_limit=20,
@@ -566,11 +574,20 @@ class ImageTransformNet(nn.Sequential):
                 continue
             for batch in tqdm(train_loader):
                 batch = batch.squeeze(1).to(constants.DEVICE)
+                if bucket is not None:
+                    batch = st_dist.shard(batch)
 
                 def closure():
-                    optimizer.zero_grad()
-                    total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight)
+                    if bucket is None:
+                        optimizer.zero_grad()
+                    else:
+                        bucket.rebind()
+                        bucket.zero()
+                    total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight,
+                                                      tv_scale=float(world))
                     total_loss.backward()
+                    if bucket is not None:
+                        bucket.all_reduce()
                     return total_loss
 
                 if iteration % 20 == 0:
@@ -650,7 +667,7 @@ class VideoTransformNet(ImageTransformNet):
                                  current_stylized.contiguous().float(), float(temporal_weight))
 
     def closure_loss_video(self, batch, old_images, loss_network, temporal_weight=0.8,
-                           style_weight=100_000, content_weight=1):
+                           style_weight=100_000, content_weight=1, tv_scale=1.0):
         """Closure body of video_train (network.py:984-1037); updates ``old_images`` in place."""
         old_content_images, old_styled_images = old_images
         batch_with_old_content = torch.cat([batch, old_styled_images], dim=1)
@@ -659,6 +676,8 @@ class VideoTransformNet(ImageTransformNet):
         style_loss = loss_network.get_total_current_style_loss(weight=style_weight)
         content_loss = loss_network.get_total_current_content_loss(weight=content_weight)
         regularization_loss = self.get_total_variation_regularization_loss(transformed_image)
+        if tv_scale != 1.0:
+            regularization_loss = regularization_loss * tv_scale
         temporal_loss = self.get_temporal_loss(old_content_images, old_styled_images, batch, transformed_image,
                                                temporal_weight=temporal_weight)
         total_loss = style_loss + content_loss + regularization_loss + temporal_loss
@@ -676,6 +695,10 @@ class VideoTransformNet(ImageTransformNet):
         style_loss_network.compute_feature_loss = False
         optimizer = self.get_optimizer(optimizer=optim.Adam)
         LOGGER.info('Training video network with "%s" optimizer', type(optimizer))
+        # data parallel over CLIPS (frames of a clip are sequentially dependent);
+        # the temporal loss uses the norms of the rank's own clips (per-shard norms)
+        world = st_dist.world_size()
+        bucket = st_dist.GradBucket(self.parameters()) if world > 1 else None
         iteration = 0
         if video_loader is None:
             video_loader = dataset.VideoDataset(batch_size=self.batch_size)
@@ -699,6 +722,8 @@ class VideoTransformNet(ImageTransformNet):
                 old_images = None
                 for batch in dataset.iterate_on_video_batches(video_batch):
                     batch = batch.to(constants.DEVICE)
+                    if bucket is not None:
+                        batch = st_dist.shard(batch)
                     if old_images is None:
                         old_images = [batch, batch]
                     # the closure reads the previous frame's images as they were BEFORE this
@@ -706,12 +731,18 @@ class VideoTransformNet(ImageTransformNet):
                     frozen = [old_images[0], old_images[1]]
 
                     def closure():
-                        optimizer.zero_grad()
+                        if bucket is None:
+                            optimizer.zero_grad()
+                        else:
+                            bucket.rebind()
+                            bucket.zero()
                         state = [frozen[0], frozen[1]]
                         total_loss, _ = self.closure_loss_video(batch, state, style_loss_network, temporal_weight,
-                                                                style_weight, content_weight)
+                                                                style_weight, content_weight, tv_scale=float(world))
                         old_images[0], old_images[1] = state
                         total_loss.backward()
+                        if bucket is not None:
+                            bucket.all_reduce()
                         return total_loss
 
                     if iteration % 20 == 0:

@@ -188,3 +188,33 @@ def test_gradient_discontinuity_floor():
     assert grads_err(g1, g0) < 1e-6
     assert float((o2 - o0).norm() / o0.norm()) < 1e-3 and abs(float(t2 - t0)) / float(t0) < 1e-4
     assert grads_err(g2, g0) > 1e-3
+
+
+def test_cli_surface_matches_reference():
+    """python -m stransfer: same commands, arguments and option names/defaults as the reference
+    (clis/gatys_st.py:10-19, clis/fast_st.py:17-50, clis/video_st.py:17-72)."""
+    from click.testing import CliRunner
+    from stransfer.clis import cli
+    import stransfer.network as net_alias
+    import styletransfer_b200.network as net_real
+    assert net_alias is net_real
+    run = CliRunner()
+    top = run.invoke(cli, ['--help']).output
+    assert all(c in top for c in ('gatys_st', 'fast_st', 'video_st'))
+    g = run.invoke(cli, ['gatys_st', '--help']).output
+    assert all(o in g for o in ('--out-name', '--steps', '--content-weight', '--style-weight', '-cw', '-sw', '-n', '-s'))
+    assert 'CONTENT_IMAGE_PATH STYLE_IMAGE_PATH' in g
+    f = run.invoke(cli, ['fast_st', 'train', '--help']).output
+    assert all(o in f for o in ('--epochs', '--batch-size', '-cw', '-sw', 'STYLE_IMAGE_PATH'))
+    c = run.invoke(cli, ['fast_st', 'convert-image', '--help']).output
+    assert 'IMAGE_PATH STYLE_NAME' in c and '--out-dir' in c
+    v = run.invoke(cli, ['video_st', 'train', '--help']).output
+    assert all(o in v for o in ('--temporal-weight', '-tw', '--use-pretrained-fast-st', '--batch-size'))
+    cv = run.invoke(cli, ['video_st', 'convert-video', '--help']).output
+    assert 'VIDEO_PATH STYLE_NAME' in cv and '--fps' in cv
+    cmd = cli.commands['gatys_st']
+    defaults = {p.name: p.default for p in cmd.params}
+    assert defaults['steps'] == 300 and defaults['style_weight'] == 100_000 and defaults['content_weight'] == 1
+    assert defaults['out_name'] == 'gatys_converted.png'
+    vt = cli.commands['video_st'].commands['train']
+    assert {p.name: p.default for p in vt.params}['temporal_weight'] == 0.8
