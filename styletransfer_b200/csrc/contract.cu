@@ -154,16 +154,28 @@ __global__ void wgrad_finish_kernel(const float* partial, int splits, int Mpad, 
     dw[idx] = s;
 }
 
-// G[b][i][j] = scale * sum over splits (one result per image)
-__global__ void gram_finish_kernel(const float* partial, int splits, int Mpad, int Kpad, int C, float scale,
-                                   float* G, int total) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= total) return;
-    int q = idx; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
-    const size_t off = static_cast<size_t>(i) * Kpad + j;
+// G[b][i][j] = scale * sum over splits (one result per image): 32 outputs x 8 split lanes per
+// block, fixed-order combination (deterministic)
+__global__ void __launch_bounds__(256)
+gram_finish_kernel(const float* __restrict__ partial, int splits, int Mpad, int Kpad, int C, float scale,
+                   float* __restrict__ G, int total) {
+    __shared__ float sm[8][33];
+    const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 32 + ol;
     float s = 0.f;
-    for (int sp = 0; sp < splits; ++sp) s += partial[(static_cast<size_t>(b) * splits + sp) * Mpad * Kpad + off];
-    G[idx] = s * scale;
+    if (idx < total) {
+        int q = idx; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+        const float* base = partial + (static_cast<size_t>(b) * splits) * Mpad * Kpad + static_cast<size_t>(i) * Kpad + j;
+        for (int sp = sl; sp < splits; sp += 8) s += base[static_cast<size_t>(sp) * Mpad * Kpad];
+    }
+    sm[sl][ol] = s;
+    __syncthreads();
+    if (sl == 0 && idx < total) {
+        float t = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) t += sm[l][ol];
+        G[idx] = t * scale;
+    }
 }
 
 int pick_splits(int tiles, int pixels_per_group, int groups) {
@@ -214,7 +226,7 @@ int contract_run(const bf16* dy_hi, const bf16* dy_lo, int Cdy,
         ST_CHECK_LAUNCH("wgrad_finish_kernel");
     } else {
         const int total = N * Cdy * Cdy;
-        gram_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cdy, scale, out, total);
+        gram_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cdy, scale, out, total);
         ST_CHECK_LAUNCH("gram_finish_kernel");
     }
     return ST_OK;

@@ -34,8 +34,7 @@ struct ConvTcParams {
     int tiles_h, tiles_w, n_blocks, work;
     int w_img_rows;                 // weight-row offset per image (0: shared weights)
     int w_rows_total;               // rows of one weight plane
-    int a_planes, w_planes, out_planes;   // 1, 2 or 3 bf16 planes per tensor (see common.cuh)
-    int nb;                               // B-ring depth (fits the shared-memory budget)
+    int out_planes;                 // bf16 planes of the output tensors (1..3)
     const float* bias;              // [Cout] or null
     const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
     const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
@@ -44,51 +43,58 @@ struct ConvTcParams {
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
 };
 
-template <int KS, int BN> struct Cfg {
+// KS: 1 or 3 taps per side; BN: output channels per tile; PL: bf16 planes of BOTH operands
+// (1 -> 1 MMA per product, 2 -> 3, 3 -> 6).
+template <int KS, int BN, int PL> struct Cfg {
     static constexpr int A_ROWS = (TILE_H + KS - 1) * TILE_W;
     static constexpr int A_PLANE = A_ROWS * 128;            // bytes (64 bf16 per row)
     static constexpr int B_PLANE = BN * 128;
-    static constexpr int NA = 2;
-    static constexpr int NB_MAX = 8;
+    static constexpr int A_SLOT = PL * A_PLANE, B_SLOT = PL * B_PLANE;
     static constexpr int BAR_BYTES = 256;
-    static constexpr int SMEM_MAX = 232448;                            // 227 KB opt-in limit
-    // bytes for given plane counts and ring depth (1024 slack for alignment)
-    static constexpr int smem(int a_planes, int w_planes, int nb) {
-        return 1024 + NA * a_planes * A_PLANE + nb * w_planes * B_PLANE + BAR_BYTES;
-    }
-    static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : 256;
+    static constexpr int SMEM_MAX = 232448;                 // 227 KB opt-in limit
+    static constexpr int NA = (KS == 1 && PL < 3) ? 4 : 2;
+    static constexpr int NB_FIT = (SMEM_MAX - 1024 - BAR_BYTES - NA * A_SLOT) / B_SLOT;
+    static constexpr int NB = NB_FIT > 8 ? 8 : NB_FIT;
+    static_assert(NB >= 2, "weight ring needs two slots");
+    static constexpr int SMEM = 1024 + NA * A_SLOT + NB * B_SLOT + BAR_BYTES;
+    // PL > 1: the a0*w0 products go to a "main" accumulator, all correction terms to a second
+    // one, summed in fp32 by the epilogue.  The tensor core's accumulate truncates; keeping the
+    // ~2^-8 smaller corrections out of the main chain divides that error by the pass count.
+    static constexpr int NACC = PL > 1 ? 2 : 1;
+    static constexpr int STAGE_COLS = NACC * BN;
+    static constexpr int TMEM_COLS = (2 * STAGE_COLS <= 32) ? 32 : (2 * STAGE_COLS <= 64) ? 64 :
+                                     (2 * STAGE_COLS <= 128) ? 128 : (2 * STAGE_COLS <= 256) ? 256 : 512;
+    static_assert(2 * STAGE_COLS <= 512, "accumulators exceed TMEM");
 };
 
-template <int KS, int BN>
+template <int KS, int BN, int PL>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
                const ConvTcParams p) {
-    using C = Cfg<KS, BN>;
+    using C = Cfg<KS, BN, PL>;
+    constexpr int NA = C::NA, NB = C::NB;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    const int NB = p.nb;
-    const int a_slot = p.a_planes * C::A_PLANE, b_slot = p.w_planes * C::B_PLANE;
     uint8_t* sA = smem;
-    uint8_t* sB = smem + C::NA * a_slot;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + NB * b_slot);
+    uint8_t* sB = smem + NA * C::A_SLOT;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sB + NB * C::B_SLOT);
     uint64_t* a_full = bars;                 // [NA]
-    uint64_t* a_empty = a_full + C::NA;      // [NA]
-    uint64_t* b_full = a_empty + C::NA;      // [NB]
+    uint64_t* a_empty = a_full + NA;         // [NA]
+    uint64_t* b_full = a_empty + NA;         // [NB]
     uint64_t* b_empty = b_full + NB;         // [NB]
     uint64_t* t_full = b_empty + NB;         // [2]
     uint64_t* t_empty = t_full + 2;          // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int pad = KS / 2;
+    constexpr int pad = KS / 2;
     const int kchunks = p.Cin / KCH;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmW_hi);
-        if (p.a_planes > 1) ptx::prefetch_tmap(&tmA_lo);
-        if (p.w_planes > 1) ptx::prefetch_tmap(&tmW_lo);
-        for (int i = 0; i < C::NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
+        if (PL > 1) { ptx::prefetch_tmap(&tmA_lo); ptx::prefetch_tmap(&tmW_lo); }
+        for (int i = 0; i < NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], 4); }
         ptx::fence_barrier_init();
@@ -103,7 +109,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         // ===================== TMA producer =====================
         if (lane == 0) {
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
-            const uint32_t a_tx = a_slot, b_tx = b_slot;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x) {
                 const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
                 const int tw = t % p.tiles_w; t /= p.tiles_w;
@@ -111,23 +116,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                 const int h0 = th * TILE_H, w0 = tw * TILE_W;
                 const int wrow = n * p.w_img_rows + nb * BN;
                 for (int c = 0; c < kchunks; ++c) {
+#pragma unroll
                     for (int s = 0; s < KS; ++s) {
                         ptx::mbar_wait(&a_empty[a], aph ^ 1);
-                        ptx::mbar_expect_tx(&a_full[a], a_tx);
-                        uint8_t* dst = sA + a * a_slot;
-                        // the planes of one tensor are equally spaced, so one tensor map per tensor
-                        // with the plane index as 5th coordinate would also do; two maps keep rank 4
+                        ptx::mbar_expect_tx(&a_full[a], C::A_SLOT);
+                        uint8_t* dst = sA + a * C::A_SLOT;
+                        // planes 1 and 2 of a tensor are equally spaced: the "lo" map spans both
                         ptx::tma_load_4d(dst, &tmA_hi, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
-                        if (p.a_planes > 1) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
-                        if (p.a_planes > 2) ptx::tma_load_4d(dst + 2 * C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n + p.N);
-                        if (++a == C::NA) { a = 0; aph ^= 1; }
+                        if (PL > 1) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
+                        if (PL > 2) ptx::tma_load_4d(dst + 2 * C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n + p.N);
+                        if (++a == NA) { a = 0; aph ^= 1; }
+#pragma unroll
                         for (int r = 0; r < KS; ++r) {
                             ptx::mbar_wait(&b_empty[b], bph ^ 1);
-                            ptx::mbar_expect_tx(&b_full[b], b_tx);
-                            uint8_t* bd = sB + b * b_slot;
+                            ptx::mbar_expect_tx(&b_full[b], C::B_SLOT);
+                            uint8_t* bd = sB + b * C::B_SLOT;
                             ptx::tma_load_3d(bd, &tmW_hi, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (p.w_planes > 1) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (p.w_planes > 2) ptx::tma_load_3d(bd + 2 * C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow + p.w_rows_total);
+                            if (PL > 1) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
+                            if (PL > 2) ptx::tma_load_3d(bd + 2 * C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow + p.w_rows_total);
                             if (++b == NB) { b = 0; bph ^= 1; }
                         }
                     }
@@ -136,46 +142,60 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // the whole warp walks the pipeline state (warp-uniform -> uniform registers); one elected
+        // lane issues the tcgen05 instructions
+        {
+            const bool leader = ptx::elect_one();
             constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_M, BN);
-            const int maxord = max(p.a_planes, p.w_planes) - 1;
+            constexpr uint32_t desc_hi = ptx::umma_desc_hi_k_sw128();
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
             int it = 0;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
                 const int acc = it & 1;
                 ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * BN;
-                uint32_t accumulate = 0;
+                const uint32_t d_main = tmem_base + acc * C::STAGE_COLS;
+                const uint32_t d_corr = d_main + (C::NACC - 1) * BN;
+                uint32_t acc_main = 0, acc_corr = 0;
                 for (int c = 0; c < kchunks; ++c) {
+#pragma unroll
                     for (int s = 0; s < KS; ++s) {
                         ptx::mbar_wait(&a_full[a], aph);
                         ptx::tc_fence_after();
-                        const uint32_t a_base = ptx::smem_u32(sA + a * a_slot);
+                        const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
+#pragma unroll
                         for (int r = 0; r < KS; ++r) {
                             ptx::mbar_wait(&b_full[b], bph);
                             ptx::tc_fence_after();
-                            const uint32_t b_base = ptx::smem_u32(sB + b * b_slot);
-                            const uint32_t a_tap = a_base + r * TILE_W * 128;
+                            const uint32_t b_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sB + b * C::B_SLOT));
+                            const uint32_t a_lo = a_lo0 + ((r * TILE_W * 128) >> 4);
 #pragma unroll
                             for (int k = 0; k < KCH / 16; ++k) {
-                                // a*w = sum over plane pairs (i, j) with i + j <= maxord: 1, 3 or 6 passes
-                                for (int i = 0; i < p.a_planes; ++i) {
-                                    const uint64_t ad = ptx::umma_desc_k_sw128(a_tap + i * C::A_PLANE + k * 32);
-                                    for (int j = 0; j < p.w_planes && i + j <= maxord; ++j) {
-                                        ptx::mma_bf16_ss(d_tmem, ad, ptx::umma_desc_k_sw128(b_base + j * C::B_PLANE + k * 32), idesc, accumulate);
-                                        accumulate = 1;
+                                // correction terms first (plane pairs i + j >= 1), the main product last
+#pragma unroll
+                                for (int i = 0; i < PL; ++i) {
+#pragma unroll
+                                    for (int j = 0; j < PL; ++j) {
+                                        if (i + j == 0 || i + j > PL - 1) continue;
+                                        if (leader)
+                                            ptx::mma_bf16_ss2(d_corr, a_lo + ((i * C::A_PLANE + k * 32) >> 4), b_lo0 + ((j * C::B_PLANE + k * 32) >> 4),
+                                                              desc_hi, idesc, acc_corr);
+                                        acc_corr = 1;
                                     }
                                 }
+                                if (leader) ptx::mma_bf16_ss2(d_main, a_lo + ((k * 32) >> 4), b_lo0 + ((k * 32) >> 4), desc_hi, idesc, acc_main);
+                                acc_main = 1;
                             }
-                            ptx::tc_commit(&b_empty[b]);
+                            if (leader) ptx::tc_commit(&b_empty[b]);
+                            __syncwarp();
                             if (++b == NB) { b = 0; bph ^= 1; }
                         }
-                        ptx::tc_commit(&a_empty[a]);
-                        if (++a == C::NA) { a = 0; aph ^= 1; }
+                        if (leader) ptx::tc_commit(&a_empty[a]);
+                        if (++a == NA) { a = 0; aph ^= 1; }
                     }
                 }
-                ptx::tc_commit(&t_full[acc]);
+                if (leader) ptx::tc_commit(&t_full[acc]);
+                __syncwarp();
             }
         }
     } else {
@@ -193,11 +213,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
             ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
             ptx::tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * C::STAGE_COLS;
 #pragma unroll 1
             for (int j = 0; j < BN / 16; ++j) {
-                uint32_t r[16];
+                uint32_t r[16], rc[16];
                 ptx::tmem_ld16(taddr + j * 16, r);
+                if (C::NACC > 1) ptx::tmem_ld16(taddr + BN + j * 16, rc);
                 ptx::tmem_ld_wait();
                 if (valid) {
                     const int ch = nb * BN + j * 16;
@@ -206,7 +227,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                     for (int half = 0; half < 2; ++half) {
                         float v[8];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[half * 8 + i]);
+                        for (int i = 0; i < 8; ++i) {
+                            v[i] = __uint_as_float(r[half * 8 + i]);
+                            if (C::NACC > 1) v[i] += __uint_as_float(rc[half * 8 + i]);
+                        }
                         const size_t o = off + half * 8;
                         if (p.bias) {
                             const float4 b0 = *reinterpret_cast<const float4*>(p.bias + ch + half * 8);
@@ -306,25 +330,28 @@ int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, 
     return ST_OK;
 }
 
-template <int KS, int BN>
+template <int KS, int BN, int PL>
 int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
-           ConvTcParams p, cudaStream_t stream) {
-    using C = Cfg<KS, BN>;
+           const ConvTcParams& p, cudaStream_t stream) {
+    using C = Cfg<KS, BN, PL>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_MAX);
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) { st_set_error("conv_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
-    // deepest weight ring that fits next to the two activation slots
-    int nb = C::NB_MAX;
-    while (nb > 1 && C::smem(p.a_planes, p.w_planes, nb) > C::SMEM_MAX) --nb;
-    if (C::smem(p.a_planes, p.w_planes, nb) > C::SMEM_MAX) { st_set_error("conv_tc: tile does not fit shared memory"); return ST_ERR_UNSUPPORTED; }
-    p.nb = nb;
     int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tc_kernel<KS, BN><<<grid, NUM_THREADS, C::smem(p.a_planes, p.w_planes, nb), stream>>>(ah, al, wh, wl, p);
+    conv_tc_kernel<KS, BN, PL><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
+}
+
+template <int KS, int BN>
+int launch_planes(int planes, const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
+                  const ConvTcParams& p, cudaStream_t stream) {
+    if (planes == 3) return launch<KS, BN, 3>(ah, al, wh, wl, p, stream);
+    if (planes == 2) return launch<KS, BN, 2>(ah, al, wh, wl, p, stream);
+    return launch<KS, BN, 1>(ah, al, wh, wl, p, stream);
 }
 
 }  // namespace
@@ -345,8 +372,10 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
     p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
     p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
-    p.a_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1;
-    p.w_planes = w_lo ? (w_planes >= 3 ? 3 : 2) : 1;
+    // both operands are read at the same plane count (the lower one if they differ)
+    const int a_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1;
+    const int w_planes_ = w_lo ? (w_planes >= 3 ? 3 : 2) : 1;
+    const int planes = a_planes < w_planes_ ? a_planes : w_planes_;
     p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
@@ -354,26 +383,26 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     // the third plane follows the second at the same stride: the "lo" map simply spans both
     CUtensorMap ah, al, wh, wl;
     uint64_t ad[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-    uint64_t ad2[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N * (p.a_planes == 3 ? 2 : 1)};
+    uint64_t ad2[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N * (planes == 3 ? 2 : 1)};
     uint32_t ab[4] = {KCH, TILE_W, (uint32_t)(TILE_H + ks - 1), 1};
     uint64_t wd[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total};
-    uint64_t wd2[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total * (p.w_planes == 3 ? 2 : 1)};
+    uint64_t wd2[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total * (planes == 3 ? 2 : 1)};
     uint32_t wb[3] = {KCH, 1, (uint32_t)BN};
     int rc;
     if ((rc = make_map(&ah, x_hi, 4, ad, ab))) return rc;
     if ((rc = make_map(&wh, w_hi, 3, wd, wb))) return rc;
     al = ah; wl = wh;
-    if (x_lo && (rc = make_map(&al, x_lo, 4, ad2, ab))) return rc;
-    if (w_lo && (rc = make_map(&wl, w_lo, 3, wd2, wb))) return rc;
+    if (planes > 1 && (rc = make_map(&al, x_lo, 4, ad2, ab))) return rc;
+    if (planes > 1 && (rc = make_map(&wl, w_lo, 3, wd2, wb))) return rc;
 
     if (ks == 3) {
-        if (BN == 128) return launch<3, 128>(ah, al, wh, wl, p, stream);
-        if (BN == 64) return launch<3, 64>(ah, al, wh, wl, p, stream);
-        if (BN == 32) return launch<3, 32>(ah, al, wh, wl, p, stream);
+        if (BN == 128) return launch_planes<3, 128>(planes, ah, al, wh, wl, p, stream);
+        if (BN == 64) return launch_planes<3, 64>(planes, ah, al, wh, wl, p, stream);
+        if (BN == 32) return launch_planes<3, 32>(planes, ah, al, wh, wl, p, stream);
     } else {
-        if (BN == 128) return launch<1, 128>(ah, al, wh, wl, p, stream);
-        if (BN == 64) return launch<1, 64>(ah, al, wh, wl, p, stream);
-        if (BN == 32) return launch<1, 32>(ah, al, wh, wl, p, stream);
+        if (BN == 128) return launch_planes<1, 128>(planes, ah, al, wh, wl, p, stream);
+        if (BN == 64) return launch_planes<1, 64>(planes, ah, al, wh, wl, p, stream);
+        if (BN == 32) return launch_planes<1, 32>(planes, ah, al, wh, wl, p, stream);
     }
     st_set_error("conv_tc: unsupported tile configuration ks=%d BN=%d", ks, BN);
     return ST_ERR_UNSUPPORTED;

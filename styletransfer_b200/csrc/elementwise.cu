@@ -233,26 +233,52 @@ __global__ void style_seed_kernel(const float* __restrict__ diff, int total, flo
 }
 
 // per-channel sum over pixels (conv bias gradient): partial[blk][C], then finish
-__global__ void channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
-                                           int P, int C, int rows_per_block, float* __restrict__ partial) {
-    // blockDim.x = C (<= 256); each thread owns one channel, rows are coalesced across threads
-    const int c = threadIdx.x;
-    const int p0 = blockIdx.x * rows_per_block, p1 = min(P, p0 + rows_per_block);
-    float s = 0.f;
-    for (int p = p0; p < p1; ++p) {
-        const size_t o = static_cast<size_t>(p) * C + c;
-        float v = __bfloat162float(xh[o]);
-        if (xl) v += __bfloat162float(xl[o]);
-        s += v;
+// per-channel sum over pixels (conv bias gradient): 8 channels per thread (128-bit loads),
+// 256/Cv pixel lanes per block, grid-stride over pixels; per-block partials, then a
+// fixed-order finish (deterministic, no atomics)
+__global__ void __launch_bounds__(256)
+channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                           int P, int C, float* __restrict__ partial) {
+    extern __shared__ float sm[];                 // [lanes][C]
+    const int Cv = C / 8, lanes = 256 / Cv;
+    const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
+    float s[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = 0.f;
+    if (pl < lanes) {
+        for (int p = blockIdx.x * lanes + pl; p < P; p += gridDim.x * lanes) {
+            float v[8];
+            load8(xh, xl, static_cast<size_t>(p) * C + cv * 8, v);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s[i] += v[i];
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sm[pl * C + cv * 8 + i] = s[i];
     }
-    partial[static_cast<size_t>(blockIdx.x) * C + c] = s;
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += 256) {
+        float t = 0.f;
+        for (int l = 0; l < lanes; ++l) t += sm[l * C + c];
+        partial[static_cast<size_t>(blockIdx.x) * C + c] = t;
+    }
 }
-__global__ void channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, float* __restrict__ out) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= Cout) return;
+// out[c] = sum_b partial[b][c]: 32 columns x 8 row lanes per block
+__global__ void __launch_bounds__(256)
+channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, float* __restrict__ out) {
+    __shared__ float sm[8][33];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
     float s = 0.f;
-    for (int b = 0; b < nblk; ++b) s += partial[static_cast<size_t>(b) * C + c];
-    out[c] = s;
+    if (c < C)
+        for (int b = rl; b < nblk; b += 8) s += partial[static_cast<size_t>(b) * C + c];
+    sm[rl][cl] = s;
+    __syncthreads();
+    if (rl == 0 && c < Cout) {
+        float t = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) t += sm[l][cl];
+        out[c] = t;
+    }
 }
 
 inline int grid_for(size_t n, int block, int cap_mult = 8) {
@@ -322,11 +348,13 @@ int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw,
 }
 // ws: >= nblk*C floats with nblk = min(1024, ceil(P/64))
 int ew_channel_sum(const bf16* xh, const bf16* xl, int P, int C, int Cout, float* out, float* ws, cudaStream_t st) {
-    int nblk = (P + 63) / 64; if (nblk > 1024) nblk = 1024;
-    const int rows = (P + nblk - 1) / nblk;
-    nblk = (P + rows - 1) / rows;
-    channel_sum_partial_kernel<<<nblk, C, 0, st>>>(xh, xl, P, C, rows, ws);
+    const int lanes = 256 / (C / 8);
+    int nblk = (P + lanes * 8 - 1) / (lanes * 8);               // >= 8 pixels per lane
+    const int cap = st_num_sms() * 4 < 1024 ? st_num_sms() * 4 : 1024;   // ws holds >= 1024 * C floats
+    if (nblk > cap) nblk = cap;
+    if (nblk < 1) nblk = 1;
+    channel_sum_partial_kernel<<<nblk, 256, lanes * C * sizeof(float), st>>>(xh, xl, P, C, ws);
     ST_CHECK_LAUNCH("channel_sum_partial_kernel");
-    channel_sum_finish_kernel<<<(Cout + 127) / 128, 128, 0, st>>>(ws, nblk, C, Cout, out);
+    channel_sum_finish_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, nblk, C, Cout, out);
     ST_CHECK_LAUNCH("channel_sum_finish_kernel"); return ST_OK;
 }

@@ -100,23 +100,37 @@ __global__ void in_finalize_fwd_kernel(const float* __restrict__ partial, int NC
     rstd[i] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
 }
 
-// backward finalize: s1 = sum dy_eff, s2 = sum dy_eff*xhat per (n,c); dgamma/dbeta = sums over n
-__global__ void in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int splits,
-                                       float* __restrict__ s1, float* __restrict__ s2,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+// backward finalize: s1 = sum dy_eff, s2 = sum dy_eff*xhat per (n,c); dgamma/dbeta = sums over n.
+// block = 32 channels x 8 image lanes; fixed-order combination over the lanes (deterministic)
+__global__ void __launch_bounds__(256)
+in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int splits,
+                       float* __restrict__ s1, float* __restrict__ s2,
+                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    __shared__ float sg[8][33], sb[8][33];
+    const int cl = threadIdx.x & 31, nl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
     float dg = 0.f, db = 0.f;
-    for (int n = 0; n < N; ++n) {
-        float a = 0.f, b = 0.f;
-        for (int sp = 0; sp < splits; ++sp) {
-            a += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + c];
-            b += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + C + c];
+    if (c < C) {
+        for (int n = nl; n < N; n += 8) {
+            float a = 0.f, b = 0.f;
+            const float* base = partial + (static_cast<size_t>(n) * splits) * 2 * C + c;
+#pragma unroll 4
+            for (int sp = 0; sp < splits; ++sp) {
+                a += base[static_cast<size_t>(sp) * 2 * C];
+                b += base[static_cast<size_t>(sp) * 2 * C + C];
+            }
+            s1[n * C + c] = a; s2[n * C + c] = b;
+            db += a; dg += b;
         }
-        s1[n * C + c] = a; s2[n * C + c] = b;
-        db += a; dg += b;
     }
-    dgamma[c] = dg; dbeta[c] = db;
+    sg[nl][cl] = dg; sb[nl][cl] = db;
+    __syncthreads();
+    if (nl == 0 && c < C) {
+        float g = 0.f, b = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) { g += sg[l][cl]; b += sb[l][cl]; }
+        dgamma[c] = g; dbeta[c] = b;
+    }
 }
 
 // forward apply: y = gamma * (x - mean) * rstd + beta  (+ReLU) (+ x2 nearest upsample on write)
@@ -319,7 +333,7 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
     in_stats_kernel<1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
         xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, up, x_planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
-    in_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
+    in_finalize_bwd_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
     in_apply_bwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
         xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, N, H, W, C, relu, up, x_planes);

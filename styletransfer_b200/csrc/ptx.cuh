@@ -102,6 +102,18 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t d_tmem, uint64_t a_desc, ui
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same, descriptors given as (lo, hi) halves: only the 14-bit start-address field of lo varies
+__device__ __forceinline__ void mma_bf16_ss2(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
+                                             uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // 32 lanes x 16 consecutive fp32 columns: thread i of the warp gets lane (base_lane + i)
 __device__ __forceinline__ void tmem_ld16(uint32_t addr, uint32_t (&r)[16]) {
@@ -129,6 +141,13 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
     d |= static_cast<uint64_t>(1) << 46;
     d |= static_cast<uint64_t>(2) << 61;
     return d;
+}
+// the same descriptor as two 32-bit halves: lo = start address field | LBO, hi = SBO | version | layout
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
+    return ((smem_addr & 0x3ffff) >> 4) | (1u << 16);
+}
+__host__ __device__ constexpr uint32_t umma_desc_hi_k_sw128() {
+    return static_cast<uint32_t>(1024 >> 4) | (1u << 14) | (2u << 29);
 }
 // Instruction descriptor for kind::f16: bf16 A/B (K-major both), fp32 accumulate.
 //   [4,6) c_format=1 (f32)  [7,10) a_format=1 (bf16)  [10,13) b_format=1 (bf16)
