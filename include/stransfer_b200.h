@@ -76,6 +76,18 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
               void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes,
               float* out_nchw, int Cnchw, void* stream);
 
+/* First VGG layer (torchvision vgg19.features[0], 3 -> Cout channels, 3x3, zero padding 1;
+ * run by StyleNetwork.run_through_pieces network.py:316-340) in exact fp32 on the CUDA cores:
+ * x is the NCHW fp32 image (module boundary format), w [Cout][3][3][3] and bias [Cout] fp32;
+ * out = pre-ReLU tap, relu_out = relu(tap) (either may be NULL), split-bf16 NHWC with `planes`
+ * planes.  Cout: multiple of 8, <= 256. */
+int st_conv3x3_image_fwd(const float* x, const float* w, const float* bias, void* out_hi, void* out_lo,
+                         void* relu_hi, void* relu_lo, int planes, int N, int H, int W, int Cout, void* stream);
+/* its backward-data to the image (autograd of network.py:451): g = gradient of the tap
+ * (split-bf16 NHWC, g_planes planes), gx NCHW fp32 [N][3][H][W]. */
+int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, const float* w, float* gx,
+                           int N, int H, int W, int Cout, void* stream);
+
 /* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]) */
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks);
 int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy,

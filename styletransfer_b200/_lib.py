@@ -29,6 +29,8 @@ SIGNATURES = {
                        _P, _P, _P, _P,                      # bias mask add_hi add_lo
                        _P, _P, _P, _P, _I,                  # out_hi out_lo relu_hi relu_lo out_planes
                        _P, _I, _P]),                        # out_nchw Cnchw stream
+    'st_conv3x3_image_fwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    'st_conv3x3_image_dgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
     'st_conv2d_wgrad_workspace_bytes': (_Z, [_I, _I, _I, _I, _I, _I]),
     'st_conv2d_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                              _P, _P, _P, _Z, _P]),

@@ -18,6 +18,8 @@ int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, 
 int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*,
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
+int conv_image_fwd(const float*, const float*, const float*, bf16*, bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
+int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, int, int, int, cudaStream_t);
 size_t contract_workspace_bytes(int N, int Ho, int Wo, int Cdy, int Ktot, int groups);
 int contract_run(const bf16*, const bf16*, int, const bf16*, const bf16*, int, int, int, int, int, int, int, int, int, int,
                  int, int, int, float, float*, void*, size_t, cudaStream_t);
@@ -103,6 +105,20 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
     return conv_gen_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, up, CBF(w_hi), CBF(w_lo), w_planes, ks, stride, pad, transposed,
                         Ho, Wo, Cout_pad, Cout_pad, Cbias, bias, CBF(mask), CBF(add_hi), CBF(add_lo),
                         BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw, STRM(stream));
+}
+
+int st_conv3x3_image_fwd(const float* x, const float* w, const float* bias, void* out_hi, void* out_lo,
+                         void* relu_hi, void* relu_lo, int planes, int N, int H, int W, int Cout, void* stream) {
+    ST_CHECK_ARG(x && w && (out_hi || relu_hi), "st_conv3x3_image_fwd: null pointer");
+    ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Cout % 8 == 0 && Cout > 0 && Cout <= 256, "st_conv3x3_image_fwd: bad shape (Cout %% 8, <= 256)");
+    ST_CHECK_ARG(planes >= 1 && planes <= 3 && (planes == 1 || ((!out_hi || out_lo) && (!relu_hi || relu_lo))), "st_conv3x3_image_fwd: planes/lo mismatch");
+    return conv_image_fwd(x, w, bias, BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), planes, N, H, W, Cout, STRM(stream));
+}
+int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, const float* w, float* gx,
+                           int N, int H, int W, int Cout, void* stream) {
+    ST_CHECK_ARG(g_hi && w && gx, "st_conv3x3_image_dgrad: null pointer");
+    ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Cout % 8 == 0 && Cout > 0 && Cout <= 256, "st_conv3x3_image_dgrad: bad shape (Cout %% 8, <= 256)");
+    return conv_image_dgrad(CBF(g_hi), CBF(g_lo), g_lo ? g_planes : 1, w, gx, N, H, W, Cout, STRM(stream));
 }
 
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {

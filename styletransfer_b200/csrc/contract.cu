@@ -179,7 +179,7 @@ gram_finish_kernel(const float* __restrict__ partial, int splits, int Mpad, int 
 }
 
 int pick_splits(int tiles, int pixels_per_group, int groups) {
-    const int target = 2 * st_num_sms();
+    const int target = 8 * st_num_sms();       // ~8 resident CTAs per SM hide the gather latency
     int splits = (target + tiles * groups - 1) / (tiles * groups);
     const int max_splits = (pixels_per_group + 4 * TK - 1) / (4 * TK);     // at least 128 pixels per split
     if (splits > max_splits) splits = max_splits;

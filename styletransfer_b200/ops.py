@@ -160,6 +160,29 @@ def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
     return out, relu, nchw
 
 
+def conv_image_fwd(x, w, bias, want_out=True, want_relu=False):
+    """VGG conv1_1 on the NCHW fp32 image (exact fp32, CUDA cores) -> (tap Split, relu Split)."""
+    _require_cuda(x, 'conv_image_fwd')
+    N, C, H, W = x.shape
+    assert C == 3 and tuple(w.shape[1:]) == (3, 3, 3), 'conv_image_fwd: 3-channel image, 3x3 kernel'
+    cout = w.shape[0]
+    out = Split(N, H, W, cout, x.device) if want_out else None
+    relu = Split(N, H, W, cout, x.device) if want_relu else None
+    planes = (out or relu).planes
+    _lib.check(_lib.lib().st_conv3x3_image_fwd(x.data_ptr(), w.data_ptr(), _p(bias), out.hi if out else None, out.lo if out else None,
+                                               relu.hi if relu else None, relu.lo if relu else None, planes, N, H, W, cout, _stream()),
+               'st_conv3x3_image_fwd')
+    return out, relu
+
+
+def conv_image_dgrad(g, w):
+    """Gradient of the image (NCHW fp32) from the gradient of the conv1_1 tap."""
+    gx = torch.empty((g.N, 3, g.H, g.W), dtype=torch.float32, device=g.buf.device)
+    _lib.check(_lib.lib().st_conv3x3_image_dgrad(g.hi, g.lo, g.planes, w.data_ptr(), gx.data_ptr(), g.N, g.H, g.W, g.C, _stream()),
+               'st_conv3x3_image_dgrad')
+    return gx
+
+
 _ws_cache = {}
 
 

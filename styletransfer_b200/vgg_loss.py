@@ -27,23 +27,31 @@ class VGGPrefix:
         self.fwd, self.bwd, self.bias = [], [], []
         for i, (w, b) in enumerate(weights):
             ops._require_cuda(w, 'VGGPrefix')
-            cin_pad = 8 if i == 0 else w.shape[1]
-            self.fwd.append(ops.PackedWeight(w, 0, cols_pad=cin_pad))
-            # backward-data: conv1_1 goes through the gather form (3 output channels, padded to 8),
-            # the others run as forward convs with flipped taps on the tcgen05 kernel
-            self.bwd.append(ops.PackedWeight(w, 1 if i == 0 else 2, rows_pad=cin_pad))
+            if i == 0:
+                # conv1_1 (K = 27) runs in exact fp32 on the CUDA cores, forward and backward-data,
+                # straight from / to the NCHW fp32 image (conv_image.cu): the fp32 weight is the operand
+                self.w0 = w.detach().contiguous().float()
+                self.fwd.append(None)
+                self.bwd.append(None)
+            else:
+                self.fwd.append(ops.PackedWeight(w, 0, cols_pad=w.shape[1]))
+                # backward-data runs as a forward conv with flipped taps on the tcgen05 kernel
+                self.bwd.append(ops.PackedWeight(w, 2, rows_pad=w.shape[1]))
             self.bias.append(b.detach().contiguous().float())
 
     def taps(self, x, upto=5, keep_all=True):
         """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto."""
-        h = ops.from_nchw(x, cpad=8)
+        h = None
         taps = []
         for i in range(upto):
             pool_next = i + 1 < 5 and PREFIX[i + 1][2]
             last = i + 1 == upto
             # a tap feeds either relu+maxpool (separate kernel) or a conv that wants relu(tap)
             want_relu = not last and not pool_next
-            tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=True, want_relu=want_relu)
+            if i == 0:
+                tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=True, want_relu=want_relu)
+            else:
+                tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=True, want_relu=want_relu)
             taps.append(tap)
             if last:
                 break
@@ -96,7 +104,7 @@ class _VGGLossFn(torch.autograd.Function):
         gp1, _, _ = ops.conv2d(g3, net.bwd[2])
         g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1))
         g1, _, _ = ops.conv2d(g2, net.bwd[1], mask=taps[0], add=style_grad(0))
-        _, _, gx = ops.conv2d(g1, net.bwd[0], transposed=1, want_out=False, out_nchw_channels=ctx.in_shape[1])
+        gx = ops.conv_image_dgrad(g1, net.w0)
         ctx.taps = ctx.diffs = None
         return gx, None, None, None, None
 

@@ -242,3 +242,21 @@ def test_tv_and_temporal(ops):
     assert abs(float(out3[0]) - float(tl)) / float(tl) < 1e-5
     g = ops.temporal_bwd(os_, cs.detach(), 0.8, out3, torch.tensor([1.0], device='cuda'))
     assert rel_l2(g, cs.grad) < 1e-5
+
+
+@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64)])
+def test_conv_image_fwd_and_dgrad(ops, N, H, W):
+    """VGG conv1_1 (3 -> 64) in exact fp32 on the CUDA cores, NCHW fp32 image in, image gradient out."""
+    x = seeded((N, 3, H, W), 71, device='cuda').requires_grad_(True)
+    w = seeded((64, 3, 3, 3), 72, 0.2, device='cuda')
+    b = seeded((64,), 73, 0.1, device='cuda')
+    ref = F.conv2d(x, w, b, padding=1)
+    gy = seeded(tuple(ref.shape), 74, device='cuda')
+    ref.backward(gy)
+    tap, relu = ops.conv_image_fwd(x.detach(), w, b, want_out=True, want_relu=True)
+    assert rel_l2(nhwc(tap), ref) < 2e-6
+    assert rel_l2(nhwc(relu), F.relu(ref)) < 2e-6
+    only_relu = ops.conv_image_fwd(x.detach(), w, b, want_out=False, want_relu=True)
+    assert only_relu[0] is None and rel_l2(nhwc(only_relu[1]), F.relu(ref)) < 2e-6
+    gx = ops.conv_image_dgrad(ops.from_nchw(gy, planes=2), w)
+    assert gx.shape == x.shape and rel_l2(gx, x.grad) < 2e-5
