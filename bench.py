@@ -225,13 +225,10 @@ def run_ours(args, rank, world, local_rank):
     net.compute_feature_loss = False           # train_gatys never reads the feature node
     x = content.clone().requires_grad_(True)
 
-    def closure():
-        x.grad = None
-        net(x, content)
-        total = (net.get_total_current_style_loss(weight=STYLE_WEIGHT) +
-                 net.get_total_current_content_loss(weight=CONTENT_WEIGHT))
-        total.backward()
-        return total
+    # the closure train_gatys runs (network.py:438-451): captured once into a CUDA graph and
+    # replayed per step unless --no-graph
+    closure = net.gatys_closure(x, content, STYLE_WEIGHT, CONTENT_WEIGHT, graph=not args.no_graph)
+    eager_closure = net.gatys_closure(x, content, STYLE_WEIGHT, CONTENT_WEIGHT, graph=False)
 
     def barrier():
         if world > 1:
@@ -261,6 +258,8 @@ def run_ours(args, rank, world, local_rank):
     n0 = L.st_launch_count()
     ms = timed(closure, args.steps)
     launches = L.st_launch_count() - n0
+    if not args.no_graph:
+        launches = closure.launches * args.steps      # kernels inside the replayed graph
     clocks = sampler.stop() if sampler else None
 
     # ---- end to end: host image in pinned memory -> closure -> loss back on the host ----
@@ -295,7 +294,7 @@ def run_ours(args, rank, world, local_rank):
     ops.conv2d = traced_conv2d
     torch.cuda.synchronize()
     for _ in range(args.steps):
-        closure()
+        eager_closure()
     torch.cuda.synchronize()
     ops.conv2d = real_conv2d
     groups = {}
@@ -318,7 +317,7 @@ def run_ours(args, rank, world, local_rank):
                   for k, g in sorted(groups.items())}
 
     # free the Gatys working set, then the secondary fast_st training metric (all ranks take part)
-    del net
+    del net, closure, eager_closure
     torch.cuda.empty_cache()
     fast = None
     if not args.no_fast_st:
@@ -339,6 +338,7 @@ def run_ours(args, rank, world, local_rank):
             'config': {'workload': 'gatys_st 512x512 single pair per GPU, closure fwd+bwd (BASELINE configs[1])',
                        'size': SIZE, 'pairs': world, 'parallelism': f'{world} independent pairs, no collective',
                        'l2': 'working set ~1.5 GB per closure >> 126 MB L2 (no flush needed)',
+                       'launch': 'eager' if args.no_graph else 'cuda graph replay',
                        'algorithmic_gflop_per_step': GF_CLOSURE},
             'tflops_algorithmic': value / world * GF_CLOSURE / 1e3,
             'e2e': {'value': e2e_value, 'unit': 'it/s', 'h2d_bytes_per_step': host_img.numel() * 4, 'd2h_bytes_per_step': 4,
@@ -365,6 +365,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--precision', default='bf16x6', choices=['bf16x6', 'bf16x3', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='launch the closure eagerly instead of replaying a CUDA graph')
     ap.add_argument('--no-fast-st', action='store_true', help='skip the secondary fast_st training metric')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))

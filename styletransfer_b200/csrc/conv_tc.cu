@@ -304,10 +304,13 @@ struct MapKeyHash {
 std::mutex g_map_mu;
 std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
-// bf16 tensor, dims innermost first, contiguous; 128B swizzle, zero OOB fill.
-int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box) {
+}  // namespace
+
+// bf16 tensor, dims innermost first, contiguous; 128B (or 64B) swizzle, zero OOB fill.
+// Shared with wgrad_tc.cu (declared in tmap.cuh).
+int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box, int swizzle_bytes) {
     MapKey key; memset(&key, 0, sizeof(key));
-    key.ptr = ptr; key.rank = rank;
+    key.ptr = ptr; key.rank = rank | (swizzle_bytes << 8);
     for (int i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.box[i] = box[i]; }
     std::lock_guard<std::mutex> lk(g_map_mu);
     auto itf = g_maps.find(key);
@@ -322,12 +325,18 @@ int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, 
         if (i < rank - 1) gs[i] = stride;
     }
     CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gd, gs, bx, es,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { st_set_error("cuTensorMapEncodeTiled failed: %d", (int)r); return ST_ERR_CUDA; }
     if (g_maps.size() > 8192) g_maps.clear();
     g_maps.emplace(key, *out);
     return ST_OK;
+}
+
+namespace {
+inline int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box) {
+    return st_make_tmap(out, ptr, rank, dims, box, 128);
 }
 
 template <int KS, int BN, int PL>

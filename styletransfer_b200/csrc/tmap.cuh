@@ -1,0 +1,6 @@
+// Cached cuTensorMapEncodeTiled wrapper (defined in conv_tc.cu): bf16 tensor, dims innermost
+// first, contiguous, zero out-of-bounds fill, 128-byte or 64-byte swizzle.
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box, int swizzle_bytes);

@@ -1,0 +1,229 @@
+// tcgen05 / TMEM / TMA backward-weight of a stride-1 "same" convolution (transform net:
+// autograd of the nn.Conv2d call sites network.py:468-481, :582-599).
+//
+//   dW[co][ci][r][s] = sum over pixels p of  dy[p][co] * x[p + (r - pad, s - pad)][ci]
+//
+// GEMM view (both operands are pixel-major in memory, NHWC, so both are "MN-major" UMMA
+// operands: the contraction index K = pixel is the slow one):
+//   K = 128 pixels (an 8 x 16 patch), N = Cdy gradient channels (32 / 64 / 128),
+//   M = 128 = TWO vertical taps (r, r+1) x 64 input channels of one horizontal tap s:
+//       one TMA box of (8 + KH - 1) x 16 pixels x 64 channels holds every vertical tap, tap r
+//       starts r * 2048 bytes into it, so the M-group stride (LBO) is simply 2048.
+//   An odd last tap pairs with 128 rows of don't-care data (rows are independent; they are
+//   never written out).
+// Work item = (horizontal tap s, 64-channel chunk of Cin, pixel split); the CTA walks its pixel
+// tiles accumulating ceil(KH/2) accumulators of 128 x Cdy in TMEM, then writes fp32 partials; a
+// finish kernel sums the splits in a fixed order (deterministic, no atomics) into the PyTorch
+// weight-gradient layout.  Gradients carry 2 bf16 planes: 3 MMAs per product.
+//
+// Warp roles (192 threads): warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "tmap.cuh"
+
+namespace {
+
+constexpr int TILE_H = 8, TILE_W = 16, TILE_PIX = 128;
+constexpr int NUM_THREADS = 192;
+constexpr int PL = 2;                       // planes read from each operand
+
+struct WgradParams {
+    int N, H, W, Cin, Cdy;
+    int tiles_h, tiles_w, tiles;            // pixel tiles
+    int chunks;                             // Cin / 64
+    int splits, tiles_per_split;
+    float* partial;                         // [split][s][chunk][acc][128][Cdy]
+};
+
+template <int KH, int CDY> struct WCfg {
+    static constexpr int A_ROWS = (TILE_H + KH - 1) * TILE_W;
+    static constexpr int A_PLANE = A_ROWS * 128;                 // 64 channels per row
+    static constexpr int NBOX = CDY > 64 ? CDY / 64 : 1;            // dy boxes per plane
+    static constexpr int DROW = CDY >= 64 ? 128 : CDY * 2;          // bytes per dy row (per box)
+    static constexpr int B_BOX = TILE_PIX * DROW;
+    static constexpr int B_PLANE = NBOX * B_BOX;
+    static constexpr int STAGE = PL * (A_PLANE + B_PLANE);
+    static constexpr int NACC = (KH + 1) / 2;
+    static constexpr int TMEM_NEED = NACC * CDY;
+    static constexpr int TMEM_COLS = TMEM_NEED <= 32 ? 32 : TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+    static_assert(TMEM_NEED <= 512, "accumulators exceed TMEM");
+    static constexpr int SMEM_MAX = 232448;
+    static constexpr int SLACK = 4096;                               // the odd tap's partner reads past the last box
+    static constexpr int NS_FIT = (SMEM_MAX - 1024 - 256 - SLACK) / STAGE;
+    static constexpr int NS = NS_FIT > 4 ? 4 : NS_FIT;
+    static_assert(NS >= 2, "need two pipeline stages");
+    static constexpr int SMEM = 1024 + NS * STAGE + SLACK + 256;
+};
+
+// MN-major shared-memory descriptor halves (SWIZZLE_128B: layout 2, rows of 128 B, 8-row groups
+// 1024 B apart; SWIZZLE_64B: layout 4, rows of 64 B, groups 512 B apart)
+__device__ __forceinline__ uint32_t mn_desc_lo(uint32_t addr, uint32_t lbo_bytes) {
+    return ((addr & 0x3ffff) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+__host__ __device__ constexpr uint32_t mn_desc_hi(int row_bytes) {
+    return static_cast<uint32_t>((8 * row_bytes) >> 4) | (1u << 14) | ((row_bytes == 128 ? 2u : 4u) << 29);
+}
+// kind::f16 instruction descriptor, bf16 x bf16 -> fp32, BOTH operands MN-major (bits 15, 16)
+__host__ __device__ constexpr uint32_t idesc_mn(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+           (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                       uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+template <int KH, int CDY>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmD, const WgradParams p) {
+    using C = WCfg<KH, CDY>;
+    constexpr int NS = C::NS;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * C::STAGE + C::SLACK);
+    uint64_t* full = bars;              // [NS]
+    uint64_t* empty = full + NS;        // [NS]
+    uint64_t* done = empty + NS;        // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int pad = KH / 2;
+    // work item
+    const int split = blockIdx.x % p.splits;
+    int item = blockIdx.x / p.splits;
+    const int chunk = item % p.chunks;
+    const int s = item / p.chunks;                    // horizontal tap (KW = KH or 1: the host sizes the grid)
+    const int t0 = split * p.tiles_per_split;
+    const int t1 = min(p.tiles, t0 + p.tiles_per_split);
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmX); ptx::prefetch_tmap(&tmD);
+        for (int i = 0; i < NS; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
+        ptx::mbar_init(done, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int st = 0; uint32_t ph = 0;
+            for (int t = t0; t < t1; ++t) {
+                int q = t; const int tw = q % p.tiles_w; q /= p.tiles_w;
+                const int th = q % p.tiles_h; const int n = q / p.tiles_h;
+                const int h0 = th * TILE_H, w0 = tw * TILE_W;
+                ptx::mbar_wait(&empty[st], ph ^ 1);
+                ptx::mbar_expect_tx(&full[st], C::STAGE);
+                uint8_t* dst = smem + st * C::STAGE;
+#pragma unroll
+                for (int pl = 0; pl < PL; ++pl) {
+                    // planes of one tensor are equally spaced: plane index rides on the batch coordinate
+                    ptx::tma_load_4d(dst + pl * C::A_PLANE, &tmX, &full[st], chunk * 64, w0 + s - p.pad_w_dummy(), h0 - pad, n + pl * p.N);
+                }
+                uint8_t* db = dst + PL * C::A_PLANE;
+#pragma unroll
+                for (int pl = 0; pl < PL; ++pl)
+#pragma unroll
+                    for (int b = 0; b < C::NBOX; ++b)
+                        ptx::tma_load_4d(db + pl * C::B_PLANE + b * C::B_BOX, &tmD, &full[st], b * 64, w0, h0, n + pl * p.N);
+                if (++st == NS) { st = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        const bool leader = ptx::elect_one();
+        constexpr uint32_t idesc = idesc_mn(128, CDY);
+        constexpr uint32_t a_hi = mn_desc_hi(128);
+        constexpr uint32_t b_hi = mn_desc_hi(C::DROW);
+        int st = 0; uint32_t ph = 0;
+        uint32_t accumulate = 0;
+        for (int t = t0; t < t1; ++t) {
+            ptx::mbar_wait(&full[st], ph);
+            ptx::tc_fence_after();
+            const uint32_t a0 = ptx::smem_u32(smem + st * C::STAGE);
+            const uint32_t b0 = a0 + PL * C::A_PLANE;
+#pragma unroll
+            for (int g = 0; g < C::NACC; ++g) {
+#pragma unroll
+                for (int k = 0; k < TILE_PIX / 16; ++k) {
+                    // a*b = a0*b0 + a0*b1 + a1*b0  (planes)
+#pragma unroll
+                    for (int pa = 0; pa < PL; ++pa) {
+#pragma unroll
+                        for (int pb = 0; pb < PL; ++pb) {
+                            if (pa + pb > 1) continue;
+                            const uint32_t a_lo = mn_desc_lo(a0 + pa * C::A_PLANE + g * 2 * TILE_W * 128 + k * 16 * 128, TILE_W * 128);
+                            const uint32_t b_lo = mn_desc_lo(b0 + pb * C::B_PLANE + k * 16 * C::DROW, C::B_BOX);
+                            if (leader) mma_ss(tmem_base + g * CDY, a_lo, a_hi, b_lo, b_hi, idesc, (k | pa | pb) ? 1u : accumulate);
+                        }
+                    }
+                }
+            }
+            accumulate = 1;
+            if (leader) ptx::tc_commit(&empty[st]);
+            __syncwarp();
+            if (++st == NS) { st = 0; ph ^= 1; }
+        }
+        if (leader) ptx::tc_commit(done);
+        __syncwarp();
+    } else {
+        // ===================== epilogue (warps 2..5): TMEM -> fp32 partials =====================
+        const int q = warp & 3;
+        const int m = q * 32 + lane;                  // accumulator row: (tap within the pair) * 64 + channel
+        ptx::mbar_wait(done, 0);
+        ptx::tc_fence_after();
+        const bool any = t1 > t0;
+        float* out = p.partial + (static_cast<size_t>(blockIdx.x) * C::NACC) * 128 * CDY;
+#pragma unroll 1
+        for (int g = 0; g < C::NACC; ++g) {
+#pragma unroll 1
+            for (int j = 0; j < CDY / 16; ++j) {
+                uint32_t r[16];
+                ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + g * CDY + j * 16, r);
+                ptx::tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(out + (static_cast<size_t>(g) * 128 + m) * CDY + j * 16);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    dst[i] = any ? make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
+                                               __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        ptx::tc_fence_before();
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
+}
+
+// dw[co][ci][r][s] = sum over splits of partial[split][s][chunk][acc = r / 2][(r % 2) * 64 + ci % 64][co]
+__global__ void wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, int chunks, int nacc, int CDY,
+                                       int Cout, int Cin, int KH, float* __restrict__ dw) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = Cout * Cin * KH * KW;
+    if (idx >= total) return;
+    int q = idx; const int s = q % KW; q /= KW; const int r = q % KH; q /= KH; const int ci = q % Cin; const int co = q / Cin;
+    const int chunk = ci / 64;
+    const size_t per_cta = static_cast<size_t>(nacc) * 128 * CDY;
+    const size_t within = (static_cast<size_t>(r / 2) * 128 + (r % 2) * 64 + (ci % 64)) * CDY + co;
+    float acc = 0.f;
+    for (int sp = 0; sp < splits; ++sp) {
+        const size_t cta = static_cast<size_t>(s * chunks + chunk) * splits + sp;
+        acc += partial[cta * per_cta + within];
+    }
+    dw[idx] = acc;
+}
+
+}  // namespace

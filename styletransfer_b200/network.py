@@ -55,6 +55,44 @@ def _load_latest_model_weigths(model_name: str, style_name: str, models_path='da
     return adaptive_torch_load(models_path + latest_weight_name)
 
 
+class GraphedClosure:
+    """A closure (forward + backward that writes the ``.grad`` of its leaves) captured ONCE into a
+    CUDA graph and replayed afterwards: the ~50 kernel launches of a Gatys closure then cost one
+    ``cudaGraphLaunch`` instead of ~50 Python->ctypes round trips.
+    ``fn`` must leave the leaves' ``.grad`` as None before its backward so that the gradient
+    buffers are created inside the graph's memory pool and rewritten in place by every replay;
+    everything ``fn`` reads (image, targets, weights) must live at fixed addresses."""
+
+    def __init__(self, fn, leaves=(), warmup=3):
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(warmup):              # first-launch setup (attributes, workspaces) stays outside
+                fn()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        from ._lib import lib
+        n0 = lib().st_launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        # same stream as the warm-up: the leaves' AccumulateGrad nodes were created on it
+        with torch.cuda.graph(self.graph, stream=side):
+            self.out = fn()
+        self.launches = int(lib().st_launch_count() - n0)     # kernels of ours per replay
+        self.leaves = [(leaf, leaf.grad) for leaf in leaves]   # gradient buffers inside the graph's pool
+
+    def __call__(self):
+        for leaf, grad in self.leaves:
+            if leaf.grad is not grad:            # an eager backward or zero_grad() replaced it
+                leaf.grad = grad
+        self.graph.replay()
+        return self.out
+
+
+def cuda_graphs_enabled():
+    return os.environ.get('STRANSFER_CUDA_GRAPH', '1') != '0'
+
+
 # --------------------------------------------------------------------------
 # stand-alone loss modules (reference network.py:79-201)
 # --------------------------------------------------------------------------
@@ -333,6 +371,29 @@ class StyleNetwork(nn.Module):
         self.content_losses[0][0].loss = losses[5]
         self.feature_losses[0][0].loss = losses[6]
 
+    def gatys_closure(self, input_image, content_image, style_weight=100_000, content_weight=1, graph=None):
+        """The body of train_gatys' closure (network.py:438-451): zero_grad -> forward ->
+        style_weight * style + content_weight * content -> backward into ``input_image.grad``.
+        Returns a callable; with CUDA graphs enabled (default) it replays a captured graph."""
+        input_image.requires_grad_()
+
+        def body():
+            input_image.grad = None
+            self(input_image, content_image)
+            total_loss = (self.get_total_current_style_loss(weight=style_weight) +
+                          self.get_total_current_content_loss(weight=content_weight))
+            total_loss.backward()
+            return total_loss
+        if graph is None:
+            graph = cuda_graphs_enabled()
+        if not graph:
+            return body
+        # drop the autograd graphs kept alive by earlier ``node.loss`` tensors: their AccumulateGrad
+        # node for the image lives on another stream and would invalidate the capture
+        for node, _ in self.style_losses + self.content_losses + self.feature_losses:
+            node.loss = None
+        return GraphedClosure(body, leaves=[input_image])
+
     def get_content_optimizer(self, input_img, optt=optim.Adam):
         """network.py:403-409"""
         return optt([input_img.requires_grad_()])
@@ -347,14 +408,10 @@ class StyleNetwork(nn.Module):
         optimizer = self.get_content_optimizer(input_image, optt=optim.LBFGS)
         self.compute_feature_loss = False           # never read by this loop
         n_closure = [0]
+        evaluate = self.gatys_closure(input_image, content_image, style_weight, content_weight)
         for step in tqdm(range(steps)):
             def closure():
-                optimizer.zero_grad()
-                self(input_image, content_image)
-                style_loss = self.get_total_current_style_loss(weight=style_weight)
-                content_loss = self.get_total_current_content_loss(weight=content_weight)
-                total_loss = style_loss + content_loss
-                total_loss.backward()
+                total_loss = evaluate()
                 n_closure[0] += 1
                 if n_closure[0] % 50 == 0:
                     LOGGER.info('Loss: %s', total_loss)

@@ -158,3 +158,28 @@ def test_full_size_properties(net_mod):
     _, _, g1, _ = _closure(net_mod, content, style, x0, 1e5, 1.0)
     _, _, g2, _ = _closure(net_mod, content, style, x0, 2e5, 2.0)
     assert rel_l2(g2, 2 * g1) < 1e-4
+
+
+def test_cuda_graph_closure_matches_eager(net_mod):
+    """train_gatys replays the closure as a CUDA graph: same loss and gradient as the eager
+    closure, and a replay sees in-place updates of the image (what L-BFGS does between calls)."""
+    h, w = 48, 80
+    content, style = seeded((1, 3, h, w), 81, device='cuda'), seeded((1, 3, h, w), 82, device='cuda')
+    net = net_mod.StyleNetwork(style, content, vgg_weights=_vgg_cuda())
+    net.compute_feature_loss = False
+    x = (content + 0.2 * seeded((1, 3, h, w), 83, device='cuda')).requires_grad_(True)
+    eager = net.gatys_closure(x, content, 1e5, 1, graph=False)
+    l0 = eager().detach().clone()
+    g0 = x.grad.detach().clone()
+    graphed = net.gatys_closure(x, content, 1e5, 1, graph=True)
+    assert graphed.launches > 20
+    l1 = graphed().detach().clone()
+    assert torch.equal(l0, l1) and torch.equal(g0, x.grad)
+    with torch.no_grad():
+        x.add_(0.05 * seeded((1, 3, h, w), 84, device='cuda'))
+    l2, g2 = graphed().detach().clone(), x.grad.detach().clone()
+    l3 = eager().detach().clone()
+    assert not torch.equal(l2, l1)
+    assert torch.equal(l2, l3) and torch.equal(g2, x.grad)
+    out = net.train_gatys(style, content, steps=2)          # L-BFGS through the graphed closure
+    assert out.shape == content.shape and torch.isfinite(out).all()
