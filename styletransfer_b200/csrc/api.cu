@@ -20,6 +20,9 @@ int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const b
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
 int conv_image_fwd(const float*, const float*, const float*, bf16*, bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, int, int, int, cudaStream_t);
+bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes);
+size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks);
+int wgrad_tc_run(const bf16*, const bf16*, int, int, int, int, int, int, int, int, float*, void*, size_t, cudaStream_t);
 size_t contract_workspace_bytes(int N, int Ho, int Wo, int Cdy, int Ktot, int groups);
 int contract_run(const bf16*, const bf16*, int, const bf16*, const bf16*, int, int, int, int, int, int, int, int, int, int,
                  int, int, int, float, float*, void*, size_t, cudaStream_t);
@@ -124,7 +127,9 @@ int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, con
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {
     size_t a = contract_workspace_bytes(N, Ho, Wo, Cdy, ks * ks * CinPad, 1);
     size_t b = static_cast<size_t>(1024) * Cdy * sizeof(float);
-    return a > b ? a : b;
+    size_t c = (ks == 3 && CinPad % 64 == 0) ? wgrad_tc_workspace_bytes(N, Ho, Wo, CinPad, Cdy, ks) : 0;
+    if (b > a) a = b;
+    return a > c ? a : c;
 }
 int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy, const void* x_hi, const void* x_lo,
                     int N, int H, int W, int CinPad, int up, int Ho, int Wo, int ks, int stride, int pad,
@@ -132,7 +137,14 @@ int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy, const void* x
     ST_CHECK_ARG(dy_hi && x_hi && dw && workspace, "st_conv2d_wgrad: null pointer");
     ST_CHECK_ARG(Cdy % 8 == 0 && CinPad % 8 == 0 && Cout <= Cdy && Cin <= CinPad, "st_conv2d_wgrad: bad channel counts");
     ST_CHECK_ARG(workspace_bytes >= st_conv2d_wgrad_workspace_bytes(N, Ho, Wo, Cdy, CinPad, ks), "st_conv2d_wgrad: workspace too small");
-    int rc = contract_run(CBF(dy_hi), CBF(dy_lo), Cdy, CBF(x_hi), CBF(x_lo), N, H, W, CinPad, up, Ho, Wo, ks, stride, pad,
+    int rc;
+    // tcgen05 path: stride-1 3x3, 64-channel multiples, both tensors with their planes one plane stride apart
+    const size_t x_plane = static_cast<size_t>(N) * H * W * CinPad, d_plane = static_cast<size_t>(N) * Ho * Wo * Cdy;
+    const bool planes_ok = dy_lo && x_lo && CBF(x_lo) == CBF(x_hi) + x_plane && CBF(dy_lo) == CBF(dy_hi) + d_plane;
+    if (g_conv_path == 0 && Ho == H && Wo == W && wgrad_tc_eligible(ks, stride, pad, up, CinPad, Cdy, planes_ok))
+        rc = wgrad_tc_run(CBF(dy_hi), CBF(x_hi), N, H, W, CinPad, Cdy, ks, Cout, Cin, dw, workspace, workspace_bytes, STRM(stream));
+    else
+        rc = contract_run(CBF(dy_hi), CBF(dy_lo), Cdy, CBF(x_hi), CBF(x_lo), N, H, W, CinPad, up, Ho, Wo, ks, stride, pad,
                           0, Cout, Cin, 1.f, dw, workspace, workspace_bytes, STRM(stream));
     if (rc) return rc;
     if (db) {

@@ -32,6 +32,7 @@ struct WgradParams {
     int tiles_h, tiles_w, tiles;            // pixel tiles
     int chunks;                             // Cin / 64
     int splits, tiles_per_split;
+    int pad_w;                              // horizontal padding (KW / 2)
     float* partial;                         // [split][s][chunk][acc][128][Cdy]
 };
 
@@ -129,7 +130,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 #pragma unroll
                 for (int pl = 0; pl < PL; ++pl) {
                     // planes of one tensor are equally spaced: plane index rides on the batch coordinate
-                    ptx::tma_load_4d(dst + pl * C::A_PLANE, &tmX, &full[st], chunk * 64, w0 + s - p.pad_w_dummy(), h0 - pad, n + pl * p.N);
+                    ptx::tma_load_4d(dst + pl * C::A_PLANE, &tmX, &full[st], chunk * 64, w0 + s - p.pad_w, h0 - pad, n + pl * p.N);
                 }
                 uint8_t* db = dst + PL * C::A_PLANE;
 #pragma unroll
@@ -226,4 +227,67 @@ __global__ void wgrad_tc_finish_kernel(const float* __restrict__ partial, int sp
     dw[idx] = acc;
 }
 
+template <int KH, int CDY>
+int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& td, const WgradParams& p, int grid, cudaStream_t stream) {
+    using C = WCfg<KH, CDY>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel<KH, CDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) { st_set_error("wgrad_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
+        attr_set = true;
+    }
+    wgrad_tc_kernel<KH, CDY><<<grid, NUM_THREADS, C::SMEM, stream>>>(tx, td, p);
+    ST_CHECK_LAUNCH("wgrad_tc_kernel");
+    return ST_OK;
+}
+
+struct WgradPlan { int tiles, chunks, kw, items, splits, tiles_per_split, grid, nacc; };
+WgradPlan plan_wgrad(int N, int H, int W, int CinPad, int kh, int kw) {
+    WgradPlan q;
+    q.tiles = N * ((H + TILE_H - 1) / TILE_H) * ((W + TILE_W - 1) / TILE_W);
+    q.chunks = CinPad / 64; q.kw = kw; q.items = kw * q.chunks;
+    int splits = st_num_sms() / q.items; if (splits < 1) splits = 1; if (splits > q.tiles) splits = q.tiles;
+    q.tiles_per_split = (q.tiles + splits - 1) / splits;
+    q.splits = (q.tiles + q.tiles_per_split - 1) / q.tiles_per_split;
+    q.grid = q.items * q.splits; q.nacc = (kh + 1) / 2;
+    return q;
+}
+
 }  // namespace
+
+bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes) {
+    return ks == 3 && stride == 1 && pad == 1 && !up && CinPad % 64 == 0 && (Cdy == 32 || Cdy == 64 || Cdy == 128) && two_planes;
+}
+size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks) {
+    const WgradPlan q = plan_wgrad(N, H, W, CinPad, ks, ks);
+    return static_cast<size_t>(q.grid) * q.nacc * 128 * Cdy * sizeof(float);
+}
+
+// dy [planes][N][H][W][Cdy], x [planes][N][H][W][CinPad] (plane stride = N*H*W*C elements), dw [Cout][Cin][ks][ks]
+int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, int N, int H, int W, int CinPad, int Cdy, int ks,
+                 int Cout, int Cin, float* dw, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    const WgradPlan q = plan_wgrad(N, H, W, CinPad, ks, ks);
+    const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * Cdy * sizeof(float);
+    ST_CHECK_ARG(workspace && workspace_bytes >= need, "wgrad_tc: workspace too small (%zu < %zu)", workspace_bytes, need);
+    WgradParams p;
+    p.N = N; p.H = H; p.W = W; p.Cin = CinPad; p.Cdy = Cdy;
+    p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W; p.tiles = q.tiles;
+    p.chunks = q.chunks; p.splits = q.splits; p.tiles_per_split = q.tiles_per_split; p.pad_w = ks / 2;
+    p.partial = static_cast<float*>(workspace);
+    CUtensorMap tx, td;
+    uint64_t xd[4] = {(uint64_t)CinPad, (uint64_t)W, (uint64_t)H, (uint64_t)N * PL};
+    uint32_t xb[4] = {64, TILE_W, (uint32_t)(TILE_H + ks - 1), 1};
+    uint64_t dd[4] = {(uint64_t)Cdy, (uint64_t)W, (uint64_t)H, (uint64_t)N * PL};
+    uint32_t db[4] = {(uint32_t)(Cdy < 64 ? Cdy : 64), TILE_W, TILE_H, 1};
+    int rc;
+    if ((rc = st_make_tmap(&tx, x_hi, 4, xd, xb, 128))) return rc;
+    if ((rc = st_make_tmap(&td, dy_hi, 4, dd, db, Cdy < 64 ? 64 : 128))) return rc;
+    if (Cdy == 128) rc = launch_wgrad<3, 128>(tx, td, p, q.grid, stream);
+    else if (Cdy == 64) rc = launch_wgrad<3, 64>(tx, td, p, q.grid, stream);
+    else rc = launch_wgrad<3, 32>(tx, td, p, q.grid, stream);
+    if (rc) return rc;
+    const int total = Cout * Cin * ks * ks;
+    wgrad_tc_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dw);
+    ST_CHECK_LAUNCH("wgrad_tc_finish_kernel");
+    return ST_OK;
+}

@@ -129,9 +129,21 @@ def test_conv_dgrad(ops, cin, cout, ks, stride, path):
 
 
 @pytest.mark.parametrize('cin,cout,ks,stride,up', [
-    (128, 128, 3, 1, 0), (3, 32, 9, 1, 0), (32, 64, 3, 2, 0), (128, 64, 3, 1, 1), (32, 3, 9, 1, 0)])
+    (128, 128, 3, 1, 0), (3, 32, 9, 1, 0), (32, 64, 3, 2, 0), (128, 64, 3, 1, 1), (32, 3, 9, 1, 0),
+    (128, 64, 3, 1, 0), (64, 32, 3, 1, 0), (64, 64, 3, 1, 0)])
 def test_conv_wgrad(ops, cin, cout, ks, stride, up):
     N, H, W = 2, 12, 20
+    _wgrad_case(ops, N, H, W, cin, cout, ks, stride, up)
+
+
+def test_conv_wgrad_tcgen05_many_tiles(ops):
+    """more pixel tiles than splits (several pipeline wraps per CTA) and a ragged image"""
+    _wgrad_case(ops, 3, 64, 96, 128, 128, 3, 1, 0)
+    _wgrad_case(ops, 2, 37, 53, 64, 32, 3, 1, 0)
+    _wgrad_case(ops, 1, 128, 128, 128, 64, 3, 1, 0)
+
+
+def _wgrad_case(ops, N, H, W, cin, cout, ks, stride, up):
     x = seeded((N, cin, H, W), 11, device='cuda')
     w = seeded((cout, cin, ks, ks), 12, 0.05, device='cuda').requires_grad_(True)
     b = torch.zeros(cout, device='cuda', requires_grad=True)
