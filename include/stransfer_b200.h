@@ -88,6 +88,24 @@ int st_conv3x3_image_fwd(const float* x, const float* w, const float* bias, void
 int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, const float* w, float* gx,
                            int N, int H, int W, int Cout, void* stream);
 
+/* ---- the transform net's 9x9 layers (network.py:525-530 / :850-855: 3|6 -> 32; :604-609: 32 -> 3)
+ * as exact-fp32 direct convolutions on the CUDA cores (one side has 3 / 6 channels).
+ * "Small" tensors are NCHW fp32 (module boundary): channels 0..2 are read from s0, 3..5 from s1,
+ * both with `sc` channels per sample (a 6-channel tensor x: s0 = x, s1 = x + 3*H*W, sc = 6).
+ * "Big" tensors have 32 channels, split-bf16 NHWC. */
+/* small -> big.  flip = 0: forward of layer 0, w [32][CS][9][9], bias [32].
+ *                flip = 1: backward-data of layer 22, small = dy, w [CS][32][9][9] (the layer's weight). */
+int st_conv9_expand(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
+                    void* out_hi, void* out_lo, int planes, int N, int H, int W, void* stream);
+/* big -> small: forward of layer 22, w [3][32][9][9], bias [3], out NCHW fp32 [N][3][H][W] */
+int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float* w, const float* bias, float* out,
+                    int N, int H, int W, void* stream);
+/* backward-weight (+ bias).  mode 0: layer 0, big = dy, small = the layer's input -> dw [32][CS][9][9], db [32];
+ *                            mode 1: layer 22, big = the layer's input, small = dy -> dw [CS][32][9][9], db [CS] */
+size_t st_conv9_wgrad_workspace_bytes(int CS);
+int st_conv9_wgrad(const void* b_hi, const void* b_lo, int b_planes, const float* s0, const float* s1, int sc, int CS, int mode,
+                   float* dw, float* db, void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream);
+
 /* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]) */
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks);
 int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy,

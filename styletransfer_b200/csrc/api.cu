@@ -20,6 +20,10 @@ int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const b
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
 int conv_image_fwd(const float*, const float*, const float*, bf16*, bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, int, int, int, cudaStream_t);
+int conv9_expand_run(const float*, const float*, int, int, const float*, const float*, int, bf16*, bf16*, int, int, int, int, cudaStream_t);
+int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
+size_t conv9_wgrad_workspace_bytes(int CS);
+int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, cudaStream_t);
 bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes);
 size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks);
 int wgrad_tc_run(const bf16*, const bf16*, int, int, int, int, int, int, int, int, float*, void*, size_t, cudaStream_t);
@@ -122,6 +126,27 @@ int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, con
     ST_CHECK_ARG(g_hi && w && gx, "st_conv3x3_image_dgrad: null pointer");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Cout % 8 == 0 && Cout > 0 && Cout <= 256, "st_conv3x3_image_dgrad: bad shape (Cout %% 8, <= 256)");
     return conv_image_dgrad(CBF(g_hi), CBF(g_lo), g_lo ? g_planes : 1, w, gx, N, H, W, Cout, STRM(stream));
+}
+
+int st_conv9_expand(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
+                    void* out_hi, void* out_lo, int planes, int N, int H, int W, void* stream) {
+    ST_CHECK_ARG(s0 && w && out_hi && (CS == 3 || (CS == 6 && s1)), "st_conv9_expand: null pointer or CS not 3/6");
+    ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && sc >= 3 && planes >= 1 && planes <= 3 && (planes == 1 || out_lo), "st_conv9_expand: bad shape/planes");
+    return conv9_expand_run(s0, s1, sc, CS, w, bias, flip, BF(out_hi), BF(out_lo), planes, N, H, W, STRM(stream));
+}
+int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float* w, const float* bias, float* out,
+                    int N, int H, int W, void* stream) {
+    ST_CHECK_ARG(x_hi && w && out && N > 0 && H > 0 && W > 0, "st_conv9_reduce: null pointer or empty shape");
+    return conv9_reduce_run(CBF(x_hi), CBF(x_lo), x_lo ? planes : 1, w, bias, out, N, H, W, STRM(stream));
+}
+size_t st_conv9_wgrad_workspace_bytes(int CS) { return (CS == 3 || CS == 6) ? conv9_wgrad_workspace_bytes(CS) : 0; }
+int st_conv9_wgrad(const void* b_hi, const void* b_lo, int b_planes, const float* s0, const float* s1, int sc, int CS, int mode,
+                   float* dw, float* db, void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream) {
+    ST_CHECK_ARG(b_hi && s0 && dw && workspace && (CS == 3 || (CS == 6 && s1)) && (mode == 0 || mode == 1), "st_conv9_wgrad: bad arguments");
+    ST_CHECK_ARG(mode == 0 || CS == 3, "st_conv9_wgrad: layer 22 has 3 output channels");
+    ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && sc >= 3, "st_conv9_wgrad: empty shape");
+    return conv9_wgrad_run(CBF(b_hi), CBF(b_lo), b_lo ? b_planes : 1, s0, s1, sc, CS, mode, dw, db,
+                           static_cast<float*>(workspace), workspace_bytes, N, H, W, STRM(stream));
 }
 
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {

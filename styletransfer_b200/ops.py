@@ -183,6 +183,53 @@ def conv_image_dgrad(g, w):
     return gx
 
 
+def _small_ptrs(x):
+    """(s0, s1, channels per sample) of an NCHW fp32 tensor with 3 or 6 channels."""
+    N, C, H, W = x.shape
+    assert C in (3, 6), 'the 9x9 kernels take 3- or 6-channel NCHW tensors'
+    return x.data_ptr(), (x.data_ptr() + 3 * H * W * 4 if C == 6 else None), C
+
+
+def conv9_expand(x, w, bias=None, flip=False, planes=None):
+    """9x9 conv from a 3/6-channel NCHW fp32 tensor to 32 channels (Split).  flip=False: layer-0
+    forward (w [32][C][9][9]); flip=True: layer-22 backward-data of dy (w [3][32][9][9])."""
+    _require_cuda(x, 'conv9_expand')
+    x = x.contiguous().float()
+    N, C, H, W = x.shape
+    s0, s1, sc = _small_ptrs(x)
+    assert tuple(w.shape) == ((C, 32, 9, 9) if flip else (32, C, 9, 9))
+    out = Split(N, H, W, 32, x.device, planes=planes)
+    _lib.check(_lib.lib().st_conv9_expand(s0, s1, sc, C, w.data_ptr(), _p(bias), int(flip), out.hi, out.lo, out.planes,
+                                          N, H, W, _stream()), 'st_conv9_expand')
+    return out
+
+
+def conv9_reduce(x, w, bias=None):
+    """9x9 conv from a 32-channel Split to a 3-channel NCHW fp32 tensor (layer-22 forward)."""
+    assert x.C == 32 and tuple(w.shape) == (3, 32, 9, 9)
+    out = torch.empty((x.N, 3, x.H, x.W), dtype=torch.float32, device=x.buf.device)
+    _lib.check(_lib.lib().st_conv9_reduce(x.hi, x.lo, x.planes, w.data_ptr(), _p(bias), out.data_ptr(), x.N, x.H, x.W, _stream()),
+               'st_conv9_reduce')
+    return out
+
+
+def conv9_wgrad(big, small, mode, want_bias=True):
+    """Backward-weight of the 9x9 layers.  mode 0: layer 0 (big = dy Split, small = input NCHW) ->
+    dw [32][C][9][9]; mode 1: layer 22 (big = input Split, small = dy NCHW) -> dw [3][32][9][9]."""
+    L = _lib.lib()
+    small = small.contiguous().float()
+    N, C, H, W = small.shape
+    s0, s1, sc = _small_ptrs(small)
+    assert big.C == 32 and big.shape[:3] == (N, H, W)
+    dev = big.buf.device
+    ws = workspace(L.st_conv9_wgrad_workspace_bytes(C), dev)
+    dw = torch.empty((32, C, 9, 9) if mode == 0 else (C, 32, 9, 9), dtype=torch.float32, device=dev)
+    db = torch.empty((32 if mode == 0 else C,), dtype=torch.float32, device=dev) if want_bias else None
+    _lib.check(L.st_conv9_wgrad(big.hi, big.lo, big.planes, s0, s1, sc, C, mode, dw.data_ptr(), _p(db), ws.data_ptr(), ws.numel(),
+                                N, H, W, _stream()), 'st_conv9_wgrad')
+    return dw, db
+
+
 _ws_cache = {}
 
 

@@ -272,3 +272,35 @@ def test_conv_image_fwd_and_dgrad(ops, N, H, W):
     assert only_relu[0] is None and rel_l2(nhwc(only_relu[1]), F.relu(ref)) < 2e-6
     gx = ops.conv_image_dgrad(ops.from_nchw(gy, planes=2), w)
     assert gx.shape == x.shape and rel_l2(gx, x.grad) < 2e-5
+
+
+@pytest.mark.parametrize('C,N,H,W', [(3, 2, 20, 36), (6, 1, 13, 45), (3, 1, 64, 160)])
+def test_conv9_layers(ops, C, N, H, W):
+    """The 9x9 layers as exact-fp32 direct convolutions: layer 0 (C -> 32) forward + backward-weight,
+    layer 22 (32 -> 3) forward + backward-data + backward-weight, against torch fp32."""
+    # layer 0
+    x = seeded((N, C, H, W), 81, device='cuda')
+    w0 = seeded((32, C, 9, 9), 82, 0.06, device='cuda').requires_grad_(True)
+    b0 = seeded((32,), 83, 0.1, device='cuda').requires_grad_(True)
+    y = F.conv2d(x, w0, b0, padding=4)
+    gy = seeded(tuple(y.shape), 84, device='cuda')
+    y.backward(gy)
+    out = ops.conv9_expand(x, w0.detach(), b0.detach())
+    assert rel_l2(nhwc(out), y) < 2e-6
+    dw, db = ops.conv9_wgrad(ops.from_nchw(gy, planes=2), x, 0)
+    assert rel_l2(dw, w0.grad) < 2e-5 and rel_l2(db, b0.grad) < 2e-5
+    if C != 3:
+        return
+    # layer 22
+    xb = seeded((N, 32, H, W), 85, device='cuda').requires_grad_(True)
+    w2 = seeded((3, 32, 9, 9), 86, 0.02, device='cuda').requires_grad_(True)
+    b2 = seeded((3,), 87, 0.1, device='cuda').requires_grad_(True)
+    y2 = F.conv2d(xb, w2, b2, padding=4)
+    g2 = seeded(tuple(y2.shape), 88, device='cuda')
+    y2.backward(g2)
+    xs = ops.from_nchw(xb.detach())
+    assert rel_l2(ops.conv9_reduce(xs, w2.detach(), b2.detach()), y2) < 2e-6
+    dx = ops.conv9_expand(g2, w2.detach(), flip=True, planes=2)
+    assert rel_l2(nhwc(dx), xb.grad) < 2e-5
+    dw2, db2 = ops.conv9_wgrad(xs, g2, 1)
+    assert rel_l2(dw2, w2.grad) < 2e-6 and rel_l2(db2, b2.grad) < 2e-6
