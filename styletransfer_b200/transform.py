@@ -87,6 +87,14 @@ def plan():
 PLAN = plan()
 
 
+def _is_conv9_in(w):
+    return w.shape[0] == 32 and w.shape[1] in (3, 6) and tuple(w.shape[2:]) == (9, 9)
+
+
+def _is_conv9_out(w):
+    return tuple(w.shape) == (3, 32, 9, 9)
+
+
 class _PackCache:
     """Packed (split-bf16, K-major) copies of the conv weights, refreshed when the fp32
     master weight changes (optimizer step bumps ``_version``)."""
@@ -112,7 +120,7 @@ class TransformNetFn(torch.autograd.Function):
     def forward(ctx, x, cache, *params):
         p = dict(zip(PARAM_NAMES, params))
         N, cin, H, W = x.shape
-        h = ops.from_nchw(x, cpad=ops.pad8(cin))
+        h = None            # the first conv reads the NCHW fp32 input itself (9x9 direct kernel)
         saved = []          # per stage: what backward needs
         residual = None
         out_nchw = None
@@ -126,8 +134,20 @@ class TransformNetFn(torch.autograd.Function):
                 _, name, k, stride, add_res = st
                 seen += 1
                 w, b = p[name + '.weight'], p[name + '.bias']
-                pw = cache.get(name, w, 0, cols_pad=h.C)
                 last = seen == n_conv
+                if seen == 1 and _is_conv9_in(w):
+                    # layer 0: 3|6 -> 32 channels, 9x9: exact-fp32 direct kernel on the NCHW input
+                    h = ops.conv9_expand(x, w, b)
+                    saved.append(None)
+                    continue
+                if h is None:
+                    h = ops.from_nchw(x, cpad=ops.pad8(cin))
+                if last and _is_conv9_out(w) and h.C == 32:
+                    # layer 22: 32 -> 3 channels, 9x9: direct kernel writing the NCHW fp32 output
+                    out_nchw = ops.conv9_reduce(h, w, b)
+                    saved.append(h)
+                    continue
+                pw = cache.get(name, w, 0, cols_pad=h.C)
                 if last:
                     _, _, out_nchw = ops.conv2d(h, pw, b, stride=stride, want_out=False, out_nchw_channels=w.shape[0])
                     saved.append(h)
@@ -140,7 +160,7 @@ class TransformNetFn(torch.autograd.Function):
                 y, stats = ops.instnorm_fwd(h, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
                 saved.append((h, stats))
                 h = y
-        ctx.saved, ctx.cache, ctx.params, ctx.in_shape = saved, cache, params, x.shape
+        ctx.saved, ctx.cache, ctx.params, ctx.in_shape, ctx.x = saved, cache, params, x.shape, x
         return out_nchw
 
     @staticmethod
@@ -150,11 +170,33 @@ class TransformNetFn(torch.autograd.Function):
         grads = {}
         cache = ctx.cache
         N, cin, H, W = ctx.in_shape
-        g = ops.from_nchw(gy.contiguous().float(), cpad=8, planes=ops.bwd_planes())
+        gy = gy.contiguous().float()
+        g = None             # built lazily: the 9x9 output layer consumes the NCHW fp32 gradient directly
         res_grad = None      # gradient flowing into the residual branch of the current block
         first_conv = next(i for i, s in enumerate(PLAN) if s[0] == 'conv')
+        last_conv = max(i for i, s in enumerate(PLAN) if s[0] == 'conv')
         for idx in range(len(PLAN) - 1, -1, -1):
             st = PLAN[idx]
+            if st[0] == 'conv' and idx == last_conv and _is_conv9_out(p[st[1] + '.weight']) and ctx.saved[idx].C == 32:
+                name = st[1]
+                w = p[name + '.weight']
+                if need[name + '.weight'] or need[name + '.bias']:
+                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(ctx.saved[idx], gy, 1)
+                g = ops.conv9_expand(gy, w, flip=True, planes=ops.bwd_planes())
+                continue
+            if g is None:
+                g = ops.from_nchw(gy, cpad=8, planes=ops.bwd_planes())
+            if st[0] == 'conv' and idx == first_conv and ctx.saved[idx] is None:
+                name = st[1]
+                w = p[name + '.weight']
+                if need[name + '.weight'] or need[name + '.bias']:
+                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(g, ctx.x, 0)
+                if ctx.needs_input_grad[0]:
+                    # rare (tests / image optimisation through the net): gather-form backward-data
+                    pw = cache.get(name, w, 1, rows_pad=ops.pad8(cin), cols_pad=g.C)
+                    _, _, gx = ops.conv2d(g, pw, stride=1, transposed=1, out_hw=(H, W), want_out=False, out_nchw_channels=cin)
+                    grads['__input__'] = gx
+                break
             if st[0] == 'mark':
                 # g is the gradient wrt conv1's input; the residual branch was added by conv1's dgrad epilogue
                 res_grad = None
