@@ -24,6 +24,9 @@ int conv9_expand_run(const float*, const float*, int, int, const float*, const f
 int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
 size_t conv9_wgrad_workspace_bytes(int CS);
 int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, cudaStream_t);
+bool gram_tc_eligible(int C, bool two_planes);
+size_t gram_tc_workspace_bytes(int B, int HW, int C);
+int gram_tc_run(const bf16*, int, int, int, float, float*, void*, size_t, cudaStream_t);
 bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes);
 size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks);
 int wgrad_tc_run(const bf16*, const bf16*, int, int, int, int, int, int, int, int, float*, void*, size_t, cudaStream_t);
@@ -189,11 +192,19 @@ int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi
     return ew_relu_maxpool_bwd(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), x_lo ? x_planes : 1, N, H, W, C, STRM(stream));
 }
 
-size_t st_gram_workspace_bytes(int B, int HW, int C) { return contract_workspace_bytes(B, HW, 1, C, C, B); }
+size_t st_gram_workspace_bytes(int B, int HW, int C) {
+    const size_t a = contract_workspace_bytes(B, HW, 1, C, C, B);
+    const size_t b = gram_tc_eligible(C, true) ? gram_tc_workspace_bytes(B, HW, C) : 0;
+    return a > b ? a : b;
+}
 int st_gram_fwd(const void* f_hi, const void* f_lo, int B, int HW, int C, float* G, void* workspace, size_t workspace_bytes, void* stream) {
     ST_CHECK_ARG(f_hi && G && workspace && B > 0 && HW > 0, "st_gram_fwd: null pointer or empty shape");
     ST_CHECK_ARG(C % 8 == 0, "st_gram_fwd: C %% 8 != 0");
     const float scale = 1.0f / (static_cast<float>(C) * static_cast<float>(HW));
+    // tcgen05 path: 64 / 128 / 256 channels, planes one plane stride apart
+    const bool planes_ok = f_lo && CBF(f_lo) == CBF(f_hi) + static_cast<size_t>(B) * HW * C;
+    if (g_conv_path == 0 && gram_tc_eligible(C, planes_ok))
+        return gram_tc_run(CBF(f_hi), B, HW, C, scale, G, workspace, workspace_bytes, STRM(stream));
     return contract_run(CBF(f_hi), CBF(f_lo), C, CBF(f_hi), CBF(f_lo), B, HW, 1, C, 0, HW, 1, 1, 1, 0,
                         1, C, C, scale, G, workspace, workspace_bytes, STRM(stream));
 }

@@ -227,6 +227,186 @@ __global__ void wgrad_tc_finish_kernel(const float* __restrict__ partial, int sp
     dw[idx] = acc;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Gram matrix  G[b] = F_b^T F_b  (StyleLoss.gram_matrix, network.py:92-108) on the same MN-major
+// scheme: F is [B][HW][C] pixel-major, a tile is TP consecutive pixels x C channels (C/64 TMA boxes
+// per plane), M = 128 = two 64-channel groups (LBO = one box), N = C, and the SAME shared-memory
+// tile is both operands.  One CTA = (image, pixel split); fp32 partials, deterministic finish.
+// ---------------------------------------------------------------------------------------------
+struct GramParams {
+    int B, HW, tiles, splits, tiles_per_split;
+    float* partial;                         // [b][split][acc][128][C]
+};
+
+template <int C_> struct GCfg {
+    static constexpr int TP = C_ > 128 ? 64 : 128;                // pixels per tile
+    static constexpr int NBOX = C_ / 64;
+    static constexpr int BOX = TP * 128;
+    static constexpr int PLANE = NBOX * BOX;
+    static constexpr int STAGE = PL * PLANE;
+    static constexpr int NACC = C_ > 128 ? C_ / 128 : 1;
+    static constexpr int TMEM_NEED = NACC * C_;
+    static constexpr int TMEM_COLS = TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
+    static constexpr int SLACK = C_ == 64 ? BOX : 0;              // C = 64: the second M group is don't-care data
+    static constexpr int NS_FIT = (232448 - 1024 - 256 - SLACK) / STAGE;
+    static constexpr int NS = NS_FIT > 4 ? 4 : NS_FIT;
+    static_assert(NS >= 2, "need two pipeline stages");
+    static constexpr int SMEM = 1024 + NS * STAGE + SLACK + 256;
+};
+
+template <int C_>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
+    using G = GCfg<C_>;
+    constexpr int NS = G::NS;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS * G::STAGE + G::SLACK);
+    uint64_t* full = bars; uint64_t* empty = full + NS; uint64_t* done = empty + NS;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int split = blockIdx.x % p.splits, b = blockIdx.x / p.splits;
+    const int t0 = split * p.tiles_per_split, t1 = min(p.tiles, t0 + p.tiles_per_split);
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tmF);
+        for (int i = 0; i < NS; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
+        ptx::mbar_init(done, 1);
+        ptx::fence_barrier_init();
+    }
+    if (warp == 1) { ptx::tmem_alloc(tmem_slot, G::TMEM_COLS); ptx::tmem_relinquish(); }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int st = 0; uint32_t ph = 0;
+            for (int t = t0; t < t1; ++t) {
+                ptx::mbar_wait(&empty[st], ph ^ 1);
+                ptx::mbar_expect_tx(&full[st], G::STAGE);
+                uint8_t* dst = smem + st * G::STAGE;
+#pragma unroll
+                for (int pl = 0; pl < PL; ++pl)
+#pragma unroll
+                    for (int bx = 0; bx < G::NBOX; ++bx)
+                        ptx::tma_load_3d(dst + pl * G::PLANE + bx * G::BOX, &tmF, &full[st], bx * 64, t * G::TP, b + pl * p.B);
+                if (++st == NS) { st = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        const bool leader = ptx::elect_one();
+        constexpr uint32_t idesc = idesc_mn(128, C_);
+        constexpr uint32_t hi = mn_desc_hi(128);
+        int st = 0; uint32_t ph = 0;
+        uint32_t accumulate = 0;
+        for (int t = t0; t < t1; ++t) {
+            ptx::mbar_wait(&full[st], ph);
+            ptx::tc_fence_after();
+            const uint32_t base = ptx::smem_u32(smem + st * G::STAGE);
+#pragma unroll
+            for (int g = 0; g < G::NACC; ++g) {
+#pragma unroll
+                for (int k = 0; k < G::TP / 16; ++k) {
+#pragma unroll
+                    for (int pa = 0; pa < PL; ++pa) {
+#pragma unroll
+                        for (int pb = 0; pb < PL; ++pb) {
+                            if (pa + pb > 1) continue;
+                            const uint32_t a_lo = mn_desc_lo(base + pa * G::PLANE + g * 2 * G::BOX + k * 16 * 128, G::BOX);
+                            const uint32_t b_lo = mn_desc_lo(base + pb * G::PLANE + k * 16 * 128, G::BOX);
+                            if (leader) mma_ss(tmem_base + g * C_, a_lo, hi, b_lo, hi, idesc, (k | pa | pb) ? 1u : accumulate);
+                        }
+                    }
+                }
+            }
+            accumulate = 1;
+            if (leader) ptx::tc_commit(&empty[st]);
+            __syncwarp();
+            if (++st == NS) { st = 0; ph ^= 1; }
+        }
+        if (leader) ptx::tc_commit(done);
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        const int m = q * 32 + lane;
+        ptx::mbar_wait(done, 0);
+        ptx::tc_fence_after();
+        const bool any = t1 > t0;
+        float* out = p.partial + (static_cast<size_t>(blockIdx.x) * G::NACC) * 128 * C_;
+#pragma unroll 1
+        for (int g = 0; g < G::NACC; ++g) {
+            if (g * 128 + m >= C_) continue;                         // C = 64: rows 64..127 are don't-care
+#pragma unroll 1
+            for (int j = 0; j < C_ / 16; ++j) {
+                uint32_t r[16];
+                ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + g * C_ + j * 16, r);
+                ptx::tmem_ld_wait();
+                float4* dst = reinterpret_cast<float4*>(out + (static_cast<size_t>(g) * 128 + m) * C_ + j * 16);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    dst[i] = any ? make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
+                                               __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]))
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        ptx::tc_fence_before();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc(tmem_base, G::TMEM_COLS);
+}
+
+// G[b][i][j] = scale * sum over splits of partial[b][split][i / 128][i % 128][j]
+__global__ void __launch_bounds__(256)
+gram_tc_finish_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, float* __restrict__ Gm, int total) {
+    __shared__ float sm[8][33];
+    const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 32 + ol;
+    float s = 0.f;
+    if (idx < total) {
+        int q = idx; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+        const size_t per = static_cast<size_t>(nacc) * 128 * C;
+        const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
+        for (int sp = sl; sp < splits; sp += 8) s += base[static_cast<size_t>(sp) * per];
+    }
+    sm[sl][ol] = s;
+    __syncthreads();
+    if (sl == 0 && idx < total) {
+        float t = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) t += sm[l][ol];
+        Gm[idx] = t * scale;
+    }
+}
+
+struct GramPlan { int tiles, splits, tiles_per_split, grid, nacc; };
+GramPlan plan_gram(int B, int HW, int C) {
+    GramPlan q;
+    const int tp = C > 128 ? 64 : 128;
+    q.tiles = (HW + tp - 1) / tp;
+    int splits = st_num_sms() / B; if (splits < 1) splits = 1; if (splits > q.tiles) splits = q.tiles;
+    q.tiles_per_split = (q.tiles + splits - 1) / splits;
+    q.splits = (q.tiles + q.tiles_per_split - 1) / q.tiles_per_split;
+    q.grid = B * q.splits; q.nacc = C > 128 ? C / 128 : 1;
+    return q;
+}
+
+template <int C_>
+int launch_gram(const CUtensorMap& tf, const GramParams& p, int grid, cudaStream_t stream) {
+    using G = GCfg<C_>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gram_tc_kernel<C_>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM);
+        if (e != cudaSuccess) { st_set_error("gram_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
+        attr_set = true;
+    }
+    gram_tc_kernel<C_><<<grid, NUM_THREADS, G::SMEM, stream>>>(tf, p);
+    ST_CHECK_LAUNCH("gram_tc_kernel");
+    return ST_OK;
+}
+
 template <int KH, int CDY>
 int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& td, const WgradParams& p, int grid, cudaStream_t stream) {
     using C = WCfg<KH, CDY>;
@@ -254,6 +434,34 @@ WgradPlan plan_wgrad(int N, int H, int W, int CinPad, int kh, int kw) {
 }
 
 }  // namespace
+
+bool gram_tc_eligible(int C, bool two_planes) { return (C == 64 || C == 128 || C == 256) && two_planes; }
+size_t gram_tc_workspace_bytes(int B, int HW, int C) {
+    const GramPlan q = plan_gram(B, HW, C);
+    return static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
+}
+// f [planes][B][HW][C] (plane stride B*HW*C elements) -> Gm [B][C][C] * scale
+int gram_tc_run(const bf16* f_hi, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+    const GramPlan q = plan_gram(B, HW, C);
+    const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
+    ST_CHECK_ARG(workspace && workspace_bytes >= need, "gram_tc: workspace too small (%zu < %zu)", workspace_bytes, need);
+    GramParams p;
+    p.B = B; p.HW = HW; p.tiles = q.tiles; p.splits = q.splits; p.tiles_per_split = q.tiles_per_split;
+    p.partial = static_cast<float*>(workspace);
+    CUtensorMap tf;
+    uint64_t fd[3] = {(uint64_t)C, (uint64_t)HW, (uint64_t)B * PL};
+    uint32_t fb[3] = {64, (uint32_t)(C > 128 ? 64 : 128), 1};
+    int rc;
+    if ((rc = st_make_tmap(&tf, f_hi, 3, fd, fb, 128))) return rc;
+    if (C == 64) rc = launch_gram<64>(tf, p, q.grid, stream);
+    else if (C == 128) rc = launch_gram<128>(tf, p, q.grid, stream);
+    else rc = launch_gram<256>(tf, p, q.grid, stream);
+    if (rc) return rc;
+    const int total = B * C * C;
+    gram_tc_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total);
+    ST_CHECK_LAUNCH("gram_tc_finish_kernel");
+    return ST_OK;
+}
 
 bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes) {
     return ks == 3 && stride == 1 && pad == 1 && !up && CinPad % 64 == 0 && (Cdy == 32 || Cdy == 64 || Cdy == 128) && two_planes;
