@@ -18,6 +18,7 @@ SIGNATURES = {
     'st_arch': (_I, []),
     'st_last_error': (c_char_p, []),
     'st_set_conv_path': (_I, [_I]),
+    'st_last_conv_kernel': (_I, []),
     'st_launch_count': (ctypes.c_longlong, []),
     'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
     'st_nhwc_to_nchw': (_I, [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P]),

@@ -24,6 +24,9 @@ int conv9_expand_run(const float*, const float*, int, int, const float*, const f
 int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
 size_t conv9_wgrad_workspace_bytes(int CS);
 int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, cudaStream_t);
+bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho, int Wo);
+int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
+                 const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, cudaStream_t);
 bool gram_tc_eligible(int C, bool two_planes);
 size_t gram_tc_workspace_bytes(int B, int HW, int C);
 int gram_tc_run(const bf16*, int, int, int, float, float*, void*, size_t, cudaStream_t);
@@ -61,6 +64,8 @@ extern "C" {
 int st_arch(void) { return 100; }
 const char* st_last_error(void) { return g_err; }
 int st_set_conv_path(int path) { g_conv_path = path; return ST_OK; }
+static int g_last_conv_kernel = 0;
+int st_last_conv_kernel(void) { return g_last_conv_kernel; }
 long long st_launch_count(void) { return g_st_launches; }
 
 int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int planes, int N, int C1, int C2, int H, int W, int Cpad, void* stream) {
@@ -94,9 +99,18 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
     ST_CHECK_ARG(!(add_lo && !add_hi), "st_conv2d: add_lo without add_hi");
     const bool tc = g_conv_path == 0 && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && !out_nchw &&
                     w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad);
+    g_last_conv_kernel = tc ? 1 : 3;
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, STRM(stream));
+    // run-time-geometry tcgen05 kernel: stride-2 3x3 (forward / transposed) and 32-channel K chunks
+    const int xmode = transposed ? 2 : (stride == 2 ? 1 : 0);
+    const bool tcx = g_conv_path == 0 && !up && pad == 1 && stride <= 2 && (!transposed || stride == 2) && !out_nchw && w_img_rows == 0 &&
+                     (!bias || Cbias == Cout_pad) && w_rows_total >= Cout_pad && conv_tcx_eligible(xmode, ks, Cin, Cout_pad, H, W, Ho, Wo);
+    if (tcx) g_last_conv_kernel = 2;
+    if (tcx)
+        return conv_tcx_run(xmode, CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, Cout_pad, Ho, Wo,
+                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, STRM(stream));
     if (w_img_rows != 0) {
         // per-image weights on the generic path: one launch per image
         for (int n = 0; n < N; ++n) {

@@ -117,18 +117,30 @@ __global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int
     dw[idx] = s;
 }
 
-// per-channel sum of an NCHW fp32 tensor with 3 channels (bias gradient of layer 22)
-__global__ void __launch_bounds__(1024)
-nchw3_channel_sum_kernel(const float* __restrict__ g, int sc, int N, size_t HW, float* __restrict__ out) {
+// per-channel sum of an NCHW fp32 tensor with 3 channels (bias gradient of layer 22), two
+// deterministic stages: grid (CS_PARTS, 3) partial sums, then one block adds them in order
+constexpr int CS_PARTS = 128;
+__global__ void __launch_bounds__(256)
+nchw3_channel_sum_kernel(const float* __restrict__ g, int sc, int N, size_t HW, float* __restrict__ part) {
     __shared__ float smr[32];
-    const int c = blockIdx.x;
+    const int c = blockIdx.y;
     float s = 0.f;
-    for (int n = 0; n < N; ++n) {
-        const float* p = g + (static_cast<size_t>(n) * sc + c) * HW;
-        for (size_t i = threadIdx.x; i < HW; i += blockDim.x) s += p[i];
+    const size_t total = static_cast<size_t>(N) * HW;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * 256 + threadIdx.x; i < total; i += static_cast<size_t>(CS_PARTS) * 256) {
+        const size_t n = i / HW;
+        s += __ldg(g + (n * sc + c) * HW + (i - n * HW));
     }
     s = block_sum(s, smr);
-    if (threadIdx.x == 0) out[c] = s;
+    if (threadIdx.x == 0) part[c * CS_PARTS + blockIdx.x] = s;
+}
+__global__ void __launch_bounds__(96)
+nchw3_channel_sum_finish_kernel(const float* __restrict__ part, float* __restrict__ out) {
+    const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float s = 0.f;
+    for (int i = lane; i < CS_PARTS; i += 32) s += part[c * CS_PARTS + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[c] = s;
 }
 
 inline int conv9_grid() { return st_num_sms() * 2; }
@@ -197,8 +209,10 @@ int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float*
     ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
     if (db) {
         if (mode == 0) return ew_channel_sum(b_hi, b_lo, N * H * W, CB, CB, db, ws, st);
-        nchw3_channel_sum_kernel<<<3, 1024, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, db);
+        nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
         ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
+        nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);
+        ST_CHECK_LAUNCH("nchw3_channel_sum_finish_kernel");
     }
     return ST_OK;
 }

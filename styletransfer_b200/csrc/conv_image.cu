@@ -16,141 +16,205 @@
 namespace {
 
 constexpr int IMG_THREADS = 256;
+constexpr int IM_TH = 4, IM_TW = 32;               // output tile: 4 x 32 pixels
+constexpr int IM_SH = IM_TH + 2;                   // staged rows
+constexpr int IM_SW = IM_TW + 8;                   // staged fp32 image row: column x <-> iw = w0 + x - 4 (float4 aligned)
+constexpr int IM_GW = IM_TW + 2;                   // staged gradient row (pixels)
 
-// weights in shared memory as [tap = (c*3 + r)*3 + s][Cout] fp32
+// shared-memory channel permutation: channel ch = g*8 + half*4 + k lives at [half][g][k], so the 8
+// lanes of a pixel read 128 contiguous bytes per LDS.128 (no bank conflicts)
+__device__ __forceinline__ int perm64(int ch) { return ((ch >> 2) & 1) * 32 + (ch >> 3) * 4 + (ch & 3); }
+
+// forward: 256 threads = 32 pixel quads (4 along w) x 8 channel groups; 4 px x 8 ch accumulators
 __global__ void __launch_bounds__(IMG_THREADS)
 conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                       bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, bf16* __restrict__ relu_hi, bf16* __restrict__ relu_lo,
-                      int planes, int N, int H, int W, int Cout) {
-    extern __shared__ float sw[];                 // [27][Cout] + [Cout]
-    float* sb = sw + 27 * Cout;
-    for (int i = threadIdx.x; i < 27 * Cout; i += IMG_THREADS) {
-        const int co = i % Cout, tap = i / Cout;                  // w: [Cout][3][3][3] -> tap index = c*9 + r*3 + s
-        sw[i] = w[co * 27 + tap];
+                      int planes, int N, int H, int W, int tiles_h, int tiles_w) {
+    __shared__ __align__(16) float sw[27 * 64];                      // [tap = (c*3 + r)*3 + s][perm64(co)]
+    __shared__ __align__(16) float st[3 * IM_SH * IM_SW];
+    for (int i = threadIdx.x; i < 27 * 64; i += IMG_THREADS) {
+        const int co = i & 63, tap = i >> 6;                         // w: [64][3][3][3]
+        sw[tap * 64 + perm64(co)] = w[co * 27 + tap];
     }
-    for (int i = threadIdx.x; i < Cout; i += IMG_THREADS) sb[i] = bias ? bias[i] : 0.f;
-    __syncthreads();
-    const int groups = Cout / 8;
-    const size_t HW = static_cast<size_t>(H) * W;
-    const size_t total = static_cast<size_t>(N) * HW * groups;
-    for (size_t idx = static_cast<size_t>(blockIdx.x) * IMG_THREADS + threadIdx.x; idx < total;
-         idx += static_cast<size_t>(gridDim.x) * IMG_THREADS) {
-        const int g = idx % groups; const size_t pix = idx / groups;
-        const int n = pix / HW; const int rem = pix - static_cast<size_t>(n) * HW;
-        const int h = rem / W, wq = rem - h * W;
-        float acc[8];
+    const int g = threadIdx.x & 7, quad = threadIdx.x >> 3;
+    const int qx = quad & 7, qy = quad >> 3;
+    float b8[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = sb[g * 8 + j];
-        const float* xn = x + static_cast<size_t>(n) * 3 * HW;
+    for (int j = 0; j < 8; ++j) b8[j] = bias ? bias[g * 8 + j] : 0.f;
+    const size_t HW = static_cast<size_t>(H) * W;
+    const int tiles = N * tiles_h * tiles_w;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
+        const int h0 = th * IM_TH, w0 = tw * IM_TW;
+        __syncthreads();
+        for (int i = threadIdx.x; i < 3 * IM_SH * IM_SW; i += IMG_THREADS) {
+            const int xx = i % IM_SW; int r = i / IM_SW; const int y = r % IM_SH; const int c = r / IM_SH;
+            const int ih = h0 + y - 1, iw = w0 + xx - 4;
+            float v = 0.f;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (static_cast<size_t>(n) * 3 + c) * HW + static_cast<size_t>(ih) * W + iw);
+            st[i] = v;
+        }
+        __syncthreads();
+        float acc[4][8];
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[p][j] = b8[j];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
 #pragma unroll
             for (int r = 0; r < 3; ++r) {
-                const int ih = h + r - 1;
+                const float* row = st + (c * IM_SH + qy + r) * IM_SW + qx * 4;
+                float in[12];
 #pragma unroll
-                for (int s = 0; s < 3; ++s) {
-                    const int iw = wq + s - 1;
-                    const bool ok = ih >= 0 && ih < H && iw >= 0 && iw < W;
-                    const float v = ok ? __ldg(xn + c * HW + static_cast<size_t>(ih) * W + iw) : 0.f;
-                    const float4 w0 = *reinterpret_cast<const float4*>(sw + ((c * 3 + r) * 3 + s) * Cout + g * 8);
-                    const float4 w1 = *reinterpret_cast<const float4*>(sw + ((c * 3 + r) * 3 + s) * Cout + g * 8 + 4);
-                    acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
-                    acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
-                    acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
-                    acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+                for (int v = 0; v < 3; ++v) {
+                    const float4 t = *reinterpret_cast<const float4*>(row + v * 4);
+                    in[v * 4] = t.x; in[v * 4 + 1] = t.y; in[v * 4 + 2] = t.z; in[v * 4 + 3] = t.w;
+                }
+#pragma unroll
+                for (int sx = 0; sx < 3; ++sx) {
+                    const float* wr = sw + ((c * 3 + r) * 3 + sx) * 64 + g * 4;
+                    const float4 wa = *reinterpret_cast<const float4*>(wr);
+                    const float4 wb = *reinterpret_cast<const float4*>(wr + 32);
+                    const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+                    for (int p = 0; p < 4; ++p)
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[p][j] = fmaf(in[p + sx + 3], wv[j], acc[p][j]);
                 }
             }
         }
-        const size_t o = pix * Cout + g * 8;
-        if (out_hi) store8p(out_hi, out_lo, planes, o, acc);
-        if (relu_hi) {
+        const int oh = h0 + qy;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
-            store8p(relu_hi, relu_lo, planes, o, acc);
+        for (int p = 0; p < 4; ++p) {
+            const int ow = w0 + qx * 4 + p;
+            if (oh < H && ow < W) {
+                const size_t o = ((static_cast<size_t>(n) * H + oh) * W + ow) * 64 + g * 8;
+                if (out_hi) store8p(out_hi, out_lo, planes, o, acc[p]);
+                if (relu_hi) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[p][j] = fmaxf(acc[p][j], 0.f);
+                    store8p(relu_hi, relu_lo, planes, o, acc[p]);
+                }
+            }
         }
     }
 }
 
 // gx[n][c][h][w] = sum_{co,r,s} g[n][h+1-r][w+1-s][co] * w[co][c][r][s]
-// 8 lanes per output pixel, lane j owns gradient channels j*8 .. j*8+7 (+ 64 per extra round);
-// the 3 channel sums are combined with warp shuffles.
+// the gradient tile (+1 halo) is staged as fp32 [row][pixel][perm64(co)]; 256 threads = 32 strips of
+// 4 pixels x 8 channel groups; each thread: 4 px x 3 outputs over its 8 channels, then a shuffle
+// reduction over the 8 channel groups.
 __global__ void __launch_bounds__(IMG_THREADS)
 conv_image_dgrad_kernel(const bf16* __restrict__ g_hi, const bf16* __restrict__ g_lo, int g_planes,
-                        const float* __restrict__ w, float* __restrict__ gx, int N, int H, int W, int Cout) {
-    extern __shared__ float sw[];                 // [9 taps][3 c][Cout]
-    for (int i = threadIdx.x; i < 27 * Cout; i += IMG_THREADS) {
-        const int co = i % Cout; int q = i / Cout; const int c = q % 3; const int tap = q / 3;   // tap = r*3 + s
-        sw[i] = w[(co * 3 + c) * 9 + tap];
+                        const float* __restrict__ w, float* __restrict__ gx, int N, int H, int W, int tiles_h, int tiles_w) {
+    extern __shared__ __align__(16) float smd[];
+    float* sw = smd;                                   // [tap = r*3 + s][c][perm64(co)]
+    float* st = smd + 27 * 64;                         // [IM_SH][IM_GW][64]
+    for (int i = threadIdx.x; i < 27 * 64; i += IMG_THREADS) {
+        const int co = i & 63; int q = i >> 6; const int c = q % 3; const int tap = q / 3;
+        sw[(tap * 3 + c) * 64 + perm64(co)] = w[(co * 3 + c) * 9 + tap];
     }
-    __syncthreads();
+    const int cg = threadIdx.x & 7, strip = threadIdx.x >> 3;
+    const int sx = strip & 7, sy = strip >> 3;
     const size_t HW = static_cast<size_t>(H) * W;
-    const size_t total = static_cast<size_t>(N) * HW * 8;
-    const size_t total_pad = (total + 31) / 32 * 32;          // whole warps stay in the loop for the shuffles
-    for (size_t idx = static_cast<size_t>(blockIdx.x) * IMG_THREADS + threadIdx.x; idx < total_pad;
-         idx += static_cast<size_t>(gridDim.x) * IMG_THREADS) {
-        const int j = idx & 7; const size_t pix = idx >> 3;
-        const bool live = idx < total;
-        const int n = live ? pix / HW : 0; const int rem = live ? pix - static_cast<size_t>(n) * HW : 0;
-        const int h = rem / W, wq = rem - h * W;
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-        if (live) {
-            for (int cb = j * 8; cb < Cout; cb += 64) {
+    const int tiles = N * tiles_h * tiles_w;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
+        const int h0 = th * IM_TH, w0 = tw * IM_TW;
+        __syncthreads();
+        for (int i = threadIdx.x; i < IM_SH * IM_GW * 8; i += IMG_THREADS) {
+            const int v8 = i & 7; int r = i >> 3; const int xx = r % IM_GW; const int y = r / IM_GW;
+            const int ih = h0 + y - 1, iw = w0 + xx - 1;
+            float v[8];
 #pragma unroll
-                for (int r = 0; r < 3; ++r) {
-                    const int ih = h + 1 - r;
-                    if (ih < 0 || ih >= H) continue;
+            for (int j = 0; j < 8; ++j) v[j] = 0.f;
+            if (ih >= 0 && ih < H && iw >= 0 && iw < W)
+                load8p(g_hi, g_lo, g_planes, ((static_cast<size_t>(n) * H + ih) * W + iw) * 64 + v8 * 8, v);
+            float* dst = st + (y * IM_GW + xx) * 64 + v8 * 4;
+            *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(dst + 32) = make_float4(v[4], v[5], v[6], v[7]);
+        }
+        __syncthreads();
+        float acc[4][3];
 #pragma unroll
-                    for (int s = 0; s < 3; ++s) {
-                        const int iw = wq + 1 - s;
-                        if (iw < 0 || iw >= W) continue;
-                        float v[8];
-                        load8p(g_hi, g_lo, g_planes, ((static_cast<size_t>(n) * H + ih) * W + iw) * Cout + cb, v);
-                        const float* wt = sw + (r * 3 + s) * 3 * Cout + cb;
+        for (int p = 0; p < 4; ++p) { acc[p][0] = 0.f; acc[p][1] = 0.f; acc[p][2] = 0.f; }
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            a0 = fmaf(v[k], wt[k], a0);
-                            a1 = fmaf(v[k], wt[Cout + k], a1);
-                            a2 = fmaf(v[k], wt[2 * Cout + k], a2);
-                        }
-                    }
+        for (int r = 0; r < 3; ++r) {
+            // output row sy reads gradient row sy + 1 - r (+1 halo) ; output col p reads col p + 1 - s (+1 halo)
+            const float* row = st + ((sy + 2 - r) * IM_GW + sx * 4) * 64 + cg * 4;
+            float in[6][8];
+#pragma unroll
+            for (int xx = 0; xx < 6; ++xx) {
+                const float4 a = *reinterpret_cast<const float4*>(row + xx * 64);
+                const float4 b = *reinterpret_cast<const float4*>(row + xx * 64 + 32);
+                in[xx][0] = a.x; in[xx][1] = a.y; in[xx][2] = a.z; in[xx][3] = a.w;
+                in[xx][4] = b.x; in[xx][5] = b.y; in[xx][6] = b.z; in[xx][7] = b.w;
+            }
+#pragma unroll
+            for (int s = 0; s < 3; ++s) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float* wr = sw + ((r * 3 + s) * 3 + c) * 64 + cg * 4;
+                    const float4 wa = *reinterpret_cast<const float4*>(wr);
+                    const float4 wb = *reinterpret_cast<const float4*>(wr + 32);
+                    const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+                    for (int p = 0; p < 4; ++p)
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) acc[p][c] = fmaf(in[p + 2 - s][k], wv[k], acc[p][c]);
                 }
             }
         }
 #pragma unroll
-        for (int o = 4; o > 0; o >>= 1) {
-            a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-            a1 += __shfl_xor_sync(0xffffffffu, a1, o);
-            a2 += __shfl_xor_sync(0xffffffffu, a2, o);
-        }
-        if (live && j < 3) {
-            const float v = j == 0 ? a0 : (j == 1 ? a1 : a2);
-            gx[(static_cast<size_t>(n) * 3 + j) * HW + rem] = v;
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float v = acc[p][c];
+                v += __shfl_xor_sync(0xffffffffu, v, 1);
+                v += __shfl_xor_sync(0xffffffffu, v, 2);
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                acc[p][c] = v;
+            }
+        // lane cg < 4 writes pixel p = cg of the strip, lanes 4..6 idle; 3 channels each
+        const int oh = h0 + sy, ow = w0 + sx * 4 + (cg & 3);
+        if (cg < 4 && oh < H && ow < W) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float v = 0.f;
+#pragma unroll
+                for (int p = 0; p < 4; ++p) v = (p == cg) ? acc[p][c] : v;
+                gx[(static_cast<size_t>(n) * 3 + c) * HW + static_cast<size_t>(oh) * W + ow] = v;
+            }
         }
     }
 }
 
-inline int img_grid(size_t work) {
-    size_t g = (work + IMG_THREADS - 1) / IMG_THREADS;
-    const size_t cap = static_cast<size_t>(st_num_sms()) * 8;
-    return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+inline int img_grid(int tiles) {
+    const int cap = st_num_sms() * 4;
+    return tiles < cap ? tiles : cap;
 }
 
 }  // namespace
 
 int conv_image_fwd(const float* x, const float* w, const float* bias, bf16* out_hi, bf16* out_lo,
                    bf16* relu_hi, bf16* relu_lo, int planes, int N, int H, int W, int Cout, cudaStream_t st) {
-    const size_t work = static_cast<size_t>(N) * H * W * (Cout / 8);
-    conv_image_fwd_kernel<<<img_grid(work), IMG_THREADS, 28 * Cout * sizeof(float), st>>>(
-        x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, Cout);
+    ST_CHECK_ARG(Cout == 64, "conv_image_fwd: Cout must be 64 (got %d)", Cout);
+    const int th = (H + IM_TH - 1) / IM_TH, tw = (W + IM_TW - 1) / IM_TW;
+    conv_image_fwd_kernel<<<img_grid(N * th * tw), IMG_THREADS, 0, st>>>(
+        x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, th, tw);
     ST_CHECK_LAUNCH("conv_image_fwd_kernel");
     return ST_OK;
 }
 
 int conv_image_dgrad(const bf16* g_hi, const bf16* g_lo, int g_planes, const float* w, float* gx,
                      int N, int H, int W, int Cout, cudaStream_t st) {
-    const size_t work = static_cast<size_t>(N) * H * W * 8;
-    conv_image_dgrad_kernel<<<img_grid(work), IMG_THREADS, 27 * Cout * sizeof(float), st>>>(
-        g_hi, g_lo, g_planes, w, gx, N, H, W, Cout);
+    ST_CHECK_ARG(Cout == 64, "conv_image_dgrad: Cout must be 64 (got %d)", Cout);
+    const int th = (H + IM_TH - 1) / IM_TH, tw = (W + IM_TW - 1) / IM_TW;
+    const int smem = (27 * 64 + IM_SH * IM_GW * 64) * sizeof(float);
+    static bool set = false;
+    if (!set) { cudaFuncSetAttribute(conv_image_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); set = true; }
+    conv_image_dgrad_kernel<<<img_grid(N * th * tw), IMG_THREADS, smem, st>>>(g_hi, g_lo, g_planes, w, gx, N, H, W, th, tw);
     ST_CHECK_LAUNCH("conv_image_dgrad_kernel");
     return ST_OK;
 }

@@ -19,6 +19,7 @@
 // Pipelines: A ring (halo boxes), B ring (weight tiles), 2 TMEM accumulators.
 #include "common.cuh"
 #include "ptx.cuh"
+#include "conv_tc_epilogue.cuh"
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -26,22 +27,7 @@
 
 namespace {
 
-constexpr int TILE_H = 8, TILE_W = 16, BLOCK_M = 128, KCH = 64;
-constexpr int NUM_THREADS = 192;
-
-struct ConvTcParams {
-    int N, H, W, Cin, Cout;
-    int tiles_h, tiles_w, n_blocks, work;
-    int w_img_rows;                 // weight-row offset per image (0: shared weights)
-    int w_rows_total;               // rows of one weight plane
-    int out_planes;                 // bf16 planes of the output tensors (1..3)
-    const float* bias;              // [Cout] or null
-    const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
-    const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
-    const bf16* add_lo;
-    bf16* out_hi; bf16* out_lo;     // result (pre-activation)
-    bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
-};
+constexpr int KCH = 64;
 
 // KS: 1 or 3 taps per side; BN: output channels per tile; PL: bf16 planes of BOTH operands
 // (1 -> 1 MMA per product, 2 -> 3, 3 -> 6).
@@ -214,51 +200,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * C::STAGE_COLS;
-#pragma unroll 1
-            for (int j = 0; j < BN / 16; ++j) {
-                uint32_t r[16], rc[16];
-                ptx::tmem_ld16(taddr + j * 16, r);
-                if (C::NACC > 1) ptx::tmem_ld16(taddr + BN + j * 16, rc);
-                ptx::tmem_ld_wait();
-                if (valid) {
-                    const int ch = nb * BN + j * 16;
-                    const size_t off = pix * p.Cout + ch;
-#pragma unroll
-                    for (int half = 0; half < 2; ++half) {
-                        float v[8];
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            v[i] = __uint_as_float(r[half * 8 + i]);
-                            if (C::NACC > 1) v[i] += __uint_as_float(rc[half * 8 + i]);
-                        }
-                        const size_t o = off + half * 8;
-                        if (p.bias) {
-                            const float4 b0 = *reinterpret_cast<const float4*>(p.bias + ch + half * 8);
-                            const float4 b1 = *reinterpret_cast<const float4*>(p.bias + ch + half * 8 + 4);
-                            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-                            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-                        }
-                        if (p.mask) {
-                            float mk[8];
-                            load8(p.mask, nullptr, o, mk);
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = mk[i] > 0.f ? v[i] : 0.f;
-                        }
-                        if (p.add_hi) {
-                            float ad[8];
-                            load8p(p.add_hi, p.add_lo, p.add_lo ? p.out_planes : 1, o, ad);   // add carries the output's planes
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] += ad[i];
-                        }
-                        if (p.out_hi) store8p(p.out_hi, p.out_lo, p.out_planes, o, v);
-                        if (p.relu_hi) {
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-                            store8p(p.relu_hi, p.relu_lo, p.out_planes, o, v);
-                        }
-                    }
-                }
-            }
+            tc_epilogue_row<BN, C::NACC>(p, taddr, nb, pix, valid);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
@@ -308,9 +250,9 @@ std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
 // bf16 tensor, dims innermost first, contiguous; 128B (or 64B) swizzle, zero OOB fill.
 // Shared with wgrad_tc.cu (declared in tmap.cuh).
-int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box, int swizzle_bytes) {
+int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box, int swizzle_bytes, int pixel_stride) {
     MapKey key; memset(&key, 0, sizeof(key));
-    key.ptr = ptr; key.rank = rank | (swizzle_bytes << 8);
+    key.ptr = ptr; key.rank = rank | (swizzle_bytes << 8) | (pixel_stride << 16);
     for (int i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.box[i] = box[i]; }
     std::lock_guard<std::mutex> lk(g_map_mu);
     auto itf = g_maps.find(key);
@@ -320,7 +262,7 @@ int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* di
     cuuint64_t gd[4], gs[3]; cuuint32_t bx[4], es[4];
     uint64_t stride = 2;
     for (int i = 0; i < rank; ++i) {
-        gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1;
+        gd[i] = dims[i]; bx[i] = box[i]; es[i] = (i == 1 || i == 2) ? pixel_stride : 1;
         stride *= dims[i];
         if (i < rank - 1) gs[i] = stride;
     }
@@ -336,7 +278,7 @@ int st_make_tmap(CUtensorMap* out, const void* ptr, int rank, const uint64_t* di
 
 namespace {
 inline int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint32_t* box) {
-    return st_make_tmap(out, ptr, rank, dims, box, 128);
+    return st_make_tmap(out, ptr, rank, dims, box, 128, 1);
 }
 
 template <int KS, int BN, int PL>

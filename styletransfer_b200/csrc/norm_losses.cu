@@ -14,13 +14,30 @@ constexpr int IN_THREADS = 256;
 // MODE 1 (backward stats): a = dy_eff, b = dy_eff * xhat, with
 //        dy_eff = (relu ? dy * (gamma*xhat+beta > 0) : dy), dy summed over the 2x2
 //        upsampled positions when up != 0.
-template <int MODE>
-__global__ void __launch_bounds__(IN_THREADS)
+// gradient of one pixel: dy itself, or the sum over the 2x2 fan-out of a fused nearest upsample
+template <int UP>
+__device__ __forceinline__ void in_load_grad(const bf16* __restrict__ gh, const bf16* __restrict__ gl,
+                                             int n, int HW, int W, int C, int p, int cv, float (&g)[8]) {
+    if (!UP) {
+        load8(gh, gl, (static_cast<size_t>(n) * HW + p) * C + cv * 8, g);
+    } else {
+        const int h = p / W, w = p - h * W, W2 = W * 2;
+        const size_t base = ((static_cast<size_t>(n) * HW * 4) + static_cast<size_t>(h * 2) * W2 + w * 2) * C + cv * 8;
+        float t0[8], t1[8], t2[8], t3[8];
+        load8(gh, gl, base, t0); load8(gh, gl, base + C, t1);
+        load8(gh, gl, base + static_cast<size_t>(W2) * C, t2); load8(gh, gl, base + static_cast<size_t>(W2) * C + C, t3);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] = (t0[i] + t1[i]) + (t2[i] + t3[i]);
+    }
+}
+
+template <int MODE, int UP>
+__global__ void __launch_bounds__(IN_THREADS, 2)
 in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                 const bf16* __restrict__ gh, const bf16* __restrict__ gl,
                 const float* __restrict__ mean, const float* __restrict__ rstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
-                int HW, int W, int C, int splits, int chunk, int relu, int up, int x_planes,
+                int HW, int W, int C, int splits, int chunk, int relu, int x_planes,
                 float* __restrict__ partial /* [N][splits][2][C] */) {
     extern __shared__ float sm[];                 // [lanes][2][C]
     const int n = blockIdx.x / splits, sp = blockIdx.x % splits;
@@ -30,44 +47,62 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
     float sa[8], sb[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { sa[i] = 0.f; sb[i] = 0.f; }
-    float mu[8], rs[8], ga[8], be[8];
+    // backward: relu mask  gamma*xhat + beta > 0  <=>  ra*x + rb > 0 ; sums of ge and ge*(x - mu), scaled by rstd at the end
+    float mu[8], ra[8], rb[8];
     if (MODE == 1) {
+        const float4* m4 = reinterpret_cast<const float4*>(mean + n * C + cv * 8);
+        const float4* r4 = reinterpret_cast<const float4*>(rstd + n * C + cv * 8);
+        const float4* g4 = reinterpret_cast<const float4*>(gamma + cv * 8);
+        const float4* b4 = reinterpret_cast<const float4*>(beta + cv * 8);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            mu[i] = mean[n * C + cv * 8 + i]; rs[i] = rstd[n * C + cv * 8 + i];
-            ga[i] = gamma[cv * 8 + i]; be[i] = beta[cv * 8 + i];
+        for (int h = 0; h < 2; ++h) {
+            const float4 m = m4[h], r = r4[h], g = g4[h], b = b4[h];
+            const float mm[4] = {m.x, m.y, m.z, m.w}, rr[4] = {r.x, r.y, r.z, r.w};
+            const float gg[4] = {g.x, g.y, g.z, g.w}, bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                mu[h * 4 + i] = mm[i];
+                ra[h * 4 + i] = relu ? gg[i] * rr[i] : 0.f;
+                rb[h * 4 + i] = relu ? bb[i] - gg[i] * rr[i] * mm[i] : 1.f;
+            }
         }
     }
     if (pl < lanes) {
-        for (int p = p0 + pl; p < p1; p += lanes) {
-            float x[8];
-            load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
-            if (MODE == 0) {
+        if (MODE == 0) {
+#pragma unroll 2
+            for (int p = p0 + pl; p < p1; p += lanes) {
+                float x[8];
+                load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { sa[i] += x[i]; sb[i] += x[i] * x[i]; }
-            } else {
-                float g[8];
-                if (!up) {
-                    load8(gh, gl, (static_cast<size_t>(n) * HW + p) * C + cv * 8, g);
+            }
+        } else {
+            for (int p = p0 + pl; p < p1; p += 2 * lanes) {
+                const bool two = p + lanes < p1;
+                float x0[8], x1[8], g0[8], g1[8];
+                load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x0);
+                in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
+                if (two) {
+                    load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p + lanes) * C + cv * 8, x1);
+                    in_load_grad<UP>(gh, gl, n, HW, W, C, p + lanes, cv, g1);
                 } else {
-                    const int h = p / W, w = p - h * W, W2 = W * 2;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) g[i] = 0.f;
-#pragma unroll
-                    for (int d = 0; d < 4; ++d) {
-                        float t[8];
-                        load8(gh, gl, ((static_cast<size_t>(n) * HW * 4) + static_cast<size_t>(h * 2 + (d >> 1)) * W2 + w * 2 + (d & 1)) * C + cv * 8, t);
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) g[i] += t[i];
-                    }
+                    for (int i = 0; i < 8; ++i) { x1[i] = 0.f; g1[i] = 0.f; }
                 }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const float xhat = (x[i] - mu[i]) * rs[i];
-                    const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g[i];
-                    sa[i] += ge; sb[i] += ge * xhat;
+                    // NaN-safe form of the mask: keep the gradient only where the activation is > 0
+                    const float e0 = (fmaf(ra[i], x0[i], rb[i]) > 0.f) ? g0[i] : 0.f;
+                    const float e1 = (fmaf(ra[i], x1[i], rb[i]) > 0.f) ? g1[i] : 0.f;
+                    sa[i] += e0 + e1;
+                    sb[i] = fmaf(e0, x0[i] - mu[i], fmaf(e1, x1[i] - mu[i], sb[i]));
                 }
             }
+            const float4* r4 = reinterpret_cast<const float4*>(rstd + n * C + cv * 8);
+            const float4 r0 = r4[0], r1 = r4[1];
+            const float rr[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sb[i] *= rr[i];
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -288,10 +323,10 @@ __global__ void temporal_bwd_kernel(const float* __restrict__ os, const float* _
 }
 
 inline int in_splits(int N, int HW) {
-    int splits = (3 * st_num_sms() + N - 1) / N;
+    int splits = (4 * st_num_sms()) / N;              // N * splits = two full waves at 2 CTAs per SM
     const int maxs = (HW + 255) / 256;
     if (splits > maxs) splits = maxs;
-    if (splits > 64) splits = 64;
+    if (splits > 128) splits = 128;                  // = IN_MAX_SPLITS (workspace sizing below)
     if (splits < 1) splits = 1;
     return splits;
 }
@@ -302,7 +337,8 @@ inline int ew_grid(size_t n, int block) {
 
 }  // namespace
 
-size_t in_workspace_floats(int N, int C) { return static_cast<size_t>(N) * 64 * 2 * C; }
+constexpr int IN_MAX_SPLITS = 128;
+size_t in_workspace_floats(int N, int C) { return static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C; }
 
 int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* beta, float eps,
                bf16* yh, bf16* yl, int planes, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
@@ -310,8 +346,8 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
     const int lanes = IN_THREADS / (C / 8);
-    in_stats_kernel<0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, 0, planes, ws);
+    in_stats_kernel<0, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
     in_finalize_fwd_kernel<<<(N * C + 127) / 128, 128, 0, st>>>(ws, N * C, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
@@ -330,8 +366,12 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
     const int lanes = IN_THREADS / (C / 8);
     float* s1 = ws + static_cast<size_t>(N) * splits * 2 * C;
     float* s2 = s1 + static_cast<size_t>(N) * C;
-    in_stats_kernel<1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-        xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, up, x_planes, ws);
+    if (up)
+        in_stats_kernel<1, 1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws);
+    else
+        in_stats_kernel<1, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
     in_finalize_bwd_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");

@@ -4,7 +4,7 @@
 # Usage (on the GPU box): bash tests/run_gpu_groups.sh > gpurun_out/groups.log 2>&1
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv
-for k in layout generic "tcgen05_3x3" many_tiles plain_bf16 fp32_accurate dgrad wgrad maxpool gram test_mse instance tv; do
+for k in layout generic "tcgen05_3x3" tcx many_tiles plain_bf16 fp32_accurate dgrad wgrad maxpool gram test_mse instance tv; do
   echo "=== group $k"
   timeout 600 python -m pytest tests/test_kernels_gpu.py -q -m gpu -k "$k" -p no:cacheprovider --tb=short 2>&1 | tail -40
 done

@@ -101,6 +101,49 @@ def test_forward_conv_is_fp32_accurate(ops):
     assert rel_l2(nhwc(out, 64), ref) < 2e-5
 
 
+@pytest.mark.parametrize('cin,cout,H,W', [(32, 64, 20, 28), (64, 128, 16, 32), (32, 64, 33, 47), (64, 128, 9, 19)])
+def test_conv_tcx_stride2_forward(ops, cin, cout, H, W):
+    """3x3 stride-2 forward on the run-time-geometry tcgen05 kernel (strided TMA boxes)"""
+    from styletransfer_b200 import _lib
+    assert _conv_case(ops, 2, H, W, cin, cout, 3, 2, path=0) < TOL
+    assert _lib.lib().st_last_conv_kernel() == 2
+
+
+@pytest.mark.parametrize('cin,cout,H,W', [(32, 64, 16, 32), (64, 128, 24, 40), (64, 128, 34, 18)])
+def test_conv_tcx_stride2_dgrad(ops, cin, cout, H, W):
+    """backward-data of the stride-2 convs as 4 output-parity classes"""
+    from styletransfer_b200 import _lib
+    N = 2
+    w = seeded((cout, cin, 3, 3), 5, 1.0 / (cin * 9) ** 0.5, device='cuda')
+    gy = seeded((N, cout, H // 2, W // 2), 6, device='cuda')
+    x = seeded((N, cin, H, W), 7, device='cuda').requires_grad_(True)
+    F.conv2d(x, w, None, stride=2, padding=1).backward(gy)
+    gys = ops.from_nchw(gy)
+    pw = ops.PackedWeight(w, 1, rows_pad=cin, cols_pad=gys.C)
+    out, _, _ = ops.conv2d(gys, pw, stride=2, transposed=1, out_hw=(H, W))
+    assert _lib.lib().st_last_conv_kernel() == 2
+    assert rel_l2(nhwc(out, cin), x.grad) < TOL
+
+
+@pytest.mark.parametrize('cin,cout,H,W', [(32, 64, 16, 32), (32, 64, 21, 37), (32, 32, 8, 16), (96, 64, 12, 20)])
+def test_conv_tcx_32_channel_chunks(ops, cin, cout, H, W):
+    """stride-1 3x3 with a K side of 32-channel chunks (64-byte swizzle), forward and masked dgrad"""
+    from styletransfer_b200 import _lib
+    assert _conv_case(ops, 2, H, W, cin, cout, 3, 1, path=0) < TOL
+    assert _lib.lib().st_last_conv_kernel() == 2
+    N = 2
+    w = seeded((cin, cout, 3, 3), 5, 1.0 / (cout * 9) ** 0.5, device='cuda')     # forward layer cout -> cin
+    gy = seeded((N, cin, H, W), 6, device='cuda')
+    x = seeded((N, cout, H, W), 7, device='cuda').requires_grad_(True)
+    F.conv2d(x, w, None, padding=1).backward(gy)
+    gys = ops.from_nchw(gy)
+    pw = ops.PackedWeight(w, 2, rows_pad=cout, cols_pad=gys.C)
+    tap, add = seeded((N, cout, H, W), 8, device='cuda'), seeded((N, cout, H, W), 9, device='cuda')
+    out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=ops.from_nchw(add))
+    assert _lib.lib().st_last_conv_kernel() == 2
+    assert rel_l2(nhwc(out, cout), x.grad * (tap > 0) + add) < TOL
+
+
 @pytest.mark.parametrize('cin,cout,ks,stride,path', [
     (64, 64, 3, 1, 0), (128, 256, 3, 1, 0), (64, 128, 3, 1, 0), (3, 64, 3, 1, 1),
     (32, 64, 3, 2, 1), (64, 128, 3, 2, 1), (32, 3, 9, 1, 1), (3, 32, 9, 1, 1)])
