@@ -105,6 +105,35 @@ __device__ __forceinline__ void store8p(bf16* hi, bf16* lo, int planes, size_t o
     bf16* p2 = third_plane(hi, lo, planes);
     if (p2) *reinterpret_cast<uint4*>(p2 + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
 }
+// 256-bit global accesses (sm_100): one full 32-byte sector per lane
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&w)[8]) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
+                 "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
+}
+__device__ __forceinline__ void ldg256(const void* p, uint32_t (&w)[8]) {
+    asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]),
+                 "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(p));
+}
+// 16 consecutive channels -> up to three bf16 planes, 32 bytes each (off: multiple of 16 elements)
+__device__ __forceinline__ void store16p(bf16* hi, bf16* lo, int planes, size_t off, const float (&v)[16]) {
+    uint32_t hw[8], mw[8], lw[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float a = v[2 * i], b = v[2 * i + 1];
+        hw[i] = pack_bf16x2(a, b);
+        const float ra = a - bf16lo_to_f(hw[i]), rb = b - bf16hi_to_f(hw[i]);
+        mw[i] = pack_bf16x2(ra, rb);
+        lw[i] = pack_bf16x2(ra - bf16lo_to_f(mw[i]), rb - bf16hi_to_f(mw[i]));
+    }
+    stg256(hi + off, hw);
+    if (planes >= 2 && lo) stg256(lo + off, mw);
+    bf16* p2 = third_plane(hi, lo, planes);
+    if (p2) stg256(p2 + off, lw);
+}
+__device__ __forceinline__ void unpack16(const uint32_t (&w)[8], float (&v)[16]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[2 * i] = bf16lo_to_f(w[i]); v[2 * i + 1] = bf16hi_to_f(w[i]); }
+}
 // 2 values -> up to three bf16x2 words
 __device__ __forceinline__ void split2p(float a, float b, uint32_t& h, uint32_t& m, uint32_t& l) {
     h = pack_bf16x2(a, b);

@@ -46,7 +46,7 @@ template <int KS, int BN, int PL> struct Cfg {
     // PL > 1: the a0*w0 products go to a "main" accumulator, all correction terms to a second
     // one, summed in fp32 by the epilogue.  The tensor core's accumulate truncates; keeping the
     // ~2^-8 smaller corrections out of the main chain divides that error by the pass count.
-    static constexpr int NACC = PL > 1 ? 2 : 1;
+    static constexpr int NACC = PL == 1 ? 1 : (PL == 3 && BN <= 64) ? 3 : 2;
     static constexpr int STAGE_COLS = NACC * BN;
     static constexpr int TMEM_COLS = (2 * STAGE_COLS <= 32) ? 32 : (2 * STAGE_COLS <= 64) ? 64 :
                                      (2 * STAGE_COLS <= 128) ? 128 : (2 * STAGE_COLS <= 256) ? 256 : 512;
@@ -141,8 +141,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                 ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t d_main = tmem_base + acc * C::STAGE_COLS;
-                const uint32_t d_corr = d_main + (C::NACC - 1) * BN;
-                uint32_t acc_main = 0, acc_corr = 0;
+                    uint32_t acc_main = 0;
                 for (int c = 0; c < kchunks; ++c) {
 #pragma unroll
                     for (int s = 0; s < KS; ++s) {
@@ -157,19 +156,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                             const uint32_t a_lo = a_lo0 + ((r * TILE_W * 128) >> 4);
 #pragma unroll
                             for (int k = 0; k < KCH / 16; ++k) {
-                                // correction terms first (plane pairs i + j >= 1), the main product last
-#pragma unroll
-                                for (int i = 0; i < PL; ++i) {
-#pragma unroll
-                                    for (int j = 0; j < PL; ++j) {
-                                        if (i + j == 0 || i + j > PL - 1) continue;
-                                        if (leader)
-                                            ptx::mma_bf16_ss2(d_corr, a_lo + ((i * C::A_PLANE + k * 32) >> 4), b_lo0 + ((j * C::B_PLANE + k * 32) >> 4),
-                                                              desc_hi, idesc, acc_corr);
-                                        acc_corr = 1;
+                                // planes of B are consecutive N rows in shared memory, so one MMA of N = 2*BN / 3*BN
+                                // multiplies a plane of A with several planes of B (A is read once, not per pass):
+                                //   D0 = a0 w0 | D1 = a0 w1 + a1 w0 | D2 = a0 w2 + a1 w1 + a2 w0   (adjacent TMEM columns)
+                                const uint32_t ak = a_lo + ((k * 32) >> 4), bk = b_lo0 + ((k * 32) >> 4);
+                                if (PL == 1) {
+                                    if (leader) ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), acc_main);
+                                } else if (PL == 2) {
+                                    if (leader) {
+                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), acc_main);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), 1u);
+                                    }
+                                } else if (C::NACC == 3) {
+                                    if (leader) {
+                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 3 * BN), acc_main);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), 1u);
+                                        ptx::mma_bf16_ss2(d_main + 2 * BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), 1u);
+                                    }
+                                } else {
+                                    // 3 planes, BN = 128: N = 256 is the widest MMA; the 2^-16 terms share the D1 accumulator
+                                    if (leader) {
+                                        constexpr uint32_t id1 = ptx::umma_idesc_bf16(BLOCK_M, BN);
+                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), acc_main);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak, bk + ((2 * C::B_PLANE) >> 4), desc_hi, id1, 1u);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk + (C::B_PLANE >> 4), desc_hi, id1, 1u);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, id1, 1u);
+                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, id1, 1u);
                                     }
                                 }
-                                if (leader) ptx::mma_bf16_ss2(d_main, a_lo + ((k * 32) >> 4), b_lo0 + ((k * 32) >> 4), desc_hi, idesc, acc_main);
                                 acc_main = 1;
                             }
                             if (leader) ptx::tc_commit(&b_empty[b]);
@@ -197,10 +211,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             const int h = th * TILE_H + m / TILE_W, w = tw * TILE_W + m % TILE_W;
             const bool valid = (h < p.H) && (w < p.W);
             const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
+            TcEpilogue<BN, C::NACC> epi;
+            const bool fused = p.mask || p.add_hi;        // warp-uniform
+            if (fused) epi.prefetch(p, nb, pix, valid, 0);
             ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
             ptx::tc_fence_after();
             const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * C::STAGE_COLS;
-            tc_epilogue_row<BN, C::NACC>(p, taddr, nb, pix, valid);
+            if (fused) {
+#pragma unroll
+                for (int g = 0; g < TcEpilogue<BN, C::NACC>::NG; ++g) {
+                    if (g > 0) epi.prefetch(p, nb, pix, valid, g);
+                    epi.process(p, taddr, nb, pix, valid, g);
+                }
+            } else {
+                tc_epilogue_row<BN, C::NACC>(p, taddr, nb, pix, valid);
+            }
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
