@@ -14,7 +14,7 @@ long long g_st_launches = 0;
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
 int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
-                const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, cudaStream_t);
+                const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
 int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*,
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
@@ -97,12 +97,14 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
     ST_CHECK_ARG(ks >= 1 && ks <= 11 && (ks & 1) && stride >= 1, "st_conv2d: unsupported kernel size/stride");
     ST_CHECK_ARG(out_hi || relu_hi || out_nchw, "st_conv2d: no output requested");
     ST_CHECK_ARG(!(add_lo && !add_hi), "st_conv2d: add_lo without add_hi");
-    const bool tc = g_conv_path == 0 && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && !out_nchw &&
-                    w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad);
+    // an fp32 NCHW output (the image gradient) is taken by the 16-channel tile, unfused launches only
+    const bool nchw_ok = !out_nchw || (Cout_pad == 16 && Cnchw <= 4 && !mask && !add_hi);
+    const bool tc = g_conv_path == 0 && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && nchw_ok &&
+                    w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad) && (Cout_pad != 16 || out_nchw);
     g_last_conv_kernel = tc ? 1 : 3;
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
-                           bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, STRM(stream));
+                           bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw, STRM(stream));
     // run-time-geometry tcgen05 kernel: stride-2 3x3 (forward / transposed) and 32-channel K chunks
     const int xmode = transposed ? 2 : (stride == 2 ? 1 : 0);
     const bool tcx = g_conv_path == 0 && !up && pad == 1 && stride <= 2 && (!transposed || stride == 2) && !out_nchw && w_img_rows == 0 &&

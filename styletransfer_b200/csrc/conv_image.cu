@@ -43,18 +43,33 @@ conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, 
     for (int j = 0; j < 8; ++j) b8[j] = bias ? bias[g * 8 + j] : 0.f;
     const size_t HW = static_cast<size_t>(H) * W;
     const int tiles = N * tiles_h * tiles_w;
+    // the staged image tile of the NEXT iteration is fetched into registers while this one is computed
+    constexpr int ST_N = 3 * IM_SH * IM_SW, ST_PER = (ST_N + IMG_THREADS - 1) / IMG_THREADS;
+    float pre[ST_PER];
+    auto fetch = [&](int tile) {
+        int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
+#pragma unroll
+        for (int k = 0; k < ST_PER; ++k) {
+            const int i = threadIdx.x + k * IMG_THREADS;
+            const int xx = i % IM_SW; int r = i / IM_SW; const int y = r % IM_SH; const int c = r / IM_SH;
+            const int ih = th * IM_TH + y - 1, iw = tw * IM_TW + xx - 4;
+            float v = 0.f;
+            if (i < ST_N && ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (static_cast<size_t>(n) * 3 + c) * HW + static_cast<size_t>(ih) * W + iw);
+            pre[k] = v;
+        }
+    };
+    if (blockIdx.x < tiles) fetch(blockIdx.x);
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
         const int h0 = th * IM_TH, w0 = tw * IM_TW;
         __syncthreads();
-        for (int i = threadIdx.x; i < 3 * IM_SH * IM_SW; i += IMG_THREADS) {
-            const int xx = i % IM_SW; int r = i / IM_SW; const int y = r % IM_SH; const int c = r / IM_SH;
-            const int ih = h0 + y - 1, iw = w0 + xx - 4;
-            float v = 0.f;
-            if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (static_cast<size_t>(n) * 3 + c) * HW + static_cast<size_t>(ih) * W + iw);
-            st[i] = v;
+#pragma unroll
+        for (int k = 0; k < ST_PER; ++k) {
+            const int i = threadIdx.x + k * IMG_THREADS;
+            if (i < ST_N) st[i] = pre[k];
         }
         __syncthreads();
+        if (tile + gridDim.x < tiles) fetch(tile + gridDim.x);
         float acc[4][8];
 #pragma unroll
         for (int p = 0; p < 4; ++p)

@@ -334,15 +334,16 @@ int launch_planes(int planes, const CUtensorMap& ah, const CUtensorMap& al, cons
 
 // Eligibility of the tcgen05 path (the generic kernel covers everything else).
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout) {
-    return (ks == 3 || ks == 1) && stride == 1 && Cin % 64 == 0 && (Cout % 128 == 0 || Cout == 64 || Cout == 32);
+    return (ks == 3 || ks == 1) && stride == 1 && Cin % 64 == 0 && (Cout % 128 == 0 || Cout == 64 || Cout == 32 || (Cout == 16 && ks == 3));
 }
 
 int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin,
                 const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout,
                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
-                bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, cudaStream_t stream) {
+                bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_nchw, int Cnchw, cudaStream_t stream) {
     const int BN = (Cout % 128 == 0) ? 128 : Cout;
     const int taps = ks * ks;
+    ST_CHECK_ARG(!out_nchw || (Cnchw >= 1 && Cnchw <= 4 && !mask && !add_hi), "conv_tc: the NCHW output takes <= 4 channels and no mask / addend");
     ConvTcParams p;
     p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
     p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
@@ -355,6 +356,7 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
+    p.out_nchw = out_nchw; p.nchw_c = Cnchw;
 
     // the third plane follows the second at the same stride: the "lo" map simply spans both
     CUtensorMap ah, al, wh, wl;
@@ -375,6 +377,7 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
         if (BN == 128) return launch_planes<3, 128>(planes, ah, al, wh, wl, p, stream);
         if (BN == 64) return launch_planes<3, 64>(planes, ah, al, wh, wl, p, stream);
         if (BN == 32) return launch_planes<3, 32>(planes, ah, al, wh, wl, p, stream);
+        if (BN == 16) return launch_planes<3, 16>(planes, ah, al, wh, wl, p, stream);
     } else {
         if (BN == 128) return launch_planes<1, 128>(planes, ah, al, wh, wl, p, stream);
         if (BN == 64) return launch_planes<1, 64>(planes, ah, al, wh, wl, p, stream);

@@ -22,6 +22,7 @@ struct ConvTcParams {
     const bf16* add_lo;
     bf16* out_hi; bf16* out_lo;     // result (pre-activation)
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
+    float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
 };
 
 // Epilogue of one accumulator row in groups of up to 64 channels.  The ReLU mask and the addend of a
@@ -143,6 +144,14 @@ __device__ __forceinline__ void tc_epilogue_row(const ConvTcParams& p, uint32_t 
                 }
             }
             if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
+            if (p.out_nchw && j == 0) {
+                // module-boundary output (image gradient): lanes are consecutive pixels of a row
+                const size_t HW = static_cast<size_t>(p.H) * p.W;
+                const size_t n = pix / HW, rem = pix - n * HW;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (c < p.nchw_c) p.out_nchw[(n * p.nchw_c + c) * HW + rem] = v[c];
+            }
             if (p.relu_hi) {
 #pragma unroll
                 for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);

@@ -328,6 +328,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
+    p.out_nchw = nullptr; p.nchw_c = 0;
 
     CUtensorMap ah, al, wh, wl;
     const int ps = mode == 1 ? 2 : 1;

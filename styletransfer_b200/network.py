@@ -64,6 +64,7 @@ class GraphedClosure:
     everything ``fn`` reads (image, targets, weights) must live at fixed addresses."""
 
     def __init__(self, fn, leaves=(), warmup=3):
+        self.fn = fn                             # keeps every tensor the closure captured (baked into the graph) alive
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
         side.wait_stream(cur)
@@ -366,6 +367,7 @@ class StyleNetwork(nn.Module):
                     node.target = ops.gram(tap)
         losses = vgg_loss.vgg_losses(input_image, self.vgg, [n[0].target for n in self.style_losses],
                                      self.content_losses[0][0]._target_split, self.compute_feature_loss)
+        self._loss_vector = losses                       # [5 style, content, feature]
         for i, (node, _) in enumerate(self.style_losses):
             node.loss = losses[i]
         self.content_losses[0][0].loss = losses[5]
@@ -377,11 +379,15 @@ class StyleNetwork(nn.Module):
         Returns a callable; with CUDA graphs enabled (default) it replays a captured graph."""
         input_image.requires_grad_()
 
+        # style_weight * sum(style losses) + content_weight * content loss as one dot product with the
+        # loss vector (an elementwise product and a sum instead of the stack / sum / mul / add chain of the getters)
+        weights = torch.tensor([float(style_weight)] * 5 + [float(content_weight), 0.0], dtype=torch.float32,
+                               device=input_image.device)
+
         def body():
             input_image.grad = None
             self(input_image, content_image)
-            total_loss = (self.get_total_current_style_loss(weight=style_weight) +
-                          self.get_total_current_content_loss(weight=content_weight))
+            total_loss = (self._loss_vector * weights).sum()
             total_loss.backward()
             return total_loss
         if graph is None:
@@ -392,6 +398,7 @@ class StyleNetwork(nn.Module):
         # node for the image lives on another stream and would invalidate the capture
         for node, _ in self.style_losses + self.content_losses + self.feature_losses:
             node.loss = None
+        self._loss_vector = None
         return GraphedClosure(body, leaves=[input_image])
 
     def get_content_optimizer(self, input_img, optt=optim.Adam):

@@ -16,6 +16,8 @@ from . import ops
 PREFIX = [(3, 64, False), (64, 64, False), (64, 128, True), (128, 128, False), (128, 256, True)]
 CONTENT_TAP = 3
 N_LOSSES = 7
+# backward-data of conv1_1: tcgen05 16-channel tile (default) or the exact-fp32 CUDA-core kernel
+IMAGE_GRAD_TC = True
 
 
 class VGGPrefix:
@@ -28,11 +30,13 @@ class VGGPrefix:
         for i, (w, b) in enumerate(weights):
             ops._require_cuda(w, 'VGGPrefix')
             if i == 0:
-                # conv1_1 (K = 27) runs in exact fp32 on the CUDA cores, forward and backward-data,
-                # straight from / to the NCHW fp32 image (conv_image.cu): the fp32 weight is the operand
+                # conv1_1 forward (K = 27) runs in exact fp32 on the CUDA cores straight from the NCHW
+                # fp32 image (conv_image.cu): the fp32 weight is the operand
                 self.w0 = w.detach().contiguous().float()
                 self.fwd.append(None)
-                self.bwd.append(None)
+                # backward-data to the image: tcgen05 kernel with a 16-channel tile (3 used) that writes
+                # the NCHW fp32 gradient from its epilogue
+                self.bwd.append(ops.PackedWeight(w, 2, rows_pad=16))
             else:
                 self.fwd.append(ops.PackedWeight(w, 0, cols_pad=w.shape[1]))
                 # backward-data runs as a forward conv with flipped taps on the tcgen05 kernel
@@ -104,7 +108,10 @@ class _VGGLossFn(torch.autograd.Function):
         gp1, _, _ = ops.conv2d(g3, net.bwd[2])
         g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1))
         g1, _, _ = ops.conv2d(g2, net.bwd[1], mask=taps[0], add=style_grad(0))
-        gx = ops.conv_image_dgrad(g1, net.w0)
+        if IMAGE_GRAD_TC:
+            _, _, gx = ops.conv2d(g1, net.bwd[0], want_out=False, out_nchw_channels=3)
+        else:
+            gx = ops.conv_image_dgrad(g1, net.w0)
         ctx.taps = ctx.diffs = None
         return gx, None, None, None, None
 

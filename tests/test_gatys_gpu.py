@@ -181,5 +181,15 @@ def test_cuda_graph_closure_matches_eager(net_mod):
     l3 = eager().detach().clone()
     assert not torch.equal(l2, l1)
     assert torch.equal(l2, l3) and torch.equal(g2, x.grad)
+    # everything the captured closure reads must stay alive: small allocations between replays
+    # must not be able to land on memory the graph has baked in
+    for k in range(4):
+        junk = [torch.full((7,), float(k + i), device='cuda') for i in range(64)]
+        with torch.no_grad():
+            x.add_(0.05 * seeded((1, 3, h, w), 85 + k, device='cuda'))
+        lg, gg = graphed().detach().clone(), x.grad.detach().clone()
+        le = eager().detach().clone()
+        assert torch.equal(lg, le) and torch.equal(gg, x.grad), k
+        del junk
     out = net.train_gatys(style, content, steps=2)          # L-BFGS through the graphed closure
     assert out.shape == content.shape and torch.isfinite(out).all()

@@ -101,6 +101,20 @@ def test_forward_conv_is_fp32_accurate(ops):
     assert rel_l2(nhwc(out, 64), ref) < 2e-5
 
 
+@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64)])
+def test_conv_tcgen05_image_gradient(ops, N, H, W):
+    """backward-data of conv1_1 on the 16-channel tcgen05 tile, fp32 NCHW output from the epilogue"""
+    from styletransfer_b200 import _lib
+    x = seeded((N, 3, H, W), 71, device='cuda').requires_grad_(True)
+    w = seeded((64, 3, 3, 3), 72, 0.2, device='cuda')
+    gy = seeded((N, 64, H, W), 74, device='cuda')
+    F.conv2d(x, w, None, padding=1).backward(gy)
+    pw = ops.PackedWeight(w, 2, rows_pad=16)
+    _, _, gx = ops.conv2d(ops.from_nchw(gy, planes=2), pw, want_out=False, out_nchw_channels=3)
+    assert _lib.lib().st_last_conv_kernel() == 1
+    assert rel_l2(gx, x.grad) < TOL
+
+
 @pytest.mark.parametrize('cin,cout,H,W', [(32, 64, 20, 28), (64, 128, 16, 32), (32, 64, 33, 47), (64, 128, 9, 19)])
 def test_conv_tcx_stride2_forward(ops, cin, cout, H, W):
     """3x3 stride-2 forward on the run-time-geometry tcgen05 kernel (strided TMA boxes)"""
