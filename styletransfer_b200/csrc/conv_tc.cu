@@ -13,9 +13,9 @@
 // r*16 rows = r*2048 bytes into the box, which keeps the 1024-byte alignment the
 // 128B swizzle needs.  Zero padding comes from TMA out-of-bounds fill.
 //
-// Warp roles (192 threads, persistent, one CTA per SM):
+// Warp roles (320 threads, persistent, one CTA per SM):
 //   warp 0  TMA producer      warp 1  tcgen05.mma issuer (+ TMEM alloc)
-//   warps 2-5  epilogue: tcgen05.ld -> bias / mask / add -> split-bf16 stores
+//   warps 2-9  epilogue (two per TMEM lane quarter): tcgen05.ld -> bias / mask / add -> split-bf16 stores
 // Pipelines: A ring (halo boxes), B ring (weight tiles), 2 TMEM accumulators.
 #include "common.cuh"
 #include "ptx.cuh"
@@ -40,7 +40,7 @@ template <int KS, int BN, int PL> struct Cfg {
     static constexpr int SMEM_MAX = 232448;                 // 227 KB opt-in limit
     static constexpr int NA = (KS == 1 && PL < 3) ? 4 : 2;
     static constexpr int NB_FIT = (SMEM_MAX - 1024 - BAR_BYTES - NA * A_SLOT) / B_SLOT;
-    static constexpr int NB = NB_FIT > 8 ? 8 : NB_FIT;
+    static constexpr int NB = NB_FIT > 9 ? 9 : NB_FIT;      // 9 slots = all taps of a 3x3 layer resident (see w_resident)
     static_assert(NB >= 2, "weight ring needs two slots");
     static constexpr int SMEM = 1024 + NA * A_SLOT + NB * B_SLOT + BAR_BYTES;
     // PL > 1: the a0*w0 products go to a "main" accumulator, all correction terms to a second
@@ -82,7 +82,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         if (PL > 1) { ptx::prefetch_tmap(&tmA_lo); ptx::prefetch_tmap(&tmW_lo); }
         for (int i = 0; i < NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], 4); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], EPI_WARPS); }
         ptx::fence_barrier_init();
     }
     if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
@@ -114,6 +114,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                         if (++a == NA) { a = 0; aph ^= 1; }
 #pragma unroll
                         for (int r = 0; r < KS; ++r) {
+                            // resident weights: slot = tap, filled once (first tile), never released
+                            if (p.w_resident && wk != static_cast<int>(blockIdx.x)) continue;
                             ptx::mbar_wait(&b_empty[b], bph ^ 1);
                             ptx::mbar_expect_tx(&b_full[b], C::B_SLOT);
                             uint8_t* bd = sB + b * C::B_SLOT;
@@ -150,8 +152,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                         const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
 #pragma unroll
                         for (int r = 0; r < KS; ++r) {
-                            ptx::mbar_wait(&b_full[b], bph);
-                            ptx::tc_fence_after();
+                            if (!p.w_resident || it == 0) {
+                                ptx::mbar_wait(&b_full[b], bph);
+                                ptx::tc_fence_after();
+                            }
                             const uint32_t b_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sB + b * C::B_SLOT));
                             const uint32_t a_lo = a_lo0 + ((r * TILE_W * 128) >> 4);
 #pragma unroll
@@ -186,7 +190,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                                 }
                                 acc_main = 1;
                             }
-                            if (leader) ptx::tc_commit(&b_empty[b]);
+                            if (leader && !p.w_resident) ptx::tc_commit(&b_empty[b]);
                             __syncwarp();
                             if (++b == NB) { b = 0; bph ^= 1; }
                         }
@@ -199,37 +203,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             }
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int q = warp & 3;                       // TMEM lane quarter this warp may read
-        const int m = q * 32 + lane;                  // accumulator row = pixel within the patch
-        int it = 0;
-        for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
-            const int acc = it & 1;
-            const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
+        // ===================== epilogue (warps 2..9) =====================
+        auto dec = [&](int wk, int m) {
+            TcPix px;
+            px.nb = wk % p.n_blocks; int t = wk / p.n_blocks;
             const int tw = t % p.tiles_w; t /= p.tiles_w;
             const int th = t % p.tiles_h; const int n = t / p.tiles_h;
             const int h = th * TILE_H + m / TILE_W, w = tw * TILE_W + m % TILE_W;
-            const bool valid = (h < p.H) && (w < p.W);
-            const size_t pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
-            TcEpilogue<BN, C::NACC> epi;
-            const bool fused = p.mask || p.add_hi;        // warp-uniform
-            if (fused) epi.prefetch(p, nb, pix, valid, 0);
-            ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
-            ptx::tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * C::STAGE_COLS;
-            if (fused) {
-#pragma unroll
-                for (int g = 0; g < TcEpilogue<BN, C::NACC>::NG; ++g) {
-                    if (g > 0) epi.prefetch(p, nb, pix, valid, g);
-                    epi.process(p, taddr, nb, pix, valid, g);
-                }
-            } else {
-                tc_epilogue_row<BN, C::NACC>(p, taddr, nb, pix, valid);
-            }
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
-        }
+            px.valid = (h < p.H) && (w < p.W);
+            px.pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
+            return px;
+        };
+        tc_epilogue_warps<BN, C::NACC>(p, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
     }
 
     ptx::tc_fence_before();
@@ -317,7 +302,10 @@ int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, 
         attr_set = true;
     }
     int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tc_kernel<KS, BN, PL><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
+    ConvTcParams q = p;
+    // one K chunk, one channel block, shared weights, and the ring holds all taps: load the weights once
+    q.w_resident = (C::NB == KS * KS && p.Cin == KCH && p.n_blocks == 1 && p.w_img_rows == 0) ? 1 : 0;
+    conv_tc_kernel<KS, BN, PL><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, q);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
 }
@@ -349,6 +337,7 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
     p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
     p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
+    p.w_resident = 0;        // set by launch<> when every weight tile of the layer fits the B ring
     // both operands are read at the same plane count (the lower one if they differ)
     const int a_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1;
     const int w_planes_ = w_lo ? (w_planes >= 3 ? 3 : 2) : 1;

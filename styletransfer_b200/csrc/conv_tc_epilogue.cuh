@@ -8,13 +8,15 @@
 namespace {
 
 constexpr int TILE_H = 8, TILE_W = 16, BLOCK_M = 128;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;                 // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int EPI_WARPS = 8;
 
 struct ConvTcParams {
     int N, H, W, Cin, Cout;
     int tiles_h, tiles_w, n_blocks, work;
     int w_img_rows;                 // weight-row offset per image (0: shared weights)
     int w_rows_total;               // rows of one weight plane
+    int w_resident;                 // conv_tc: all weight tiles stay in shared memory (loaded once per CTA)
     int out_planes;                 // bf16 planes of the output tensors (1..3)
     const float* bias;              // [Cout] or null
     const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
@@ -25,138 +27,181 @@ struct ConvTcParams {
     float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
 };
 
-// Epilogue of one accumulator row in groups of up to 64 channels.  The ReLU mask and the addend of a
-// group do not depend on the accumulator: prefetch() issues those loads BEFORE the wait on the
-// accumulator barrier, so their latency overlaps the MMAs of the tile instead of following them
-// (the backward-data launches were bound by exactly that latency).  All global accesses are 256-bit:
-// the 16 channels one tcgen05.ld delivers are one full 32-byte sector per plane.
-template <int BN, int NACC>
-struct TcEpilogue {
-    static constexpr int GC = BN < 64 ? BN : 64;     // channels per group
-    static constexpr int GV = GC / 16, NG = BN / GC;
-    uint32_t mk[GV][8], ah[GV][8], al[GV][8];
+// ---------------------------------------------------------------------------------------------
+// Epilogue: 8 warps, two per TMEM lane quarter, each owning half of the tile's BN columns.
+//   unfused launches (no mask / addend): rolled loop over 16-column chunks;
+//   fused launches: the mask / addend of a 32-channel group live in a register buffer that is
+//   filled one tile AHEAD (two buffers), so their global-load latency never sits between the
+//   accumulator becoming ready and its store (the backward-data launches were bound by that).
+// All global accesses are 256-bit: the 16 channels one tcgen05.ld delivers are one 32-byte sector
+// per plane.
+// ---------------------------------------------------------------------------------------------
+struct TcPix { int nb; size_t pix; bool valid; };
+struct TcPre { uint32_t mk[2][8], ah[2][8], al[2][8]; };
 
-    __device__ __forceinline__ void prefetch(const ConvTcParams& p, int nb, size_t pix, bool valid, int g) {
-        if (!valid) return;
-        const size_t off = pix * p.Cout + nb * BN + g * GC;
+template <int GCH>
+__device__ __forceinline__ void tc_prefetch(const ConvTcParams& p, TcPre& b, const TcPix& px, int ch0) {
+    if (!px.valid) return;
+    const size_t off = px.pix * p.Cout + ch0;
+    if (p.mask) {
+#pragma unroll
+        for (int v = 0; v < GCH / 16; ++v) ldg256(p.mask + off + v * 16, b.mk[v]);
+    }
+    if (p.add_hi) {
+#pragma unroll
+        for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_hi + off + v * 16, b.ah[v]);
+        if (p.add_lo && p.out_planes >= 2) {
+#pragma unroll
+            for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_lo + off + v * 16, b.al[v]);
+        }
+    }
+}
+
+// one 16-channel chunk: accumulators -> bias -> mask -> addend -> stores
+template <int BN, int NACC, bool FUSED>
+__device__ __forceinline__ void tc_chunk(const ConvTcParams& p, uint32_t taddr, const TcPix& px, int col,
+                                         const uint32_t* mk, const uint32_t* ah, const uint32_t* al) {
+    uint32_t r[16], rc[16], rd[16];
+    ptx::tmem_ld16(taddr + col, r);
+    if (NACC > 1) ptx::tmem_ld16(taddr + BN + col, rc);
+    if (NACC > 2) ptx::tmem_ld16(taddr + 2 * BN + col, rd);
+    ptx::tmem_ld_wait();
+    if (!px.valid) return;
+    const int ch = px.nb * BN + col;
+    const size_t o = px.pix * p.Cout + ch;
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        v[i] = __uint_as_float(r[i]);
+        if (NACC == 2) v[i] += __uint_as_float(rc[i]);
+        if (NACC == 3) v[i] += __uint_as_float(rc[i]) + __uint_as_float(rd[i]);   // small terms first
+    }
+    if (p.bias) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 b = *reinterpret_cast<const float4*>(p.bias + ch + i * 4);
+            v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+        }
+    }
+    if (FUSED) {
         if (p.mask) {
 #pragma unroll
-            for (int v = 0; v < GV; ++v) ldg256(p.mask + off + v * 16, mk[v]);
+            for (int i = 0; i < 8; ++i) {
+                v[2 * i] = bf16lo_to_f(mk[i]) > 0.f ? v[2 * i] : 0.f;
+                v[2 * i + 1] = bf16hi_to_f(mk[i]) > 0.f ? v[2 * i + 1] : 0.f;
+            }
         }
         if (p.add_hi) {
+            const bool lo = p.add_lo && p.out_planes >= 2;
 #pragma unroll
-            for (int v = 0; v < GV; ++v) ldg256(p.add_hi + off + v * 16, ah[v]);
-            if (p.add_lo && p.out_planes >= 2) {
+            for (int i = 0; i < 8; ++i) {
+                float a0 = bf16lo_to_f(ah[i]), a1 = bf16hi_to_f(ah[i]);
+                if (lo) { a0 += bf16lo_to_f(al[i]); a1 += bf16hi_to_f(al[i]); }
+                v[2 * i] += a0; v[2 * i + 1] += a1;
+            }
+            const bf16* p2 = lo ? third_plane(p.add_hi, p.add_lo, p.out_planes) : nullptr;   // add carries the output's planes
+            if (p2) {
+                uint32_t w[8];
+                ldg256(p2 + o, w);
 #pragma unroll
-                for (int v = 0; v < GV; ++v) ldg256(p.add_lo + off + v * 16, al[v]);
+                for (int i = 0; i < 8; ++i) { v[2 * i] += bf16lo_to_f(w[i]); v[2 * i + 1] += bf16hi_to_f(w[i]); }
             }
         }
     }
-
-    // taddr: TMEM address of this warp's lane quarter / accumulator stage; pix: output pixel index
-    __device__ __forceinline__ void process(const ConvTcParams& p, uint32_t taddr, int nb, size_t pix, bool valid, int g) {
+    if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
+    if (!FUSED && p.out_nchw && ch == 0) {
+        // module-boundary output (image gradient): lanes are consecutive pixels of a row
+        const size_t HW = static_cast<size_t>(p.H) * p.W;
+        const size_t n = px.pix / HW, rem = px.pix - n * HW;
 #pragma unroll
-        for (int j = 0; j < GV; ++j) {
-            const int col = g * GC + j * 16;
-            uint32_t r[16], rc[16], rd[16];
-            ptx::tmem_ld16(taddr + col, r);
-            if (NACC > 1) ptx::tmem_ld16(taddr + BN + col, rc);
-            if (NACC > 2) ptx::tmem_ld16(taddr + 2 * BN + col, rd);
-            ptx::tmem_ld_wait();
-            if (valid) {
-                const int ch = nb * BN + col;
-                const size_t o = pix * p.Cout + ch;
-                float v[16];
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    v[i] = __uint_as_float(r[i]);
-                    if (NACC == 2) v[i] += __uint_as_float(rc[i]);
-                    if (NACC == 3) v[i] += __uint_as_float(rc[i]) + __uint_as_float(rd[i]);   // small terms first
-                }
-                if (p.bias) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const float4 b = *reinterpret_cast<const float4*>(p.bias + ch + i * 4);
-                        v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
-                    }
-                }
-                if (p.mask) {
-                    float mv[16];
-                    unpack16(mk[j], mv);
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = mv[i] > 0.f ? v[i] : 0.f;
-                }
-                if (p.add_hi) {
-                    float ad[16], t[16];
-                    unpack16(ah[j], ad);
-                    if (p.add_lo && p.out_planes >= 2) {
-                        unpack16(al[j], t);
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) ad[i] += t[i];
-                        const bf16* p2 = third_plane(p.add_hi, p.add_lo, p.out_planes);   // add carries the output's planes
-                        if (p2) {
-                            uint32_t w[8];
-                            ldg256(p2 + o, w);
-                            unpack16(w, t);
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) ad[i] += t[i];
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] += ad[i];
-                }
-                if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
-                if (p.relu_hi) {
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
-                    store16p(p.relu_hi, p.relu_lo, p.out_planes, o, v);
-                }
-            }
-        }
+        for (int c = 0; c < 4; ++c)
+            if (c < p.nchw_c) p.out_nchw[(n * p.nchw_c + c) * HW + rem] = v[c];
     }
-};
+    if (p.relu_hi) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+        store16p(p.relu_hi, p.relu_lo, p.out_planes, o, v);
+    }
+}
 
-// Rolled epilogue for launches without mask / addend (forward convs, Gram backward).
-template <int BN, int NACC>
-__device__ __forceinline__ void tc_epilogue_row(const ConvTcParams& p, uint32_t taddr, int nb, size_t pix, bool valid) {
+template <int BN, int NACC, int GCH>
+__device__ __forceinline__ void tc_process(const ConvTcParams& p, const TcPre& b, uint32_t taddr, const TcPix& px, int col0) {
+#pragma unroll
+    for (int j = 0; j < GCH / 16; ++j) tc_chunk<BN, NACC, true>(p, taddr, px, col0 + j * 16, b.mk[j], b.ah[j], b.al[j]);
+}
+
+// dec(wk, m) -> TcPix of accumulator row m of work item wk
+template <int BN, int NACC, class Decode>
+__device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_t tmem_base, int stage_cols,
+                                                  uint64_t* t_full, uint64_t* t_empty, int warp, int lane, const Decode& dec) {
+    constexpr int CW = BN >= 32 ? BN / 2 : BN;            // columns per warp
+    constexpr int GCH = CW < 32 ? CW : 32;                // channels per register buffer
+    constexpr int NGRP = CW / GCH;
+    const int q = warp & 3, hf = (warp - 2) >> 2;
+    const int m = q * 32 + lane;
+    const bool active = BN >= 32 || hf == 0;
+    const int col_base = BN >= 32 ? hf * CW : 0;
+    const bool fused = p.mask || p.add_hi;                // warp-uniform
+    const int step = gridDim.x;
+    auto taddr_of = [&](int it) { return tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (it & 1) * stage_cols; };
+    auto begin_tile = [&](int it) { ptx::mbar_wait(&t_full[it & 1], (it >> 1) & 1); ptx::tc_fence_after(); };
+    auto end_tile = [&](int it) { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
+
+    if (!fused || !active) {
+        int it = 0;
+        for (int wk = blockIdx.x; wk < p.work; wk += step, ++it) {
+            const TcPix px = dec(wk, m);
+            begin_tile(it);
+            if (active) {
 #pragma unroll 1
-    for (int j = 0; j < BN / 16; ++j) {
-        uint32_t r[16], rc[16], rd[16];
-        ptx::tmem_ld16(taddr + j * 16, r);
-        if (NACC > 1) ptx::tmem_ld16(taddr + BN + j * 16, rc);
-        if (NACC > 2) ptx::tmem_ld16(taddr + 2 * BN + j * 16, rd);
-        ptx::tmem_ld_wait();
-        if (valid) {
-            const int ch = nb * BN + j * 16;
-            const size_t o = pix * p.Cout + ch;
-            float v[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                v[i] = __uint_as_float(r[i]);
-                if (NACC == 2) v[i] += __uint_as_float(rc[i]);
-                if (NACC == 3) v[i] += __uint_as_float(rc[i]) + __uint_as_float(rd[i]);   // small terms first
+                for (int j = 0; j < CW / 16; ++j) tc_chunk<BN, NACC, false>(p, taddr_of(it), px, col_base + j * 16, nullptr, nullptr, nullptr);
             }
-            if (p.bias) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const float4 b = *reinterpret_cast<const float4*>(p.bias + ch + i * 4);
-                    v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
-                }
+            end_tile(it);
+        }
+        return;
+    }
+    TcPre A, B;
+    if (NGRP == 2) {
+        // buffer A = first 32 channels, B = second 32 channels; each is refilled for the next tile right after use
+        int wk = blockIdx.x;
+        if (wk < p.work) { const TcPix px = dec(wk, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base + GCH); }
+        for (int it = 0; wk < p.work; wk += step, ++it) {
+            const TcPix px = dec(wk, m);
+            const bool more = wk + step < p.work;
+            TcPix nx = px;
+            if (more) nx = dec(wk + step, m);
+            begin_tile(it);
+            tc_process<BN, NACC, GCH>(p, A, taddr_of(it), px, col_base);
+            if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
+            tc_process<BN, NACC, GCH>(p, B, taddr_of(it), px, col_base + GCH);
+            if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
+            end_tile(it);
+        }
+    } else {
+        // buffers alternate between tiles: A holds tile k, B tile k + 1; tile k + 2 is fetched into A after tile k
+        int wk0 = blockIdx.x, wk1 = wk0 + step;
+        if (wk0 < p.work) { const TcPix px = dec(wk0, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
+        if (wk1 < p.work) { const TcPix px = dec(wk1, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
+        int it = 0;
+        while (wk0 < p.work) {
+            {
+                const TcPix px = dec(wk0, m);
+                begin_tile(it);
+                tc_process<BN, NACC, GCH>(p, A, taddr_of(it), px, col_base);
+                end_tile(it); ++it;
             }
-            if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
-            if (p.out_nchw && j == 0) {
-                // module-boundary output (image gradient): lanes are consecutive pixels of a row
-                const size_t HW = static_cast<size_t>(p.H) * p.W;
-                const size_t n = pix / HW, rem = pix - n * HW;
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    if (c < p.nchw_c) p.out_nchw[(n * p.nchw_c + c) * HW + rem] = v[c];
+            const int wk2 = wk0 + 2 * step;
+            if (wk2 < p.work) { const TcPix px = dec(wk2, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
+            if (wk1 >= p.work) break;
+            {
+                const TcPix px = dec(wk1, m);
+                begin_tile(it);
+                tc_process<BN, NACC, GCH>(p, B, taddr_of(it), px, col_base);
+                end_tile(it); ++it;
             }
-            if (p.relu_hi) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
-                store16p(p.relu_hi, p.relu_lo, p.out_planes, o, v);
-            }
+            const int wk3 = wk1 + 2 * step;
+            if (wk3 < p.work) { const TcPix px = dec(wk3, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
+            wk0 = wk2; wk1 = wk3;
         }
     }
 }

@@ -6,7 +6,7 @@
 //     no multiplications by the inserted zeros),
 //   * 3x3 stride-1 convs whose K side has 32 channels (backward-data of the 64 -> 32 layer,
 //     network.py:594-599) with 64-byte-swizzled operand rows.
-// Same structure as conv_tc_kernel (warp 0 TMA producer, warp 1 MMA issuer, warps 2-5 epilogue,
+// Same structure as conv_tc_kernel (warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue,
 // A ring / B ring / two TMEM stages, main + correction accumulators); what differs is that the list
 // of A boxes per K chunk, the taps each box feeds (row offset into the box, weight tap index) and
 // the output pixel mapping come from a small table in the kernel parameters:
@@ -92,7 +92,7 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         if (PL > 1) { ptx::prefetch_tmap(&tmA_lo); ptx::prefetch_tmap(&tmW_lo); }
         for (int i = 0; i < NA; ++i) { ptx::mbar_init(&a_full[i], 1); ptx::mbar_init(&a_empty[i], 1); }
         for (int i = 0; i < NB; ++i) { ptx::mbar_init(&b_full[i], 1); ptx::mbar_init(&b_empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], 4); }
+        for (int i = 0; i < 2; ++i) { ptx::mbar_init(&t_full[i], 1); ptx::mbar_init(&t_empty[i], EPI_WARPS); }
         ptx::fence_barrier_init();
     }
     if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
@@ -202,36 +202,18 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             __syncwarp();
         }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
-        const int q = warp & 3;
-        const int m = q * 32 + lane;
-        int it = 0;
-        for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
-            const int acc = it & 1;
+        // ===================== epilogue (warps 2..9) =====================
+        auto dec = [&](int wk, int m) {
             const XWork w = x_decode(wk, p, geo.per_cls);
             const XClass& g = geo.cls[w.cls];
             const int oh = (w.th * TILE_H + m / TILE_W) * geo.os + g.oa, ow = (w.tw * TILE_W + m % TILE_W) * geo.os + g.ob;
-            const bool valid = (oh < geo.OH) && (ow < geo.OW);
-            const size_t pix = (static_cast<size_t>(w.n) * geo.OH + oh) * geo.OW + ow;
-            TcEpilogue<BN, C::NACC> epi;
-            const bool fused = p.mask || p.add_hi;        // warp-uniform
-            if (fused) epi.prefetch(p, w.nb, pix, valid, 0);
-            ptx::mbar_wait(&t_full[acc], (it >> 1) & 1);
-            ptx::tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * C::STAGE_COLS;
-            if (fused) {
-#pragma unroll
-                for (int g = 0; g < TcEpilogue<BN, C::NACC>::NG; ++g) {
-                    if (g > 0) epi.prefetch(p, w.nb, pix, valid, g);
-                    epi.process(p, taddr, w.nb, pix, valid, g);
-                }
-            } else {
-                tc_epilogue_row<BN, C::NACC>(p, taddr, w.nb, pix, valid);
-            }
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
-        }
+            TcPix px;
+            px.nb = w.nb;
+            px.valid = (oh < geo.OH) && (ow < geo.OW);
+            px.pix = (static_cast<size_t>(w.n) * geo.OH + oh) * geo.OW + ow;
+            return px;
+        };
+        tc_epilogue_warps<BN, C::NACC>(p, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
     }
 
     ptx::tc_fence_before();
