@@ -281,11 +281,15 @@ def run_ours(args, rank, world, local_rank):
     def traced_conv2d(xs, w, *a, **k):
         ks = w.ks if w is not None else k['w_ptrs'][3]
         cin = xs.C
-        cout = w.rows if w is not None else k['w_img_rows']
+        # algorithmic output channels (the packed row count is padded, e.g. 3 -> 16 for the image gradient)
+        cout = (w.cout if w.mode == 0 else w.cin) if w is not None else k['w_img_rows']
         tc = ks in (1, 3) and k.get('stride', 1) == 1 and not k.get('up') and not k.get('transposed') and cin % 64 == 0
         if not tc:
             return real_conv2d(xs, w, *a, **k)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        # keep the GPU busy while the host queues the launch, so that the events bracket the kernel
+        # alone and not the host's launch latency
+        torch.cuda._sleep(150000)
         e0.record()
         out = real_conv2d(xs, w, *a, **k)
         e1.record()
@@ -307,9 +311,10 @@ def run_ours(args, rank, world, local_rank):
     n3 = sum(g[2] for k, g in groups.items() if '<3x3>' in k)
     passes = {'bf16x6': 4.5, 'bf16x3': 3, 'bf16': 1}[args.precision]   # fwd 6 / bwd 3 passes in bf16x6
     achieved = fl3 / (ms3 * 1e-3) / 1e12 if ms3 > 0 else 0.0
-    roofline = {'bound': 'tensor', 'kernel': 'conv_tc_kernel<3x3> (8 launches per closure: 4 fwd + 4 dgrad)',
+    traffic, traffic_src = ncu_dram_traffic_per_launch()
+    roofline = {'bound': 'tensor', 'kernel': 'conv_tc_kernel<3x3> (9 launches per closure: 4 fwd + 5 dgrad)',
                 'achieved': achieved, 'peak': pk['tf_sustained'], 'unit': 'TFLOP/s', 'frac': achieved / pk['tf_sustained'],
-                'peak_source': pk['src'] + ' bf16_tflops_sustained', 'traffic': None,
+                'peak_source': pk['src'] + ' bf16_tflops_sustained', 'traffic': traffic, 'traffic_source': traffic_src,
                 'avg_launch_ms': ms3 / max(n3, 1), 'algorithmic_gflop_per_launch': fl3 / max(n3, 1) / 1e9,
                 'mma_passes_per_product': passes, 'issued_frac': achieved * passes / pk['tf_sustained'],
                 'share_of_step': (ms3 / args.steps) / (ms / args.steps)}
@@ -355,6 +360,22 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def ncu_dram_traffic_per_launch():
+    """dram__bytes_read.sum + dram__bytes_write.sum per 3x3 conv_tc launch, averaged over the launches
+    of one Gatys closure, from the committed `ncu --set full` capture (profiles/)."""
+    import csv
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles', 'r01g_conv_tc_ncu_full_summary.csv')
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr = rows[0]
+        ir, iw = hdr.index('dram__bytes_read.sum'), hdr.index('dram__bytes_write.sum')
+        unit = {'Mbyte': 1e6, 'Gbyte': 1e9, 'Kbyte': 1e3, 'byte': 1.0}[rows[1][ir]]
+        vals = [(float(r[ir]) + float(r[iw])) * unit for r in rows[2:] if r[0].startswith('conv_tc_kernel<3')]
+        return (sum(vals) / len(vals), 'profiles/r01g_conv_tc_ncu_full_summary.csv') if vals else (None, None)
+    except (OSError, ValueError, KeyError, IndexError):
+        return None, None
 
 
 def main():

@@ -23,7 +23,7 @@ int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, i
 int conv9_expand_run(const float*, const float*, int, int, const float*, const float*, int, bf16*, bf16*, int, int, int, int, cudaStream_t);
 int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
 size_t conv9_wgrad_workspace_bytes(int CS);
-int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, cudaStream_t);
+int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, int, cudaStream_t);
 bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho, int Wo);
 int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, cudaStream_t);
@@ -165,7 +165,7 @@ int st_conv9_wgrad(const void* b_hi, const void* b_lo, int b_planes, const float
     ST_CHECK_ARG(mode == 0 || CS == 3, "st_conv9_wgrad: layer 22 has 3 output channels");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && sc >= 3, "st_conv9_wgrad: empty shape");
     return conv9_wgrad_run(CBF(b_hi), CBF(b_lo), b_lo ? b_planes : 1, s0, s1, sc, CS, mode, dw, db,
-                           static_cast<float*>(workspace), workspace_bytes, N, H, W, STRM(stream));
+                           static_cast<float*>(workspace), workspace_bytes, N, H, W, g_conv_path == 0, STRM(stream));
 }
 
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks) {

@@ -188,9 +188,30 @@ size_t conv9_wgrad_workspace_bytes(int CS) {
 }
 
 // mode 0: layer 0 (B = dy [N,H,W,32], S = input image(s)); mode 1: layer 22 (B = x, S = dy NCHW fp32)
+int conv9_correlate_tc_run(const bf16* b_hi, const float* s, int sc, int cs_total, int c_off, float* partial,
+                           int N, int H, int W, int* nparts, cudaStream_t stream);
+
+// use_tc: tensor-core correlation (conv9_tc.cu) when the two planes of the big tensor are one plane
+// stride apart; otherwise (or with st_set_conv_path(1)) the CUDA-core kernel below
 int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float* s0, const float* s1, int sc, int CS, int mode,
-                    float* dw, float* db, float* ws, size_t ws_bytes, int N, int H, int W, cudaStream_t st) {
+                    float* dw, float* db, float* ws, size_t ws_bytes, int N, int H, int W, int use_tc, cudaStream_t st) {
     ST_CHECK_ARG(ws && ws_bytes >= conv9_wgrad_workspace_bytes(CS), "conv9_wgrad: workspace too small");
+    if (use_tc && planes >= 2 && b_lo == b_hi + static_cast<size_t>(N) * H * W * CB) {
+        int nparts = 0, rc;
+        if ((rc = conv9_correlate_tc_run(b_hi, s0, sc, CS, 0, ws, N, H, W, &nparts, st))) return rc;
+        if (CS == 6 && (rc = conv9_correlate_tc_run(b_hi, s1, sc, CS, 3, ws, N, H, W, &nparts, st))) return rc;
+        const int total = CB * CS * 81;
+        conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, nparts, CS, mode, dw);
+        ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
+        if (db) {
+            if (mode == 0) return ew_channel_sum(b_hi, b_lo, N * H * W, CB, CB, db, ws, st);
+            nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
+            ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
+            nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);
+            ST_CHECK_LAUNCH("nchw3_channel_sum_finish_kernel");
+        }
+        return ST_OK;
+    }
     const int rows = 6 / CS;
     const int work = N * ((H + rows - 1) / rows) * ((W + CR_WC - 1) / CR_WC);
     const int grid = work < conv9_grid() ? work : conv9_grid();

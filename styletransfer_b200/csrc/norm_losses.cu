@@ -168,77 +168,100 @@ in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int spli
     }
 }
 
+// Apply kernels: one block = (image n, pixel chunk); a thread keeps its 8 channels for the whole chunk,
+// so the per-channel statistics and affine parameters are loaded into registers once.
+__device__ __forceinline__ void load8f(const float* p, float (&v)[8]) {
+    const float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+
 // forward apply: y = gamma * (x - mean) * rstd + beta  (+ReLU) (+ x2 nearest upsample on write)
-__global__ void in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
-                                    const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta,
-                                    bf16* __restrict__ yh, bf16* __restrict__ yl,
-                                    int N, int H, int W, int C, int relu, int up, int planes) {
-    const int Cv = C / 8;
-    const size_t total = static_cast<size_t>(N) * H * W * Cv;
-    for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
-         idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const int cv = idx % Cv; const size_t pix = idx / Cv;
-        const int n = pix / (static_cast<size_t>(H) * W);
+template <int UP>
+__global__ void __launch_bounds__(IN_THREADS)
+in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                    bf16* __restrict__ yh, bf16* __restrict__ yl,
+                    int HW, int W, int C, int chunk, int relu, int planes) {
+    const int n = blockIdx.y;
+    const int Cv = C / 8, lanes = IN_THREADS / Cv;
+    const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
+    if (pl >= lanes) return;
+    const int p0 = blockIdx.x * chunk, p1 = min(HW, p0 + chunk);
+    float mu[8], rs[8], ga[8], be[8];
+    load8f(mean + n * C + cv * 8, mu); load8f(rstd + n * C + cv * 8, rs);
+    load8f(gamma + cv * 8, ga); load8f(beta + cv * 8, be);
+    const size_t img = static_cast<size_t>(n) * HW;
+#pragma unroll 2
+    for (int p = p0 + pl; p < p1; p += lanes) {
         float x[8];
-        load8p(xh, xl, planes, pix * C + cv * 8, x);
+        load8p(xh, xl, planes, (img + p) * C + cv * 8, x);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const int c = cv * 8 + i;
-            float y = gamma[c] * (x[i] - mean[n * C + c]) * rstd[n * C + c] + beta[c];
+            const float y = ga[i] * (x[i] - mu[i]) * rs[i] + be[i];
             x[i] = relu ? fmaxf(y, 0.f) : y;
         }
-        if (!up) {
-            store8p(yh, yl, planes, pix * C + cv * 8, x);
+        if (!UP) {
+            store8p(yh, yl, planes, (img + p) * C + cv * 8, x);
         } else {
-            const int p = pix - static_cast<size_t>(n) * H * W; const int h = p / W, w = p - h * W;
-#pragma unroll
-            for (int d = 0; d < 4; ++d)
-                store8p(yh, yl, planes, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, x);
+            const int h = p / W, w = p - h * W;
+            const size_t o = ((img * 4) + static_cast<size_t>(h * 2) * (W * 2) + w * 2) * C + cv * 8;
+            store8p(yh, yl, planes, o, x); store8p(yh, yl, planes, o + C, x);
+            store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C, x); store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C + C, x);
         }
     }
 }
 
 // backward apply: dx = gamma*rstd/HW * (HW*dy_eff - s1 - xhat*s2)
-__global__ void in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
-                                    const bf16* __restrict__ gh, const bf16* __restrict__ gl,
-                                    const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta,
-                                    const float* __restrict__ s1, const float* __restrict__ s2,
-                                    bf16* __restrict__ dxh, bf16* __restrict__ dxl,
-                                    int N, int H, int W, int C, int relu, int up, int x_planes) {
-    const int Cv = C / 8, HW = H * W;
+template <int UP>
+__global__ void __launch_bounds__(IN_THREADS)
+in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                    const bf16* __restrict__ gh, const bf16* __restrict__ gl,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ s1, const float* __restrict__ s2,
+                    bf16* __restrict__ dxh, bf16* __restrict__ dxl,
+                    int HW, int W, int C, int chunk, int relu, int x_planes) {
+    const int n = blockIdx.y;
+    const int Cv = C / 8, lanes = IN_THREADS / Cv;
+    const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
+    if (pl >= lanes) return;
+    const int p0 = blockIdx.x * chunk, p1 = min(HW, p0 + chunk);
     const float inv_hw = 1.0f / HW;
-    const size_t total = static_cast<size_t>(N) * HW * Cv;
-    for (size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total;
-         idx += static_cast<size_t>(gridDim.x) * blockDim.x) {
-        const int cv = idx % Cv; const size_t pix = idx / Cv;
-        const int n = pix / HW;
-        float x[8], g[8];
-        load8p(xh, xl, x_planes, pix * C + cv * 8, x);
-        if (!up) {
-            load8(gh, gl, pix * C + cv * 8, g);
-        } else {
-            const int p = pix - static_cast<size_t>(n) * HW; const int h = p / W, w = p - h * W;
+    float mu[8], rs[8], ga[8], be[8], a1[8], a2[8];
+    load8f(mean + n * C + cv * 8, mu); load8f(rstd + n * C + cv * 8, rs);
+    load8f(gamma + cv * 8, ga); load8f(beta + cv * 8, be);
+    load8f(s1 + n * C + cv * 8, a1); load8f(s2 + n * C + cv * 8, a2);
+    float gr[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) g[i] = 0.f;
-#pragma unroll
-            for (int d = 0; d < 4; ++d) {
-                float t[8];
-                load8(gh, gl, ((static_cast<size_t>(n) * H * 2 + h * 2 + (d >> 1)) * W * 2 + w * 2 + (d & 1)) * C + cv * 8, t);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) g[i] += t[i];
-            }
+    for (int i = 0; i < 8; ++i) gr[i] = ga[i] * rs[i];
+    const size_t img = static_cast<size_t>(n) * HW;
+    for (int p = p0 + pl; p < p1; p += (UP ? 1 : 2) * lanes) {
+        // two pixels per iteration, all loads first (one with the 2x2 gradient gather of the upsample)
+        const bool two = !UP && p + lanes < p1;
+        float x0[8], g0[8], x1[8], g1[8];
+        load8p(xh, xl, x_planes, (img + p) * C + cv * 8, x0);
+        in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
+        if (two) {
+            load8p(xh, xl, x_planes, (img + p + lanes) * C + cv * 8, x1);
+            in_load_grad<UP>(gh, gl, n, HW, W, C, p + lanes, cv, g1);
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const int c = cv * 8 + i;
-            const float rs = rstd[n * C + c];
-            const float xhat = (x[i] - mean[n * C + c]) * rs;
-            const float ge = (relu && !(gamma[c] * xhat + beta[c] > 0.f)) ? 0.f : g[i];
-            x[i] = gamma[c] * rs * (ge - inv_hw * (s1[n * C + c] + xhat * s2[n * C + c]));
+            const float xhat = (x0[i] - mu[i]) * rs[i];
+            const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g0[i];
+            x0[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
         }
-        store8(dxh, dxl, pix * C + cv * 8, x);
+        store8(dxh, dxl, (img + p) * C + cv * 8, x0);
+        if (two) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float xhat = (x1[i] - mu[i]) * rs[i];
+                const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g1[i];
+                x1[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
+            }
+            store8(dxh, dxl, (img + p + lanes) * C + cv * 8, x1);
+        }
     }
 }
 
@@ -330,6 +353,13 @@ inline int in_splits(int N, int HW) {
     if (splits < 1) splits = 1;
     return splits;
 }
+// blocks per image of the apply kernels: about 8 CTAs per SM over the batch, at least 64 pixels each
+inline int in_apply_blocks(int N, int HW) {
+    int b = (8 * st_num_sms() + N - 1) / N;
+    const int maxb = (HW + 63) / 64;
+    if (b > maxb) b = maxb;
+    return b < 1 ? 1 : b;
+}
 inline int ew_grid(size_t n, int block) {
     size_t g = (n + block - 1) / block; size_t cap = static_cast<size_t>(st_num_sms()) * 8;
     return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
@@ -351,8 +381,9 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
     in_finalize_fwd_kernel<<<(N * C + 127) / 128, 128, 0, st>>>(ws, N * C, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
-    in_apply_fwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
-        xh, xl, mean, rstd, gamma, beta, yh, yl, N, H, W, C, relu, up, planes);
+    const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
+    if (up) in_apply_fwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
+    else in_apply_fwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
     ST_CHECK_LAUNCH("in_apply_fwd_kernel");
     return ST_OK;
 }
@@ -375,8 +406,9 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
     in_finalize_bwd_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
-    in_apply_bwd_kernel<<<ew_grid(static_cast<size_t>(N) * HW * (C / 8), 256), 256, 0, st>>>(
-        xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, N, H, W, C, relu, up, x_planes);
+    const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
+    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes);
+    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes);
     ST_CHECK_LAUNCH("in_apply_bwd_kernel");
     return ST_OK;
 }

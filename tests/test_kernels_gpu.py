@@ -360,4 +360,4 @@ def test_conv9_layers(ops, C, N, H, W):
     dx = ops.conv9_expand(g2, w2.detach(), flip=True, planes=2)
     assert rel_l2(nhwc(dx), xb.grad) < 2e-5
     dw2, db2 = ops.conv9_wgrad(xs, g2, 1)
-    assert rel_l2(dw2, w2.grad) < 2e-6 and rel_l2(db2, b2.grad) < 2e-6
+    assert rel_l2(dw2, w2.grad) < 2e-5 and rel_l2(db2, b2.grad) < 2e-6
