@@ -20,7 +20,7 @@ int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const b
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, cudaStream_t);
 int conv_image_fwd(const float*, const float*, const float*, bf16*, bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, int, int, int, cudaStream_t);
-int conv9_expand_run(const float*, const float*, int, int, const float*, const float*, int, bf16*, bf16*, int, int, int, int, cudaStream_t);
+int conv9_expand_run(const float*, const float*, int, int, const float*, const float*, int, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
 size_t conv9_wgrad_workspace_bytes(int CS);
 int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, int, cudaStream_t);
@@ -151,7 +151,7 @@ int st_conv9_expand(const float* s0, const float* s1, int sc, int CS, const floa
                     void* out_hi, void* out_lo, int planes, int N, int H, int W, void* stream) {
     ST_CHECK_ARG(s0 && w && out_hi && (CS == 3 || (CS == 6 && s1)), "st_conv9_expand: null pointer or CS not 3/6");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && sc >= 3 && planes >= 1 && planes <= 3 && (planes == 1 || out_lo), "st_conv9_expand: bad shape/planes");
-    return conv9_expand_run(s0, s1, sc, CS, w, bias, flip, BF(out_hi), BF(out_lo), planes, N, H, W, STRM(stream));
+    return conv9_expand_run(s0, s1, sc, CS, w, bias, flip, BF(out_hi), BF(out_lo), planes, N, H, W, g_conv_path == 0, STRM(stream));
 }
 int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float* w, const float* bias, float* out,
                     int N, int H, int W, void* stream) {

@@ -149,8 +149,13 @@ inline int conv9_grid() { return st_num_sms() * 2; }
 
 int ew_channel_sum(const bf16* xh, const bf16* xl, int P, int C, int Cout, float* out, float* ws, cudaStream_t st);
 
+int conv9_expand_tc_run(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
+                        bf16* out_hi, bf16* out_lo, int planes, int N, int H, int W, cudaStream_t stream);
+
 int conv9_expand_run(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
-                     bf16* out_hi, bf16* out_lo, int planes, int N, int H, int W, cudaStream_t st) {
+                     bf16* out_hi, bf16* out_lo, int planes, int N, int H, int W, int use_tc, cudaStream_t st) {
+    // tensor-core path (conv9_tc.cu) for 2 / 3 output planes; st_set_conv_path(1) selects the CUDA-core kernel
+    if (use_tc && planes >= 2 && out_lo) return conv9_expand_tc_run(s0, s1, sc, CS, w, bias, flip, out_hi, out_lo, planes, N, H, W, st);
     const int th = (H + EX_TH - 1) / EX_TH, tw = (W + EX_TW - 1) / EX_TW;
     const int tiles = N * th * tw;
     const int grid = tiles < conv9_grid() ? tiles : conv9_grid();
