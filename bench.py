@@ -57,6 +57,25 @@ class ClockSampler:
         except OSError:
             self.p = None
 
+    def lines(self):
+        try:
+            with open(self.f.name) as fh:
+                return sum(1 for ln in fh if ln.count(',') >= 5)
+        except OSError:
+            return 0
+
+    def busy_until(self, n, work, timeout_s):
+        """Keeps the GPU under the benchmark's own load until n samples exist (the timed region of a
+        short run is shorter than one nvidia-smi period; samples taken right before and right after
+        it under the identical load bracket it)."""
+        if self.p is None:
+            return
+        t0 = time.perf_counter()
+        while self.lines() < n and time.perf_counter() - t0 < timeout_s:
+            for _ in range(20):
+                work()
+            torch.cuda.synchronize()
+
     def stop(self):
         if self.p is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
@@ -255,12 +274,18 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(max(args.warmup, 3)):
         closure()
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.busy_until(2, closure, 4.0)           # the same closure, untimed, until nvidia-smi reports
     n0 = L.st_launch_count()
     ms = timed(closure, args.steps)
     launches = L.st_launch_count() - n0
     if not args.no_graph:
         launches = closure.launches * args.steps      # kernels inside the replayed graph
+    if sampler:
+        sampler.busy_until(sampler.lines() + 2, closure, 2.0)
     clocks = sampler.stop() if sampler else None
+    if clocks is not None:
+        clocks['sampling'] = 'nvidia-smi every 100 ms under the continuous closure load around the timed steps'
 
     # ---- end to end: host image in pinned memory -> closure -> loss back on the host ----
     host_img = content.detach().cpu().pin_memory()
