@@ -100,9 +100,12 @@ int st_conv3x3_image_dgrad(const void* g_hi, const void* g_lo, int g_planes, con
  *                flip = 1: backward-data of layer 22, small = dy, w [CS][32][9][9] (the layer's weight). */
 int st_conv9_expand(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
                     void* out_hi, void* out_lo, int planes, int N, int H, int W, void* stream);
-/* big -> small: forward of layer 22, w [3][32][9][9], bias [3], out NCHW fp32 [N][3][H][W] */
+/* big -> small: forward of layer 22, w [3][32][9][9], bias [3], out NCHW fp32 [N][3][H][W].
+ * workspace (st_conv9_reduce_workspace_bytes) holds the fp32 partial outputs of the vertical stage of the
+ * tensor-core path; with workspace == NULL the CUDA-core kernel runs. */
+size_t st_conv9_reduce_workspace_bytes(int N, int H, int W);
 int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float* w, const float* bias, float* out,
-                    int N, int H, int W, void* stream);
+                    void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream);
 /* backward-weight (+ bias).  mode 0: layer 0, big = dy, small = the layer's input -> dw [32][CS][9][9], db [32];
  *                            mode 1: layer 22, big = the layer's input, small = dy -> dw [CS][32][9][9], db [CS] */
 size_t st_conv9_wgrad_workspace_bytes(int CS);

@@ -33,7 +33,8 @@ SIGNATURES = {
     'st_conv3x3_image_fwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_conv3x3_image_dgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
     'st_conv9_expand': (_I, [_P, _P, _I, _I, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
-    'st_conv9_reduce': (_I, [_P, _P, _I, _P, _P, _P, _I, _I, _I, _P]),
+    'st_conv9_reduce_workspace_bytes': (_Z, [_I, _I, _I]),
+    'st_conv9_reduce': (_I, [_P, _P, _I, _P, _P, _P, _P, _Z, _I, _I, _I, _P]),
     'st_conv9_wgrad_workspace_bytes': (_Z, [_I]),
     'st_conv9_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _P, _Z, _I, _I, _I, _P]),
     'st_conv2d_wgrad_workspace_bytes': (_Z, [_I, _I, _I, _I, _I, _I]),

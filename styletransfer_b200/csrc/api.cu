@@ -23,10 +23,12 @@ int conv_image_dgrad(const bf16*, const bf16*, int, const float*, float*, int, i
 int conv9_expand_run(const float*, const float*, int, int, const float*, const float*, int, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int conv9_reduce_run(const bf16*, const bf16*, int, const float*, const float*, float*, int, int, int, cudaStream_t);
 size_t conv9_wgrad_workspace_bytes(int CS);
+size_t conv9_reduce_workspace_bytes(int N, int H, int W);
+int conv9_reduce_tc_run(const bf16*, const bf16*, int, const float*, const float*, float*, void*, size_t, int, int, int, cudaStream_t);
 int conv9_wgrad_run(const bf16*, const bf16*, int, const float*, const float*, int, int, int, float*, float*, float*, size_t, int, int, int, int, cudaStream_t);
 bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho, int Wo);
 int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
-                 const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, cudaStream_t);
+                 const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, float*, cudaStream_t);
 bool gram_tc_eligible(int C, bool two_planes);
 size_t gram_tc_workspace_bytes(int B, int HW, int C);
 int gram_tc_run(const bf16*, int, int, int, float, float*, void*, size_t, cudaStream_t);
@@ -112,7 +114,7 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
     if (tcx) g_last_conv_kernel = 2;
     if (tcx)
         return conv_tcx_run(xmode, CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, Cout_pad, Ho, Wo,
-                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, STRM(stream));
+                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, nullptr, STRM(stream));
     if (w_img_rows != 0) {
         // per-image weights on the generic path: one launch per image
         for (int n = 0; n < N; ++n) {
@@ -153,9 +155,14 @@ int st_conv9_expand(const float* s0, const float* s1, int sc, int CS, const floa
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && sc >= 3 && planes >= 1 && planes <= 3 && (planes == 1 || out_lo), "st_conv9_expand: bad shape/planes");
     return conv9_expand_run(s0, s1, sc, CS, w, bias, flip, BF(out_hi), BF(out_lo), planes, N, H, W, g_conv_path == 0, STRM(stream));
 }
+size_t st_conv9_reduce_workspace_bytes(int N, int H, int W) { return (N > 0 && H > 0 && W > 0) ? conv9_reduce_workspace_bytes(N, H, W) : 0; }
 int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float* w, const float* bias, float* out,
-                    int N, int H, int W, void* stream) {
+                    void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream) {
     ST_CHECK_ARG(x_hi && w && out && N > 0 && H > 0 && W > 0, "st_conv9_reduce: null pointer or empty shape");
+    // tensor-core path: planes one plane stride apart (the TMA map spans them), workspace given
+    const bool planes_ok = !x_lo || CBF(x_lo) == CBF(x_hi) + static_cast<size_t>(N) * H * W * 32;
+    if (workspace && g_conv_path == 0 && planes_ok)
+        return conv9_reduce_tc_run(CBF(x_hi), CBF(x_lo), x_lo ? planes : 1, w, bias, out, workspace, workspace_bytes, N, H, W, STRM(stream));
     return conv9_reduce_run(CBF(x_hi), CBF(x_lo), x_lo ? planes : 1, w, bias, out, N, H, W, STRM(stream));
 }
 size_t st_conv9_wgrad_workspace_bytes(int CS) { return (CS == 3 || CS == 6) ? conv9_wgrad_workspace_bytes(CS) : 0; }

@@ -191,3 +191,98 @@ conv9_reduce_kernel(const bf16* __restrict__ x_hi, const bf16* __restrict__ x_lo
 }  // namespace
 
 #include "conv9_wgrad.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// Layer-22 forward (32 -> 3, 9x9) on the tensor cores, in two stages:
+//   (1) T[p][co*9 + s] = sum_{r, ci} X[p + (r - 4) rows][ci] * W[co][ci][r][s]   -- a VERTICAL 9-tap conv
+//       32 -> 27 (padded 32) channels: K = 288 per output instead of K = 2592 for 3 outputs, so the
+//       activation tile is read 9 times from shared memory, not 81 (conv_tcx mode 3, fp32 output);
+//   (2) out[co][p] = bias[co] + sum_s T[p + (s - 4) columns][co*9 + s]            -- horizontal gather-sum.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+// weights [3][32][9][9] fp32 -> split-bf16 [planes][row = co*9 + s (32, 27 used)][tap = r (9)][ci (32)]
+__global__ void conv9_pack_vertical_kernel(const float* __restrict__ w, bf16* __restrict__ hi, int planes) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int total = 32 * 9 * CB;
+    if (idx >= total) return;
+    const int ci = idx % CB; int q = idx / CB; const int r = q % 9; const int row = q / 9;
+    float v = 0.f;
+    if (row < 27) { const int co = row / 9, s = row % 9; v = w[((co * CB + ci) * 9 + r) * 9 + s]; }
+#pragma unroll 1
+    for (int pl = 0; pl < planes; ++pl) {
+        const bf16 h = __float2bfloat16_rn(v);
+        hi[static_cast<size_t>(pl) * total + idx] = h;
+        v -= __bfloat162float(h);
+    }
+}
+
+// one thread per output pixel; the T rows of 256 consecutive pixels (+4 on each side) are staged in
+// shared memory with coalesced 128-bit loads (row stride 33 words: conflict-free gathers)
+constexpr int GA_PIX = 256, GA_ROWS = GA_PIX + 2 * PAD9, GA_LD = 33;
+__global__ void __launch_bounds__(GA_PIX)
+conv9_gather_kernel(const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out, int N, int H, int W) {
+    __shared__ float sT[GA_ROWS * GA_LD];
+    const size_t HW = static_cast<size_t>(H) * W;
+    const long long total = static_cast<long long>(N) * HW;
+    const float b0 = bias ? bias[0] : 0.f, b1 = bias ? bias[1] : 0.f, b2 = bias ? bias[2] : 0.f;
+    for (long long base = static_cast<long long>(blockIdx.x) * GA_PIX; base < total; base += static_cast<long long>(gridDim.x) * GA_PIX) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < GA_ROWS * 8; i += GA_PIX) {
+            const int row = i >> 3, q4 = i & 7;
+            const long long gp = base - PAD9 + row;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (gp >= 0 && gp < total) v = __ldg(reinterpret_cast<const float4*>(T + gp * CB) + q4);
+            float* d = sT + row * GA_LD + q4 * 4;
+            d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+        }
+        __syncthreads();
+        const long long pix = base + threadIdx.x;
+        if (pix < total) {
+            const size_t n = pix / HW; const size_t rem = pix - n * HW;
+            const int w = static_cast<int>(rem % W);
+            float a0 = b0, a1 = b1, a2 = b2;
+#pragma unroll
+            for (int s = 0; s < 9; ++s) {
+                const int iw = w + s - PAD9;
+                if (iw < 0 || iw >= W) continue;
+                const float* t = sT + (threadIdx.x + s) * GA_LD;
+                a0 += t[s]; a1 += t[9 + s]; a2 += t[18 + s];
+            }
+            out[(n * 3 + 0) * HW + rem] = a0;
+            out[(n * 3 + 1) * HW + rem] = a1;
+            out[(n * 3 + 2) * HW + rem] = a2;
+        }
+    }
+}
+
+}  // namespace
+
+int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
+                 const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, float*, cudaStream_t);
+
+size_t conv9_reduce_workspace_bytes(int N, int H, int W) {
+    return static_cast<size_t>(N) * H * W * CB * sizeof(float) + 3 * 32 * 9 * CB * sizeof(bf16) + 1024;
+}
+
+// workspace: [T fp32 N*H*W*32][packed weights 3 planes]
+int conv9_reduce_tc_run(const bf16* x_hi, const bf16* x_lo, int planes, const float* w, const float* bias, float* out,
+                        void* workspace, size_t workspace_bytes, int N, int H, int W, cudaStream_t st) {
+    ST_CHECK_ARG(workspace && workspace_bytes >= conv9_reduce_workspace_bytes(N, H, W), "conv9_reduce: workspace too small");
+    float* T = static_cast<float*>(workspace);
+    const size_t t_bytes = (static_cast<size_t>(N) * H * W * CB * sizeof(float) + 1023) / 1024 * 1024;
+    bf16* wp = reinterpret_cast<bf16*>(static_cast<uint8_t*>(workspace) + t_bytes);
+    const int wplanes = planes >= 3 ? 3 : (planes == 2 ? 2 : 1);
+    const int total = 32 * 9 * CB;
+    conv9_pack_vertical_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, wp, wplanes);
+    ST_CHECK_LAUNCH("conv9_pack_vertical_kernel");
+    int rc = conv_tcx_run(3, x_hi, x_lo, planes, N, H, W, CB, wp, wplanes > 1 ? wp + total : nullptr, wplanes, 32, 32, H, W,
+                          nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, T, st);
+    if (rc) return rc;
+    size_t blocks = (static_cast<size_t>(N) * H * W + GA_PIX - 1) / GA_PIX;
+    const size_t cap = static_cast<size_t>(st_num_sms()) * 6;
+    if (blocks > cap) blocks = cap;
+    conv9_gather_kernel<<<static_cast<unsigned>(blocks), GA_PIX, 0, st>>>(T, bias, out, N, H, W);
+    ST_CHECK_LAUNCH("conv9_gather_kernel");
+    return ST_OK;
+}

@@ -345,7 +345,7 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
-    p.out_nchw = out_nchw; p.nchw_c = Cnchw;
+    p.out_nchw = out_nchw; p.nchw_c = Cnchw; p.out_f32 = nullptr;
 
     // the third plane follows the second at the same stride: the "lo" map simply spans both
     CUtensorMap ah, al, wh, wl;

@@ -25,6 +25,7 @@ struct ConvTcParams {
     bf16* out_hi; bf16* out_lo;     // result (pre-activation)
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
     float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
+    float* out_f32;                 // optional fp32 [pixel][Cout] output (unfused launches only)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -109,6 +110,12 @@ __device__ __forceinline__ void tc_chunk(const ConvTcParams& p, uint32_t taddr, 
         }
     }
     if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
+    if (!FUSED && p.out_f32) {
+        uint32_t w0[8], w1[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { w0[i] = __float_as_uint(v[i]); w1[i] = __float_as_uint(v[8 + i]); }
+        stg256(p.out_f32 + o, w0); stg256(p.out_f32 + o + 8, w1);
+    }
     if (!FUSED && p.out_nchw && ch == 0) {
         // module-boundary output (image gradient): lanes are consecutive pixels of a row
         const size_t HW = static_cast<size_t>(p.H) * p.W;

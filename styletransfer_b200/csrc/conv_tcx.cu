@@ -22,8 +22,9 @@
 
 namespace {
 
-constexpr int X_MAX_BOX = 6, X_MAX_TAP = 3, X_MAX_CLS = 4;
-constexpr int X_ROWS = TILE_H + 2;                 // pixel rows of the largest A box
+constexpr int X_MAX_BOX = 6, X_MAX_TAP = 9, X_MAX_CLS = 4;
+constexpr int X_ROWS = TILE_H + 2;                 // pixel rows of the largest A box of the 3x3 modes
+constexpr int X_ROWS9 = TILE_H + 8;                // ... of the vertical 9-tap mode
 
 struct XBox { int dw, dh, ntap; int row_off[X_MAX_TAP]; int widx[X_MAX_TAP]; };
 struct XClass { int nbox, oa, ob, taps; XBox box[X_MAX_BOX]; };
@@ -33,9 +34,9 @@ struct XGeom {
     XClass cls[X_MAX_CLS];
 };
 
-template <int BN, int PL, int KC> struct XCfg {
+template <int BN, int PL, int KC, int ROWS = X_ROWS> struct XCfg {
     static constexpr int ROWB = KC * 2;                                  // operand row: 64 or 128 bytes
-    static constexpr int A_PLANE = X_ROWS * TILE_W * ROWB;
+    static constexpr int A_PLANE = ROWS * TILE_W * ROWB;
     static constexpr int B_PLANE = BN * ROWB;
     static constexpr int A_SLOT = PL * A_PLANE, B_SLOT = PL * B_PLANE;
     static constexpr int BAR_BYTES = 256;
@@ -64,12 +65,12 @@ __device__ __forceinline__ XWork x_decode(int wk, const ConvTcParams& p, int per
     return w;
 }
 
-template <int BN, int PL, int KC>
+template <int BN, int PL, int KC, int ROWS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
                 const ConvTcParams p, const __grid_constant__ XGeom geo) {
-    using C = XCfg<BN, PL, KC>;
+    using C = XCfg<BN, PL, KC, ROWS>;
     constexpr int NA = C::NA, NB = C::NB;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -221,18 +222,18 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     if (warp == 1) ptx::tmem_dealloc(tmem_base, C::TMEM_COLS);
 }
 
-template <int BN, int PL, int KC>
+template <int BN, int PL, int KC, int ROWS = X_ROWS>
 int xlaunch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
             const ConvTcParams& p, const XGeom& g, cudaStream_t stream) {
-    using C = XCfg<BN, PL, KC>;
+    using C = XCfg<BN, PL, KC, ROWS>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tcx_kernel<BN, PL, KC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv_tcx_kernel<BN, PL, KC, ROWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) { st_set_error("conv_tcx smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
     const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tcx_kernel<BN, PL, KC><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p, g);
+    conv_tcx_kernel<BN, PL, KC, ROWS><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p, g);
     ST_CHECK_LAUNCH("conv_tcx_kernel");
     return ST_OK;
 }
@@ -254,7 +255,10 @@ void x_add_tap(XClass& c, int row_off, int widx) { XBox& b = c.box[c.nbox - 1]; 
 // mode 0: 3x3 stride 1 pad 1 (weight tap r*3+s reads pixel + (r-1, s-1))
 // mode 1: 3x3 stride 2 pad 1 forward
 // mode 2: backward-data of mode 1 (weights packed rows = ci, cols = co, unflipped taps), Ho = 2H, Wo = 2W
+// mode 3: vertical 9-tap conv (pad 4), 32 -> 32 channels, fp32 output [pixel][32] (first stage of the
+//         32 -> 3 9x9 layer: weight row co*9 + s, tap r; see conv9_reduce_tc_run)
 bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho, int Wo) {
+    if (mode == 3) return ks == 9 && Cin == 32 && Cout == 32 && Ho == H && Wo == W;
     if (ks != 3 || Cin % 32 != 0 || !(Cout % 128 == 0 || Cout == 64 || Cout == 32)) return false;
     if (mode == 0) return Ho == H && Wo == W;
     if (mode == 1) return Ho == (H - 1) / 2 + 1 && Wo == (W - 1) / 2 + 1;
@@ -264,7 +268,7 @@ bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho
 int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin,
                  const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int Cout, int Ho, int Wo,
                  const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
-                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, cudaStream_t stream) {
+                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_f32, cudaStream_t stream) {
     const int BN = (Cout % 128 == 0) ? 128 : Cout;
     const int KC = (Cin % 64 == 0) ? 64 : 32;
     const int IH = mode == 1 ? Ho : H, IW = mode == 1 ? Wo : W;      // tile iteration space
@@ -277,6 +281,10 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
             x_add_box(g.cls[0], s - 1, -1);
             for (int r = 0; r < 3; ++r) x_add_tap(g.cls[0], r, r * 3 + s);
         }
+    } else if (mode == 3) {
+        g.ncls = 1; rows = X_ROWS9;
+        x_add_box(g.cls[0], 0, -4);
+        for (int r = 0; r < 9; ++r) x_add_tap(g.cls[0], r, r);
     } else if (mode == 1) {
         // input row 2*oh + r - 1: r = 1 reads even rows, r = 0 / 2 the odd rows oh - 1 / oh of one strided box
         g.ncls = 1; rows = TILE_H + 1;
@@ -310,7 +318,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.out_planes = out_planes;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
-    p.out_nchw = nullptr; p.nchw_c = 0;
+    p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32;
 
     CUtensorMap ah, al, wh, wl;
     const int ps = mode == 1 ? 2 : 1;
@@ -326,6 +334,11 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     al = ah; wl = wh;
     if (planes > 1 && (rc = st_make_tmap(&al, x_lo, 4, ad2, ab, KC * 2, ps))) return rc;
     if (planes > 1 && (rc = st_make_tmap(&wl, w_lo, 3, wd2, wb, KC * 2))) return rc;
+    if (mode == 3) {
+        if (planes == 3) return xlaunch<32, 3, 32, X_ROWS9>(ah, al, wh, wl, p, g, stream);
+        if (planes == 2) return xlaunch<32, 2, 32, X_ROWS9>(ah, al, wh, wl, p, g, stream);
+        return xlaunch<32, 1, 32, X_ROWS9>(ah, al, wh, wl, p, g, stream);
+    }
     if (KC == 64) {
         if (BN == 128) return xlaunch_planes<128, 64>(planes, ah, al, wh, wl, p, g, stream);
         if (BN == 64) return xlaunch_planes<64, 64>(planes, ah, al, wh, wl, p, g, stream);

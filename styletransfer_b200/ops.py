@@ -207,9 +207,11 @@ def conv9_expand(x, w, bias=None, flip=False, planes=None):
 def conv9_reduce(x, w, bias=None):
     """9x9 conv from a 32-channel Split to a 3-channel NCHW fp32 tensor (layer-22 forward)."""
     assert x.C == 32 and tuple(w.shape) == (3, 32, 9, 9)
+    L = _lib.lib()
     out = torch.empty((x.N, 3, x.H, x.W), dtype=torch.float32, device=x.buf.device)
-    _lib.check(_lib.lib().st_conv9_reduce(x.hi, x.lo, x.planes, w.data_ptr(), _p(bias), out.data_ptr(), x.N, x.H, x.W, _stream()),
-               'st_conv9_reduce')
+    ws = workspace(L.st_conv9_reduce_workspace_bytes(x.N, x.H, x.W), x.buf.device, 'conv9')
+    _lib.check(L.st_conv9_reduce(x.hi, x.lo, x.planes, w.data_ptr(), _p(bias), out.data_ptr(), ws.data_ptr(), ws.numel(),
+                                 x.N, x.H, x.W, _stream()), 'st_conv9_reduce')
     return out
 
 

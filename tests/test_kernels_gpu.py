@@ -331,10 +331,21 @@ def test_conv_image_fwd_and_dgrad(ops, N, H, W):
     assert gx.shape == x.shape and rel_l2(gx, x.grad) < 2e-5
 
 
+@pytest.mark.parametrize('path', [0, 1])
 @pytest.mark.parametrize('C,N,H,W', [(3, 2, 20, 36), (6, 1, 13, 45), (3, 1, 64, 160)])
-def test_conv9_layers(ops, C, N, H, W):
-    """The 9x9 layers as exact-fp32 direct convolutions: layer 0 (C -> 32) forward + backward-weight,
+def test_conv9_layers(ops, C, N, H, W, path):
+    """The 9x9 layers on the tensor cores (path 0: hand-built shifted-window operands, vertical-stage
+    reduce) and as exact-fp32 direct convolutions (path 1): layer 0 (C -> 32) forward + backward-weight,
     layer 22 (32 -> 3) forward + backward-data + backward-weight, against torch fp32."""
+    from styletransfer_b200 import _lib
+    _lib.lib().st_set_conv_path(path)
+    try:
+        _conv9_layers(ops, C, N, H, W)
+    finally:
+        _lib.lib().st_set_conv_path(0)
+
+
+def _conv9_layers(ops, C, N, H, W):
     # layer 0
     x = seeded((N, C, H, W), 81, device='cuda')
     w0 = seeded((32, C, 9, 9), 82, 0.06, device='cuda').requires_grad_(True)
