@@ -163,13 +163,11 @@ def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
     global_batch = seeded((FAST_B, 3, FAST_S, FAST_S), 202)
     batch = global_batch[rank * per:(rank + 1) * per].to(dev)
     last = [None]
+    # the closure static_train hands to optimizer.step: a replayed CUDA graph (default) + all-reduce
+    train_closure = net.training_closure(batch, loss_net, bucket, graph=not args.no_graph)
 
     def closure():
-        bucket.rebind()
-        bucket.zero()
-        total, _ = net.closure_loss(batch, loss_net, tv_scale=float(world))
-        total.backward()
-        bucket.all_reduce()
+        total = train_closure()
         last[0] = total.detach()
         return total
 
@@ -181,13 +179,10 @@ def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
     n0 = L.st_launch_count()
     ms = timed(step, args.steps)
     launches = L.st_launch_count() - n0
+    if hasattr(train_closure, 'launches'):
+        launches = train_closure.launches * args.steps       # kernels inside the replayed graph
     host_batch = batch.detach().cpu().pin_memory()
-    host_loss = torch.zeros(1).pin_memory()
-
-    def e2e_step():
-        batch.copy_(host_batch, non_blocking=True)
-        step()
-        host_loss.copy_(last[0].reshape(1), non_blocking=False)
+    e2e_step = HostFedStep(host_batch, batch, step, lambda: last[0])
     for _ in range(2):
         e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
@@ -289,12 +284,11 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- end to end: host image in pinned memory -> closure -> loss back on the host ----
     host_img = content.detach().cpu().pin_memory()
-    host_loss = torch.zeros(1).pin_memory()
+    e2e_last = [None]
 
-    def e2e_step():
-        with torch.no_grad():
-            x.copy_(host_img, non_blocking=True)
-        host_loss.copy_(closure().detach().reshape(1), non_blocking=False)
+    def e2e_run():
+        e2e_last[0] = closure()
+    e2e_step = HostFedStep(host_img, x, e2e_run, lambda: e2e_last[0])
     for _ in range(3):
         e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
@@ -385,6 +379,52 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+class HostFedStep:
+    """One end-to-end step with HOST buffers, pipelined the way an input pipeline feeds a training
+    loop: while the device runs step i, a copy stream uploads the input of step i+1 from pinned
+    host memory into a staging buffer; step i+1 starts with a device-to-device copy into the
+    tensor the step reads.  The loss of every step is copied to pinned host memory and the host
+    waits for it one step later (it never runs more than one step ahead of the device)."""
+
+    def __init__(self, host_in, dev_in, run, get_loss):
+        self.host_in, self.dev_in, self.run, self.get_loss = host_in, dev_in, run, get_loss
+        self.copy_stream = torch.cuda.Stream()
+        self.stage = [torch.empty_like(dev_in), torch.empty_like(dev_in)]
+        self.uploaded = [torch.cuda.Event(), torch.cuda.Event()]
+        self.consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        self.done = [torch.cuda.Event(), torch.cuda.Event()]
+        self.host_loss = [torch.zeros(1).pin_memory(), torch.zeros(1).pin_memory()]
+        self.i = 0
+        for ev in self.consumed:
+            ev.record()
+        self._upload(0)
+
+    def _upload(self, slot):
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.consumed[slot])        # the staging buffer's previous content was read
+            self.stage[slot].copy_(self.host_in, non_blocking=True)
+            self.uploaded[slot].record()
+
+    def __call__(self):
+        slot = self.i & 1
+        self._upload(slot ^ 1)                                       # input of the next step
+        cur = torch.cuda.current_stream()
+        cur.wait_event(self.uploaded[slot])
+        with torch.no_grad():
+            self.dev_in.copy_(self.stage[slot])
+        self.consumed[slot].record()
+        self.run()
+        self.host_loss[slot].copy_(self.get_loss().detach().reshape(1), non_blocking=True)
+        self.done[slot].record()
+        if self.i > 0:
+            self.done[slot ^ 1].synchronize()                        # the previous step's loss is on the host
+        self.i += 1
+
+    def loss(self):
+        torch.cuda.synchronize()
+        return float(self.host_loss[(self.i - 1) & 1])
 
 
 def ncu_dram_traffic_per_launch():

@@ -163,9 +163,10 @@ size_t st_instnorm_workspace_bytes(int N, int C);
 int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
                     void* y_hi, void* y_lo, int planes, float* mean, float* rstd,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
+/* dsum (optional, [C]): sum of dx over images and pixels = bias gradient of the convolution in front */
 int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                     const float* mean, const float* rstd, const float* gamma, const float* beta,
-                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int x_planes,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dsum, int x_planes,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 
 #ifdef __cplusplus

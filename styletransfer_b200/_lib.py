@@ -54,7 +54,7 @@ SIGNATURES = {
     'st_temporal_bwd': (_I, [_P, _P, _Z, _F, _P, _P, _P, _P]),
     'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
     'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
-    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
 }
 
 _lib = None

@@ -51,7 +51,7 @@ int ew_channel_sum(const bf16*, const bf16*, int, int, int, float*, float*, cuda
 size_t in_workspace_floats(int N, int C);
 int in_forward(const bf16*, const bf16*, const float*, const float*, float, bf16*, bf16*, int, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
 int in_backward(const bf16*, const bf16*, const bf16*, const bf16*, const float*, const float*, const float*, const float*,
-                bf16*, bf16*, float*, float*, int, int, int, int, int, int, int, float*, cudaStream_t);
+                bf16*, bf16*, float*, float*, float*, int, int, int, int, int, int, int, float*, cudaStream_t);
 int tv_forward(const float*, size_t, int, int, float, float*, float*, cudaStream_t);
 int tv_backward(const float*, size_t, int, int, float, const float*, float*, cudaStream_t);
 int temporal_forward(const float*, const float*, const float*, const float*, size_t, float, float*, float*, cudaStream_t);
@@ -281,12 +281,12 @@ int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, cons
 }
 int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                     const float* mean, const float* rstd, const float* gamma, const float* beta,
-                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, int x_planes, int N, int H, int W, int C, int relu, int up,
+                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dsum, int x_planes, int N, int H, int W, int C, int relu, int up,
                     void* workspace, void* stream) {
     ST_CHECK_ARG(x_hi && gy_hi && mean && rstd && gamma && beta && dx_hi && dgamma && dbeta && workspace, "st_instnorm_bwd: null pointer");
     ST_CHECK_ARG(in_channels_ok(C), "st_instnorm_bwd: C must be a power of two in [8,256] (got %d)", C);
     return in_backward(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), mean, rstd, gamma, beta, BF(dx_hi), BF(dx_lo),
-                       dgamma, dbeta, x_lo ? x_planes : 1, N, H, W, C, relu, up, static_cast<float*>(workspace), STRM(stream));
+                       dgamma, dbeta, dsum, x_lo ? x_planes : 1, N, H, W, C, relu, up, static_cast<float*>(workspace), STRM(stream));
 }
 
 }  // extern "C"

@@ -119,51 +119,72 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
 }
 
 // forward finalize: mean / rstd per (n,c)    (biased variance, eps inside the sqrt)
-__global__ void in_finalize_fwd_kernel(const float* __restrict__ partial, int NC, int C, int splits, int HW, float eps,
-                                       float* __restrict__ mean, float* __restrict__ rstd) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= NC) return;
-    const int n = i / C, c = i % C;
+// block = (32 channels, image n) x 8 split lanes, combined in double in a fixed order
+__global__ void __launch_bounds__(256)
+in_finalize_fwd_kernel(const float* __restrict__ partial, int C, int splits, int HW, float eps,
+                       float* __restrict__ mean, float* __restrict__ rstd) {
+    __shared__ double ss[8][33], sq[8][33];
+    const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl, n = blockIdx.y;
     double s = 0.0, q = 0.0;
-    for (int sp = 0; sp < splits; ++sp) {
-        s += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + c];
-        q += partial[(static_cast<size_t>(n) * splits + sp) * 2 * C + C + c];
+    if (c < C) {
+        const float* base = partial + (static_cast<size_t>(n) * splits) * 2 * C + c;
+        for (int sp = sl; sp < splits; sp += 8) {
+            s += base[static_cast<size_t>(sp) * 2 * C];
+            q += base[static_cast<size_t>(sp) * 2 * C + C];
+        }
     }
-    const double m = s / HW;
-    double var = q / HW - m * m; if (var < 0.0) var = 0.0;
-    mean[i] = static_cast<float>(m);
-    rstd[i] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    ss[sl][cl] = s; sq[sl][cl] = q;
+    __syncthreads();
+    if (sl == 0 && c < C) {
+        double S = 0.0, Q = 0.0;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) { S += ss[l][cl]; Q += sq[l][cl]; }
+        const double m = S / HW;
+        double var = Q / HW - m * m; if (var < 0.0) var = 0.0;
+        mean[n * C + c] = static_cast<float>(m);
+        rstd[n * C + c] = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+    }
 }
 
 // backward finalize: s1 = sum dy_eff, s2 = sum dy_eff*xhat per (n,c); dgamma/dbeta = sums over n.
-// block = 32 channels x 8 image lanes; fixed-order combination over the lanes (deterministic)
-__global__ void __launch_bounds__(256)
+// block = 32 channels x 32 lanes; a lane is (image lane, split lane); fixed-order combination (deterministic)
+__global__ void __launch_bounds__(1024)
 in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int splits,
                        float* __restrict__ s1, float* __restrict__ s2,
                        float* __restrict__ dgamma, float* __restrict__ dbeta) {
-    __shared__ float sg[8][33], sb[8][33];
-    const int cl = threadIdx.x & 31, nl = threadIdx.x >> 5;
+    __shared__ float sa[32][33], sb[32][33];
+    const int cl = threadIdx.x & 31, l = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
+    const int NL = N < 32 ? N : 32, SL = 32 / NL;            // image lanes x split lanes (<= 32)
+    const int nl = l % NL, sl = l / NL;
+    const bool lane_on = sl < SL && c < C;
     float dg = 0.f, db = 0.f;
-    if (c < C) {
-        for (int n = nl; n < N; n += 8) {
-            float a = 0.f, b = 0.f;
+    for (int n0 = 0; n0 < N; n0 += NL) {
+        const int n = n0 + nl;
+        float a = 0.f, b = 0.f;
+        if (lane_on && n < N) {
             const float* base = partial + (static_cast<size_t>(n) * splits) * 2 * C + c;
-#pragma unroll 4
-            for (int sp = 0; sp < splits; ++sp) {
+            for (int sp = sl; sp < splits; sp += SL) {
                 a += base[static_cast<size_t>(sp) * 2 * C];
                 b += base[static_cast<size_t>(sp) * 2 * C + C];
             }
-            s1[n * C + c] = a; s2[n * C + c] = b;
-            db += a; dg += b;
         }
+        sa[l][cl] = a; sb[l][cl] = b;
+        __syncthreads();
+        if (sl == 0 && c < C && n < N) {
+            float A = 0.f, B = 0.f;
+            for (int k = 0; k < SL; ++k) { A += sa[k * NL + nl][cl]; B += sb[k * NL + nl][cl]; }
+            s1[n * C + c] = A; s2[n * C + c] = B;
+            db += A; dg += B;
+        }
+        __syncthreads();
     }
-    sg[nl][cl] = dg; sb[nl][cl] = db;
+    sa[l][cl] = db; sb[l][cl] = dg;
     __syncthreads();
-    if (nl == 0 && c < C) {
+    if (l == 0 && c < C) {
         float g = 0.f, b = 0.f;
-#pragma unroll
-        for (int l = 0; l < 8; ++l) { g += sg[l][cl]; b += sb[l][cl]; }
+        for (int k = 0; k < NL; ++k) { b += sa[k][cl]; g += sb[k][cl]; }      // lanes with sl == 0 are l = nl < NL
         dgamma[c] = g; dbeta[c] = b;
     }
 }
@@ -221,13 +242,17 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ s1, const float* __restrict__ s2,
                     bf16* __restrict__ dxh, bf16* __restrict__ dxl,
-                    int HW, int W, int C, int chunk, int relu, int x_planes) {
+                    int HW, int W, int C, int chunk, int relu, int x_planes, float* __restrict__ dsum_partial) {
+    extern __shared__ float sm_ds[];                  // [lanes][C], only when dsum_partial != null
     const int n = blockIdx.y;
     const int Cv = C / 8, lanes = IN_THREADS / Cv;
     const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
-    if (pl >= lanes) return;
     const int p0 = blockIdx.x * chunk, p1 = min(HW, p0 + chunk);
     const float inv_hw = 1.0f / HW;
+    float ds[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ds[i] = 0.f;
+    if (pl < lanes) {
     float mu[8], rs[8], ga[8], be[8], a1[8], a2[8];
     load8f(mean + n * C + cv * 8, mu); load8f(rstd + n * C + cv * 8, rs);
     load8f(gamma + cv * 8, ga); load8f(beta + cv * 8, be);
@@ -253,6 +278,8 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
             x0[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
         }
         store8(dxh, dxl, (img + p) * C + cv * 8, x0);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ds[i] += x0[i];
         if (two) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -261,7 +288,42 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                 x1[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
             }
             store8(dxh, dxl, (img + p + lanes) * C + cv * 8, x1);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ds[i] += x1[i];
         }
+    }
+    }
+    // sum of dx per channel over this block's pixels (= bias gradient of the convolution in front)
+    if (dsum_partial) {
+        if (pl < lanes) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) sm_ds[pl * C + cv * 8 + i] = ds[i];
+        }
+        __syncthreads();
+        for (int c = threadIdx.x; c < C; c += IN_THREADS) {
+            float t = 0.f;
+            for (int l = 0; l < lanes; ++l) t += sm_ds[l * C + c];
+            dsum_partial[(static_cast<size_t>(n) * gridDim.x + blockIdx.x) * C + c] = t;
+        }
+    }
+}
+
+// out[c] = sum over rows of partial[row][c]; 32 channels x 32 row lanes per block
+__global__ void __launch_bounds__(1024)
+in_colsum_kernel(const float* __restrict__ partial, int rows, int C, float* __restrict__ out) {
+    __shared__ float sm[32][33];
+    const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
+    float s = 0.f;
+    if (c < C)
+        for (int r = rl; r < rows; r += 32) s += partial[static_cast<size_t>(r) * C + c];
+    sm[rl][cl] = s;
+    __syncthreads();
+    if (rl == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int l = 0; l < 32; ++l) t += sm[l][cl];
+        out[c] = t;
     }
 }
 
@@ -368,7 +430,10 @@ inline int ew_grid(size_t n, int block) {
 }  // namespace
 
 constexpr int IN_MAX_SPLITS = 128;
-size_t in_workspace_floats(int N, int C) { return static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C; }
+size_t in_workspace_floats(int N, int C) {
+    // stats partials [N][splits][2][C] + (api adds s1, s2 [N][C]) + per-block sums of dx [8 * SMs + N][C]
+    return static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C + static_cast<size_t>(8 * st_num_sms() + N) * C;
+}
 
 int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* beta, float eps,
                bf16* yh, bf16* yl, int planes, float* mean, float* rstd, int N, int H, int W, int C, int relu, int up,
@@ -379,7 +444,7 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     in_stats_kernel<0, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
         xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
-    in_finalize_fwd_kernel<<<(N * C + 127) / 128, 128, 0, st>>>(ws, N * C, C, splits, HW, eps, mean, rstd);
+    in_finalize_fwd_kernel<<<dim3((C + 31) / 32, N), 256, 0, st>>>(ws, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
     const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
     if (up) in_apply_fwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
@@ -390,7 +455,7 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
 
 int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
                 const float* mean, const float* rstd, const float* gamma, const float* beta,
-                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, int x_planes, int N, int H, int W, int C, int relu, int up,
+                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, float* dsum, int x_planes, int N, int H, int W, int C, int relu, int up,
                 float* ws, cudaStream_t st) {
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
@@ -404,12 +469,18 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
         in_stats_kernel<1, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
             xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
-    in_finalize_bwd_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
+    in_finalize_bwd_kernel<<<(C + 31) / 32, 1024, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
     const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
-    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes);
-    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes);
+    float* dpart = dsum ? s2 + static_cast<size_t>(N) * C : nullptr;        // [N * ablocks][C]
+    const size_t dsm = dsum ? static_cast<size_t>(IN_THREADS / (C / 8)) * C * sizeof(float) : 0;
+    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes, dpart);
+    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes, dpart);
     ST_CHECK_LAUNCH("in_apply_bwd_kernel");
+    if (dsum) {
+        in_colsum_kernel<<<(C + 31) / 32, 1024, 0, st>>>(dpart, N * ablocks, C, dsum);
+        ST_CHECK_LAUNCH("in_colsum_kernel");
+    }
     return ST_OK;
 }
 

@@ -210,21 +210,35 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 }
 
 // dw[co][ci][r][s] = sum over splits of partial[split][s][chunk][acc = r / 2][(r % 2) * 64 + ci % 64][co]
-__global__ void wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, int chunks, int nacc, int CDY,
-                                       int Cout, int Cin, int KH, float* __restrict__ dw) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const int total = Cout * Cin * KH * KW;
-    if (idx >= total) return;
-    int q = idx; const int s = q % KW; q /= KW; const int r = q % KH; q /= KH; const int ci = q % Cin; const int co = q / Cin;
-    const int chunk = ci / 64;
+// block = 32 output channels x 8 consecutive j = (ci, r, s): the partials are read with co fastest
+// (coalesced), the tile is transposed through shared memory and written with j fastest.
+__global__ void __launch_bounds__(256)
+wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, int chunks, int nacc, int CDY,
+                       int Cout, int Cin, int KH, float* __restrict__ dw) {
+    __shared__ float tile[8][33];
+    const int J = Cin * KH * KW;
+    const int co0 = blockIdx.y * 32, j0 = blockIdx.x * 8;
+    const int cl = threadIdx.x & 31, jl = threadIdx.x >> 5;
     const size_t per_cta = static_cast<size_t>(nacc) * 128 * CDY;
-    const size_t within = (static_cast<size_t>(r / 2) * 128 + (r % 2) * 64 + (ci % 64)) * CDY + co;
-    float acc = 0.f;
-    for (int sp = 0; sp < splits; ++sp) {
-        const size_t cta = static_cast<size_t>(s * chunks + chunk) * splits + sp;
-        acc += partial[cta * per_cta + within];
+    {
+        const int j = j0 + jl, co = co0 + cl;
+        float a0 = 0.f, a1 = 0.f;
+        if (j < J && co < Cout) {
+            int q = j; const int s = q % KW; q /= KW; const int r = q % KH; const int ci = q / KH;
+            const int chunk = ci / 64;
+            const size_t within = (static_cast<size_t>(r / 2) * 128 + (r % 2) * 64 + (ci % 64)) * CDY + co;
+            const float* base = partial + static_cast<size_t>(s * chunks + chunk) * splits * per_cta + within;
+            int sp = 0;
+            for (; sp + 1 < splits; sp += 2) { a0 += base[static_cast<size_t>(sp) * per_cta]; a1 += base[static_cast<size_t>(sp + 1) * per_cta]; }
+            if (sp < splits) a0 += base[static_cast<size_t>(sp) * per_cta];
+        }
+        tile[jl][cl] = a0 + a1;
     }
-    dw[idx] = acc;
+    __syncthreads();
+    {
+        const int co = co0 + (threadIdx.x >> 3), j = j0 + (threadIdx.x & 7);
+        if (co < Cout && j < J) dw[static_cast<size_t>(co) * J + j] = tile[threadIdx.x & 7][threadIdx.x >> 3];
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -494,8 +508,8 @@ int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, int N, int H, int W, int C
     else if (Cdy == 64) rc = launch_wgrad<3, 64>(tx, td, p, q.grid, stream);
     else rc = launch_wgrad<3, 32>(tx, td, p, q.grid, stream);
     if (rc) return rc;
-    const int total = Cout * Cin * ks * ks;
-    wgrad_tc_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dw);
+    const int J = Cin * ks * ks;
+    wgrad_tc_finish_kernel<<<dim3((J + 7) / 8, (Cout + 31) / 32), 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dw);
     ST_CHECK_LAUNCH("wgrad_tc_finish_kernel");
     return ST_OK;
 }

@@ -611,6 +611,49 @@ class ImageTransformNet(nn.Sequential):
             regularization_loss = regularization_loss * tv_scale
         return style_loss + content_loss + regularization_loss, transformed_image
 
+    def training_closure(self, batch, loss_network, bucket, style_weight=100_000, content_weight=1, graph=None):
+        """The closure ``static_train`` hands to ``optimizer.step`` (network.py:690-731) for a batch
+        held in the fixed tensor ``batch`` (the loop copies every new batch into it): zero the
+        gradient bucket -> transform net -> loss network -> backward (-> all-reduce).  With CUDA
+        graphs enabled (default) everything up to the all-reduce is captured once and replayed, so a
+        step costs one graph launch plus the collective and the optimizer instead of ~290 launches
+        from Python.  Everything the graph reads lives at fixed addresses: the batch, the fp32 master
+        weights (updated in place by the optimizer; their packed copies are rebuilt inside the graph)
+        and the flat gradient bucket."""
+        world = st_dist.world_size()
+
+        def body():
+            loss_network._content_key = None             # the content image is the batch: new targets every step
+            bucket.rebind()
+            bucket.zero()
+            total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight, tv_scale=float(world))
+            total_loss.backward()
+            return total_loss
+        if graph is None:
+            graph = cuda_graphs_enabled()
+        if not graph:
+            def eager():
+                total_loss = body()
+                bucket.all_reduce()
+                return total_loss
+            return eager
+        for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
+            node.loss = None
+        loss_network._loss_vector = None
+        self._pack_cache.always_repack = True
+        try:
+            graphed = GraphedClosure(body, leaves=[p for p in self.parameters() if p.requires_grad])
+        finally:
+            self._pack_cache.always_repack = False
+            self._pack_cache.entries.clear()             # packed copies made during capture belong to the graph
+
+        def replay():
+            total_loss = graphed()
+            bucket.all_reduce()
+            return total_loss
+        replay.launches = graphed.launches
+        return replay
+
     def static_train(self, style_name='nsp', epochs=50, style_weight=100_000, content_weight=1,
                      train_loader=None, test_loader=None, max_iterations=None):
         """network.py:651-770.  ``train_loader`` / ``test_loader`` (extra, optional) replace the
@@ -624,7 +667,8 @@ class ImageTransformNet(nn.Sequential):
         # data parallel (launched under torchrun): loader batches are GLOBAL batches, sharded
         # over the ranks; one flat-bucket all-reduce per closure (dist.py)
         world = st_dist.world_size()
-        bucket = st_dist.GradBucket(self.parameters()) if world > 1 else None
+        bucket = st_dist.GradBucket(self.parameters())   # one flat gradient buffer (also the all-reduce bucket)
+        train_buf, closure = None, None
         iteration = 0
         if train_loader is None:
             test_loader, train_loader = dataset.get_coco_loader(test_split=0.10, test_limit=20,
@@ -638,21 +682,14 @@ class ImageTransformNet(nn.Sequential):
                 continue
             for batch in tqdm(train_loader):
                 batch = batch.squeeze(1).to(constants.DEVICE)
-                if bucket is not None:
+                if world > 1:
                     batch = st_dist.shard(batch)
-
-                def closure():
-                    if bucket is None:
-                        optimizer.zero_grad()
-                    else:
-                        bucket.rebind()
-                        bucket.zero()
-                    total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight,
-                                                      tv_scale=float(world))
-                    total_loss.backward()
-                    if bucket is not None:
-                        bucket.all_reduce()
-                    return total_loss
+                # the closure (a replayed CUDA graph by default) reads the batch from a fixed buffer
+                if train_buf is None or train_buf.shape != batch.shape:
+                    train_buf = batch.detach().clone().contiguous().float()
+                    closure = self.training_closure(train_buf, loss_network, bucket, style_weight, content_weight)
+                else:
+                    train_buf.copy_(batch)
 
                 if iteration % 20 == 0:
                     total_loss = closure()

@@ -331,17 +331,21 @@ def instnorm_fwd(x, gamma, beta, relu=False, up=False, eps=1e-5):
     return y, stats
 
 
-def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False):
+def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False, want_dsum=False):
+    """Returns (dx, dgamma, dbeta[, dsum]); dsum = per-channel sum of dx = the bias gradient of the
+    convolution in front of the norm.  The saved input is read at the gradient precision."""
     L = _lib.lib()
     dev = x.buf.device
     ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
     dx = x.grad_like()
     dgamma = torch.empty_like(gamma)
     dbeta = torch.empty_like(beta)
+    dsum = torch.empty((x.C,), dtype=torch.float32, device=dev) if want_dsum else None
     _lib.check(L.st_instnorm_bwd(x.hi, x.lo, gy.hi, gy.lo, stats[0].data_ptr(), stats[1].data_ptr(),
-                                 gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(), x.planes,
-                                 x.N, x.H, x.W, x.C, int(relu), int(up), ws.data_ptr(), _stream()), 'st_instnorm_bwd')
-    return dx, dgamma, dbeta
+                                 gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(), _p(dsum),
+                                 min(x.planes, bwd_planes()), x.N, x.H, x.W, x.C, int(relu), int(up), ws.data_ptr(), _stream()),
+               'st_instnorm_bwd')
+    return (dx, dgamma, dbeta, dsum) if want_dsum else (dx, dgamma, dbeta)
 
 
 def tv_fwd(x, factor):

@@ -101,12 +101,13 @@ class _PackCache:
 
     def __init__(self):
         self.entries = {}
+        self.always_repack = False      # CUDA-graph capture: the packing kernels must be part of every replay
 
     def get(self, name, w, mode, **kw):
         key = (name, mode, ops.PRECISION)
         tag = (w.data_ptr(), w._version, tuple(w.shape))
         hit = self.entries.get(key)
-        if hit is None or hit[0] != tag:
+        if self.always_repack or hit is None or hit[0] != tag:
             hit = (tag, ops.PackedWeight(w, mode, **kw))
             self.entries[key] = hit
         return hit[1]
@@ -173,6 +174,7 @@ class TransformNetFn(torch.autograd.Function):
         gy = gy.contiguous().float()
         g = None             # built lazily: the 9x9 output layer consumes the NCHW fp32 gradient directly
         res_grad = None      # gradient flowing into the residual branch of the current block
+        pending_db = None    # sum of dy per channel from the InstanceNorm backward right after a conv
         first_conv = next(i for i, s in enumerate(PLAN) if s[0] == 'conv')
         last_conv = max(i for i, s in enumerate(PLAN) if s[0] == 'conv')
         for idx in range(len(PLAN) - 1, -1, -1):
@@ -206,8 +208,10 @@ class TransformNetFn(torch.autograd.Function):
                 w = p[name + '.weight']
                 cout, cin_w = w.shape[0], w.shape[1]
                 if need[name + '.weight'] or need[name + '.bias']:
-                    dw, db = ops.conv2d_wgrad(g, xin, k, stride, k // 2, 0, cout, cin_w)
-                    grads[name + '.weight'], grads[name + '.bias'] = dw, db
+                    # the bias gradient (sum of dy) came out of the InstanceNorm backward that produced dy
+                    dw, db = ops.conv2d_wgrad(g, xin, k, stride, k // 2, 0, cout, cin_w, want_bias=pending_db is None)
+                    grads[name + '.weight'], grads[name + '.bias'] = dw, (db if pending_db is None else pending_db[:cout])
+                pending_db = None
                 if add_res:
                     res_grad = g                    # d(out)/d(residual) = identity
                 if idx == first_conv:
@@ -229,7 +233,8 @@ class TransformNetFn(torch.autograd.Function):
             else:
                 _, name, relu, up = st
                 xin, stats = ctx.saved[idx]
-                g, dgam, dbet = ops.instnorm_bwd(xin, g, stats, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
+                g, dgam, dbet, pending_db = ops.instnorm_bwd(xin, g, stats, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up,
+                                                             want_dsum=True)
                 grads[name + '.weight'], grads[name + '.bias'] = dgam, dbet
         ctx.saved = None
         out = [grads.get('__input__'), None]

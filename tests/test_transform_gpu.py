@@ -212,3 +212,34 @@ def test_training_steps_follow_oracle_trajectory(network):
     with torch.no_grad():
         last, _ = net.closure_loss(loader[0].squeeze(1).cuda(), loss_net)
     assert record('adam6/loss_rel', abs(float(last) - ref_last) / ref_last) < 2e-2
+
+
+def test_graphed_training_closure_matches_eager(network):
+    """The CUDA-graph replay of the static_train closure (packing kernels, content targets, forward,
+    backward into the flat bucket) follows the eager closure through four Adam steps on new batches."""
+    from styletransfer_b200 import dist as st_dist
+    style = seeded((1, 3, 32, 32), 71).cuda()
+    params = oracle.make_transform_params(8, 3)
+    batches = [seeded((2, 3, 48, 32), 90 + i).cuda() for i in range(4)]
+    results = []
+    for graph in (False, True):
+        net = _build(network, network.ImageTransformNet, params, style, 2)
+        loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
+        loss_net.compute_feature_loss = False
+        opt = net.get_optimizer()
+        bucket = st_dist.GradBucket(net.parameters())
+        buf = batches[0].clone()
+        closure = net.training_closure(buf, loss_net, bucket, graph=graph)
+        assert graph == hasattr(closure, 'launches')
+        losses = []
+        for b in batches:
+            buf.copy_(b)
+            junk = [torch.full((5,), 1.0, device='cuda') for _ in range(32)]     # allocator churn between replays
+            losses.append(float(opt.step(closure)))
+            del junk
+        results.append((losses, {k: v.detach().clone() for k, v in net.state_dict().items()}))
+    (l0, p0), (l1, p1) = results
+    assert max(abs(a - b) / abs(a) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
+    assert l0[0] != l0[1]
+    worst = max(float((p0[k] - p1[k]).abs().max()) for k in p0)
+    assert record('graph_train/param_max_abs_diff', worst) < 1e-6
