@@ -350,7 +350,7 @@ class StyleNetwork(nn.Module):
         key = (content_image.data_ptr(), content_image._version, tuple(content_image.shape))
         if key != self._content_key:
             with torch.no_grad():
-                tap = self.vgg.taps(content_image.detach(), upto=4)[3]
+                tap = self.vgg.taps(content_image.detach(), upto=4, keep_all=False)[3]
             self.content_losses[0][0].set_target(tap)
             self.feature_losses[0][0].set_target(self._relu_split(tap) if self.compute_feature_loss else tap)
             self._content_key = key

@@ -44,7 +44,9 @@ class VGGPrefix:
             self.bias.append(b.detach().contiguous().float())
 
     def taps(self, x, upto=5, keep_all=True):
-        """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto."""
+        """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto.  keep_all=False:
+        only the last tap is wanted (content targets); layers whose ReLU copy feeds the next conv then
+        skip the store of their pre-ReLU tap (None in the returned list)."""
         h = None
         taps = []
         for i in range(upto):
@@ -52,10 +54,11 @@ class VGGPrefix:
             last = i + 1 == upto
             # a tap feeds either relu+maxpool (separate kernel) or a conv that wants relu(tap)
             want_relu = not last and not pool_next
+            want_out = keep_all or not want_relu
             if i == 0:
-                tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=True, want_relu=want_relu)
+                tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=want_out, want_relu=want_relu)
             else:
-                tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=True, want_relu=want_relu)
+                tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=want_out, want_relu=want_relu)
             taps.append(tap)
             if last:
                 break

@@ -62,6 +62,7 @@ def main():
 
             def closure():
                 opt.zero_grad()
+                loss_net._content_key = None          # a training step sees a new batch: new content targets
                 total, _ = tnet.closure_loss(batch, loss_net)
                 total.backward()
                 return total
