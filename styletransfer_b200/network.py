@@ -585,7 +585,25 @@ class ImageTransformNet(nn.Sequential):
         ops._require_cuda(input, type(self).__name__ + '.forward')
         sd = dict(self.named_parameters())
         params = [sd[n] for n in transform.PARAM_NAMES]
-        return transform.TransformNetFn.apply(input.contiguous().float(), self._pack_cache, *params)
+        x = input.contiguous().float()
+        if not torch.is_grad_enabled():
+            return self._infer(x, params)
+        return transform.TransformNetFn.apply(x, self._pack_cache, *params)
+
+    INFER_PIXELS_PER_CHUNK = 1 << 23      # 4 frames of 1080x1920 (32-channel tensors stay below 2^31 elements)
+
+    def _infer(self, x, params):
+        """Forward without a graph (process_image / process_video / static_test,
+        network.py:798-832, :1117-1134, :772-796): the batch goes through the fused pipeline in
+        chunks of whole frames, every intermediate is released once consumed."""
+        N, _, H, W = x.shape
+        per = max(1, self.INFER_PIXELS_PER_CHUNK // (H * W))
+        if N <= per:
+            return transform.run_forward(x, self._pack_cache, params, keep=False)[0]
+        out = torch.empty(N, 3, H, W, dtype=torch.float32, device=x.device)
+        for i in range(0, N, per):
+            out[i:i + per] = transform.run_forward(x[i:i + per], self._pack_cache, params, keep=False)[0]
+        return out
 
     def get_total_variation_regularization_loss(self, transformed_image: torch.Tensor,
                                                 regularization_factor=1e-6) -> torch.Tensor:

@@ -113,54 +113,66 @@ class _PackCache:
         return hit[1]
 
 
+def _keep(saved, keep, item):
+    saved.append(item if keep else None)
+
+
+def run_forward(x, cache, params, keep):
+    """The fused forward over PLAN.  ``keep``: retain what the backward needs (training);
+    without it every intermediate is released as soon as the next stage has consumed it
+    (inference: process_image / process_video, network.py:798-832, :1117-1134)."""
+    p = dict(zip(PARAM_NAMES, params))
+    N, cin, H, W = x.shape
+    h = None            # the first conv reads the NCHW fp32 input itself (9x9 direct kernel)
+    saved = []          # per stage: what backward needs
+    residual = None
+    out_nchw = None
+    n_conv = sum(1 for s in PLAN if s[0] == 'conv')
+    seen = 0
+    for st in PLAN:
+        if st[0] == 'mark':
+            residual = h
+            _keep(saved, keep, None)
+        elif st[0] == 'conv':
+            _, name, k, stride, add_res = st
+            seen += 1
+            w, b = p[name + '.weight'], p[name + '.bias']
+            last = seen == n_conv
+            if seen == 1 and _is_conv9_in(w):
+                # layer 0: 3|6 -> 32 channels, 9x9: exact-fp32 direct kernel on the NCHW input
+                h = ops.conv9_expand(x, w, b)
+                _keep(saved, keep, None)
+                continue
+            if h is None:
+                h = ops.from_nchw(x, cpad=ops.pad8(cin))
+            if last and _is_conv9_out(w) and h.C == 32:
+                # layer 22: 32 -> 3 channels, 9x9: direct kernel writing the NCHW fp32 output
+                out_nchw = ops.conv9_reduce(h, w, b)
+                _keep(saved, keep, h)
+                continue
+            pw = cache.get(name, w, 0, cols_pad=h.C)
+            if last:
+                _, _, out_nchw = ops.conv2d(h, pw, b, stride=stride, want_out=False, out_nchw_channels=w.shape[0])
+                _keep(saved, keep, h)
+            else:
+                y, _, _ = ops.conv2d(h, pw, b, stride=stride, add=residual if add_res else None)
+                _keep(saved, keep, h)
+                h = y
+        else:
+            _, name, relu, up = st
+            y, stats = ops.instnorm_fwd(h, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
+            _keep(saved, keep, (h, stats))
+            h = y
+    return out_nchw, saved
+
+
 class TransformNetFn(torch.autograd.Function):
     """y = net(x).  args: x NCHW fp32 [N, Cin, H, W], cache, then the 62 parameters in
     PARAM_NAMES order."""
 
     @staticmethod
     def forward(ctx, x, cache, *params):
-        p = dict(zip(PARAM_NAMES, params))
-        N, cin, H, W = x.shape
-        h = None            # the first conv reads the NCHW fp32 input itself (9x9 direct kernel)
-        saved = []          # per stage: what backward needs
-        residual = None
-        out_nchw = None
-        n_conv = sum(1 for s in PLAN if s[0] == 'conv')
-        seen = 0
-        for st in PLAN:
-            if st[0] == 'mark':
-                residual = h
-                saved.append(None)
-            elif st[0] == 'conv':
-                _, name, k, stride, add_res = st
-                seen += 1
-                w, b = p[name + '.weight'], p[name + '.bias']
-                last = seen == n_conv
-                if seen == 1 and _is_conv9_in(w):
-                    # layer 0: 3|6 -> 32 channels, 9x9: exact-fp32 direct kernel on the NCHW input
-                    h = ops.conv9_expand(x, w, b)
-                    saved.append(None)
-                    continue
-                if h is None:
-                    h = ops.from_nchw(x, cpad=ops.pad8(cin))
-                if last and _is_conv9_out(w) and h.C == 32:
-                    # layer 22: 32 -> 3 channels, 9x9: direct kernel writing the NCHW fp32 output
-                    out_nchw = ops.conv9_reduce(h, w, b)
-                    saved.append(h)
-                    continue
-                pw = cache.get(name, w, 0, cols_pad=h.C)
-                if last:
-                    _, _, out_nchw = ops.conv2d(h, pw, b, stride=stride, want_out=False, out_nchw_channels=w.shape[0])
-                    saved.append(h)
-                else:
-                    y, _, _ = ops.conv2d(h, pw, b, stride=stride, add=residual if add_res else None)
-                    saved.append(h)
-                    h = y
-            else:
-                _, name, relu, up = st
-                y, stats = ops.instnorm_fwd(h, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up)
-                saved.append((h, stats))
-                h = y
+        out_nchw, saved = run_forward(x, cache, params, keep=True)
         ctx.saved, ctx.cache, ctx.params, ctx.in_shape, ctx.x = saved, cache, params, x.shape, x
         return out_nchw
 
