@@ -159,7 +159,7 @@ def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
                                     vgg_weights=network.load_vgg19_prefix_weights(seed=1))
     loss_net.compute_feature_loss = False
     opt = net.get_optimizer()
-    bucket = st_dist.GradBucket(net.parameters())
+    bucket = getattr(opt, 'bucket', None) or st_dist.GradBucket(net.parameters())   # FusedAdam owns the flat gradient buffer
     global_batch = seeded((FAST_B, 3, FAST_S, FAST_S), 202)
     batch = global_batch[rank * per:(rank + 1) * per].to(dev)
     last = [None]
@@ -200,6 +200,155 @@ def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
         rate, n, b, cores = cpu_reference_fast_st_rate()
         out['cpu_baseline'] = {'value': rate, 'unit': 'img/s', 'cores': cores, 'kind': 'port',
                                'sample': f'{n} closures of batch {b} at 256x256 (oracle.fast_st_closure, torch fp32 CPU, no Adam step)'}
+    return out
+
+
+INFER_B, INFER_H, INFER_W = 32, 1080, 1920
+GF_INFER_PER_FRAME = 637.8
+
+
+def run_convert_image(args, dev, L, timed):
+    """Secondary metric (BASELINE configs[3]): fast_st convert-image, ImageTransformNet inference on a batch
+    of 32 synthetic 1080x1920 frames (network.py:798-832 applied to a batch), frames per second; `value` with
+    the frames resident in HBM, `e2e` host-to-host through ImageTransformNet.stylize_host_batch."""
+    from oracle import oracle
+    from styletransfer_b200 import network
+    style = seeded((1, 3, FAST_S, FAST_S), 201).to(dev)
+    net = network.ImageTransformNet(style, INFER_B).to(dev)
+    net.load_state_dict({k: v.clone() for k, v in oracle.make_transform_params(2, 3).items()})
+    host = torch.empty((INFER_B, 3, INFER_H, INFER_W), dtype=torch.float32).pin_memory()
+    four = seeded((4, 3, INFER_H, INFER_W), 301)
+    for i in range(0, INFER_B, 4):
+        host[i:i + 4] = four
+    host_out = torch.empty_like(host).pin_memory()
+    x = host.to(dev)
+    steps = max(2, min(args.steps, 4))
+
+    def step():
+        with torch.no_grad():
+            net(x)
+    for _ in range(2):
+        step()
+    n0 = L.st_launch_count()
+    ms = timed(step, steps)
+    launches = L.st_launch_count() - n0
+
+    def e2e_step():
+        net.stylize_host_batch(host, host_out)
+    e2e_step()
+    ms_e2e = timed(e2e_step, steps)
+    value = INFER_B * steps / (ms * 1e-3)
+    return {'metric': 'fast_st_convert_image_frames_per_s_1080p', 'value': value, 'unit': 'frames/s', 'ms_per_step': ms / steps,
+            'steps': steps, 'config': {'workload': 'fast_st convert-image: ImageTransformNet forward, batch 32 of 1080x1920 '
+                                                   '(BASELINE configs[3]), chunks of 4 frames', 'parallelism': 'replicas only'},
+            'tflops_algorithmic': value * GF_INFER_PER_FRAME / 1e3, 'algorithmic_gflop_per_frame': GF_INFER_PER_FRAME,
+            'e2e': {'value': INFER_B * steps / (ms_e2e * 1e-3), 'unit': 'frames/s', 'h2d_bytes_per_step': host.numel() * 4,
+                    'd2h_bytes_per_step': host_out.numel() * 4, 'ms_per_step': ms_e2e / steps},
+            'gpu_launches': int(launches)}
+
+
+VIDEO_B, VIDEO_S, VIDEO_FRAMES = 8, 512, 8
+GF_VIDEO_PER_FRAME = 434.0       # SURVEY.md section 8d (video_st training at 512x512, 6-channel input)
+
+
+def run_video_st(args, rank, world, dev, L, timed):
+    """Secondary metric (BASELINE configs[4]): video_st training frames/s on 8-frame synthetic 512x512 clips,
+    global batch of 8 clips sharded over the ranks; one step = the video_train closure on one frame batch
+    (network.py:984-1037: recurrent 6-channel input, style + content + TV + temporal loss, backward) +
+    all-reduce + Adam.  The reference's temporal loss has no optical flow."""
+    from oracle import oracle
+    from styletransfer_b200 import network
+    per = VIDEO_B // world
+    style = seeded((1, 3, FAST_S, FAST_S), 201).to(dev)
+    net = network.VideoTransformNet(style, per).to(dev)
+    net.load_state_dict({k: v.clone() for k, v in oracle.make_transform_params(2, 6).items()})
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, FAST_S, FAST_S]).to(dev),
+                                    vgg_weights=network.load_vgg19_prefix_weights(seed=1))
+    loss_net.compute_feature_loss = False
+    opt = net.get_optimizer()
+    from styletransfer_b200 import dist as st_dist
+    bucket = getattr(opt, 'bucket', None) or st_dist.GradBucket(net.parameters())
+    frames = [seeded((VIDEO_B, 3, VIDEO_S, VIDEO_S), 400)]
+    for t in range(1, VIDEO_FRAMES):
+        frames.append(frames[-1] + 0.05 * seeded((VIDEO_B, 3, VIDEO_S, VIDEO_S), 400 + t))
+    host_frames = [f[rank * per:(rank + 1) * per].contiguous().pin_memory() for f in frames]
+    dev_frames = [f.to(dev) for f in host_frames]
+    frame_buf = torch.empty_like(dev_frames[0])
+    state = {'t': 0, 'old': None, 'last': None, 'resident': True}
+
+    def step():
+        t = state['t'] % VIDEO_FRAMES
+        if state['resident']:
+            frame_buf.copy_(dev_frames[t])
+        batch = frame_buf.clone()                      # the closure keeps the frame as next step's old content
+        if t == 0:
+            state['old'] = [batch, batch]
+        frozen = [state['old'][0], state['old'][1]]
+
+        def closure():
+            bucket.rebind()
+            bucket.zero()
+            st = [frozen[0], frozen[1]]
+            total, _ = net.closure_loss_video(batch, st, loss_net, 0.8, tv_scale=float(world))
+            state['old'] = st
+            total.backward()
+            bucket.all_reduce()
+            state['last'] = total.detach()
+            return total
+        opt.step(closure)
+        state['t'] += 1
+    for _ in range(max(args.warmup, 3)):
+        step()
+    state['t'] = 0
+    n0 = L.st_launch_count()
+    ms = timed(step, args.steps)
+    launches = L.st_launch_count() - n0
+    state['t'], state['resident'] = 0, False
+    e2e_step = HostFedStep(host_frames, frame_buf, step, lambda: state['last'])
+    for _ in range(2):
+        e2e_step()
+    state['t'] = 2
+    ms_e2e = timed(e2e_step, args.steps)
+    value = VIDEO_B * args.steps / (ms * 1e-3)
+    return {'metric': 'video_st_train_frames_per_s_512', 'value': value, 'unit': 'frames/s', 'ms_per_step': ms / args.steps,
+            'scaling': 'strong', 'global_batch_clips': VIDEO_B, 'per_gpu_clips': per,
+            'config': {'workload': 'video_st train: 8-frame synthetic 512x512 clips, global batch 8 clips, one frame batch per step, '
+                                   'closure + all-reduce + Adam (BASELINE configs[4]; temporal loss without flow warp as in the reference)',
+                       'parallelism': f'dp{world}', 'launch': 'eager'},
+            'tflops_algorithmic': value * GF_VIDEO_PER_FRAME / 1e3, 'algorithmic_gflop_per_frame': GF_VIDEO_PER_FRAME,
+            'e2e': {'value': VIDEO_B * args.steps / (ms_e2e * 1e-3), 'unit': 'frames/s',
+                    'h2d_bytes_per_step': host_frames[0].numel() * 4 * world, 'd2h_bytes_per_step': 4 * world,
+                    'ms_per_step': ms_e2e / args.steps},
+            'gpu_launches': int(launches), 'loss_after': float(state['last'])}
+
+
+def run_lbfgs_loop(net, content, dev, L):
+    """The loop train_gatys runs (network.py:435-456): optimizer.step(closure) with L-BFGS at torch's defaults
+    (20 closures per step, history 100), closures per second with a FULL history, for the device-resident
+    optimizer (optim.DeviceLBFGS, the default) and for torch.optim.LBFGS driving the same graph closure."""
+    from styletransfer_b200 import optim as st_optim
+    out = {}
+    for name, make in (('device_lbfgs', st_optim.DeviceLBFGS), ('torch_lbfgs', torch.optim.LBFGS)):
+        x = content.clone().requires_grad_(True)
+        evaluate = net.gatys_closure(x, content, STYLE_WEIGHT, CONTENT_WEIGHT)
+        opt = make([x])
+        n0 = L.st_launch_count()
+        for _ in range(6):                             # 120 iterations: the history ring is full
+            opt.step(evaluate)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        steps = 3
+        for _ in range(steps):
+            opt.step(evaluate)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        out[name] = {'closures_per_s': 20 * steps / (ms * 1e-3), 'ms_per_iteration': ms / (20 * steps),
+                     'loss': float(evaluate())}
+        del opt, evaluate, x
+        torch.cuda.empty_cache()
+    out['config'] = 'train_gatys loop at 512x512: 3 optimizer.step calls = 60 closures + 60 L-BFGS iterations, history 100 full'
     return out
 
 
@@ -308,22 +457,29 @@ def run_ours(args, rank, world, local_rank):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         # keep the GPU busy while the host queues the launch, so that the events bracket the kernel
         # alone and not the host's launch latency
-        torch.cuda._sleep(150000)
+        torch.cuda._sleep(300000)
         e0.record()
         out = real_conv2d(xs, w, *a, **k)
         e1.record()
         records.append((ks, cin, cout, 2.0 * xs.N * xs.H * xs.W * cin * cout * ks * ks, e0, e1))
         return out
+    for _ in range(2):
+        eager_closure()          # untimed: the eager path's buffers come out of cudaMalloc on first use
     ops.conv2d = traced_conv2d
     torch.cuda.synchronize()
     for _ in range(args.steps):
         eager_closure()
     torch.cuda.synchronize()
     ops.conv2d = real_conv2d
+    # the launches of one closure come in a fixed order: launch i of every step is the same kernel on the
+    # same shapes; its duration is the MEDIAN over the steps (a bracket that caught a host stall is dropped)
+    per_step = len(records) // max(args.steps, 1)
     groups = {}
-    for ks, cin, cout, fl, e0, e1 in records:
+    for i in range(per_step):
+        ks, cin, cout, fl = records[i][:4]
+        t = statistics.median(r[4].elapsed_time(r[5]) for r in records[i::per_step])
         g = groups.setdefault(f'conv_tc_kernel<{ks}x{ks}> {cin}->{cout}', [0.0, 0.0, 0])
-        g[0] += fl; g[1] += e0.elapsed_time(e1); g[2] += 1
+        g[0] += fl * args.steps; g[1] += t * args.steps; g[2] += args.steps
     pk = peaks()
     fl3 = sum(g[0] for k, g in groups.items() if '<3x3>' in k)
     ms3 = sum(g[1] for k, g in groups.items() if '<3x3>' in k)
@@ -340,12 +496,21 @@ def run_ours(args, rank, world, local_rank):
     per_kernel = {k: {'tflops': g[0] / (g[1] * 1e-3) / 1e12, 'ms_per_launch': g[1] / g[2], 'launches_per_step': g[2] / args.steps}
                   for k, g in sorted(groups.items())}
 
+    lbfgs = None
+    if world == 1 and not args.no_secondary:
+        lbfgs = run_lbfgs_loop(net, content, dev, L)
     # free the Gatys working set, then the secondary fast_st training metric (all ranks take part)
     del net, closure, eager_closure
     torch.cuda.empty_cache()
-    fast = None
+    fast = video = convert = None
     if not args.no_fast_st:
         fast = run_fast_st(args, rank, world, dev, L, timed, with_cpu=(rank == 0 and world == 1 and not args.no_cpu_baseline))
+    if not args.no_secondary:
+        torch.cuda.empty_cache()
+        video = run_video_st(args, rank, world, dev, L, timed)
+        if world == 1:
+            torch.cuda.empty_cache()
+            convert = run_convert_image(args, dev, L, timed)
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -370,6 +535,12 @@ def run_ours(args, rank, world, local_rank):
             'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roofline, 'kernels': per_kernel}
     if fast is not None:
         line['fast_st'] = fast
+    if video is not None:
+        line['video_st'] = video
+    if convert is not None:
+        line['convert_image'] = convert
+    if lbfgs is not None:
+        line['gatys_lbfgs_loop'] = lbfgs
     if world == 1 and not args.no_cpu_baseline:
         rate, n, cores = cpu_reference_closure_rate(budget_s=20.0, max_steps=8, warmup=1)
         line['cpu_baseline'] = {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port',
@@ -397,14 +568,19 @@ class HostFedStep:
         self.done = [torch.cuda.Event(), torch.cuda.Event()]
         self.host_loss = [torch.zeros(1).pin_memory(), torch.zeros(1).pin_memory()]
         self.i = 0
+        self.n_uploaded = 0
         for ev in self.consumed:
             ev.record()
         self._upload(0)
 
     def _upload(self, slot):
+        src = self.host_in
+        if isinstance(src, (list, tuple)):                           # a sequence of host inputs, one per step, cycled
+            src = src[self.n_uploaded % len(src)]
+        self.n_uploaded += 1
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self.consumed[slot])        # the staging buffer's previous content was read
-            self.stage[slot].copy_(self.host_in, non_blocking=True)
+            self.stage[slot].copy_(src, non_blocking=True)
             self.uploaded[slot].record()
 
     def __call__(self):
@@ -452,6 +628,7 @@ def main():
     ap.add_argument('--precision', default='bf16x6', choices=['bf16x6', 'bf16x3', 'bf16'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='launch the closure eagerly instead of replaying a CUDA graph')
+    ap.add_argument('--no-secondary', action='store_true', help='skip the video_st / convert-image / L-BFGS loop metrics')
     ap.add_argument('--no-fast-st', action='store_true', help='skip the secondary fast_st training metric')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))

@@ -169,6 +169,31 @@ int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const
                     void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dsum, int x_planes,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 
+/* ---- optimizer steps on the device ---------- */
+/* torch.optim.Adam.step over every parameter tensor of a transform net in one launch
+ * (network.py:643-649, :765).  param / grad / exp_avg / exp_avg_sq are flat fp32 arrays of
+ * sum(seg_numel) elements, one segment per parameter tensor in order; `steps` / `active` are
+ * device int[nseg] (torch's per-parameter step count; active = the tensor has a gradient).
+ * `chunks` is a device copy of the table st_adam_fill_chunks() writes on the host
+ * (st_adam_chunk_count() entries of 16 bytes).  grad_scale multiplies the gradient first
+ * (1/world of the data-parallel average). */
+size_t st_adam_chunk_count(const long long* seg_numel, int nseg);
+int st_adam_fill_chunks(const long long* seg_numel, int nseg, void* host_chunks);
+int st_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, const void* chunks,
+                 size_t nchunks, int* steps, const int* active, int nseg, double lr, double beta1, double beta2,
+                 double eps, double weight_decay, double grad_scale, void* stream);
+/* One iteration of torch.optim.LBFGS (no line search; network.py:435, :456) on the flat fp32
+ * vector x [n] given the gradient and the loss of the closure at x (device pointers): history
+ * update, two-loop recursion in coefficient space, x += t*d, torch's stopping rules on a device
+ * flag (first_of_step = 1 for the first iteration of an optimizer.step call: clears the flag).
+ * g_prev, dir: [n] scratch owned by the caller; S, Y: history rings [history][ld], ld >= n,
+ * ld % 4 == 0; state: st_lbfgs_state_bytes() bytes, set up by st_lbfgs_init().  The first 32
+ * doubles of state are readable diagnostics (k, head, n_iter, t, H_diag, ...; see optim.cu). */
+size_t st_lbfgs_state_bytes(int history, size_t n);
+int st_lbfgs_init(void* state, int history, size_t n, double lr, double tolerance_grad, double tolerance_change, void* stream);
+int st_lbfgs_iteration(float* x, const float* grad, const float* loss, float* g_prev, float* dir, float* S, float* Y,
+                       size_t n, size_t ld, int history, void* state, int first_of_step, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,12 +6,12 @@ in-tree shared object.
 """
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_size_t, c_void_p
+from ctypes import c_char_p, c_double, c_float, c_int, c_size_t, c_void_p
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libstransfer_b200.so')
 
-_P, _I, _F, _Z = c_void_p, c_int, c_float, c_size_t
+_P, _I, _F, _Z, _D = c_void_p, c_int, c_float, c_size_t, c_double
 
 # name -> (restype, argtypes); mirrors include/stransfer_b200.h one to one
 SIGNATURES = {
@@ -54,6 +54,12 @@ SIGNATURES = {
     'st_temporal_bwd': (_I, [_P, _P, _Z, _F, _P, _P, _P, _P]),
     'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
     'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_adam_chunk_count': (_Z, [_P, _I]),
+    'st_adam_fill_chunks': (_I, [_P, _I, _P]),
+    'st_adam_step': (_I, [_P, _P, _P, _P, _P, _Z, _P, _P, _I, _D, _D, _D, _D, _D, _D, _P]),
+    'st_lbfgs_state_bytes': (_Z, [_I, _Z]),
+    'st_lbfgs_init': (_I, [_P, _I, _Z, _D, _D, _D, _P]),
+    'st_lbfgs_iteration': (_I, [_P, _P, _P, _P, _P, _P, _P, _Z, _Z, _I, _P, _I, _P]),
     'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
 }
 

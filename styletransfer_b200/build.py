@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, 'csrc')
 INCLUDE = os.path.join(os.path.dirname(HERE), 'include')
 LIB = os.path.join(HERE, 'libstransfer_b200.so')
 STAMP = os.path.join(HERE, '.build_stamp')
-SOURCES = ['api.cu', 'conv_tc.cu', 'conv_tcx.cu', 'conv_generic.cu', 'conv_image.cu', 'conv9.cu', 'conv9_tc.cu', 'contract.cu', 'wgrad_tc.cu', 'elementwise.cu', 'norm_losses.cu']
+SOURCES = ['api.cu', 'conv_tc.cu', 'conv_tcx.cu', 'conv_generic.cu', 'conv_image.cu', 'conv9.cu', 'conv9_tc.cu', 'contract.cu', 'wgrad_tc.cu', 'elementwise.cu', 'norm_losses.cu', 'optim.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '--use_fast_math', '-Xcompiler', '-fPIC', '-Xptxas', '-v', '-shared', '-cudart', 'shared']
 

@@ -14,7 +14,7 @@ import torch.nn as nn
 import torch.optim as optim
 from tqdm import tqdm
 
-from . import c_logging, constants, dist as st_dist, ops, transform, vgg_loss
+from . import c_logging, constants, dist as st_dist, ops, optim as st_optim, transform, vgg_loss
 from ._lib import StransferError
 
 LOGGER = c_logging.get_logger()
@@ -402,7 +402,11 @@ class StyleNetwork(nn.Module):
         return GraphedClosure(body, leaves=[input_image])
 
     def get_content_optimizer(self, input_img, optt=optim.Adam):
-        """network.py:403-409"""
+        """network.py:403-409.  ``optim.LBFGS`` (what train_gatys asks for) is served by the
+        device-resident ``optim.DeviceLBFGS`` -- same defaults and stopping rules, three launches
+        per iteration and no host round trip; ``STRANSFER_DEVICE_LBFGS=0`` keeps torch's own."""
+        if optt is optim.LBFGS and input_img.is_cuda and os.environ.get('STRANSFER_DEVICE_LBFGS', '1') != '0':
+            return st_optim.DeviceLBFGS([input_img.requires_grad_()])
         return optt([input_img.requires_grad_()])
 
     def train_gatys(self, style_image: torch.Tensor, content_image: torch.Tensor,
@@ -605,6 +609,57 @@ class ImageTransformNet(nn.Sequential):
             out[i:i + per] = transform.run_forward(x[i:i + per], self._pack_cache, params, keep=False)[0]
         return out
 
+    def stylize_host_batch(self, frames: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
+        """Streaming inference for convert-image / convert-video style workloads (network.py:798-832;
+        SURVEY section 8f rank 3): ``frames`` [N, C, H, W] fp32 in (pinned) HOST memory -> stylised frames in
+        (pinned) host memory.  Chunks of whole frames are double-buffered: a copy stream uploads chunk
+        i+1 while the kernels run chunk i and a second copy stream downloads the result of chunk i-1."""
+        if frames.device.type != 'cpu' or frames.dtype != torch.float32 or frames.dim() != 4:
+            raise StransferError('stylize_host_batch: an fp32 [N, C, H, W] host tensor is required')
+        dev = next(self.parameters()).device
+        if dev.type != 'cuda':
+            raise StransferError('stylize_host_batch: the network is not on a CUDA device (no CPU fallback)')
+        N, C, H, W = frames.shape
+        per = min(N, max(1, self.INFER_PIXELS_PER_CHUNK // (H * W)))
+        if out is None:
+            out = torch.empty((N, 3, H, W), dtype=torch.float32).pin_memory()
+        sd = dict(self.named_parameters())
+        params = [sd[n] for n in transform.PARAM_NAMES]
+        cur = torch.cuda.current_stream(dev)
+        up, down = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        stage_in = [torch.empty((per, C, H, W), dtype=torch.float32, device=dev) for _ in range(2)]
+        stage_out = [torch.empty((per, 3, H, W), dtype=torch.float32, device=dev) for _ in range(2)]
+        uploaded, consumed, produced, drained = ([torch.cuda.Event() for _ in range(2)] for _ in range(4))
+        for ev in consumed + drained:
+            ev.record(cur)
+        starts = list(range(0, N, per))
+
+        def upload(ci):
+            slot, i = ci & 1, starts[ci]
+            n = min(per, N - i)
+            with torch.cuda.stream(up):
+                up.wait_event(consumed[slot])
+                stage_in[slot][:n].copy_(frames[i:i + n], non_blocking=True)
+                uploaded[slot].record(up)
+        upload(0)
+        with torch.no_grad():
+            for ci, i in enumerate(starts):
+                slot, n = ci & 1, min(per, N - i)
+                if ci + 1 < len(starts):
+                    upload(ci + 1)
+                cur.wait_event(uploaded[slot])
+                cur.wait_event(drained[slot])
+                stage_out[slot][:n].copy_(transform.run_forward(stage_in[slot][:n], self._pack_cache, params, keep=False)[0])
+                consumed[slot].record(cur)
+                produced[slot].record(cur)
+                with torch.cuda.stream(down):
+                    down.wait_event(produced[slot])
+                    out[i:i + n].copy_(stage_out[slot][:n], non_blocking=True)
+                    drained[slot].record(down)
+        cur.wait_stream(down)
+        cur.wait_stream(up)
+        return out
+
     def get_total_variation_regularization_loss(self, transformed_image: torch.Tensor,
                                                 regularization_factor=1e-6) -> torch.Tensor:
         """network.py:621-641"""
@@ -612,8 +667,13 @@ class ImageTransformNet(nn.Sequential):
         return _TVFn.apply(transformed_image.contiguous().float(), float(regularization_factor))
 
     def get_optimizer(self, optimizer=optim.Adam):
-        """network.py:643-649"""
-        return optimizer(self.parameters())
+        """network.py:643-649.  ``optim.Adam`` is served by ``optim.FusedAdam`` (same update rule,
+        one launch over the flat parameter / gradient / moment buffers; its ``.bucket`` is the flat
+        gradient buffer the training closures write); ``STRANSFER_FUSED_ADAM=0`` keeps torch's own."""
+        params = list(self.parameters())
+        if optimizer is optim.Adam and params[0].is_cuda and os.environ.get('STRANSFER_FUSED_ADAM', '1') != '0':
+            return st_optim.FusedAdam(params)
+        return optimizer(params)
 
     # -- the closure body of static_train (network.py:690-731), factored out so that the
     #    benchmark and the parity tests run exactly what the training loop runs
@@ -685,7 +745,8 @@ class ImageTransformNet(nn.Sequential):
         # data parallel (launched under torchrun): loader batches are GLOBAL batches, sharded
         # over the ranks; one flat-bucket all-reduce per closure (dist.py)
         world = st_dist.world_size()
-        bucket = st_dist.GradBucket(self.parameters())   # one flat gradient buffer (also the all-reduce bucket)
+        # one flat gradient buffer (also the all-reduce bucket); FusedAdam reads it in place
+        bucket = getattr(optimizer, 'bucket', None) or st_dist.GradBucket(self.parameters())
         train_buf, closure = None, None
         iteration = 0
         if train_loader is None:
@@ -817,7 +878,7 @@ class VideoTransformNet(ImageTransformNet):
         # data parallel over CLIPS (frames of a clip are sequentially dependent);
         # the temporal loss uses the norms of the rank's own clips (per-shard norms)
         world = st_dist.world_size()
-        bucket = st_dist.GradBucket(self.parameters()) if world > 1 else None
+        bucket = getattr(optimizer, 'bucket', None) or (st_dist.GradBucket(self.parameters()) if world > 1 else None)
         iteration = 0
         if video_loader is None:
             video_loader = dataset.VideoDataset(batch_size=self.batch_size)

@@ -218,3 +218,41 @@ def test_cli_surface_matches_reference():
     assert defaults['out_name'] == 'gatys_converted.png'
     vt = cli.commands['video_st'].commands['train']
     assert {p.name: p.default for p in vt.params}['temporal_weight'] == 0.8
+
+
+@pytest.mark.parametrize('hist', [5, 100])
+def test_lbfgs_model_follows_torch_lbfgs(hist):
+    """oracle/lbfgs_model.py (the CPU restatement of csrc/optim.cu's coefficient-space L-BFGS) against
+    torch.optim.LBFGS, the optimizer the reference runs (network.py:435): 20 iterations of one step,
+    history 5 wraps the ring 15 times."""
+    from oracle.lbfgs_model import LBFGSModel
+    n = 300
+    gen = torch.Generator().manual_seed(0)
+    A = torch.randn(n, n, generator=gen) / n ** 0.5
+    b = torch.randn(n, generator=gen)
+    x0 = torch.randn(n, generator=gen)
+
+    def f(x):
+        r = A @ x - b
+        return torch.sqrt(1 + r * r).sum() + 0.05 * (x ** 4).sum()
+    xt = x0.clone().requires_grad_(True)
+    opt = torch.optim.LBFGS([xt], history_size=hist)
+
+    def closure():
+        opt.zero_grad()
+        loss = f(xt)
+        loss.backward()
+        return loss
+    mod = LBFGSModel(x0.clone().numpy(), history_size=hist)
+
+    def model_closure():
+        x = torch.from_numpy(mod.x).clone().requires_grad_(True)
+        loss = f(x)
+        loss.backward()
+        return float(loss.detach()), x.grad.numpy().copy()
+    opt.step(closure)
+    mod.step(model_closure)
+    err = float((xt.detach() - torch.from_numpy(mod.x)).norm() / xt.detach().norm())
+    assert opt.state[xt]['n_iter'] == mod.n_iter == 20
+    assert mod.k == min(hist, 19)
+    assert err < 1e-4, err

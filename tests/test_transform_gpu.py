@@ -227,7 +227,7 @@ def test_graphed_training_closure_matches_eager(network):
         loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
         loss_net.compute_feature_loss = False
         opt = net.get_optimizer()
-        bucket = st_dist.GradBucket(net.parameters())
+        bucket = getattr(opt, 'bucket', None) or st_dist.GradBucket(net.parameters())
         buf = batches[0].clone()
         closure = net.training_closure(buf, loss_net, bucket, graph=graph)
         assert graph == hasattr(closure, 'launches')
@@ -243,3 +243,48 @@ def test_graphed_training_closure_matches_eager(network):
     assert l0[0] != l0[1]
     worst = max(float((p0[k] - p1[k]).abs().max()) for k in p0)
     assert record('graph_train/param_max_abs_diff', worst) < 1e-6
+
+
+@pytest.mark.parametrize('shape', [(1, 3, 136, 200), (2, 3, 60, 92)])
+def test_inference_ragged_shapes_match_oracle(network, shape):
+    """process_image / convert-image (network.py:798-832; BASELINE configs[3] is 1080x1920, i.e. 270x480
+    at the residual blocks: not a multiple of the 8x16 pixel tile): the graph-free inference path on
+    sizes that leave ragged tiles at every resolution, against the CPU oracle and the training-mode forward."""
+    params = oracle.make_transform_params(8, 3)
+    x = seeded(shape, 140)
+    ref = oracle.transform_net(x, params)
+    net = _build(network, network.ImageTransformNet, params, seeded((1, 3, 32, 32), 71).cuda(), shape[0])
+    with torch.no_grad():
+        out = net(x.cuda())
+    assert out.shape == ref.shape
+    assert record(f'infer/{shape[2]}x{shape[3]}/rel_l2', rel_l2(out, ref)) < 1e-3
+    out_train = net(x.cuda())
+    assert out_train.requires_grad and torch.equal(out_train.detach(), out)
+
+
+def test_inference_chunks_whole_frames(network):
+    """A batch beyond INFER_PIXELS_PER_CHUNK goes through in chunks of whole frames (InstanceNorm is per
+    sample): bit-identical to the unchunked forward, 6-channel video net included (network.py:1117-1134)."""
+    params = oracle.make_transform_params(8, 6)
+    net = _build(network, network.VideoTransformNet, params, seeded((1, 3, 32, 32), 71).cuda(), 5)
+    x = seeded((5, 6, 32, 48), 141).cuda()
+    with torch.no_grad():
+        whole = net(x)
+        net.INFER_PIXELS_PER_CHUNK = 2 * 32 * 48
+        chunked = net(x)
+    assert torch.equal(whole, chunked)
+    assert rel_l2(whole, oracle.transform_net(x.cpu(), params)) < 1e-3
+
+
+def test_stylize_host_batch_streams_chunks(network):
+    """Host-to-host streaming inference (double-buffered upload / compute / download) returns exactly what
+    the resident forward returns, ragged last chunk included."""
+    params = oracle.make_transform_params(8, 3)
+    net = _build(network, network.ImageTransformNet, params, seeded((1, 3, 32, 32), 71).cuda(), 5)
+    x = seeded((5, 3, 40, 56), 142).pin_memory()
+    with torch.no_grad():
+        want = net(x.cuda()).cpu()
+    net.INFER_PIXELS_PER_CHUNK = 2 * 40 * 56
+    got = net.stylize_host_batch(x)
+    torch.cuda.synchronize()
+    assert got.is_pinned() and torch.equal(got, want)

@@ -60,12 +60,9 @@ def main():
             loss_net.compute_feature_loss = False
             opt = tnet.get_optimizer()
 
-            def closure():
-                opt.zero_grad()
-                loss_net._content_key = None          # a training step sees a new batch: new content targets
-                total, _ = tnet.closure_loss(batch, loss_net)
-                total.backward()
-                return total
+            from styletransfer_b200 import dist as st_dist
+            bucket = getattr(opt, 'bucket', None) or st_dist.GradBucket(tnet.parameters())
+            closure = tnet.training_closure(batch, loss_net, bucket, graph=False)    # eager: every launch visible to ncu
 
             def step():
                 opt.step(closure)
