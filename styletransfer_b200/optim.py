@@ -109,7 +109,8 @@ class DeviceLBFGS(torch.optim.Optimizer):
     contiguous fp32 CUDA tensor (the Gatys image, network.py:403-409).  ``step(closure)`` runs
     ``max_iter`` rounds of closure -> st_lbfgs_iteration; torch's early exits (gradient /
     step / loss-change tolerances, non-descent direction) set a flag on the device that turns the
-    remaining rounds of the call into no-ops, so nothing is read back.  The closure must write
+    remaining rounds of the call into no-ops; the host reads the flag RUN_AHEAD rounds late (off the
+    critical path: the device queue stays that deep) and leaves the loop then.  The closure must write
     ``param.grad`` (any storage; its address is read after every call) and return the loss as a
     device scalar."""
 
@@ -139,6 +140,12 @@ class DeviceLBFGS(torch.optim.Optimizer):
         self.dir = torch.zeros(self.n, dtype=torch.float32, device=dev)
         _lib.check(self.L.st_lbfgs_init(self.state_buf.data_ptr(), self.m, self.n, float(lr), float(tolerance_grad),
                                         float(tolerance_change), _stream()), 'st_lbfgs_init')
+        # the halt flag of iteration j is copied to pinned memory; the host looks at it RUN_AHEAD iterations
+        # later (the device queue stays that deep), so a stopped step costs at most RUN_AHEAD spare closures
+        self._flag = [torch.zeros(1, dtype=torch.float64).pin_memory() for _ in range(self.RUN_AHEAD + 1)]
+        self._flag_ev = [torch.cuda.Event() for _ in range(self.RUN_AHEAD + 1)]
+
+    RUN_AHEAD = 2
 
     FIELDS = ('k', 'head', 'n_iter', 't', 'H_diag', 'd_dot_g', 'g_dot_g', 'halt', 'skip', 'loss_prev', 'pushed', 'new',
               'cg', 't_old', 'run_b', 'lr', 'tol_grad', 'tol_change', 'm', 'gtd', 'gmax', 'dmax', 'loss')
@@ -152,7 +159,12 @@ class DeviceLBFGS(torch.optim.Optimizer):
     def step(self, closure):
         g = self.param_groups[0]
         first_loss = None
+        ring = self.RUN_AHEAD + 1
         for it in range(int(g['max_iter'])):
+            if it >= self.RUN_AHEAD:
+                self._flag_ev[(it - self.RUN_AHEAD) % ring].synchronize()
+                if float(self._flag[(it - self.RUN_AHEAD) % ring]) != 0.0:
+                    break                      # torch left its loop here; the remaining rounds would be no-ops
             with torch.enable_grad():
                 loss = closure()
             if first_loss is None:
@@ -166,4 +178,6 @@ class DeviceLBFGS(torch.optim.Optimizer):
                                                  self.Y.data_ptr(), self.n, self.ld, self.m, self.state_buf.data_ptr(),
                                                  1 if it == 0 else 0, _stream()), 'st_lbfgs_iteration')
             _bump_versions([self.p])
+            self._flag[it % ring].copy_(self.state_buf[7:8], non_blocking=True)        # H_HALT
+            self._flag_ev[it % ring].record()
         return first_loss

@@ -22,9 +22,10 @@ def seeded(shape, seed):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--workload', default='gatys', choices=['gatys', 'fast_st', 'infer'])
+    ap.add_argument('--workload', default='gatys', choices=['gatys', 'fast_st', 'infer', 'lbfgs'])
     ap.add_argument('--size', type=int, default=0)
     ap.add_argument('--batch', type=int, default=0)
+    ap.add_argument('--width', type=int, default=0, help='infer: frame width (height = --size)')
     ap.add_argument('--warmup', type=int, default=2)
     ap.add_argument('--steps', type=int, default=1)
     ap.add_argument('--precision', default='bf16x6')
@@ -34,7 +35,21 @@ def main():
     ops.set_precision(args.precision)
     dev = torch.device('cuda', 0)
     vw = network.load_vgg19_prefix_weights(seed=1)
-    if args.workload == 'gatys':
+    if args.workload == 'lbfgs':
+        # one optimizer.step of the train_gatys loop (20 closures + 20 device L-BFGS iterations), history full
+        S = args.size or 512
+        content = seeded((1, 3, S, S), 100).to(dev)
+        style = torch.nn.functional.interpolate(seeded((1, 3, S // 16, S // 16), 111) * 2.0, scale_factor=16, mode='nearest').to(dev)
+        net = network.StyleNetwork(style, content, vgg_weights=vw)
+        net.compute_feature_loss = False
+        x = content.clone().requires_grad_(True)
+        evaluate = net.gatys_closure(x, content, graph=False)
+        opt = net.get_content_optimizer(x, optt=torch.optim.LBFGS)
+        args.warmup = max(args.warmup, 6)
+
+        def step():
+            opt.step(evaluate)
+    elif args.workload == 'gatys':
         S = args.size or 512
         content, style = seeded((1, 3, S, S), 100).to(dev), seeded((1, 3, S, S), 101).to(dev)
         net = network.StyleNetwork(style, content, vgg_weights=vw)
@@ -50,7 +65,7 @@ def main():
         style = seeded((1, 3, 256, 256), 201).to(dev)
         tnet = network.ImageTransformNet(style, B).to(dev)
         tnet.load_state_dict({k: v.clone() for k, v in oracle.make_transform_params(2, 3).items()})
-        batch = seeded((B, 3, S, S), 202).to(dev)
+        batch = seeded((B, 3, S, args.width or S), 202).to(dev)
         if args.workload == 'infer':
             def step():
                 with torch.no_grad():
