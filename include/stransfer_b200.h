@@ -190,6 +190,8 @@ int st_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg
  * ld % 4 == 0; state: st_lbfgs_state_bytes() bytes, set up by st_lbfgs_init().  The first 32
  * doubles of state are readable diagnostics (k, head, n_iter, t, H_diag, ...; see optim.cu). */
 size_t st_lbfgs_state_bytes(int history, size_t n);
+/* tuning hook: 0 (default) = dots pass with 3 CTAs per SM, 1 = 2 CTAs per SM with software-pipelined loads; returns the old value */
+int st_set_lbfgs_variant(int variant);
 int st_lbfgs_init(void* state, int history, size_t n, double lr, double tolerance_grad, double tolerance_change, void* stream);
 int st_lbfgs_iteration(float* x, const float* grad, const float* loss, float* g_prev, float* dir, float* S, float* Y,
                        size_t n, size_t ld, int history, void* state, int first_of_step, void* stream);

@@ -58,6 +58,7 @@ SIGNATURES = {
     'st_adam_fill_chunks': (_I, [_P, _I, _P]),
     'st_adam_step': (_I, [_P, _P, _P, _P, _P, _Z, _P, _P, _I, _D, _D, _D, _D, _D, _D, _P]),
     'st_lbfgs_state_bytes': (_Z, [_I, _Z]),
+    'st_set_lbfgs_variant': (_I, [_I]),
     'st_lbfgs_init': (_I, [_P, _I, _Z, _D, _D, _D, _P]),
     'st_lbfgs_iteration': (_I, [_P, _P, _P, _P, _P, _P, _P, _Z, _Z, _I, _P, _I, _P]),
     'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),

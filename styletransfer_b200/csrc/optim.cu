@@ -116,11 +116,21 @@ struct LbfgsState {                      // offsets in doubles
     __host__ __device__ size_t YY() const { return SY() + (size_t)m * m; }
     __host__ __device__ size_t partials() const { return YY() + (size_t)m * m; }
 };
-static inline size_t lb_blocks(size_t n) { return (n + LB_EPB - 1) / LB_EPB; }
+static inline size_t lb_chunks(size_t n) { return (n + LB_EPB - 1) / LB_EPB; }
+// chunks per CTA so that the dots pass runs at most 3 CTAs per SM (all resident at 80 registers), evenly loaded
+static int g_lbfgs_variant = 0;          // 0: 3 CTAs per SM, loads issued per slot pair; 1: 2 CTAs per SM, loads software-pipelined
+extern "C" int st_set_lbfgs_variant(int v) { const int old = g_lbfgs_variant; g_lbfgs_variant = v ? 1 : 0; return old; }
+static inline size_t lb_cpb(size_t n) { const size_t lim = 3 * (size_t)st_num_sms(); return (lb_chunks(n) + lim - 1) / lim; }
+static inline size_t lb_blocks(size_t n) { const size_t c = lb_cpb(n); return (lb_chunks(n) + c - 1) / c; }
 
 __device__ __forceinline__ double shfl_xor_d(double v, int o) {
     int lo = __double2loint(v), hi = __double2hiint(v);
     lo = __shfl_xor_sync(0xffffffffu, lo, o); hi = __shfl_xor_sync(0xffffffffu, hi, o);
+    return __hiloint2double(hi, lo);
+}
+__device__ __forceinline__ double shfl_idx_d(double v, int src) {
+    int lo = __double2loint(v), hi = __double2hiint(v);
+    lo = __shfl_sync(0xffffffffu, lo, src); hi = __shfl_sync(0xffffffffu, hi, src);
     return __hiloint2double(hi, lo);
 }
 // sums of 4 values over the warp with 6 fp64 shuffles; lanes 0/8/16/24 end up holding slots 0/1/2/3
@@ -156,44 +166,72 @@ __device__ __forceinline__ double dot4d(const double (&g)[4], float4 v) {
     return g[0] * (double)v.x + g[1] * (double)v.y + g[2] * (double)v.z + g[3] * (double)v.w;
 }
 
-// ---- pass A: partial dots of the gradient with the history, the previous gradient and the direction
-__global__ void __launch_bounds__(256) lbfgs_dots_kernel(const float* __restrict__ g, const float* __restrict__ gp,
+// ---- pass A: partial dots of the gradient with the history, the previous gradient and the direction.
+// Each CTA walks `chunks_per_block` chunks of LB_EPB elements and keeps its per-warp sums in shared memory,
+// so the solve kernel has gridDim.x (<= 3 x SMs) rows to add up.
+template <bool PIPE>
+__global__ void __launch_bounds__(256, PIPE ? 2 : 3) lbfgs_dots_kernel(const float* __restrict__ g, const float* __restrict__ gp,
                                                          const float* __restrict__ d, const float* __restrict__ S,
                                                          const float* __restrict__ Y, size_t n, size_t ld, int m,
-                                                         const double* __restrict__ st, int first, double* __restrict__ partials) {
+                                                         const double* __restrict__ st, int first, int chunks_per_block,
+                                                         double* __restrict__ partials) {
     if (!first && st[H_HALT] != 0.0) return;
     const int k = (int)st[H_K];
     const int SL = LB_SL(m);
     __shared__ double red[8][LB_SL(LB_MAX_M)];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    const size_t e0 = (size_t)blockIdx.x * LB_EPB + (size_t)tid * 4, e1 = e0 + 1024;
-    const float4 ga = ld4g(g, e0, n), gb = ld4g(g, e1, n);
-    const double g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
-    for (int j = 0; j < k; j += 2) {
-        const int j1 = j + 1 < k ? j + 1 : j;
-        const float* s0 = S + (size_t)j * ld; const float* s1 = S + (size_t)j1 * ld;
-        const float* y0 = Y + (size_t)j * ld; const float* y1 = Y + (size_t)j1 * ld;
-        const float4 a0 = ld4g(s0, e0, n), a1 = ld4g(s0, e1, n), b0 = ld4g(s1, e0, n), b1 = ld4g(s1, e1, n);
-        const float4 c0 = ld4g(y0, e0, n), c1 = ld4g(y0, e1, n), d0 = ld4g(y1, e0, n), d1 = ld4g(y1, e1, n);
-        const double a[4] = {dot4d(g0, a0) + dot4d(g1, a1), dot4d(g0, b0) + dot4d(g1, b1),
-                             dot4d(g0, c0) + dot4d(g1, c1), dot4d(g0, d0) + dot4d(g1, d1)};
-        const double r = warp_sum4(a, lane);
-        if ((lane & 7) == 0) {
-            const int q = lane >> 3;                       // 0: s_j  1: s_j1  2: y_j  3: y_j1
-            if (!(q & 1) || j + 1 < k) red[w][(q >> 1) * m + j + (q & 1)] = r;
+    for (int c = 0; c < chunks_per_block; ++c) {
+        const size_t e0 = ((size_t)blockIdx.x * chunks_per_block + c) * LB_EPB + (size_t)tid * 4, e1 = e0 + 1024;
+        const bool more = c > 0;
+        const float4 ga = ld4g(g, e0, n), gb = ld4g(g, e1, n);
+        const double g0[4] = {ga.x, ga.y, ga.z, ga.w}, g1[4] = {gb.x, gb.y, gb.z, gb.w};
+        // software pipeline: the 8 loads of the next slot pair are in flight while this pair is reduced
+        float4 nx[8];
+        auto fetch = [&](int j) {
+            const int j1 = j + 1 < k ? j + 1 : j;
+            const float* s0 = S + (size_t)j * ld; const float* s1 = S + (size_t)j1 * ld;
+            const float* y0 = Y + (size_t)j * ld; const float* y1 = Y + (size_t)j1 * ld;
+            nx[0] = ld4g(s0, e0, n); nx[1] = ld4g(s0, e1, n); nx[2] = ld4g(s1, e0, n); nx[3] = ld4g(s1, e1, n);
+            nx[4] = ld4g(y0, e0, n); nx[5] = ld4g(y0, e1, n); nx[6] = ld4g(y1, e0, n); nx[7] = ld4g(y1, e1, n);
+        };
+        if (PIPE && k > 0) fetch(0);
+        for (int j = 0; j < k; j += 2) {
+            double a[4];
+            if constexpr (PIPE) {
+                float4 cu[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) cu[i] = nx[i];
+                if (j + 2 < k) fetch(j + 2);
+                a[0] = dot4d(g0, cu[0]) + dot4d(g1, cu[1]); a[1] = dot4d(g0, cu[2]) + dot4d(g1, cu[3]);
+                a[2] = dot4d(g0, cu[4]) + dot4d(g1, cu[5]); a[3] = dot4d(g0, cu[6]) + dot4d(g1, cu[7]);
+            } else {
+                const int j1 = j + 1 < k ? j + 1 : j;
+                const float* s0 = S + (size_t)j * ld; const float* s1 = S + (size_t)j1 * ld;
+                const float* y0 = Y + (size_t)j * ld; const float* y1 = Y + (size_t)j1 * ld;
+                const float4 a0 = ld4g(s0, e0, n), a1 = ld4g(s0, e1, n), b0 = ld4g(s1, e0, n), b1 = ld4g(s1, e1, n);
+                const float4 c0 = ld4g(y0, e0, n), c1 = ld4g(y0, e1, n), d0 = ld4g(y1, e0, n), d1 = ld4g(y1, e1, n);
+                a[0] = dot4d(g0, a0) + dot4d(g1, a1); a[1] = dot4d(g0, b0) + dot4d(g1, b1);
+                a[2] = dot4d(g0, c0) + dot4d(g1, c1); a[3] = dot4d(g0, d0) + dot4d(g1, d1);
+            }
+            const double r = warp_sum4(a, lane);
+            if ((lane & 7) == 0) {
+                const int q = lane >> 3;                       // 0: s_j  1: s_j1  2: y_j  3: y_j1
+                if (!(q & 1) || j + 1 < k) {
+                    double* dst = &red[w][(q >> 1) * m + j + (q & 1)];
+                    *dst = more ? *dst + r : r;
+                }
+            }
         }
-    }
-    {
         const float4 p0 = ld4g(gp, e0, n), p1 = ld4g(gp, e1, n), q0 = ld4g(d, e0, n), q1 = ld4g(d, e1, n);
         double sabs = 0.0; float mx = 0.f;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { sabs += fabs(g0[i]) + fabs(g1[i]); mx = fmaxf(mx, fmaxf(fabsf((float)g0[i]), fabsf((float)g1[i]))); }
         const double a[4] = {dot4d(g0, ga) + dot4d(g1, gb), dot4d(g0, p0) + dot4d(g1, p1), dot4d(g0, q0) + dot4d(g1, q1), sabs};
         const double r = warp_sum4(a, lane);
-        if ((lane & 7) == 0) red[w][2 * m + (lane >> 3)] = r;
+        if ((lane & 7) == 0) { double* dst = &red[w][2 * m + (lane >> 3)]; *dst = more ? *dst + r : r; }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        if (lane == 0) red[w][2 * m + 4] = (double)mx;
+        if (lane == 0) { double* dst = &red[w][2 * m + 4]; *dst = more ? fmax(*dst, (double)mx) : (double)mx; }
     }
     __syncthreads();
     for (int s = tid; s < SL; s += 256) {
@@ -215,8 +253,9 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
     const int tid = threadIdx.x, lane = tid & 31;
     const int SL = LB_SL(m);
     if (!first && st[H_HALT] != 0.0) { if (tid == 0) st[H_RUNB] = 0.0; return; }
-    double* SY = sm; double* YY = SY + m * m;
-    double* dots = YY + m * m;                 // SL
+    const int LDM = m | 1;                     // odd row stride (in doubles): column walks of SY stay off a single bank
+    double* SY = sm; double* YY = SY + m * LDM;
+    double* dots = YY + m * LDM;               // SL
     double* grp = dots + SL;                   // 4 * SL
     double* qy = grp + 4 * SL; double* rs = qy + m; double* al = rs + m; double* ro = al + m;
     double* cy = ro + m; double* cs = cy + m; double* sgp = cs + m; double* ygp = sgp + m;
@@ -232,10 +271,12 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
             double acc = 0.0;
             const size_t per = (nblocks + 3) / 4, b0 = grpi * per, b1 = b0 + per < nblocks ? b0 + per : nblocks;
             size_t b = b0;
-            for (; b + 4 <= b1; b += 4) {
-                const double v0 = partials[b * SL + s], v1 = partials[(b + 1) * SL + s], v2 = partials[(b + 2) * SL + s],
-                             v3 = partials[(b + 3) * SL + s];
-                if (is_max) acc = fmax(fmax(acc, fmax(v0, v1)), fmax(v2, v3)); else acc += (v0 + v1) + (v2 + v3);
+            for (; b + 8 <= b1; b += 8) {
+                double v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = partials[(b + u) * SL + s];
+                if (is_max) acc = fmax(acc, fmax(fmax(fmax(v[0], v[1]), fmax(v[2], v[3])), fmax(fmax(v[4], v[5]), fmax(v[6], v[7]))));
+                else acc += ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
             }
             for (; b < b1; ++b) { const double v = partials[b * SL + s]; if (is_max) acc = fmax(acc, v); else acc += v; }
             grp[grpi * SL + s] = acc;
@@ -244,8 +285,8 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
     // phase 2: history matrices and vectors into shared memory
     for (int idx = tid; idx < k * k; idx += 1024) {
         const int i = idx / k, j = idx - i * k;
-        SY[i * m + j] = st[L.SY() + (size_t)i * m + j];
-        YY[i * m + j] = st[L.YY() + (size_t)i * m + j];
+        SY[i * LDM + j] = st[L.SY() + (size_t)i * m + j];
+        YY[i * LDM + j] = st[L.YY() + (size_t)i * m + j];
     }
     if (tid < m) {
         ro[tid] = st[L.ro() + tid]; cy[tid] = st[L.cy() + tid]; cs[tid] = st[L.cs() + tid];
@@ -298,21 +339,21 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
         if (tid < k) {
             const int j = tid;
             double acc = cg_old * ygp[j];
-            for (int i = 0; i < k; ++i) acc += cy[i] * YY[i * m + j] + cs[i] * SY[i * m + j];
+            for (int i = 0; i < k; ++i) acc += cy[i] * YY[i * LDM + j] + cs[i] * SY[i * LDM + j];
             row_sy[j] = t_old * acc;
         }
         __syncthreads();
         if (tid < k && tid != nw) {
             const int j = tid;
             const double r = row_sy[j], c = sg[j] - sgp[j], y = yg[j] - ygp[j];
-            SY[nw * m + j] = r; SY[j * m + nw] = c; YY[nw * m + j] = y; YY[j * m + nw] = y;
+            SY[nw * LDM + j] = r; SY[j * LDM + nw] = c; YY[nw * LDM + j] = y; YY[j * LDM + nw] = y;
             st[L.SY() + (size_t)nw * m + j] = r; st[L.SY() + (size_t)j * m + nw] = c;
             st[L.YY() + (size_t)nw * m + j] = y; st[L.YY() + (size_t)j * m + nw] = y;
         }
         __syncthreads();
         if (tid == 0) {
             const double ys = sc[1], yy = sc[2];
-            SY[nw * m + nw] = ys; YY[nw * m + nw] = yy;
+            SY[nw * LDM + nw] = ys; YY[nw * LDM + nw] = yy;
             st[L.SY() + (size_t)nw * m + nw] = ys; st[L.YY() + (size_t)nw * m + nw] = yy;
             ro[nw] = 1.0 / ys; st[L.ro() + nw] = 1.0 / ys;
             sg[nw] = t_old * dg; yg[nw] = gg - ggp;
@@ -328,29 +369,51 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
         if (tid == 0) st[H_HDIAG] = 1.0;
     } else {
         const double qg = -1.0;
+        // Two-loop recursion without reductions: u[j] = s_j.q and w[j] = y_j.q are kept for ALL j and updated by
+        // one axpy per step (q -= al_i*y_i  =>  u[j] -= al_i*SY[j][i], w[j] -= al_i*YY[j][i]); the second loop
+        // keeps v[j] = y_j.r the same way (r += c*s_i  =>  v[j] += c*SY[i][j]).  One warp, k/32 entries per lane.
+        static_assert(LB_MAX_M <= 128, "four register entries per lane");
         if (tid < 32) {
-            for (int idx = kn - 1; idx >= 0; --idx) {
-                const int i = (headn + idx) % m;
-                double p = 0.0;
-                for (int j = lane; j < kn; j += 32) p += qy[j] * SY[i * m + j];
-                p = warp_sum_d(p);
-                const double a = ro[i] * (qg * sg[i] + p);
-                if (lane == 0) { al[i] = a; qy[i] -= a; }
-                __syncwarp();
+            // entries j = lane + 32*t of u / w / v live in registers; the pivot entry is fetched with one shuffle
+            double u[4], w[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int j = lane + 32 * t;
+                u[t] = j < kn ? qg * sg[j] : 0.0; w[t] = j < kn ? qg * yg[j] : 0.0;
             }
+            int i = (headn + kn - 1) % m;
+            for (int idx = kn - 1; idx >= 0; --idx) {
+                const int t = i >> 5;
+                const double ui = shfl_idx_d(t == 0 ? u[0] : t == 1 ? u[1] : t == 2 ? u[2] : u[3], i & 31);
+                const double a = ro[i] * ui;
+#pragma unroll
+                for (int t2 = 0; t2 < 4; ++t2) {
+                    const int j = lane + 32 * t2;
+                    if (j < kn) { u[t2] -= a * SY[j * LDM + i]; w[t2] -= a * YY[i * LDM + j]; }
+                }
+                if (lane == 0) qy[i] = -a;
+                i = i == 0 ? m - 1 : i - 1;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int t = 0; t < 4; ++t) w[t] *= H;                       // v[j] = y_j . (H q)
+            i = headn;
             for (int idx = 0; idx < kn; ++idx) {
-                const int i = (headn + idx) % m;
-                double p = 0.0;
-                for (int j = lane; j < kn; j += 32) p += H * qy[j] * YY[i * m + j] + rs[j] * SY[j * m + i];
-                p = warp_sum_d(p);
-                const double be = ro[i] * (H * qg * yg[i] + p);
-                if (lane == 0) rs[i] += al[i] - be;
-                __syncwarp();
+                const int t = i >> 5;
+                const double vi = shfl_idx_d(t == 0 ? w[0] : t == 1 ? w[1] : t == 2 ? w[2] : w[3], i & 31);
+                const double c = -qy[i] - ro[i] * vi;
+#pragma unroll
+                for (int t2 = 0; t2 < 4; ++t2) {
+                    const int j = lane + 32 * t2;
+                    if (j < kn) w[t2] += c * SY[i * LDM + j];
+                }
+                if (lane == 0) cs[i] = c;
+                i = i + 1 == m ? 0 : i + 1;
             }
         }
         __syncthreads();
         cg = H * qg;
-        if (tid < m) { cy[tid] = H * qy[tid]; cs[tid] = rs[tid]; }
+        if (tid < m) { cy[tid] = H * qy[tid]; if (tid >= kn) cs[tid] = 0.0; }
     }
     __syncthreads();
     if (tid < m) {
@@ -374,7 +437,7 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
 }
 
 // ---- pass B: new pair into the ring, direction, x += t*d, g_prev = g
-__global__ void __launch_bounds__(256) lbfgs_update_kernel(float* __restrict__ x, const float* __restrict__ g, float* __restrict__ gp,
+__global__ void __launch_bounds__(256, 3) lbfgs_update_kernel(float* __restrict__ x, const float* __restrict__ g, float* __restrict__ gp,
                                                            float* __restrict__ d, float* __restrict__ S, float* __restrict__ Y,
                                                            size_t n, size_t ld, int m, double* __restrict__ st) {
     if (st[H_RUNB] == 0.0) return;
@@ -398,12 +461,17 @@ __global__ void __launch_bounds__(256) lbfgs_update_kernel(float* __restrict__ x
             acc[0] += a * (double)v.x; acc[1] += a * (double)v.y; acc[2] += a * (double)v.z; acc[3] += a * (double)v.w;
         };
         int j = 0;
-        for (; j + 2 <= k; j += 2) {
-            float4 y0 = (j == nw) ? yn : ld4g(Y + (size_t)j * ld, e, n), s0 = (j == nw) ? sn : ld4g(S + (size_t)j * ld, e, n);
-            float4 y1 = (j + 1 == nw) ? yn : ld4g(Y + (size_t)(j + 1) * ld, e, n), s1 = (j + 1 == nw) ? sn : ld4g(S + (size_t)(j + 1) * ld, e, n);
-            add(cy[j], y0); add(cs[j], s0); add(cy[j + 1], y1); add(cs[j + 1], s1);
+        for (; j + 4 <= k; j += 4) {                   // 8 independent 16-byte loads in flight per thread
+            float4 yv[4], sv[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                yv[u] = (j + u == nw) ? yn : ld4g(Y + (size_t)(j + u) * ld, e, n);
+                sv[u] = (j + u == nw) ? sn : ld4g(S + (size_t)(j + u) * ld, e, n);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { add(cy[j + u], yv[u]); add(cs[j + u], sv[u]); }
         }
-        if (j < k) {
+        for (; j < k; ++j) {
             float4 y0 = (j == nw) ? yn : ld4g(Y + (size_t)j * ld, e, n), s0 = (j == nw) ? sn : ld4g(S + (size_t)j * ld, e, n);
             add(cy[j], y0); add(cs[j], s0);
         }
@@ -439,7 +507,7 @@ __global__ void lbfgs_init_kernel(double* st, int m, double lr, double tolg, dou
 }
 
 static size_t lb_solve_smem(int m) {
-    return sizeof(double) * ((size_t)2 * m * m + 5 * (size_t)LB_SL(m) + 9 * (size_t)m + 16);
+    return sizeof(double) * ((size_t)2 * m * (m | 1) + 5 * (size_t)LB_SL(m) + 9 * (size_t)m + 16);
 }
 
 extern "C" size_t st_lbfgs_state_bytes(int history, size_t n) {
@@ -477,7 +545,12 @@ extern "C" int st_lbfgs_iteration(float* x, const float* grad, const float* loss
         }
         attr = true;
     }
-    lbfgs_dots_kernel<<<(unsigned)nb, 256, 0, s>>>(grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, st + L.partials());
+    if (g_lbfgs_variant)
+        lbfgs_dots_kernel<true><<<(unsigned)nb, 256, 0, s>>>(grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
+                                                             st + L.partials());
+    else
+        lbfgs_dots_kernel<false><<<(unsigned)nb, 256, 0, s>>>(grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
+                                                              st + L.partials());
     ST_CHECK_LAUNCH("lbfgs_dots_kernel");
     lbfgs_solve_kernel<<<1, 1024, lb_solve_smem(history), s>>>(st, history, nb, loss, first_of_step);
     ST_CHECK_LAUNCH("lbfgs_solve_kernel");

@@ -43,7 +43,7 @@ def main():
         net = network.StyleNetwork(style, content, vgg_weights=vw)
         net.compute_feature_loss = False
         x = content.clone().requires_grad_(True)
-        evaluate = net.gatys_closure(x, content, graph=False)
+        evaluate = net.gatys_closure(x, content, style_weight=1e10, content_weight=1e5, graph=False)    # see bench.LBFGS_LOSS_SCALE
         opt = net.get_content_optimizer(x, optt=torch.optim.LBFGS)
         args.warmup = max(args.warmup, 6)
 
