@@ -23,6 +23,7 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+_REAL_STDOUT = sys.stdout
 SIZE = 512
 STYLE_WEIGHT, CONTENT_WEIGHT = 100_000.0, 1.0
 # algorithmic work of one closure at SxS, batch 1
@@ -401,7 +402,7 @@ def run_reference(args, rank, world):
             'cpu_baseline': {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': rate, 'unit': 'it/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
-    print(json.dumps(line))
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -585,7 +586,7 @@ def run_ours(args, rank, world, local_rank):
         line['cpu_baseline'] = {'value': rate, 'unit': 'it/s', 'cores': cores, 'kind': 'port',
                                 'sample': f'{n} closures at 512x512 of the as-executed reference closure '
                                           f'(oracle.gatys_closure_as_executed, torch fp32 CPU)'}
-    print(json.dumps(line))
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -673,6 +674,12 @@ def main():
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
     local_rank = int(os.environ.get('LOCAL_RANK', 0))
+    # stdout carries exactly ONE JSON line: whatever libraries print there (NCCL's version banner under
+    # NCCL_DEBUG=VERSION, ...) goes to stderr; print() below writes to the saved descriptor
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
     if args.impl == 'reference':
         run_reference(args, rank, world)
     else:

@@ -155,6 +155,15 @@ int st_temporal_fwd(const float* old_content, const float* old_stylized, const f
                     const float* cur_stylized, size_t numel, float tw, float* out3, float* ws, void* stream);
 int st_temporal_bwd(const float* old_stylized, const float* cur_stylized, size_t numel, float tw,
                     const float* stats3, const float* gw, float* g, void* stream);
+/* EXTENSION without reference code (the reference's temporal loss has no optical flow; BASELINE.json
+ * words the loss as flow-warped): the previous content / stylised frames are warped by flow [N][2][H][W] (dx, dy in
+ * pixels; bilinear, zeros outside = torch grid_sample(align_corners=True) in pixel units) on the fly:
+ * loss = tw * ||cs - warp(os)|| / (||cc - warp(oc)|| + 1); out3 / stats3 / ws as st_temporal_fwd. */
+int st_temporal_warp_fwd(const float* old_content, const float* old_stylized, const float* cur_content,
+                         const float* cur_stylized, const float* flow, int N, int C, int H, int W, float tw,
+                         float* out3, float* ws, void* stream);
+int st_temporal_warp_bwd(const float* old_stylized, const float* cur_stylized, const float* flow, int N, int C, int H, int W,
+                         float tw, const float* stats3, const float* gw, float* g, void* stream);
 
 /* ---- InstanceNorm2d(affine) (network.py:474, :483, :531-600) ------------- */
 size_t st_instnorm_workspace_bytes(int N, int C);

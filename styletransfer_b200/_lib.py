@@ -52,6 +52,8 @@ SIGNATURES = {
     'st_tv_bwd': (_I, [_P, _I, _I, _I, _I, _F, _P, _P, _P]),
     'st_temporal_fwd': (_I, [_P, _P, _P, _P, _Z, _F, _P, _P, _P]),
     'st_temporal_bwd': (_I, [_P, _P, _Z, _F, _P, _P, _P, _P]),
+    'st_temporal_warp_fwd': (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _P, _P, _P]),
+    'st_temporal_warp_bwd': (_I, [_P, _P, _P, _I, _I, _I, _I, _F, _P, _P, _P, _P]),
     'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
     'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     'st_adam_chunk_count': (_Z, [_P, _I]),

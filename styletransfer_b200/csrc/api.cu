@@ -56,6 +56,8 @@ int tv_forward(const float*, size_t, int, int, float, float*, float*, cudaStream
 int tv_backward(const float*, size_t, int, int, float, const float*, float*, cudaStream_t);
 int temporal_forward(const float*, const float*, const float*, const float*, size_t, float, float*, float*, cudaStream_t);
 int temporal_backward(const float*, const float*, size_t, float, const float*, const float*, float*, cudaStream_t);
+int temporal_warp_forward(const float*, const float*, const float*, const float*, const float*, int, int, int, int, float, float*, float*, cudaStream_t);
+int temporal_warp_backward(const float*, const float*, const float*, int, int, int, int, float, const float*, const float*, float*, cudaStream_t);
 
 #define BF(p) static_cast<bf16*>(p)
 #define CBF(p) static_cast<const bf16*>(p)
@@ -263,6 +265,16 @@ int st_temporal_fwd(const float* oc, const float* os, const float* cc, const flo
                     float* out3, float* ws, void* stream) {
     ST_CHECK_ARG(oc && os && cc && cs && out3 && ws && numel > 0, "st_temporal_fwd: null pointer or empty shape");
     return temporal_forward(oc, os, cc, cs, numel, tw, out3, ws, STRM(stream));
+}
+int st_temporal_warp_fwd(const float* oc, const float* os, const float* cc, const float* cs, const float* flow, int N, int C, int H,
+                         int W, float tw, float* out3, float* ws, void* stream) {
+    ST_CHECK_ARG(oc && os && cc && cs && flow && out3 && ws && N > 0 && C > 0 && H > 0 && W > 0, "st_temporal_warp_fwd: null pointer or empty shape");
+    return temporal_warp_forward(oc, os, cc, cs, flow, N, C, H, W, tw, out3, ws, STRM(stream));
+}
+int st_temporal_warp_bwd(const float* os, const float* cs, const float* flow, int N, int C, int H, int W, float tw,
+                         const float* stats3, const float* gw, float* g, void* stream) {
+    ST_CHECK_ARG(os && cs && flow && stats3 && gw && g && N > 0 && C > 0 && H > 0 && W > 0, "st_temporal_warp_bwd: null pointer or empty shape");
+    return temporal_warp_backward(os, cs, flow, N, C, H, W, tw, stats3, gw, g, STRM(stream));
 }
 int st_temporal_bwd(const float* os, const float* cs, size_t numel, float tw, const float* stats3, const float* gw, float* g, void* stream) {
     ST_CHECK_ARG(os && cs && stats3 && gw && g && numel > 0, "st_temporal_bwd: null pointer or empty shape");

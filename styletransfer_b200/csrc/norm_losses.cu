@@ -407,6 +407,71 @@ __global__ void temporal_bwd_kernel(const float* __restrict__ os, const float* _
         g[i] = coef * (cs[i] - os[i]);
 }
 
+// ---------------------------------------------------------------------------
+// EXTENSION (no reference code: the reference's temporal loss has no optical flow; BASELINE.json
+// words it as "temporal (optical-flow-warped) loss").  The previous frame is warped by a dense flow field before
+// the comparison:  tw * ||cs - warp(os)|| / (||cc - warp(oc)|| + 1),  warp(img)(x, y) = bilinear(img, x + dx, y + dy)
+// with zeros outside the frame (torch grid_sample, bilinear, padding_mode='zeros', align_corners=True in pixel units).
+// flow: [N][2][H][W] fp32 (dx, dy) in pixels.  The warped frames are never materialised: both kernels gather on the fly.
+// ---------------------------------------------------------------------------
+struct WarpTaps { int i00, i01, i10, i11; float w00, w01, w10, w11; };
+__device__ __forceinline__ WarpTaps warp_taps(float fx, float fy, int H, int W) {
+    WarpTaps t;
+    const float x0f = floorf(fx), y0f = floorf(fy);
+    const int x0 = (int)x0f, y0 = (int)y0f, x1 = x0 + 1, y1 = y0 + 1;
+    const float ax = fx - x0f, ay = fy - y0f;
+    const bool vx0 = x0 >= 0 && x0 < W, vx1 = x1 >= 0 && x1 < W, vy0 = y0 >= 0 && y0 < H, vy1 = y1 >= 0 && y1 < H;
+    t.w00 = (vx0 && vy0) ? (1.f - ax) * (1.f - ay) : 0.f; t.w01 = (vx1 && vy0) ? ax * (1.f - ay) : 0.f;
+    t.w10 = (vx0 && vy1) ? (1.f - ax) * ay : 0.f;         t.w11 = (vx1 && vy1) ? ax * ay : 0.f;
+    const int cx0 = min(max(x0, 0), W - 1), cx1 = min(max(x1, 0), W - 1), cy0 = min(max(y0, 0), H - 1), cy1 = min(max(y1, 0), H - 1);
+    t.i00 = cy0 * W + cx0; t.i01 = cy0 * W + cx1; t.i10 = cy1 * W + cx0; t.i11 = cy1 * W + cx1;
+    return t;
+}
+__device__ __forceinline__ float warp_gather(const float* __restrict__ plane, const WarpTaps& t) {
+    return t.w00 * plane[t.i00] + t.w01 * plane[t.i01] + t.w10 * plane[t.i10] + t.w11 * plane[t.i11];
+}
+__global__ void temporal_warp_partial_kernel(const float* __restrict__ oc, const float* __restrict__ os,
+                                             const float* __restrict__ cc, const float* __restrict__ cs,
+                                             const float* __restrict__ flow, int N, int C, int H, int W,
+                                             float* __restrict__ partial /* [grid][2] */) {
+    __shared__ float sm[32];
+    const size_t HW = (size_t)H * W, pixels = (size_t)N * HW;
+    float a = 0.f, b = 0.f;
+    for (size_t p = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; p < pixels;
+         p += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int n = (int)(p / HW); const size_t r = p - (size_t)n * HW;
+        const int y = (int)(r / W), x = (int)(r - (size_t)y * W);
+        const float* f = flow + (size_t)n * 2 * HW;
+        const WarpTaps t = warp_taps((float)x + f[r], (float)y + f[HW + r], H, W);
+        for (int c = 0; c < C; ++c) {
+            const size_t base = ((size_t)n * C + c) * HW;
+            const float ds = cs[base + r] - warp_gather(os + base, t), dc = cc[base + r] - warp_gather(oc + base, t);
+            a += ds * ds; b += dc * dc;
+        }
+    }
+    a = block_sum(a, sm);
+    b = block_sum(b, sm);
+    if (threadIdx.x == 0) { partial[blockIdx.x * 2] = a; partial[blockIdx.x * 2 + 1] = b; }
+}
+__global__ void temporal_warp_bwd_kernel(const float* __restrict__ os, const float* __restrict__ cs, const float* __restrict__ flow,
+                                         int N, int C, int H, int W, float tw, const float* __restrict__ stats,
+                                         const float* __restrict__ gw, float* __restrict__ g) {
+    const float ns = stats[1], nc = stats[2];
+    const float coef = ns > 0.f ? gw[0] * tw / ((nc + 1.f) * ns) : 0.f;
+    const size_t HW = (size_t)H * W, pixels = (size_t)N * HW;
+    for (size_t p = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; p < pixels;
+         p += static_cast<size_t>(gridDim.x) * blockDim.x) {
+        const int n = (int)(p / HW); const size_t r = p - (size_t)n * HW;
+        const int y = (int)(r / W), x = (int)(r - (size_t)y * W);
+        const float* f = flow + (size_t)n * 2 * HW;
+        const WarpTaps t = warp_taps((float)x + f[r], (float)y + f[HW + r], H, W);
+        for (int c = 0; c < C; ++c) {
+            const size_t base = ((size_t)n * C + c) * HW;
+            g[base + r] = coef * (cs[base + r] - warp_gather(os + base, t));
+        }
+    }
+}
+
 inline int in_splits(int N, int HW) {
     int splits = (4 * st_num_sms()) / N;              // N * splits = two full waves at 2 CTAs per SM
     const int maxs = (HW + 255) / 256;
@@ -504,6 +569,21 @@ int temporal_forward(const float* oc, const float* os, const float* cc, const fl
     ST_CHECK_LAUNCH("temporal_partial_kernel");
     temporal_finish_kernel<<<1, 256, 0, st>>>(ws, grid, tw, out3);
     ST_CHECK_LAUNCH("temporal_finish_kernel");
+    return ST_OK;
+}
+int temporal_warp_forward(const float* oc, const float* os, const float* cc, const float* cs, const float* flow, int N, int C,
+                          int H, int W, float tw, float* out3, float* ws, cudaStream_t st) {
+    int grid = ew_grid((size_t)N * H * W, 256); if (grid > 1024) grid = 1024;
+    temporal_warp_partial_kernel<<<grid, 256, 0, st>>>(oc, os, cc, cs, flow, N, C, H, W, ws);
+    ST_CHECK_LAUNCH("temporal_warp_partial_kernel");
+    temporal_finish_kernel<<<1, 256, 0, st>>>(ws, grid, tw, out3);
+    ST_CHECK_LAUNCH("temporal_finish_kernel");
+    return ST_OK;
+}
+int temporal_warp_backward(const float* os, const float* cs, const float* flow, int N, int C, int H, int W, float tw,
+                           const float* stats, const float* gw, float* g, cudaStream_t st) {
+    temporal_warp_bwd_kernel<<<ew_grid((size_t)N * H * W, 256), 256, 0, st>>>(os, cs, flow, N, C, H, W, tw, stats, gw, g);
+    ST_CHECK_LAUNCH("temporal_warp_bwd_kernel");
     return ST_OK;
 }
 int temporal_backward(const float* os, const float* cs, size_t total, float tw, const float* stats, const float* gw,

@@ -549,15 +549,22 @@ class _TVFn(torch.autograd.Function):
 
 class _TemporalFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, old_content, old_stylized, cur_content, cur_stylized, tw):
-        out3 = ops.temporal_fwd(old_content, old_stylized, cur_content, cur_stylized, tw)
-        ctx.os, ctx.cs, ctx.tw, ctx.out3 = old_stylized, cur_stylized, tw, out3
+    def forward(ctx, old_content, old_stylized, cur_content, cur_stylized, tw, flow=None):
+        if flow is None:
+            out3 = ops.temporal_fwd(old_content, old_stylized, cur_content, cur_stylized, tw)
+        else:
+            out3 = ops.temporal_warp_fwd(old_content, old_stylized, cur_content, cur_stylized, flow, tw)
+        ctx.os, ctx.cs, ctx.tw, ctx.out3, ctx.flow = old_stylized, cur_stylized, tw, out3, flow
         return out3[0]
 
     @staticmethod
     def backward(ctx, g):
-        gs = ops.temporal_bwd(ctx.os, ctx.cs, ctx.tw, ctx.out3, g.reshape(1).contiguous().float())
-        return None, None, None, gs, None
+        gw = g.reshape(1).contiguous().float()
+        if ctx.flow is None:
+            gs = ops.temporal_bwd(ctx.os, ctx.cs, ctx.tw, ctx.out3, gw)
+        else:
+            gs = ops.temporal_warp_bwd(ctx.os, ctx.cs, ctx.flow, ctx.tw, ctx.out3, gw)
+        return None, None, None, gs, None, None
 
 
 # --------------------------------------------------------------------------
@@ -838,16 +845,20 @@ class VideoTransformNet(ImageTransformNet):
             self.has_external_weights = False
 
     def get_temporal_loss(self, old_content, old_stylized, current_content, current_stylized,
-                          temporal_weight=1) -> torch.Tensor:
+                          temporal_weight=1, flow=None) -> torch.Tensor:
         """network.py:885-903: tw * ||cur_sty - old_sty|| / (||cur_con - old_con|| + 1); the
-        gradient flows into ``current_stylized`` only."""
+        gradient flows into ``current_stylized`` only.  ``flow`` (extension, no reference code: SURVEY F9)
+        [B, 2, H, W] in pixels warps the two previous frames bilinearly before the comparison."""
         ops._require_cuda(current_stylized, 'get_temporal_loss')
         c = lambda t: t.detach().contiguous().float()
+        if flow is not None:
+            assert tuple(flow.shape) == (current_stylized.shape[0], 2) + tuple(current_stylized.shape[2:]), 'flow must be [B, 2, H, W]'
+            flow = c(flow)
         return _TemporalFn.apply(c(old_content), c(old_stylized), c(current_content),
-                                 current_stylized.contiguous().float(), float(temporal_weight))
+                                 current_stylized.contiguous().float(), float(temporal_weight), flow)
 
     def closure_loss_video(self, batch, old_images, loss_network, temporal_weight=0.8,
-                           style_weight=100_000, content_weight=1, tv_scale=1.0):
+                           style_weight=100_000, content_weight=1, tv_scale=1.0, flow=None):
         """Closure body of video_train (network.py:984-1037); updates ``old_images`` in place."""
         old_content_images, old_styled_images = old_images
         batch_with_old_content = torch.cat([batch, old_styled_images], dim=1)
@@ -859,7 +870,7 @@ class VideoTransformNet(ImageTransformNet):
         if tv_scale != 1.0:
             regularization_loss = regularization_loss * tv_scale
         temporal_loss = self.get_temporal_loss(old_content_images, old_styled_images, batch, transformed_image,
-                                               temporal_weight=temporal_weight)
+                                               temporal_weight=temporal_weight, flow=flow)
         total_loss = style_loss + content_loss + regularization_loss + temporal_loss
         old_images[0] = batch.detach()
         old_images[1] = transformed_image.detach()

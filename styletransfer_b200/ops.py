@@ -374,6 +374,27 @@ def temporal_fwd(old_content, old_stylized, cur_content, cur_stylized, tw):
     return out3
 
 
+def temporal_warp_fwd(old_content, old_stylized, cur_content, cur_stylized, flow, tw):
+    """Extension: temporal loss against the flow-warped previous frame."""
+    _require_cuda(cur_stylized, 'temporal_warp_fwd')
+    N, C, H, W = cur_stylized.shape
+    out3 = torch.empty((3,), dtype=torch.float32, device=cur_stylized.device)
+    ws = workspace(4096 * 4, cur_stylized.device, 'small')
+    _lib.check(_lib.lib().st_temporal_warp_fwd(old_content.data_ptr(), old_stylized.data_ptr(), cur_content.data_ptr(),
+                                               cur_stylized.data_ptr(), flow.data_ptr(), N, C, H, W, float(tw), out3.data_ptr(),
+                                               ws.data_ptr(), _stream()), 'st_temporal_warp_fwd')
+    return out3
+
+
+def temporal_warp_bwd(old_stylized, cur_stylized, flow, tw, stats3, gw):
+    N, C, H, W = cur_stylized.shape
+    g = torch.empty_like(cur_stylized)
+    _lib.check(_lib.lib().st_temporal_warp_bwd(old_stylized.data_ptr(), cur_stylized.data_ptr(), flow.data_ptr(), N, C, H, W,
+                                               float(tw), stats3.data_ptr(), gw.data_ptr(), g.data_ptr(), _stream()),
+               'st_temporal_warp_bwd')
+    return g
+
+
 def temporal_bwd(old_stylized, cur_stylized, tw, stats3, gw):
     g = torch.empty_like(cur_stylized)
     _lib.check(_lib.lib().st_temporal_bwd(old_stylized.data_ptr(), cur_stylized.data_ptr(), cur_stylized.numel(), float(tw),

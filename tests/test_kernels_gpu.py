@@ -313,6 +313,36 @@ def test_tv_and_temporal(ops):
     assert rel_l2(g, cs.grad) < 1e-5
 
 
+def test_temporal_flow_warp_extension(ops):
+    """EXTENSION, parity unpinned (the reference's temporal loss has no optical flow): the flow-warped
+    temporal loss against torch's grid_sample (bilinear, zeros, align_corners=True, flow in pixels), including
+    samples that leave the frame; zero flow reproduces the reference form; the gradient reaches cur_stylized only."""
+    N, C, H, W = 2, 3, 19, 27
+    oc, os_, cc = (seeded((N, C, H, W), s, device='cuda') for s in (62, 63, 64))
+    cs = seeded((N, C, H, W), 65, device='cuda').requires_grad_(True)
+    flow = seeded((N, 2, H, W), 66, 2.5, device='cuda')
+    ys, xs = torch.meshgrid(torch.arange(H, device='cuda', dtype=torch.float32),
+                            torch.arange(W, device='cuda', dtype=torch.float32), indexing='ij')
+    gx = 2 * (xs[None] + flow[:, 0]) / (W - 1) - 1
+    gy = 2 * (ys[None] + flow[:, 1]) / (H - 1) - 1
+    grid = torch.stack([gx, gy], dim=-1)
+    warp = lambda t: F.grid_sample(t, grid, mode='bilinear', padding_mode='zeros', align_corners=True)
+    tl = ((cs - warp(os_)).norm() / ((cc - warp(oc)).norm() + 1)) * 0.8
+    tl.backward()
+    out3 = ops.temporal_warp_fwd(oc, os_, cc, cs.detach(), flow, 0.8)
+    assert abs(float(out3[0]) - float(tl)) / float(tl) < 1e-5
+    g = ops.temporal_warp_bwd(os_, cs.detach(), flow, 0.8, out3, torch.tensor([1.0], device='cuda'))
+    assert rel_l2(g, cs.grad) < 1e-5
+    zero = torch.zeros_like(flow)
+    assert torch.allclose(ops.temporal_warp_fwd(oc, os_, cc, cs.detach(), zero, 0.8), ops.temporal_fwd(oc, os_, cc, cs.detach(), 0.8), rtol=1e-6)
+    from styletransfer_b200 import network
+    net = network.VideoTransformNet.__new__(network.VideoTransformNet)
+    cs2 = cs.detach().clone().requires_grad_(True)
+    loss = network.VideoTransformNet.get_temporal_loss(net, oc, os_, cc, cs2, temporal_weight=0.8, flow=flow)
+    loss.backward()
+    assert abs(float(loss) - float(tl)) / float(tl) < 1e-5 and rel_l2(cs2.grad, cs.grad) < 1e-5
+
+
 @pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64)])
 def test_conv_image_fwd_and_dgrad(ops, N, H, W):
     """VGG conv1_1 (3 -> 64) in exact fp32 on the CUDA cores, NCHW fp32 image in, image gradient out."""
