@@ -6,6 +6,8 @@ in-tree shared object.
 """
 import ctypes
 import os
+import sys
+import time
 from ctypes import c_char_p, c_double, c_float, c_int, c_size_t, c_void_p
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -80,10 +82,20 @@ def lib():
         return _lib
     from . import build as _build
     if not _build.up_to_date():
-        _build.build()
+        sys.stderr.write('styletransfer_b200: libstransfer_b200.so is stale or missing -- rebuilding with nvcc (about a minute)\n')
+        _build.build()                      # serialised across processes by a file lock, published atomically
     if not os.path.exists(LIB_PATH):
         raise StransferError(f'{LIB_PATH} is missing: run `python -m styletransfer_b200.build`')
-    handle = ctypes.CDLL(LIB_PATH)
+    handle = None
+    for attempt in range(5):
+        try:
+            handle = ctypes.CDLL(LIB_PATH)
+            break
+        except OSError as e:                # e.g. a snapshot of the tree that is still being materialised
+            if attempt == 4:
+                raise StransferError(f'cannot load {LIB_PATH}: {e}') from e
+            sys.stderr.write(f'styletransfer_b200: loading {LIB_PATH} failed ({e}); retrying\n')
+            time.sleep(2.0 * (attempt + 1))
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(handle, name)          # AttributeError if the symbol is not exported
         fn.restype = res

@@ -45,20 +45,34 @@ def up_to_date():
 
 
 def build(force=False, verbose=False):
-    if not force and up_to_date():
-        return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + ['-I', INCLUDE, '-o', LIB] + [os.path.join(CSRC, s) for s in SOURCES]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    log = res.stdout + res.stderr
-    with open(os.path.join(HERE, 'build.log'), 'w') as f:
-        f.write(' '.join(cmd) + '\n' + log)
-    if res.returncode != 0:
-        raise RuntimeError('nvcc failed:\n' + log[-6000:])
-    if verbose:
-        print(log)
-    with open(STAMP, 'w') as f:
-        f.write(_digest())
-    return LIB
+    """Builds under an exclusive file lock and publishes the library with an atomic rename: the ranks of a
+    torchrun launch may all get here at once; one of them compiles, the others wait and find it up to date,
+    and no process can ever dlopen a half-written file."""
+    import fcntl
+    with open(os.path.join(HERE, '.build_lock'), 'w') as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and up_to_date():
+                return LIB
+            tmp = LIB + f'.tmp{os.getpid()}'
+            cmd = [_nvcc()] + NVCC_FLAGS + ['-I', INCLUDE, '-o', tmp] + [os.path.join(CSRC, s) for s in SOURCES]
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            log = res.stdout + res.stderr
+            with open(os.path.join(HERE, 'build.log'), 'w') as f:
+                f.write(' '.join(cmd) + '\n' + log)
+            if res.returncode != 0:
+                if os.path.exists(tmp):
+                    os.unlink(tmp)
+                raise RuntimeError('nvcc failed:\n' + log[-6000:])
+            if verbose:
+                print(log)
+            os.replace(tmp, LIB)
+            with open(STAMP + '.tmp', 'w') as f:
+                f.write(_digest())
+            os.replace(STAMP + '.tmp', STAMP)
+            return LIB
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
 
 
 if __name__ == '__main__':
