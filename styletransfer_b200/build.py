@@ -31,7 +31,7 @@ def _digest():
     for name in files:
         path = name if os.path.isabs(name) else os.path.join(CSRC, name)
         with open(path, 'rb') as f:
-            h.update(name.encode())
+            h.update(os.path.basename(name).encode())      # never the absolute path: the tree is copied to other roots
             h.update(f.read())
     h.update(' '.join(NVCC_FLAGS).encode())
     return h.hexdigest()
