@@ -256,3 +256,26 @@ def test_lbfgs_model_follows_torch_lbfgs(hist):
     assert opt.state[xt]['n_iter'] == mod.n_iter == 20
     assert mod.k == min(hist, 19)
     assert err < 1e-4, err
+
+
+def test_build_stamp_survives_copying_the_tree(tmp_path):
+    """gpurun copies the repo to another root on the GPU box: the stamp next to the built library must still
+    match there (it once hashed the header's absolute path, so every process on the box rebuilt the library)."""
+    import importlib.util
+    import shutil
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, 'styletransfer_b200')
+    from styletransfer_b200 import build as live
+    if not live.up_to_date():
+        live.build()
+    dst = tmp_path / 'elsewhere' / 'styletransfer_b200'
+    shutil.copytree(os.path.join(pkg, 'csrc'), dst / 'csrc')
+    (tmp_path / 'elsewhere' / 'include').mkdir()
+    shutil.copy(os.path.join(root, 'include', 'stransfer_b200.h'), tmp_path / 'elsewhere' / 'include')
+    shutil.copy(os.path.join(pkg, 'build.py'), dst)
+    shutil.copy(os.path.join(pkg, '.build_stamp'), dst)
+    os.symlink(os.path.join(pkg, 'libstransfer_b200.so'), dst / 'libstransfer_b200.so')
+    spec = importlib.util.spec_from_file_location('copied_build', dst / 'build.py')
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.up_to_date()
