@@ -274,29 +274,28 @@ def run_video_st(args, rank, world, dev, L, timed):
         frames.append(frames[-1] + 0.05 * seeded((VIDEO_B, 3, VIDEO_S, VIDEO_S), 400 + t))
     host_frames = [f[rank * per:(rank + 1) * per].contiguous().pin_memory() for f in frames]
     dev_frames = [f.to(dev) for f in host_frames]
-    frame_buf = torch.empty_like(dev_frames[0])
-    state = {'t': 0, 'old': None, 'last': None, 'resident': True}
+    # fixed buffers of the video_train loop (network.py:905-1069): this frame, the previous frame's content and
+    # stylised images as they were before the iteration, and the slot receiving this frame's stylised output
+    frame_buf, old_content, old_stylized, next_stylized = (torch.empty_like(dev_frames[0]) for _ in range(4))
+    train_closure = net.video_training_closure(frame_buf, old_content, old_stylized, next_stylized, loss_net, bucket,
+                                               temporal_weight=0.8, graph=not args.no_graph)
+    state = {'t': 0, 'last': None, 'resident': True}
+
+    def closure():
+        total = train_closure()
+        state['last'] = total.detach()
+        return total
 
     def step():
         t = state['t'] % VIDEO_FRAMES
         if state['resident']:
             frame_buf.copy_(dev_frames[t])
-        batch = frame_buf.clone()                      # the closure keeps the frame as next step's old content
-        if t == 0:
-            state['old'] = [batch, batch]
-        frozen = [state['old'][0], state['old'][1]]
-
-        def closure():
-            bucket.rebind()
-            bucket.zero()
-            st = [frozen[0], frozen[1]]
-            total, _ = net.closure_loss_video(batch, st, loss_net, 0.8, tv_scale=float(world))
-            state['old'] = st
-            total.backward()
-            bucket.all_reduce()
-            state['last'] = total.detach()
-            return total
+        if t == 0:                                     # new clip: the previous frame is the frame itself
+            old_content.copy_(frame_buf)
+            old_stylized.copy_(frame_buf)
         opt.step(closure)
+        old_content.copy_(frame_buf)
+        old_stylized.copy_(next_stylized)
         state['t'] += 1
     for _ in range(max(args.warmup, 3)):
         step()
@@ -304,6 +303,8 @@ def run_video_st(args, rank, world, dev, L, timed):
     n0 = L.st_launch_count()
     ms = timed(step, args.steps)
     launches = L.st_launch_count() - n0
+    if hasattr(train_closure, 'launches'):
+        launches = (train_closure.launches + 2) * args.steps     # kernels inside the replayed graph + the Adam step
     state['t'], state['resident'] = 0, False
     e2e_step = HostFedStep(host_frames, frame_buf, step, lambda: state['last'])
     for _ in range(2):
@@ -315,7 +316,7 @@ def run_video_st(args, rank, world, dev, L, timed):
             'scaling': 'strong', 'global_batch_clips': VIDEO_B, 'per_gpu_clips': per,
             'config': {'workload': 'video_st train: 8-frame synthetic 512x512 clips, global batch 8 clips, one frame batch per step, '
                                    'closure + all-reduce + Adam (BASELINE configs[4]; temporal loss without flow warp as in the reference)',
-                       'parallelism': f'dp{world}', 'launch': 'eager'},
+                       'parallelism': f'dp{world}', 'launch': 'eager' if args.no_graph else 'cuda graph replay'},
             'tflops_algorithmic': value * GF_VIDEO_PER_FRAME / 1e3, 'algorithmic_gflop_per_frame': GF_VIDEO_PER_FRAME,
             'e2e': {'value': VIDEO_B * args.steps / (ms_e2e * 1e-3), 'unit': 'frames/s',
                     'h2d_bytes_per_step': host_frames[0].numel() * 4 * world, 'd2h_bytes_per_step': 4 * world,

@@ -876,6 +876,53 @@ class VideoTransformNet(ImageTransformNet):
         old_images[1] = transformed_image.detach()
         return total_loss, transformed_image
 
+    def video_training_closure(self, batch, old_content, old_stylized, next_stylized, loss_network, bucket,
+                               temporal_weight=0.8, style_weight=100_000, content_weight=1, graph=None):
+        """The closure ``video_train`` hands to ``optimizer.step`` (network.py:988-1037) on FIXED tensors: the
+        frame batch, the previous frame's content / stylised images as they were before this iteration
+        (network.py:980-986 binds them outside the closure) and ``next_stylized``, which receives this frame's
+        stylised output (the loop makes it the next ``old_stylized`` after the optimizer step).  zero the
+        bucket -> 6-channel forward -> loss network -> TV + temporal loss -> backward (-> all-reduce).  With
+        CUDA graphs everything up to the all-reduce is one replayed graph: at one clip per GPU the ~260
+        eager launches cost more host time than device time."""
+        world = st_dist.world_size()
+
+        def body():
+            loss_network._content_key = None
+            bucket.rebind()
+            bucket.zero()
+            state = [old_content, old_stylized]
+            total_loss, transformed = self.closure_loss_video(batch, state, loss_network, temporal_weight, style_weight,
+                                                              content_weight, tv_scale=float(world))
+            total_loss.backward()
+            with torch.no_grad():
+                next_stylized.copy_(transformed)
+            return total_loss
+        if graph is None:
+            graph = cuda_graphs_enabled()
+        if not graph:
+            def eager():
+                total_loss = body()
+                bucket.all_reduce()
+                return total_loss
+            return eager
+        for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
+            node.loss = None
+        loss_network._loss_vector = None
+        self._pack_cache.always_repack = True
+        try:
+            graphed = GraphedClosure(body, leaves=[p for p in self.parameters() if p.requires_grad])
+        finally:
+            self._pack_cache.always_repack = False
+            self._pack_cache.entries.clear()
+
+        def replay():
+            total_loss = graphed()
+            bucket.all_reduce()
+            return total_loss
+        replay.launches = graphed.launches
+        return replay
+
     def video_train(self, style_name='nsp', epochs=50, temporal_weight=0.8, style_weight=100_000,
                     feature_weight=1, content_weight=1, video_loader=None, max_iterations=None) -> None:
         """network.py:905-1069.  ``video_loader`` (extra, optional): an iterable of clips, each an
@@ -889,10 +936,11 @@ class VideoTransformNet(ImageTransformNet):
         # data parallel over CLIPS (frames of a clip are sequentially dependent);
         # the temporal loss uses the norms of the rank's own clips (per-shard norms)
         world = st_dist.world_size()
-        bucket = getattr(optimizer, 'bucket', None) or (st_dist.GradBucket(self.parameters()) if world > 1 else None)
+        bucket = getattr(optimizer, 'bucket', None) or st_dist.GradBucket(self.parameters())
         iteration = 0
         if video_loader is None:
             video_loader = dataset.VideoDataset(batch_size=self.batch_size)
+        bufs, closure, closure_key = None, None, None
         for epoch in range(epochs):
             if epoch == 0 and self.has_external_weights:
                 LOGGER.info('Freezing weights imported from fast transfer network for the first epoch')
@@ -910,31 +958,26 @@ class VideoTransformNet(ImageTransformNet):
                 continue
             LOGGER.info('Starting epoch %d', epoch)
             for video_batch in video_loader:
-                old_images = None
+                first_frame = True
                 for batch in dataset.iterate_on_video_batches(video_batch):
                     batch = batch.to(constants.DEVICE)
-                    if bucket is not None:
+                    if world > 1:
                         batch = st_dist.shard(batch)
-                    if old_images is None:
-                        old_images = [batch, batch]
-                    # the closure reads the previous frame's images as they were BEFORE this
-                    # iteration (network.py:980-986 binds them outside the closure)
-                    frozen = [old_images[0], old_images[1]]
-
-                    def closure():
-                        if bucket is None:
-                            optimizer.zero_grad()
-                        else:
-                            bucket.rebind()
-                            bucket.zero()
-                        state = [frozen[0], frozen[1]]
-                        total_loss, _ = self.closure_loss_video(batch, state, style_loss_network, temporal_weight,
-                                                                style_weight, content_weight, tv_scale=float(world))
-                        old_images[0], old_images[1] = state
-                        total_loss.backward()
-                        if bucket is not None:
-                            bucket.all_reduce()
-                        return total_loss
+                    batch = batch.contiguous().float()
+                    # fixed buffers the closure (a replayed CUDA graph by default) reads: this frame, the previous
+                    # frame's content / stylised images as they were BEFORE this iteration (network.py:980-986 binds
+                    # them outside the closure), and the slot that receives this frame's stylised output
+                    key = (tuple(batch.shape), tuple(p.requires_grad for p in self.parameters()))
+                    if key != closure_key:
+                        bufs = [torch.empty_like(batch) for _ in range(4)]      # batch, old content, old stylised, next stylised
+                        closure = self.video_training_closure(bufs[0], bufs[1], bufs[2], bufs[3], style_loss_network, bucket,
+                                                              temporal_weight, style_weight, content_weight)
+                        closure_key, first_frame = key, True
+                    bufs[0].copy_(batch)
+                    if first_frame:                      # new clip: the previous frame is the frame itself (network.py:977-978)
+                        bufs[1].copy_(batch)
+                        bufs[2].copy_(batch)
+                        first_frame = False
 
                     if iteration % 20 == 0:
                         total_loss = closure()
@@ -942,6 +985,8 @@ class VideoTransformNet(ImageTransformNet):
                         LOGGER.info('Epoch: %d\tBatch Loss: %.4f', epoch, total_loss)
                     iteration += 1
                     optimizer.step(closure)
+                    bufs[1].copy_(bufs[0])               # old_images = [batch, transformed_image] (network.py:1016-1017)
+                    bufs[2].copy_(bufs[3])
                     if max_iterations is not None and iteration >= max_iterations:
                         return
             os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)

@@ -288,3 +288,50 @@ def test_stylize_host_batch_streams_chunks(network):
     got = net.stylize_host_batch(x)
     torch.cuda.synchronize()
     assert got.is_pinned() and torch.equal(got, want)
+
+
+def test_video_training_closure_graph_matches_eager_and_oracle(network):
+    """video_train (network.py:905-1069) on a synthetic clip: the CUDA-graph replay of the closure follows the
+    eager closure through four recurrent frames and Adam steps, and both follow the CPU oracle's recurrence
+    (old content / old stylised images are the previous frame's, bound before the closure)."""
+    style = seeded((1, 3, 32, 32), 71)
+    params = oracle.make_transform_params(8, 6)
+    frames = [seeded((2, 3, 32, 48), 150)]
+    for t in range(1, 4):
+        frames.append(frames[-1] + 0.05 * seeded((2, 3, 32, 48), 150 + t))
+    # oracle recurrence with torch.optim.Adam
+    vw = oracle.make_vgg_weights(1)
+    targets = oracle.style_targets(style, vw)
+    ps = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    opt = torch.optim.Adam(list(ps.values()))
+    old_c, old_s, ref_losses = frames[0], frames[0], []
+    for b in frames:
+        opt.zero_grad()
+        out = oracle.transform_net(torch.cat([b, old_s], dim=1), ps)
+        losses, _ = oracle.loss_network(out, b, targets, vw)
+        total = 1e5 * losses[:5].sum() + losses[5] + oracle.tv_loss(out) + oracle.temporal_loss(old_c, old_s, b, out, 0.8)
+        total.backward()
+        ref_losses.append(float(total.detach()))
+        opt.step()
+        old_c, old_s = b, out.detach()
+    results = []
+    for graph in (False, True):
+        net = _build(network, network.VideoTransformNet, params, style.cuda(), 2)
+        loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
+        loss_net.compute_feature_loss = False
+        o = net.get_optimizer()
+        bufs = [torch.empty(2, 3, 32, 48, device='cuda') for _ in range(4)]
+        closure = net.video_training_closure(bufs[0], bufs[1], bufs[2], bufs[3], loss_net, o.bucket, graph=graph)
+        assert graph == hasattr(closure, 'launches')
+        losses = []
+        for t, b in enumerate(frames):
+            bufs[0].copy_(b.cuda())
+            if t == 0:
+                bufs[1].copy_(b.cuda()); bufs[2].copy_(b.cuda())
+            losses.append(float(o.step(closure)))
+            bufs[1].copy_(bufs[0]); bufs[2].copy_(bufs[3])
+        results.append((losses, {k: v.detach().clone() for k, v in net.state_dict().items()}))
+    (l0, p0), (l1, p1) = results
+    assert max(abs(a - b) / abs(a) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
+    assert record('graph_video/param_max_abs_diff', max(float((p0[k] - p1[k]).abs().max()) for k in p0)) < 1e-6
+    assert record('video4/loss_rel_vs_oracle', max(abs(a - b) / abs(b) for a, b in zip(l0, ref_losses))) < 2e-2, (l0, ref_losses)
