@@ -8,6 +8,8 @@ prefixes by ONE fused backward-data chain to the image.  VGG weights are frozen
 [style x5, content, feature] whose gradient weights (grad_output) are read on the
 device, so no host synchronisation happens anywhere in forward or backward.
 """
+import os
+
 import torch
 
 from . import ops
@@ -18,6 +20,20 @@ CONTENT_TAP = 3
 N_LOSSES = 7
 # backward-data of conv1_1: tcgen05 16-channel tile (default) or the exact-fp32 CUDA-core kernel
 IMAGE_GRAD_TC = True
+
+
+# STRANSFER_OVERLAP_LOSSES=1 runs the loss branches of the taps on a side stream.  Measured on B200 (Gatys 512x512:
+# 1077 vs 1060-1079 closures/s, fast_st 1426 vs 1431 img/s): within run-to-run noise, because the Gram kernels are
+# persistent and occupy every SM anyway -- so the default keeps everything on one stream.
+OVERLAP_LOSS_BRANCHES = os.environ.get('STRANSFER_OVERLAP_LOSSES', '0') != '0'
+_SIDE_STREAMS = {}
+
+
+def _side_stream(device):
+    key = (device.type, device.index)
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(device)
+    return _SIDE_STREAMS[key]
 
 
 class VGGPrefix:
@@ -43,10 +59,11 @@ class VGGPrefix:
                 self.bwd.append(ops.PackedWeight(w, 2, rows_pad=w.shape[1]))
             self.bias.append(b.detach().contiguous().float())
 
-    def taps(self, x, upto=5, keep_all=True):
+    def taps(self, x, upto=5, keep_all=True, on_tap=None):
         """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto.  keep_all=False:
         only the last tap is wanted (content targets); layers whose ReLU copy feeds the next conv then
-        skip the store of their pre-ReLU tap (None in the returned list)."""
+        skip the store of their pre-ReLU tap (None in the returned list).  ``on_tap(i, tap)`` is called as
+        soon as tap i has been launched (the loss branch of the tap can then run beside the next layer)."""
         h = None
         taps = []
         for i in range(upto):
@@ -60,6 +77,8 @@ class VGGPrefix:
             else:
                 tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=want_out, want_relu=want_relu)
             taps.append(tap)
+            if on_tap is not None:
+                on_tap(i, tap)
             if last:
                 break
             h = ops.relu_maxpool_fwd(tap) if pool_next else relu
@@ -69,18 +88,36 @@ class VGGPrefix:
 class _VGGLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, net, style_targets, content_target, with_feature):
-        taps = net.taps(x)
         losses = torch.zeros(N_LOSSES, dtype=torch.float32, device=x.device)
-        diffs = []
-        for i, tap in enumerate(taps):
+        diffs = [None] * 5
+        feat = [None]
+        # The loss branch of tap i (Gram -> split-K finish -> style MSE, and the content / feature MSE at
+        # tap 4) does not feed the next layer: it runs on a side stream beside conv i+1, so its small
+        # finish / reduction kernels fill SMs the convolution leaves idle (inside a captured CUDA graph the
+        # two streams become parallel branches).  The streams join before forward returns.
+        cur = torch.cuda.current_stream(x.device)
+        side = _side_stream(x.device) if OVERLAP_LOSS_BRANCHES else None
+
+        def branch(i, tap):
             G = ops.gram(tap)
-            diffs.append(ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1]))
-        ops.mse_fwd(taps[CONTENT_TAP], content_target, losses[5:6])
-        feat_mse = None
-        if with_feature:
-            feat_mse = torch.empty(1, dtype=torch.float32, device=x.device)
-            ops.mse_fwd(taps[CONTENT_TAP], content_target, feat_mse, relu=True)
-            ops.mse_fwd(taps[CONTENT_TAP], content_target, losses[6:7], relu=True, feature_form=True)
+            diffs[i] = ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1])
+            if i == CONTENT_TAP:
+                ops.mse_fwd(tap, content_target, losses[5:6])
+                if with_feature:
+                    feat[0] = torch.empty(1, dtype=torch.float32, device=x.device)
+                    ops.mse_fwd(tap, content_target, feat[0], relu=True)
+                    ops.mse_fwd(tap, content_target, losses[6:7], relu=True, feature_form=True)
+
+        def on_tap(i, tap):
+            if side is None:
+                return branch(i, tap)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                branch(i, tap)
+        taps = net.taps(x, on_tap=on_tap)
+        if side is not None:
+            cur.wait_stream(side)
+        feat_mse = feat[0]
         ctx.net, ctx.taps, ctx.diffs = net, taps, diffs
         ctx.content_target, ctx.feat_mse = content_target, feat_mse
         ctx.in_shape = x.shape
