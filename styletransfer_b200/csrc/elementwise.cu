@@ -269,8 +269,16 @@ channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, in
     const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
     float s = 0.f;
-    if (c < C)
-        for (int b = rl; b < nblk; b += 8) s += partial[static_cast<size_t>(b) * C + c];
+    if (c < C) {
+        float s1 = 0.f, s2 = 0.f, s3 = 0.f;        // independent accumulators: the loads are L2 round trips
+        int b = rl;
+        for (; b + 24 < nblk; b += 32) {
+            s += partial[static_cast<size_t>(b) * C + c];       s1 += partial[static_cast<size_t>(b + 8) * C + c];
+            s2 += partial[static_cast<size_t>(b + 16) * C + c]; s3 += partial[static_cast<size_t>(b + 24) * C + c];
+        }
+        for (; b < nblk; b += 8) s += partial[static_cast<size_t>(b) * C + c];
+        s = (s + s1) + (s2 + s3);
+    }
     sm[rl][cl] = s;
     __syncthreads();
     if (rl == 0 && c < Cout) {
