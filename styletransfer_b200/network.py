@@ -696,6 +696,16 @@ class ImageTransformNet(nn.Sequential):
             regularization_loss = regularization_loss * tv_scale
         return style_loss + content_loss + regularization_loss, transformed_image
 
+    def _backward_into_bucket(self, total_loss):
+        """backward() with the parameters' (zeroed, bucket-view) ``.grad`` tensors as gradient sinks: the
+        backward kernels write dW / db / dgamma / dbeta straight into the flat bucket instead of handing 62
+        tensors to autograd's accumulate kernels (transform._PackCache.grad_sink)."""
+        self._pack_cache.grad_sink = {n: p.grad for n, p in self.named_parameters() if p.grad is not None}
+        try:
+            total_loss.backward()
+        finally:
+            self._pack_cache.grad_sink = None
+
     def training_closure(self, batch, loss_network, bucket, style_weight=100_000, content_weight=1, graph=None):
         """The closure ``static_train`` hands to ``optimizer.step`` (network.py:690-731) for a batch
         held in the fixed tensor ``batch`` (the loop copies every new batch into it): zero the
@@ -712,7 +722,7 @@ class ImageTransformNet(nn.Sequential):
             bucket.rebind()
             bucket.zero()
             total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight, tv_scale=float(world))
-            total_loss.backward()
+            self._backward_into_bucket(total_loss)
             return total_loss
         if graph is None:
             graph = cuda_graphs_enabled()
@@ -894,7 +904,7 @@ class VideoTransformNet(ImageTransformNet):
             state = [old_content, old_stylized]
             total_loss, transformed = self.closure_loss_video(batch, state, loss_network, temporal_weight, style_weight,
                                                               content_weight, tv_scale=float(world))
-            total_loss.backward()
+            self._backward_into_bucket(total_loss)
             with torch.no_grad():
                 next_stylized.copy_(transformed)
             return total_loss

@@ -215,7 +215,15 @@ def conv9_reduce(x, w, bias=None):
     return out
 
 
-def conv9_wgrad(big, small, mode, want_bias=True):
+def _grad_out(out, shape, dev):
+    """A caller-provided gradient buffer (a view of the flat gradient bucket) or a fresh tensor."""
+    if out is None:
+        return torch.empty(shape, dtype=torch.float32, device=dev)
+    assert out.is_contiguous() and out.dtype == torch.float32 and tuple(out.shape) == tuple(shape), (out.shape, shape)
+    return out
+
+
+def conv9_wgrad(big, small, mode, want_bias=True, dw_out=None, db_out=None):
     """Backward-weight of the 9x9 layers.  mode 0: layer 0 (big = dy Split, small = input NCHW) ->
     dw [32][C][9][9]; mode 1: layer 22 (big = input Split, small = dy NCHW) -> dw [3][32][9][9]."""
     L = _lib.lib()
@@ -225,8 +233,8 @@ def conv9_wgrad(big, small, mode, want_bias=True):
     assert big.C == 32 and big.shape[:3] == (N, H, W)
     dev = big.buf.device
     ws = workspace(L.st_conv9_wgrad_workspace_bytes(C), dev)
-    dw = torch.empty((32, C, 9, 9) if mode == 0 else (C, 32, 9, 9), dtype=torch.float32, device=dev)
-    db = torch.empty((32 if mode == 0 else C,), dtype=torch.float32, device=dev) if want_bias else None
+    dw = _grad_out(dw_out, (32, C, 9, 9) if mode == 0 else (C, 32, 9, 9), dev)
+    db = _grad_out(db_out, (32 if mode == 0 else C,), dev) if want_bias else None
     _lib.check(L.st_conv9_wgrad(big.hi, big.lo, big.planes, s0, s1, sc, C, mode, dw.data_ptr(), _p(db), ws.data_ptr(), ws.numel(),
                                 N, H, W, _stream()), 'st_conv9_wgrad')
     return dw, db
@@ -245,13 +253,13 @@ def workspace(nbytes, device, tag='ws'):
     return buf
 
 
-def conv2d_wgrad(dy, x, ks, stride, pad, up, cout, cin, want_bias=True):
+def conv2d_wgrad(dy, x, ks, stride, pad, up, cout, cin, want_bias=True, dw_out=None, db_out=None):
     L = _lib.lib()
     dev = x.buf.device
     nbytes = L.st_conv2d_wgrad_workspace_bytes(dy.N, dy.H, dy.W, dy.C, x.C, ks)
     ws = workspace(nbytes, dev)
-    dw = torch.empty((cout, cin, ks, ks), dtype=torch.float32, device=dev)
-    db = torch.empty((cout,), dtype=torch.float32, device=dev) if want_bias else None
+    dw = _grad_out(dw_out, (cout, cin, ks, ks), dev)
+    db = _grad_out(db_out, (cout,), dev) if want_bias else None
     _lib.check(L.st_conv2d_wgrad(dy.hi, dy.lo, dy.C, x.hi, x.lo, x.N, x.H, x.W, x.C, up, dy.H, dy.W, ks, stride, pad,
                                  cout, cin, dw.data_ptr(), _p(db), ws.data_ptr(), ws.numel(), _stream()), 'st_conv2d_wgrad')
     return dw, db
@@ -331,16 +339,17 @@ def instnorm_fwd(x, gamma, beta, relu=False, up=False, eps=1e-5):
     return y, stats
 
 
-def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False, want_dsum=False):
+def instnorm_bwd(x, gy, stats, gamma, beta, relu=False, up=False, want_dsum=False, dgamma_out=None, dbeta_out=None,
+                 dsum_out=None):
     """Returns (dx, dgamma, dbeta[, dsum]); dsum = per-channel sum of dx = the bias gradient of the
     convolution in front of the norm.  The saved input is read at the gradient precision."""
     L = _lib.lib()
     dev = x.buf.device
     ws = workspace(L.st_instnorm_workspace_bytes(x.N, x.C), dev)
     dx = x.grad_like()
-    dgamma = torch.empty_like(gamma)
-    dbeta = torch.empty_like(beta)
-    dsum = torch.empty((x.C,), dtype=torch.float32, device=dev) if want_dsum else None
+    dgamma = _grad_out(dgamma_out, gamma.shape, dev)
+    dbeta = _grad_out(dbeta_out, beta.shape, dev)
+    dsum = _grad_out(dsum_out, (x.C,), dev) if want_dsum else None
     _lib.check(L.st_instnorm_bwd(x.hi, x.lo, gy.hi, gy.lo, stats[0].data_ptr(), stats[1].data_ptr(),
                                  gamma.data_ptr(), beta.data_ptr(), dx.hi, dx.lo, dgamma.data_ptr(), dbeta.data_ptr(), _p(dsum),
                                  min(x.planes, bwd_planes()), x.N, x.H, x.W, x.C, int(relu), int(up), ws.data_ptr(), _stream()),

@@ -102,6 +102,10 @@ class _PackCache:
     def __init__(self):
         self.entries = {}
         self.always_repack = False      # CUDA-graph capture: the packing kernels must be part of every replay
+        # {state-dict key: zeroed fp32 buffer}: when set (training closures: the views of the flat gradient
+        # bucket that are the parameters' .grad), the backward kernels write the parameter gradients
+        # straight into these buffers and autograd gets None for them -- no per-tensor accumulate kernels
+        self.grad_sink = None
 
     def get(self, name, w, mode, **kw):
         key = (name, mode, ops.PRECISION)
@@ -182,6 +186,11 @@ class TransformNetFn(torch.autograd.Function):
         need = dict(zip(PARAM_NAMES, ctx.needs_input_grad[2:]))
         grads = {}
         cache = ctx.cache
+        sink = cache.grad_sink or {}
+
+        def out_of(name):
+            """The sink buffer of a parameter gradient (the kernel writes it; autograd then gets None)."""
+            return sink.get(name) if need[name] else None
         N, cin, H, W = ctx.in_shape
         gy = gy.contiguous().float()
         g = None             # built lazily: the 9x9 output layer consumes the NCHW fp32 gradient directly
@@ -195,7 +204,8 @@ class TransformNetFn(torch.autograd.Function):
                 name = st[1]
                 w = p[name + '.weight']
                 if need[name + '.weight'] or need[name + '.bias']:
-                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(ctx.saved[idx], gy, 1)
+                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(
+                        ctx.saved[idx], gy, 1, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'))
                 g = ops.conv9_expand(gy, w, flip=True, planes=ops.bwd_planes())
                 continue
             if g is None:
@@ -204,7 +214,8 @@ class TransformNetFn(torch.autograd.Function):
                 name = st[1]
                 w = p[name + '.weight']
                 if need[name + '.weight'] or need[name + '.bias']:
-                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(g, ctx.x, 0)
+                    grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(
+                        g, ctx.x, 0, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'))
                 if ctx.needs_input_grad[0]:
                     # rare (tests / image optimisation through the net): gather-form backward-data
                     pw = cache.get(name, w, 1, rows_pad=ops.pad8(cin), cols_pad=g.C)
@@ -221,7 +232,9 @@ class TransformNetFn(torch.autograd.Function):
                 cout, cin_w = w.shape[0], w.shape[1]
                 if need[name + '.weight'] or need[name + '.bias']:
                     # the bias gradient (sum of dy) came out of the InstanceNorm backward that produced dy
-                    dw, db = ops.conv2d_wgrad(g, xin, k, stride, k // 2, 0, cout, cin_w, want_bias=pending_db is None)
+                    dw, db = ops.conv2d_wgrad(g, xin, k, stride, k // 2, 0, cout, cin_w, want_bias=pending_db is None,
+                                              dw_out=out_of(name + '.weight'),
+                                              db_out=out_of(name + '.bias') if pending_db is None else None)
                     grads[name + '.weight'], grads[name + '.bias'] = dw, (db if pending_db is None else pending_db[:cout])
                 pending_db = None
                 if add_res:
@@ -245,11 +258,19 @@ class TransformNetFn(torch.autograd.Function):
             else:
                 _, name, relu, up = st
                 xin, stats = ctx.saved[idx]
+                # the bias gradient of the convolution in front (the stage before an 'in' stage is its conv)
+                conv_bias = PLAN[idx - 1][1] + '.bias'
+                dsum_out = out_of(conv_bias) if (PLAN[idx - 1][0] == 'conv' and p[conv_bias].numel() == xin.C) else None
                 g, dgam, dbet, pending_db = ops.instnorm_bwd(xin, g, stats, p[name + '.weight'], p[name + '.bias'], relu=relu, up=up,
-                                                             want_dsum=True)
+                                                             want_dsum=True, dgamma_out=out_of(name + '.weight'),
+                                                             dbeta_out=out_of(name + '.bias'), dsum_out=dsum_out)
                 grads[name + '.weight'], grads[name + '.bias'] = dgam, dbet
         ctx.saved = None
         out = [grads.get('__input__'), None]
         for n in PARAM_NAMES:
-            out.append(grads.get(n) if need[n] else None)
+            gn = grads.get(n) if need[n] else None
+            # a gradient the kernels wrote into its sink (same storage) is already where autograd would add it
+            if gn is not None and n in sink and gn.data_ptr() == sink[n].data_ptr():
+                gn = None
+            out.append(gn)
         return tuple(out)

@@ -335,3 +335,46 @@ def test_video_training_closure_graph_matches_eager_and_oracle(network):
     assert max(abs(a - b) / abs(a) for a, b in zip(l0, l1)) < 1e-6, (l0, l1)
     assert record('graph_video/param_max_abs_diff', max(float((p0[k] - p1[k]).abs().max()) for k in p0)) < 1e-6
     assert record('video4/loss_rel_vs_oracle', max(abs(a - b) / abs(b) for a, b in zip(l0, ref_losses))) < 2e-2, (l0, ref_losses)
+
+
+@pytest.mark.parametrize('video', [False, True])
+def test_bucket_gradient_sinks_match_autograd(network, video):
+    """The training closures let the backward kernels write every parameter gradient straight into the flat
+    bucket (no autograd accumulate): the bucket must hold exactly what a plain backward() leaves in .grad --
+    bit for bit, the same kernels produce both -- including with a frozen tensor (no sink, no gradient)."""
+    from styletransfer_b200 import dist as st_dist
+    style = seeded((1, 3, 32, 32), 71).cuda()
+    cin = 6 if video else 3
+    params = oracle.make_transform_params(8, cin)
+    cls = network.VideoTransformNet if video else network.ImageTransformNet
+    batch = seeded((2, 3, 32, 48), 160).cuda()
+    old_c, old_s = seeded((2, 3, 32, 48), 161).cuda(), seeded((2, 3, 32, 48), 162).cuda()
+    net = _build(network, cls, params, style, 2)
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
+    loss_net.compute_feature_loss = False
+    frozen = dict(net.named_parameters())['11.insn1.weight']
+    frozen.requires_grad = False
+    # plain autograd
+    if video:
+        total, _ = net.closure_loss_video(batch, [old_c, old_s], loss_net, 0.8)
+    else:
+        total, _ = net.closure_loss(batch, loss_net)
+    total.backward()
+    want = {n: p.grad.detach().clone() for n, p in net.named_parameters() if p.grad is not None}
+    assert '11.insn1.weight' not in want and len(want) == 61
+    for p in net.parameters():
+        p.grad = None
+    # bucket sinks
+    bucket = st_dist.GradBucket(net.parameters())
+    if video:
+        nxt = torch.empty_like(batch)
+        closure = net.video_training_closure(batch, old_c, old_s, nxt, loss_net, bucket, graph=False)
+    else:
+        closure = net.training_closure(batch, loss_net, bucket, graph=False)
+    total2 = closure()
+    assert float(total2) == float(total)
+    got = {n: p.grad for n, p in net.named_parameters() if p.grad is not None}
+    assert set(got) == set(want)
+    for n in want:
+        assert got[n].data_ptr() >= bucket.flat.data_ptr() and torch.equal(got[n], want[n]), n
+    assert net._pack_cache.grad_sink is None
