@@ -700,7 +700,8 @@ class ImageTransformNet(nn.Sequential):
         """backward() with the parameters' (zeroed, bucket-view) ``.grad`` tensors as gradient sinks: the
         backward kernels write dW / db / dgamma / dbeta straight into the flat bucket instead of handing 62
         tensors to autograd's accumulate kernels (transform._PackCache.grad_sink)."""
-        self._pack_cache.grad_sink = {n: p.grad for n, p in self.named_parameters() if p.grad is not None}
+        if os.environ.get('STRANSFER_GRAD_SINKS', '1') != '0':
+            self._pack_cache.grad_sink = {n: p.grad for n, p in self.named_parameters() if p.grad is not None}
         try:
             total_loss.backward()
         finally:
