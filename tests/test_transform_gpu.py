@@ -378,3 +378,61 @@ def test_bucket_gradient_sinks_match_autograd(network, video):
     for n in want:
         assert got[n].data_ptr() >= bucket.flat.data_ptr() and torch.equal(got[n], want[n]), n
     assert net._pack_cache.grad_sink is None
+
+
+def test_fast_st_full_size_properties(network):
+    """BASELINE configs[2] at full size (batch 16 of 256x256), where the CPU oracle takes minutes: size-independent
+    properties.  (a) two evaluations of the training closure are bit-identical (deterministic reductions);
+    (b) the data-parallel identity of dist.py: the gradient of the global batch equals the average of the gradients
+    of its two halves with the (sum-type) TV term doubled -- the style / content terms are means over the batch;
+    (c) the stylised batch does not depend on which other images share the batch (InstanceNorm is per sample)."""
+    from styletransfer_b200 import dist as st_dist
+    style = seeded((1, 3, 256, 256), 201).cuda()
+    params = oracle.make_transform_params(2, 3)
+    batch = seeded((16, 3, 256, 256), 202).cuda()
+    net = _build(network, network.ImageTransformNet, params, style, 16)
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, 256, 256]).cuda(), vgg_weights=_vgg_cuda())
+    loss_net.compute_feature_loss = False
+    bucket = st_dist.GradBucket(net.parameters())
+
+    def grad_of(b, tv_scale):
+        loss_net._content_key = None
+        bucket.rebind(); bucket.zero()
+        total, out = net.closure_loss(b, loss_net, tv_scale=tv_scale)
+        total.backward()
+        return bucket.flat.clone(), float(total), out.detach()
+    g_all, l_all, out_all = grad_of(batch, 1.0)
+    g_again, l_again, _ = grad_of(batch, 1.0)
+    assert l_all == l_again and torch.equal(g_all, g_again)
+    assert torch.isfinite(g_all).all() and float(g_all.abs().max()) > 0
+    g_a, _, out_a = grad_of(batch[:8].contiguous(), 2.0)
+    g_b, _, _ = grad_of(batch[8:].contiguous(), 2.0)
+    assert record('fast_st_full/dp_identity_rel_l2', rel_l2(0.5 * (g_a + g_b), g_all)) < 1e-4
+    assert rel_l2(out_a, out_all[:8]) < 1e-6
+
+
+def test_video_full_size_properties(network):
+    """BASELINE configs[4] frame size (512x512, 6-channel input): determinism and finiteness of the video closure,
+    and the temporal term vanishes when the stylised frame equals the previous stylised frame's role
+    (old_stylized := output of the same evaluation gives zero temporal loss and gradient contribution)."""
+    style = seeded((1, 3, 256, 256), 201).cuda()
+    params = oracle.make_transform_params(2, 6)
+    net = _build(network, network.VideoTransformNet, params, style, 1)
+    loss_net = network.StyleNetwork(style, torch.rand([1, 3, 256, 256]).cuda(), vgg_weights=_vgg_cuda())
+    loss_net.compute_feature_loss = False
+    frame, prev = seeded((1, 3, 512, 512), 210).cuda(), seeded((1, 3, 512, 512), 211).cuda()
+
+    def run(tw):
+        for p in net.parameters():
+            p.grad = None
+        total, out = net.closure_loss_video(frame, [prev, prev], loss_net, tw)
+        total.backward()
+        return float(total), torch.cat([p.grad.reshape(-1) for p in net.parameters()]), out.detach()
+    l1, g1, out1 = run(0.8)
+    l2, g2, _ = run(0.8)
+    assert l1 == l2 and torch.equal(g1, g2) and torch.isfinite(g1).all()
+    l0, _, out0 = run(0.0)
+    assert torch.equal(out0, out1)
+    t = float(net.get_temporal_loss(prev, prev, frame, out1, temporal_weight=0.8))
+    assert abs((l1 - l0) - t) / max(abs(t), 1e-12) < 1e-3
+    assert float(net.get_temporal_loss(prev, out1, frame, out1, temporal_weight=0.8)) == 0.0
