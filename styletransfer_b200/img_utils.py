@@ -23,7 +23,7 @@ def image_loader_transform(image: Image.Image) -> torch.Tensor:
     arr = np.asarray(image, dtype=np.float32) / 255.0
     if arr.ndim == 2:
         arr = arr[:, :, None]
-    t = torch.from_numpy(arr).permute(2, 0, 1).unsqueeze(0).to(constants.DEVICE, torch.float)
+    t = torch.from_numpy(arr).permute(2, 0, 1).unsqueeze(0).contiguous().to(constants.DEVICE, torch.float)
     mean, std = _stats(t.device)
     if t.shape[1] == 3:
         t = (t - mean) / std

@@ -405,7 +405,8 @@ class StyleNetwork(nn.Module):
         """network.py:403-409.  ``optim.LBFGS`` (what train_gatys asks for) is served by the
         device-resident ``optim.DeviceLBFGS`` -- same defaults and stopping rules, three launches
         per iteration and no host round trip; ``STRANSFER_DEVICE_LBFGS=0`` keeps torch's own."""
-        if optt is optim.LBFGS and input_img.is_cuda and os.environ.get('STRANSFER_DEVICE_LBFGS', '1') != '0':
+        dense = input_img.is_cuda and input_img.is_contiguous() and input_img.dtype == torch.float32
+        if optt is optim.LBFGS and dense and os.environ.get('STRANSFER_DEVICE_LBFGS', '1') != '0':
             return st_optim.DeviceLBFGS([input_img.requires_grad_()])
         return optt([input_img.requires_grad_()])
 
@@ -415,7 +416,8 @@ class StyleNetwork(nn.Module):
         loss (a device sync every closure, network.py:453) is emitted every 50th closure."""
         assert isinstance(style_image, torch.Tensor), 'Images need to be already loaded'
         assert isinstance(content_image, torch.Tensor), 'Images need to be already loaded'
-        input_image = content_image.clone()
+        # start from the content image (network.py:429); a loader's permuted HWC->CHW view becomes a dense NCHW tensor
+        input_image = content_image.detach().clone(memory_format=torch.contiguous_format).float()
         optimizer = self.get_content_optimizer(input_image, optt=optim.LBFGS)
         self.compute_feature_loss = False           # never read by this loop (SURVEY F3)
         n_closure = [0]
