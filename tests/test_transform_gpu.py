@@ -407,7 +407,9 @@ def test_fast_st_full_size_properties(network):
     assert torch.isfinite(g_all).all() and float(g_all.abs().max()) > 0
     g_a, _, out_a = grad_of(batch[:8].contiguous(), 2.0)
     g_b, _, _ = grad_of(batch[8:].contiguous(), 2.0)
-    assert record('fast_st_full/dp_identity_rel_l2', rel_l2(0.5 * (g_a + g_b), g_all)) < 1e-4
+    # not bit-exact: the split-K partition of the weight-gradient kernels follows the batch size and the tensor
+    # core's fp32 accumulation truncates (measured 1.7e-4; 8e-7 at 96x96 where the partitions coincide)
+    assert record('fast_st_full/dp_identity_rel_l2', rel_l2(0.5 * (g_a + g_b), g_all)) < 1e-3
     assert rel_l2(out_a, out_all[:8]) < 1e-6
 
 
