@@ -37,3 +37,44 @@ def test_gatys_st_cli_writes_a_picture(tmp_path, monkeypatch):
     finally:
         if os.path.exists(out):
             os.unlink(out)
+
+
+def test_fast_st_convert_image_cli_uses_a_saved_checkpoint(tmp_path):
+    """clis/fast_st.py:45-64 -> ImageTransformNet.process_image (network.py:798-832): a state dict saved the way
+    static_train saves it (network.py:767-770, reference key names) is found by the 'latest weights' rule, loaded,
+    and the stylised picture equals the module's own forward on the loaded image."""
+    from click.testing import CliRunner
+    from PIL import Image
+    from oracle import oracle
+    from stransfer.clis import cli
+    from styletransfer_b200 import constants, img_utils, network
+    style_name = f'pyteststyle{os.getpid()}'
+    models = os.path.join(constants.PROJECT_ROOT_PATH, 'data', 'models')
+    os.makedirs(models, exist_ok=True)
+    ckpt = os.path.join(models, f'fast_st_{style_name}_epoch0.pth')
+    params = oracle.make_transform_params(8, 3)
+    torch.save({k: v.clone() for k, v in params.items()}, ckpt)
+    picture = tmp_path / 'photo.png'
+    Image.fromarray(np.random.default_rng(1).integers(0, 255, (260, 300, 3), dtype=np.uint8)).save(picture)
+    out_dir = os.path.join('results', f'pytest_{os.getpid()}') + '/'
+    out_file = os.path.join(constants.PROJECT_ROOT_PATH, out_dir, f'converted_fast_st_{style_name}.png')
+    try:
+        res = CliRunner().invoke(cli, ['fast_st', 'convert-image', str(picture), style_name, '-o', out_dir], catch_exceptions=False)
+        assert res.exit_code == 0, res.output
+        got = np.asarray(Image.open(out_file)).astype(np.int32)
+        x = img_utils.image_loader(str(picture))
+        net = network.ImageTransformNet(torch.zeros(1, 3, 8, 8, device='cuda')).cuda()
+        net.load_state_dict({k: v.clone() for k, v in params.items()})
+        with torch.no_grad():
+            want = net(x)
+        ref_path = tmp_path / 'want.png'
+        img_utils.imshow(want, path=str(ref_path))
+        assert got.shape == (constants.IMSIZE, constants.IMSIZE, 3)
+        assert np.abs(got - np.asarray(Image.open(ref_path)).astype(np.int32)).max() == 0
+    finally:
+        for f in (ckpt, out_file):
+            if os.path.exists(f):
+                os.unlink(f)
+        d = os.path.join(constants.PROJECT_ROOT_PATH, out_dir)
+        if os.path.isdir(d) and not os.listdir(d):
+            os.rmdir(d)

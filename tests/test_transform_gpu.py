@@ -438,3 +438,50 @@ def test_video_full_size_properties(network):
     t = float(net.get_temporal_loss(prev, prev, frame, out1, temporal_weight=0.8))
     assert abs((l1 - l0) - t) < max(1e-3 * abs(t), 4e-6 * abs(l1))        # the totals are fp32 sums of four terms
     assert float(net.get_temporal_loss(prev, out1, frame, out1, temporal_weight=0.8)) == 0.0
+
+
+def test_video_train_loop_matches_manual_recurrence(network):
+    """VideoTransformNet.video_train (network.py:905-1069) on a synthetic loader of two clips: the loop's fixed
+    buffers / replayed closure / clip restart reproduce a hand-written eager recurrence with the same optimizer."""
+    style = seeded((1, 3, 32, 32), 71).cuda()
+    params = oracle.make_transform_params(8, 6)
+    clips = []
+    for c in range(2):
+        frames = [seeded((2, 3, 32, 48), 170 + 10 * c)]
+        for t in range(1, 3):
+            frames.append(frames[-1] + 0.05 * seeded((2, 3, 32, 48), 170 + 10 * c + t))
+        clips.append(frames)
+    import styletransfer_b200.network as nw
+    orig = nw.load_vgg19_prefix_weights
+    nw.load_vgg19_prefix_weights = lambda seed=None: _vgg_cuda()
+    try:
+        net = _build(network, network.VideoTransformNet, params, style, 2)
+        net.video_train('unit', epochs=1, video_loader=clips, max_iterations=6)
+        # manual: eager closure on fresh tensors, new clip -> previous frame is the frame itself
+        ref = _build(network, network.VideoTransformNet, params, style, 2)
+        loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda())
+        loss_net.compute_feature_loss = False
+        opt = ref.get_optimizer()
+        for frames in clips:
+            old = None
+            for b in frames:
+                b = b.cuda()
+                if old is None:
+                    old = [b, b]
+                frozen = [old[0], old[1]]
+
+                def closure():
+                    loss_net._content_key = None
+                    opt.bucket.rebind(); opt.bucket.zero()
+                    st = [frozen[0], frozen[1]]
+                    total, _ = ref.closure_loss_video(b, st, loss_net, 0.8)
+                    old[0], old[1] = st
+                    total.backward()
+                    return total
+                opt.step(closure)
+    finally:
+        nw.load_vgg19_prefix_weights = orig
+    a, b_ = net.state_dict(), ref.state_dict()
+    worst = max(float((a[k] - b_[k]).abs().max()) for k in a)
+    assert record('video_train/param_max_abs_diff_vs_manual', worst) < 1e-6
+    assert any(float((a[k].cpu() - params[k]).abs().max()) > 1e-4 for k in a)      # it did train
