@@ -78,3 +78,38 @@ def test_fast_st_convert_image_cli_uses_a_saved_checkpoint(tmp_path):
         d = os.path.join(constants.PROJECT_ROOT_PATH, out_dir)
         if os.path.isdir(d) and not os.listdir(d):
             os.rmdir(d)
+
+
+def test_process_video_recurrence_from_a_checkpoint(tmp_path):
+    """VideoTransformNet.process_video (network.py:1071-1158) on an iterable of frames: loads the latest
+    video_st checkpoint, feeds frame_t ++ stylised_{t-1} (the first frame with itself) and writes one PNG per
+    frame; the outputs equal a hand-written recurrence on the same weights."""
+    from oracle import oracle
+    from styletransfer_b200 import constants, network
+    style_name = f'pytestvideo{os.getpid()}'
+    models = os.path.join(constants.PROJECT_ROOT_PATH, 'data', 'models')
+    os.makedirs(models, exist_ok=True)
+    ckpt = os.path.join(models, f'video_st_{style_name}_epoch3.pth')
+    params = oracle.make_transform_params(8, 6)
+    torch.save({k: v.clone() for k, v in params.items()}, ckpt)
+    gen = torch.Generator().manual_seed(3)
+    frames = [torch.randn(1, 3, 32, 48, generator=gen) for _ in range(3)]
+    work = str(tmp_path / 'work') + '/'
+    try:
+        net = network.VideoTransformNet(torch.zeros(1, 3, 8, 8, device='cuda')).cuda()
+        outs = net.process_video('unused.mp4', style_name=style_name, working_dir=work, out_dir=str(tmp_path / 'out'),
+                                 frames=[f.clone() for f in frames])
+        assert sorted(os.listdir(work), key=lambda x: int(x.split('.')[0])) == ['0.png', '1.png', '2.png']
+        ref = network.VideoTransformNet(torch.zeros(1, 3, 8, 8, device='cuda')).cuda()
+        ref.load_state_dict({k: v.clone() for k, v in params.items()})
+        old = None
+        with torch.no_grad():
+            for f, got in zip(frames, outs):
+                f = f.cuda()
+                old = f if old is None else old
+                want = ref(torch.cat([f, old], dim=1))
+                assert torch.equal(want, got)
+                old = want
+    finally:
+        if os.path.exists(ckpt):
+            os.unlink(ckpt)
