@@ -127,6 +127,13 @@ int st_relu_maxpool2x2_fwd(const void* x_hi, const void* x_lo, void* y_hi, void*
 int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                            const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int x_planes,
                            int N, int H, int W, int C, void* stream);
+/* The same pair with the routing decision saved by the forward: arg [N][H/2][W/2][C] bytes = position 0..3 of the
+ * first maximum of relu(x) in the window, 4 = nothing routed (relu'(x) = 0).  The backward reads 1 byte per pooled
+ * element instead of every plane of the full-resolution tap. */
+int st_relu_maxpool2x2_fwd_idx(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, unsigned char* arg, int planes,
+                               int N, int H, int W, int C, void* stream);
+int st_relu_maxpool2x2_bwd_idx(const unsigned char* arg, const void* gy_hi, const void* gy_lo, const void* add_hi,
+                               const void* add_lo, void* gx_hi, void* gx_lo, int N, int H, int W, int C, void* stream);
 
 /* ---- losses ------------------------------------------------------------ */
 /* StyleLoss.gram_matrix (network.py:92-108): G[b] = F_b^T F_b / (C*H*W), fp32 [B][C][C] */

@@ -43,6 +43,8 @@ int ew_nhwc_to_nchw(const bf16*, const bf16*, int, float*, int, int, int, int, i
 int ew_pack_weight(const float*, bf16*, bf16*, int, int, int, int, int, int, int, cudaStream_t);
 int ew_relu_maxpool_fwd(const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
 int ew_relu_maxpool_bwd(const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_fwd_idx(const bf16*, const bf16*, bf16*, bf16*, unsigned char*, int, int, int, int, int, cudaStream_t);
+int ew_relu_maxpool_bwd_idx(const unsigned char*, const bf16*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, int, int, int, int, cudaStream_t);
 int ew_mse_fwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, int, float*, float*, cudaStream_t);
 int ew_mse_bwd(const bf16*, const bf16*, const bf16*, const bf16*, size_t, int, float, const float*, const float*, int, bf16*, bf16*, cudaStream_t);
 int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, cudaStream_t);
@@ -215,6 +217,17 @@ int st_relu_maxpool2x2_bwd(const void* x_hi, const void* x_lo, const void* gy_hi
                            const void* add_hi, const void* add_lo, void* gx_hi, void* gx_lo, int x_planes, int N, int H, int W, int C, void* stream) {
     ST_CHECK_ARG(x_hi && gy_hi && gx_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_bwd: null pointer or C %% 8 != 0");
     return ew_relu_maxpool_bwd(CBF(x_hi), CBF(x_lo), CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), x_lo ? x_planes : 1, N, H, W, C, STRM(stream));
+}
+
+int st_relu_maxpool2x2_fwd_idx(const void* x_hi, const void* x_lo, void* y_hi, void* y_lo, unsigned char* arg, int planes,
+                               int N, int H, int W, int C, void* stream) {
+    ST_CHECK_ARG(x_hi && y_hi && arg && C % 8 == 0 && N > 0 && H >= 2 && W >= 2, "st_relu_maxpool2x2_fwd_idx: null pointer, C %% 8 != 0 or H/W < 2");
+    return ew_relu_maxpool_fwd_idx(CBF(x_hi), CBF(x_lo), BF(y_hi), BF(y_lo), arg, x_lo ? planes : 1, N, H, W, C, STRM(stream));
+}
+int st_relu_maxpool2x2_bwd_idx(const unsigned char* arg, const void* gy_hi, const void* gy_lo, const void* add_hi, const void* add_lo,
+                               void* gx_hi, void* gx_lo, int N, int H, int W, int C, void* stream) {
+    ST_CHECK_ARG(arg && gy_hi && gx_hi && C % 8 == 0 && N > 0, "st_relu_maxpool2x2_bwd_idx: null pointer or C %% 8 != 0");
+    return ew_relu_maxpool_bwd_idx(arg, CBF(gy_hi), CBF(gy_lo), CBF(add_hi), CBF(add_lo), BF(gx_hi), BF(gx_lo), N, H, W, C, STRM(stream));
 }
 
 size_t st_gram_workspace_bytes(int B, int HW, int C) {

@@ -150,6 +150,72 @@ __global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16*
     }
 }
 
+// ---- the same pair with the routing decision saved by the forward: arg[n][oh][ow][c] (one byte) = position
+// 0..3 of the first maximum of relu(x) in the 2x2 window, or 4 when relu'(x) = 0 there.  The backward then reads
+// 1 byte per pooled element instead of all planes of the full-resolution tap (100 MB -> 4 MB at 512x512x64).
+__global__ void relu_maxpool_fwd_idx_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+                                            bf16* __restrict__ yh, bf16* __restrict__ yl, unsigned char* __restrict__ arg,
+                                            int N, int H, int W, int C, int planes) {
+    const int Ho = H / 2, Wo = W / 2, Cv = C / 8;
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
+    size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wo; q /= Wo; const int oh = q % Ho; const int n = q / Ho;
+    float x[4][8];
+#pragma unroll
+    for (int d = 0; d < 4; ++d)
+        load8p(xh, xl, planes, ((static_cast<size_t>(n) * H + oh * 2 + (d >> 1)) * W + ow * 2 + (d & 1)) * C + cv * 8, x[d]);
+    float m[8]; uint32_t a_lo = 0, a_hi = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float best = -1.f, bx = 0.f; uint32_t a = 4;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) { const float v = fmaxf(x[d][i], 0.f); if (v > best) { best = v; a = d; bx = x[d][i]; } }
+        if (!(bx > 0.f)) a = 4;                              // relu'(x) = 0: nothing is routed
+        m[i] = best;
+        if (i < 4) a_lo |= a << (8 * i); else a_hi |= a << (8 * (i - 4));
+    }
+    const size_t o = ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8;
+    store8p(yh, yl, planes, o, m);
+    *reinterpret_cast<uint2*>(arg + o) = make_uint2(a_lo, a_hi);
+}
+__global__ void relu_maxpool_bwd_idx_kernel(const unsigned char* __restrict__ arg,
+                                            const bf16* __restrict__ gyh, const bf16* __restrict__ gyl,
+                                            const bf16* __restrict__ addh, const bf16* __restrict__ addl,
+                                            bf16* __restrict__ gxh, bf16* __restrict__ gxl, int N, int H, int W, int C) {
+    const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, Cv = C / 8;
+    const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
+    size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wc; q /= Wc; const int oh = q % Hc; const int n = q / Hc;
+    const bool pooled = oh < Ho && ow < Wo;
+    float g[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = 0.f;
+    uint2 a = make_uint2(0x04040404u, 0x04040404u);
+    if (pooled) {
+        const size_t o = ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8;
+        load8(gyh, gyl, o, g);
+        a = *reinterpret_cast<const uint2*>(arg + o);
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        const int h = oh * 2 + (d >> 1), w = ow * 2 + (d & 1);
+        if (h >= H || w >= W) continue;
+        const size_t off = ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8;
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t ai = ((i < 4 ? a.x : a.y) >> (8 * (i & 3))) & 0xffu;
+            o[i] = (ai == static_cast<uint32_t>(d)) ? g[i] : 0.f;
+        }
+        if (addh) {
+            float ad[8]; load8(addh, addl, off, ad);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] += ad[i];
+        }
+        store8(gxh, gxl, off, o);
+    }
+}
+
 // ---------------------------------------------------------------------------
 // MSE forward: partial[b] = sum over this block's slice of (f(x) - f(t))^2,
 // f = identity or relu (FeatureReconstructionLoss sits on ReLU_4, network.py:230-232)
@@ -317,6 +383,18 @@ int ew_relu_maxpool_fwd(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, int 
     if (n == 0) return ST_OK;
     relu_maxpool_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, N, H, W, C, planes);
     ST_CHECK_LAUNCH("relu_maxpool_fwd_kernel"); return ST_OK;
+}
+int ew_relu_maxpool_fwd_idx(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, unsigned char* arg, int planes, int N, int H, int W,
+                            int C, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * (H / 2) * (W / 2) * (C / 8);
+    relu_maxpool_fwd_idx_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, arg, N, H, W, C, planes);
+    ST_CHECK_LAUNCH("relu_maxpool_fwd_idx_kernel"); return ST_OK;
+}
+int ew_relu_maxpool_bwd_idx(const unsigned char* arg, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
+                            bf16* gxh, bf16* gxl, int N, int H, int W, int C, cudaStream_t st) {
+    const size_t n = static_cast<size_t>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
+    relu_maxpool_bwd_idx_kernel<<<(n + 255) / 256, 256, 0, st>>>(arg, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C);
+    ST_CHECK_LAUNCH("relu_maxpool_bwd_idx_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_bwd(const bf16* xh, const bf16* xl, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
                         bf16* gxh, bf16* gxl, int x_planes, int N, int H, int W, int C, cudaStream_t st) {

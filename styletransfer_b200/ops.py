@@ -265,14 +265,25 @@ def conv2d_wgrad(dy, x, ks, stride, pad, up, cout, cin, want_bias=True, dw_out=N
     return dw, db
 
 
-def relu_maxpool_fwd(x):
+def relu_maxpool_fwd(x, want_idx=False):
+    """want_idx: also return the byte map of routing decisions (which of the 4 window positions receives the
+    gradient, 4 = none) that relu_maxpool_bwd(idx=...) consumes instead of re-reading x."""
     y = Split(x.N, x.H // 2, x.W // 2, x.C, x.buf.device, planes=x.planes)
+    if want_idx:
+        idx = torch.empty((x.N, x.H // 2, x.W // 2, x.C), dtype=torch.uint8, device=x.buf.device)
+        _lib.check(_lib.lib().st_relu_maxpool2x2_fwd_idx(x.hi, x.lo, y.hi, y.lo, idx.data_ptr(), x.planes, x.N, x.H, x.W, x.C,
+                                                         _stream()), 'st_relu_maxpool2x2_fwd_idx')
+        return y, idx
     _lib.check(_lib.lib().st_relu_maxpool2x2_fwd(x.hi, x.lo, y.hi, y.lo, x.planes, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_fwd')
     return y
 
 
-def relu_maxpool_bwd(x, gy, add=None):
+def relu_maxpool_bwd(x, gy, add=None, idx=None):
     gx = x.grad_like()
+    if idx is not None:
+        _lib.check(_lib.lib().st_relu_maxpool2x2_bwd_idx(idx.data_ptr(), gy.hi, gy.lo, add.hi if add else None, add.lo if add else None,
+                                                         gx.hi, gx.lo, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_bwd_idx')
+        return gx
     _lib.check(_lib.lib().st_relu_maxpool2x2_bwd(x.hi, x.lo, gy.hi, gy.lo, add.hi if add else None, add.lo if add else None,
                                                  gx.hi, gx.lo, x.planes, x.N, x.H, x.W, x.C, _stream()), 'st_relu_maxpool2x2_bwd')
     return gx

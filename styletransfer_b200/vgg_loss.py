@@ -59,11 +59,13 @@ class VGGPrefix:
                 self.bwd.append(ops.PackedWeight(w, 2, rows_pad=w.shape[1]))
             self.bias.append(b.detach().contiguous().float())
 
-    def taps(self, x, upto=5, keep_all=True, on_tap=None):
+    def taps(self, x, upto=5, keep_all=True, on_tap=None, pool_idx=None):
         """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto.  keep_all=False:
         only the last tap is wanted (content targets); layers whose ReLU copy feeds the next conv then
         skip the store of their pre-ReLU tap (None in the returned list).  ``on_tap(i, tap)`` is called as
-        soon as tap i has been launched (the loss branch of the tap can then run beside the next layer)."""
+        soon as tap i has been launched (the loss branch of the tap can then run beside the next layer).
+        ``pool_idx`` (dict): filled with {tap index: routing byte map of the relu+maxpool that follows it}, which
+        the backward uses instead of re-reading the full-resolution tap."""
         h = None
         taps = []
         for i in range(upto):
@@ -81,7 +83,10 @@ class VGGPrefix:
                 on_tap(i, tap)
             if last:
                 break
-            h = ops.relu_maxpool_fwd(tap) if pool_next else relu
+            if pool_next and pool_idx is not None:
+                h, pool_idx[i] = ops.relu_maxpool_fwd(tap, want_idx=True)
+            else:
+                h = ops.relu_maxpool_fwd(tap) if pool_next else relu
         return taps
 
 
@@ -114,11 +119,12 @@ class _VGGLossFn(torch.autograd.Function):
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 branch(i, tap)
-        taps = net.taps(x, on_tap=on_tap)
+        pool_idx = {} if ctx.needs_input_grad[0] else None       # routing maps of the two max-pools, for the backward
+        taps = net.taps(x, on_tap=on_tap, pool_idx=pool_idx)
         if side is not None:
             cur.wait_stream(side)
         feat_mse = feat[0]
-        ctx.net, ctx.taps, ctx.diffs = net, taps, diffs
+        ctx.net, ctx.taps, ctx.diffs, ctx.pool_idx = net, taps, diffs, pool_idx or {}
         ctx.content_target, ctx.feat_mse = content_target, feat_mse
         ctx.in_shape = x.shape
         return losses
@@ -143,10 +149,10 @@ class _VGGLossFn(torch.autograd.Function):
                         relu=True, mul=ctx.feat_mse)
         g5 = style_grad(4)
         gp2, _, _ = ops.conv2d(g5, net.bwd[4])                                   # -> grad of pool2 output
-        g4 = ops.relu_maxpool_bwd(t4, gp2, add=style_grad(3, add=cgrad))         # -> grad of tap4
+        g4 = ops.relu_maxpool_bwd(t4, gp2, add=style_grad(3, add=cgrad), idx=ctx.pool_idx.get(3))   # -> grad of tap4
         g3, _, _ = ops.conv2d(g4, net.bwd[3], mask=taps[2], add=style_grad(2))   # relu'(tap3) fused
         gp1, _, _ = ops.conv2d(g3, net.bwd[2])
-        g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1))
+        g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1), idx=ctx.pool_idx.get(1))
         g1, _, _ = ops.conv2d(g2, net.bwd[1], mask=taps[0], add=style_grad(0))
         if IMAGE_GRAD_TC:
             _, _, gx = ops.conv2d(g1, net.bwd[0], want_out=False, out_nchw_channels=3)

@@ -226,6 +226,17 @@ def test_relu_maxpool(ops, H, W):
     add = seeded((2, 64, H, W), 23, device='cuda')
     gx = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=ops.from_nchw(add))
     assert rel_l2(nhwc(gx), x.grad + add) < 1e-5
+    # the variant whose forward saves the routing decision (1 byte per pooled element) and whose backward does not
+    # read x again: bit-identical outputs, odd borders included; ties (relu'(x) = 0 windows) route nothing
+    ys2, idx = ops.relu_maxpool_fwd(xs, want_idx=True)
+    assert torch.equal(ys2.buf, ys.buf) and idx.shape == (2, H // 2, W // 2, 64) and int(idx.max()) <= 4
+    for a in (ops.from_nchw(add), None):
+        g_ref = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=a)
+        g_idx = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=a, idx=idx)
+        assert torch.equal(g_idx.buf, g_ref.buf)
+    neg = ops.from_nchw(-x.detach().abs())
+    _, idx_neg = ops.relu_maxpool_fwd(neg, want_idx=True)
+    assert int(idx_neg.min()) == 4
 
 
 @pytest.mark.parametrize('B,C,H,W', [(1, 64, 32, 32), (2, 128, 20, 12), (3, 256, 9, 7), (1, 64, 128, 128)])
