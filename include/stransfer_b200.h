@@ -138,6 +138,8 @@ int st_relu_maxpool2x2_bwd_idx(const unsigned char* arg, const void* gy_hi, cons
 /* ---- losses ------------------------------------------------------------ */
 /* StyleLoss.gram_matrix (network.py:92-108): G[b] = F_b^T F_b / (C*H*W), fp32 [B][C][C] */
 size_t st_gram_workspace_bytes(int B, int HW, int C);
+/* tuning hook: cap on the pixel split-K of the Gram kernel (0 = automatic); returns the old value */
+int st_set_gram_max_splits(int max_splits);
 int st_gram_fwd(const void* f_hi, const void* f_lo, int B, int HW, int C, float* G,
                 void* workspace, size_t workspace_bytes, void* stream);
 /* StyleLoss.forward (network.py:110-123): loss = mean((G - T)^2), T [C][C] broadcast;

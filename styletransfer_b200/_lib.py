@@ -47,6 +47,7 @@ SIGNATURES = {
     'st_relu_maxpool2x2_fwd_idx': (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_relu_maxpool2x2_bwd_idx': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     'st_gram_workspace_bytes': (_Z, [_I, _I, _I]),
+    'st_set_gram_max_splits': (_I, [_I]),
     'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _P, _P, _Z, _P]),
     'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P]),
     'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),

@@ -21,6 +21,9 @@
 #include "ptx.cuh"
 #include "tmap.cuh"
 
+static int g_gram_max_splits = 0;     // 0: automatic (see plan_gram); > 0: tuning override (st_set_gram_max_splits)
+extern "C" int st_set_gram_max_splits(int v) { const int old = g_gram_max_splits; g_gram_max_splits = v; return old; }
+
 namespace {
 
 constexpr int TILE_H = 8, TILE_W = 16, TILE_PIX = 128;
@@ -414,6 +417,10 @@ GramPlan plan_gram(int B, int HW, int C) {
     const int tp = C > 128 ? 64 : 128;
     q.tiles = (HW + tp - 1) / tp;
     int splits = st_num_sms() / B; if (splits < 1) splits = 1; if (splits > q.tiles) splits = q.tiles;
+    // Tuning override only.  Measured (tools/bench_gram.py, profiles/r01n_gram_split_sweep.txt): capping the split
+    // to cut the C x C partial traffic (39 MB at C = 256) makes every tap SLOWER -- the kernel is bound by the
+    // per-CTA tile loop (MMA issue + TMEM epilogue), not by the partials -- so the automatic plan uses every SM.
+    if (g_gram_max_splits > 0 && splits > g_gram_max_splits) splits = g_gram_max_splits;
     q.tiles_per_split = (q.tiles + splits - 1) / splits;
     q.splits = (q.tiles + q.tiles_per_split - 1) / q.tiles_per_split;
     q.grid = B * q.splits; q.nacc = C > 128 ? C / 128 : 1;
