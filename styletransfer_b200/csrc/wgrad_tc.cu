@@ -411,6 +411,31 @@ gram_tc_finish_kernel(const float* __restrict__ partial, int splits, int nacc, i
     }
 }
 
+// the same sum for a SMALL split count (batched training: 148 / B splits per image): one thread per 4 adjacent
+// outputs walks the splits itself -- the 8-lane layout above would leave most lanes of its 32768 blocks idle
+__global__ void __launch_bounds__(256)
+gram_tc_finish_small_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, float* __restrict__ Gm, int total4) {
+    const int v = blockIdx.x * 256 + threadIdx.x;
+    if (v >= total4) return;
+    int q = v * 4; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+    const size_t per = static_cast<size_t>(nacc) * 128 * C;
+    const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    int sp = 0;
+    for (; sp + 1 < splits; sp += 2) {
+        const float4 x0 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per);
+        const float4 x1 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp + 1) * per);
+        a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+        a1.x += x1.x; a1.y += x1.y; a1.z += x1.z; a1.w += x1.w;
+    }
+    if (sp < splits) {
+        const float4 x0 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per);
+        a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+    }
+    *reinterpret_cast<float4*>(Gm + static_cast<size_t>(v) * 4) =
+        make_float4((a0.x + a1.x) * scale, (a0.y + a1.y) * scale, (a0.z + a1.z) * scale, (a0.w + a1.w) * scale);
+}
+
 struct GramPlan { int tiles, splits, tiles_per_split, grid, nacc; };
 GramPlan plan_gram(int B, int HW, int C) {
     GramPlan q;
@@ -492,8 +517,13 @@ int gram_tc_run(const bf16* f_hi, int B, int HW, int C, float scale, float* Gm, 
     else rc = launch_gram<256>(tf, p, q.grid, stream);
     if (rc) return rc;
     const int total = B * C * C;
-    gram_tc_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total);
-    ST_CHECK_LAUNCH("gram_tc_finish_kernel");
+    if (q.splits <= 16) {
+        gram_tc_finish_small_kernel<<<(total / 4 + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total / 4);
+        ST_CHECK_LAUNCH("gram_tc_finish_small_kernel");
+    } else {
+        gram_tc_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total);
+        ST_CHECK_LAUNCH("gram_tc_finish_kernel");
+    }
     return ST_OK;
 }
 

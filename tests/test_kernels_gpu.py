@@ -239,7 +239,7 @@ def test_relu_maxpool(ops, H, W):
     assert int(idx_neg.min()) == 4
 
 
-@pytest.mark.parametrize('B,C,H,W', [(1, 64, 32, 32), (2, 128, 20, 12), (3, 256, 9, 7), (1, 64, 128, 128)])
+@pytest.mark.parametrize('B,C,H,W', [(1, 64, 32, 32), (2, 128, 20, 12), (3, 256, 9, 7), (1, 64, 128, 128), (16, 256, 32, 32), (16, 64, 64, 64)])
 def test_gram_and_style_loss(ops, B, C, H, W):
     f = seeded((B, C, H, W), 31, device='cuda').requires_grad_(True)
     T = seeded((1, C, C), 32, 0.01, device='cuda')
