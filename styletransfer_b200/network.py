@@ -387,8 +387,11 @@ class StyleNetwork(nn.Module):
         def body():
             input_image.grad = None
             self(input_image, content_image)
-            total_loss = (self._loss_vector * weights).sum()
-            total_loss.backward()
+            # total = <losses, weights> as one dot product; the weights go into the backward as the gradient of
+            # the loss vector itself (no mul / sum nodes for autograd to walk back through)
+            losses = self._loss_vector
+            total_loss = torch.dot(losses.detach(), weights)
+            torch.autograd.backward(losses, grad_tensors=weights)
             return total_loss
         if graph is None:
             graph = cuda_graphs_enabled()
