@@ -149,13 +149,74 @@ def video_case(ref, name, b, s, sw=100_000.0, cw=1.0, tw=0.8):
                         **summarize_grads(rgrads))
 
 
+# L-BFGS fixtures: BASELINE configs[0] size.  On seeded noise with the CLI's default weights the first gradient is
+# already below torch's tolerance_grad (1e-7) at 256x256 and L-BFGS returns without moving; the loop is exercised
+# with both weights x 1e5 (what bench.py's gatys_lbfgs_loop does too), where curvature pairs are stored.
+LBFGS_SIZE, LBFGS_STEPS, LBFGS_SW, LBFGS_CW = 256, 100, 1e10, 1e5
+
+
+def lbfgs_inputs():
+    s = LBFGS_SIZE
+    return seeded((1, 3, s, s), 80), seeded((1, 3, s, s), 81)
+
+
+def psnr(a, b):
+    mse = float(((a.double() - b.double()) ** 2).mean())
+    peak = float(b.max() - b.min())
+    return 10 * np.log10(peak * peak / max(mse, 1e-30))
+
+
+def lbfgs_oracle_case(name='gatys_lbfgs_256_oracle'):
+    """100 steps of torch.optim.LBFGS (defaults, as train_gatys network.py:435-456) on the ORACLE closure."""
+    vw = oracle.make_vgg_weights(1)
+    content, style = lbfgs_inputs()
+    targets = oracle.style_targets(style, vw)
+    x = content.clone().requires_grad_(True)
+    opt = torch.optim.LBFGS([x])
+    n = [0]
+
+    def closure():
+        opt.zero_grad()
+        losses, _ = oracle.loss_network(x, content, targets, vw)
+        total = LBFGS_SW * losses[:5].sum() + LBFGS_CW * losses[5]
+        total.backward()
+        n[0] += 1
+        return total
+    for _ in range(LBFGS_STEPS):
+        last = opt.step(closure)
+    st = opt.state[opt._params[0]]
+    print(name, 'closures', n[0], 'pairs', len(st.get('old_dirs', [])), 'last loss', float(last.detach()))
+    np.savez_compressed(os.path.join(GOLDEN, name + '.npz'), s=LBFGS_SIZE, steps=LBFGS_STEPS, sw=LBFGS_SW, cw=LBFGS_CW,
+                        out=x.detach().numpy(), closures=n[0], pairs=len(st.get('old_dirs', [])),
+                        last_loss=np.float64(float(last.detach())))
+    return x.detach()
+
+
+def lbfgs_reference_case(ref, name='gatys_lbfgs_256_reference'):
+    """The reference's own train_gatys (network.py:411-458) for 100 steps: as-executed (7+2 prefix passes per closure)."""
+    content, style = lbfgs_inputs()
+    net = ref.StyleNetwork(style, content)
+    out = net.train_gatys(style, content, steps=LBFGS_STEPS, style_weight=LBFGS_SW, content_weight=LBFGS_CW).detach()
+    np.savez_compressed(os.path.join(GOLDEN, name + '.npz'), s=LBFGS_SIZE, steps=LBFGS_STEPS, sw=LBFGS_SW, cw=LBFGS_CW,
+                        out=out.numpy())
+    return out
+
+
 def main():
     assert reference_shim.available(), 'needs /root/reference'
     os.makedirs(GOLDEN, exist_ok=True)
     torch.manual_seed(0)
     ref = reference_shim.load_reference(vgg_seed=1)
+    if '--lbfgs' in sys.argv:
+        # slow (minutes for the oracle, tens of minutes for the as-executed reference): run on demand
+        o = lbfgs_oracle_case()
+        if '--lbfgs-reference' in sys.argv:
+            r = lbfgs_reference_case(ref)
+            print('PSNR oracle vs reference after %d L-BFGS steps: %.1f dB' % (LBFGS_STEPS, psnr(o, r)))
+        return
     gatys_case(ref, 'gatys_64x64', 64, 64)
     gatys_case(ref, 'gatys_40x56', 40, 56)       # ragged: not a multiple of the 8x16 tile
+    gatys_case(ref, 'gatys_256x256', 256, 256)   # BASELINE configs[0] size, from the live reference
     fast_case(ref, 'fast_st_b2_32', 2, 32)
     video_case(ref, 'video_st_b2_32', 2, 32)
     print('golden fixtures written to', GOLDEN)

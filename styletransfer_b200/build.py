@@ -1,7 +1,14 @@
 """Build libstransfer_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
 
     python -m styletransfer_b200.build [--force] [--verbose]
+
+Every ``csrc/*.cu`` is compiled to its own object (in parallel, cached under ``build/`` by a digest
+of the source, the headers and the flags) and the objects are linked into one shared library.
+``--use_fast_math`` is a PER-FILE choice: only the tensor-core convolution kernels (whose epilogues are
+adds, compares and bf16/fp16 conversions) get it; the normalisation / loss / optimizer files are
+compiled with IEEE division and square root.
 """
+import concurrent.futures
 import hashlib
 import os
 import shutil
@@ -13,9 +20,17 @@ CSRC = os.path.join(HERE, 'csrc')
 INCLUDE = os.path.join(os.path.dirname(HERE), 'include')
 LIB = os.path.join(HERE, 'libstransfer_b200.so')
 STAMP = os.path.join(HERE, '.build_stamp')
-SOURCES = ['api.cu', 'conv_tc.cu', 'conv_tcx.cu', 'conv_generic.cu', 'conv_image.cu', 'conv9.cu', 'conv9_tc.cu', 'contract.cu', 'wgrad_tc.cu', 'elementwise.cu', 'norm_losses.cu', 'optim.cu']
+OBJ_DIR = os.path.join(HERE, 'build')
+# source -> extra flags
+FAST = ['--use_fast_math']
+SOURCES = {
+    'api.cu': [], 'conv_tc.cu': FAST, 'conv_tcx.cu': FAST, 'conv_generic.cu': FAST, 'conv_image.cu': FAST,
+    'conv9.cu': FAST, 'conv9_tc.cu': FAST, 'contract.cu': FAST, 'wgrad_tc.cu': FAST,
+    'elementwise.cu': [], 'norm_losses.cu': [], 'optim.cu': [],
+}
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
-              '--use_fast_math', '-Xcompiler', '-fPIC', '-Xptxas', '-v', '-shared', '-cudart', 'shared']
+              '-Xcompiler', '-fPIC', '-Xptxas', '-v']
+LINK_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-cudart', 'shared']
 
 
 def _nvcc():
@@ -25,15 +40,33 @@ def _nvcc():
     raise RuntimeError('nvcc not found')
 
 
-def _digest():
+def _headers_digest():
     h = hashlib.sha256()
-    files = sorted(os.listdir(CSRC)) + [os.path.join(INCLUDE, 'stransfer_b200.h')]
-    for name in files:
-        path = name if os.path.isabs(name) else os.path.join(CSRC, name)
+    files = [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n.endswith(('.cuh', '.h'))]
+    files.append(os.path.join(INCLUDE, 'stransfer_b200.h'))
+    for path in files:
         with open(path, 'rb') as f:
-            h.update(os.path.basename(name).encode())      # never the absolute path: the tree is copied to other roots
+            h.update(os.path.basename(path).encode())      # never the absolute path: the tree is copied to other roots
             h.update(f.read())
-    h.update(' '.join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
+def _source_digest(name, hdr):
+    h = hashlib.sha256()
+    with open(os.path.join(CSRC, name), 'rb') as f:
+        h.update(name.encode())
+        h.update(f.read())
+    h.update(hdr.encode())
+    h.update(' '.join(NVCC_FLAGS + SOURCES[name]).encode())
+    return h.hexdigest()
+
+
+def _digest():
+    hdr = _headers_digest()
+    h = hashlib.sha256()
+    for name in sorted(SOURCES):
+        h.update(_source_digest(name, hdr).encode())
+    h.update(' '.join(LINK_FLAGS).encode())
     return h.hexdigest()
 
 
@@ -42,6 +75,21 @@ def up_to_date():
         return False
     with open(STAMP) as f:
         return f.read().strip() == _digest()
+
+
+def _compile_one(nvcc, name, digest, force):
+    obj = os.path.join(OBJ_DIR, name + '.o')
+    tag = obj + '.digest'
+    if not force and os.path.exists(obj) and os.path.exists(tag):
+        with open(tag) as f:
+            if f.read().strip() == digest:
+                return name, 0, '(cached)\n'
+    cmd = [nvcc] + NVCC_FLAGS + SOURCES[name] + ['-I', INCLUDE, '-c', '-o', obj, os.path.join(CSRC, name)]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode == 0:
+        with open(tag, 'w') as f:
+            f.write(digest)
+    return name, res.returncode, ' '.join(cmd) + '\n' + res.stdout + res.stderr
 
 
 def build(force=False, verbose=False):
@@ -54,16 +102,31 @@ def build(force=False, verbose=False):
         try:
             if not force and up_to_date():
                 return LIB
+            nvcc = _nvcc()
+            os.makedirs(OBJ_DIR, exist_ok=True)
+            hdr = _headers_digest()
+            logs, failed = [], []
+            with concurrent.futures.ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as pool:
+                jobs = [pool.submit(_compile_one, nvcc, n, _source_digest(n, hdr), force) for n in sorted(SOURCES)]
+                for j in jobs:
+                    name, rc, log = j.result()
+                    logs.append(f'==== {name}\n{log}')
+                    if rc != 0:
+                        failed.append(name)
             tmp = LIB + f'.tmp{os.getpid()}'
-            cmd = [_nvcc()] + NVCC_FLAGS + ['-I', INCLUDE, '-o', tmp] + [os.path.join(CSRC, s) for s in SOURCES]
-            res = subprocess.run(cmd, capture_output=True, text=True)
-            log = res.stdout + res.stderr
+            if not failed:
+                cmd = [nvcc] + LINK_FLAGS + ['-o', tmp] + [os.path.join(OBJ_DIR, n + '.o') for n in sorted(SOURCES)]
+                res = subprocess.run(cmd, capture_output=True, text=True)
+                logs.append('==== link\n' + ' '.join(cmd) + '\n' + res.stdout + res.stderr)
+                if res.returncode != 0:
+                    failed.append('link')
+            log = '\n'.join(logs)
             with open(os.path.join(HERE, 'build.log'), 'w') as f:
-                f.write(' '.join(cmd) + '\n' + log)
-            if res.returncode != 0:
+                f.write(log)
+            if failed:
                 if os.path.exists(tmp):
                     os.unlink(tmp)
-                raise RuntimeError('nvcc failed:\n' + log[-6000:])
+                raise RuntimeError(f'nvcc failed ({failed}):\n' + log[-8000:])
             if verbose:
                 print(log)
             os.replace(tmp, LIB)

@@ -15,7 +15,16 @@ LOG_PATH = os.path.join(RUNS_PATH, 'runtime.log')
 IMAGENET_MEAN = [0.485, 0.456, 0.406]
 IMAGENET_STD = [0.229, 0.224, 0.225]
 
-DEVICE = torch.device("cuda" if torch.cuda.is_available() else "cpu")
+def _device():
+    """Under torchrun every rank owns the GPU named by LOCAL_RANK (a bare ``cuda`` device would put all the
+    ranks of ``torchrun -m stransfer fast_st train ...`` on cuda:0)."""
+    if not torch.cuda.is_available():
+        return torch.device('cpu')
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    return torch.device('cuda', local if local < torch.cuda.device_count() else 0)
+
+
+DEVICE = _device()
 
 IMSIZE = int(os.environ.get('STRANSFER_IMSIZE', 256))
 

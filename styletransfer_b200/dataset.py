@@ -65,9 +65,11 @@ class SyntheticImages(Dataset):
         return torch.randn(1, 3, self.size, self.size, generator=g)
 
 
-def get_coco_loader(batch_size=4, test_split=0.10, test_limit=None, train_limit=None, synthetic=None):
+def get_coco_loader(batch_size=4, test_split=0.10, test_limit=None, train_limit=None, synthetic=None, seed=0):
     """dataset.py:314-360 -> (test_loader, train_loader), batches [B, 1, 3, S, S].
-    ``synthetic`` = number of seeded random images to use when no image folder exists."""
+    ``synthetic`` = number of seeded random images to use when no image folder exists.  The shuffle is seeded
+    (``seed``): under data parallelism every rank draws the SAME permutation, so that ``dist.shard`` cuts disjoint
+    slices of one global batch."""
     if os.path.isdir(IMAGE_FOLDER_PATH) and synthetic is None:
         all_images = sorted(os.listdir(IMAGE_FOLDER_PATH))
         split_idx = int(len(all_images) * test_split)
@@ -80,8 +82,9 @@ def get_coco_loader(batch_size=4, test_split=0.10, test_limit=None, train_limit=
         test_dataset, train_dataset = SyntheticImages(n_test, seed=1), SyntheticImages(min(train_limit or n, n), seed=2)
     LOGGER.info('Train set has %d entries', len(train_dataset))
     LOGGER.info('Test set has %d entries', len(test_dataset))
-    mk = lambda ds: DataLoader(ds, batch_size=batch_size, num_workers=0, drop_last=True, shuffle=True)
-    return mk(test_dataset), mk(train_dataset)
+    mk = lambda ds, k: DataLoader(ds, batch_size=batch_size, num_workers=0, drop_last=True, shuffle=True,
+                                  generator=torch.Generator().manual_seed(seed * 2 + k))
+    return mk(test_dataset, 0), mk(train_dataset, 1)
 
 
 class FrameFolderReader:

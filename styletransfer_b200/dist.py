@@ -27,14 +27,29 @@ def env_rank_world():
 
 def init(backend=None, device=None):
     """Initialise torch.distributed from the torchrun environment (no-op for one process)."""
-    rank, world, _ = env_rank_world()
+    rank, world, local = env_rank_world()
     if world > 1 and not dist.is_initialized():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         os.environ.setdefault('MASTER_PORT', '29500')
         backend = backend or ('nccl' if torch.cuda.is_available() else 'gloo')
-        kw = {'device_id': device} if (backend == 'nccl' and device is not None) else {}
+        kw = {}
+        if backend == 'nccl':
+            # one GPU per rank: bind it BEFORE the process group exists (NCCL otherwise sees every rank on cuda:0)
+            if device is None:
+                device = torch.device('cuda', local % max(torch.cuda.device_count(), 1))
+            torch.cuda.set_device(device)
+            kw = {'device_id': device}
         dist.init_process_group(backend, rank=rank, world_size=world, **kw)
     return rank, world
+
+
+def rank():
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def barrier():
+    if dist.is_initialized():
+        dist.barrier()
 
 
 def world_size():

@@ -26,14 +26,16 @@ LOGGER = c_logging.get_logger()
 def get_tensorboard_writer(path: str):
     """network.py:25-35 -- tensorboardX is replaced by torch.utils.tensorboard when
     available, else by a no-op writer (observability sidecar, out of scope)."""
+    class _Null:
+        def add_scalar(self, *a, **k): pass
+        def add_image(self, *a, **k): pass
+    if path is None:                                      # ranks other than 0 of a data-parallel run
+        return _Null()
     shutil.rmtree(path, ignore_errors=True)
     try:
         from torch.utils.tensorboard import SummaryWriter
         return SummaryWriter(path)
     except Exception:                                     # pragma: no cover
-        class _Null:
-            def add_scalar(self, *a, **k): pass
-            def add_image(self, *a, **k): pass
         return _Null()
 
 
@@ -80,6 +82,9 @@ class GraphedClosure:
         with torch.cuda.graph(self.graph, stream=side):
             self.out = fn()
         self.launches = int(lib().st_launch_count() - n0)     # kernels of ours per replay
+        # the scratch buffers the captured kernels were given are baked into the graph as raw addresses: keep them
+        # alive even when a later, larger request replaces them in the grow-only cache (ops.workspace)
+        self._workspaces = list(ops._ws_cache.values())
         self.leaves = [(leaf, leaf.grad) for leaf in leaves]   # gradient buffers inside the graph's pool
 
     def __call__(self):
@@ -219,20 +224,24 @@ _VGG_CONV_IDX = [0, 2, 5, 7, 10]
 def load_vgg19_prefix_weights(seed=None):
     """[(weight, bias)] x5 for conv1_1, conv1_2, conv2_1, conv2_2, conv3_1 on DEVICE.
 
-    The reference uses ``torchvision.models.vgg19(pretrained=True)`` (network.py:246).
-    With ``seed`` given, or when the pretrained checkpoint cannot be obtained
-    (offline), a seeded random-init VGG-19 (torchvision's kaiming-normal fan_out
-    init) is used instead and a warning is logged."""
+    The reference uses ``torchvision.models.vgg19(pretrained=True)`` (network.py:246) and fails when the
+    checkpoint cannot be obtained; so does this function (``StransferError``).  A seeded random-init VGG-19
+    (torchvision's kaiming-normal fan_out init) is an explicit opt-in only: the ``seed`` argument, or the
+    ``STRANSFER_VGG_SEED`` environment variable (tests, benchmarks and offline smoke runs)."""
     import math
+    if seed is None and os.environ.get('STRANSFER_VGG_SEED'):
+        seed = int(os.environ['STRANSFER_VGG_SEED'])
+        LOGGER.warning('STRANSFER_VGG_SEED=%d: the loss network is a seeded RANDOM-INIT VGG-19, not the pretrained one', seed)
     if seed is None:
         try:
             import torchvision
             feats = torchvision.models.vgg19(weights='IMAGENET1K_V1').features
-            return [(feats[i].weight.detach().to(constants.DEVICE), feats[i].bias.detach().to(constants.DEVICE))
-                    for i in _VGG_CONV_IDX]
         except Exception as exc:                       # no network / no torchvision
-            LOGGER.warning('pretrained VGG-19 unavailable (%s); using seeded random init', type(exc).__name__)
-            seed = 1
+            raise StransferError('the pretrained VGG-19 weights could not be loaded (%s: %s); pass vgg_weights= / seed=, '
+                                 'or set STRANSFER_VGG_SEED to opt in to a seeded random-init loss network'
+                                 % (type(exc).__name__, exc)) from exc
+        return [(feats[i].weight.detach().to(constants.DEVICE), feats[i].bias.detach().to(constants.DEVICE))
+                for i in _VGG_CONV_IDX]
     g = torch.Generator().manual_seed(seed)
     out = []
     for cin, cout, _ in vgg_loss.PREFIX:
@@ -345,15 +354,17 @@ class StyleNetwork(nn.Module):
         return weight * torch.stack([x[0].loss for x in self.style_losses]).sum()
 
     def _set_content(self, content_image):
-        # the reference recomputes the content/feature targets on every call
-        # (network.py:378-382); identical tensors (same storage, same version) are cached
-        key = (content_image.data_ptr(), content_image._version, tuple(content_image.shape))
-        if key != self._content_key:
+        """The reference recomputes the content / feature targets on every call (network.py:378-382).  The targets
+        of THE SAME tensor object at the same autograd version are reused (the Gatys loop passes one fixed content
+        image to every closure); the cache holds a strong reference to that tensor, so its storage cannot be
+        recycled for another image while the key is alive, and the loops that feed new batches reset it."""
+        key = self._content_key
+        if key is None or key[0] is not content_image or key[1] != content_image._version:
             with torch.no_grad():
                 tap = self.vgg.taps(content_image.detach(), upto=4, keep_all=False)[3]
             self.content_losses[0][0].set_target(tap)
             self.feature_losses[0][0].set_target(self._relu_split(tap) if self.compute_feature_loss else tap)
-            self._content_key = key
+            self._content_key = (content_image, content_image._version)
 
     def forward(self, input_image: torch.Tensor, content_image=None, style_image=None) -> None:
         """network.py:366-401: evaluates every loss node; results live in ``node.loss``."""
@@ -422,6 +433,7 @@ class StyleNetwork(nn.Module):
         # start from the content image (network.py:429); a loader's permuted HWC->CHW view becomes a dense NCHW tensor
         input_image = content_image.detach().clone(memory_format=torch.contiguous_format).float()
         optimizer = self.get_content_optimizer(input_image, optt=optim.LBFGS)
+        self._content_key = None                    # targets of THIS content image, whatever was cached before
         self.compute_feature_loss = False           # never read by this loop
         n_closure = [0]
         evaluate = self.gatys_closure(input_image, content_image, style_weight, content_weight)
@@ -760,7 +772,9 @@ class ImageTransformNet(nn.Sequential):
         """network.py:651-770.  ``train_loader`` / ``test_loader`` (extra, optional) replace the
         COCO loaders -- the dataset download is host glue outside the hot path."""
         from . import dataset
-        tb_writer = get_tensorboard_writer(f'runs/fast-image-style-transfer-still-image_{style_name}')
+        # rank 0 alone owns the log directory, the test-loss log and the checkpoints (every rank holds the same weights)
+        rank0 = st_dist.rank() == 0
+        tb_writer = get_tensorboard_writer(f'runs/fast-image-style-transfer-still-image_{style_name}' if rank0 else None)
         loss_network = StyleNetwork(self.style_image, torch.rand([1, 3, 256, 256]).to(constants.DEVICE))
         loss_network.compute_feature_loss = False        # the training closure never reads it
         optimizer = self.get_optimizer(optimizer=optim.Adam)
@@ -797,15 +811,17 @@ class ImageTransformNet(nn.Sequential):
                     total_loss = closure()
                     tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
                     LOGGER.info('Batch Loss: %.8f', total_loss)
-                if iteration % 150 == 0 and test_loader is not None:
+                if iteration % 150 == 0 and test_loader is not None and rank0:
                     average_test_loss = self.static_test(test_loader, loss_network)
                     tb_writer.add_scalar('data/fst_test_loss', average_test_loss, iteration)
                 iteration += 1
                 optimizer.step(closure)
                 if max_iterations is not None and iteration >= max_iterations:
                     return
-            os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
-            torch.save(self.state_dict(), epoch_checkpoint_name)
+            if rank0:
+                os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
+                torch.save(self.state_dict(), epoch_checkpoint_name)
+            st_dist.barrier()
 
     def static_test(self, test_loader, loss_network, style_weight=100_000, feature_weight=1):
         """network.py:772-796"""
@@ -815,6 +831,7 @@ class ImageTransformNet(nn.Sequential):
         with torch.no_grad():
             for test_batch in test_loader:
                 test_batch = test_batch.squeeze(1).to(constants.DEVICE)
+                loss_network._content_key = None     # every test batch sets its own targets (network.py:786)
                 transformed_image = torch.clamp(self(test_batch), min=0, max=255)
                 loss_network(transformed_image, content_image=test_batch)
                 style_loss = style_weight * loss_network.get_total_current_style_loss()
@@ -944,7 +961,8 @@ class VideoTransformNet(ImageTransformNet):
         """network.py:905-1069.  ``video_loader`` (extra, optional): an iterable of clips, each an
         iterable of frame batches [B,3,H,W] (replaces VideoDataset + iterate_on_video_batches)."""
         from . import dataset
-        tb_writer = get_tensorboard_writer(f'runs/video-style-transfer_{style_name}')
+        rank0 = st_dist.rank() == 0
+        tb_writer = get_tensorboard_writer(f'runs/video-style-transfer_{style_name}' if rank0 else None)
         style_loss_network = StyleNetwork(self.style_image, torch.rand([1, 3, 256, 256]).to(constants.DEVICE))
         style_loss_network.compute_feature_loss = False
         optimizer = self.get_optimizer(optimizer=optim.Adam)
@@ -1005,8 +1023,10 @@ class VideoTransformNet(ImageTransformNet):
                     bufs[2].copy_(bufs[3])
                     if max_iterations is not None and iteration >= max_iterations:
                         return
-            os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
-            torch.save(self.state_dict(), epoch_checkpoint_name)
+            if rank0:
+                os.makedirs(os.path.dirname(epoch_checkpoint_name), exist_ok=True)
+                torch.save(self.state_dict(), epoch_checkpoint_name)
+            st_dist.barrier()
 
     def process_video(self, video_path: str, style_name='nsp', working_dir='workdir/', out_dir='results/',
                       fps=24.0, frames=None):

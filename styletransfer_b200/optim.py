@@ -168,7 +168,7 @@ class DeviceLBFGS(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
             if first_loss is None:
-                first_loss = loss
+                first_loss = loss.detach().clone()       # torch returns orig_loss; a graphed closure reuses the buffer
             grad = self.p.grad
             if grad is None or not grad.is_contiguous() or grad.dtype != torch.float32:
                 raise _lib.StransferError('DeviceLBFGS: the closure must leave a contiguous fp32 .grad on the image')

@@ -1,0 +1,176 @@
+"""Parity against the CPU oracle AT THE SIZES BASELINE.json QUOTES THE METRIC ON:
+Gatys closure at 256x256 (configs[0]) and 512x512 (configs[1]), the fast_st training closure at batch 16 of
+256x256 (configs[2]), the video closure at 512x512 with the temporal term (configs[4]) and the 100-step
+L-BFGS loop at 256x256 against a committed fixture (oracle/make_golden.py --lbfgs).
+
+North-star tolerances: per-layer features and Gram matrices <= 1e-2 relative L2; total loss
+and input gradient <= 1e-3 relative; PSNR >= 40 dB after 100 L-BFGS steps.  Parameter gradients of the transform-net
+CHAIN stay at the 3e-2 bound argued in tests/test_transform_gpu.py; the measured worst is recorded
+(gpurun_out/parity.jsonl -> profiles/*_parity_margins.jsonl)."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle
+from oracle.make_golden import grads_err
+from tests.util import nhwc, record, rel_l2, seeded
+
+pytestmark = pytest.mark.gpu
+TOL_FEATURE, TOL_LOSS_GRAD, TOL_CHAIN_GRAD = 1e-2, 1e-3, 3e-2
+
+
+@pytest.fixture(scope='module')
+def network():
+    from styletransfer_b200 import network
+    return network
+
+
+def _vgg_cuda():
+    return [(w.cuda(), b.cuda()) for w, b in oracle.make_vgg_weights(1)]
+
+
+def _build(network, cls, params, style, b):
+    net = cls(style, b).cuda()
+    net.load_state_dict({k: v.clone() for k, v in params.items()})
+    return net
+
+
+@pytest.mark.parametrize('s', [256, 512])
+def test_gatys_closure_matches_oracle_at_baseline_size(network, s):
+    """network.py:438-454 at the configs[0] / configs[1] image size: five taps, five Grams, per-node losses, total
+    and the gradient of the image."""
+    from styletransfer_b200 import ops, vgg_loss
+    vw = oracle.make_vgg_weights(1)
+    content, style = seeded((1, 3, s, s), 10), seeded((1, 3, s, s), 11)
+    x0 = content + 0.3 * seeded((1, 3, s, s), 12)
+    targets = oracle.style_targets(style, vw)
+    o_total, o_grad, o_losses = oracle.gatys_closure(x0, content, targets, vw)
+    taps_ref = oracle.vgg_taps(x0, vw)
+    prefix = vgg_loss.VGGPrefix(_vgg_cuda())
+    for i, (t, r) in enumerate(zip(prefix.taps(x0.cuda()), taps_ref)):
+        assert record(f'gatys{s}/tap{i + 1}_rel_l2', rel_l2(nhwc(t), r)) < TOL_FEATURE
+        assert record(f'gatys{s}/gram{i + 1}_rel_l2', rel_l2(ops.gram(t), oracle.gram_matrix(r))) < TOL_FEATURE
+    del taps_ref
+    net = network.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
+    for (node, _), ref in zip(net.style_losses, targets):
+        assert rel_l2(node.target, ref) < TOL_FEATURE
+    x = x0.cuda().requires_grad_(True)
+    net(x, content.cuda())
+    total = net.get_total_current_style_loss(weight=1e5) + net.get_total_current_content_loss(weight=1)
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
+    assert record(f'gatys{s}/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(f'gatys{s}/losses_rel_l2', rel_l2(per_node, o_losses)) < TOL_LOSS_GRAD
+    assert record(f'gatys{s}/grad_rel_l2', rel_l2(x.grad, o_grad)) < TOL_LOSS_GRAD
+    # the graph-replayed closure train_gatys runs is the same arithmetic
+    xg = x0.cuda().requires_grad_(True)
+    net.compute_feature_loss = False
+    closure = net.gatys_closure(xg, content.cuda(), 1e5, 1)
+    loss = closure()
+    assert record(f'gatys{s}/graph_total_rel', abs(float(loss) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(f'gatys{s}/graph_grad_rel_l2', rel_l2(xg.grad, o_grad)) < TOL_LOSS_GRAD
+
+
+def test_gatys_closure_matches_reference_golden_256(network, golden_dir):
+    """Fixture written by the UNMODIFIED reference at 256x256 (oracle/make_golden.py gatys_case)."""
+    g = np.load(os.path.join(golden_dir, 'gatys_256x256.npz'))
+    h, w = int(g['h']), int(g['w'])
+    content, style = seeded((1, 3, h, w), 10, device='cuda'), seeded((1, 3, h, w), 11, device='cuda')
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12, device='cuda')
+    net = network.StyleNetwork(style, content, vgg_weights=_vgg_cuda())
+    x = x0.clone().requires_grad_(True)
+    net(x, content)
+    total = net.get_total_current_style_loss(weight=float(g['sw'])) + net.get_total_current_content_loss(weight=float(g['cw']))
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
+    assert record('gatys_golden256/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
+    assert rel_l2(per_node, torch.from_numpy(g['losses'])) < TOL_LOSS_GRAD
+    assert record('gatys_golden256/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
+
+
+def test_fast_st_closure_matches_oracle_at_baseline_size(network):
+    """network.py:690-731 at configs[2]: batch 16 of 256x256, every parameter-gradient tensor in full."""
+    b, s = 16, 256
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(2, 3)
+    style, batch = seeded((1, 3, s, s), 201), seeded((b, 3, s, s), 202)
+    o_total, o_grads, o_out, o_losses = oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw)
+    net = _build(network, network.ImageTransformNet, params, style.cuda(), b)
+    loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, s, s]).cuda(), vgg_weights=_vgg_cuda())
+    total, out = net.closure_loss(batch.cuda(), loss_net)
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in loss_net.style_losses + loss_net.content_losses]).detach()
+    assert record('fast_st_16x256/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
+    assert record('fast_st_16x256/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record('fast_st_16x256/losses_rel_l2', rel_l2(per_node, o_losses[:6])) < TOL_LOSS_GRAD
+    got = {k: p.grad.detach().cpu() for k, p in net.named_parameters()}
+    assert record('fast_st_16x256/grads_worst', grads_err(got, o_grads)) < TOL_CHAIN_GRAD
+    flat = lambda d: torch.cat([d[k].reshape(-1) for k in sorted(d)])
+    record('fast_st_16x256/grads_flat_rel_l2', rel_l2(flat(got), flat(o_grads)))
+
+
+@pytest.mark.parametrize('clips', [1, 2])
+def test_video_closure_matches_oracle_at_baseline_size(network, clips):
+    """network.py:984-1037 at the configs[4] frame size (512x512, 6-channel input), temporal term included."""
+    s = 512
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(3, 6)
+    style, batch = seeded((1, 3, 256, 256), 31), seeded((clips, 3, s, s), 32)
+    old_content = batch + 0.05 * seeded((clips, 3, s, s), 33)
+    old_stylized = seeded((clips, 3, s, s), 34)
+    o_total, o_grads, o_out, _ = oracle.video_closure(batch, old_content, old_stylized, params,
+                                                      oracle.style_targets(style, vw), vw)
+    o_temporal = oracle.temporal_loss(old_content, old_stylized, batch, o_out, 0.8)
+    net = _build(network, network.VideoTransformNet, params, style.cuda(), clips)
+    loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, 256, 256]).cuda(), vgg_weights=_vgg_cuda())
+    state = [old_content.cuda(), old_stylized.cuda()]
+    total, out = net.closure_loss_video(batch.cuda(), state, loss_net, 0.8)
+    total.backward()
+    tag = f'video_{clips}x512'
+    assert record(tag + '/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
+    assert record(tag + '/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    t = net.get_temporal_loss(old_content.cuda(), old_stylized.cuda(), batch.cuda(), out.detach(), temporal_weight=0.8)
+    assert record(tag + '/temporal_rel', abs(float(t) - float(o_temporal)) / abs(float(o_temporal))) < TOL_LOSS_GRAD
+    got = {k: p.grad.detach().cpu() for k, p in net.named_parameters()}
+    assert record(tag + '/grads_worst', grads_err(got, o_grads)) < TOL_CHAIN_GRAD
+
+
+def _psnr(a, b):
+    mse = float(((a.double() - b.double()) ** 2).mean())
+    peak = float(b.max() - b.min())
+    return 10 * math.log10(peak * peak / max(mse, 1e-30))
+
+
+def test_lbfgs_100_steps_psnr_256(network, golden_dir):
+    """train_gatys (network.py:411-458) for 100 L-BFGS steps at 256x256 (BASELINE configs[0] size) against the
+    committed output of torch.optim.LBFGS on the CPU oracle closure (and, when present, of the reference's own
+    train_gatys); the history must actually hold curvature pairs (the two-loop recursion is exercised)."""
+    from oracle.make_golden import LBFGS_CW, LBFGS_SW, lbfgs_inputs
+    g = np.load(os.path.join(golden_dir, 'gatys_lbfgs_256_oracle.npz'))
+    assert int(g['pairs']) > 0
+    content, style = lbfgs_inputs()
+    net = network.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
+    made = []
+    orig = net.get_content_optimizer
+
+    def spy(*a, **k):
+        made.append(orig(*a, **k))
+        return made[-1]
+    net.get_content_optimizer = spy
+    out = net.train_gatys(style.cuda(), content.cuda(), steps=int(g['steps']), style_weight=LBFGS_SW, content_weight=LBFGS_CW)
+    info = made[0].info()
+    record('lbfgs100_256/pairs', info['k'])
+    assert info['k'] > 0, info
+    ref = torch.from_numpy(g['out'])
+    moved = _psnr(content, ref)
+    record('lbfgs100_256/psnr_of_unoptimised_image_db', moved)
+    psnr = record('lbfgs100_256/psnr_vs_oracle_db', _psnr(out.detach().cpu(), ref))
+    assert psnr >= 40.0 and psnr > moved + 10.0, (psnr, moved)
+    path = os.path.join(golden_dir, 'gatys_lbfgs_256_reference.npz')
+    if os.path.exists(path):
+        r = torch.from_numpy(np.load(path)['out'])
+        record('lbfgs100_256/psnr_oracle_vs_reference_db', _psnr(ref, r))
+        assert record('lbfgs100_256/psnr_vs_reference_db', _psnr(out.detach().cpu(), r)) >= 40.0
