@@ -416,6 +416,8 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group('nccl', device_id=dev)
     from styletransfer_b200 import _lib, network, ops
     L = _lib.lib()
+    if args.precision is None:
+        args.precision = ops.PRECISION
     ops.set_precision(args.precision)
 
     # one independent content/style pair per rank (BASELINE configs[1]: no communication)
@@ -521,7 +523,7 @@ def run_ours(args, rank, world, local_rank):
     fl3 = sum(g[0] for k, g in groups.items() if '<3x3>' in k)
     ms3 = sum(g[1] for k, g in groups.items() if '<3x3>' in k)
     n3 = sum(g[2] for k, g in groups.items() if '<3x3>' in k)
-    passes = {'bf16x6': 4.5, 'bf16x3': 3, 'bf16': 1}[args.precision]   # fwd 6 / bwd 3 passes in bf16x6
+    passes = {'f16x3': 3, 'bf16x6': 4.5, 'bf16x3': 3, 'bf16': 1}[args.precision]   # fwd 6 / bwd 3 passes in bf16x6
     achieved = fl3 / (ms3 * 1e-3) / 1e12 if ms3 > 0 else 0.0
     traffic, traffic_src = ncu_dram_traffic_per_launch()
     roofline = {'bound': 'tensor', 'kernel': 'conv_tc_kernel<3x3> (9 launches per closure: 4 fwd + 5 dgrad)',
@@ -563,6 +565,7 @@ def run_ours(args, rank, world, local_rank):
             'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms / args.steps,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': {'bf16x6': 'bf16x6 (split-bf16 operands: forward 3 planes / 6 tcgen05 passes, backward 2 planes / 3 passes, fp32 accumulate)',
+                      'f16x3': 'f16x3 (forward: 2 fp16 planes / 3 passes; backward: 2 planes / 3 passes)',
                       'bf16x3': 'bf16x3 (2 planes / 3 passes)', 'bf16': 'bf16'}[args.precision],
             'data': 'synthetic',
             'config': {'workload': 'gatys_st 512x512 single pair per GPU, closure fwd+bwd (BASELINE configs[1])',
@@ -666,7 +669,8 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--precision', default='bf16x6', choices=['bf16x6', 'bf16x3', 'bf16'])
+    ap.add_argument('--precision', default=None, choices=['f16x3', 'bf16x6', 'bf16x3', 'bf16'],
+                    help='default: styletransfer_b200.ops.PRECISION')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='launch the closure eagerly instead of replaying a CUDA graph')
     ap.add_argument('--no-secondary', action='store_true', help='skip the video_st / convert-image / L-BFGS loop metrics')

@@ -14,13 +14,26 @@
  *    size the matching *_workspace_bytes() query returns.
  *  - every launch is stream-ordered on `stream` (a cudaStream_t); no hidden
  *    synchronisation, so the calls can be captured in a CUDA graph.
- *  - activations use the "split-bf16 NHWC" format: channels-last, two bf16
- *    planes hi = bf16(x), lo = bf16(x - hi).  A NULL lo plane selects plain
- *    bf16 (1 tensor-core pass per product instead of 3).  Where a `planes`
- *    argument is 3 a THIRD plane bf16(x - hi - lo) lives one plane stride after
- *    lo (at lo + (lo - hi)): ~24 mantissa bits, 6 tensor-core passes per
- *    product.  Forward activations need it: ReLU masks / max-pool argmaxes flip
- *    on 1e-5 errors and each flip costs a whole gradient entry.
+ *  - activations use the "split 16-bit NHWC" format: channels-last, two 16-bit
+ *    planes hi = rn16(x), lo = rn16(x - hi).  A NULL lo plane selects a single
+ *    plane (1 tensor-core pass per product instead of 3).  Every `planes`
+ *    argument is a PLANE CODE: bits 0..3 = number of planes, bit 4
+ *    (ST_PLANES_F16) = the planes hold fp16 instead of bf16:
+ *      bf16, 3 planes: a THIRD plane bf16(x - hi - lo) lives one plane stride
+ *        after lo (at lo + (lo - hi)): ~24 mantissa bits, 6 tensor-core passes
+ *        per product;
+ *      fp16, 2 planes: 22 mantissa bits in 3 passes; values saturate at
+ *        +-65504 and keep an absolute precision of 2^-25 below 2^-3.
+ *    Forward activations need > 16 bits: ReLU masks / max-pool argmaxes flip on
+ *    1e-5 errors and each flip costs a whole gradient entry.
+ *    The tensor cores multiply two operands of ONE format (fp16 x bf16 is an
+ *    illegal tcgen05.mma): where the operands of a product differ, the mma.sync
+ *    kernel that converts on load is used instead.
+ *  - a tensor whose values may leave the fp16 range (gradients) is stored
+ *    multiplied by a power of two held in a 2-float device SCALE SLOT
+ *    {s, 1/s}; its producer writes the slot, its consumers take the slot and
+ *    multiply their results by slot[1].  fp16-packed conv weights carry the
+ *    fixed factor 256 (acc_mul = 1/256 at the consumer).
  *    Channel counts are multiples of 8 (images are padded 3/6 -> 8 with zeros).
  *  - scalars that come from autograd (loss weights = grad_output entries) are
  *    passed as device pointers (`gw`) so that no host sync is needed.
@@ -36,6 +49,7 @@ extern "C" {
 #define ST_ERR_INVALID (-1)
 #define ST_ERR_CUDA (-2)
 #define ST_ERR_UNSUPPORTED (-3)
+#define ST_PLANES_F16 16     /* plane-code bit: fp16 planes */
 
 /* build info: compute capability the kernels were compiled for (100) */
 int st_arch(void);
@@ -53,7 +67,8 @@ long long st_launch_count(void);
  * channels, network.py:984-986) -> split-bf16 NHWC with Cpad channels. */
 int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int planes,
                     int N, int C1, int C2, int H, int W, int Cpad, void* stream);
-int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, float* out,
+/* slot (optional): scale slot of the tensor; the values are multiplied by slot[1] */
+int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, const float* slot, float* out,
                     int N, int C, int H, int W, int Cpad, void* stream);
 /* nn.Conv2d.weight [Cout][Cin][ks][ks] fp32 -> packed [rows_pad][ks*ks][cols_pad] split-bf16.
  * mode 0 forward; 1 backward-data (gather form, any stride); 2 backward-data as a
@@ -69,15 +84,19 @@ int st_pack_conv_weight(const float* w, void* hi, void* lo, int planes, int Cout
  * gather (weights packed with mode 1).  w_img_rows != 0 selects per-image weights
  * (rows n*w_img_rows.. of the packed matrix): used for the Gram backward dF = F*D.
  * out_nchw (optional) receives the first Cnchw channels as NCHW fp32.
- * x_planes / w_planes / out_planes: 1..3 (see the conventions above); `add`, `out` and
- * `relu_out` all carry out_planes planes; `mask` is read from its hi plane only. */
+ * x_planes / w_planes / add_planes / out_planes: plane codes (see the conventions above);
+ * `out` and `relu_out` carry out_planes; `mask` is read from its hi plane only (sign test,
+ * either format).  Before the bias the accumulator is multiplied by
+ * acc_mul * (acc_mul_slot ? acc_mul_slot[1] : 1) (1/256 for fp16-packed weights; the scale slot of a
+ * scaled operand); the addend is multiplied by add_mul_slot[1] when that slot is given. */
 int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
               const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows,
               int ks, int stride, int pad, int transposed,
               int Ho, int Wo, int Cout_pad, int Cbias,
-              const float* bias, const void* mask, const void* add_hi, const void* add_lo,
+              const float* bias, const void* mask, const void* add_hi, const void* add_lo, int add_planes,
               void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes,
-              float* out_nchw, int Cnchw, void* stream);
+              float* out_nchw, int Cnchw, float acc_mul, const float* acc_mul_slot, const float* add_mul_slot,
+              void* stream);
 
 /* First VGG layer (torchvision vgg19.features[0], 3 -> Cout channels, 3x3, zero padding 1;
  * run by StyleNetwork.run_through_pieces network.py:316-340) in exact fp32 on the CUDA cores:
@@ -108,14 +127,19 @@ int st_conv9_reduce(const void* x_hi, const void* x_lo, int planes, const float*
                     void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream);
 /* backward-weight (+ bias).  mode 0: layer 0, big = dy, small = the layer's input -> dw [32][CS][9][9], db [32];
  *                            mode 1: layer 22, big = the layer's input, small = dy -> dw [CS][32][9][9], db [CS] */
+/* big_slot (optional): scale slot of the big tensor (a scaled fp16 gradient); small_slot (optional): when the big
+ * tensor has fp16 planes the small fp32 tensor is multiplied by small_slot[0] on its way into fp16 operands
+ * (st_absmax_slot of a gradient image); dw / db come out unscaled. */
 size_t st_conv9_wgrad_workspace_bytes(int CS);
-int st_conv9_wgrad(const void* b_hi, const void* b_lo, int b_planes, const float* s0, const float* s1, int sc, int CS, int mode,
+int st_conv9_wgrad(const void* b_hi, const void* b_lo, int b_planes, const float* big_slot, const float* small_slot,
+                   const float* s0, const float* s1, int sc, int CS, int mode,
                    float* dw, float* db, void* workspace, size_t workspace_bytes, int N, int H, int W, void* stream);
 
-/* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]) */
+/* autograd backward-weight of nn.Conv2d: dw [Cout][Cin][ks][ks] fp32 (+ db [Cout]).  dy_planes / x_planes: plane
+ * codes; dy_slot (optional): scale slot of dy (undone in dw / db). */
 size_t st_conv2d_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cdy, int CinPad, int ks);
-int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int Cdy,
-                    const void* x_hi, const void* x_lo, int N, int H, int W, int CinPad, int up,
+int st_conv2d_wgrad(const void* dy_hi, const void* dy_lo, int dy_planes, const float* dy_slot, int Cdy,
+                    const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int CinPad, int up,
                     int Ho, int Wo, int ks, int stride, int pad, int Cout, int Cin,
                     float* dw, float* db, void* workspace, size_t workspace_bytes, void* stream);
 
@@ -140,21 +164,27 @@ int st_relu_maxpool2x2_bwd_idx(const unsigned char* arg, const void* gy_hi, cons
 size_t st_gram_workspace_bytes(int B, int HW, int C);
 /* tuning hook: cap on the pixel split-K of the Gram kernel (0 = automatic); returns the old value */
 int st_set_gram_max_splits(int max_splits);
-int st_gram_fwd(const void* f_hi, const void* f_lo, int B, int HW, int C, float* G,
+int st_gram_fwd(const void* f_hi, const void* f_lo, int f_planes, int B, int HW, int C, float* G,
                 void* workspace, size_t workspace_bytes, void* stream);
 /* StyleLoss.forward (network.py:110-123): loss = mean((G - T)^2), T [C][C] broadcast;
- * diff = G - T is kept for the backward.  ws: >= 4096 floats */
-int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* ws, void* stream);
-/* backward seed: D = (*gw) * 4/(B*C^2*C*HW) * diff, packed split-bf16 [B*C][C];
- * dF = F * D is then st_conv2d(ks=1, w_img_rows=C). */
-int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* gw, void* d_hi, void* d_lo, void* stream);
+ * diff = G - T is kept for the backward; diff_amax (optional) receives max |diff|.  ws: >= 4096 floats */
+int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* diff_amax,
+                     float* ws, void* stream);
+/* backward seed: D = (*gw) * 4/(B*C^2*C*HW) * diff, packed [B*C][C] with plane code d_planes;
+ * dF = F * D is then st_conv2d(ks=1, w_img_rows=C).  fp16 planes: D is stored multiplied by the power of two
+ * that maps max|D| (from diff_amax) to 2^10 and d_slot receives {s, 1/s} (acc_mul_slot of that conv). */
+int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* gw, void* d_hi, void* d_lo,
+                          int d_planes, const float* diff_amax, float* d_slot, void* stream);
+/* slot = {s, 1/s}, s the power of two that maps max|x| of a flat fp32 array to 2^target_log2 (the scale under which
+ * a gradient image enters fp16 tensor-core operands).  ws: >= 1024 floats */
+int st_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, void* stream);
 /* ContentLoss (network.py:155-164) / FeatureReconstructionLoss (network.py:186-201):
  * relu=1 compares relu(x) with relu(t); feature_form=1 returns mse^2/numel. */
-int st_mse_fwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel,
-               int relu, int feature_form, float* loss, float* ws, void* stream);
-/* g (+)= scale * (*gw) * (mul ? *mul : 1) * (f(x) - f(t)) * f'(x) */
-int st_mse_bwd(const void* x_hi, const void* x_lo, const void* t_hi, const void* t_lo, size_t numel,
-               int relu, float scale, const float* gw, const float* mul, int accumulate,
+int st_mse_fwd(const void* x_hi, const void* x_lo, int x_planes, const void* t_hi, const void* t_lo, int t_planes,
+               size_t numel, int relu, int feature_form, float* loss, float* ws, void* stream);
+/* g (+)= scale * (*gw) * (mul ? *mul : 1) * (f(x) - f(t)) * f'(x); g: two bf16 planes */
+int st_mse_bwd(const void* x_hi, const void* x_lo, int x_planes, const void* t_hi, const void* t_lo, int t_planes,
+               size_t numel, int relu, float scale, const float* gw, const float* mul, int accumulate,
                void* g_hi, void* g_lo, void* stream);
 /* total variation (network.py:621-641) on NCHW fp32; ws >= 2048 floats */
 int st_tv_fwd(const float* x, int N, int C, int H, int W, float factor, float* loss, float* ws, void* stream);
@@ -181,11 +211,14 @@ size_t st_instnorm_workspace_bytes(int N, int C);
 int st_instnorm_fwd(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
                     void* y_hi, void* y_lo, int planes, float* mean, float* rstd,
                     int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
-/* dsum (optional, [C]): sum of dx over images and pixels = bias gradient of the convolution in front */
+/* gy: two bf16 planes.  dsum (optional, [C]): sum of dx over images and pixels = bias gradient of the convolution in
+ * front.  dx_planes: plane code of dx; with fp16 planes dx is stored multiplied by a power of two chosen from a bound
+ * of |dx| that the statistics pass measures, and dx_slot receives {s, 1/s} (dx feeds the backward-data and
+ * backward-weight tensor-core products of the convolution in front). */
 int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const void* gy_lo,
                     const float* mean, const float* rstd, const float* gamma, const float* beta,
-                    void* dx_hi, void* dx_lo, float* dgamma, float* dbeta, float* dsum, int x_planes,
-                    int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
+                    void* dx_hi, void* dx_lo, int dx_planes, float* dx_slot, float* dgamma, float* dbeta, float* dsum,
+                    int x_planes, int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 
 /* ---- optimizer steps on the device ---------- */
 /* torch.optim.Adam.step over every parameter tensor of a transform net in one launch

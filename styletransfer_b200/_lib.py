@@ -23,24 +23,24 @@ SIGNATURES = {
     'st_last_conv_kernel': (_I, []),
     'st_launch_count': (ctypes.c_longlong, []),
     'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
-    'st_nhwc_to_nchw': (_I, [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P]),
+    'st_nhwc_to_nchw': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_pack_conv_weight': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
     'st_conv2d': (_I, [_P, _P, _I, _I, _I, _I, _I, _I,      # x, planes, N H W Cin up
                        _P, _P, _I, _I, _I,                  # w, planes, rows_total, img_rows
                        _I, _I, _I, _I,                      # ks stride pad transposed
                        _I, _I, _I, _I,                      # Ho Wo Cout_pad Cbias
-                       _P, _P, _P, _P,                      # bias mask add_hi add_lo
+                       _P, _P, _P, _P, _I,                  # bias mask add_hi add_lo add_planes
                        _P, _P, _P, _P, _I,                  # out_hi out_lo relu_hi relu_lo out_planes
-                       _P, _I, _P]),                        # out_nchw Cnchw stream
+                       _P, _I, _F, _P, _P, _P]),            # out_nchw Cnchw acc_mul acc_mul_slot add_mul_slot stream
     'st_conv3x3_image_fwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_conv3x3_image_dgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
     'st_conv9_expand': (_I, [_P, _P, _I, _I, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
     'st_conv9_reduce_workspace_bytes': (_Z, [_I, _I, _I]),
     'st_conv9_reduce': (_I, [_P, _P, _I, _P, _P, _P, _P, _Z, _I, _I, _I, _P]),
     'st_conv9_wgrad_workspace_bytes': (_Z, [_I]),
-    'st_conv9_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _P, _Z, _I, _I, _I, _P]),
+    'st_conv9_wgrad': (_I, [_P, _P, _I, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _Z, _I, _I, _I, _P]),
     'st_conv2d_wgrad_workspace_bytes': (_Z, [_I, _I, _I, _I, _I, _I]),
-    'st_conv2d_wgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
+    'st_conv2d_wgrad': (_I, [_P, _P, _I, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I, _I,
                              _P, _P, _P, _Z, _P]),
     'st_relu_maxpool2x2_fwd': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_relu_maxpool2x2_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
@@ -48,11 +48,12 @@ SIGNATURES = {
     'st_relu_maxpool2x2_bwd_idx': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     'st_gram_workspace_bytes': (_Z, [_I, _I, _I]),
     'st_set_gram_max_splits': (_I, [_I]),
-    'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _P, _P, _Z, _P]),
-    'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P]),
-    'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _P]),
-    'st_mse_fwd': (_I, [_P, _P, _P, _P, _Z, _I, _I, _P, _P, _P]),
-    'st_mse_bwd': (_I, [_P, _P, _P, _P, _Z, _I, _F, _P, _P, _I, _P, _P, _P]),
+    'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _Z, _P]),
+    'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P]),
+    'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P]),
+    'st_absmax_slot': (_I, [_P, _Z, _F, _P, _P, _P]),
+    'st_mse_fwd': (_I, [_P, _P, _I, _P, _P, _I, _Z, _I, _I, _P, _P, _P]),
+    'st_mse_bwd': (_I, [_P, _P, _I, _P, _P, _I, _Z, _I, _F, _P, _P, _I, _P, _P, _P]),
     'st_tv_fwd': (_I, [_P, _I, _I, _I, _I, _F, _P, _P, _P]),
     'st_tv_bwd': (_I, [_P, _I, _I, _I, _I, _F, _P, _P, _P]),
     'st_temporal_fwd': (_I, [_P, _P, _P, _P, _Z, _F, _P, _P, _P]),
@@ -68,7 +69,7 @@ SIGNATURES = {
     'st_set_lbfgs_variant': (_I, [_I]),
     'st_lbfgs_init': (_I, [_P, _I, _Z, _D, _D, _D, _P]),
     'st_lbfgs_iteration': (_I, [_P, _P, _P, _P, _P, _P, _P, _Z, _Z, _I, _P, _I, _P]),
-    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_bwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P]),
 }
 
 _lib = None

@@ -27,6 +27,7 @@ struct ContractParams {
     int chunk;        // pixels per split (multiple of TK)
     float* partial;   // [groups*splits][Mrows_pad][Ktot_pad]
     int Mpad, Kpad;
+    int dy_f16, x_f16; // fp16 source planes are re-split into bf16 hi / lo on load
 };
 
 __device__ __forceinline__ void ldm_x4_t(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
@@ -77,6 +78,7 @@ __global__ void __launch_bounds__(128) contract_kernel(const ContractParams p) {
                     const size_t off = static_cast<size_t>(g) * p.Cdy + m0 + vcol;
                     dh = *reinterpret_cast<const uint4*>(p.dy_hi + off);
                     if (d_lo) dl = *reinterpret_cast<const uint4*>(p.dy_lo + off);
+                    if (p.dy_f16) { uint4 d2; f16x8_to_bf16_planes(dh, dl, d2); }
                 }
                 if (kvalid) {
                     int q = g; const int ow = q % p.Wo; q /= p.Wo; const int oh = q % p.Ho; const int n = q / p.Ho;
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(128) contract_kernel(const ContractParams p) {
                         const size_t off = ((static_cast<size_t>(n) * p.H + ih) * p.W + iw) * p.Cin + ci;
                         xh = *reinterpret_cast<const uint4*>(p.x_hi + off);
                         if (x_lo) xl = *reinterpret_cast<const uint4*>(p.x_lo + off);
+                        if (p.x_f16) { uint4 x2; f16x8_to_bf16_planes(xh, xl, x2); }
                     }
                 }
             }
@@ -143,7 +146,7 @@ __global__ void __launch_bounds__(128) contract_kernel(const ContractParams p) {
 
 // dW[co][ci][r][s] (PyTorch layout, fp32) = sum over splits of partial[split][co][tap*CinPad + ci]
 __global__ void wgrad_finish_kernel(const float* partial, int splits, int Mpad, int Kpad,
-                                    int Cout, int Cin, int CinPad, int taps, float* dw) {
+                                    int Cout, int Cin, int CinPad, int taps, const float* dy_slot, float* dw) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = Cout * Cin * taps;
     if (idx >= total) return;
@@ -151,7 +154,7 @@ __global__ void wgrad_finish_kernel(const float* partial, int splits, int Mpad, 
     const size_t off = static_cast<size_t>(co) * Kpad + tap * CinPad + ci;
     float s = 0.f;
     for (int sp = 0; sp < splits; ++sp) s += partial[static_cast<size_t>(sp) * Mpad * Kpad + off];
-    dw[idx] = s;
+    dw[idx] = s * slot_inv(dy_slot);
 }
 
 // G[b][i][j] = scale * sum over splits (one result per image): 32 outputs x 8 split lanes per
@@ -198,13 +201,15 @@ size_t contract_workspace_bytes(int N, int Ho, int Wo, int Cdy, int Ktot, int gr
 }
 
 // mode 0: wgrad -> dw [Cout][Cin][ks][ks];  mode 1: gram -> G [N][C][C] * scale
-int contract_run(const bf16* dy_hi, const bf16* dy_lo, int Cdy,
-                 const bf16* x_hi, const bf16* x_lo, int N, int H, int W, int CinPad, int up,
+// dy_f16 / x_f16: the planes of that tensor are fp16; dy_slot (optional): power-of-two scale slot of dy (mode 0)
+int contract_run(const bf16* dy_hi, const bf16* dy_lo, int Cdy, bool dy_f16, const float* dy_slot,
+                 const bf16* x_hi, const bf16* x_lo, bool x_f16, int N, int H, int W, int CinPad, int up,
                  int Ho, int Wo, int ks, int stride, int pad,
                  int mode, int Cout, int Cin, float scale, float* out,
                  void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     const int groups = mode == 1 ? N : 1;
     ContractParams p;
+    p.dy_f16 = dy_f16; p.x_f16 = x_f16;
     p.dy_hi = dy_hi; p.dy_lo = dy_lo; p.Cdy = Cdy;
     p.x_hi = x_hi; p.x_lo = x_lo; p.H = H; p.W = W; p.Cin = CinPad; p.up = up;
     p.N = N; p.Ho = Ho; p.Wo = Wo; p.ks = ks; p.stride = stride; p.pad = pad;
@@ -222,7 +227,7 @@ int contract_run(const bf16* dy_hi, const bf16* dy_lo, int Cdy,
     ST_CHECK_LAUNCH("contract_kernel");
     if (mode == 0) {
         const int total = Cout * Cin * ks * ks;
-        wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cout, Cin, CinPad, ks * ks, out);
+        wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cout, Cin, CinPad, ks * ks, dy_slot, out);
         ST_CHECK_LAUNCH("wgrad_finish_kernel");
     } else {
         const int total = N * Cdy * Cdy;

@@ -202,13 +202,21 @@ conv9_reduce_kernel(const bf16* __restrict__ x_hi, const bf16* __restrict__ x_lo
 namespace {
 
 // weights [3][32][9][9] fp32 -> split-bf16 [planes][row = co*9 + s (32, 27 used)][tap = r (9)][ci (32)]
-__global__ void conv9_pack_vertical_kernel(const float* __restrict__ w, bf16* __restrict__ hi, int planes) {
+// (plane code with the fp16 bit: fp16 planes of ST_W_F16_SCALE * w)
+__global__ void conv9_pack_vertical_kernel(const float* __restrict__ w, bf16* __restrict__ hi, int code) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = 32 * 9 * CB;
     if (idx >= total) return;
     const int ci = idx % CB; int q = idx / CB; const int r = q % 9; const int row = q / 9;
     float v = 0.f;
     if (row < 27) { const int co = row / 9, s = row % 9; v = w[((co * CB + ci) * 9 + r) * 9 + s]; }
+    const int planes = pc_planes(code);
+    if (pc_f16(code)) {
+        uint32_t h2, l2; split2h(v * ST_W_F16_SCALE, 0.f, h2, l2);
+        reinterpret_cast<uint16_t*>(hi)[idx] = static_cast<uint16_t>(h2 & 0xffffu);
+        if (planes > 1) reinterpret_cast<uint16_t*>(hi)[static_cast<size_t>(total) + idx] = static_cast<uint16_t>(l2 & 0xffffu);
+        return;
+    }
 #pragma unroll 1
     for (int pl = 0; pl < planes; ++pl) {
         const bf16 h = __float2bfloat16_rn(v);
@@ -259,7 +267,8 @@ conv9_gather_kernel(const float* __restrict__ T, const float* __restrict__ bias,
 }  // namespace
 
 int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
-                 const float*, const bf16*, const bf16*, const bf16*, bf16*, bf16*, bf16*, bf16*, int, float*, cudaStream_t);
+                 const float*, const bf16*, const bf16*, const bf16*, int, bf16*, bf16*, bf16*, bf16*, int, float*,
+                 float, const float*, const float*, cudaStream_t);
 
 size_t conv9_reduce_workspace_bytes(int N, int H, int W) {
     return static_cast<size_t>(N) * H * W * CB * sizeof(float) + 3 * 32 * 9 * CB * sizeof(bf16) + 1024;
@@ -272,12 +281,17 @@ int conv9_reduce_tc_run(const bf16* x_hi, const bf16* x_lo, int planes, const fl
     float* T = static_cast<float*>(workspace);
     const size_t t_bytes = (static_cast<size_t>(N) * H * W * CB * sizeof(float) + 1023) / 1024 * 1024;
     bf16* wp = reinterpret_cast<bf16*>(static_cast<uint8_t*>(workspace) + t_bytes);
-    const int wplanes = planes >= 3 ? 3 : (planes == 2 ? 2 : 1);
+    // the weights are packed in the format of the activation planes (a tensor-core product takes one format)
+    const bool f16 = pc_f16(planes);
+    const int np = pc_planes(planes);
+    const int wplanes = np >= 3 ? 3 : (np == 2 ? 2 : 1);
+    const int wcode = wplanes | (f16 ? ST_FMT_F16 : 0);
     const int total = 32 * 9 * CB;
-    conv9_pack_vertical_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, wp, wplanes);
+    conv9_pack_vertical_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, wp, wcode);
     ST_CHECK_LAUNCH("conv9_pack_vertical_kernel");
-    int rc = conv_tcx_run(3, x_hi, x_lo, planes, N, H, W, CB, wp, wplanes > 1 ? wp + total : nullptr, wplanes, 32, 32, H, W,
-                          nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1, T, st);
+    int rc = conv_tcx_run(3, x_hi, x_lo, planes, N, H, W, CB, wp, wplanes > 1 ? wp + total : nullptr, wcode, 32, 32, H, W,
+                          nullptr, nullptr, nullptr, nullptr, 1, nullptr, nullptr, nullptr, nullptr, 1, T,
+                          f16 ? ST_W_F16_INV_SCALE : 1.f, nullptr, nullptr, st);
     if (rc) return rc;
     size_t blocks = (static_cast<size_t>(N) * H * W + GA_PIX - 1) / GA_PIX;
     const size_t cap = static_cast<size_t>(st_num_sms()) * 6;

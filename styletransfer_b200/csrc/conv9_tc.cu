@@ -43,10 +43,30 @@ struct C9Params {
     int N, H, W, wblocks, work;
     float* partial; int part_stride;            // one partial per CTA: [32][cs_total][81]
     int cs_total, c_off;
+    int f16;                                    // the big tensor holds fp16 planes: the builders make fp16 rows too
+    const float* small_slot;                    // optional {s, 1/s}: the small tensor is multiplied by s before the fp16 split
 };
 
+// (operand format bits, ptx::umma_fmt_bits, are OR-ed in at run time)
 __host__ __device__ constexpr uint32_t idesc_k_mn(int M, int N) {     // A K-major, B MN-major
-    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+    return (1u << 4) | (1u << 16) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+// 16 floats -> 16-bit patterns of the hi / lo planes (bf16, or fp16 of mul * v)
+__device__ __forceinline__ void split16(const float (&v)[16], bool f16, float mul, uint32_t (&hi)[16], uint32_t (&lo)[16]) {
+    if (f16) {
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+            uint32_t h2, l2; split2h(v[i] * mul, v[i + 1] * mul, h2, l2);
+            hi[i] = h2 & 0xffffu; hi[i + 1] = h2 >> 16; lo[i] = l2 & 0xffffu; lo[i + 1] = l2 >> 16;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const bf16 h = __float2bfloat16_rn(v[i]);
+            const bf16 l = __float2bfloat16_rn(v[i] - __bfloat162float(h));
+            hi[i] = __bfloat16_as_ushort(h); lo[i] = __bfloat16_as_ushort(l);
+        }
+    }
 }
 __device__ __forceinline__ uint32_t mn_lo(uint32_t addr, uint32_t lbo_bytes) { return ((addr & 0x3ffff) >> 4) | ((lbo_bytes >> 4) << 16); }
 __device__ __forceinline__ void mma2(uint32_t d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t acc) {
@@ -98,6 +118,7 @@ conv9_correlate_tc_kernel(const __grid_constant__ CUtensorMap tmB, const C9Param
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         const bool leader = ptx::elect_one();
+        const uint32_t fmt = ptx::umma_fmt_bits(p.f16 != 0);
         constexpr uint32_t a_hi = ptx::umma_desc_hi_k_sw128();
         constexpr uint32_t b_hi = static_cast<uint32_t>((8 * 64) >> 4) | (1u << 14) | (4u << 29);      // MN-major, 64-byte swizzle
         int st = 0; uint32_t ph = 0;
@@ -114,8 +135,8 @@ conv9_correlate_tc_kernel(const __grid_constant__ CUtensorMap tmB, const C9Param
                     const uint32_t ak = a0 + mb * A_MBLOCK + k * 32;
                     const uint32_t bk = mn_lo(b0 + k * 16 * 64, B_PLANE);
                     if (leader) {
-                        mma2(tmem_base + mb * 64, ptx::umma_desc_lo(ak), a_hi, bk, b_hi, idesc_k_mn(128, 64), k ? 1u : first);
-                        mma2(tmem_base + mb * 64 + 32, ptx::umma_desc_lo(ak + A_PLANE), a_hi, bk, b_hi, idesc_k_mn(128, 32), 1u);
+                        mma2(tmem_base + mb * 64, ptx::umma_desc_lo(ak), a_hi, bk, b_hi, idesc_k_mn(128, 64) | fmt, k ? 1u : first);
+                        mma2(tmem_base + mb * 64 + 32, ptx::umma_desc_lo(ak + A_PLANE), a_hi, bk, b_hi, idesc_k_mn(128, 32) | fmt, 1u);
                     }
                 }
             }
@@ -154,14 +175,9 @@ conv9_correlate_tc_kernel(const __grid_constant__ CUtensorMap tmB, const C9Param
         for (int wk = wk_first; wk < p.work; wk += wk_step) {
             const int nwk = wk + wk_step;
             if (nwk < p.work) fetch(nwk, nxt);
-            // split into bf16 hi / lo (16-bit patterns)
+            // split into hi / lo planes (16-bit patterns) in the format of the big tensor
             uint32_t hi[16], lo[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const bf16 h = __float2bfloat16_rn(cur[i]);
-                const bf16 l = __float2bfloat16_rn(cur[i] - __bfloat162float(h));
-                hi[i] = __bfloat16_as_ushort(h); lo[i] = __bfloat16_as_ushort(l);
-            }
+            split16(cur, p.f16 != 0, p.small_slot ? p.small_slot[0] : 1.f, hi, lo);
             ptx::mbar_wait(&empty[st], ph ^ 1);
             if (active) {
                 uint8_t* A = smem + st * STAGE9;
@@ -252,7 +268,7 @@ template <int CS, int PL> struct X9Cfg {
 };
 
 __host__ __device__ constexpr uint32_t idesc_mn_k(int M, int N) {     // A MN-major, B K-major
-    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+    return (1u << 4) | (1u << 15) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
 template <int CS, int PL>
@@ -268,6 +284,7 @@ conv9_expand_tc_kernel(const X9Params p) {
     uint64_t* a_full = bars; uint64_t* a_empty = a_full + NSTG; uint64_t* t_full = a_empty + NSTG; uint64_t* t_empty = t_full + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool f16 = PL == 2 && pc_f16(p.planes);          // operand format = format of the output planes
 
     if (warp == 0 && lane == 0) {
         for (int i = 0; i < NSTG; ++i) { ptx::mbar_init(&a_full[i], X_BUILD_WARPS); ptx::mbar_init(&a_empty[i], 1); }
@@ -286,6 +303,13 @@ conv9_expand_tc_kernel(const X9Params p) {
             v = p.flip ? p.w[((c * TCB + co) * 9 + (8 - r)) * 9 + (8 - sft)] : p.w[((co * CS + c) * 9 + r) * 9 + sft];
         }
         uint8_t* dst = sB + q * PL * XB_PLANE + co * 128 + (((kk >> 3) ^ (co & 7)) << 4) + (kk & 7) * 2;
+        if (f16) {
+            // fp16 operands (PL = 2): planes of ST_W_F16_SCALE * w; the epilogue multiplies by the inverse
+            uint32_t h2, l2; split2h(v * ST_W_F16_SCALE, 0.f, h2, l2);
+            *reinterpret_cast<uint16_t*>(dst) = static_cast<uint16_t>(h2 & 0xffffu);
+            *reinterpret_cast<uint16_t*>(dst + XB_PLANE) = static_cast<uint16_t>(l2 & 0xffffu);
+            continue;
+        }
         float rem = v;
 #pragma unroll
         for (int pl = 0; pl < PL; ++pl) {
@@ -304,6 +328,7 @@ conv9_expand_tc_kernel(const X9Params p) {
     if (warp == 1) {
         // ===================== MMA issuer =====================
         const bool leader = ptx::elect_one();
+        const uint32_t fmt = ptx::umma_fmt_bits(f16);
         constexpr uint32_t a_hi = static_cast<uint32_t>(1024 >> 4) | (1u << 14) | (2u << 29);      // MN-major SW128: 8 k rows = 1024 B
         constexpr uint32_t b_hi = ptx::umma_desc_hi_k_sw128();
         int st = 0; uint32_t ph = 0; int it = 0;
@@ -325,7 +350,7 @@ conv9_expand_tc_kernel(const X9Params p) {
 #pragma unroll
                         for (int pa = 0; pa < PL; ++pa) {
                             const uint32_t ak = mn_lo(a0 + pa * 2 * XA_GROUP + k * 16 * 128, XA_GROUP);
-                            mma2(d0 + pa * TCB, ak, a_hi, bk, b_hi, idesc_mn_k(128, (PL - pa) * TCB), pa ? 1u : accum);
+                            mma2(d0 + pa * TCB, ak, a_hi, bk, b_hi, idesc_mn_k(128, (PL - pa) * TCB) | fmt, pa ? 1u : accum);
                         }
                     }
                     accum = 1;
@@ -370,14 +395,23 @@ conv9_expand_tc_kernel(const X9Params p) {
             if (i + X_GROUPS < items) fetch_item(i + X_GROUPS, nxt);
             const int st = i % NSTG; const uint32_t ph = (i / NSTG) & 1;
             uint32_t pw[PL][16];
+            if (f16) {
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                float rem = cur[k];
+                for (int k = 0; k < 16; k += 2) {
+                    uint32_t h2, l2; split2h(cur[k], cur[k + 1], h2, l2);
+                    pw[0][k] = h2 & 0xffffu; pw[0][k + 1] = h2 >> 16;
+                    pw[PL - 1][k] = l2 & 0xffffu; pw[PL - 1][k + 1] = l2 >> 16;
+                }
+            } else {
 #pragma unroll
-                for (int pl = 0; pl < PL; ++pl) {
-                    const bf16 h = __float2bfloat16_rn(rem);
-                    pw[pl][k] = __bfloat16_as_ushort(h);
-                    rem -= __bfloat162float(h);
+                for (int k = 0; k < 16; ++k) {
+                    float rem = cur[k];
+#pragma unroll
+                    for (int pl = 0; pl < PL; ++pl) {
+                        const bf16 h = __float2bfloat16_rn(rem);
+                        pw[pl][k] = __bfloat16_as_ushort(h);
+                        rem -= __bfloat162float(h);
+                    }
                 }
             }
             ptx::mbar_wait(&a_empty[st], ph ^ 1);
@@ -429,6 +463,7 @@ conv9_expand_tc_kernel(const X9Params p) {
                         float t = __uint_as_float(d[PL - 1][i]);                  // smallest terms first
 #pragma unroll
                         for (int pl = PL - 2; pl >= 0; --pl) t += __uint_as_float(d[pl][i]);
+                        if (f16) t *= ST_W_F16_INV_SCALE;
                         v[i] = t + (p.bias ? p.bias[hb * 16 + i] : 0.f);
                     }
                     store16p(p.out_hi, p.out_lo, p.planes, o + hb * 16, v);
@@ -468,14 +503,16 @@ int conv9_expand_tc_run(const float* s0, const float* s1, int sc, int CS, const 
     p.s0 = s0; p.s1 = s1; p.sc = sc; p.w = w; p.bias = bias; p.flip = flip;
     p.out_hi = out_hi; p.out_lo = out_lo; p.planes = planes;
     p.N = N; p.H = H; p.W = W; p.wtiles = (W + 127) / 128; p.tiles = N * H * p.wtiles;
-    if (CS == 3) return planes >= 3 ? launch_expand<3, 3>(p, stream) : launch_expand<3, 2>(p, stream);
-    return planes >= 3 ? launch_expand<6, 3>(p, stream) : launch_expand<6, 2>(p, stream);
+    const bool three = pc_planes(planes) >= 3 && !pc_f16(planes);
+    if (CS == 3) return three ? launch_expand<3, 3>(p, stream) : launch_expand<3, 2>(p, stream);
+    return three ? launch_expand<6, 3>(p, stream) : launch_expand<6, 2>(p, stream);
 }
 
 // One 3-channel slice of the small tensor.  Returns the number of partials written (= grid).
-int conv9_correlate_tc_run(const bf16* b_hi, const float* s, int sc, int cs_total, int c_off, float* partial,
-                           int N, int H, int W, int* nparts, cudaStream_t stream) {
+int conv9_correlate_tc_run(const bf16* b_hi, bool f16, const float* small_slot, const float* s, int sc, int cs_total, int c_off,
+                           float* partial, int N, int H, int W, int* nparts, cudaStream_t stream) {
     C9Params p;
+    p.f16 = f16 ? 1 : 0; p.small_slot = small_slot;
     p.s = s; p.sc = sc; p.N = N; p.H = H; p.W = W;
     p.wblocks = (W + KB - 1) / KB; p.work = N * H * p.wblocks;
     p.partial = partial; p.part_stride = TCB * cs_total * 81; p.cs_total = cs_total; p.c_off = c_off;

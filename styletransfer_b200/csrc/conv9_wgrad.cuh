@@ -103,7 +103,9 @@ conv9_correlate_kernel(const bf16* __restrict__ b_hi, const bf16* __restrict__ b
 
 // mode 0: dw[b][c][r][s] = O[b][c][r][s]                 (layer 0:  B = dy, S = x)
 // mode 1: dw[c][b][r][s] = O[b][c][8-r][8-s]             (layer 22: B = x,  S = dy)
-__global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int nparts, int CS, int mode, float* __restrict__ dw) {
+// mul_a / mul_b (optional scale slots of the operands): the sum is multiplied by slot[1] of each
+__global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int nparts, int CS, int mode,
+                                          const float* __restrict__ mul_a, const float* __restrict__ mul_b, float* __restrict__ dw) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = CB * CS * 81;
     if (idx >= total) return;
@@ -114,7 +116,7 @@ __global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int
     }
     float s = 0.f;
     for (int p = 0; p < nparts; ++p) s += partial[static_cast<size_t>(p) * total + src];
-    dw[idx] = s;
+    dw[idx] = s * slot_inv(mul_a) * slot_inv(mul_b);
 }
 
 // per-channel sum of an NCHW fp32 tensor with 3 channels (bias gradient of layer 22), two
@@ -147,7 +149,7 @@ inline int conv9_grid() { return st_num_sms() * 2; }
 
 }  // namespace
 
-int ew_channel_sum(const bf16* xh, const bf16* xl, int P, int C, int Cout, float* out, float* ws, cudaStream_t st);
+int ew_channel_sum(const bf16* xh, const bf16* xl, int code, const float* slot, int P, int C, int Cout, float* out, float* ws, cudaStream_t st);
 
 int conv9_expand_tc_run(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
                         bf16* out_hi, bf16* out_lo, int planes, int N, int H, int W, cudaStream_t stream);
@@ -155,7 +157,7 @@ int conv9_expand_tc_run(const float* s0, const float* s1, int sc, int CS, const 
 int conv9_expand_run(const float* s0, const float* s1, int sc, int CS, const float* w, const float* bias, int flip,
                      bf16* out_hi, bf16* out_lo, int planes, int N, int H, int W, int use_tc, cudaStream_t st) {
     // tensor-core path (conv9_tc.cu) for 2 / 3 output planes; st_set_conv_path(1) selects the CUDA-core kernel
-    if (use_tc && planes >= 2 && out_lo) return conv9_expand_tc_run(s0, s1, sc, CS, w, bias, flip, out_hi, out_lo, planes, N, H, W, st);
+    if (use_tc && pc_planes(planes) >= 2 && out_lo) return conv9_expand_tc_run(s0, s1, sc, CS, w, bias, flip, out_hi, out_lo, planes, N, H, W, st);
     const int th = (H + EX_TH - 1) / EX_TH, tw = (W + EX_TW - 1) / EX_TW;
     const int tiles = N * th * tw;
     const int grid = tiles < conv9_grid() ? tiles : conv9_grid();
@@ -193,23 +195,31 @@ size_t conv9_wgrad_workspace_bytes(int CS) {
 }
 
 // mode 0: layer 0 (B = dy [N,H,W,32], S = input image(s)); mode 1: layer 22 (B = x, S = dy NCHW fp32)
-int conv9_correlate_tc_run(const bf16* b_hi, const float* s, int sc, int cs_total, int c_off, float* partial,
-                           int N, int H, int W, int* nparts, cudaStream_t stream);
+// f16: the big tensor holds fp16 planes (the builder then converts the small tensor to fp16 too, multiplied by
+// small_slot[0] when given); the partial sums carry the scales of both operands
+int conv9_correlate_tc_run(const bf16* b_hi, bool f16, const float* small_slot, const float* s, int sc, int cs_total, int c_off,
+                           float* partial, int N, int H, int W, int* nparts, cudaStream_t stream);
 
 // use_tc: tensor-core correlation (conv9_tc.cu) when the two planes of the big tensor are one plane
-// stride apart; otherwise (or with st_set_conv_path(1)) the CUDA-core kernel below
-int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float* s0, const float* s1, int sc, int CS, int mode,
+// stride apart; otherwise (or with st_set_conv_path(1)) the CUDA-core kernel below.
+// planes: plane code of the big tensor; big_slot / small_slot (optional): power-of-two scale slots -- the big
+// tensor is STORED multiplied by big_slot[0]; the small (fp32) tensor is multiplied by small_slot[0] when it is
+// converted to fp16 operands (tensor-core path with fp16 planes only)
+int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float* big_slot, const float* small_slot,
+                    const float* s0, const float* s1, int sc, int CS, int mode,
                     float* dw, float* db, float* ws, size_t ws_bytes, int N, int H, int W, int use_tc, cudaStream_t st) {
     ST_CHECK_ARG(ws && ws_bytes >= conv9_wgrad_workspace_bytes(CS), "conv9_wgrad: workspace too small");
-    if (use_tc && planes >= 2 && b_lo == b_hi + static_cast<size_t>(N) * H * W * CB) {
+    const bool f16 = pc_f16(planes);
+    if (use_tc && pc_planes(planes) >= 2 && b_lo == b_hi + static_cast<size_t>(N) * H * W * CB) {
         int nparts = 0, rc;
-        if ((rc = conv9_correlate_tc_run(b_hi, s0, sc, CS, 0, ws, N, H, W, &nparts, st))) return rc;
-        if (CS == 6 && (rc = conv9_correlate_tc_run(b_hi, s1, sc, CS, 3, ws, N, H, W, &nparts, st))) return rc;
+        const float* sslot = f16 ? small_slot : nullptr;
+        if ((rc = conv9_correlate_tc_run(b_hi, f16, sslot, s0, sc, CS, 0, ws, N, H, W, &nparts, st))) return rc;
+        if (CS == 6 && (rc = conv9_correlate_tc_run(b_hi, f16, sslot, s1, sc, CS, 3, ws, N, H, W, &nparts, st))) return rc;
         const int total = CB * CS * 81;
-        conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, nparts, CS, mode, dw);
+        conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, nparts, CS, mode, big_slot, sslot, dw);
         ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
         if (db) {
-            if (mode == 0) return ew_channel_sum(b_hi, b_lo, N * H * W, CB, CB, db, ws, st);
+            if (mode == 0) return ew_channel_sum(b_hi, b_lo, planes, big_slot, N * H * W, CB, CB, db, ws, st);
             nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
             ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
             nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);
@@ -231,10 +241,10 @@ int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float*
     else conv9_correlate_kernel<6><<<grid, CR_THREADS, smem, st>>>(b_hi, b_lo, planes, s0, s1, sc, ws, N, H, W);
     ST_CHECK_LAUNCH("conv9_correlate_kernel");
     const int total = CB * CS * 81;
-    conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, grid * rows, CS, mode, dw);
+    conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, grid * rows, CS, mode, big_slot, nullptr, dw);
     ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
     if (db) {
-        if (mode == 0) return ew_channel_sum(b_hi, b_lo, N * H * W, CB, CB, db, ws, st);
+        if (mode == 0) return ew_channel_sum(b_hi, b_lo, planes, big_slot, N * H * W, CB, CB, db, ws, st);
         nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
         ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
         nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);

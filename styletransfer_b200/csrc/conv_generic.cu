@@ -14,7 +14,9 @@ constexpr int BM = 64, BK = 32, LDS = 40;   // LDS: padded smem row (bf16) -> co
 
 struct GenParams {
     const bf16* x_hi; const bf16* x_lo;
-    int x_planes, w_planes, out_planes;   // 1..3 bf16 planes (third plane: common.cuh)
+    int x_planes, w_planes, out_planes;   // plane counts of the MMA operands (1..3 bf16 planes after conversion) / plane CODE of the outputs
+    int x_f16, w_f16, add_code;           // fp16 source planes are converted to bf16 planes on load; plane code of the addend
+    float acc_mul; const float* acc_mul_slot; const float* add_mul_slot;   // as ConvTcParams
     int N, H, W, Cin;          // stored input tensor
     int up;                    // 1: input is read through a nearest x2 upsample (K6)
     const bf16* w_hi; const bf16* w_lo;
@@ -48,8 +50,9 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     const int ap = p.x_planes, wp = p.w_planes, maxord = max(ap, wp) - 1;
-    const bf16* x_p2 = third_plane(p.x_hi, p.x_lo, ap);
-    const bf16* w_p2 = third_plane(p.w_hi, p.w_lo, wp);
+    const bf16* x_p2 = p.x_f16 ? nullptr : third_plane(p.x_hi, p.x_lo, ap);
+    const bf16* w_p2 = p.w_f16 ? nullptr : third_plane(p.w_hi, p.w_lo, wp);
+    const float acc_mul = p.acc_mul * slot_inv(p.acc_mul_slot), add_mul = slot_inv(p.add_mul_slot);
     const int Hl = p.H << p.up, Wl = p.W << p.up;
 
     // the two A rows this thread gathers
@@ -91,8 +94,9 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
                 if (ok) {
                     const size_t off = ((static_cast<size_t>(pn[i]) * p.H + ih) * p.W + iw) * p.Cin + ci;
                     vh = *reinterpret_cast<const uint4*>(p.x_hi + off);
-                    if (ap > 1) vl = *reinterpret_cast<const uint4*>(p.x_lo + off);
+                    if (p.x_lo) vl = *reinterpret_cast<const uint4*>(p.x_lo + off);
                     if (x_p2) v2 = *reinterpret_cast<const uint4*>(x_p2 + off);
+                    if (p.x_f16) f16x8_to_bf16_planes(vh, vl, v2);
                 }
             }
             const int row = (t >> 2) + i * 32;
@@ -107,8 +111,9 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
             if (n0 + row < p.Cout_pad && k0 + kb < p.Ktot) {
                 const size_t off = static_cast<size_t>(n0 + row) * p.Ktot + k0 + kb;
                 vh = *reinterpret_cast<const uint4*>(p.w_hi + off);
-                if (wp > 1) vl = *reinterpret_cast<const uint4*>(p.w_lo + off);
+                if (p.w_lo) vl = *reinterpret_cast<const uint4*>(p.w_lo + off);
                 if (w_p2) v2 = *reinterpret_cast<const uint4*>(w_p2 + off);
+                if (p.w_f16) f16x8_to_bf16_planes(vh, vl, v2);
             }
             *reinterpret_cast<uint4*>(&Bs[0][row][kb]) = vh;
             *reinterpret_cast<uint4*>(&Bs[1][row][kb]) = vl;
@@ -150,36 +155,37 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
 #pragma unroll
         for (int j = 0; j < BN / 8; ++j) {
             const int ch = n0 + j * 8 + (lane & 3) * 2;
-            float v0 = acc[j][half * 2], v1 = acc[j][half * 2 + 1];
+            float v0 = acc[j][half * 2] * acc_mul, v1 = acc[j][half * 2 + 1] * acc_mul;
             if (p.bias) { if (ch < p.Cbias) v0 += p.bias[ch]; if (ch + 1 < p.Cbias) v1 += p.bias[ch + 1]; }
             if (ch < p.Cstore) {
                 const size_t o = static_cast<size_t>(m) * p.Cstore + ch;
                 if (p.mask) {
                     const uint32_t mk = *reinterpret_cast<const uint32_t*>(p.mask + o);
-                    if (!(bf16lo_to_f(mk) > 0.f)) v0 = 0.f;
-                    if (!(bf16hi_to_f(mk) > 0.f)) v1 = 0.f;
+                    if (!pos16_lo(mk)) v0 = 0.f;
+                    if (!pos16_hi(mk)) v1 = 0.f;
                 }
                 if (p.add_hi) {
-                    const uint32_t a = *reinterpret_cast<const uint32_t*>(p.add_hi + o);
-                    v0 += bf16lo_to_f(a); v1 += bf16hi_to_f(a);
-                    if (p.add_lo) {
-                        const uint32_t b = *reinterpret_cast<const uint32_t*>(p.add_lo + o);
-                        v0 += bf16lo_to_f(b); v1 += bf16hi_to_f(b);
-                        const bf16* a2 = third_plane(p.add_hi, p.add_lo, p.out_planes);   // add carries the output's planes
-                        if (a2) { const uint32_t c = *reinterpret_cast<const uint32_t*>(a2 + o); v0 += bf16lo_to_f(c); v1 += bf16hi_to_f(c); }
+                    const bool af = pc_f16(p.add_code);
+                    float2 a = unpack16x2(*reinterpret_cast<const uint32_t*>(p.add_hi + o), af);
+                    if (p.add_lo && pc_planes(p.add_code) > 1) {
+                        const float2 b = unpack16x2(*reinterpret_cast<const uint32_t*>(p.add_lo + o), af);
+                        a.x += b.x; a.y += b.y;
+                        const bf16* a2 = third_plane(p.add_hi, p.add_lo, p.add_code);
+                        if (a2) { const uint32_t c = *reinterpret_cast<const uint32_t*>(a2 + o); a.x += bf16lo_to_f(c); a.y += bf16hi_to_f(c); }
                     }
+                    v0 = fmaf(a.x, add_mul, v0); v1 = fmaf(a.y, add_mul, v1);
                 }
                 if (p.out_hi) {
-                    uint32_t h, m, l; split2p(v0, v1, h, m, l);
+                    uint32_t h, m, l; split2c(v0, v1, p.out_planes, h, m, l);
                     *reinterpret_cast<uint32_t*>(p.out_hi + o) = h;
-                    if (p.out_lo && p.out_planes > 1) *reinterpret_cast<uint32_t*>(p.out_lo + o) = m;
+                    if (p.out_lo && pc_planes(p.out_planes) > 1) *reinterpret_cast<uint32_t*>(p.out_lo + o) = m;
                     bf16* o2 = third_plane(p.out_hi, p.out_lo, p.out_planes);
                     if (o2) *reinterpret_cast<uint32_t*>(o2 + o) = l;
                 }
                 if (p.relu_hi) {
-                    uint32_t h, m, l; split2p(fmaxf(v0, 0.f), fmaxf(v1, 0.f), h, m, l);
+                    uint32_t h, m, l; split2c(fmaxf(v0, 0.f), fmaxf(v1, 0.f), p.out_planes, h, m, l);
                     *reinterpret_cast<uint32_t*>(p.relu_hi + o) = h;
-                    if (p.relu_lo && p.out_planes > 1) *reinterpret_cast<uint32_t*>(p.relu_lo + o) = m;
+                    if (p.relu_lo && pc_planes(p.out_planes) > 1) *reinterpret_cast<uint32_t*>(p.relu_lo + o) = m;
                     bf16* o2 = third_plane(p.relu_hi, p.relu_lo, p.out_planes);
                     if (o2) *reinterpret_cast<uint32_t*>(o2 + o) = l;
                 }
@@ -196,14 +202,21 @@ __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
 
 }  // namespace
 
+// x_planes / w_planes / out_planes / add_code: plane CODES; fp16 source planes are re-split into three bf16 planes on load
 int conv_gen_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
                  const bf16* w_hi, const bf16* w_lo, int w_planes, int ks, int stride, int pad, int transposed,
                  int Ho, int Wo, int Cout_pad, int Cstore, int Cbias,
-                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
+                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo, int add_code,
                  bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes,
-                 float* out_nchw, int Cnchw, cudaStream_t stream) {
+                 float* out_nchw, int Cnchw, float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, cudaStream_t stream) {
     GenParams p;
-    p.x_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1; p.w_planes = w_lo ? (w_planes >= 3 ? 3 : 2) : 1; p.out_planes = out_planes;
+    p.x_f16 = pc_f16(x_planes); p.w_f16 = pc_f16(w_planes);
+    if (!x_lo || pc_planes(x_planes) < 2) x_lo = nullptr;
+    if (!w_lo || pc_planes(w_planes) < 2) w_lo = nullptr;
+    p.x_planes = p.x_f16 ? 3 : (x_lo ? (pc_planes(x_planes) >= 3 ? 3 : 2) : 1);
+    p.w_planes = p.w_f16 ? 3 : (w_lo ? (pc_planes(w_planes) >= 3 ? 3 : 2) : 1);
+    p.out_planes = out_planes; p.add_code = add_code;
+    p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.x_hi = x_hi; p.x_lo = x_lo; p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.up = up;
     p.w_hi = w_hi; p.w_lo = w_lo; p.Ktot = ks * ks * Cin;
     p.ks = ks; p.stride = stride; p.pad = pad; p.transposed = transposed;

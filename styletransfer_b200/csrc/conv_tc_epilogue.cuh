@@ -17,9 +17,14 @@ struct ConvTcParams {
     int w_img_rows;                 // weight-row offset per image (0: shared weights)
     int w_rows_total;               // rows of one weight plane
     int w_resident;                 // conv_tc: all weight tiles stay in shared memory (loaded once per CTA)
-    int out_planes;                 // bf16 planes of the output tensors (1..3)
+    uint32_t fmt_bits;              // operand-format bits of the instruction descriptor (ptx::umma_fmt_bits)
+    int out_planes;                 // plane CODE (common.cuh) of the output tensors
+    int add_code;                   // plane code of the addend
+    float acc_mul;                  // acc *= acc_mul * (acc_mul_slot ? acc_mul_slot[1] : 1) before the bias: undoes the
+    const float* acc_mul_slot;      //   fixed factor of fp16 weights and the power-of-two scale slot of a scaled operand
+    const float* add_mul_slot;      // the addend is multiplied by add_mul_slot[1] (a scaled fp16 gradient)
     const float* bias;              // [Cout] or null
-    const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0)
+    const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0); hi plane, bf16 or fp16 (sign test only)
     const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
     const bf16* add_lo;
     bf16* out_hi; bf16* out_lo;     // result (pre-activation)
@@ -51,7 +56,7 @@ __device__ __forceinline__ void tc_prefetch(const ConvTcParams& p, TcPre& b, con
     if (p.add_hi) {
 #pragma unroll
         for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_hi + off + v * 16, b.ah[v]);
-        if (p.add_lo && p.out_planes >= 2) {
+        if (p.add_lo && pc_planes(p.add_code) >= 2) {
 #pragma unroll
             for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_lo + off + v * 16, b.al[v]);
         }
@@ -59,8 +64,16 @@ __device__ __forceinline__ void tc_prefetch(const ConvTcParams& p, TcPre& b, con
 }
 
 // one 16-channel chunk: accumulators -> bias -> mask -> addend -> stores
+struct TcMul { float acc, add; };      // accumulator / addend multipliers of this launch (1 unless fp16 operands are involved)
+__device__ __forceinline__ TcMul tc_muls(const ConvTcParams& p) {
+    TcMul m;
+    m.acc = p.acc_mul * slot_inv(p.acc_mul_slot);
+    m.add = slot_inv(p.add_mul_slot);
+    return m;
+}
+
 template <int BN, int NACC, bool FUSED>
-__device__ __forceinline__ void tc_chunk(const ConvTcParams& p, uint32_t taddr, const TcPix& px, int col,
+__device__ __forceinline__ void tc_chunk(const ConvTcParams& p, const TcMul& mul, uint32_t taddr, const TcPix& px, int col,
                                          const uint32_t* mk, const uint32_t* ah, const uint32_t* al) {
     uint32_t r[16], rc[16], rd[16];
     ptx::tmem_ld16(taddr + col, r);
@@ -81,32 +94,39 @@ __device__ __forceinline__ void tc_chunk(const ConvTcParams& p, uint32_t taddr, 
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const float4 b = *reinterpret_cast<const float4*>(p.bias + ch + i * 4);
-            v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+            v[4 * i] = fmaf(v[4 * i], mul.acc, b.x); v[4 * i + 1] = fmaf(v[4 * i + 1], mul.acc, b.y);
+            v[4 * i + 2] = fmaf(v[4 * i + 2], mul.acc, b.z); v[4 * i + 3] = fmaf(v[4 * i + 3], mul.acc, b.w);
         }
+    } else if (mul.acc != 1.f) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] *= mul.acc;
     }
     if (FUSED) {
         if (p.mask) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                v[2 * i] = bf16lo_to_f(mk[i]) > 0.f ? v[2 * i] : 0.f;
-                v[2 * i + 1] = bf16hi_to_f(mk[i]) > 0.f ? v[2 * i + 1] : 0.f;
+                v[2 * i] = pos16_lo(mk[i]) ? v[2 * i] : 0.f;
+                v[2 * i + 1] = pos16_hi(mk[i]) ? v[2 * i + 1] : 0.f;
             }
         }
         if (p.add_hi) {
-            const bool lo = p.add_lo && p.out_planes >= 2;
+            const bool lo = p.add_lo && pc_planes(p.add_code) >= 2, f16 = pc_f16(p.add_code);
+            float a[16];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                float a0 = bf16lo_to_f(ah[i]), a1 = bf16hi_to_f(ah[i]);
-                if (lo) { a0 += bf16lo_to_f(al[i]); a1 += bf16hi_to_f(al[i]); }
-                v[2 * i] += a0; v[2 * i + 1] += a1;
+                float2 t = unpack16x2(ah[i], f16);
+                if (lo) { const float2 u = unpack16x2(al[i], f16); t.x += u.x; t.y += u.y; }
+                a[2 * i] = t.x; a[2 * i + 1] = t.y;
             }
-            const bf16* p2 = lo ? third_plane(p.add_hi, p.add_lo, p.out_planes) : nullptr;   // add carries the output's planes
+            const bf16* p2 = lo ? third_plane(p.add_hi, p.add_lo, p.add_code) : nullptr;
             if (p2) {
                 uint32_t w[8];
                 ldg256(p2 + o, w);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) { v[2 * i] += bf16lo_to_f(w[i]); v[2 * i + 1] += bf16hi_to_f(w[i]); }
+                for (int i = 0; i < 8; ++i) { a[2 * i] += bf16lo_to_f(w[i]); a[2 * i + 1] += bf16hi_to_f(w[i]); }
             }
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fmaf(a[i], mul.add, v[i]);
         }
     }
     if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
@@ -132,9 +152,9 @@ __device__ __forceinline__ void tc_chunk(const ConvTcParams& p, uint32_t taddr, 
 }
 
 template <int BN, int NACC, int GCH>
-__device__ __forceinline__ void tc_process(const ConvTcParams& p, const TcPre& b, uint32_t taddr, const TcPix& px, int col0) {
+__device__ __forceinline__ void tc_process(const ConvTcParams& p, const TcMul& mul, const TcPre& b, uint32_t taddr, const TcPix& px, int col0) {
 #pragma unroll
-    for (int j = 0; j < GCH / 16; ++j) tc_chunk<BN, NACC, true>(p, taddr, px, col0 + j * 16, b.mk[j], b.ah[j], b.al[j]);
+    for (int j = 0; j < GCH / 16; ++j) tc_chunk<BN, NACC, true>(p, mul, taddr, px, col0 + j * 16, b.mk[j], b.ah[j], b.al[j]);
 }
 
 // dec(wk, m) -> TcPix of accumulator row m of work item wk
@@ -149,6 +169,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
     const bool active = BN >= 32 || hf == 0;
     const int col_base = BN >= 32 ? hf * CW : 0;
     const bool fused = p.mask || p.add_hi;                // warp-uniform
+    const TcMul mul = tc_muls(p);
     const int step = gridDim.x;
     auto taddr_of = [&](int it) { return tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (it & 1) * stage_cols; };
     auto begin_tile = [&](int it) { ptx::mbar_wait(&t_full[it & 1], (it >> 1) & 1); ptx::tc_fence_after(); };
@@ -161,7 +182,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             begin_tile(it);
             if (active) {
 #pragma unroll 1
-                for (int j = 0; j < CW / 16; ++j) tc_chunk<BN, NACC, false>(p, taddr_of(it), px, col_base + j * 16, nullptr, nullptr, nullptr);
+                for (int j = 0; j < CW / 16; ++j) tc_chunk<BN, NACC, false>(p, mul, taddr_of(it), px, col_base + j * 16, nullptr, nullptr, nullptr);
             }
             end_tile(it);
         }
@@ -178,9 +199,9 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             TcPix nx = px;
             if (more) nx = dec(wk + step, m);
             begin_tile(it);
-            tc_process<BN, NACC, GCH>(p, A, taddr_of(it), px, col_base);
+            tc_process<BN, NACC, GCH>(p, mul, A, taddr_of(it), px, col_base);
             if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
-            tc_process<BN, NACC, GCH>(p, B, taddr_of(it), px, col_base + GCH);
+            tc_process<BN, NACC, GCH>(p, mul, B, taddr_of(it), px, col_base + GCH);
             if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
             end_tile(it);
         }
@@ -194,7 +215,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             {
                 const TcPix px = dec(wk0, m);
                 begin_tile(it);
-                tc_process<BN, NACC, GCH>(p, A, taddr_of(it), px, col_base);
+                tc_process<BN, NACC, GCH>(p, mul, A, taddr_of(it), px, col_base);
                 end_tile(it); ++it;
             }
             const int wk2 = wk0 + 2 * step;
@@ -203,7 +224,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             {
                 const TcPix px = dec(wk1, m);
                 begin_tile(it);
-                tc_process<BN, NACC, GCH>(p, B, taddr_of(it), px, col_base);
+                tc_process<BN, NACC, GCH>(p, mul, B, taddr_of(it), px, col_base);
                 end_tile(it); ++it;
             }
             const int wk3 = wk1 + 2 * step;

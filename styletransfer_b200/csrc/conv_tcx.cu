@@ -137,7 +137,7 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     } else if (warp == 1) {
         // ===================== MMA issuer (warp-uniform walk, one elected lane issues) =====================
         const bool leader = ptx::elect_one();
-        constexpr uint32_t idesc = ptx::umma_idesc_bf16(BLOCK_M, BN);
+        const uint32_t fmt = p.fmt_bits;
         constexpr uint32_t desc_hi = C::DESC_HI;
         int a = 0, b = 0; uint32_t aph = 0, bph = 0;
         int it = 0;
@@ -166,23 +166,23 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
                             //   D0 = a0 w0 | D1 = a0 w1 + a1 w0 | D2 = a0 w2 + a1 w1 + a2 w0   (adjacent TMEM columns)
                             const uint32_t ak = a_lo + ((k * 32) >> 4), bk = b_lo0 + ((k * 32) >> 4);
                             if (PL == 1) {
-                                if (leader) ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), acc_main);
+                                if (leader) ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), acc_main);
                             } else if (PL == 2) {
                                 if (leader) {
-                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), acc_main);
-                                    ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), 1u);
+                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc_main);
+                                    ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
                                 }
                             } else if (C::NACC == 3) {
                                 if (leader) {
-                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 3 * BN), acc_main);
-                                    ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), 1u);
-                                    ptx::mma_bf16_ss2(d_main + 2 * BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, BN), 1u);
+                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 3 * BN) | fmt), acc_main);
+                                    ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), 1u);
+                                    ptx::mma_bf16_ss2(d_main + 2 * BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
                                 }
                             } else {
                                 // 3 planes, BN = 128: N = 256 is the widest MMA; the 2^-16 terms share the D1 accumulator
                                 if (leader) {
-                                    constexpr uint32_t id1 = ptx::umma_idesc_bf16(BLOCK_M, BN);
-                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, ptx::umma_idesc_bf16(BLOCK_M, 2 * BN), acc_main);
+                                    const uint32_t id1 = (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt);
+                                    ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc_main);
                                     ptx::mma_bf16_ss2(d_main + BN, ak, bk + ((2 * C::B_PLANE) >> 4), desc_hi, id1, 1u);
                                     ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk + (C::B_PLANE >> 4), desc_hi, id1, 1u);
                                     ptx::mma_bf16_ss2(d_main + BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, id1, 1u);
@@ -265,10 +265,13 @@ bool conv_tcx_eligible(int mode, int ks, int Cin, int Cout, int H, int W, int Ho
     return Ho == 2 * H && Wo == 2 * W;
 }
 
+// x_planes / w_planes / out_planes / add_code are plane CODES (common.cuh); acc_mul, acc_mul_slot, add_mul_slot: see ConvTcParams
 int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, int W, int Cin,
                  const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int Cout, int Ho, int Wo,
-                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo,
-                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_f32, cudaStream_t stream) {
+                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo, int add_code,
+                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_f32,
+                 float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, cudaStream_t stream) {
+    ST_CHECK_ARG(pc_f16(x_planes) == pc_f16(w_planes), "conv_tcx: activation and weight planes must have the same 16-bit format");
     const int BN = (Cout % 128 == 0) ? 128 : Cout;
     const int KC = (Cin % 64 == 0) ? 64 : 32;
     const int IH = mode == 1 ? Ho : H, IW = mode == 1 ? Wo : W;      // tile iteration space
@@ -311,11 +314,14 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.n_blocks = Cout / BN;
     g.per_cls = N * p.tiles_h * p.tiles_w * p.n_blocks; p.work = g.per_cls * g.ncls;
     p.w_img_rows = 0; p.w_rows_total = w_rows_total;
-    const int a_planes = x_lo ? (x_planes >= 3 ? 3 : 2) : 1;
-    const int w_planes_ = w_lo ? (w_planes >= 3 ? 3 : 2) : 1;
+    const int xp = pc_planes(x_planes), wp = pc_planes(w_planes);
+    const int a_planes = x_lo ? (xp >= 3 ? 3 : (xp >= 2 ? 2 : 1)) : 1;
+    const int w_planes_ = w_lo ? (wp >= 3 ? 3 : (wp >= 2 ? 2 : 1)) : 1;
     const int planes = a_planes < w_planes_ ? a_planes : w_planes_;
     g.a_tx = planes * rows * TILE_W * KC * 2;
-    p.out_planes = out_planes;
+    p.fmt_bits = ptx::umma_fmt_bits(pc_f16(x_planes));
+    p.out_planes = out_planes; p.add_code = add_code;
+    p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32;

@@ -35,16 +35,18 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __
 
 // NHWC split-bf16 (Cpad channels stored) -> NCHW fp32 (first C channels)
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __restrict__ lo,
-                                    float* __restrict__ out, int N, int C, int HW, int Cpad, int planes) {
+                                    float* __restrict__ out, int N, int C, int HW, int Cpad, int planes,
+                                    const float* __restrict__ slot) {
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * HW) return;
     const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
+    const float mul = slot_inv(slot);
     for (int c0 = 0; c0 < C; c0 += 8) {
         float v[8];
         load8p(hi, lo, planes, idx * Cpad + c0, v);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            if (c0 + i < C) out[(static_cast<size_t>(n) * C + c0 + i) * HW + px] = v[i];
+            if (c0 + i < C) out[(static_cast<size_t>(n) * C + c0 + i) * HW + px] = v[i] * mul;
     }
 }
 
@@ -67,9 +69,16 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict
     if (mode == 2) { r = ks - 1 - r; s = ks - 1 - s; }
     float v = 0.f;
     if (co < Cout && ci < Cin) v = w[((static_cast<size_t>(co) * Cin + ci) * ks + r) * ks + s];
+    if (pc_f16(planes)) {
+        // fp16 planes of ST_W_F16_SCALE * w (the consumers multiply their accumulators by ST_W_F16_INV_SCALE)
+        uint32_t h2, l2; split2h(v * ST_W_F16_SCALE, 0.f, h2, l2);
+        reinterpret_cast<uint16_t*>(hi)[idx] = static_cast<uint16_t>(h2 & 0xffffu);
+        if (lo && pc_planes(planes) > 1) reinterpret_cast<uint16_t*>(lo)[idx] = static_cast<uint16_t>(l2 & 0xffffu);
+        return;
+    }
     bf16 h, l; split_bf16(v, h, l);
     hi[idx] = h;
-    if (lo && planes > 1) lo[idx] = l;
+    if (lo && pc_planes(planes) > 1) lo[idx] = l;
     bf16* p2 = third_plane(hi, lo, planes);
     if (p2) p2[idx] = __float2bfloat16_rn(v - __bfloat162float(h) - __bfloat162float(l));
 }
@@ -220,15 +229,15 @@ __global__ void relu_maxpool_bwd_idx_kernel(const unsigned char* __restrict__ ar
 // MSE forward: partial[b] = sum over this block's slice of (f(x) - f(t))^2,
 // f = identity or relu (FeatureReconstructionLoss sits on ReLU_4, network.py:230-232)
 // ---------------------------------------------------------------------------
-__global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
-                                   const bf16* __restrict__ th, const bf16* __restrict__ tl,
+__global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl, int x_code,
+                                   const bf16* __restrict__ th, const bf16* __restrict__ tl, int t_code,
                                    size_t nvec, int relu, float* __restrict__ partial) {
     __shared__ float sm[32];
     float s = 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
         float a[8], b[8];
-        load8(xh, xl, i * 8, a); load8(th, tl, i * 8, b);
+        load8p(xh, xl, x_code, i * 8, a); load8p(th, tl, t_code, i * 8, b);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             float d = relu ? (fmaxf(a[k], 0.f) - fmaxf(b[k], 0.f)) : (a[k] - b[k]);
@@ -240,18 +249,25 @@ __global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __re
 }
 
 // out[0] = scale * sum(partial[0..n)) ; optionally squared first (feature loss: mse^2 / numel)
+// amax_out (optional): also max(partial[n .. 2n)) -- the second half of the partials holds per-block maxima
 __global__ void sum_partials_kernel(const float* __restrict__ partial, int n, float scale, int square,
-                                    float post_scale, float* __restrict__ out) {
+                                    float post_scale, float* __restrict__ out, float* __restrict__ amax_out) {
     __shared__ float sm[32];
     float s = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
     s = block_sum(s, sm);
     if (threadIdx.x == 0) { s *= scale; if (square) s = s * s * post_scale; out[0] = s; }
+    if (amax_out) {
+        float m = 0.f;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, partial[n + i]);
+        m = block_max(m, sm);
+        if (threadIdx.x == 0) amax_out[0] = m;
+    }
 }
 
 // MSE backward: g = coef * (f(x) - f(t)) * f'(x),  coef = scale * (*gw) * (mul ? *mul : 1)
-__global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
-                               const bf16* __restrict__ th, const bf16* __restrict__ tl,
+__global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl, int x_code,
+                               const bf16* __restrict__ th, const bf16* __restrict__ tl, int t_code,
                                size_t nvec, int relu, float scale, const float* __restrict__ gw,
                                const float* __restrict__ mul, int accumulate,
                                bf16* __restrict__ gh, bf16* __restrict__ gl) {
@@ -259,7 +275,7 @@ __global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restri
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
         float a[8], b[8], o[8];
-        load8(xh, xl, i * 8, a); load8(th, tl, i * 8, b);
+        load8p(xh, xl, x_code, i * 8, a); load8p(th, tl, t_code, i * 8, b);
         if (accumulate) load8(gh, gl, i * 8, o);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
@@ -274,28 +290,62 @@ __global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restri
 // Style loss on the (small) Gram matrices: diff = G - T (T broadcast over the batch),
 // partial sums of diff^2 per block.   network.py:110-123
 // ---------------------------------------------------------------------------
+// partial[0 .. grid) = per-block sums of diff^2, partial[grid .. 2 grid) = per-block max |diff|
 __global__ void style_diff_kernel(const float* __restrict__ G, const float* __restrict__ T, int CC, int total,
                                   float* __restrict__ diff, float* __restrict__ partial) {
     __shared__ float sm[32];
-    float s = 0.f;
+    float s = 0.f, m = 0.f;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const float d = G[i] - T[i % CC];
         diff[i] = d;
-        s += d * d;
+        s += d * d; m = fmaxf(m, fabsf(d));
     }
     s = block_sum(s, sm);
     if (threadIdx.x == 0) partial[blockIdx.x] = s;
+    m = block_max(m, sm);
+    if (threadIdx.x == 0) partial[gridDim.x + blockIdx.x] = m;
 }
 
 // D = (*gw) * scale * diff, packed split-bf16 [B*C rows][C] (the per-image "weights" of the
 // 1x1 conv that evaluates dF = F * D on the tensor cores)
+// f16 (plane code bit): D is stored as fp16 planes of s * D with the power of two s that maps
+// max|D| = amax(diff) * |scale * gw| to 2^10; slot = {s, 1/s} for the epilogue of the dF = F * D convolution
 __global__ void style_seed_kernel(const float* __restrict__ diff, int total, float scale, const float* __restrict__ gw,
-                                  bf16* __restrict__ dh, bf16* __restrict__ dl) {
+                                  bf16* __restrict__ dh, bf16* __restrict__ dl, int code,
+                                  const float* __restrict__ diff_amax, float* __restrict__ slot) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const float coef = scale * gw[0];
+    if (pc_f16(code)) {
+        const float sc = pow2_scale_for(diff_amax[0] * fabsf(coef), 10.f);
+        if (i == 0) { slot[0] = sc; slot[1] = 1.f / sc; }
+        if (i >= total) return;
+        uint32_t h2, l2; split2h(diff[i] * coef * sc, 0.f, h2, l2);
+        reinterpret_cast<uint16_t*>(dh)[i] = static_cast<uint16_t>(h2 & 0xffffu);
+        if (dl) reinterpret_cast<uint16_t*>(dl)[i] = static_cast<uint16_t>(l2 & 0xffffu);
+        return;
+    }
     if (i >= total) return;
-    bf16 h, l; split_bf16(diff[i] * scale * gw[0], h, l);
+    bf16 h, l; split_bf16(diff[i] * coef, h, l);
     dh[i] = h;
     if (dl) dl[i] = l;
+}
+
+// max |x| over a flat fp32 array: per-block partial maxima, then one block -> slot = {s, 1/s} with the power of two s
+// that maps the maximum to 2^target_log2 (the scale under which a gradient image is fed to fp16 tensor-core operands)
+__global__ void absmax_partial_kernel(const float* __restrict__ x, size_t n, float* __restrict__ partial) {
+    __shared__ float sm[32];
+    float m = 0.f;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        m = fmaxf(m, fabsf(x[i]));
+    m = block_max(m, sm);
+    if (threadIdx.x == 0) partial[blockIdx.x] = m;
+}
+__global__ void absmax_finish_kernel(const float* __restrict__ partial, int n, float target_log2, float* __restrict__ slot) {
+    __shared__ float sm[32];
+    float m = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, partial[i]);
+    m = block_max(m, sm);
+    if (threadIdx.x == 0) { const float sc = pow2_scale_for(m, target_log2); slot[0] = sc; slot[1] = 1.f / sc; }
 }
 
 // per-channel sum over pixels (conv bias gradient): partial[blk][C], then finish
@@ -303,7 +353,7 @@ __global__ void style_seed_kernel(const float* __restrict__ diff, int total, flo
 // 256/Cv pixel lanes per block, grid-stride over pixels; per-block partials, then a
 // fixed-order finish (deterministic, no atomics)
 __global__ void __launch_bounds__(256)
-channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
+channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl, int code,
                            int P, int C, float* __restrict__ partial) {
     extern __shared__ float sm[];                 // [lanes][C]
     const int Cv = C / 8, lanes = 256 / Cv;
@@ -314,7 +364,7 @@ channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__
     if (pl < lanes) {
         for (int p = blockIdx.x * lanes + pl; p < P; p += gridDim.x * lanes) {
             float v[8];
-            load8(xh, xl, static_cast<size_t>(p) * C + cv * 8, v);
+            load8p(xh, xl, code, static_cast<size_t>(p) * C + cv * 8, v);
 #pragma unroll
             for (int i = 0; i < 8; ++i) s[i] += v[i];
         }
@@ -330,7 +380,8 @@ channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__
 }
 // out[c] = sum_b partial[b][c]: 32 columns x 8 row lanes per block
 __global__ void __launch_bounds__(256)
-channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, float* __restrict__ out) {
+channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, const float* __restrict__ slot,
+                          float* __restrict__ out) {
     __shared__ float sm[8][33];
     const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
@@ -351,7 +402,7 @@ channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, in
         float t = 0.f;
 #pragma unroll
         for (int l = 0; l < 8; ++l) t += sm[l][cl];
-        out[c] = t;
+        out[c] = t * slot_inv(slot);
     }
 }
 
@@ -368,9 +419,9 @@ int ew_nchw_to_nhwc(const float* a, const float* b, bf16* hi, bf16* lo, int plan
     nchw_to_nhwc_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, hi, lo, N, C1, C2, H * W, Cpad, planes);
     ST_CHECK_LAUNCH("nchw_to_nhwc_kernel"); return ST_OK;
 }
-int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, int planes, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
+int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, int planes, const float* slot, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * H * W;
-    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad, planes);
+    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad, planes, slot);
     ST_CHECK_LAUNCH("nhwc_to_nchw_kernel"); return ST_OK;
 }
 int ew_pack_weight(const float* w, bf16* hi, bf16* lo, int planes, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, cudaStream_t st) {
@@ -403,44 +454,54 @@ int ew_relu_maxpool_bwd(const bf16* xh, const bf16* xl, const bf16* gyh, const b
     ST_CHECK_LAUNCH("relu_maxpool_bwd_kernel"); return ST_OK;
 }
 // workspace: >= 4096 floats
-int ew_mse_fwd(const bf16* xh, const bf16* xl, const bf16* th, const bf16* tl, size_t n, int relu, int feature_form,
+int ew_mse_fwd(const bf16* xh, const bf16* xl, int x_code, const bf16* th, const bf16* tl, int t_code, size_t n, int relu, int feature_form,
                float* loss_out, float* ws, cudaStream_t st) {
     const size_t nvec = n / 8;
     int grid = grid_for(nvec, 256, 4); if (grid > 4096) grid = 4096;
-    mse_partial_kernel<<<grid, 256, 0, st>>>(xh, xl, th, tl, nvec, relu, ws);
+    mse_partial_kernel<<<grid, 256, 0, st>>>(xh, xl, x_code, th, tl, t_code, nvec, relu, ws);
     ST_CHECK_LAUNCH("mse_partial_kernel");
     // feature_form: (mse)^2 / numel   network.py:193-199
-    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(n), feature_form, 1.0f / static_cast<float>(n), loss_out);
+    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(n), feature_form, 1.0f / static_cast<float>(n), loss_out, nullptr);
     ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
 }
-int ew_mse_bwd(const bf16* xh, const bf16* xl, const bf16* th, const bf16* tl, size_t n, int relu, float scale,
+int ew_mse_bwd(const bf16* xh, const bf16* xl, int x_code, const bf16* th, const bf16* tl, int t_code, size_t n, int relu, float scale,
                const float* gw, const float* mul, int accumulate, bf16* gh, bf16* gl, cudaStream_t st) {
     const size_t nvec = n / 8;
-    mse_bwd_kernel<<<grid_for(nvec, 256), 256, 0, st>>>(xh, xl, th, tl, nvec, relu, scale, gw, mul, accumulate, gh, gl);
+    mse_bwd_kernel<<<grid_for(nvec, 256), 256, 0, st>>>(xh, xl, x_code, th, tl, t_code, nvec, relu, scale, gw, mul, accumulate, gh, gl);
     ST_CHECK_LAUNCH("mse_bwd_kernel"); return ST_OK;
 }
-int ew_style_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss_out, float* ws, cudaStream_t st) {
+// ws: >= 4096 floats (2 x 2048 per-block partials); diff_amax (optional): receives max |diff|
+int ew_style_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss_out, float* diff_amax, float* ws, cudaStream_t st) {
     const int total = B * C * C;
-    int grid = grid_for(total, 256, 2); if (grid > 4096) grid = 4096;
+    int grid = grid_for(total, 256, 2); if (grid > 2048) grid = 2048;
     style_diff_kernel<<<grid, 256, 0, st>>>(G, T, C * C, total, diff, ws);
     ST_CHECK_LAUNCH("style_diff_kernel");
-    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(total), 0, 1.f, loss_out);
+    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(total), 0, 1.f, loss_out, diff_amax);
     ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
 }
-int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw, bf16* dh, bf16* dl, cudaStream_t st) {
+int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw, bf16* dh, bf16* dl, int code,
+                  const float* diff_amax, float* slot, cudaStream_t st) {
     const int total = B * C * C;
-    style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl);
+    style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl, code, diff_amax, slot);
     ST_CHECK_LAUNCH("style_seed_kernel"); return ST_OK;
 }
+// slot = {s, 1/s}: power of two mapping max|x| to 2^target_log2; ws >= 1024 floats
+int ew_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, cudaStream_t st) {
+    int grid = grid_for(n, 1024, 2); if (grid > 1024) grid = 1024;
+    absmax_partial_kernel<<<grid, 256, 0, st>>>(x, n, ws);
+    ST_CHECK_LAUNCH("absmax_partial_kernel");
+    absmax_finish_kernel<<<1, 256, 0, st>>>(ws, grid, target_log2, slot);
+    ST_CHECK_LAUNCH("absmax_finish_kernel"); return ST_OK;
+}
 // ws: >= nblk*C floats with nblk = min(1024, ceil(P/64))
-int ew_channel_sum(const bf16* xh, const bf16* xl, int P, int C, int Cout, float* out, float* ws, cudaStream_t st) {
+int ew_channel_sum(const bf16* xh, const bf16* xl, int code, const float* slot, int P, int C, int Cout, float* out, float* ws, cudaStream_t st) {
     const int lanes = 256 / (C / 8);
     int nblk = (P + lanes * 8 - 1) / (lanes * 8);               // >= 8 pixels per lane
     const int cap = st_num_sms() * 4 < 1024 ? st_num_sms() * 4 : 1024;   // ws holds >= 1024 * C floats
     if (nblk > cap) nblk = cap;
     if (nblk < 1) nblk = 1;
-    channel_sum_partial_kernel<<<nblk, 256, lanes * C * sizeof(float), st>>>(xh, xl, P, C, ws);
+    channel_sum_partial_kernel<<<nblk, 256, lanes * C * sizeof(float), st>>>(xh, xl, code, P, C, ws);
     ST_CHECK_LAUNCH("channel_sum_partial_kernel");
-    channel_sum_finish_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, nblk, C, Cout, out);
+    channel_sum_finish_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, nblk, C, Cout, slot, out);
     ST_CHECK_LAUNCH("channel_sum_finish_kernel"); return ST_OK;
 }

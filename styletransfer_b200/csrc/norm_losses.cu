@@ -38,8 +38,10 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                 const float* __restrict__ mean, const float* __restrict__ rstd,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 int HW, int W, int C, int splits, int chunk, int relu, int x_planes,
-                float* __restrict__ partial /* [N][splits][2][C] */) {
+                float* __restrict__ partial /* [N][splits][2][C] */, float* __restrict__ gmax_partial /* [N*splits] or null */) {
     extern __shared__ float sm[];                 // [lanes][2][C]
+    __shared__ float smx[32];
+    float gmax = 0.f;                             // MODE 1: max |dy_eff| of this block (bound of the fp16 scale of dx)
     const int n = blockIdx.x / splits, sp = blockIdx.x % splits;
     const int Cv = C / 8, lanes = IN_THREADS / Cv;
     const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
@@ -94,6 +96,7 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     // NaN-safe form of the mask: keep the gradient only where the activation is > 0
                     const float e0 = (fmaf(ra[i], x0[i], rb[i]) > 0.f) ? g0[i] : 0.f;
                     const float e1 = (fmaf(ra[i], x1[i], rb[i]) > 0.f) ? g1[i] : 0.f;
+                    gmax = fmaxf(gmax, fmaxf(fabsf(e0), fabsf(e1)));
                     sa[i] += e0 + e1;
                     sb[i] = fmaf(e0, x0[i] - mu[i], fmaf(e1, x1[i] - mu[i], sb[i]));
                 }
@@ -115,6 +118,10 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
         float s = 0.f;
         for (int l = 0; l < lanes; ++l) s += sm[l * 2 * C + j];
         partial[(static_cast<size_t>(blockIdx.x)) * 2 * C + j] = s;
+    }
+    if (MODE == 1 && gmax_partial) {
+        gmax = block_max(gmax, smx);
+        if (threadIdx.x == 0) gmax_partial[blockIdx.x] = gmax;
     }
 }
 
@@ -152,8 +159,22 @@ in_finalize_fwd_kernel(const float* __restrict__ partial, int C, int splits, int
 __global__ void __launch_bounds__(1024)
 in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int splits,
                        float* __restrict__ s1, float* __restrict__ s2,
-                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                       const float* __restrict__ gmax_partial, int ngmax, const float* __restrict__ gamma,
+                       const float* __restrict__ rstd, float inv_hw, float* __restrict__ bound_part) {
     __shared__ float sa[32][33], sb[32][33];
+    __shared__ float smx[32];
+    // bound of |dx| = |gamma rstd| * |dy_eff - (s1 + xhat s2) / HW| for the fp16 scale of dx (when asked for):
+    // max |dy_eff| is measured, |xhat| <= 16 is assumed (the scale leaves another factor 64 of head room)
+    float G = 0.f, bmax = 0.f;
+    if (bound_part) {
+        for (int i = threadIdx.x; i < ngmax; i += 1024) G = fmaxf(G, gmax_partial[i]);
+        G = block_max(G, smx);
+        if (threadIdx.x == 0) smx[0] = G;
+        __syncthreads();
+        G = smx[0];
+        __syncthreads();
+    }
     const int cl = threadIdx.x & 31, l = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
     const int NL = N < 32 ? N : 32, SL = 32 / NL;            // image lanes x split lanes (<= 32)
@@ -188,6 +209,7 @@ in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int spli
             for (int k = 0; k < SL; ++k) { A += sa[k * NL + nl][cl]; B += sb[k * NL + nl][cl]; }
             s1[n * C + c] = A; s2[n * C + c] = B;
             db += A; dg += B;
+            if (bound_part) bmax = fmaxf(bmax, fabsf(gamma[c] * rstd[n * C + c]) * (G + (fabsf(A) + 16.f * fabsf(B)) * inv_hw));
         }
         __syncthreads();
     }
@@ -197,6 +219,10 @@ in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int spli
         float g = 0.f, b = 0.f;
         for (int k = 0; k < NL; ++k) { b += sa[k][cl]; g += sb[k][cl]; }      // lanes with sl == 0 are l = nl < NL
         dgamma[c] = g; dbeta[c] = b;
+    }
+    if (bound_part) {
+        bmax = block_max(bmax, smx);
+        if (threadIdx.x == 0) bound_part[blockIdx.x] = bmax;
     }
 }
 
@@ -252,10 +278,19 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
                     const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ s1, const float* __restrict__ s2,
-                    bf16* __restrict__ dxh, bf16* __restrict__ dxl,
+                    bf16* __restrict__ dxh, bf16* __restrict__ dxl, int dx_code,
+                    const float* __restrict__ bound_part, int nbound, float* __restrict__ dx_slot,
                     int HW, int W, int C, int chunk, int relu, int x_planes, float* __restrict__ dsum_partial) {
     extern __shared__ float sm_ds[];                  // [lanes][C], only when dsum_partial != null
     const int n = blockIdx.y;
+    // dx_slot: dx is stored multiplied by the power of two that maps its bound to 2^10 (fp16 planes)
+    float dx_scale = 1.f;
+    if (dx_slot) {
+        float b = 0.f;
+        for (int i = 0; i < nbound; ++i) b = fmaxf(b, bound_part[i]);
+        dx_scale = pow2_scale_for(b, 10.f);
+        if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) { dx_slot[0] = dx_scale; dx_slot[1] = 1.f / dx_scale; }
+    }
     const int Cv = C / 8, lanes = IN_THREADS / Cv;
     const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
     const int p0 = blockIdx.x * chunk, p1 = min(HW, p0 + chunk);
@@ -274,34 +309,22 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
     const size_t img = static_cast<size_t>(n) * HW;
 #pragma unroll(UP ? 1 : 2)
     for (int p = p0 + pl; p < p1; p += lanes) {
-        const bool two = false;                       // (two pixels per iteration measured slower here)
-        float x0[8], g0[8], x1[8], g1[8];
+        float x0[8], g0[8];                           // (two pixels per iteration measured slower here)
         load8p(xh, xl, x_planes, (img + p) * C + cv * 8, x0);
         in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
-        if (two) {
-            load8p(xh, xl, x_planes, (img + p + lanes) * C + cv * 8, x1);
-            in_load_grad<UP>(gh, gl, n, HW, W, C, p + lanes, cv, g1);
-        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float xhat = (x0[i] - mu[i]) * rs[i];
             const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g0[i];
             x0[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
         }
-        store8(dxh, dxl, (img + p) * C + cv * 8, x0);
 #pragma unroll
         for (int i = 0; i < 8; ++i) ds[i] += x0[i];
-        if (two) {
+        if (dx_slot) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float xhat = (x1[i] - mu[i]) * rs[i];
-                const float ge = (relu && !(ga[i] * xhat + be[i] > 0.f)) ? 0.f : g1[i];
-                x1[i] = gr[i] * (ge - inv_hw * (a1[i] + xhat * a2[i]));
-            }
-            store8(dxh, dxl, (img + p + lanes) * C + cv * 8, x1);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) ds[i] += x1[i];
+            for (int i = 0; i < 8; ++i) x0[i] *= dx_scale;
         }
+        store8p(dxh, dxl, dx_code, (img + p) * C + cv * 8, x0);
     }
     }
     // sum of dx per channel over this block's pixels (= bias gradient of the convolution in front)
@@ -518,7 +541,9 @@ inline int ew_grid(size_t n, int block) {
 constexpr int IN_MAX_SPLITS = 128;
 size_t in_workspace_floats(int N, int C) {
     // stats partials [N][splits][2][C] + (api adds s1, s2 [N][C]) + per-block sums of dx [8 * SMs + N][C]
-    return static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C + static_cast<size_t>(8 * st_num_sms() + N) * C;
+    // + per-block max |dy_eff| [N][splits] + per-channel-block bounds of |dx| [16]
+    return static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C + static_cast<size_t>(8 * st_num_sms() + N) * C +
+           static_cast<size_t>(N) * IN_MAX_SPLITS + 16;
 }
 
 int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* beta, float eps,
@@ -528,7 +553,7 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     const int chunk = (HW + splits - 1) / splits;
     const int lanes = IN_THREADS / (C / 8);
     in_stats_kernel<0, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, planes, ws);
+        xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, planes, ws, nullptr);
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
     in_finalize_fwd_kernel<<<dim3((C + 31) / 32, N), 256, 0, st>>>(ws, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
@@ -539,29 +564,36 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     return ST_OK;
 }
 
+// dx_code: plane code of dx; dx_slot (required when dx has fp16 planes, else null): receives {s, 1/s}, dx is stored
+// multiplied by s (a power of two chosen from a bound of |dx| that the statistics pass measures)
 int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
                 const float* mean, const float* rstd, const float* gamma, const float* beta,
-                bf16* dxh, bf16* dxl, float* dgamma, float* dbeta, float* dsum, int x_planes, int N, int H, int W, int C, int relu, int up,
-                float* ws, cudaStream_t st) {
+                bf16* dxh, bf16* dxl, int dx_code, float* dx_slot, float* dgamma, float* dbeta, float* dsum, int x_planes,
+                int N, int H, int W, int C, int relu, int up, float* ws, cudaStream_t st) {
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
     const int lanes = IN_THREADS / (C / 8);
     float* s1 = ws + static_cast<size_t>(N) * splits * 2 * C;
     float* s2 = s1 + static_cast<size_t>(N) * C;
+    float* gmaxp = ws + static_cast<size_t>(N) * IN_MAX_SPLITS * 2 * C + static_cast<size_t>(8 * st_num_sms() + N) * C + 2 * static_cast<size_t>(N) * C;
+    float* boundp = gmaxp + static_cast<size_t>(N) * IN_MAX_SPLITS;
+    float* gmax_arg = dx_slot ? gmaxp : nullptr;
     if (up)
         in_stats_kernel<1, 1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws);
+            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws, gmax_arg);
     else
         in_stats_kernel<1, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
-            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws);
+            xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws, gmax_arg);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
-    in_finalize_bwd_kernel<<<(C + 31) / 32, 1024, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta);
+    const int nbound = (C + 31) / 32;
+    in_finalize_bwd_kernel<<<nbound, 1024, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta, gmaxp, N * splits, gamma, rstd,
+                                                    1.0f / HW, dx_slot ? boundp : nullptr);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
     const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
     float* dpart = dsum ? s2 + static_cast<size_t>(N) * C : nullptr;        // [N * ablocks][C]
     const size_t dsm = dsum ? static_cast<size_t>(IN_THREADS / (C / 8)) * C * sizeof(float) : 0;
-    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes, dpart);
-    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, HW, W, C, achunk, relu, x_planes, dpart);
+    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
+    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
     ST_CHECK_LAUNCH("in_apply_bwd_kernel");
     if (dsum) {
         in_colsum_kernel<<<(C + 7) / 8, 1024, 0, st>>>(dpart, N * ablocks, C, dsum);

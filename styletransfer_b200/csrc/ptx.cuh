@@ -156,5 +156,12 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(N >> 3) << 17) |
            (static_cast<uint32_t>(M >> 4) << 24);
 }
+// The same descriptor without the operand formats: OR umma_fmt_bits(f16) into it.  kind::f16 takes fp16
+// (format 0) or bf16 (format 1) operands, but BOTH operands must have the same format: a_format != b_format
+// is an illegal instruction on sm_100a (profiles/r02a_probe_mixed_mma.log).
+__host__ __device__ constexpr uint32_t umma_idesc_nofmt(int M, int N) {
+    return (1u << 4) | (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
+}
+__host__ __device__ constexpr uint32_t umma_fmt_bits(bool f16) { return f16 ? 0u : ((1u << 7) | (1u << 10)); }
 
 }  // namespace ptx

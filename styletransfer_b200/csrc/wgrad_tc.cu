@@ -36,6 +36,7 @@ struct WgradParams {
     int chunks;                             // Cin / 64
     int splits, tiles_per_split;
     int pad_w;                              // horizontal padding (KW / 2)
+    uint32_t fmt_bits;                      // operand format bits of the instruction descriptor (both operands alike)
     float* partial;                         // [split][s][chunk][acc][128][Cdy]
 };
 
@@ -67,9 +68,10 @@ __device__ __forceinline__ uint32_t mn_desc_lo(uint32_t addr, uint32_t lbo_bytes
 __host__ __device__ constexpr uint32_t mn_desc_hi(int row_bytes) {
     return static_cast<uint32_t>((8 * row_bytes) >> 4) | (1u << 14) | ((row_bytes == 128 ? 2u : 4u) << 29);
 }
-// kind::f16 instruction descriptor, bf16 x bf16 -> fp32, BOTH operands MN-major (bits 15, 16)
+// kind::f16 instruction descriptor, fp32 accumulate, BOTH operands MN-major (bits 15, 16); the operand format
+// bits (ptx::umma_fmt_bits: bf16 or fp16, the same for both operands) are OR-ed in at run time
 __host__ __device__ constexpr uint32_t idesc_mn(int M, int N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+    return (1u << 4) | (1u << 15) | (1u << 16) |
            (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 __device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
@@ -147,7 +149,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         const bool leader = ptx::elect_one();
-        constexpr uint32_t idesc = idesc_mn(128, CDY);
+        const uint32_t idesc = idesc_mn(128, CDY) | p.fmt_bits;
         constexpr uint32_t a_hi = mn_desc_hi(128);
         constexpr uint32_t b_hi = mn_desc_hi(C::DROW);
         int st = 0; uint32_t ph = 0;
@@ -217,7 +219,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 // (coalesced), the tile is transposed through shared memory and written with j fastest.
 __global__ void __launch_bounds__(256)
 wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, int chunks, int nacc, int CDY,
-                       int Cout, int Cin, int KH, float* __restrict__ dw) {
+                       int Cout, int Cin, int KH, const float* __restrict__ dy_slot, float* __restrict__ dw) {
     __shared__ float tile[8][33];
     const int J = Cin * KH * KW;
     const int co0 = blockIdx.y * 32, j0 = blockIdx.x * 8;
@@ -245,7 +247,7 @@ wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, in
     __syncthreads();
     {
         const int co = co0 + (threadIdx.x >> 3), j = j0 + (threadIdx.x & 7);
-        if (co < Cout && j < J) dw[static_cast<size_t>(co) * J + j] = tile[threadIdx.x & 7][threadIdx.x >> 3];
+        if (co < Cout && j < J) dw[static_cast<size_t>(co) * J + j] = tile[threadIdx.x & 7][threadIdx.x >> 3] * slot_inv(dy_slot);
     }
 }
 
@@ -257,6 +259,7 @@ wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, in
 // ---------------------------------------------------------------------------------------------
 struct GramParams {
     int B, HW, tiles, splits, tiles_per_split;
+    uint32_t fmt_bits;
     float* partial;                         // [b][split][acc][128][C]
 };
 
@@ -319,7 +322,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
         }
     } else if (warp == 1) {
         const bool leader = ptx::elect_one();
-        constexpr uint32_t idesc = idesc_mn(128, C_);
+        const uint32_t idesc = idesc_mn(128, C_) | p.fmt_bits;
         constexpr uint32_t hi = mn_desc_hi(128);
         int st = 0; uint32_t ph = 0;
         uint32_t accumulate = 0;
@@ -499,13 +502,14 @@ size_t gram_tc_workspace_bytes(int B, int HW, int C) {
     const GramPlan q = plan_gram(B, HW, C);
     return static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
 }
-// f [planes][B][HW][C] (plane stride B*HW*C elements) -> Gm [B][C][C] * scale
-int gram_tc_run(const bf16* f_hi, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+// f [planes][B][HW][C] (plane stride B*HW*C elements; f16: the planes are fp16) -> Gm [B][C][C] * scale
+int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     const GramPlan q = plan_gram(B, HW, C);
     const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
     ST_CHECK_ARG(workspace && workspace_bytes >= need, "gram_tc: workspace too small (%zu < %zu)", workspace_bytes, need);
     GramParams p;
     p.B = B; p.HW = HW; p.tiles = q.tiles; p.splits = q.splits; p.tiles_per_split = q.tiles_per_split;
+    p.fmt_bits = ptx::umma_fmt_bits(f16);
     p.partial = static_cast<float*>(workspace);
     CUtensorMap tf;
     uint64_t fd[3] = {(uint64_t)C, (uint64_t)HW, (uint64_t)B * PL};
@@ -535,8 +539,9 @@ size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks
     return static_cast<size_t>(q.grid) * q.nacc * 128 * Cdy * sizeof(float);
 }
 
-// dy [planes][N][H][W][Cdy], x [planes][N][H][W][CinPad] (plane stride = N*H*W*C elements), dw [Cout][Cin][ks][ks]
-int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, int N, int H, int W, int CinPad, int Cdy, int ks,
+// dy [planes][N][H][W][Cdy], x [planes][N][H][W][CinPad] (plane stride = N*H*W*C elements), dw [Cout][Cin][ks][ks].
+// f16: both tensors hold fp16 planes; dy_slot (optional): the power-of-two scale slot of dy, undone by the finish kernel
+int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, bool f16, const float* dy_slot, int N, int H, int W, int CinPad, int Cdy, int ks,
                  int Cout, int Cin, float* dw, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
     const WgradPlan q = plan_wgrad(N, H, W, CinPad, ks, ks);
     const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * Cdy * sizeof(float);
@@ -545,6 +550,7 @@ int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, int N, int H, int W, int C
     p.N = N; p.H = H; p.W = W; p.Cin = CinPad; p.Cdy = Cdy;
     p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W; p.tiles = q.tiles;
     p.chunks = q.chunks; p.splits = q.splits; p.tiles_per_split = q.tiles_per_split; p.pad_w = ks / 2;
+    p.fmt_bits = ptx::umma_fmt_bits(f16);
     p.partial = static_cast<float*>(workspace);
     CUtensorMap tx, td;
     uint64_t xd[4] = {(uint64_t)CinPad, (uint64_t)W, (uint64_t)H, (uint64_t)N * PL};
@@ -559,7 +565,7 @@ int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, int N, int H, int W, int C
     else rc = launch_wgrad<3, 32>(tx, td, p, q.grid, stream);
     if (rc) return rc;
     const int J = Cin * ks * ks;
-    wgrad_tc_finish_kernel<<<dim3((J + 7) / 8, (Cout + 31) / 32), 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dw);
+    wgrad_tc_finish_kernel<<<dim3((J + 7) / 8, (Cout + 31) / 32), 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dy_slot, dw);
     ST_CHECK_LAUNCH("wgrad_tc_finish_kernel");
     return ST_OK;
 }

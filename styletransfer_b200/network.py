@@ -117,7 +117,7 @@ class _GramMSE(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         f = ctx.f
-        _buf, wp = ops.style_seed(ctx.diff, f.H * f.W, g.reshape(1).contiguous().float())
+        _keep, wp = ops.style_seed(ctx.diff[0], ctx.diff[1], f.H * f.W, g.reshape(1).contiguous().float(), f.fmt)
         out, _, _ = ops.conv2d(f, None, w_ptrs=wp, w_img_rows=f.C)
         return ops.to_nchw(out, ctx.C), None
 
@@ -297,13 +297,7 @@ class StyleNetwork(nn.Module):
     @staticmethod
     def _relu_split(tap):
         """relu of a Split (the ReLU_4 feature target).  Off the hot path (targets only)."""
-        out = tap.like()
-        rest = tap.float().clamp_(min=0)
-        for p in range(out.planes):
-            plane = rest.to(torch.bfloat16)
-            out.buf[p].copy_(plane)
-            rest = rest - plane.float()
-        return out
+        return tap.like().set_from_float(tap.float().clamp_(min=0))
 
     @staticmethod
     def _build_pieces(weights):

@@ -108,7 +108,7 @@ class _PackCache:
         self.grad_sink = None
 
     def get(self, name, w, mode, **kw):
-        key = (name, mode, ops.PRECISION)
+        key = (name, mode, ops.PRECISION, kw.get('fmt'))
         tag = (w.data_ptr(), w._version, tuple(w.shape))
         hit = self.entries.get(key)
         if self.always_repack or hit is None or hit[0] != tag:
@@ -193,6 +193,10 @@ class TransformNetFn(torch.autograd.Function):
             return sink.get(name) if need[name] else None
         N, cin, H, W = ctx.in_shape
         gy = gy.contiguous().float()
+        # f16x3 mode: gradients that meet forward activations in a tensor-core product are fp16 planes under a
+        # power-of-two scale slot (InstanceNorm-backward outputs carry their own; the gradient image gets one here)
+        dyf = ops.dy_fmt()
+        gy_slot = None
         g = None             # built lazily: the 9x9 output layer consumes the NCHW fp32 gradient directly
         res_grad = None      # gradient flowing into the residual branch of the current block
         pending_db = None    # sum of dy per channel from the InstanceNorm backward right after a conv
@@ -204,9 +208,11 @@ class TransformNetFn(torch.autograd.Function):
                 name = st[1]
                 w = p[name + '.weight']
                 if need[name + '.weight'] or need[name + '.bias']:
+                    if dyf:
+                        gy_slot = ops.absmax_slot(gy)
                     grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(
-                        ctx.saved[idx], gy, 1, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'))
-                g = ops.conv9_expand(gy, w, flip=True, planes=ops.bwd_planes())
+                        ctx.saved[idx], gy, 1, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'), small_slot=gy_slot)
+                g = ops.conv9_expand(gy, w, flip=True, planes=ops.bwd_planes(), fmt=0)      # feeds an InstanceNorm backward
                 continue
             if g is None:
                 g = ops.from_nchw(gy, cpad=8, planes=ops.bwd_planes())
@@ -218,7 +224,7 @@ class TransformNetFn(torch.autograd.Function):
                         g, ctx.x, 0, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'))
                 if ctx.needs_input_grad[0]:
                     # rare (tests / image optimisation through the net): gather-form backward-data
-                    pw = cache.get(name, w, 1, rows_pad=ops.pad8(cin), cols_pad=g.C)
+                    pw = cache.get(name, w, 1, rows_pad=ops.pad8(cin), cols_pad=g.C, fmt=g.fmt)
                     _, _, gx = ops.conv2d(g, pw, stride=1, transposed=1, out_hw=(H, W), want_out=False, out_nchw_channels=cin)
                     grads['__input__'] = gx
                 break
@@ -241,7 +247,7 @@ class TransformNetFn(torch.autograd.Function):
                     res_grad = g                    # d(out)/d(residual) = identity
                 if idx == first_conv:
                     if ctx.needs_input_grad[0]:
-                        pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C)
+                        pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C, fmt=g.fmt)
                         _, _, gx = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xin.H, xin.W),
                                               want_out=False, out_nchw_channels=cin)
                         grads['__input__'] = gx
@@ -249,11 +255,12 @@ class TransformNetFn(torch.autograd.Function):
                 tc = k == 3 and stride == 1
                 # the conv after a residual 'mark' (conv1) adds the block's residual gradient
                 add = res_grad if (PLAN[idx - 1][0] == 'mark') else None
+                # backward-data weights in the format of the gradient they multiply
                 if tc:
-                    pw = cache.get(name, w, 2, rows_pad=xin.C, cols_pad=g.C)
+                    pw = cache.get(name, w, 2, rows_pad=xin.C, cols_pad=g.C, fmt=g.fmt)
                     g, _, _ = ops.conv2d(g, pw, add=add)
                 else:
-                    pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C)
+                    pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C, fmt=g.fmt)
                     g, _, _ = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xin.H, xin.W), add=add)
             else:
                 _, name, relu, up = st

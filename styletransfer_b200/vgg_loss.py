@@ -105,7 +105,7 @@ class _VGGLossFn(torch.autograd.Function):
 
         def branch(i, tap):
             G = ops.gram(tap)
-            diffs[i] = ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1])
+            diffs[i] = ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1])      # (diff, max |diff|)
             if i == CONTENT_TAP:
                 ops.mse_fwd(tap, content_target, losses[5:6])
                 if with_feature:
@@ -136,7 +136,8 @@ class _VGGLossFn(torch.autograd.Function):
         # dF_l = F_l * D_l  (Gram backward, per-image 1x1 conv on the tensor cores)
         def style_grad(i, add=None):
             tap = taps[i]
-            _buf, wp = ops.style_seed(diffs[i], tap.H * tap.W, gl[i:i + 1])
+            # the per-image weights D take the plane format of the tap they multiply (one format per tensor-core product)
+            _keep, wp = ops.style_seed(diffs[i][0], diffs[i][1], tap.H * tap.W, gl[i:i + 1], tap.fmt)
             out, _, _ = ops.conv2d(tap, None, w_ptrs=wp, w_img_rows=tap.C, add=add)
             return out
 

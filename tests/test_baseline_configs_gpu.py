@@ -22,10 +22,29 @@ pytestmark = pytest.mark.gpu
 TOL_FEATURE, TOL_LOSS_GRAD, TOL_CHAIN_GRAD = 1e-2, 1e-3, 3e-2
 
 
-@pytest.fixture(scope='module')
-def network():
-    from styletransfer_b200 import network
-    return network
+@pytest.fixture(scope='module', params=['f16x3', 'bf16x6'])
+def network(request):
+    """Both parity-grade precision modes (DESIGN.md "Precision")."""
+    from styletransfer_b200 import network, ops
+    prev = ops.PRECISION
+    ops.set_precision(request.param)
+    yield network
+    ops.set_precision(prev)
+
+
+_ORACLE = {}
+
+
+def memo(key, fn):
+    """The CPU oracle of a case is evaluated once and shared by the precision modes."""
+    if key not in _ORACLE:
+        _ORACLE[key] = fn()
+    return _ORACLE[key]
+
+
+def PREC():
+    from styletransfer_b200 import ops
+    return ops.PRECISION
 
 
 def _vgg_cuda():
@@ -46,13 +65,18 @@ def test_gatys_closure_matches_oracle_at_baseline_size(network, s):
     vw = oracle.make_vgg_weights(1)
     content, style = seeded((1, 3, s, s), 10), seeded((1, 3, s, s), 11)
     x0 = content + 0.3 * seeded((1, 3, s, s), 12)
-    targets = oracle.style_targets(style, vw)
-    o_total, o_grad, o_losses = oracle.gatys_closure(x0, content, targets, vw)
+    targets = memo(('gatys_targets', s), lambda: oracle.style_targets(style, vw))
+    o_total, o_grad, o_losses = memo(('gatys', s), lambda: oracle.gatys_closure(x0, content, targets, vw))
+    # how far the fp32 reference arithmetic itself is from exact arithmetic at this size (flipped ReLU / max-pool
+    # decisions: DESIGN.md "Precision"): the same closure in fp64 on the CPU
+    d = lambda t: t.double()
+    g64 = memo(('gatys64', s), lambda: oracle.gatys_closure(d(x0), d(content), [d(t) for t in targets], [(d(w), d(b)) for w, b in vw])[1])
+    record(f'oracle/gatys{s}/fp32_vs_fp64_grad_rel_l2', rel_l2(o_grad, g64))
     taps_ref = oracle.vgg_taps(x0, vw)
     prefix = vgg_loss.VGGPrefix(_vgg_cuda())
     for i, (t, r) in enumerate(zip(prefix.taps(x0.cuda()), taps_ref)):
-        assert record(f'gatys{s}/tap{i + 1}_rel_l2', rel_l2(nhwc(t), r)) < TOL_FEATURE
-        assert record(f'gatys{s}/gram{i + 1}_rel_l2', rel_l2(ops.gram(t), oracle.gram_matrix(r))) < TOL_FEATURE
+        assert record(f'{PREC()}/gatys{s}/tap{i + 1}_rel_l2', rel_l2(nhwc(t), r)) < TOL_FEATURE
+        assert record(f'{PREC()}/gatys{s}/gram{i + 1}_rel_l2', rel_l2(ops.gram(t), oracle.gram_matrix(r))) < TOL_FEATURE
     del taps_ref
     net = network.StyleNetwork(style.cuda(), content.cuda(), vgg_weights=_vgg_cuda())
     for (node, _), ref in zip(net.style_losses, targets):
@@ -62,16 +86,17 @@ def test_gatys_closure_matches_oracle_at_baseline_size(network, s):
     total = net.get_total_current_style_loss(weight=1e5) + net.get_total_current_content_loss(weight=1)
     total.backward()
     per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
-    assert record(f'gatys{s}/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
-    assert record(f'gatys{s}/losses_rel_l2', rel_l2(per_node, o_losses)) < TOL_LOSS_GRAD
-    assert record(f'gatys{s}/grad_rel_l2', rel_l2(x.grad, o_grad)) < TOL_LOSS_GRAD
+    assert record(f'{PREC()}/gatys{s}/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(f'{PREC()}/gatys{s}/losses_rel_l2', rel_l2(per_node, o_losses)) < TOL_LOSS_GRAD
+    assert record(f'{PREC()}/gatys{s}/grad_rel_l2', rel_l2(x.grad, o_grad)) < TOL_LOSS_GRAD
+    record(f'{PREC()}/gatys{s}/grad_rel_l2_vs_fp64', rel_l2(x.grad, g64))
     # the graph-replayed closure train_gatys runs is the same arithmetic
     xg = x0.cuda().requires_grad_(True)
     net.compute_feature_loss = False
     closure = net.gatys_closure(xg, content.cuda(), 1e5, 1)
     loss = closure()
-    assert record(f'gatys{s}/graph_total_rel', abs(float(loss) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
-    assert record(f'gatys{s}/graph_grad_rel_l2', rel_l2(xg.grad, o_grad)) < TOL_LOSS_GRAD
+    assert record(f'{PREC()}/gatys{s}/graph_total_rel', abs(float(loss) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(f'{PREC()}/gatys{s}/graph_grad_rel_l2', rel_l2(xg.grad, o_grad)) < TOL_LOSS_GRAD
 
 
 def test_gatys_closure_matches_reference_golden_256(network, golden_dir):
@@ -86,9 +111,9 @@ def test_gatys_closure_matches_reference_golden_256(network, golden_dir):
     total = net.get_total_current_style_loss(weight=float(g['sw'])) + net.get_total_current_content_loss(weight=float(g['cw']))
     total.backward()
     per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
-    assert record('gatys_golden256/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
+    assert record(PREC() + '/gatys_golden256/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
     assert rel_l2(per_node, torch.from_numpy(g['losses'])) < TOL_LOSS_GRAD
-    assert record('gatys_golden256/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
+    assert record(PREC() + '/gatys_golden256/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
 
 
 def test_fast_st_closure_matches_oracle_at_baseline_size(network):
@@ -97,19 +122,19 @@ def test_fast_st_closure_matches_oracle_at_baseline_size(network):
     vw = oracle.make_vgg_weights(1)
     params = oracle.make_transform_params(2, 3)
     style, batch = seeded((1, 3, s, s), 201), seeded((b, 3, s, s), 202)
-    o_total, o_grads, o_out, o_losses = oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw)
+    o_total, o_grads, o_out, o_losses = memo('fast_st', lambda: oracle.fast_st_closure(batch, params, oracle.style_targets(style, vw), vw))
     net = _build(network, network.ImageTransformNet, params, style.cuda(), b)
     loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, s, s]).cuda(), vgg_weights=_vgg_cuda())
     total, out = net.closure_loss(batch.cuda(), loss_net)
     total.backward()
     per_node = torch.stack([n[0].loss for n in loss_net.style_losses + loss_net.content_losses]).detach()
-    assert record('fast_st_16x256/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
-    assert record('fast_st_16x256/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
-    assert record('fast_st_16x256/losses_rel_l2', rel_l2(per_node, o_losses[:6])) < TOL_LOSS_GRAD
+    assert record(PREC() + '/fast_st_16x256/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
+    assert record(PREC() + '/fast_st_16x256/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record(PREC() + '/fast_st_16x256/losses_rel_l2', rel_l2(per_node, o_losses[:6])) < TOL_LOSS_GRAD
     got = {k: p.grad.detach().cpu() for k, p in net.named_parameters()}
-    assert record('fast_st_16x256/grads_worst', grads_err(got, o_grads)) < TOL_CHAIN_GRAD
+    assert record(PREC() + '/fast_st_16x256/grads_worst', grads_err(got, o_grads)) < TOL_CHAIN_GRAD
     flat = lambda d: torch.cat([d[k].reshape(-1) for k in sorted(d)])
-    record('fast_st_16x256/grads_flat_rel_l2', rel_l2(flat(got), flat(o_grads)))
+    record(PREC() + '/fast_st_16x256/grads_flat_rel_l2', rel_l2(flat(got), flat(o_grads)))
 
 
 @pytest.mark.parametrize('clips', [1, 2])
@@ -121,15 +146,15 @@ def test_video_closure_matches_oracle_at_baseline_size(network, clips):
     style, batch = seeded((1, 3, 256, 256), 31), seeded((clips, 3, s, s), 32)
     old_content = batch + 0.05 * seeded((clips, 3, s, s), 33)
     old_stylized = seeded((clips, 3, s, s), 34)
-    o_total, o_grads, o_out, _ = oracle.video_closure(batch, old_content, old_stylized, params,
-                                                      oracle.style_targets(style, vw), vw)
+    o_total, o_grads, o_out, _ = memo(('video', clips), lambda: oracle.video_closure(batch, old_content, old_stylized, params,
+                                                                                      oracle.style_targets(style, vw), vw))
     o_temporal = oracle.temporal_loss(old_content, old_stylized, batch, o_out, 0.8)
     net = _build(network, network.VideoTransformNet, params, style.cuda(), clips)
     loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, 256, 256]).cuda(), vgg_weights=_vgg_cuda())
     state = [old_content.cuda(), old_stylized.cuda()]
     total, out = net.closure_loss_video(batch.cuda(), state, loss_net, 0.8)
     total.backward()
-    tag = f'video_{clips}x512'
+    tag = f'{PREC()}/video_{clips}x512'
     assert record(tag + '/out_rel_l2', rel_l2(out, o_out)) < TOL_FEATURE
     assert record(tag + '/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
     t = net.get_temporal_loss(old_content.cuda(), old_stylized.cuda(), batch.cuda(), out.detach(), temporal_weight=0.8)
@@ -162,15 +187,15 @@ def test_lbfgs_100_steps_psnr_256(network, golden_dir):
     net.get_content_optimizer = spy
     out = net.train_gatys(style.cuda(), content.cuda(), steps=int(g['steps']), style_weight=LBFGS_SW, content_weight=LBFGS_CW)
     info = made[0].info()
-    record('lbfgs100_256/pairs', info['k'])
+    record(PREC() + '/lbfgs100_256/pairs', info['k'])
     assert info['k'] > 0, info
     ref = torch.from_numpy(g['out'])
     moved = _psnr(content, ref)
-    record('lbfgs100_256/psnr_of_unoptimised_image_db', moved)
-    psnr = record('lbfgs100_256/psnr_vs_oracle_db', _psnr(out.detach().cpu(), ref))
+    record(PREC() + '/lbfgs100_256/psnr_of_unoptimised_image_db', moved)
+    psnr = record(PREC() + '/lbfgs100_256/psnr_vs_oracle_db', _psnr(out.detach().cpu(), ref))
     assert psnr >= 40.0 and psnr > moved + 10.0, (psnr, moved)
     path = os.path.join(golden_dir, 'gatys_lbfgs_256_reference.npz')
     if os.path.exists(path):
         r = torch.from_numpy(np.load(path)['out'])
-        record('lbfgs100_256/psnr_oracle_vs_reference_db', _psnr(ref, r))
-        assert record('lbfgs100_256/psnr_vs_reference_db', _psnr(out.detach().cpu(), r)) >= 40.0
+        record(PREC() + '/lbfgs100_256/psnr_oracle_vs_reference_db', _psnr(ref, r))
+        assert record(PREC() + '/lbfgs100_256/psnr_vs_reference_db', _psnr(out.detach().cpu(), r)) >= 40.0

@@ -107,10 +107,31 @@ def test_library_exports_every_declared_symbol():
     assert L.st_arch() == 100
     # argument validation happens before any CUDA call
     assert L.st_conv2d(None, None, 1, 1, 8, 8, 8, 0, None, None, 1, 8, 0, 3, 1, 1, 0, 8, 8, 8, 0,
-                       None, None, None, None, None, None, None, None, 1, None, 0, None) == -1
+                       None, None, None, None, 1, None, None, None, None, 1, None, 0, 1.0, None, None, None) == -1
     assert b'null' in L.st_last_error()
     assert L.st_instnorm_workspace_bytes(4, 128) > 0
     assert L.st_gram_workspace_bytes(1, 512 * 512, 64) > 0
+
+
+def test_ctypes_signatures_match_the_header_prototypes():
+    """Every prototype of include/stransfer_b200.h against the ctypes table: same arity, and pointer / integer /
+    floating-point / size_t class per argument (a mismatch would corrupt the call silently)."""
+    from styletransfer_b200 import _lib
+    text = open(os.path.join(ROOT, 'include', 'stransfer_b200.h')).read()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    protos = re.findall(r'\b[a-z_ ]+?[ *]+(st_[a-z0-9_]+)\s*\(([^)]*)\)\s*;', text)
+    assert len(protos) == len(_lib.SIGNATURES)
+
+    def cls(arg):
+        arg = arg.strip()
+        if '*' in arg:
+            return ctypes.c_void_p
+        base = arg.rsplit(' ', 1)[0].strip() if ' ' in arg else arg
+        return {'int': ctypes.c_int, 'float': ctypes.c_float, 'double': ctypes.c_double, 'size_t': ctypes.c_size_t}[base]
+    for name, args in protos:
+        args = [a for a in args.split(',') if a.strip() and a.strip() != 'void']
+        want = [cls(a) for a in args]
+        assert _lib.SIGNATURES[name][1] == want, (name, [t.__name__ for t in want], [t.__name__ for t in _lib.SIGNATURES[name][1]])
 
 
 def test_sass_has_blackwell_tensor_and_tma_instructions():

@@ -19,11 +19,14 @@ pytestmark = pytest.mark.gpu
 TOL_FEATURE, TOL_LOSS_GRAD = 1e-2, 1e-3
 
 
-@pytest.fixture(scope='module')
-def net_mod():
+@pytest.fixture(scope='module', params=['f16x3', 'bf16x6'])
+def net_mod(request):
+    """Both parity-grade precision modes (DESIGN.md "Precision")."""
     from styletransfer_b200 import network, ops
-    ops.set_precision('bf16x6')
-    return network
+    prev = ops.PRECISION
+    ops.set_precision(request.param)
+    yield network
+    ops.set_precision(prev)
 
 
 def _vgg_cuda():

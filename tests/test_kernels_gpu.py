@@ -1,5 +1,6 @@
 """Per-kernel parity: each C-ABI entry point against a plain PyTorch fp32 op on the
-same GPU (TF32 off).  Tolerances: split-bf16 storage carries ~16 mantissa bits, so
+same GPU (TF32 off), in both parity-grade precision modes (f16x3: two fp16 planes / 3 tensor-core passes;
+bf16x6: three bf16 planes / 6 passes).  Tolerances: gradients carry ~16 mantissa bits, so
 rel-L2 <= 1e-4 on single ops (north star: features/Grams <= 1e-2)."""
 import pytest
 import torch
@@ -11,13 +12,26 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-4
 
 
-@pytest.fixture(scope='module')
-def ops():
+@pytest.fixture(scope='module', params=['f16x3', 'bf16x6'])
+def ops(request):
     fp32_reference_mode()
     from styletransfer_b200 import _lib, ops as o
     _lib.lib()
-    o.set_precision('bf16x6')
-    return o
+    prev = o.PRECISION
+    o.set_precision(request.param)
+    yield o
+    o.set_precision(prev)
+
+
+def _grad(ops, gy, cpad=None):
+    """A gradient tensor as the product makes them where they meet forward activations in a tensor-core product
+    (fp16 planes in the f16x3 mode -- unscaled here: the test values fit the fp16 range)."""
+    return ops.from_nchw(gy, cpad=cpad, planes=ops.bwd_planes(), fmt=ops.dy_fmt())
+
+
+def _bf16_grad(ops, gy):
+    """A gradient tensor of the bf16 chain (conv backward-data outputs, pooling / loss gradients)."""
+    return ops.from_nchw(gy, planes=ops.bwd_planes(), fmt=0)
 
 
 def test_layout_roundtrip(ops):
@@ -74,6 +88,7 @@ def test_conv_tcgen05_many_tiles(ops):
 
 def test_conv_tcgen05_plain_bf16(ops):
     """the cheaper precision modes: 1 plane / 1 pass and 2 planes / 3 passes"""
+    prev = ops.PRECISION
     try:
         ops.set_precision('bf16')
         assert _conv_case(ops, 1, 16, 32, 64, 64, 3, 1, path=0) < 1e-2
@@ -82,12 +97,12 @@ def test_conv_tcgen05_plain_bf16(ops):
         assert _conv_case(ops, 2, 24, 40, 128, 128, 3, 1, path=0) < 1e-4
         assert _conv_case(ops, 1, 16, 32, 3, 32, 9, 1, path=1) < 1e-4
     finally:
-        ops.set_precision('bf16x6')
+        ops.set_precision(prev)
 
 
 def test_forward_conv_is_fp32_accurate(ops):
-    """bf16x6 forward: 3 planes x 6 passes carry 24 mantissa bits; what remains is the
-    tensor core's truncating fp32 accumulation over the K loop (~1e-5 at K = 1152 x 6 passes,
+    """Parity-grade forward (3 bf16 planes / 6 passes = 24 mantissa bits, or 2 fp16 planes / 3 passes = 22 bits):
+    what remains is the tensor core's truncating fp32 accumulation over the K loop (~1e-5 at K = 1152,
     DESIGN.md "Precision").  Compared against an fp64 convolution."""
     x = seeded((1, 128, 24, 40), 91, device='cuda')
     w = seeded((128, 128, 3, 3), 92, 0.03, device='cuda')
@@ -110,7 +125,7 @@ def test_conv_tcgen05_image_gradient(ops, N, H, W):
     gy = seeded((N, 64, H, W), 74, device='cuda')
     F.conv2d(x, w, None, padding=1).backward(gy)
     pw = ops.PackedWeight(w, 2, rows_pad=16)
-    _, _, gx = ops.conv2d(ops.from_nchw(gy, planes=2), pw, want_out=False, out_nchw_channels=3)
+    _, _, gx = ops.conv2d(_bf16_grad(ops, gy), pw, want_out=False, out_nchw_channels=3)
     assert _lib.lib().st_last_conv_kernel() == 1
     assert rel_l2(gx, x.grad) < TOL
 
@@ -132,8 +147,8 @@ def test_conv_tcx_stride2_dgrad(ops, cin, cout, H, W):
     gy = seeded((N, cout, H // 2, W // 2), 6, device='cuda')
     x = seeded((N, cin, H, W), 7, device='cuda').requires_grad_(True)
     F.conv2d(x, w, None, stride=2, padding=1).backward(gy)
-    gys = ops.from_nchw(gy)
-    pw = ops.PackedWeight(w, 1, rows_pad=cin, cols_pad=gys.C)
+    gys = _grad(ops, gy)
+    pw = ops.PackedWeight(w, 1, rows_pad=cin, cols_pad=gys.C, fmt=gys.fmt)
     out, _, _ = ops.conv2d(gys, pw, stride=2, transposed=1, out_hw=(H, W))
     assert _lib.lib().st_last_conv_kernel() == 2
     assert rel_l2(nhwc(out, cin), x.grad) < TOL
@@ -150,10 +165,10 @@ def test_conv_tcx_32_channel_chunks(ops, cin, cout, H, W):
     gy = seeded((N, cin, H, W), 6, device='cuda')
     x = seeded((N, cout, H, W), 7, device='cuda').requires_grad_(True)
     F.conv2d(x, w, None, padding=1).backward(gy)
-    gys = ops.from_nchw(gy)
-    pw = ops.PackedWeight(w, 2, rows_pad=cout, cols_pad=gys.C)
+    gys = _grad(ops, gy)
+    pw = ops.PackedWeight(w, 2, rows_pad=cout, cols_pad=gys.C, fmt=gys.fmt)
     tap, add = seeded((N, cout, H, W), 8, device='cuda'), seeded((N, cout, H, W), 9, device='cuda')
-    out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=ops.from_nchw(add))
+    out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=_grad(ops, add))
     assert _lib.lib().st_last_conv_kernel() == 2
     assert rel_l2(nhwc(out, cout), x.grad * (tap > 0) + add) < TOL
 
@@ -169,17 +184,19 @@ def test_conv_dgrad(ops, cin, cout, ks, stride, path):
     gy = seeded((N, cout, Ho, Wo), 6, device='cuda')
     x = seeded((N, cin, H, W), 7, device='cuda').requires_grad_(True)
     F.conv2d(x, w, None, stride=stride, padding=ks // 2).backward(gy)
-    gys = ops.from_nchw(gy)
+    gys = _grad(ops, gy)
     cin_pad = ops.pad8(cin)
     if path == 0:
-        pw = ops.PackedWeight(w, 2, rows_pad=cin_pad, cols_pad=gys.C)
+        pw = ops.PackedWeight(w, 2, rows_pad=cin_pad, cols_pad=gys.C, fmt=gys.fmt)
         tap = seeded((N, cin, H, W), 8, device='cuda')
         add = seeded((N, cin, H, W), 9, device='cuda')
-        out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=ops.from_nchw(add))
-        ref = x.grad * (tap > 0) + add
-        assert rel_l2(nhwc(out, cin), ref) < TOL
+        # the addend of a backward-data epilogue is a bf16 gradient, or a (scaled) fp16 one (residual blocks)
+        for a in (_bf16_grad(ops, add), _grad(ops, add)):
+            out, _, _ = ops.conv2d(gys, pw, mask=ops.from_nchw(tap), add=a)
+            ref = x.grad * (tap > 0) + add
+            assert rel_l2(nhwc(out, cin), ref) < TOL
     else:
-        pw = ops.PackedWeight(w, 1, rows_pad=cin_pad, cols_pad=gys.C)
+        pw = ops.PackedWeight(w, 1, rows_pad=cin_pad, cols_pad=gys.C, fmt=gys.fmt)
         out, _, nchw = ops.conv2d(gys, pw, stride=stride, transposed=1, out_hw=(H, W), out_nchw_channels=cin)
         assert rel_l2(nhwc(out, cin), x.grad) < TOL
         assert rel_l2(nchw, x.grad) < TOL
@@ -208,9 +225,12 @@ def _wgrad_case(ops, N, H, W, cin, cout, ks, stride, up):
     y = F.conv2d(xin, w, b, stride=stride, padding=ks // 2)
     gy = seeded(tuple(y.shape), 13, device='cuda')
     y.backward(gy)
-    dw, db = ops.conv2d_wgrad(ops.from_nchw(gy), ops.from_nchw(x), ks, stride, ks // 2, up, cout, cin)
+    dw, db = ops.conv2d_wgrad(_grad(ops, gy), ops.from_nchw(x), ks, stride, ks // 2, up, cout, cin)
     assert rel_l2(dw, w.grad) < TOL
     assert rel_l2(db, b.grad) < TOL
+    # a bf16 gradient against (possibly fp16) activations: the converting mma.sync kernel takes mixed formats
+    dw, db = ops.conv2d_wgrad(_bf16_grad(ops, gy), ops.from_nchw(x), ks, stride, ks // 2, up, cout, cin)
+    assert rel_l2(dw, w.grad) < TOL and rel_l2(db, b.grad) < TOL
 
 
 @pytest.mark.parametrize('H,W', [(16, 32), (15, 21)])
@@ -224,15 +244,15 @@ def test_relu_maxpool(ops, H, W):
     # the pooled value is rounded to split-bf16 twice (input and output)
     assert rel_l2(nhwc(ys), y) < 1e-5
     add = seeded((2, 64, H, W), 23, device='cuda')
-    gx = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=ops.from_nchw(add))
+    gx = ops.relu_maxpool_bwd(xs, _bf16_grad(ops, gy), add=_bf16_grad(ops, add))
     assert rel_l2(nhwc(gx), x.grad + add) < 1e-5
     # the variant whose forward saves the routing decision (1 byte per pooled element) and whose backward does not
     # read x again: bit-identical outputs, odd borders included; ties (relu'(x) = 0 windows) route nothing
     ys2, idx = ops.relu_maxpool_fwd(xs, want_idx=True)
     assert torch.equal(ys2.buf, ys.buf) and idx.shape == (2, H // 2, W // 2, 64) and int(idx.max()) <= 4
-    for a in (ops.from_nchw(add), None):
-        g_ref = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=a)
-        g_idx = ops.relu_maxpool_bwd(xs, ops.from_nchw(gy), add=a, idx=idx)
+    for a in (_bf16_grad(ops, add), None):
+        g_ref = ops.relu_maxpool_bwd(xs, _bf16_grad(ops, gy), add=a)
+        g_idx = ops.relu_maxpool_bwd(xs, _bf16_grad(ops, gy), add=a, idx=idx)
         assert torch.equal(g_idx.buf, g_ref.buf)
     neg = ops.from_nchw(-x.detach().abs())
     _, idx_neg = ops.relu_maxpool_fwd(neg, want_idx=True)
@@ -251,12 +271,15 @@ def test_gram_and_style_loss(ops, B, C, H, W):
     Gk = ops.gram(fs)
     assert rel_l2(Gk, G) < TOL
     lk = torch.zeros(1, device='cuda')
-    diff = ops.style_mse_fwd(Gk, T, lk)
+    diff, amax = ops.style_mse_fwd(Gk, T, lk)
     assert abs(float(lk) - float(loss)) / float(loss) < 1e-4
-    gw = torch.tensor([1.0], device='cuda')
-    _buf, wp = ops.style_seed(diff, H * W, gw)
-    dF, _, _ = ops.conv2d(fs, None, w_ptrs=wp, w_img_rows=C)
-    assert rel_l2(nhwc(dF), f.grad) < 2e-4
+    assert abs(float(amax) - float((G - T).abs().max())) <= 1e-4 * float(amax)
+    # loss weights of very different size: the per-tensor power-of-two scale of the fp16 seed follows them
+    for weight in (1.0, 1e5, 1e-6):
+        gw = torch.tensor([weight], device='cuda')
+        _keep, wp = ops.style_seed(diff, amax, H * W, gw, fs.fmt)
+        dF, _, _ = ops.conv2d(fs, None, w_ptrs=wp, w_img_rows=C)
+        assert rel_l2(nhwc(dF), weight * f.grad) < 2e-4
 
 
 def test_mse(ops):
@@ -300,10 +323,14 @@ def test_instance_norm(ops, C, H, W, relu, up):
     xs = ops.from_nchw(x.detach())
     ys, stats = ops.instnorm_fwd(xs, gamma.detach(), beta.detach(), relu=relu, up=up)
     assert rel_l2(nhwc(ys), y) < 1e-4
-    dx, dg, db = ops.instnorm_bwd(xs, ops.from_nchw(gy), stats, gamma.detach(), beta.detach(), relu=relu, up=up)
-    assert rel_l2(nhwc(dx), x.grad) < 2e-4
-    assert rel_l2(dg, gamma.grad) < 2e-4
-    assert rel_l2(db, beta.grad) < 2e-4
+    # gradients of very different size: dx is stored under a per-tensor power-of-two scale in the f16x3 mode
+    for weight in (1.0, 3e-7, 2e4):
+        dx, dg, db = ops.instnorm_bwd(xs, _bf16_grad(ops, weight * gy), stats, gamma.detach(), beta.detach(), relu=relu, up=up)
+        assert (dx.slot is not None) == bool(ops.dy_fmt())
+        assert rel_l2(nhwc(dx), weight * x.grad) < 2e-4
+        assert rel_l2(dg, weight * gamma.grad) < 2e-4
+        assert rel_l2(db, weight * beta.grad) < 2e-4
+        assert rel_l2(ops.to_nchw(dx), weight * x.grad) < 2e-4
 
 
 def test_tv_and_temporal(ops):
@@ -368,7 +395,7 @@ def test_conv_image_fwd_and_dgrad(ops, N, H, W):
     assert rel_l2(nhwc(relu), F.relu(ref)) < 2e-6
     only_relu = ops.conv_image_fwd(x.detach(), w, b, want_out=False, want_relu=True)
     assert only_relu[0] is None and rel_l2(nhwc(only_relu[1]), F.relu(ref)) < 2e-6
-    gx = ops.conv_image_dgrad(ops.from_nchw(gy, planes=2), w)
+    gx = ops.conv_image_dgrad(_bf16_grad(ops, gy), w)
     assert gx.shape == x.shape and rel_l2(gx, x.grad) < 2e-5
 
 
@@ -396,7 +423,7 @@ def _conv9_layers(ops, C, N, H, W):
     y.backward(gy)
     out = ops.conv9_expand(x, w0.detach(), b0.detach())
     assert rel_l2(nhwc(out), y) < 2e-6
-    dw, db = ops.conv9_wgrad(ops.from_nchw(gy, planes=2), x, 0)
+    dw, db = ops.conv9_wgrad(_grad(ops, gy), x, 0)
     assert rel_l2(dw, w0.grad) < 2e-5 and rel_l2(db, b0.grad) < 2e-5
     if C != 3:
         return
@@ -409,7 +436,10 @@ def _conv9_layers(ops, C, N, H, W):
     y2.backward(g2)
     xs = ops.from_nchw(xb.detach())
     assert rel_l2(ops.conv9_reduce(xs, w2.detach(), b2.detach()), y2) < 2e-6
-    dx = ops.conv9_expand(g2, w2.detach(), flip=True, planes=2)
+    dx = ops.conv9_expand(g2, w2.detach(), flip=True, planes=2, fmt=0)
     assert rel_l2(nhwc(dx), xb.grad) < 2e-5
-    dw2, db2 = ops.conv9_wgrad(xs, g2, 1)
-    assert rel_l2(dw2, w2.grad) < 2e-5 and rel_l2(db2, b2.grad) < 2e-6
+    # a tiny gradient image: it enters the fp16 operands of the f16x3 mode under the power-of-two scale of its maximum
+    for weight in (1.0, 1e-7):
+        slot = ops.absmax_slot(weight * g2) if ops.dy_fmt() else None
+        dw2, db2 = ops.conv9_wgrad(xs, weight * g2, 1, small_slot=slot)
+        assert rel_l2(dw2, weight * w2.grad) < 2e-5 and rel_l2(db2, weight * b2.grad) < 2e-6

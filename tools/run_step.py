@@ -28,11 +28,11 @@ def main():
     ap.add_argument('--width', type=int, default=0, help='infer: frame width (height = --size)')
     ap.add_argument('--warmup', type=int, default=2)
     ap.add_argument('--steps', type=int, default=1)
-    ap.add_argument('--precision', default='bf16x6')
+    ap.add_argument('--precision', default=None)
     args = ap.parse_args()
     from oracle import oracle
     from styletransfer_b200 import network, ops
-    ops.set_precision(args.precision)
+    ops.set_precision(args.precision or ops.PRECISION)
     dev = torch.device('cuda', 0)
     vw = network.load_vgg19_prefix_weights(seed=1)
     if args.workload == 'lbfgs':
