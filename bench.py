@@ -165,7 +165,7 @@ def run_fast_st(args, rank, world, dev, L, timed, with_cpu):
     batch = global_batch[rank * per:(rank + 1) * per].to(dev)
     last = [None]
     # the closure static_train hands to optimizer.step: a replayed CUDA graph (default) + all-reduce
-    train_closure = net.training_closure(batch, loss_net, bucket, graph=not args.no_graph)
+    train_closure = net.training_closure(batch, loss_net, bucket, graph=not args.no_graph, optimizer=opt)
 
     def closure():
         total = train_closure()
@@ -278,7 +278,7 @@ def run_video_st(args, rank, world, dev, L, timed):
     # stylised images as they were before the iteration, and the slot receiving this frame's stylised output
     frame_buf, old_content, old_stylized, next_stylized = (torch.empty_like(dev_frames[0]) for _ in range(4))
     train_closure = net.video_training_closure(frame_buf, old_content, old_stylized, next_stylized, loss_net, bucket,
-                                               temporal_weight=0.8, graph=not args.no_graph)
+                                               temporal_weight=0.8, graph=not args.no_graph, optimizer=opt)
     state = {'t': 0, 'last': None, 'resident': True}
 
     def closure():
@@ -304,7 +304,7 @@ def run_video_st(args, rank, world, dev, L, timed):
     ms = timed(step, args.steps)
     launches = L.st_launch_count() - n0
     if hasattr(train_closure, 'launches'):
-        launches = (train_closure.launches + 2) * args.steps     # kernels inside the replayed graph + the Adam step
+        launches = train_closure.launches * args.steps           # kernels inside the replayed graph (Adam included)
     state['t'], state['resident'] = 0, False
     e2e_step = HostFedStep(host_frames, frame_buf, step, lambda: state['last'])
     for _ in range(2):

@@ -70,6 +70,11 @@ int st_nchw_to_nhwc(const float* a, const float* b, void* hi, void* lo, int plan
 /* slot (optional): scale slot of the tensor; the values are multiplied by slot[1] */
 int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, const float* slot, float* out,
                     int N, int C, int H, int W, int Cpad, void* stream);
+/* Image boundary on the device (reference img_utils.py:33-42 ToTensor + Normalize, and :105-109 de-normalise + clamp
+ * of imshow): u8 HWC [N][H][W][3] (device) <-> normalised NCHW fp32 [N][3][H][W]; mean3 / std3 are HOST arrays of
+ * three floats (constants.py:16-17).  Separately rounded IEEE operations: bit-identical to the reference's CPU code. */
+int st_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, void* stream);
+int st_image_nchw_to_u8(const float* in, unsigned char* out, int N, int H, int W, const float* mean3, const float* std3, void* stream);
 /* nn.Conv2d.weight [Cout][Cin][ks][ks] fp32 -> packed [rows_pad][ks*ks][cols_pad] split-bf16.
  * mode 0 forward; 1 backward-data (gather form, any stride); 2 backward-data as a
  * forward conv with flipped taps (stride 1). */
@@ -227,12 +232,15 @@ int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const
  * device int[nseg] (torch's per-parameter step count; active = the tensor has a gradient).
  * `chunks` is a device copy of the table st_adam_fill_chunks() writes on the host
  * (st_adam_chunk_count() entries of 16 bytes).  grad_scale multiplies the gradient first
- * (1/world of the data-parallel average). */
+ * (1/world of the data-parallel average).  packs (optional): device array of nseg 88-byte records
+ *   { int64 seg_off; int32 cout, cin, ks, ndst; { void* hi; void* lo; int32 rows_pad, cols_pad, mode, code; } dst[2]; }
+ * describing the packed copies (st_pack_conv_weight layouts, plane code `code`) of each convolution weight: the
+ * kernel rewrites them from the updated fp32 value, so no packing launch follows an optimizer step. */
 size_t st_adam_chunk_count(const long long* seg_numel, int nseg);
 int st_adam_fill_chunks(const long long* seg_numel, int nseg, void* host_chunks);
 int st_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, const void* chunks,
                  size_t nchunks, int* steps, const int* active, int nseg, double lr, double beta1, double beta2,
-                 double eps, double weight_decay, double grad_scale, void* stream);
+                 double eps, double weight_decay, double grad_scale, const void* packs, void* stream);
 /* One iteration of torch.optim.LBFGS (no line search; network.py:435, :456) on the flat fp32
  * vector x [n] given the gradient and the loss of the closure at x (device pointers): history
  * update, two-loop recursion in coefficient space, x += t*d, torch's stopping rules on a device

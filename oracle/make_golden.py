@@ -86,6 +86,44 @@ def gatys_case(ref, name, h, w, sw=100_000.0, cw=1.0):
         style_target_gram0=targets[0].numpy())
 
 
+# a NON-DEFAULT loss-layer set (the reference's builder is generic over these class attributes, network.py:214-232):
+# style nodes on conv, ReLU and max-pool layers up to conv 9, content nodes on ReLU_7 and Conv2d_10, feature node on ReLU_10
+GENERIC_LAYERS = dict(style=['Conv2d_1', 'ReLU_2', 'Conv2d_3', 'MaxPool2d_4', 'Conv2d_6', 'Conv2d_9'],
+                      content=['ReLU_7', 'Conv2d_10'], feature=['ReLU_10'])
+GENERIC_CONVS = 10
+
+
+def generic_case(name, h, w, sw=100_000.0, cw=1.0):
+    """The reference's StyleNetwork with edited layer lists (a subclass), closure body of train_gatys."""
+    ref = reference_shim.load_reference(vgg_seed=1, n_convs=GENERIC_CONVS)
+    vw = oracle.make_vgg_weights(1, GENERIC_CONVS)
+
+    class Net(ref.StyleNetwork):
+        style_layers, content_layers, feature_loss_layers = GENERIC_LAYERS['style'], GENERIC_LAYERS['content'], GENERIC_LAYERS['feature']
+    content, style = seeded((1, 3, h, w), 10), seeded((1, 3, h, w), 11)
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12)
+    net = Net(style, content)
+    pieces = [[n for n, _ in p.named_children()] for p in net.net_pieces]
+    x = x0.clone().requires_grad_(True)
+    net(x, content)
+    s, c, per_node = ref_closure_losses(net, sw, cw)
+    (s + c).backward()
+    o_total, o_grad, o_losses = oracle.generic_closure(x0, content, style, vw, GENERIC_LAYERS['style'], GENERIC_LAYERS['content'],
+                                                       GENERIC_LAYERS['feature'], sw, cw)
+    errs = dict(total=abs(o_total.item() - (s + c).item()) / abs((s + c).item()), grad=rel(o_grad, x.grad),
+                losses=rel(o_losses, per_node.detach()))
+    print(name, 'oracle-vs-reference', errs)
+    assert errs['total'] < 1e-5 and errs['grad'] < 1e-4 and errs['losses'] < 1e-5, errs
+    with torch.no_grad():
+        through_all = net.run_through_pieces(content)
+    np.savez_compressed(os.path.join(GOLDEN, name + '.npz'), h=h, w=w, sw=sw, cw=cw, total=np.float64((s + c).item()),
+                        losses=per_node.detach().numpy(), grad=x.grad.numpy(),
+                        piece_of_style=np.array([p for _, p in net.style_losses]),
+                        piece_of_content=np.array([p for _, p in net.content_losses]),
+                        piece_of_feature=np.array([p for _, p in net.feature_losses]),
+                        n_pieces=len(pieces), through_all_shape=np.array(through_all.shape))
+
+
 def load_params(module, params):
     sd = module.state_dict()
     assert set(sd.keys()) == set(params.keys()), set(sd.keys()) ^ set(params.keys())
@@ -217,6 +255,7 @@ def main():
     gatys_case(ref, 'gatys_64x64', 64, 64)
     gatys_case(ref, 'gatys_40x56', 40, 56)       # ragged: not a multiple of the 8x16 tile
     gatys_case(ref, 'gatys_256x256', 256, 256)   # BASELINE configs[0] size, from the live reference
+    generic_case('gatys_generic_64x96', 64, 96)  # non-default loss layers (reloads the reference with 10 seeded convs)
     fast_case(ref, 'fast_st_b2_32', 2, 32)
     video_case(ref, 'video_st_b2_32', 2, 32)
     print('golden fixtures written to', GOLDEN)

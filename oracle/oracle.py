@@ -34,8 +34,23 @@ CONTENT_TAP = 3          # 'Conv2d_4'   network.py:214-220
 FEATURE_TAP = 3          # 'ReLU_4' = relu(Conv2d_4)  network.py:230-232
 
 
-def make_vgg_weights(seed=1):
-    """Seeded random-init weights for the five executed VGG-19 convs.
+# torchvision VGG-19 configuration "E" (all 16 convs): (cin, cout, pool_after) per conv
+VGG_CFG_E = [64, 64, 'M', 128, 128, 'M', 256, 256, 256, 256, 'M', 512, 512, 512, 512, 'M', 512, 512, 512, 512, 'M']
+
+
+def vgg_blocks():
+    out, cin = [], 3
+    for i, v in enumerate(VGG_CFG_E):
+        if v == 'M':
+            continue
+        out.append((cin, v, i + 1 < len(VGG_CFG_E) and VGG_CFG_E[i + 1] == 'M'))
+        cin = v
+    return out
+
+
+def make_vgg_weights(seed=1, n=5):
+    """Seeded random-init weights for the first ``n`` VGG-19 convs (the default loss layers execute five; the
+    first five draws do not depend on n).
 
     torchvision's VGG init (kaiming-normal fan_out, zero bias) restated with an
     explicit generator so that no torchvision import is needed on the GPU box.
@@ -43,7 +58,7 @@ def make_vgg_weights(seed=1):
     """
     g = torch.Generator().manual_seed(seed)
     out = []
-    for cin, cout, _ in VGG_PREFIX:
+    for cin, cout, _ in vgg_blocks()[:n]:
         std = math.sqrt(2.0 / (cout * 9))
         w = torch.randn(cout, cin, 3, 3, generator=g) * std
         b = torch.randn(cout, generator=g) * 0.05
@@ -65,6 +80,59 @@ def vgg_taps(x, weights, upto=5):
         x = F.conv2d(x, w, b, padding=1)
         taps.append(x)
     return taps
+
+
+def vgg_layer_outputs(x, weights, names):
+    """{name: output of that layer} for layers of vgg19().features named as the reference names them
+    (network.py:257-270: 'Conv2d_k' / 'ReLU_k' / 'MaxPool2d_k', k counts the convs); ReLU not in place, zero padding."""
+    want, out = set(names), {}
+    for k, ((w, b), (_, _, pool)) in enumerate(zip(weights, vgg_blocks()), start=1):
+        x = F.conv2d(x, w, b, padding=1)
+        if f'Conv2d_{k}' in want:
+            out[f'Conv2d_{k}'] = x
+        x = F.relu(x)
+        if f'ReLU_{k}' in want:
+            out[f'ReLU_{k}'] = x
+        if pool:
+            x = F.max_pool2d(x, 2, 2)
+            if f'MaxPool2d_{k}' in want:
+                out[f'MaxPool2d_{k}'] = x
+        if len(out) == len(want):
+            break
+    missing = want - set(out)
+    assert not missing, f'layers not reached with {len(weights)} conv weights: {sorted(missing)}'
+    return out
+
+
+def generic_closure(x, content_image, style_image, weights, style_layers, content_layers, feature_layers=(),
+                    style_weight=100_000.0, content_weight=1.0):
+    """StyleNetwork.forward + the Gatys closure (network.py:366-401, :438-454) for ARBITRARY loss-layer lists
+    (the reference's piece builder is generic over its class attributes, network.py:214-232, :257-314).
+    Returns (total, grad of x, per-node losses [style..., content..., feature...] in network order)."""
+    order = {}
+    k = 0
+    for i, v in enumerate(VGG_CFG_E):
+        if v != 'M':
+            k += 1
+            order[f'Conv2d_{k}'] = 3 * i
+            order[f'ReLU_{k}'] = 3 * i + 1
+        else:
+            order[f'MaxPool2d_{k}'] = 3 * i
+    srt = lambda names: sorted(names, key=lambda n: order[n])
+    style_layers, content_layers, feature_layers = srt(style_layers), srt(content_layers), srt(feature_layers)
+    names = set(style_layers) | set(content_layers) | set(feature_layers)
+    with torch.no_grad():
+        s_out = vgg_layer_outputs(style_image, weights, style_layers) if style_layers else {}
+        c_out = vgg_layer_outputs(content_image, weights, set(content_layers) | set(feature_layers))
+    x = x.detach().clone().requires_grad_(True)
+    out = vgg_layer_outputs(x, weights, names)
+    losses = [style_loss(out[n], gram_matrix(s_out[n])) for n in style_layers]
+    losses += [content_loss(out[n], c_out[n]) for n in content_layers]
+    losses += [feature_loss(out[n], c_out[n]) for n in feature_layers]
+    ns, nc = len(style_layers), len(content_layers)
+    total = style_weight * torch.stack(losses[:ns]).sum() + (content_weight * torch.stack(losses[ns:ns + nc]).sum() if nc else 0.0)
+    total.backward()
+    return total.detach(), x.grad.detach(), torch.stack(losses).detach()
 
 
 def gram_matrix(f):
@@ -228,6 +296,18 @@ def fast_st_closure(batch, params, targets, vgg_w, style_weight=100_000.0, conte
     total = (style_weight * losses[:5].sum() + content_weight * losses[5] + tv_loss(out))
     total.backward()
     return total.detach(), {k: v.grad.detach() for k, v in ps.items()}, out.detach(), losses.detach()
+
+
+def static_test(batches, params, targets, vgg_w, style_weight=100_000.0, feature_weight=1.0):
+    """ImageTransformNet.static_test (network.py:772-796): per test batch clamp(net(x), 0, 255) -> loss network with
+    the batch as content image -> style_weight * sum(style) + feature_weight * feature; the mean over the batches."""
+    losses = []
+    with torch.no_grad():
+        for batch in batches:
+            out = torch.clamp(transform_net(batch, params), min=0, max=255)
+            node, _ = loss_network(out, batch, targets, vgg_w)
+            losses.append(float(style_weight * node[:5].sum() + feature_weight * node[6]))
+    return torch.mean(torch.Tensor(losses))
 
 
 def video_closure(batch, old_content, old_stylized, params, targets, vgg_w,

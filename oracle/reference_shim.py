@@ -17,7 +17,20 @@ import types
 import torch
 import torch.nn as nn
 
-REFERENCE_ROOT = os.environ.get('STRANSFER_REFERENCE_ROOT', '/root/reference')
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _reference_root():
+    """The reference's sources in the build container; on the GPU box the sourceless bytecode staged by
+    ``oracle/build_ref.py`` under ``oracle/_ref`` (git-ignored, travels with gpurun)."""
+    for cand in (os.environ.get('STRANSFER_REFERENCE_ROOT'), '/root/reference', os.path.join(_HERE, '_ref')):
+        if cand and (os.path.isfile(os.path.join(cand, 'stransfer', 'network.py')) or
+                     os.path.isfile(os.path.join(cand, 'stransfer', 'network.pyc'))):
+            return cand
+    return '/root/reference'
+
+
+REFERENCE_ROOT = _reference_root()
 
 
 def available():
@@ -67,8 +80,9 @@ def _conv_init(self, *a, **k):
     _ORIG_CONV_INIT(self, *a, **k)
 
 
-def load_reference(vgg_seed=1, workdir='/tmp/stransfer_ref_cwd'):
-    """Returns the reference's ``stransfer.network`` module (CPU)."""
+def load_reference(vgg_seed=1, workdir='/tmp/stransfer_ref_cwd', n_convs=5):
+    """Returns the reference's ``stransfer.network`` module (CPU).  The first ``n_convs`` convs of its VGG-19 carry
+    ``oracle.make_vgg_weights(vgg_seed, n_convs)`` (the rest keep torchvision's unseeded random init)."""
     import warnings
     import torchvision
     from oracle import oracle
@@ -78,10 +92,11 @@ def load_reference(vgg_seed=1, workdir='/tmp/stransfer_ref_cwd'):
 
     def vgg19(pretrained=False, **kw):
         m = torchvision.models.vgg.vgg19(weights=None)
+        convs = [layer for layer in m.features if isinstance(layer, nn.Conv2d)]
         with torch.no_grad():
-            for idx, (w, b) in zip(oracle.VGG_FEATURE_IDX, oracle.make_vgg_weights(vgg_seed)):
-                m.features[idx].weight.copy_(w)
-                m.features[idx].bias.copy_(b)
+            for conv, (w, b) in zip(convs, oracle.make_vgg_weights(vgg_seed, n_convs)):
+                conv.weight.copy_(w)
+                conv.bias.copy_(b)
         return m
     torchvision.models.vgg19 = vgg19
 

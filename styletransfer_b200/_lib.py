@@ -24,6 +24,8 @@ SIGNATURES = {
     'st_launch_count': (ctypes.c_longlong, []),
     'st_nchw_to_nhwc': (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
     'st_nhwc_to_nchw': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P]),
+    'st_image_u8_to_nchw': (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
+    'st_image_nchw_to_u8': (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     'st_pack_conv_weight': (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
     'st_conv2d': (_I, [_P, _P, _I, _I, _I, _I, _I, _I,      # x, planes, N H W Cin up
                        _P, _P, _I, _I, _I,                  # w, planes, rows_total, img_rows
@@ -64,7 +66,7 @@ SIGNATURES = {
     'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
     'st_adam_chunk_count': (_Z, [_P, _I]),
     'st_adam_fill_chunks': (_I, [_P, _I, _P]),
-    'st_adam_step': (_I, [_P, _P, _P, _P, _P, _Z, _P, _P, _I, _D, _D, _D, _D, _D, _D, _P]),
+    'st_adam_step': (_I, [_P, _P, _P, _P, _P, _Z, _P, _P, _I, _D, _D, _D, _D, _D, _D, _P, _P]),
     'st_lbfgs_state_bytes': (_Z, [_I, _Z]),
     'st_set_lbfgs_variant': (_I, [_I]),
     'st_lbfgs_init': (_I, [_P, _I, _Z, _D, _D, _D, _P]),

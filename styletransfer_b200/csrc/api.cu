@@ -52,6 +52,8 @@ int ew_mse_bwd(const bf16*, const bf16*, int, const bf16*, const bf16*, int, siz
 int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, float*, cudaStream_t);
 int ew_style_seed(const float*, int, int, float, const float*, bf16*, bf16*, int, const float*, float*, cudaStream_t);
 int ew_absmax_slot(const float*, size_t, float, float*, float*, cudaStream_t);
+int ew_image_u8_to_nchw(const unsigned char*, float*, int, int, int, const float*, const float*, cudaStream_t);
+int ew_image_nchw_to_u8(const float*, unsigned char*, int, int, int, const float*, const float*, cudaStream_t);
 int ew_channel_sum(const bf16*, const bf16*, int, const float*, int, int, int, float*, float*, cudaStream_t);
 size_t in_workspace_floats(int N, int C);
 int in_forward(const bf16*, const bf16*, const float*, const float*, float, bf16*, bf16*, int, float*, float*, int, int, int, int, int, int, float*, cudaStream_t);
@@ -91,6 +93,14 @@ int st_nhwc_to_nchw(const void* hi, const void* lo, int planes, const float* slo
     ST_CHECK_ARG(hi && out && N > 0 && H > 0 && W > 0, "st_nhwc_to_nchw: null pointer or empty shape");
     ST_CHECK_ARG(Cpad % 8 == 0 && C <= Cpad, "st_nhwc_to_nchw: Cpad must be a multiple of 8 and >= C");
     return ew_nhwc_to_nchw(CBF(hi), CBF(lo), one_plane_if_no_lo(planes, lo), slot, out, N, C, H, W, Cpad, STRM(stream));
+}
+int st_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, void* stream) {
+    ST_CHECK_ARG(in && out && mean3 && std3 && N > 0 && H > 0 && W > 0, "st_image_u8_to_nchw: null pointer or empty shape");
+    return ew_image_u8_to_nchw(in, out, N, H, W, mean3, std3, STRM(stream));
+}
+int st_image_nchw_to_u8(const float* in, unsigned char* out, int N, int H, int W, const float* mean3, const float* std3, void* stream) {
+    ST_CHECK_ARG(in && out && mean3 && std3 && N > 0 && H > 0 && W > 0, "st_image_nchw_to_u8: null pointer or empty shape");
+    return ew_image_nchw_to_u8(in, out, N, H, W, mean3, std3, STRM(stream));
 }
 int st_pack_conv_weight(const float* w, void* hi, void* lo, int planes, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, void* stream) {
     ST_CHECK_ARG(w && hi, "st_pack_conv_weight: null pointer");

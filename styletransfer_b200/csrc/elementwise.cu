@@ -406,6 +406,36 @@ channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, in
     }
 }
 
+// ---------------------------------------------------------------------------
+// Image boundary (reference img_utils.py:33-42 and :105-109), one thread per pixel:
+//   u8 HWC [N][H][W][3] -> normalised NCHW fp32: ((x / 255) - mean) / std      (ToTensor + Normalize)
+//   NCHW fp32 -> u8 HWC: clamp(x * std + mean, 0, 1) * 255 + 0.5               (imshow's de-normalise + clamp)
+// Every operation is a separately rounded IEEE fp32 op (no FMA contraction), so the results are bit-identical to
+// the numpy / torch CPU code of the reference.
+// ---------------------------------------------------------------------------
+struct ImgStats { float mean[3], std[3]; };
+__global__ void image_u8_to_nchw_kernel(const unsigned char* __restrict__ in, float* __restrict__ out, size_t pixels, size_t HW, ImgStats st) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    const size_t n = i / HW, px = i - n * HW;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float v = __fdiv_rn(static_cast<float>(in[i * 3 + c]), 255.0f);
+        out[(n * 3 + c) * HW + px] = __fdiv_rn(__fsub_rn(v, st.mean[c]), st.std[c]);
+    }
+}
+__global__ void image_nchw_to_u8_kernel(const float* __restrict__ in, unsigned char* __restrict__ out, size_t pixels, size_t HW, ImgStats st) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    const size_t n = i / HW, px = i - n * HW;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float v = __fadd_rn(__fmul_rn(in[(n * 3 + c) * HW + px], st.std[c]), st.mean[c]);
+        v = fminf(fmaxf(v, 0.0f), 1.0f);
+        out[i * 3 + c] = static_cast<unsigned char>(__fadd_rn(__fmul_rn(v, 255.0f), 0.5f));      // truncation, as torch's .to(uint8)
+    }
+}
+
 inline int grid_for(size_t n, int block, int cap_mult = 8) {
     size_t g = (n + block - 1) / block;
     size_t cap = static_cast<size_t>(st_num_sms()) * cap_mult;
@@ -484,6 +514,18 @@ int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw,
     const int total = B * C * C;
     style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl, code, diff_amax, slot);
     ST_CHECK_LAUNCH("style_seed_kernel"); return ST_OK;
+}
+int ew_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
+    ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }
+    const size_t px = static_cast<size_t>(N) * H * W;
+    image_u8_to_nchw_kernel<<<(px + 255) / 256, 256, 0, st>>>(in, out, px, static_cast<size_t>(H) * W, s);
+    ST_CHECK_LAUNCH("image_u8_to_nchw_kernel"); return ST_OK;
+}
+int ew_image_nchw_to_u8(const float* in, unsigned char* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
+    ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }
+    const size_t px = static_cast<size_t>(N) * H * W;
+    image_nchw_to_u8_kernel<<<(px + 255) / 256, 256, 0, st>>>(in, out, px, static_cast<size_t>(H) * W, s);
+    ST_CHECK_LAUNCH("image_nchw_to_u8_kernel"); return ST_OK;
 }
 // slot = {s, 1/s}: power of two mapping max|x| to 2^target_log2; ws >= 1024 floats
 int ew_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, cudaStream_t st) {

@@ -30,14 +30,49 @@
 // ============================================================================ Adam
 struct AdamChunk { unsigned long long off; unsigned int n; int seg; };
 #define ADAM_CHUNK 2048
+// Optional per-segment description of the PACKED copies of a convolution weight (st_pack_conv_weight layouts) that
+// the Adam kernel rewrites together with the fp32 master value, so that no separate packing launch is needed after
+// an optimizer step.  88 bytes per segment; ndst = 0 for tensors without packed copies.
+struct AdamPackDst { void* hi; void* lo; int rows_pad, cols_pad, mode, code; };
+struct AdamPackSeg { long long seg_off; int cout, cin, ks, ndst; AdamPackDst dst[2]; };
+static_assert(sizeof(AdamPackSeg) == 88, "AdamPackSeg layout is part of the ABI (optim.py builds it)");
+
+__device__ __forceinline__ void adam_store_packed(const AdamPackSeg& ps, long long idx, float value) {
+    const int taps = ps.ks * ps.ks;
+    long long q = idx;
+    const int s = (int)(q % ps.ks); q /= ps.ks;
+    const int r = (int)(q % ps.ks); q /= ps.ks;
+    const int ci = (int)(q % ps.cin); const int co = (int)(q / ps.cin);
+    for (int d = 0; d < ps.ndst; ++d) {
+        const AdamPackDst& D = ps.dst[d];
+        int row, col, tap;
+        if (D.mode == 0) { row = co; col = ci; tap = r * ps.ks + s; }
+        else { row = ci; col = co; tap = (D.mode == 2) ? (ps.ks - 1 - r) * ps.ks + (ps.ks - 1 - s) : r * ps.ks + s; }
+        const size_t o = (static_cast<size_t>(row) * taps + tap) * D.cols_pad + col;
+        uint16_t* hi = static_cast<uint16_t*>(D.hi);
+        uint16_t* lo = static_cast<uint16_t*>(D.lo);
+        if (pc_f16(D.code)) {
+            uint32_t h2, l2; split2h(value * ST_W_F16_SCALE, 0.f, h2, l2);
+            hi[o] = static_cast<uint16_t>(h2 & 0xffffu);
+            if (lo && pc_planes(D.code) > 1) lo[o] = static_cast<uint16_t>(l2 & 0xffffu);
+        } else {
+            bf16 h, l; split_bf16(value, h, l);
+            hi[o] = __bfloat16_as_ushort(h);
+            if (lo && pc_planes(D.code) > 1) lo[o] = __bfloat16_as_ushort(l);
+            if (lo && pc_planes(D.code) > 2)
+                (lo + (lo - hi))[o] = __bfloat16_as_ushort(__float2bfloat16_rn(value - __bfloat162float(h) - __bfloat162float(l)));
+        }
+    }
+}
 
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, const AdamChunk* __restrict__ chunks,
                                                    const int* __restrict__ steps, const int* __restrict__ active,
                                                    double lr, double b1d, double b2d, float omb1, float omb2, float eps, float wd,
-                                                   float gscale) {
+                                                   float gscale, const AdamPackSeg* __restrict__ packs) {
     const AdamChunk c = chunks[blockIdx.x];
     if (!active[c.seg]) return;
+    const bool repack = packs && packs[c.seg].ndst > 0;
     __shared__ float s_step_size, s_rsqrt_bc2;
     if (threadIdx.x == 0) {
         const double t = (double)(steps[c.seg] + 1);
@@ -57,7 +92,9 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
         const float ve = fmaf(gr * omb2, gr, v[e] * b2);
         const float denom = __fdiv_rn(__fsqrt_rn(ve), bc2_sqrt) + eps;
         m[e] = me; v[e] = ve;
-        p[e] = pe - step_size * __fdiv_rn(me, denom);
+        const float pn = pe - step_size * __fdiv_rn(me, denom);
+        p[e] = pn;
+        if (repack) adam_store_packed(packs[c.seg], (long long)e - packs[c.seg].seg_off, pn);
     }
 }
 __global__ void adam_tick_kernel(int* steps, const int* active, int nseg) {
@@ -85,13 +122,13 @@ extern "C" int st_adam_fill_chunks(const long long* seg_numel, int nseg, void* h
 }
 extern "C" int st_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, const void* chunks,
                             size_t nchunks, int* steps, const int* active, int nseg, double lr, double beta1, double beta2,
-                            double eps, double weight_decay, double grad_scale, void* stream) {
+                            double eps, double weight_decay, double grad_scale, const void* packs, void* stream) {
     ST_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && chunks && steps && active && nchunks > 0 && nseg > 0,
                  "st_adam_step: null pointer or empty table");
     cudaStream_t st = (cudaStream_t)stream;
     adam_kernel<<<(unsigned)nchunks, 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, (const AdamChunk*)chunks, steps, active,
                                                     lr, beta1, beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps,
-                                                    (float)weight_decay, (float)grad_scale);
+                                                    (float)weight_decay, (float)grad_scale, (const AdamPackSeg*)packs);
     ST_CHECK_LAUNCH("adam_kernel");
     adam_tick_kernel<<<(nseg + 127) / 128, 128, 0, st>>>(steps, active, nseg);
     ST_CHECK_LAUNCH("adam_tick_kernel");

@@ -152,8 +152,8 @@ class VideoDataset:
 
 def iterate_on_video_batches(batch, max_frames=90 * 24):
     """dataset.py:280-311: yields [B, 3, S, S] tensors, one frame from each reader, until the
-    shortest clip ends.  An iterable of ready tensors is passed through unchanged."""
-    if not isinstance(batch, (list, tuple)) or (batch and isinstance(batch[0], torch.Tensor)):
+    shortest clip ends.  An iterable of ready tensors (or of (frames, flow) pairs) is passed through unchanged."""
+    if not isinstance(batch, (list, tuple)) or (batch and isinstance(batch[0], (torch.Tensor, tuple))):
         yield from batch
         return
     try:

@@ -105,19 +105,23 @@ class GradBucket:
                 p.grad = self.flat[off:off + n].view_as(p)
             off += n
 
-    def all_reduce(self):
+    def all_reduce(self, average=True):
+        """``average=False`` leaves the SUM over the ranks in the bucket: the fused Adam kernel folds the 1/world into
+        its gradient read (``optim.FusedAdam.grad_scale``), which saves the separate scaling pass."""
         world = world_size()
         if world == 1:
             return
         if self._side is None:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            self.flat.mul_(1.0 / world)
+            if average:
+                self.flat.mul_(1.0 / world)
             return
         cur = torch.cuda.current_stream(self.flat.device)
         self._side.wait_stream(cur)
         with torch.cuda.stream(self._side):
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
-            self.flat.mul_(1.0 / world)
+            if average:
+                self.flat.mul_(1.0 / world)
         cur.wait_stream(self._side)
 
     def nbytes(self):

@@ -215,14 +215,9 @@ class FeatureReconstructionLoss(ContentLoss):
 # --------------------------------------------------------------------------
 # VGG-19 loss network (reference network.py:204-458)
 # --------------------------------------------------------------------------
-_VGG_CFG_E = [64, 64, 'M', 128, 128, 'M', 256, 256, 256, 256, 'M',
-              512, 512, 512, 512, 'M', 512, 512, 512, 512, 'M']
-# torchvision vgg19().features indices of the five convs that are ever executed (SURVEY F1)
-_VGG_CONV_IDX = [0, 2, 5, 7, 10]
-
-
-def load_vgg19_prefix_weights(seed=None):
-    """[(weight, bias)] x5 for conv1_1, conv1_2, conv2_1, conv2_2, conv3_1 on DEVICE.
+def load_vgg19_prefix_weights(seed=None, n_convs=16):
+    """[(weight, bias)] for the first ``n_convs`` convs of torchvision's vgg19().features on DEVICE (all 16 by
+    default; the reference's default loss layers execute the first five).
 
     The reference uses ``torchvision.models.vgg19(pretrained=True)`` (network.py:246) and fails when the
     checkpoint cannot be obtained; so does this function (``StransferError``).  A seeded random-init VGG-19
@@ -240,33 +235,31 @@ def load_vgg19_prefix_weights(seed=None):
             raise StransferError('the pretrained VGG-19 weights could not be loaded (%s: %s); pass vgg_weights= / seed=, '
                                  'or set STRANSFER_VGG_SEED to opt in to a seeded random-init loss network'
                                  % (type(exc).__name__, exc)) from exc
-        return [(feats[i].weight.detach().to(constants.DEVICE), feats[i].bias.detach().to(constants.DEVICE))
-                for i in _VGG_CONV_IDX]
+        convs = [m for m in feats if isinstance(m, nn.Conv2d)][:n_convs]
+        return [(m.weight.detach().to(constants.DEVICE), m.bias.detach().to(constants.DEVICE)) for m in convs]
     g = torch.Generator().manual_seed(seed)
     out = []
-    for cin, cout, _ in vgg_loss.PREFIX:
+    for cin, cout, _ in vgg_loss.BLOCKS[:n_convs]:
         w = torch.randn(cout, cin, 3, 3, generator=g) * math.sqrt(2.0 / (cout * 9))
         out.append((w.to(constants.DEVICE), torch.zeros(cout, device=constants.DEVICE)))
     return out
 
 
 class StyleNetwork(nn.Module):
-    """network.py:204-458.  ``vgg_weights`` (extra, optional) supplies the five
-    (weight, bias) pairs explicitly -- tests and benchmarks pass seeded ones."""
+    """network.py:204-458.  ``vgg_weights`` (extra, optional) supplies the (weight, bias) pairs of the first n VGG-19
+    convs explicitly -- tests and benchmarks pass seeded ones; n must cover the deepest loss layer.
+
+    As in the reference the loss layers are CLASS attributes a user may edit (a subclass, or assignment before
+    construction): any ``Conv2d_k`` / ``ReLU_k`` / ``MaxPool2d_k`` name of ``vgg19().features`` (k = 1..16 counts the
+    convolutions, network.py:257-270).  The network is cut into pieces after every loss layer exactly like the
+    reference's builder (network.py:257-314); the compute runs through ONE fused pass (vgg_loss.py)."""
 
     content_layers = ['Conv2d_4']
     style_layers = ['Conv2d_1', 'Conv2d_2', 'Conv2d_3', 'Conv2d_4', 'Conv2d_5']
     feature_loss_layers = ['ReLU_4']
 
-    # layer name -> (piece index, tap index, relu applied) for the supported taps
-    _SUPPORTED = {'Conv2d_1': 0, 'Conv2d_2': 1, 'Conv2d_3': 2, 'Conv2d_4': 3, 'Conv2d_5': 4}
-
     def __init__(self, style_image: torch.Tensor, content_image: torch.Tensor = None, vgg_weights=None):
         super().__init__()
-        if (self.content_layers != ['Conv2d_4'] or self.feature_loss_layers != ['ReLU_4'] or
-                self.style_layers != ['Conv2d_%d' % i for i in range(1, 6)]):
-            raise NotImplementedError('the B200 loss network implements the reference default tap set '
-                                      '(style Conv2d_1..5, content Conv2d_4, feature ReLU_4)')
         ops._require_cuda(style_image, 'StyleNetwork')
         dev = style_image.device
         if content_image is None:
@@ -276,64 +269,95 @@ class StyleNetwork(nn.Module):
         self.vgg = vgg_loss.VGGPrefix(weights)
         self.compute_feature_loss = True
 
-        # the same 7 pieces the reference cuts (network.py:257-314), kept as plain
-        # containers for introspection; compute goes through self.vgg
-        self.net_pieces = self._build_pieces(weights)
+        # the pieces the reference cuts (network.py:257-314): a new piece starts after every loss layer; kept as
+        # plain containers for introspection (and run_through_pieces' indexing), compute goes through self.vgg
+        self.net_pieces, piece_of = self._build_pieces(weights)
+        self._piece_last = {}                            # piece index -> last layer point inside pieces[: index + 1]
+        last = None
+        for i, piece in enumerate(self.net_pieces):
+            names = [n for n, _ in piece.named_children()]
+            if names:
+                last = vgg_loss.parse_layer(names[-1])
+            self._piece_last[i] = last
 
-        # targets: network.py:280-307
-        with torch.no_grad():
-            staps = self.vgg.taps(style_image)
-            ctaps = self.vgg.taps(content_image, upto=4)
-        self.style_losses = []
-        for i, tap in enumerate(staps):
+        def points(names, what):
+            pts = []
+            for name in names:
+                pt = vgg_loss.parse_layer(name)
+                if name not in piece_of:
+                    raise StransferError(f'{what} layer {name} needs VGG conv {pt[1]} but only {len(weights)} conv weights were given')
+                pts.append((name, pt))
+            # the reference appends a layer's node when it reaches the layer: network order, not list order
+            return sorted(pts, key=lambda t: vgg_loss.layer_names().index(t[0]))
+        style_pts = points(self.style_layers, 'style')
+        content_pts = points(self.content_layers, 'content')
+        feature_pts = points(self.feature_loss_layers, 'feature')
+
+        # targets: network.py:280-307 (style nodes from the style image, content / feature nodes from the content image)
+        self._spec = vgg_loss.LossSpec([[pt, None] for _, pt in style_pts], [[pt, None] for _, pt in content_pts],
+                                       [[pt, None] for _, pt in feature_pts])
+        self.style_losses, self.content_losses, self.feature_losses = [], [], []
+        for name, _ in style_pts:
             node = StyleLoss.__new__(StyleLoss)
             nn.Module.__init__(node)
-            node.target = ops.gram(tap)
-            self.style_losses.append([node, [0, 1, 2, 3, 5][i]])
-        self.content_losses = [[ContentLoss(ctaps[3]), 3]]
-        self.feature_losses = [[FeatureReconstructionLoss(self._relu_split(ctaps[3])), 4]]
+            self.style_losses.append([node, piece_of[name]])
+        for name, _ in content_pts:
+            node = ContentLoss.__new__(ContentLoss)
+            nn.Module.__init__(node)
+            self.content_losses.append([node, piece_of[name]])
+        for name, _ in feature_pts:
+            node = FeatureReconstructionLoss.__new__(FeatureReconstructionLoss)
+            nn.Module.__init__(node)
+            self.feature_losses.append([node, piece_of[name]])
+        self._set_style_targets(style_image)
         self._content_key = None
+        self._set_content(content_image)
 
     @staticmethod
     def _relu_split(tap):
-        """relu of a Split (the ReLU_4 feature target).  Off the hot path (targets only)."""
+        """relu of a Split (the value of a ReLU_k layer from the conv output).  Off the hot path (targets only)."""
         return tap.like().set_from_float(tap.float().clamp_(min=0))
 
-    @staticmethod
-    def _build_pieces(weights):
-        """Pieces 0..5 hold the layers the losses execute; piece 6 (conv3_2 .. pool5,
-        never run by the reference) is left as an empty placeholder."""
-        layers, i, cin = [], 0, 3
-        for v in _VGG_CFG_E[:7]:
-            if v == 'M':
-                layers.append(('MaxPool2d_%d' % i, nn.MaxPool2d(2, 2)))
-                continue
-            i += 1
-            conv = nn.Conv2d(cin, v, 3, padding=1)
-            conv.weight.data, conv.bias.data = weights[i - 1]
-            layers.append(('Conv2d_%d' % i, conv))
-            if i < 5:
-                layers.append(('ReLU_%d' % i, nn.ReLU(inplace=False)))
-            cin = v
-        cuts = {'Conv2d_1', 'Conv2d_2', 'Conv2d_3', 'Conv2d_4', 'ReLU_4', 'Conv2d_5'}
-        pieces = [nn.Sequential()]
-        for name, layer in layers:
-            pieces[-1].add_module(name, layer)
-            if name in cuts:
-                pieces.append(nn.Sequential())
-        return pieces
+    def _build_pieces(self, weights):
+        """Generic over the three layer lists (network.py:257-314): every layer of the available VGG blocks goes into
+        the current piece under the reference's name; after a layer that carries a loss node a new piece starts.
+        Returns (pieces, {loss layer name: index of its piece})."""
+        cuts = set(self.content_layers) | set(self.style_layers) | set(self.feature_loss_layers)
+        pieces, piece_of = [nn.Sequential()], {}
+        for k, (cin, cout, pool) in enumerate(vgg_loss.BLOCKS[:len(weights)], start=1):
+            conv = nn.Conv2d(cin, cout, 3, padding=1)
+            conv.weight.data, conv.bias.data = weights[k - 1]
+            layers = [(f'Conv2d_{k}', conv), (f'ReLU_{k}', nn.ReLU(inplace=False))]
+            if pool:
+                layers.append((f'MaxPool2d_{k}', nn.MaxPool2d(2, 2)))
+            for name, layer in layers:
+                pieces[-1].add_module(name, layer)
+                if name in cuts:
+                    piece_of[name] = len(pieces) - 1
+                    pieces.append(nn.Sequential())
+        return pieces, piece_of
 
     def run_through_pieces(self, input_g: torch.Tensor, until=-1) -> torch.Tensor:
-        """network.py:316-340.  Pieces 0..5 (everything a loss node reads) run on the
-        kernels; the unused tail (piece 6, conv3_2..pool5) is not implemented."""
+        """network.py:316-340: the input through pieces[: until + 1] (all pieces for -1), on the kernels."""
         ops._require_cuda(input_g, 'StyleNetwork.run_through_pieces')
-        if until == -1 or until > 5:
-            raise NotImplementedError('pieces beyond Conv2d_5 are never executed by the reference losses')
-        tap_idx = {0: 0, 1: 1, 2: 2, 3: 3, 4: 3, 5: 4}[until]
+        n = len(self.net_pieces)
+        idx = n - 1 if until == -1 else min(until, n - 1)
+        point = self._piece_last[idx]
+        if point is None:
+            return input_g
         with torch.no_grad():
-            tap = self.vgg.taps(input_g, upto=tap_idx + 1)[tap_idx]
-            out = ops.to_nchw(tap)
-        return out.clamp_(min=0) if until == 4 else out
+            return self.vgg.value_at(input_g, point)
+
+    def _set_style_targets(self, image):
+        """Gram targets of the style nodes from ``image`` (network.py:297-301)."""
+        pts = self._spec.points(style=True, mse=False)
+        if not pts:
+            return
+        with torch.no_grad():
+            vals, _ = self.vgg.run(image.detach(), pts, keep_taps=False)
+            for (node, _), entry in zip(self.style_losses, self._spec.style):
+                node.target = ops.gram(vals[entry[0]])
+                entry[1] = node.target
 
     def get_total_current_content_loss(self, weight=1) -> torch.Tensor:
         """network.py:342-348"""
@@ -353,30 +377,45 @@ class StyleNetwork(nn.Module):
         image to every closure); the cache holds a strong reference to that tensor, so its storage cannot be
         recycled for another image while the key is alive, and the loops that feed new batches reset it."""
         key = self._content_key
-        if key is None or key[0] is not content_image or key[1] != content_image._version:
+        if key is not None and key[0] is content_image and key[1] == content_image._version and key[2] == self.compute_feature_loss:
+            return
+        pts = self._spec.points(with_feature=self.compute_feature_loss, style=False, mse=True)
+        if pts:
             with torch.no_grad():
-                tap = self.vgg.taps(content_image.detach(), upto=4, keep_all=False)[3]
-            self.content_losses[0][0].set_target(tap)
-            self.feature_losses[0][0].set_target(self._relu_split(tap) if self.compute_feature_loss else tap)
-            self._content_key = (content_image, content_image._version)
+                vals, taps = self.vgg.run(content_image.detach(), pts, keep_taps=False)
+            groups = [(self.content_losses, self._spec.content)]
+            if self.compute_feature_loss:
+                groups.append((self.feature_losses, self._spec.feature))
+            for nodes, entries in groups:
+                for (node, _), entry in zip(nodes, entries):
+                    pt = entry[0]
+                    src, relu = vgg_loss.mse_operand(pt, vals, taps)
+                    entry[1] = src                           # what the fused kernels compare against (pre-ReLU for ReLU_k)
+                    # the node's own target is the VALUE of its layer (reference semantics of node.target / node(input))
+                    node.set_target(self._relu_split(src) if relu else src)
+        self._content_key = (content_image, content_image._version, self.compute_feature_loss)
 
     def forward(self, input_image: torch.Tensor, content_image=None, style_image=None) -> None:
         """network.py:366-401: evaluates every loss node; results live in ``node.loss``."""
         ops._require_cuda(input_image, 'StyleNetwork.forward')
         if content_image is not None:
             self._set_content(content_image)
+        elif self._content_key is not None and self._content_key[2] != self.compute_feature_loss and self.compute_feature_loss:
+            self._set_content(self._content_key[0])          # the feature targets were skipped so far
         if style_image is not None:
             # bug-compatible with network.py:390-394: the *content* image sets the style targets
-            with torch.no_grad():
-                for (node, _), tap in zip(self.style_losses, self.vgg.taps(content_image)):
-                    node.target = ops.gram(tap)
-        losses = vgg_loss.vgg_losses(input_image, self.vgg, [n[0].target for n in self.style_losses],
-                                     self.content_losses[0][0]._target_split, self.compute_feature_loss)
-        self._loss_vector = losses                       # [5 style, content, feature]
-        for i, (node, _) in enumerate(self.style_losses):
+            self._set_style_targets(content_image)
+        losses = vgg_loss.vgg_losses(input_image, self.vgg, self._spec, self.compute_feature_loss)
+        self._loss_vector = losses                       # [style nodes, content nodes, feature nodes]
+        nodes = self.style_losses + self.content_losses + self.feature_losses
+        for i, (node, _) in enumerate(nodes):
             node.loss = losses[i]
-        self.content_losses[0][0].loss = losses[5]
-        self.feature_losses[0][0].loss = losses[6]
+
+    def loss_weights(self, style_weight, content_weight, feature_weight=0.0):
+        """Per-entry weights of the loss vector (device tensor)."""
+        w = ([float(style_weight)] * len(self.style_losses) + [float(content_weight)] * len(self.content_losses) +
+             [float(feature_weight)] * len(self.feature_losses))
+        return torch.tensor(w, dtype=torch.float32, device=self.vgg.device)
 
     def gatys_closure(self, input_image, content_image, style_weight=100_000, content_weight=1, graph=None):
         """The body of train_gatys' closure (network.py:438-451): zero_grad -> forward ->
@@ -386,8 +425,7 @@ class StyleNetwork(nn.Module):
 
         # style_weight * sum(style losses) + content_weight * content loss as one dot product with the
         # loss vector (an elementwise product and a sum instead of the stack / sum / mul / add chain of the getters)
-        weights = torch.tensor([float(style_weight)] * 5 + [float(content_weight), 0.0], dtype=torch.float32,
-                               device=input_image.device)
+        weights = self.loss_weights(style_weight, content_weight)
 
         def body():
             input_image.grad = None
@@ -607,24 +645,27 @@ class ImageTransformNet(nn.Sequential):
         ops._require_cuda(input, type(self).__name__ + '.forward')
         sd = dict(self.named_parameters())
         params = [sd[n] for n in transform.PARAM_NAMES]
+        if self._pack_cache.stale():               # packed copies owned by the optimizer, weights changed elsewhere
+            self._pack_cache.repack(sd)
         x = input.contiguous().float()
         if not torch.is_grad_enabled():
             return self._infer(x, params)
-        return transform.TransformNetFn.apply(x, self._pack_cache, *params)
+        return transform.TransformNetFn.apply(x, None, self._pack_cache, *params)
 
     INFER_PIXELS_PER_CHUNK = 1 << 23      # 4 frames of 1080x1920 (32-channel tensors stay below 2^31 elements)
 
-    def _infer(self, x, params):
+    def _infer(self, x, params, x2=None):
         """Forward without a graph (process_image / process_video / static_test,
         network.py:798-832, :1117-1134, :772-796): the batch goes through the fused pipeline in
         chunks of whole frames, every intermediate is released once consumed."""
         N, _, H, W = x.shape
         per = max(1, self.INFER_PIXELS_PER_CHUNK // (H * W))
         if N <= per:
-            return transform.run_forward(x, self._pack_cache, params, keep=False)[0]
+            return transform.run_forward(x, self._pack_cache, params, keep=False, x2=x2)[0]
         out = torch.empty(N, 3, H, W, dtype=torch.float32, device=x.device)
         for i in range(0, N, per):
-            out[i:i + per] = transform.run_forward(x[i:i + per], self._pack_cache, params, keep=False)[0]
+            out[i:i + per] = transform.run_forward(x[i:i + per], self._pack_cache, params, keep=False,
+                                                   x2=None if x2 is None else x2[i:i + per])[0]
         return out
 
     def stylize_host_batch(self, frames: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
@@ -718,7 +759,84 @@ class ImageTransformNet(nn.Sequential):
         finally:
             self._pack_cache.grad_sink = None
 
-    def training_closure(self, batch, loss_network, bucket, style_weight=100_000, content_weight=1, graph=None):
+
+    def _step_closure(self, body, bucket, optimizer, graph, loss_network=None):
+        """Turns the body of a training closure (zero the bucket -> forward -> backward into the bucket) into what the
+        loops hand to ``optimizer.step``.
+
+        eager:  body -> all-reduce.
+        graph, no fused optimizer: [graph: weight packing + body] -> all-reduce (average) ; the optimizer follows.
+        graph + ``optim.FusedAdam``: ONE graph replay per step holds body -> all-reduce (sum, NCCL is capturable) ->
+        Adam kernel; the 1/world of the average is the kernel's ``grad_scale`` and the kernel rewrites the packed
+        weight copies itself (no packing launches, no separate scaling pass: SURVEY section 8f rank 2).  The returned
+        callable carries ``includes_optimizer`` so that ``optimizer.step(closure)`` replays it without a second
+        update.  ``STRANSFER_GRAPH_STEP=0`` keeps the optimizer outside the graph."""
+        world = st_dist.world_size()
+        fused = isinstance(optimizer, st_optim.FusedAdam) and optimizer.bucket is bucket
+        if fused:
+            optimizer.grad_scale = 1.0 / world
+
+        def reduce():
+            bucket.all_reduce(average=not fused)
+        if not graph:
+            def eager():
+                total_loss = body()
+                reduce()
+                return total_loss
+            return eager
+        cache = self._pack_cache
+        whole_step = fused and os.environ.get('STRANSFER_GRAPH_STEP', '1') != '0'
+        if fused:
+            # one eager evaluation creates every packed weight copy the closure reads; from here on the optimizer's
+            # kernel keeps them up to date and the captured graph contains no packing kernels
+            cache.frozen = False
+            cache.entries.clear()
+            body()
+            if loss_network is not None:
+                # drop the autograd graph that evaluation left behind (node.loss): its AccumulateGrad nodes live on
+                # this stream and would invalidate the capture on the side stream
+                for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
+                    node.loss = None
+                loss_network._loss_vector = None
+            optimizer.set_packs(cache, dict(self.named_parameters()))
+            optimizer._refresh_active(optimizer.param_groups[0]['params'])
+        else:
+            cache.always_repack = True          # the packing kernels are part of every replay
+        try:
+            if whole_step:
+                def step_body():
+                    total_loss = body()
+                    reduce()
+                    optimizer.launch()
+                    return total_loss
+                # capturing must not move the weights: the warm-up runs execute the Adam kernel, so the optimizer
+                # state is saved and restored around the capture (and the packed copies rewritten from the weights)
+                state = [t.clone() for t in (optimizer.flat_param, optimizer.exp_avg, optimizer.exp_avg_sq, optimizer.steps)]
+                graphed = GraphedClosure(step_body, leaves=[p for p in self.parameters() if p.requires_grad], warmup=2)
+                for dst, src in zip((optimizer.flat_param, optimizer.exp_avg, optimizer.exp_avg_sq, optimizer.steps), state):
+                    dst.copy_(src)
+                cache.repack(dict(self.named_parameters()))
+            else:
+                graphed = GraphedClosure(body, leaves=[p for p in self.parameters() if p.requires_grad])
+        finally:
+            cache.always_repack = False
+            if not fused:
+                cache.entries.clear()           # packed copies made during capture belong to the graph
+        named = dict(self.named_parameters())
+
+        def replay():
+            if cache.stale():                   # weights changed behind the optimizer's back (load_state_dict ...)
+                cache.repack(named)
+            total_loss = graphed()
+            if not whole_step:
+                reduce()
+            return total_loss
+        replay.launches = graphed.launches
+        if whole_step:
+            replay.includes_optimizer = optimizer
+        return replay
+
+    def training_closure(self, batch, loss_network, bucket, style_weight=100_000, content_weight=1, graph=None, optimizer=None):
         """The closure ``static_train`` hands to ``optimizer.step`` (network.py:690-731) for a batch
         held in the fixed tensor ``batch`` (the loop copies every new batch into it): zero the
         gradient bucket -> transform net -> loss network -> backward (-> all-reduce).  With CUDA
@@ -738,28 +856,11 @@ class ImageTransformNet(nn.Sequential):
             return total_loss
         if graph is None:
             graph = cuda_graphs_enabled()
-        if not graph:
-            def eager():
-                total_loss = body()
-                bucket.all_reduce()
-                return total_loss
-            return eager
-        for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
-            node.loss = None
-        loss_network._loss_vector = None
-        self._pack_cache.always_repack = True
-        try:
-            graphed = GraphedClosure(body, leaves=[p for p in self.parameters() if p.requires_grad])
-        finally:
-            self._pack_cache.always_repack = False
-            self._pack_cache.entries.clear()             # packed copies made during capture belong to the graph
-
-        def replay():
-            total_loss = graphed()
-            bucket.all_reduce()
-            return total_loss
-        replay.launches = graphed.launches
-        return replay
+        if graph:
+            for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
+                node.loss = None
+            loss_network._loss_vector = None
+        return self._step_closure(body, bucket, optimizer, graph, loss_network)
 
     def static_train(self, style_name='nsp', epochs=50, style_weight=100_000, content_weight=1,
                      train_loader=None, test_loader=None, max_iterations=None):
@@ -797,19 +898,21 @@ class ImageTransformNet(nn.Sequential):
                 # the closure (a replayed CUDA graph by default) reads the batch from a fixed buffer
                 if train_buf is None or train_buf.shape != batch.shape:
                     train_buf = batch.detach().clone().contiguous().float()
-                    closure = self.training_closure(train_buf, loss_network, bucket, style_weight, content_weight)
+                    closure = self.training_closure(train_buf, loss_network, bucket, style_weight, content_weight,
+                                                    optimizer=optimizer)
                 else:
                     train_buf.copy_(batch)
 
-                if iteration % 20 == 0:
-                    total_loss = closure()
-                    tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
-                    LOGGER.info('Batch Loss: %.8f', total_loss)
                 if iteration % 150 == 0 and test_loader is not None and rank0:
                     average_test_loss = self.static_test(test_loader, loss_network)
                     tb_writer.add_scalar('data/fst_test_loss', average_test_loss, iteration)
+                # the reference evaluates an extra closure every 20th iteration to log its loss (network.py:733-741);
+                # that value is the loss optimizer.step(closure) returns for the same weights and batch
+                total_loss = optimizer.step(closure)
+                if iteration % 20 == 0:
+                    tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
+                    LOGGER.info('Batch Loss: %.8f', total_loss)
                 iteration += 1
-                optimizer.step(closure)
                 if max_iterations is not None and iteration >= max_iterations:
                     return
             if rank0:
@@ -871,6 +974,19 @@ class VideoTransformNet(ImageTransformNet):
         else:
             self.has_external_weights = False
 
+    def forward_pair(self, frame: torch.Tensor, previous: torch.Tensor) -> torch.Tensor:
+        """``self(torch.cat([frame, previous], dim=1))`` (network.py:984-986, :1123-1125) without the concatenation:
+        the first layer's loader reads its channels 0..2 from ``frame`` and 3..5 from ``previous``."""
+        ops._require_cuda(frame, 'VideoTransformNet.forward_pair')
+        sd = dict(self.named_parameters())
+        params = [sd[n] for n in transform.PARAM_NAMES]
+        a, b = frame.contiguous().float(), previous.contiguous().float()
+        if tuple(a.shape) != tuple(b.shape) or a.shape[1] != 3:
+            return self(torch.cat([a, b], dim=1))
+        if not torch.is_grad_enabled():
+            return self._infer(a, params, x2=b)
+        return transform.TransformNetFn.apply(a, b, self._pack_cache, *params)
+
     def get_temporal_loss(self, old_content, old_stylized, current_content, current_stylized,
                           temporal_weight=1, flow=None) -> torch.Tensor:
         """network.py:885-903: tw * ||cur_sty - old_sty|| / (||cur_con - old_con|| + 1); the
@@ -888,8 +1004,7 @@ class VideoTransformNet(ImageTransformNet):
                            style_weight=100_000, content_weight=1, tv_scale=1.0, flow=None):
         """Closure body of video_train (network.py:984-1037); updates ``old_images`` in place."""
         old_content_images, old_styled_images = old_images
-        batch_with_old_content = torch.cat([batch, old_styled_images], dim=1)
-        transformed_image = self(batch_with_old_content)
+        transformed_image = self.forward_pair(batch, old_styled_images)      # = self(cat([batch, old_styled], 1))
         loss_network(transformed_image, content_image=batch)
         style_loss = loss_network.get_total_current_style_loss(weight=style_weight)
         content_loss = loss_network.get_total_current_content_loss(weight=content_weight)
@@ -904,14 +1019,17 @@ class VideoTransformNet(ImageTransformNet):
         return total_loss, transformed_image
 
     def video_training_closure(self, batch, old_content, old_stylized, next_stylized, loss_network, bucket,
-                               temporal_weight=0.8, style_weight=100_000, content_weight=1, graph=None):
+                               temporal_weight=0.8, style_weight=100_000, content_weight=1, graph=None, flow=None,
+                               optimizer=None):
         """The closure ``video_train`` hands to ``optimizer.step`` (network.py:988-1037) on FIXED tensors: the
         frame batch, the previous frame's content / stylised images as they were before this iteration
         (network.py:980-986 binds them outside the closure) and ``next_stylized``, which receives this frame's
         stylised output (the loop makes it the next ``old_stylized`` after the optimizer step).  zero the
         bucket -> 6-channel forward -> loss network -> TV + temporal loss -> backward (-> all-reduce).  With
         CUDA graphs everything up to the all-reduce is one replayed graph: at one clip per GPU the ~260
-        eager launches cost more host time than device time."""
+        eager launches cost more host time than device time.  ``flow`` (extension): a FIXED [B, 2, H, W]
+        tensor of optical flow in pixels from the previous frame to this one; the temporal loss then compares against
+        the flow-warped previous frames (the loop copies every frame's flow into it)."""
         world = st_dist.world_size()
 
         def body():
@@ -920,40 +1038,25 @@ class VideoTransformNet(ImageTransformNet):
             bucket.zero()
             state = [old_content, old_stylized]
             total_loss, transformed = self.closure_loss_video(batch, state, loss_network, temporal_weight, style_weight,
-                                                              content_weight, tv_scale=float(world))
+                                                              content_weight, tv_scale=float(world), flow=flow)
             self._backward_into_bucket(total_loss)
             with torch.no_grad():
                 next_stylized.copy_(transformed)
             return total_loss
         if graph is None:
             graph = cuda_graphs_enabled()
-        if not graph:
-            def eager():
-                total_loss = body()
-                bucket.all_reduce()
-                return total_loss
-            return eager
-        for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
-            node.loss = None
-        loss_network._loss_vector = None
-        self._pack_cache.always_repack = True
-        try:
-            graphed = GraphedClosure(body, leaves=[p for p in self.parameters() if p.requires_grad])
-        finally:
-            self._pack_cache.always_repack = False
-            self._pack_cache.entries.clear()
-
-        def replay():
-            total_loss = graphed()
-            bucket.all_reduce()
-            return total_loss
-        replay.launches = graphed.launches
-        return replay
+        if graph:
+            for node, _ in loss_network.style_losses + loss_network.content_losses + loss_network.feature_losses:
+                node.loss = None
+            loss_network._loss_vector = None
+        return self._step_closure(body, bucket, optimizer, graph, loss_network)
 
     def video_train(self, style_name='nsp', epochs=50, temporal_weight=0.8, style_weight=100_000,
                     feature_weight=1, content_weight=1, video_loader=None, max_iterations=None) -> None:
         """network.py:905-1069.  ``video_loader`` (extra, optional): an iterable of clips, each an
-        iterable of frame batches [B,3,H,W] (replaces VideoDataset + iterate_on_video_batches)."""
+        iterable of frame batches [B,3,H,W] (replaces VideoDataset + iterate_on_video_batches) -- or of
+        ``(frames [B,3,H,W], flow [B,2,H,W])`` pairs: the optical flow (in pixels) from the previous frame, which
+        switches the temporal loss to its flow-warped form (extension: the reference's loss has no flow)."""
         from . import dataset
         rank0 = st_dist.rank() == 0
         tb_writer = get_tensorboard_writer(f'runs/video-style-transfer_{style_name}' if rank0 else None)
@@ -988,31 +1091,39 @@ class VideoTransformNet(ImageTransformNet):
             for video_batch in video_loader:
                 first_frame = True
                 for batch in dataset.iterate_on_video_batches(video_batch):
+                    flow = None
+                    if isinstance(batch, (tuple, list)):
+                        batch, flow = batch
+                        flow = flow.to(constants.DEVICE)
                     batch = batch.to(constants.DEVICE)
                     if world > 1:
                         batch = st_dist.shard(batch)
+                        flow = None if flow is None else st_dist.shard(flow)
                     batch = batch.contiguous().float()
                     # fixed buffers the closure (a replayed CUDA graph by default) reads: this frame, the previous
                     # frame's content / stylised images as they were BEFORE this iteration (network.py:980-986 binds
                     # them outside the closure), and the slot that receives this frame's stylised output
-                    key = (tuple(batch.shape), tuple(p.requires_grad for p in self.parameters()))
+                    key = (tuple(batch.shape), tuple(p.requires_grad for p in self.parameters()), flow is not None)
                     if key != closure_key:
                         bufs = [torch.empty_like(batch) for _ in range(4)]      # batch, old content, old stylised, next stylised
+                        flow_buf = None if flow is None else torch.zeros_like(flow, dtype=torch.float32).contiguous()
                         closure = self.video_training_closure(bufs[0], bufs[1], bufs[2], bufs[3], style_loss_network, bucket,
-                                                              temporal_weight, style_weight, content_weight)
+                                                              temporal_weight, style_weight, content_weight, flow=flow_buf,
+                                                              optimizer=optimizer)
                         closure_key, first_frame = key, True
                     bufs[0].copy_(batch)
+                    if flow is not None:
+                        flow_buf.copy_(flow)
                     if first_frame:                      # new clip: the previous frame is the frame itself (network.py:977-978)
                         bufs[1].copy_(batch)
                         bufs[2].copy_(batch)
                         first_frame = False
 
-                    if iteration % 20 == 0:
-                        total_loss = closure()
+                    total_loss = optimizer.step(closure)
+                    if iteration % 20 == 0:          # network.py:1042-1048 logs the loss of an extra closure: the same value
                         tb_writer.add_scalar('data/fst_train_loss', total_loss, iteration)
                         LOGGER.info('Epoch: %d\tBatch Loss: %.4f', epoch, total_loss)
                     iteration += 1
-                    optimizer.step(closure)
                     bufs[1].copy_(bufs[0])               # old_images = [batch, transformed_image] (network.py:1016-1017)
                     bufs[2].copy_(bufs[3])
                     if max_iterations is not None and iteration >= max_iterations:
@@ -1038,17 +1149,25 @@ class VideoTransformNet(ImageTransformNet):
         old_image = None
         LOGGER.info('Starting to process video into stylized frames')
         outputs = []
-        with torch.no_grad():
-            for i, video_frame in enumerate(frames):
-                video_frame = video_frame.to(constants.DEVICE)
-                if old_image is None:
-                    old_image = video_frame
-                transformed_image = self(torch.cat([video_frame, old_image], dim=1))
-                old_image = transformed_image.detach()
-                outputs.append(transformed_image)
-                img_utils.imshow(transformed_image[0], path=f'{working_dir}{i}.png')
-                if i % 50 == 0:
-                    LOGGER.info('.. processing, currently frame %d', i)
+        # the frame loop never waits for a picture to reach the disk (the reference's per-frame imshow is a
+        # device sync + host copy + PNG encode): conversion to uint8 on the device, asynchronous download into
+        # pinned buffers, PNG encoding on worker threads (img_utils.FrameWriter); the 6-channel input is read from
+        # its two sources by the first layer's loader (no torch.cat)
+        writer = img_utils.FrameWriter()
+        try:
+            with torch.no_grad():
+                for i, video_frame in enumerate(frames):
+                    video_frame = video_frame.to(constants.DEVICE, non_blocking=True)
+                    if old_image is None:
+                        old_image = video_frame
+                    transformed_image = self.forward_pair(video_frame, old_image)
+                    old_image = transformed_image.detach()
+                    outputs.append(transformed_image)
+                    writer.submit(transformed_image[:1], f'{working_dir}{i}.png')
+                    if i % 50 == 0:
+                        LOGGER.info('.. processing, currently frame %d', i)
+        finally:
+            writer.close()
         LOGGER.info('All frames have been stylized.')
         dataset.write_video(working_dir, os.path.join(constants.PROJECT_ROOT_PATH, out_dir), f'video_st_{style_name}.mp4', fps)
         return outputs

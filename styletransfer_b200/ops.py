@@ -21,7 +21,7 @@ F16 = 16        # plane-code bit (include/stransfer_b200.h ST_PLANES_F16): the p
 #  'bf16x3': 2 bf16 planes / 3 passes everywhere (loss 1e-5, gradient ~2e-3 at >= 128^2 images)
 #  'bf16'  : 1 plane / 1 pass (fast, ~3e-2 error on the Gatys gradient)
 _MODES = {'f16x3': (2, F16, 2, F16), 'bf16x6': (3, 0, 2, 0), 'bf16x3': (2, 0, 2, 0), 'bf16': (1, 0, 1, 0)}
-PRECISION = os.environ.get('STRANSFER_PRECISION', 'bf16x6')
+PRECISION = os.environ.get('STRANSFER_PRECISION', 'f16x3')
 assert PRECISION in _MODES, PRECISION
 W_F16_INV_SCALE = 1.0 / 256.0      # fp16-packed conv weights carry the fixed factor 256 (csrc/common.cuh)
 
@@ -173,8 +173,14 @@ class PackedWeight:
         self.buf = torch.empty((self.planes, self.rows, ks * ks, self.cols), dtype=torch.bfloat16, device=w.device)
         self.hi = self.buf[0].data_ptr()
         self.lo = self.buf[1].data_ptr() if self.planes > 1 else None
-        _lib.check(_lib.lib().st_pack_conv_weight(w.data_ptr(), self.hi, self.lo, self.code, cout, cin, ks, self.rows, self.cols,
-                                                  mode, _stream()), 'st_pack_conv_weight')
+        self.repack(w)
+
+    def repack(self, w):
+        """(Re)write the packed planes in place from the fp32 weight."""
+        w = w.detach().contiguous().float()
+        assert tuple(w.shape) == (self.cout, self.cin, self.ks, self.ks)
+        _lib.check(_lib.lib().st_pack_conv_weight(w.data_ptr(), self.hi, self.lo, self.code, self.cout, self.cin, self.ks, self.rows,
+                                                  self.cols, self.mode, _stream()), 'st_pack_conv_weight')
 
     @property
     def code(self):
@@ -254,21 +260,27 @@ def conv_image_dgrad(g, w):
     return gx
 
 
-def _small_ptrs(x):
-    """(s0, s1, channels per sample) of an NCHW fp32 tensor with 3 or 6 channels."""
+def _small_ptrs(x, x2=None):
+    """(s0, s1, channels per sample, total channels) of the "small" side of a 9x9 layer: one NCHW fp32 tensor with
+    3 or 6 channels, or TWO 3-channel tensors read as channels 0..2 and 3..5 (the video net's
+    cat([frame, previous stylised frame], 1), network.py:984-986, without materialising the concatenation)."""
     N, C, H, W = x.shape
+    if x2 is not None:
+        assert C == 3 and tuple(x2.shape) == tuple(x.shape), 'two-source input: two [N, 3, H, W] tensors'
+        return x.data_ptr(), x2.data_ptr(), 3, 6
     assert C in (3, 6), 'the 9x9 kernels take 3- or 6-channel NCHW tensors'
-    return x.data_ptr(), (x.data_ptr() + 3 * H * W * 4 if C == 6 else None), C
+    return x.data_ptr(), (x.data_ptr() + 3 * H * W * 4 if C == 6 else None), C, C
 
 
-def conv9_expand(x, w, bias=None, flip=False, planes=None, fmt=None):
+def conv9_expand(x, w, bias=None, flip=False, planes=None, fmt=None, x2=None):
     """9x9 conv from a 3/6-channel NCHW fp32 tensor to 32 channels (Split).  flip=False: layer-0
     forward (w [32][C][9][9]); flip=True: layer-22 backward-data of dy (w [3][32][9][9]).  The operands
     are built in shared memory in the format of the output planes."""
     _require_cuda(x, 'conv9_expand')
     x = x.contiguous().float()
-    N, C, H, W = x.shape
-    s0, s1, sc = _small_ptrs(x)
+    x2 = None if x2 is None else x2.contiguous().float()
+    N, _, H, W = x.shape
+    s0, s1, sc, C = _small_ptrs(x, x2)
     assert tuple(w.shape) == ((C, 32, 9, 9) if flip else (32, C, 9, 9))
     out = Split(N, H, W, 32, x.device, planes=planes, fmt=fmt)
     _lib.check(_lib.lib().st_conv9_expand(s0, s1, sc, C, w.data_ptr(), _p(bias), int(flip), out.hi, out.lo, out.code,
@@ -295,14 +307,15 @@ def _grad_out(out, shape, dev):
     return out
 
 
-def conv9_wgrad(big, small, mode, want_bias=True, dw_out=None, db_out=None, small_slot=None):
+def conv9_wgrad(big, small, mode, want_bias=True, dw_out=None, db_out=None, small_slot=None, small2=None):
     """Backward-weight of the 9x9 layers.  mode 0: layer 0 (big = dy Split, small = input NCHW) ->
     dw [32][C][9][9]; mode 1: layer 22 (big = input Split, small = dy NCHW) -> dw [3][32][9][9].
     ``small_slot`` (absmax_slot of the small tensor): the scale under which a gradient image enters fp16 operands."""
     L = _lib.lib()
     small = small.contiguous().float()
-    N, C, H, W = small.shape
-    s0, s1, sc = _small_ptrs(small)
+    small2 = None if small2 is None else small2.contiguous().float()
+    N, _, H, W = small.shape
+    s0, s1, sc, C = _small_ptrs(small, small2)
     assert big.C == 32 and big.shape[:3] == (N, H, W)
     dev = big.buf.device
     ws = workspace(L.st_conv9_wgrad_workspace_bytes(C), dev)
@@ -517,3 +530,36 @@ def temporal_bwd(old_stylized, cur_stylized, tw, stats3, gw):
     _lib.check(_lib.lib().st_temporal_bwd(old_stylized.data_ptr(), cur_stylized.data_ptr(), cur_stylized.numel(), float(tw),
                                           stats3.data_ptr(), gw.data_ptr(), g.data_ptr(), _stream()), 'st_temporal_bwd')
     return g
+
+
+def _stats3():
+    import ctypes
+    from . import constants
+    mean = (ctypes.c_float * 3)(*constants.IMAGENET_MEAN)
+    std = (ctypes.c_float * 3)(*constants.IMAGENET_STD)
+    return mean, std
+
+
+def image_u8_to_nchw(u8):
+    """[N, H, W, 3] uint8 (device) -> ImageNet-normalised [N, 3, H, W] fp32 (reference img_utils.py:33-42)."""
+    _require_cuda(u8, 'image_u8_to_nchw')
+    assert u8.dtype == torch.uint8 and u8.dim() == 4 and u8.shape[3] == 3
+    u8 = u8.contiguous()
+    N, H, W, _ = u8.shape
+    out = torch.empty((N, 3, H, W), dtype=torch.float32, device=u8.device)
+    mean, std = _stats3()
+    _lib.check(_lib.lib().st_image_u8_to_nchw(u8.data_ptr(), out.data_ptr(), N, H, W, mean, std, _stream()), 'st_image_u8_to_nchw')
+    return out
+
+
+def image_nchw_to_u8(x, out=None):
+    """[N, 3, H, W] normalised fp32 -> [N, H, W, 3] uint8 picture (de-normalise, clamp: reference img_utils.py:105-109)."""
+    _require_cuda(x, 'image_nchw_to_u8')
+    x = x.contiguous().float()
+    N, C, H, W = x.shape
+    assert C == 3
+    if out is None:
+        out = torch.empty((N, H, W, 3), dtype=torch.uint8, device=x.device)
+    mean, std = _stats3()
+    _lib.check(_lib.lib().st_image_nchw_to_u8(x.data_ptr(), out.data_ptr(), N, H, W, mean, std, _stream()), 'st_image_nchw_to_u8')
+    return out

@@ -70,7 +70,43 @@ class FusedAdam(torch.optim.Optimizer):
         self.chunks = host.to(dev)
         self._active_key = None
         self.active = torch.zeros(self.nseg, dtype=torch.int32, device=dev)
-        self.grad_scale = 1.0
+        self.grad_scale = 1.0           # 1/world when the bucket holds the SUM of the ranks' gradients (dist.GradBucket)
+        self._packs = None              # device table of the packed weight copies this optimizer keeps up to date
+        self._pack_cache = None
+
+    def set_packs(self, cache, named_params):
+        """The Adam kernel rewrites the packed (split 16-bit, K-major) copies of the convolution weights that the
+        training closure's kernels read (``transform._PackCache`` entries), so the ~28 weight-packing launches of a
+        step disappear.  ``cache`` is frozen: its entries are owned by this optimizer."""
+        import struct
+        ps = self.param_groups[0]['params']
+        index = {id(p): i for i, p in enumerate(ps)}
+        dsts = [[] for _ in ps]
+        for (name, mode, _prec, _fmt), (_tag, pw) in cache.entries.items():
+            p = named_params[name + '.weight']
+            dsts[index[id(p)]].append(pw)
+        recs, off = [], 0
+        for i, p in enumerate(ps):
+            pws = dsts[i]
+            if len(pws) > 2:
+                raise _lib.StransferError('FusedAdam.set_packs: at most two packed copies per weight')
+            if pws:
+                cout, cin, ks, _ = p.shape
+                rec = struct.pack('<qiiii', off, cout, cin, ks, len(pws))
+                for pw in pws:
+                    rec += struct.pack('<QQiiii', pw.hi, pw.lo or 0, pw.rows, pw.cols, pw.mode, pw.code)
+                rec += b'\0' * 32 * (2 - len(pws))
+            else:
+                rec = struct.pack('<qiiii', off, 0, 0, 0, 0) + b'\0' * 64
+            assert len(rec) == 88
+            recs.append(rec)
+            off += p.numel()
+        table = torch.frombuffer(bytearray(b''.join(recs)), dtype=torch.uint8).clone()
+        self._packs = table.to(self.flat_param.device)
+        self._pack_keep = [pw for d in dsts for pw in d]
+        self._pack_cache = cache
+        cache.frozen = True
+        cache.mark_synced(ps)
 
     def _refresh_active(self, ps):
         key = tuple(p.grad is not None for p in ps)
@@ -79,11 +115,8 @@ class FusedAdam(torch.optim.Optimizer):
             self._active_key = key
 
     @torch.no_grad()
-    def step(self, closure=None):
-        loss = None
-        if closure is not None:
-            with torch.enable_grad():
-                loss = closure()
+    def launch(self):
+        """The Adam kernel on the current contents of the gradient bucket (stream-ordered, capturable)."""
         g = self.param_groups[0]
         ps = g['params']
         flat = self.bucket.flat
@@ -99,9 +132,31 @@ class FusedAdam(torch.optim.Optimizer):
                                        self.exp_avg_sq.data_ptr(), self.chunks.data_ptr(), self.nchunks,
                                        self.steps.data_ptr(), self.active.data_ptr(), self.nseg,
                                        float(g['lr']), float(b1), float(b2), float(g['eps']), float(g['weight_decay']),
-                                       float(self.grad_scale), _stream()), 'st_adam_step')
-        _bump_versions(ps)
+                                       float(self.grad_scale), None if self._packs is None else self._packs.data_ptr(),
+                                       _stream()), 'st_adam_step')
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        # a closure that already CONTAINS this optimizer's update (the whole step captured in one CUDA graph:
+        # closure -> all-reduce -> Adam, network.training_closure(optimizer=...)) is simply replayed
+        if closure is not None and getattr(closure, 'includes_optimizer', None) is self:
+            with torch.enable_grad():
+                loss = closure()
+            self._after_update()
+            return loss
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        self.launch()
+        self._after_update()
         return loss
+
+    def _after_update(self):
+        ps = self.param_groups[0]['params']
+        _bump_versions(ps)
+        if self._pack_cache is not None:
+            self._pack_cache.mark_synced(ps)
 
 
 class DeviceLBFGS(torch.optim.Optimizer):

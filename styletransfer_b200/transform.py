@@ -106,27 +106,51 @@ class _PackCache:
         # bucket that are the parameters' .grad), the backward kernels write the parameter gradients
         # straight into these buffers and autograd gets None for them -- no per-tensor accumulate kernels
         self.grad_sink = None
+        # frozen: the entries are kept up to date by the optimizer (optim.FusedAdam.set_packs: the Adam kernel rewrites
+        # the packed copies), a lookup never repacks; ``synced`` remembers the parameter versions the packs belong to
+        self.frozen = False
+        self.synced = None
 
     def get(self, name, w, mode, **kw):
         key = (name, mode, ops.PRECISION, kw.get('fmt'))
-        tag = (w.data_ptr(), w._version, tuple(w.shape))
         hit = self.entries.get(key)
+        if self.frozen and hit is not None:
+            return hit[1]
+        tag = (w.data_ptr(), w._version, tuple(w.shape))
         if self.always_repack or hit is None or hit[0] != tag:
             hit = (tag, ops.PackedWeight(w, mode, **kw))
             self.entries[key] = hit
         return hit[1]
+
+    def mark_synced(self, params):
+        self.synced = [(p, p._version) for p in params]
+
+    def stale(self):
+        """Frozen packs whose fp32 master weight changed behind the optimizer's back (load_state_dict, manual edits)."""
+        return self.frozen and self.synced is not None and any(p._version != v for p, v in self.synced)
+
+    def repack(self, named_params):
+        """Rewrite every packed copy in place from the current fp32 weights (the buffers keep their addresses: they are
+        baked into a captured graph and into the optimizer's table)."""
+        for (name, _mode, _prec, _fmt), (_tag, pw) in self.entries.items():
+            pw.repack(named_params[name + '.weight'])
+        if self.synced is not None:
+            self.mark_synced([p for p, _ in self.synced])
 
 
 def _keep(saved, keep, item):
     saved.append(item if keep else None)
 
 
-def run_forward(x, cache, params, keep):
+def run_forward(x, cache, params, keep, x2=None):
     """The fused forward over PLAN.  ``keep``: retain what the backward needs (training);
     without it every intermediate is released as soon as the next stage has consumed it
-    (inference: process_image / process_video, network.py:798-832, :1117-1134)."""
+    (inference: process_image / process_video, network.py:798-832, :1117-1134).
+    ``x2``: second 3-channel source of the video net's 6-channel input (read in place of torch.cat([x, x2], 1))."""
     p = dict(zip(PARAM_NAMES, params))
     N, cin, H, W = x.shape
+    if x2 is not None:
+        cin = 6
     h = None            # the first conv reads the NCHW fp32 input itself (9x9 direct kernel)
     saved = []          # per stage: what backward needs
     residual = None
@@ -144,11 +168,11 @@ def run_forward(x, cache, params, keep):
             last = seen == n_conv
             if seen == 1 and _is_conv9_in(w):
                 # layer 0: 3|6 -> 32 channels, 9x9: exact-fp32 direct kernel on the NCHW input
-                h = ops.conv9_expand(x, w, b)
+                h = ops.conv9_expand(x, w, b, x2=x2)
                 _keep(saved, keep, None)
                 continue
             if h is None:
-                h = ops.from_nchw(x, cpad=ops.pad8(cin))
+                h = ops.from_nchw(x, x2, cpad=ops.pad8(cin))
             if last and _is_conv9_out(w) and h.C == 32:
                 # layer 22: 32 -> 3 channels, 9x9: direct kernel writing the NCHW fp32 output
                 out_nchw = ops.conv9_reduce(h, w, b)
@@ -171,19 +195,21 @@ def run_forward(x, cache, params, keep):
 
 
 class TransformNetFn(torch.autograd.Function):
-    """y = net(x).  args: x NCHW fp32 [N, Cin, H, W], cache, then the 62 parameters in
-    PARAM_NAMES order."""
+    """y = net(x) (or net(cat([x, x2], 1)) read from its two sources).  args: x NCHW fp32 [N, Cin, H, W],
+    x2 (None or a second [N, 3, H, W] source), cache, then the 62 parameters in PARAM_NAMES order."""
 
     @staticmethod
-    def forward(ctx, x, cache, *params):
-        out_nchw, saved = run_forward(x, cache, params, keep=True)
-        ctx.saved, ctx.cache, ctx.params, ctx.in_shape, ctx.x = saved, cache, params, x.shape, x
+    def forward(ctx, x, x2, cache, *params):
+        out_nchw, saved = run_forward(x, cache, params, keep=True, x2=x2)
+        shape = x.shape if x2 is None else (x.shape[0], 6) + tuple(x.shape[2:])
+        ctx.saved, ctx.cache, ctx.params, ctx.in_shape, ctx.x, ctx.x2 = saved, cache, params, shape, x, x2
         return out_nchw
 
     @staticmethod
     def backward(ctx, gy):
         p = dict(zip(PARAM_NAMES, ctx.params))
-        need = dict(zip(PARAM_NAMES, ctx.needs_input_grad[2:]))
+        need = dict(zip(PARAM_NAMES, ctx.needs_input_grad[3:]))
+        want_gx = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
         grads = {}
         cache = ctx.cache
         sink = cache.grad_sink or {}
@@ -221,8 +247,8 @@ class TransformNetFn(torch.autograd.Function):
                 w = p[name + '.weight']
                 if need[name + '.weight'] or need[name + '.bias']:
                     grads[name + '.weight'], grads[name + '.bias'] = ops.conv9_wgrad(
-                        g, ctx.x, 0, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'))
-                if ctx.needs_input_grad[0]:
+                        g, ctx.x, 0, dw_out=out_of(name + '.weight'), db_out=out_of(name + '.bias'), small2=ctx.x2)
+                if want_gx:
                     # rare (tests / image optimisation through the net): gather-form backward-data
                     pw = cache.get(name, w, 1, rows_pad=ops.pad8(cin), cols_pad=g.C, fmt=g.fmt)
                     _, _, gx = ops.conv2d(g, pw, stride=1, transposed=1, out_hw=(H, W), want_out=False, out_nchw_channels=cin)
@@ -246,7 +272,7 @@ class TransformNetFn(torch.autograd.Function):
                 if add_res:
                     res_grad = g                    # d(out)/d(residual) = identity
                 if idx == first_conv:
-                    if ctx.needs_input_grad[0]:
+                    if want_gx:
                         pw = cache.get(name, w, 1, rows_pad=xin.C, cols_pad=g.C, fmt=g.fmt)
                         _, _, gx = ops.conv2d(g, pw, stride=stride, transposed=1, out_hw=(xin.H, xin.W),
                                               want_out=False, out_nchw_channels=cin)
@@ -273,7 +299,11 @@ class TransformNetFn(torch.autograd.Function):
                                                              dbeta_out=out_of(name + '.bias'), dsum_out=dsum_out)
                 grads[name + '.weight'], grads[name + '.bias'] = dgam, dbet
         ctx.saved = None
-        out = [grads.get('__input__'), None]
+        gx = grads.get('__input__')
+        if ctx.x2 is not None and gx is not None:
+            out = [gx[:, :3].contiguous(), gx[:, 3:].contiguous(), None]
+        else:
+            out = [gx, None, None]
         for n in PARAM_NAMES:
             gn = grads.get(n) if need[n] else None
             # a gradient the kernels wrote into its sink (same storage) is already where autograd would add it

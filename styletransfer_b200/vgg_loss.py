@@ -1,12 +1,16 @@
 """Single-pass VGG-19 loss network on the B200 kernels.
 
-Replaces the seven (+2) prefix passes that StyleNetwork.forward runs per call
-(reference network.py:366-401 -> run_through_pieces :316-340) by ONE forward that
-emits the five pre-ReLU taps, and autograd's backward through the replicated
-prefixes by ONE fused backward-data chain to the image.  VGG weights are frozen
-(no wgrad).  Losses come back as a length-7 tensor
-[style x5, content, feature] whose gradient weights (grad_output) are read on the
-device, so no host synchronisation happens anywhere in forward or backward.
+Replaces the prefix passes that StyleNetwork.forward runs once PER LOSS NODE (reference network.py:366-401 ->
+run_through_pieces :316-340: seven passes of the input plus two of the content image with the default layer lists)
+by ONE forward that emits every tapped layer, and autograd's backward through the replicated prefixes by ONE fused
+backward-data chain to the image.  VGG weights are frozen (no wgrad).  Losses come back as one vector
+[style nodes..., content nodes..., feature nodes...] whose gradient weights (grad_output) are read on the device, so
+no host synchronisation happens anywhere in forward or backward.
+
+The tap set is whatever ``StyleNetwork.content_layers / style_layers / feature_loss_layers`` name (the reference's
+piece builder, network.py:257-314, is generic over those class attributes): a loss node may sit on any
+``Conv2d_k`` (pre-ReLU output of the k-th conv), ``ReLU_k`` or ``MaxPool2d_k`` layer of torchvision's
+``vgg19().features`` (k = 1..16 counts the convolutions).
 """
 import os
 
@@ -14,12 +18,46 @@ import torch
 
 from . import ops
 
-# (cin, cout, pool_before): conv1_1, conv1_2, conv2_1, conv2_2, conv3_1 = Conv2d_1..5
+# torchvision VGG-19 configuration "E": 16 convs (3x3, zero padding 1), each followed by a ReLU, 5 max-pools
+VGG_CFG_E = [64, 64, 'M', 128, 128, 'M', 256, 256, 256, 256, 'M', 512, 512, 512, 512, 'M', 512, 512, 512, 512, 'M']
+
+
+def _blocks():
+    """[(cin, cout, pool_after)] for conv k = 1..16: block k = Conv2d_k -> ReLU_k (-> MaxPool2d_k)."""
+    out, cin = [], 3
+    for i, v in enumerate(VGG_CFG_E):
+        if v == 'M':
+            continue
+        out.append((cin, v, i + 1 < len(VGG_CFG_E) and VGG_CFG_E[i + 1] == 'M'))
+        cin = v
+    return out
+
+
+BLOCKS = _blocks()
+# (cin, cout, pool_before) of the five convs the DEFAULT tap set executes (kept for callers that size weights by it)
 PREFIX = [(3, 64, False), (64, 64, False), (64, 128, True), (128, 128, False), (128, 256, True)]
-CONTENT_TAP = 3
-N_LOSSES = 7
+KINDS = {'Conv2d': 'C', 'ReLU': 'R', 'MaxPool2d': 'P'}
 # backward-data of conv1_1: tcgen05 16-channel tile (default) or the exact-fp32 CUDA-core kernel
 IMAGE_GRAD_TC = True
+
+
+def parse_layer(name):
+    """'Conv2d_4' -> ('C', 4), 'ReLU_4' -> ('R', 4), 'MaxPool2d_4' -> ('P', 4) (names of network.py:267-270)."""
+    kind, _, idx = name.rpartition('_')
+    if kind not in KINDS or not idx.isdigit() or not 1 <= int(idx) <= len(BLOCKS):
+        raise ValueError(f'"{name}" is not a layer of vgg19().features (Conv2d_k / ReLU_k / MaxPool2d_k, k = 1..16)')
+    k = int(idx)
+    if kind == 'MaxPool2d' and not BLOCKS[k - 1][2]:
+        raise ValueError(f'"{name}": no max-pool follows conv {k} in VGG-19')
+    return KINDS[kind], k
+
+
+def layer_names(n_convs=len(BLOCKS)):
+    """The layer names of vgg19().features in order (all 37, or those of the first ``n_convs`` blocks)."""
+    names = []
+    for k, (_, _, pool) in enumerate(BLOCKS[:n_convs], start=1):
+        names += [f'Conv2d_{k}', f'ReLU_{k}'] + ([f'MaxPool2d_{k}'] if pool else [])
+    return names
 
 
 # STRANSFER_OVERLAP_LOSSES=1 runs the loss branches of the taps on a side stream.  Measured on B200 (Gatys 512x512:
@@ -37,14 +75,15 @@ def _side_stream(device):
 
 
 class VGGPrefix:
-    """Packed weights of the five executed convs."""
+    """Packed weights of the first ``len(weights)`` VGG-19 convs and the fused forward over them."""
 
     def __init__(self, weights):
-        assert len(weights) == 5
+        assert 1 <= len(weights) <= len(BLOCKS)
         self.device = weights[0][0].device
         self.fwd, self.bwd, self.bias = [], [], []
         for i, (w, b) in enumerate(weights):
             ops._require_cuda(w, 'VGGPrefix')
+            assert tuple(w.shape) == (BLOCKS[i][1], BLOCKS[i][0], 3, 3), f'conv {i + 1}: unexpected weight shape {tuple(w.shape)}'
             if i == 0:
                 # conv1_1 forward (K = 27) runs in exact fp32 on the CUDA cores straight from the NCHW
                 # fp32 image (conv_image.cu): the fp32 weight is the operand
@@ -59,111 +98,226 @@ class VGGPrefix:
                 self.bwd.append(ops.PackedWeight(w, 2, rows_pad=w.shape[1]))
             self.bias.append(b.detach().contiguous().float())
 
-    def taps(self, x, upto=5, keep_all=True, on_tap=None, pool_idx=None):
-        """x: NCHW fp32.  Returns the list of pre-ReLU taps (Split) of Conv2d_1..upto.  keep_all=False:
-        only the last tap is wanted (content targets); layers whose ReLU copy feeds the next conv then
-        skip the store of their pre-ReLU tap (None in the returned list).  ``on_tap(i, tap)`` is called as
-        soon as tap i has been launched (the loss branch of the tap can then run beside the next layer).
-        ``pool_idx`` (dict): filled with {tap index: routing byte map of the relu+maxpool that follows it}, which
-        the backward uses instead of re-reading the full-resolution tap."""
+    @property
+    def n_convs(self):
+        return len(self.bias)
+
+    def run(self, x, points, keep_taps=True, on_point=None, pool_idx=None):
+        """One forward over the blocks up to the last requested point.  x: NCHW fp32.  ``points``: set of
+        ('C' | 'R' | 'P', k), plus ('R!', k) to ask for a MATERIALISED copy of relu(conv k).
+        Returns (vals, taps): vals[('C', k)] = pre-ReLU output of conv k, vals[('R', k)] = its ReLU copy where one was
+        materialised, vals[('P', k)] = the pooled tensor; taps[k] = pre-ReLU output of conv k for every executed block
+        (only where a requested point or a pool needs it when ``keep_taps`` is False).
+        ``on_point(point, vals, taps)`` is called as soon as a requested point has been launched.
+        ``pool_idx`` (dict): filled with {k: routing byte map of MaxPool2d_k} for the backward."""
+        K = max(k for _, k in points)
+        if K > self.n_convs:
+            raise ops._lib.StransferError(f'the loss layers need VGG conv {K} but only {self.n_convs} conv weights were given')
+        vals, taps = {}, {}
         h = None
-        taps = []
-        for i in range(upto):
-            pool_next = i + 1 < 5 and PREFIX[i + 1][2]
-            last = i + 1 == upto
-            # a tap feeds either relu+maxpool (separate kernel) or a conv that wants relu(tap)
-            want_relu = not last and not pool_next
-            want_out = keep_all or not want_relu
-            if i == 0:
-                tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=want_out, want_relu=want_relu)
+        for k in range(1, K + 1):
+            _, _, pool = BLOCKS[k - 1]
+            last = k == K
+            need_pool = pool and (not last or ('P', k) in points)
+            need_next = not last or need_pool
+            # relu(tap) is materialised by the conv epilogue when the next conv reads it directly, or when a
+            # loss node wants the ReLU output as a tensor-core operand (style node on ReLU_k)
+            want_relu = (need_next and not pool) or ('R!', k) in points
+            want_tap = keep_taps or ('C', k) in points or ('R', k) in points or need_pool or not want_relu
+            if k == 1:
+                tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=want_tap, want_relu=want_relu)
             else:
-                tap, relu, _ = ops.conv2d(h, self.fwd[i], self.bias[i], want_out=want_out, want_relu=want_relu)
-            taps.append(tap)
-            if on_tap is not None:
-                on_tap(i, tap)
-            if last:
-                break
-            if pool_next and pool_idx is not None:
-                h, pool_idx[i] = ops.relu_maxpool_fwd(tap, want_idx=True)
-            else:
-                h = ops.relu_maxpool_fwd(tap) if pool_next else relu
-        return taps
+                tap, relu, _ = ops.conv2d(h, self.fwd[k - 1], self.bias[k - 1], want_out=want_tap, want_relu=want_relu)
+            taps[k] = tap
+            if tap is not None:
+                vals[('C', k)] = tap
+            if relu is not None:
+                vals[('R', k)] = relu
+            for pt in (('C', k), ('R', k)):
+                if pt in points and on_point is not None:
+                    on_point(pt, vals, taps)
+            if need_pool:
+                if pool_idx is not None:
+                    h, pool_idx[k] = ops.relu_maxpool_fwd(tap, want_idx=True)
+                else:
+                    h = ops.relu_maxpool_fwd(tap)
+                vals[('P', k)] = h
+                if ('P', k) in points and on_point is not None:
+                    on_point(('P', k), vals, taps)
+            elif need_next:
+                h = relu
+        return vals, taps
+
+    def taps(self, x, upto=5, keep_all=True):
+        """Pre-ReLU outputs of Conv2d_1..upto (list of Split; None where ``keep_all`` is False and the tap is not
+        needed).  Convenience for the default five-tap layout."""
+        pts = {('C', k) for k in range(1, upto + 1)} if keep_all else {('C', upto)}
+        _, taps = self.run(x, pts, keep_taps=keep_all)
+        return [taps.get(k) if (keep_all or k == upto) else None for k in range(1, upto + 1)]
+
+    def value_at(self, x, point):
+        """NCHW fp32 value of the layer ``point`` for the image batch x (run_through_pieces)."""
+        kind, k = point
+        vals, taps = self.run(x, {point}, keep_taps=False)
+        if kind == 'P':
+            return ops.to_nchw(vals[point])
+        out = ops.to_nchw(taps[k])
+        return out.clamp_(min=0) if kind == 'R' else out
+
+
+class LossSpec:
+    """The loss nodes of a StyleNetwork in loss-vector order: style nodes, content nodes, feature nodes.
+    ``style``: [[point, target Gram [1, C, C]]]; ``content`` / ``feature``: [[point, target]] where the target of a
+    'C' or 'R' point is the PRE-ReLU tap of the target image at that conv (the kernels apply the ReLU of an 'R' point
+    themselves) and the target of a 'P' point is the pooled tensor."""
+
+    def __init__(self, style, content, feature):
+        self.style, self.content, self.feature = [list(t) for t in style], [list(t) for t in content], [list(t) for t in feature]
+
+    @property
+    def n_losses(self):
+        return len(self.style) + len(self.content) + len(self.feature)
+
+    def points(self, with_feature=True, style=True, mse=True):
+        pts = set()
+        if style:
+            for pt, _ in self.style:
+                pts.add(pt)
+                if pt[0] == 'R':        # a Gram of a ReLU output needs the ReLU copy as a tensor
+                    pts.add(('R!', pt[1]))
+        if mse:
+            for pt, _ in self.content + (self.feature if with_feature else []):
+                pts.add(pt)
+        return pts
+
+
+def mse_operand(pt, vals, taps):
+    """(tensor, relu flag) the MSE kernels read for a node at ``pt``."""
+    if pt[0] == 'P':
+        return vals[pt], False
+    return taps[pt[1]], pt[0] == 'R'
 
 
 class _VGGLossFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, net, style_targets, content_target, with_feature):
-        losses = torch.zeros(N_LOSSES, dtype=torch.float32, device=x.device)
-        diffs = [None] * 5
-        feat = [None]
-        # The loss branch of tap i (Gram -> split-K finish -> style MSE, and the content / feature MSE at
-        # tap 4) does not feed the next layer: it runs on a side stream beside conv i+1, so its small
-        # finish / reduction kernels fill SMs the convolution leaves idle (inside a captured CUDA graph the
-        # two streams become parallel branches).  The streams join before forward returns.
+    def forward(ctx, x, net, spec, with_feature):
+        n_style, n_content = len(spec.style), len(spec.content)
+        feature = spec.feature if with_feature else []
+        losses = torch.zeros(spec.n_losses, dtype=torch.float32, device=x.device)
+        diffs = [None] * n_style
+        feat_mse = [None] * len(feature)
+        by_point = {}
+        for i, (pt, _) in enumerate(spec.style):
+            by_point.setdefault(pt, []).append(('style', i))
+        for i, (pt, _) in enumerate(spec.content):
+            by_point.setdefault(pt, []).append(('content', i))
+        for i, (pt, _) in enumerate(feature):
+            by_point.setdefault(pt, []).append(('feature', i))
+        # The loss branch of a tap (Gram -> split-K finish -> style MSE, content / feature MSE) does not feed the
+        # next layer: with STRANSFER_OVERLAP_LOSSES it runs on a side stream beside the next conv (inside a captured
+        # CUDA graph the two streams become parallel branches).  The streams join before forward returns.
         cur = torch.cuda.current_stream(x.device)
         side = _side_stream(x.device) if OVERLAP_LOSS_BRANCHES else None
 
-        def branch(i, tap):
-            G = ops.gram(tap)
-            diffs[i] = ops.style_mse_fwd(G, style_targets[i], losses[i:i + 1])      # (diff, max |diff|)
-            if i == CONTENT_TAP:
-                ops.mse_fwd(tap, content_target, losses[5:6])
-                if with_feature:
-                    feat[0] = torch.empty(1, dtype=torch.float32, device=x.device)
-                    ops.mse_fwd(tap, content_target, feat[0], relu=True)
-                    ops.mse_fwd(tap, content_target, losses[6:7], relu=True, feature_form=True)
+        def branch(pt, vals, taps):
+            for kind, i in by_point.get(pt, ()):
+                if kind == 'style':
+                    G = ops.gram(vals[pt])
+                    diffs[i] = ops.style_mse_fwd(G, spec.style[i][1], losses[i:i + 1])      # (diff, max |diff|)
+                elif kind == 'content':
+                    t, relu = mse_operand(pt, vals, taps)
+                    ops.mse_fwd(t, spec.content[i][1], losses[n_style + i:n_style + i + 1], relu=relu)
+                else:
+                    t, relu = mse_operand(pt, vals, taps)
+                    feat_mse[i] = torch.empty(1, dtype=torch.float32, device=x.device)
+                    ops.mse_fwd(t, feature[i][1], feat_mse[i], relu=relu)
+                    j = n_style + n_content + i
+                    ops.mse_fwd(t, feature[i][1], losses[j:j + 1], relu=relu, feature_form=True)
 
-        def on_tap(i, tap):
+        def on_point(pt, vals, taps):
             if side is None:
-                return branch(i, tap)
+                return branch(pt, vals, taps)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
-                branch(i, tap)
-        pool_idx = {} if ctx.needs_input_grad[0] else None       # routing maps of the two max-pools, for the backward
-        taps = net.taps(x, on_tap=on_tap, pool_idx=pool_idx)
+                branch(pt, vals, taps)
+        pool_idx = {} if ctx.needs_input_grad[0] else None       # routing maps of the max-pools, for the backward
+        vals, taps = net.run(x, spec.points(with_feature), on_point=on_point, pool_idx=pool_idx)
         if side is not None:
             cur.wait_stream(side)
-        feat_mse = feat[0]
-        ctx.net, ctx.taps, ctx.diffs, ctx.pool_idx = net, taps, diffs, pool_idx or {}
-        ctx.content_target, ctx.feat_mse = content_target, feat_mse
-        ctx.in_shape = x.shape
+        ctx.net, ctx.spec, ctx.feature = net, spec, feature
+        ctx.vals, ctx.taps, ctx.diffs, ctx.feat_mse, ctx.pool_idx = vals, taps, diffs, feat_mse, pool_idx or {}
         return losses
 
     @staticmethod
     def backward(ctx, gl):
-        net, taps, diffs = ctx.net, ctx.taps, ctx.diffs
+        net, spec, vals, taps, diffs, feature = ctx.net, ctx.spec, ctx.vals, ctx.taps, ctx.diffs, ctx.feature
+        n_style, n_content = len(spec.style), len(spec.content)
         gl = gl.contiguous().float()
-        # dF_l = F_l * D_l  (Gram backward, per-image 1x1 conv on the tensor cores)
-        def style_grad(i, add=None):
-            tap = taps[i]
-            # the per-image weights D take the plane format of the tap they multiply (one format per tensor-core product)
-            _keep, wp = ops.style_seed(diffs[i][0], diffs[i][1], tap.H * tap.W, gl[i:i + 1], tap.fmt)
-            out, _, _ = ops.conv2d(tap, None, w_ptrs=wp, w_img_rows=tap.C, add=add)
-            return out
+        K = max(taps)
 
-        t4 = taps[CONTENT_TAP]
-        numel4 = t4.buf[0].numel()
-        cgrad = ops.mse_bwd(t4, ctx.content_target, gl[5:6], 2.0 / numel4)
-        if ctx.feat_mse is not None:
-            # d/dx [mse^2/numel] = 2*mse/numel * 2/numel * (relu x - relu t) * (x > 0)
-            ops.mse_bwd(t4, ctx.content_target, gl[6:7], 4.0 / (float(numel4) * float(numel4)), out=cgrad,
-                        relu=True, mul=ctx.feat_mse)
-        g5 = style_grad(4)
-        gp2, _, _ = ops.conv2d(g5, net.bwd[4])                                   # -> grad of pool2 output
-        g4 = ops.relu_maxpool_bwd(t4, gp2, add=style_grad(3, add=cgrad), idx=ctx.pool_idx.get(3))   # -> grad of tap4
-        g3, _, _ = ops.conv2d(g4, net.bwd[3], mask=taps[2], add=style_grad(2))   # relu'(tap3) fused
-        gp1, _, _ = ops.conv2d(g3, net.bwd[2])
-        g2 = ops.relu_maxpool_bwd(taps[1], gp1, add=style_grad(1), idx=ctx.pool_idx.get(1))
-        g1, _, _ = ops.conv2d(g2, net.bwd[1], mask=taps[0], add=style_grad(0))
-        if IMAGE_GRAD_TC:
-            _, _, gx = ops.conv2d(g1, net.bwd[0], want_out=False, out_nchw_channels=3)
-        else:
-            gx = ops.conv_image_dgrad(g1, net.w0)
-        ctx.taps = ctx.diffs = None
-        return gx, None, None, None, None
+        def node_grads(pt, acc=None):
+            """acc + the loss gradients of the nodes at ``pt`` with respect to the value at ``pt`` -- for 'R' points
+            with respect to the pre-ReLU tap (relu' applied).  Returns ``acc`` unchanged when no node sits there."""
+            for i, (p, target) in enumerate(spec.content):
+                if p == pt:
+                    t, relu = mse_operand(pt, vals, taps)
+                    acc = ops.mse_bwd(t, target, gl[n_style + i:n_style + i + 1], 2.0 / t.buf[0].numel(), out=acc, relu=relu)
+            for i, (p, target) in enumerate(feature):
+                if p == pt:
+                    # d/dx [mse^2 / numel] = 2 mse / numel * 2 / numel * (f(x) - f(t)) * f'(x)
+                    t, relu = mse_operand(pt, vals, taps)
+                    n = float(t.buf[0].numel())
+                    j = n_style + n_content + i
+                    acc = ops.mse_bwd(t, target, gl[j:j + 1], 4.0 / (n * n), out=acc, relu=relu, mul=ctx.feat_mse[i])
+            for i, (p, _) in enumerate(spec.style):
+                if p == pt:
+                    # dF = F * D  (Gram backward, per-image 1x1 conv on the tensor cores); the per-image weights D take
+                    # the plane format of the operand F they multiply (one format per tensor-core product)
+                    f = vals[pt]
+                    _keep, wp = ops.style_seed(diffs[i][0], diffs[i][1], f.H * f.W, gl[i:i + 1], f.fmt)
+                    acc, _, _ = ops.conv2d(f, None, w_ptrs=wp, w_img_rows=f.C, add=acc, mask=taps[pt[1]] if pt[0] == 'R' else None)
+            return acc
+
+        def tap_node_grads(k):
+            return node_grads(('R', k), node_grads(('C', k)))
+
+        g_out = None          # gradient of the OUTPUT of block k (what conv k + 1 reads), node gradients of MaxPool2d_k included
+        g_tap = None          # gradient of the pre-ReLU output of conv k when the launch below has already produced it
+        for k in range(K, 0, -1):
+            _, _, pool = BLOCKS[k - 1]
+            if g_tap is None:
+                add = tap_node_grads(k)
+                if pool and (g_out is not None or ('P', k) in vals):
+                    gy = g_out if g_out is not None else node_grads(('P', k))
+                    if gy is None:
+                        g_tap = add
+                    else:
+                        # route through the max-pool, relu', + the node gradients of this block, in one kernel
+                        g_tap = ops.relu_maxpool_bwd(taps[k], gy, add=add, idx=ctx.pool_idx.get(k))
+                else:
+                    g_tap = add                       # top block: the node gradients are the whole gradient
+                if g_tap is None:
+                    raise ops._lib.StransferError('internal: no gradient reaches the top of the loss network')
+            if k == 1:
+                if IMAGE_GRAD_TC:
+                    _, _, gx = ops.conv2d(g_tap, net.bwd[0], want_out=False, out_nchw_channels=3)
+                else:
+                    gx = ops.conv_image_dgrad(g_tap, net.w0)
+                break
+            # backward-data of conv k = gradient of block k - 1's output
+            if BLOCKS[k - 2][2]:
+                # a max-pool closes block k - 1: its node gradients ride on this launch's epilogue, the pool is routed next
+                g_out, _, _ = ops.conv2d(g_tap, net.bwd[k - 1], add=node_grads(('P', k - 1)))
+                g_tap = None
+            else:
+                # no pool: this launch's epilogue applies relu'(tap k - 1) and adds block k - 1's node gradients
+                g_tap, _, _ = ops.conv2d(g_tap, net.bwd[k - 1], mask=taps[k - 1], add=tap_node_grads(k - 1))
+                g_out = None
+        ctx.vals = ctx.taps = ctx.diffs = None
+        return gx, None, None, None
 
 
-def vgg_losses(x, net, style_targets, content_target, with_feature=True):
-    """losses[0:5] style nodes, [5] content node, [6] feature node (0 when skipped)."""
+def vgg_losses(x, net, spec, with_feature=True):
+    """Loss vector [style nodes..., content nodes..., feature nodes...] (feature entries 0 when skipped)."""
     ops._require_cuda(x, 'vgg_losses')
-    return _VGGLossFn.apply(x.contiguous().float(), net, style_targets, content_target, with_feature)
+    return _VGGLossFn.apply(x.contiguous().float(), net, spec, with_feature)

@@ -113,3 +113,63 @@ def test_process_video_recurrence_from_a_checkpoint(tmp_path):
     finally:
         if os.path.exists(ckpt):
             os.unlink(ckpt)
+
+
+def test_image_boundary_kernels_match_host_arithmetic():
+    """img_utils.image_loader_transform / imshow (reference img_utils.py:33-42, :105-109) with the normalisation and
+    the de-normalise + clamp + uint8 conversion on the device: bit-identical to the host (numpy / torch CPU) code."""
+    from styletransfer_b200 import constants, ops
+    rng = np.random.default_rng(3)
+    u8 = torch.from_numpy(rng.integers(0, 256, (2, 37, 53, 3), dtype=np.uint8))
+    mean = torch.tensor(constants.IMAGENET_MEAN).view(1, 3, 1, 1)
+    std = torch.tensor(constants.IMAGENET_STD).view(1, 3, 1, 1)
+    want = (torch.from_numpy(u8.numpy().astype(np.float32) / 255.0).permute(0, 3, 1, 2) - mean) / std
+    got = ops.image_u8_to_nchw(u8.cuda())
+    assert torch.equal(got.cpu(), want)
+    x = torch.randn(2, 3, 37, 53, generator=torch.Generator().manual_seed(5)) * 1.5
+    img = torch.clamp(x * std + mean, min=0, max=255)
+    want_u8 = (img.clamp(max=1.0) * 255.0 + 0.5).to(torch.uint8).permute(0, 2, 3, 1)
+    assert torch.equal(ops.image_nchw_to_u8(x.cuda()).cpu(), want_u8)
+
+
+def test_process_video_pipelines_frames_to_disk(tmp_path):
+    """VideoTransformNet.process_video (network.py:1071-1158): the recurrent per-frame forward with the pictures
+    converted on the device, downloaded asynchronously and encoded by worker threads -- the PNGs equal what the
+    reference's synchronous loop (imshow of every frame) writes, and the recurrence equals cat([frame, previous])."""
+    from PIL import Image
+    from oracle import oracle
+    from styletransfer_b200 import constants, img_utils, network
+    style_name = f'pytestvideo{os.getpid()}'
+    models = os.path.join(constants.PROJECT_ROOT_PATH, 'data', 'models')
+    os.makedirs(models, exist_ok=True)
+    ckpt = os.path.join(models, f'video_st_{style_name}_epoch0.pth')
+    params = oracle.make_transform_params(8, 6)
+    torch.save({k: v.clone() for k, v in params.items()}, ckpt)
+    g = torch.Generator().manual_seed(9)
+    frames = [torch.randn(1, 3, 40, 56, generator=g)]
+    for _ in range(6):
+        frames.append(frames[-1] + 0.05 * torch.randn(1, 3, 40, 56, generator=g))
+    work = f'workdir_pytest_{os.getpid()}/'
+    work_abs = os.path.join(constants.PROJECT_ROOT_PATH, work)
+    try:
+        net = network.VideoTransformNet(torch.zeros(1, 3, 8, 8, device='cuda')).cuda()
+        outs = net.process_video('unused.mp4', style_name=style_name, working_dir=work, out_dir=str(tmp_path) + '/', frames=frames)
+        assert len(outs) == len(frames) and sorted(os.listdir(work_abs), key=lambda x: int(x.split('.')[0])) == [f'{i}.png' for i in range(7)]
+        ref = network.VideoTransformNet(torch.zeros(1, 3, 8, 8, device='cuda')).cuda()
+        ref.load_state_dict({k: v.clone() for k, v in params.items()})
+        old = None
+        with torch.no_grad():
+            for i, f in enumerate(frames):
+                f = f.cuda()
+                old = f if old is None else old
+                out = ref(torch.cat([f, old], dim=1))
+                old = out
+                assert torch.equal(out, outs[i])
+                want = tmp_path / f'want{i}.png'
+                img_utils.imshow(out[0], path=str(want))
+                assert np.array_equal(np.asarray(Image.open(want)), np.asarray(Image.open(os.path.join(work_abs, f'{i}.png'))))
+    finally:
+        import shutil
+        shutil.rmtree(work_abs, ignore_errors=True)
+        if os.path.exists(ckpt):
+            os.unlink(ckpt)

@@ -85,6 +85,47 @@ def test_oracle_vs_live_reference_single_pass_equivalence():
                           ['ReLU_3', 'Conv2d_4'], ['ReLU_4'], ['MaxPool2d_4', 'Conv2d_5']]
 
 
+def test_oracle_generic_layers_vs_golden(golden_dir):
+    """oracle.generic_closure (arbitrary loss-layer lists) against the fixture the unmodified reference wrote with
+    edited class attributes (oracle/make_golden.py generic_case)."""
+    from oracle.make_golden import GENERIC_CONVS, GENERIC_LAYERS as GL
+    g = np.load(os.path.join(golden_dir, 'gatys_generic_64x96.npz'))
+    h, w = int(g['h']), int(g['w'])
+    content, style = seeded((1, 3, h, w), 10), seeded((1, 3, h, w), 11)
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12)
+    total, grad, losses = oracle.generic_closure(x0, content, style, oracle.make_vgg_weights(1, GENERIC_CONVS),
+                                                 GL['style'], GL['content'], GL['feature'], float(g['sw']), float(g['cw']))
+    assert abs(total.item() - float(g['total'])) / float(g['total']) < 1e-5
+    assert np.allclose(losses.numpy(), g['losses'], rtol=1e-4, atol=0)
+    assert float((grad - torch.from_numpy(g['grad'])).norm() / torch.from_numpy(g['grad']).norm()) < 1e-4
+
+
+@pytest.mark.skipif(not reference_shim.available(), reason='neither /root/reference nor oracle/_ref present')
+def test_oracle_static_test_vs_live_reference():
+    """oracle.static_test against the reference's own ImageTransformNet.static_test (network.py:772-796)."""
+    ref = reference_shim.load_reference(vgg_seed=1)
+    vw, params = oracle.make_vgg_weights(1), oracle.make_transform_params(8, 3)
+    style = seeded((1, 3, 32, 48), 71)
+    loader = [seeded((2, 1, 3, 32, 48), 180 + i) for i in range(2)]
+    net = ref.ImageTransformNet(style, 2)
+    net.load_state_dict({k: v.clone() for k, v in params.items()})
+    with torch.no_grad():
+        want = net.static_test(loader, ref.StyleNetwork(style, torch.rand([1, 3, 32, 48])))
+    got = oracle.static_test([b.squeeze(1) for b in loader], params, oracle.style_targets(style, vw), vw)
+    assert abs(float(got) - float(want)) / abs(float(want)) < 1e-6
+
+
+def test_gatys_pairs_file_is_split_over_the_ranks():
+    """`stransfer gatys_st --pairs-file`: rank r of W optimises lines r, r + W, ... (independent pairs, no collective)."""
+    from stransfer.clis.gatys_st import parse_pairs
+    text = 'a.jpg s.jpg\n# comment\n\nb.jpg s.jpg out_b.png\nc.jpg t.jpg   # trailing\n'
+    pairs = parse_pairs(text, 'gatys_converted.png')
+    assert pairs == [('a.jpg', 's.jpg', 'gatys_converted_0.png'), ('b.jpg', 's.jpg', 'out_b.png'), ('c.jpg', 't.jpg', 'gatys_converted_2.png')]
+    world = 2
+    shards = [pairs[r::world] for r in range(world)]
+    assert sorted(sum(shards, [])) == sorted(pairs) and [len(x) for x in shards] == [2, 1]
+
+
 # ---------------------------------------------------------------------------
 # the C-ABI library: loads, exports every declared symbol (no compute without a GPU)
 # ---------------------------------------------------------------------------

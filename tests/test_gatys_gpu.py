@@ -77,8 +77,8 @@ def test_run_through_pieces_and_modules(net_mod):
     taps = oracle.vgg_taps(content, vw)
     for piece, ref in [(0, taps[0]), (1, taps[1]), (2, taps[2]), (3, taps[3]), (4, torch.relu(taps[3])), (5, taps[4])]:
         assert rel_l2(net.run_through_pieces(content.cuda(), piece), ref) < TOL_FEATURE
-    with pytest.raises(NotImplementedError):
-        net.run_through_pieces(content.cuda())
+    # all pieces (until = -1): with five conv weights the last layer is ReLU_5
+    assert rel_l2(net.run_through_pieces(content.cuda()), torch.relu(taps[4])) < TOL_FEATURE
     # stand-alone loss modules with autograd (network.py:79-201)
     f = seeded((2, 64, 12, 20), 73)
     tgt = seeded((1, 64, 12, 20), 74)
@@ -196,3 +196,86 @@ def test_cuda_graph_closure_matches_eager(net_mod):
         del junk
     out = net.train_gatys(style, content, steps=2)          # L-BFGS through the graphed closure
     assert out.shape == content.shape and torch.isfinite(out).all()
+
+
+def _generic_net(net_mod):
+    from oracle.make_golden import GENERIC_LAYERS
+
+    class Net(net_mod.StyleNetwork):
+        style_layers, content_layers, feature_loss_layers = GENERIC_LAYERS['style'], GENERIC_LAYERS['content'], GENERIC_LAYERS['feature']
+    return Net
+
+
+def test_non_default_loss_layers_match_reference_golden(net_mod, golden_dir):
+    """The loss layers are class attributes a user may edit (network.py:214-232) and the piece builder is generic over
+    them (network.py:257-314): style nodes on conv / ReLU / max-pool layers up to conv 9 (256 -> 256, 256 -> 512
+    channels), content nodes on ReLU_7 and Conv2d_10 (512 -> 512), a feature node on ReLU_10 -- against the
+    fixture written by the UNMODIFIED reference with the same edited lists (oracle/make_golden.py generic_case)."""
+    from oracle.make_golden import GENERIC_CONVS
+    g = np.load(os.path.join(golden_dir, 'gatys_generic_64x96.npz'))
+    h, w = int(g['h']), int(g['w'])
+    vw = [(a.cuda(), b.cuda()) for a, b in oracle.make_vgg_weights(1, GENERIC_CONVS)]
+    content, style = seeded((1, 3, h, w), 10, device='cuda'), seeded((1, 3, h, w), 11, device='cuda')
+    x0 = content + 0.3 * seeded((1, 3, h, w), 12, device='cuda')
+    net = _generic_net(net_mod)(style, content, vgg_weights=vw)
+    # same pieces as the reference cuts (the last piece holds what follows the last loss layer of the available blocks)
+    assert [p for _, p in net.style_losses] == g['piece_of_style'].tolist()
+    assert [p for _, p in net.content_losses] == g['piece_of_content'].tolist()
+    assert [p for _, p in net.feature_losses] == g['piece_of_feature'].tolist()
+    x = x0.clone().requires_grad_(True)
+    net(x, content)
+    total = net.get_total_current_style_loss(weight=float(g['sw'])) + net.get_total_current_content_loss(weight=float(g['cw']))
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
+    assert record('generic_golden/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
+    assert record('generic_golden/losses_rel_l2', rel_l2(per_node, torch.from_numpy(g['losses']))) < TOL_LOSS_GRAD
+    assert record('generic_golden/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
+    # the feature node takes part in the gradient when asked for (static_test's combination)
+    xf = x0.clone().requires_grad_(True)
+    net(xf, content)
+    (net.get_total_current_style_loss(1e5) + net.get_total_current_feature_loss(1e12)).backward()
+    o = oracle.make_vgg_weights(1, GENERIC_CONVS)
+    from oracle.make_golden import GENERIC_LAYERS as GL
+    xr = x0.cpu().clone().requires_grad_(True)
+    outs = oracle.vgg_layer_outputs(xr, o, set(GL['style']) | set(GL['feature']))
+    with torch.no_grad():
+        s_out = oracle.vgg_layer_outputs(style.cpu(), o, GL['style'])
+        c_out = oracle.vgg_layer_outputs(content.cpu(), o, GL['feature'])
+    ref = 1e5 * sum(oracle.style_loss(outs[n], oracle.gram_matrix(s_out[n])) for n in GL['style']) + \
+        1e12 * sum(oracle.feature_loss(outs[n], c_out[n]) for n in GL['feature'])
+    ref.backward()
+    assert record('generic_feature/grad_rel_l2', rel_l2(xf.grad, xr.grad)) < TOL_LOSS_GRAD
+
+
+def test_non_default_loss_layers_match_oracle_and_all_pieces(net_mod):
+    """The same edited layer lists at a larger, ragged size against the CPU oracle; run_through_pieces through
+    every piece (until = -1, all 16 convs and 5 pools) and up to single pieces; the graph-replayed closure."""
+    from oracle.make_golden import GENERIC_LAYERS as GL
+    h, w = 136, 200
+    vw16 = oracle.make_vgg_weights(1, 16)
+    content, style = seeded((1, 3, h, w), 20), seeded((1, 3, h, w), 21)
+    x0 = content + 0.3 * seeded((1, 3, h, w), 22)
+    o_total, o_grad, o_losses = oracle.generic_closure(x0, content, style, vw16, GL['style'], GL['content'], GL['feature'])
+    net = _generic_net(net_mod)(style.cuda(), content.cuda(), vgg_weights=[(a.cuda(), b.cuda()) for a, b in vw16])
+    x = x0.cuda().requires_grad_(True)
+    net(x, content.cuda())
+    total = net.get_total_current_style_loss(weight=1e5) + net.get_total_current_content_loss(weight=1)
+    total.backward()
+    per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
+    assert record('generic_136x200/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
+    assert record('generic_136x200/losses_rel_l2', rel_l2(per_node, o_losses)) < TOL_LOSS_GRAD
+    assert record('generic_136x200/grad_rel_l2', rel_l2(x.grad, o_grad)) < TOL_LOSS_GRAD
+    # pieces: all of them (MaxPool2d_16), the piece of a max-pool node, of a ReLU node and of a deep conv node
+    names = ['MaxPool2d_16', 'MaxPool2d_4', 'ReLU_7', 'Conv2d_10']
+    outs = oracle.vgg_layer_outputs(content, vw16, names)
+    assert len(net.net_pieces) == 10 and sum(len(list(p.children())) for p in net.net_pieces) == 37
+    assert record('generic/all_pieces_rel_l2', rel_l2(net.run_through_pieces(content.cuda()), outs['MaxPool2d_16'])) < TOL_FEATURE
+    for (node, piece), name in ((net.style_losses[3], 'MaxPool2d_4'), (net.content_losses[0], 'ReLU_7'), (net.content_losses[1], 'Conv2d_10')):
+        assert rel_l2(net.run_through_pieces(content.cuda(), piece), outs[name]) < TOL_FEATURE
+    assert rel_l2(net.content_losses[0][0].target, outs['ReLU_7']) < TOL_FEATURE
+    # the closure train_gatys replays
+    xg = x0.cuda().requires_grad_(True)
+    net.compute_feature_loss = False
+    closure = net.gatys_closure(xg, content.cuda(), 1e5, 1)
+    loss = closure()
+    assert abs(float(loss) - float(o_total)) / abs(float(o_total)) < TOL_LOSS_GRAD and rel_l2(xg.grad, o_grad) < TOL_LOSS_GRAD

@@ -138,6 +138,25 @@ def test_transform_forward_inference_and_input_grad(network):
     assert record('transform_fwd_40x56/input_grad_rel_l2', rel_l2(xg.grad, xr.grad)) < TOL_CHAIN_GRAD
 
 
+def test_video_forward_pair_equals_concatenated_input(network):
+    """VideoTransformNet.forward_pair(frame, previous) reads the 6-channel input of network.py:984-986 from its two
+    sources: same output and parameter gradients, bit for bit, as the forward on torch.cat([frame, previous], 1)."""
+    params = oracle.make_transform_params(6, 6)
+    net = _build(network, network.VideoTransformNet, params, seeded((1, 3, 40, 56), 52).cuda(), 2)
+    a, b = seeded((2, 3, 40, 56), 53).cuda(), seeded((2, 3, 40, 56), 54).cuda()
+    w = seeded((2, 3, 40, 56), 55).cuda()
+    with torch.no_grad():
+        assert torch.equal(net.forward_pair(a, b), net(torch.cat([a, b], dim=1)))
+    grads = []
+    for pair in (True, False):
+        for p in net.parameters():
+            p.grad = None
+        y = net.forward_pair(a, b) if pair else net(torch.cat([a, b], dim=1))
+        (y * w).sum().backward()
+        grads.append(torch.cat([p.grad.reshape(-1) for p in net.parameters()]))
+    assert torch.equal(grads[0], grads[1])
+
+
 def test_standalone_modules_match_torch(network):
     """Conv2d / InstanceNorm2d / ResidualBlock used on their own (NCHW fp32 boundary)."""
     import torch.nn as nn
@@ -217,6 +236,27 @@ def test_training_steps_follow_oracle_trajectory(network):
     assert record('adam6/loss_rel', abs(float(last) - ref_last) / ref_last) < 2e-2
 
 
+def test_static_test_matches_oracle(network):
+    """ImageTransformNet.static_test (network.py:772-796): clamp -> loss network -> style_weight * style + feature,
+    averaged over the test batches; every batch sets its own content / feature targets (two batches of the same
+    shape land on the same device address: the targets must not be cached across them)."""
+    vw = oracle.make_vgg_weights(1)
+    params = oracle.make_transform_params(8, 3)
+    style = seeded((1, 3, 48, 64), 71)
+    loader = [seeded((2, 1, 3, 48, 64), 180 + i) for i in range(3)]
+    ref = oracle.static_test([b.squeeze(1) for b in loader], params, oracle.style_targets(style, vw), vw)
+    net = _build(network, network.ImageTransformNet, params, style.cuda(), 2)
+    loss_net = network.StyleNetwork(style.cuda(), torch.rand([1, 3, 48, 64]).cuda(), vgg_weights=_vgg_cuda())
+    loss_net.compute_feature_loss = False            # static_test switches the feature node on itself and restores this
+    got = net.static_test(loader, loss_net)
+    assert loss_net.compute_feature_loss is False
+    assert record('static_test/rel', abs(float(got) - float(ref)) / abs(float(ref))) < TOL_LOSS_GRAD
+    # the feature term is part of it: with a huge feature weight it dominates and still agrees
+    ref_f = oracle.static_test([b.squeeze(1) for b in loader], params, oracle.style_targets(style, vw), vw, 1.0, 1e12)
+    got_f = net.static_test(loader, loss_net, style_weight=1.0, feature_weight=1e12)
+    assert record('static_test/feature_rel', abs(float(got_f) - float(ref_f)) / abs(float(ref_f))) < TOL_LOSS_GRAD
+
+
 def test_graphed_training_closure_matches_eager(network):
     """The CUDA-graph replay of the static_train closure (packing kernels, content targets, forward,
     backward into the flat bucket) follows the eager closure through four Adam steps on new batches."""
@@ -246,6 +286,49 @@ def test_graphed_training_closure_matches_eager(network):
     assert l0[0] != l0[1]
     worst = max(float((p0[k] - p1[k]).abs().max()) for k in p0)
     assert record('graph_train/param_max_abs_diff', worst) < 1e-6
+
+
+def test_whole_step_graph_with_fused_adam_matches_eager(network):
+    """training_closure(optimizer=FusedAdam): ONE replayed graph per step holds closure -> all-reduce -> Adam, the
+    Adam kernel rewrites the packed weight copies (no packing launches).  Four steps on new batches follow the eager
+    closure + separate optimizer step bit for bit; inference afterwards reads the packs the optimizer maintained, and a
+    load_state_dict behind the optimizer's back is noticed (stale packs are rewritten)."""
+    from styletransfer_b200 import dist as st_dist
+    style = seeded((1, 3, 32, 32), 71).cuda()
+    params = oracle.make_transform_params(8, 3)
+    batches = [seeded((2, 3, 48, 32), 90 + i).cuda() for i in range(4)]
+    results = []
+    for fused in (False, True):
+        net = _build(network, network.ImageTransformNet, params, style, 2)
+        loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda(), vgg_weights=_vgg_cuda())
+        loss_net.compute_feature_loss = False
+        opt = net.get_optimizer()
+        buf = batches[0].clone()
+        if fused:
+            closure = net.training_closure(buf, loss_net, opt.bucket, graph=True, optimizer=opt)
+            assert closure.includes_optimizer is opt and opt._packs is not None and net._pack_cache.frozen
+            # closure + all-reduce + Adam in the graph, and none of the ~28 packing kernels
+            eager_graph = _build(network, network.ImageTransformNet, params, style, 2)
+            plain = eager_graph.training_closure(buf.clone(), loss_net, eager_graph.get_optimizer().bucket, graph=True)
+            assert closure.launches < plain.launches - 20
+        else:
+            closure = net.training_closure(buf, loss_net, opt.bucket, graph=False)
+        losses = []
+        for b in batches:
+            buf.copy_(b)
+            losses.append(float(opt.step(closure)))
+        with torch.no_grad():
+            out = net(batches[0])
+        results.append((losses, {k: v.detach().clone() for k, v in net.state_dict().items()}, out, net, opt))
+    (l0, p0, o0, _, _), (l1, p1, o1, net, opt) = results
+    assert l0 == l1, (l0, l1)
+    assert record('step_graph/param_max_abs_diff', max(float((p0[k] - p1[k]).abs().max()) for k in p0)) == 0.0
+    assert torch.equal(o0, o1)
+    # weights replaced behind the optimizer's back: the frozen packs are stale and get rewritten
+    net.load_state_dict({k: v.clone() for k, v in params.items()})
+    fresh = _build(network, network.ImageTransformNet, params, style, 2)
+    with torch.no_grad():
+        assert torch.equal(net(batches[1]), fresh(batches[1]))
 
 
 @pytest.mark.parametrize('shape', [(1, 3, 136, 200), (2, 3, 60, 92)])
@@ -441,6 +524,51 @@ def test_video_full_size_properties(network):
     t = float(net.get_temporal_loss(prev, prev, frame, out1, temporal_weight=0.8))
     assert abs((l1 - l0) - t) < max(1e-3 * abs(t), 4e-6 * abs(l1))        # the totals are fp32 sums of four terms
     assert float(net.get_temporal_loss(prev, out1, frame, out1, temporal_weight=0.8)) == 0.0
+
+
+def test_video_train_with_flow_matches_manual_recurrence(network):
+    """video_train fed with (frames, flow) pairs: the flow-warped temporal loss (extension; BASELINE
+    configs[4] words the loss as flow-warped) goes through the replayed closure exactly as through a hand-written
+    eager recurrence, and differs from the run without flow."""
+    style = seeded((1, 3, 32, 32), 71).cuda()
+    params = oracle.make_transform_params(8, 6)
+    frames = [seeded((2, 3, 32, 48), 190)]
+    for t in range(1, 3):
+        frames.append(frames[-1] + 0.05 * seeded((2, 3, 32, 48), 190 + t))
+    flows = [torch.zeros(2, 2, 32, 48)] + [seeded((2, 2, 32, 48), 195 + t, 1.5) for t in range(1, 3)]
+    import styletransfer_b200.network as nw
+    orig = nw.load_vgg19_prefix_weights
+    nw.load_vgg19_prefix_weights = lambda seed=None: _vgg_cuda()
+    try:
+        nets = {}
+        for name, clip in (('flow', list(zip(frames, flows))), ('plain', frames)):
+            nets[name] = _build(network, network.VideoTransformNet, params, style, 2)
+            nets[name].video_train('unit', epochs=1, video_loader=[clip], max_iterations=3)
+        ref = _build(network, network.VideoTransformNet, params, style, 2)
+        loss_net = network.StyleNetwork(style, torch.rand([1, 3, 32, 32]).cuda())
+        loss_net.compute_feature_loss = False
+        opt = ref.get_optimizer()
+        old = None
+        for b, fl in zip(frames, flows):
+            b, fl = b.cuda(), fl.cuda()
+            if old is None:
+                old = [b, b]
+            frozen = [old[0], old[1]]
+
+            def closure():
+                loss_net._content_key = None
+                opt.bucket.rebind(); opt.bucket.zero()
+                st = [frozen[0], frozen[1]]
+                total, _ = ref.closure_loss_video(b, st, loss_net, 0.8, flow=fl)
+                old[0], old[1] = st
+                total.backward()
+                return total
+            opt.step(closure)
+    finally:
+        nw.load_vgg19_prefix_weights = orig
+    a, b_, c = nets['flow'].state_dict(), ref.state_dict(), nets['plain'].state_dict()
+    assert record('video_train_flow/param_max_abs_diff_vs_manual', max(float((a[k] - b_[k]).abs().max()) for k in a)) < 1e-6
+    assert max(float((a[k] - c[k]).abs().max()) for k in a) > 1e-6          # the flow changes the training signal
 
 
 def test_video_train_loop_matches_manual_recurrence(network):
