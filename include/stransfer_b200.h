@@ -225,6 +225,20 @@ int st_instnorm_bwd(const void* x_hi, const void* x_lo, const void* gy_hi, const
                     void* dx_hi, void* dx_lo, int dx_planes, float* dx_slot, float* dgamma, float* dbeta, float* dsum,
                     int x_planes, int N, int H, int W, int C, int relu, int up, void* workspace, void* stream);
 
+/* st_instnorm_fwd without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and results as st_instnorm_fwd; the statistics partials
+ * live in a static device array of ST_INSTNORM_STATIC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit.  Limit: N*C <= ST_INSTNORM_STATIC_MAX_NC (e.g. 8 frames of 128 channels), larger problems are rejected with
+ * ST_ERR_INVALID and a message naming the limit.  The array is shared by every call and keeps the last call's
+ * contents (nothing in it needs to start at zero): calls on one stream are ordered, calls that overlap on the GPU
+ * race.  The first call on a device resolves the array's device address (cudaGetSymbolAddress, no allocation). */
+#define ST_INSTNORM_STATIC_MAX_NC 1024
+#define ST_INSTNORM_STATIC_SCRATCH_BYTES (ST_INSTNORM_STATIC_MAX_NC * 128 * 2 * 4)
+int st_instnorm_fwd_static(const void* x_hi, const void* x_lo, const float* gamma, const float* beta, float eps,
+                           void* y_hi, void* y_lo, int planes, float* mean, float* rstd,
+                           int N, int H, int W, int C, int relu, int up, void* stream);
+
 /* ---- optimizer steps on the device ---------- */
 /* torch.optim.Adam.step over every parameter tensor of a transform net in one launch
  * (network.py:643-649, :765).  param / grad / exp_avg / exp_avg_sq are flat fp32 arrays of

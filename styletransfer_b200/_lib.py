@@ -64,6 +64,7 @@ SIGNATURES = {
     'st_temporal_warp_bwd': (_I, [_P, _P, _P, _I, _I, _I, _I, _F, _P, _P, _P, _P]),
     'st_instnorm_workspace_bytes': (_Z, [_I, _I]),
     'st_instnorm_fwd': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P]),
+    'st_instnorm_fwd_static': (_I, [_P, _P, _P, _P, _F, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
     'st_adam_chunk_count': (_Z, [_P, _I]),
     'st_adam_fill_chunks': (_I, [_P, _I, _P]),
     'st_adam_step': (_I, [_P, _P, _P, _P, _P, _Z, _P, _P, _I, _D, _D, _D, _D, _D, _D, _P, _P]),

@@ -26,7 +26,7 @@ FAST = ['--use_fast_math']
 SOURCES = {
     'api.cu': [], 'conv_tc.cu': FAST, 'conv_tcx.cu': FAST, 'conv_generic.cu': FAST, 'conv_image.cu': FAST,
     'conv9.cu': FAST, 'conv9_tc.cu': FAST, 'contract.cu': FAST, 'wgrad_tc.cu': FAST,
-    'elementwise.cu': [], 'norm_losses.cu': [], 'optim.cu': [],
+    'elementwise.cu': [], 'norm_losses.cu': [], 'optim.cu': [], 'no_alloc.cu': [],
 }
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xptxas', '-v']
