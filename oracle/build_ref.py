@@ -2,7 +2,8 @@
 TEST INFRASTRUCTURE ONLY.
 
 The reference is pure Python: "building" it is byte-compiling ``/root/reference/stransfer/*.py`` where they lie
-(``py_compile``, optimisation level 0) into sourceless modules ``oracle/_ref/stransfer/*.pyc`` -- no reference source
+(``py_compile``, optimisation level 0) into sourceless modules ``oracle/_ref/stransfer/*.refbc`` (ordinary .pyc content; the
+gpurun snapshot drops ``*.pyc`` files, hence the extension, and ``oracle/reference_shim.py`` installs a finder for it) -- no reference source
 is copied anywhere, a SHA-256 manifest of the compiled sources is written beside the bytecode.  ``oracle/_ref/`` is
 git-ignored but not gpurun-ignored (like the in-tree ``.so``), and the GPU box runs the same image (same CPython,
 same bytecode magic), so ``bench.py --impl reference`` and
@@ -22,10 +23,11 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.environ.get('STRANSFER_REFERENCE_SRC', '/root/reference')
 DST = os.path.join(ROOT, 'oracle', '_ref')
+EXT = '.refbc'
 
 
 def staged():
-    return os.path.isfile(os.path.join(DST, 'stransfer', 'network.pyc'))
+    return os.path.isfile(os.path.join(DST, 'stransfer', 'network' + EXT))
 
 
 def build():
@@ -43,14 +45,14 @@ def build():
                 continue
             path = os.path.join(base, name)
             rel = os.path.relpath(path, SRC)
-            out = os.path.join(DST, rel) + 'c'
+            out = os.path.join(DST, rel[:-3] + EXT)
             os.makedirs(os.path.dirname(out), exist_ok=True)
             py_compile.compile(path, cfile=out, dfile=rel, doraise=True, optimize=0)
             with open(path, 'rb') as f:
                 manifest[rel] = hashlib.sha256(f.read()).hexdigest()
     with open(os.path.join(DST, 'MANIFEST.json'), 'w') as f:
         json.dump({'source': SRC, 'python': sys.version.split()[0], 'files': manifest}, f, indent=1, sort_keys=True)
-    assert os.path.isfile(os.path.join(dst_pkg, 'network.pyc'))
+    assert os.path.isfile(os.path.join(dst_pkg, 'network' + EXT))
     return DST
 
 

@@ -10,6 +10,9 @@ Shims, none of them on the numeric path:
   3. ``torchvision.models.vgg19(pretrained=True)`` -> random-init VGG-19 whose
      five executed convs carry ``oracle.make_vgg_weights(seed)`` (no network).
 """
+import importlib.abc
+import importlib.machinery
+import importlib.util
 import os
 import sys
 import types
@@ -25,9 +28,32 @@ def _reference_root():
     ``oracle/build_ref.py`` under ``oracle/_ref`` (git-ignored, travels with gpurun)."""
     for cand in (os.environ.get('STRANSFER_REFERENCE_ROOT'), '/root/reference', os.path.join(_HERE, '_ref')):
         if cand and (os.path.isfile(os.path.join(cand, 'stransfer', 'network.py')) or
-                     os.path.isfile(os.path.join(cand, 'stransfer', 'network.pyc'))):
+                     os.path.isfile(os.path.join(cand, 'stransfer', 'network' + BYTECODE_EXT))):
             return cand
     return '/root/reference'
+
+
+BYTECODE_EXT = '.refbc'
+
+
+class _BytecodeFinder(importlib.abc.MetaPathFinder):
+    """Imports ``stransfer`` / ``stransfer.*`` from the sourceless ``*.refbc`` files staged by oracle/build_ref.py
+    (plain .pyc content under an extension the gpurun snapshot does not drop)."""
+
+    def __init__(self, root):
+        self.root = root
+
+    def find_spec(self, name, path=None, target=None):
+        if name != 'stransfer' and not name.startswith('stransfer.'):
+            return None
+        rel = os.path.join(self.root, *name.split('.'))
+        pkg, mod = os.path.join(rel, '__init__' + BYTECODE_EXT), rel + BYTECODE_EXT
+        if os.path.isfile(pkg):
+            return importlib.util.spec_from_file_location(name, pkg, loader=importlib.machinery.SourcelessFileLoader(name, pkg),
+                                                          submodule_search_locations=[rel])
+        if os.path.isfile(mod):
+            return importlib.util.spec_from_file_location(name, mod, loader=importlib.machinery.SourcelessFileLoader(name, mod))
+        return None
 
 
 REFERENCE_ROOT = _reference_root()
@@ -108,11 +134,16 @@ def load_reference(vgg_seed=1, workdir='/tmp/stransfer_ref_cwd', n_convs=5):
     for name in [n for n in sys.modules if n == 'stransfer' or n.startswith('stransfer.')]:
         del sys.modules[name]
     sys.path.insert(0, REFERENCE_ROOT)
+    finder = _BytecodeFinder(REFERENCE_ROOT) if os.path.isfile(os.path.join(REFERENCE_ROOT, 'stransfer', 'network' + BYTECODE_EXT)) else None
+    if finder is not None:
+        sys.meta_path.insert(0, finder)
     try:
         with warnings.catch_warnings():
             warnings.simplefilter('ignore')
             import stransfer.network as ref_network
     finally:
+        if finder is not None:
+            sys.meta_path.remove(finder)
         sys.path.remove(REFERENCE_ROOT)
         os.chdir(cwd)
     assert ref_network.__file__.startswith(REFERENCE_ROOT), ref_network.__file__

@@ -61,6 +61,18 @@ def _source_digest(name, hdr):
     return h.hexdigest()
 
 
+def kernel_sources_digest():
+    """Digest of csrc/*.cu + the headers (no flags): ties a committed profile to the kernels it profiled
+    (bench.py reads profiles/conv_tc_traffic.json only when this matches)."""
+    h = hashlib.sha256()
+    h.update(_headers_digest().encode())
+    for name in sorted(SOURCES):
+        with open(os.path.join(CSRC, name), 'rb') as f:
+            h.update(name.encode())
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
 def _digest():
     hdr = _headers_digest()
     h = hashlib.sha256()

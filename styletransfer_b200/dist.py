@@ -43,17 +43,42 @@ def init(backend=None, device=None):
     return rank, world
 
 
+_FORCED_SINGLE = False
+
+
+class single_process:
+    """Context manager: inside it this process behaves as a world of one although torch.distributed is initialised
+    (no sharding, no TV scaling, no all-reduce, no barrier).  bench.py uses it on rank 0 to time the same global
+    batch on ONE GPU beside the data-parallel run (strong-scaling efficiency); the other ranks wait outside."""
+
+    def __enter__(self):
+        global _FORCED_SINGLE
+        self.prev, _FORCED_SINGLE = _FORCED_SINGLE, True
+
+    def __exit__(self, *exc):
+        global _FORCED_SINGLE
+        _FORCED_SINGLE = self.prev
+
+
+def forced_single():
+    return _FORCED_SINGLE
+
+
+def _active():
+    return dist.is_initialized() and not _FORCED_SINGLE
+
+
 def rank():
-    return dist.get_rank() if dist.is_initialized() else 0
+    return dist.get_rank() if _active() else 0
 
 
 def barrier():
-    if dist.is_initialized():
+    if _active():
         dist.barrier()
 
 
 def world_size():
-    return dist.get_world_size() if dist.is_initialized() else 1
+    return dist.get_world_size() if _active() else 1
 
 
 def tv_scale():
@@ -65,7 +90,7 @@ def tv_scale():
 def shard(batch, rank=None, world=None):
     """The rank's slice of a global batch (dim 0); the batch must divide evenly."""
     world = world_size() if world is None else world
-    rank = (dist.get_rank() if dist.is_initialized() else 0) if rank is None else rank
+    rank = (dist.get_rank() if _active() else 0) if rank is None else rank
     n = batch.shape[0]
     if n % world != 0:
         raise ValueError(f'global batch {n} does not divide over {world} ranks')

@@ -477,6 +477,10 @@ class StyleNetwork(nn.Module):
                     LOGGER.info('Loss: %s', total_loss)
                 return total_loss
             optimizer.step(closure)
+        # diagnostics for callers that time the loop (bench.py): closures evaluated, curvature pairs held at the end
+        self.last_train_stats = {'closures': n_closure[0], 'steps': steps}
+        if isinstance(optimizer, st_optim.DeviceLBFGS):
+            self.last_train_stats['history_pairs'] = int(optimizer.info()['k'])
         self.compute_feature_loss = True
         return input_image
 
