@@ -78,7 +78,8 @@ extern "C" {
 
 int st_arch(void) { return 100; }
 const char* st_last_error(void) { return g_err; }
-int st_set_conv_path(int path) { g_conv_path = path; return ST_OK; }
+int g_conv_debug = 0;        // experiment switches of conv_tc (bits 8.. of st_set_conv_path): see ConvTcParams::dbg
+int st_set_conv_path(int path) { g_conv_path = path & 0xff; g_conv_debug = path >> 8; return ST_OK; }
 static int g_last_conv_kernel = 0;
 int st_last_conv_kernel(void) { return g_last_conv_kernel; }
 long long st_launch_count(void) { return g_st_launches; }

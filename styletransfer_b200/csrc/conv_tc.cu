@@ -7,15 +7,14 @@
 //   * the Gram backward dF = F * D (a 1x1 conv with per-image weights D,
 //     reference: autograd of network.py:92-123).
 //
-// GEMM view: M = 128 output pixels (an 8 x 16 patch), N = BN output channels,
-// K = taps * Cin.  A single TMA box load of a (8+2) x 16 pixel x 64 channel halo
-// patch per horizontal tap s feeds the three vertical taps r: tap r starts
-// r*16 rows = r*2048 bytes into the box, which keeps the 1024-byte alignment the
-// 128B swizzle needs.  Zero padding comes from TMA out-of-bounds fill.
+// GEMM view: M = 128 output pixels (3x3: a 16 x 8 patch), N = BN output channels,
+// K = taps * Cin.  ONE TMA box load of an (16+2) x (8+2) pixel x 64 channel halo
+// patch per plane feeds all nine taps (see Cfg).  Zero padding comes from TMA
+// out-of-bounds fill.
 //
-// Warp roles (320 threads, persistent, one CTA per SM):
+// Warp roles (384 threads, persistent, one CTA per SM):
 //   warp 0  TMA producer      warp 1  tcgen05.mma issuer (+ TMEM alloc)
-//   warps 2-9  epilogue (two per TMEM lane quarter): tcgen05.ld -> bias / mask / add -> split-bf16 stores
+//   warps 4-11 epilogue (two per TMEM lane quarter; warps 2-3 idle, registers handed over by setmaxnreg): tcgen05.ld -> bias / mask / add -> split-bf16 stores
 // Pipelines: A ring (halo boxes), B ring (weight tiles), 2 TMEM accumulators.
 #include "common.cuh"
 #include "ptx.cuh"
@@ -25,23 +24,46 @@
 #include <string>
 #include <string.h>
 
+extern int g_conv_debug;
+
 namespace {
 
 constexpr int KCH = 64;
 
-// KS: 1 or 3 taps per side; BN: output channels per tile; PL: bf16 planes of BOTH operands
-// (1 -> 1 MMA per product, 2 -> 3, 3 -> 6).
-template <int KS, int BN, int PL> struct Cfg {
-    static constexpr int A_ROWS = (TILE_H + KS - 1) * TILE_W;
-    static constexpr int A_PLANE = A_ROWS * 128;            // bytes (64 bf16 per row)
+// KS: 1 or 3 taps per side; BN: output channels per tile; PL: 16-bit planes of BOTH operands
+// (1 -> 1 MMA per product, 2 -> 3, 3 -> 6); RES: resident-weights schedule (see below).
+//
+// Geometry.  3x3: an output tile is 16 rows x 8 pixels (M row m = h*8 + w) and ONE TMA box of (16+2) x (8+2) pixels x
+// 64 channels per plane and channel chunk feeds all nine taps: tap (r, s) is the same box read from row (r*10 + s) on,
+// with a stride of 10 rows (1280 B) between the 8-row groups of the operand -- tcgen05.mma applies the 128-byte
+// swizzle by absolute shared-memory address, exactly as TMA wrote it, so neither the start row nor the group stride
+// has to be a multiple of the 1024-byte swizzle period (ptx::umma_desc_hi_k_sw128_sbo).  Per 128 output pixels that
+// is 45 KB of L2 -> shared-memory traffic for two planes instead of the 120 KB of one 10 x 16 box per horizontal tap.
+// 1x1: tile 8 rows x 16 pixels, dense box, group stride 1024 B.
+//
+// Schedules.  General: an A slot holds all planes of one (tile, chunk) box; the weight tiles of the taps stream
+// through the B ring.  RES (PL = 2, one channel chunk, one channel block, shared weights): the nine weight tiles stay
+// in shared memory for the life of the CTA, which leaves room for three PLANE-sized A slots; a tile first runs the
+// 36 wide MMAs of its hi plane (a0 x [w0|w1]), then the 36 of its lo plane (a1 x w0), so plane slots are filled and
+// released in one fixed order and the loads run up to a whole tile ahead of the MMAs.
+template <int KS, int BN, int PL, bool RES> struct Cfg {
+    static constexpr int TH = KS == 3 ? 16 : 8, TW = KS == 3 ? 8 : 16;
+    static constexpr int BOX_W = TW + KS - 1, BOX_H = TH + KS - 1;
+    static constexpr int A_BYTES = BOX_W * BOX_H * 128;               // one plane of one box (64 channels per pixel row)
+    static constexpr int A_PLANE = (A_BYTES + 1023) & ~1023;          // slots stay 1024-byte aligned
+    static constexpr int A_SBO = KS == 3 ? BOX_W * 128 : 1024;
     static constexpr int B_PLANE = BN * 128;
-    static constexpr int A_SLOT = PL * A_PLANE, B_SLOT = PL * B_PLANE;
-    static constexpr int BAR_BYTES = 256;
+    static constexpr int A_SLOT = RES ? A_PLANE : PL * A_PLANE, B_SLOT = PL * B_PLANE;
+    static constexpr int A_TX = RES ? A_BYTES : PL * A_BYTES;
+    static constexpr int BIAS_MAX = 512;                    // output channels whose bias is staged in shared memory
+    static constexpr int BAR_BYTES = 256 + BIAS_MAX * 4;    // barriers + TMEM slot, then the bias
     static constexpr int SMEM_MAX = 232448;                 // 227 KB opt-in limit
-    static constexpr int NA = (KS == 1 && PL < 3) ? 4 : 2;
+    static constexpr int TAPS = KS * KS;
+    static constexpr int NA = RES ? 3 : (KS == 1 && PL < 3) ? 4 : 2;
     static constexpr int NB_FIT = (SMEM_MAX - 1024 - BAR_BYTES - NA * A_SLOT) / B_SLOT;
-    static constexpr int NB = NB_FIT > 9 ? 9 : NB_FIT;      // 9 slots = all taps of a 3x3 layer resident (see w_resident)
-    static_assert(NB >= 2, "weight ring needs two slots");
+    static constexpr int NB = RES ? TAPS : (NB_FIT > 9 ? 9 : NB_FIT);
+    static_assert(NB >= 2 && NB <= NB_FIT, "weight ring does not fit");
+    static_assert(!RES || (PL == 2 && KS == 3), "resident schedule: two planes, 3x3");
     static constexpr int SMEM = 1024 + NA * A_SLOT + NB * B_SLOT + BAR_BYTES;
     // PL > 1: the a0*w0 products go to a "main" accumulator, all correction terms to a second
     // one, summed in fp32 by the epilogue.  The tensor core's accumulate truncates; keeping the
@@ -51,14 +73,15 @@ template <int KS, int BN, int PL> struct Cfg {
     static constexpr int TMEM_COLS = (2 * STAGE_COLS <= 32) ? 32 : (2 * STAGE_COLS <= 64) ? 64 :
                                      (2 * STAGE_COLS <= 128) ? 128 : (2 * STAGE_COLS <= 256) ? 256 : 512;
     static_assert(2 * STAGE_COLS <= 512, "accumulators exceed TMEM");
+    static_assert(2 * NA + 2 * NB + 4 <= 256 / 8 - 1, "barrier area");
 };
 
-template <int KS, int BN, int PL>
+template <int KS, int BN, int PL, bool RES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
                const ConvTcParams p) {
-    using C = Cfg<KS, BN, PL>;
+    using C = Cfg<KS, BN, PL, RES>;
     constexpr int NA = C::NA, NB = C::NB;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -72,10 +95,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
     uint64_t* t_full = b_empty + NB;         // [2]
     uint64_t* t_empty = t_full + 2;          // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+    float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int pad = KS / 2;
     const int kchunks = p.Cin / KCH;
+    // the bias of every output channel, read by the epilogue as shared-memory broadcasts
+    const bool bias_staged = p.bias && p.Cout <= C::BIAS_MAX;
+    if (bias_staged)
+        for (int i = threadIdx.x; i < p.Cout; i += NUM_THREADS) sbias[i] = p.bias[i];
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmW_hi);
@@ -91,6 +119,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    if (warp < EPI_FIRST_WARP) {
+    ptx::reg_dec<REGS_CONTROL>();          // the whole first warpgroup: producer, MMA issuer and two idle warps
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
@@ -99,31 +129,46 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                 const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
                 const int tw = t % p.tiles_w; t /= p.tiles_w;
                 const int th = t % p.tiles_h; const int n = t / p.tiles_h;
-                const int h0 = th * TILE_H, w0 = tw * TILE_W;
+                const int h0 = th * C::TH - pad, w0 = tw * C::TW - pad;
                 const int wrow = n * p.w_img_rows + nb * BN;
-                for (int c = 0; c < kchunks; ++c) {
+                if (RES) {
+                    if (wk == static_cast<int>(blockIdx.x)) {
+                        // the nine weight tiles: loaded once, never released
 #pragma unroll
-                    for (int s = 0; s < KS; ++s) {
-                        ptx::mbar_wait(&a_empty[a], aph ^ 1);
-                        ptx::mbar_expect_tx(&a_full[a], C::A_SLOT);
-                        uint8_t* dst = sA + a * C::A_SLOT;
-                        // planes 1 and 2 of a tensor are equally spaced: the "lo" map spans both
-                        ptx::tma_load_4d(dst, &tmA_hi, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
-                        if (PL > 1) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n);
-                        if (PL > 2) ptx::tma_load_4d(dst + 2 * C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0 + s - pad, h0 - pad, n + p.N);
-                        if (++a == NA) { a = 0; aph ^= 1; }
-#pragma unroll
-                        for (int r = 0; r < KS; ++r) {
-                            // resident weights: slot = tap, filled once (first tile), never released
-                            if (p.w_resident && wk != static_cast<int>(blockIdx.x)) continue;
-                            ptx::mbar_wait(&b_empty[b], bph ^ 1);
-                            ptx::mbar_expect_tx(&b_full[b], C::B_SLOT);
-                            uint8_t* bd = sB + b * C::B_SLOT;
-                            ptx::tma_load_3d(bd, &tmW_hi, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (PL > 1) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow);
-                            if (PL > 2) ptx::tma_load_3d(bd + 2 * C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, r * KS + s, wrow + p.w_rows_total);
-                            if (++b == NB) { b = 0; bph ^= 1; }
+                        for (int tap = 0; tap < C::TAPS; ++tap) {
+                            ptx::mbar_expect_tx(&b_full[tap], C::B_SLOT);
+                            ptx::tma_load_3d(sB + tap * C::B_SLOT, &tmW_hi, &b_full[tap], 0, tap, wrow);
+                            ptx::tma_load_3d(sB + tap * C::B_SLOT + C::B_PLANE, &tmW_lo, &b_full[tap], 0, tap, wrow);
                         }
+                    }
+#pragma unroll
+                    for (int pl = 0; pl < 2; ++pl) {
+                        ptx::mbar_wait(&a_empty[a], aph ^ 1);
+                        if (p.dbg & 4) { ptx::mbar_arrive(&a_full[a]); if (++a == NA) { a = 0; aph ^= 1; } continue; }
+                        ptx::mbar_expect_tx(&a_full[a], C::A_TX);
+                        ptx::tma_load_4d(sA + a * C::A_SLOT, pl ? &tmA_lo : &tmA_hi, &a_full[a], 0, w0, h0, n);
+                        if (++a == NA) { a = 0; aph ^= 1; }
+                    }
+                    continue;
+                }
+                for (int c = 0; c < kchunks; ++c) {
+                    ptx::mbar_wait(&a_empty[a], aph ^ 1);
+                    ptx::mbar_expect_tx(&a_full[a], C::A_TX);
+                    uint8_t* dst = sA + a * C::A_SLOT;
+                    // planes 1 and 2 of a tensor are equally spaced: the "lo" map spans both
+                    ptx::tma_load_4d(dst, &tmA_hi, &a_full[a], c * KCH, w0, h0, n);
+                    if (PL > 1) ptx::tma_load_4d(dst + C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0, h0, n);
+                    if (PL > 2) ptx::tma_load_4d(dst + 2 * C::A_PLANE, &tmA_lo, &a_full[a], c * KCH, w0, h0, n + p.N);
+                    if (++a == NA) { a = 0; aph ^= 1; }
+#pragma unroll 1
+                    for (int tap = 0; tap < C::TAPS; ++tap) {
+                        ptx::mbar_wait(&b_empty[b], bph ^ 1);
+                        ptx::mbar_expect_tx(&b_full[b], C::B_SLOT);
+                        uint8_t* bd = sB + b * C::B_SLOT;
+                        ptx::tma_load_3d(bd, &tmW_hi, &b_full[b], c * KCH, tap, wrow);
+                        if (PL > 1) ptx::tma_load_3d(bd + C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, tap, wrow);
+                        if (PL > 2) ptx::tma_load_3d(bd + 2 * C::B_PLANE, &tmW_lo, &b_full[b], c * KCH, tap, wrow + p.w_rows_total);
+                        if (++b == NB) { b = 0; bph ^= 1; }
                     }
                 }
             }
@@ -135,7 +180,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         {
             const bool leader = ptx::elect_one();
             const uint32_t fmt = p.fmt_bits;
-            constexpr uint32_t desc_hi = ptx::umma_desc_hi_k_sw128();
+            constexpr uint32_t a_hi = ptx::umma_desc_hi_k_sw128_sbo(C::A_SBO), b_hi = ptx::umma_desc_hi_k_sw128();
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
             int it = 0;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
@@ -143,78 +188,113 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                 ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
                 ptx::tc_fence_after();
                 const uint32_t d_main = tmem_base + acc * C::STAGE_COLS;
-                    uint32_t acc_main = 0;
-                for (int c = 0; c < kchunks; ++c) {
-#pragma unroll
-                    for (int s = 0; s < KS; ++s) {
+                uint32_t acc_main = 0;
+                if (RES) {
+                    // rolled on purpose: a fully unrolled tile is > 1000 SASS instructions of descriptor arithmetic that
+                    // spill uniform registers and miss the instruction cache -- the issue rate of this one warp, not the
+                    // tensor pipe, then bounds the kernel (profiles/r02o: 59 % tensor-pipe activity, epilogue warps idle)
+                    if (it == 0) {
+#pragma unroll 1
+                        for (int tap = 0; tap < C::TAPS; ++tap) ptx::mbar_wait(&b_full[tap], 0);
+                        ptx::tc_fence_after();
+                    }
+#pragma unroll 1
+                    for (int pl = 0; pl < 2; ++pl) {
                         ptx::mbar_wait(&a_full[a], aph);
                         ptx::tc_fence_after();
-                        const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
+                        const uint32_t idesc = ptx::umma_idesc_nofmt(BLOCK_M, pl == 0 ? 2 * BN : BN) | fmt;
+                        const uint32_t d = pl == 0 ? d_main : d_main + BN;
+                        uint32_t a_lo = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
+                        uint32_t b_lo = ptx::umma_desc_lo(ptx::smem_u32(sB));
+#pragma unroll 1
+                        for (int r = 0; r < KS; ++r, a_lo += (C::BOX_W * 128) >> 4, b_lo += (KS * C::B_SLOT) >> 4) {
+                            if (leader && !(p.dbg & 2)) {
+                                // one filter row = 12 MMAs per elected-lane region
 #pragma unroll
-                        for (int r = 0; r < KS; ++r) {
-                            if (!p.w_resident || it == 0) {
-                                ptx::mbar_wait(&b_full[b], bph);
-                                ptx::tc_fence_after();
-                            }
-                            const uint32_t b_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sB + b * C::B_SLOT));
-                            const uint32_t a_lo = a_lo0 + ((r * TILE_W * 128) >> 4);
+                                for (int sx = 0; sx < KS; ++sx)
 #pragma unroll
-                            for (int k = 0; k < KCH / 16; ++k) {
-                                // planes of B are consecutive N rows in shared memory, so one MMA of N = 2*BN / 3*BN
-                                // multiplies a plane of A with several planes of B (A is read once, not per pass):
-                                //   D0 = a0 w0 | D1 = a0 w1 + a1 w0 | D2 = a0 w2 + a1 w1 + a2 w0   (adjacent TMEM columns)
-                                const uint32_t ak = a_lo + ((k * 32) >> 4), bk = b_lo0 + ((k * 32) >> 4);
-                                if (PL == 1) {
-                                    if (leader) ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), acc_main);
-                                } else if (PL == 2) {
-                                    if (leader) {
-                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc_main);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
-                                    }
-                                } else if (C::NACC == 3) {
-                                    if (leader) {
-                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 3 * BN) | fmt), acc_main);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), 1u);
-                                        ptx::mma_bf16_ss2(d_main + 2 * BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
-                                    }
-                                } else {
-                                    // 3 planes, BN = 128: N = 256 is the widest MMA; the 2^-16 terms share the D1 accumulator
-                                    if (leader) {
-                                        const uint32_t id1 = (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt);
-                                        ptx::mma_bf16_ss2(d_main, ak, bk, desc_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc_main);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak, bk + ((2 * C::B_PLANE) >> 4), desc_hi, id1, 1u);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk + (C::B_PLANE >> 4), desc_hi, id1, 1u);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak + ((2 * C::A_PLANE) >> 4), bk, desc_hi, id1, 1u);
-                                        ptx::mma_bf16_ss2(d_main + BN, ak + (C::A_PLANE >> 4), bk, desc_hi, id1, 1u);
-                                    }
-                                }
-                                acc_main = 1;
+                                    for (int k = 0; k < KCH / 16; ++k)
+                                        ptx::mma_ss2h(d, a_lo + ((sx * 128 + k * 32) >> 4), a_hi, b_lo + ((sx * C::B_SLOT + k * 32) >> 4), b_hi, idesc,
+                                                      (pl == 1 || sx > 0 || k > 0) ? 1u : acc_main);
                             }
-                            if (leader && !p.w_resident) ptx::tc_commit(&b_empty[b]);
                             __syncwarp();
-                            if (++b == NB) { b = 0; bph ^= 1; }
+                            acc_main = 1;
                         }
                         if (leader) ptx::tc_commit(&a_empty[a]);
+                        __syncwarp();
                         if (++a == NA) { a = 0; aph ^= 1; }
                     }
+                    if (leader) ptx::tc_commit(&t_full[acc]);
+                    __syncwarp();
+                    continue;
+                }
+                for (int c = 0; c < kchunks; ++c) {
+                    ptx::mbar_wait(&a_full[a], aph);
+                    ptx::tc_fence_after();
+                    const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
+#pragma unroll 1
+                    for (int tap = 0; tap < C::TAPS; ++tap) {
+                        ptx::mbar_wait(&b_full[b], bph);
+                        ptx::tc_fence_after();
+                        const uint32_t b_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sB + b * C::B_SLOT));
+                        const int r = tap / KS, s = tap - r * KS;
+                        const uint32_t a_lo = a_lo0 + (((r * C::BOX_W + s) * 128) >> 4);
+                        // planes of B are consecutive N rows in shared memory, so one MMA of N = 2*BN / 3*BN
+                        // multiplies a plane of A with several planes of B (A is read once, not per pass):
+                        //   D0 = a0 w0 | D1 = a0 w1 + a1 w0 | D2 = a0 w2 + a1 w1 + a2 w0   (adjacent TMEM columns)
+                        if (leader) {
+#pragma unroll
+                            for (int k = 0; k < KCH / 16; ++k) {
+                                const uint32_t ak = a_lo + ((k * 32) >> 4), bk = b_lo0 + ((k * 32) >> 4);
+                                const uint32_t acc0 = k > 0 ? 1u : acc_main;
+                                if (PL == 1) {
+                                    ptx::mma_ss2h(d_main, ak, a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), acc0);
+                                } else if (PL == 2) {
+                                    ptx::mma_ss2h(d_main, ak, a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc0);
+                                    ptx::mma_ss2h(d_main + BN, ak + (C::A_PLANE >> 4), a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
+                                } else if (C::NACC == 3) {
+                                    ptx::mma_ss2h(d_main, ak, a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 3 * BN) | fmt), acc0);
+                                    ptx::mma_ss2h(d_main + BN, ak + (C::A_PLANE >> 4), a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), 1u);
+                                    ptx::mma_ss2h(d_main + 2 * BN, ak + ((2 * C::A_PLANE) >> 4), a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt), 1u);
+                                } else {
+                                    // 3 planes, BN = 128: N = 256 is the widest MMA; the 2^-16 terms share the D1 accumulator
+                                    const uint32_t id1 = (ptx::umma_idesc_nofmt(BLOCK_M, BN) | fmt);
+                                    ptx::mma_ss2h(d_main, ak, a_hi, bk, b_hi, (ptx::umma_idesc_nofmt(BLOCK_M, 2 * BN) | fmt), acc0);
+                                    ptx::mma_ss2h(d_main + BN, ak, a_hi, bk + ((2 * C::B_PLANE) >> 4), b_hi, id1, 1u);
+                                    ptx::mma_ss2h(d_main + BN, ak + (C::A_PLANE >> 4), a_hi, bk + (C::B_PLANE >> 4), b_hi, id1, 1u);
+                                    ptx::mma_ss2h(d_main + BN, ak + ((2 * C::A_PLANE) >> 4), a_hi, bk, b_hi, id1, 1u);
+                                    ptx::mma_ss2h(d_main + BN, ak + (C::A_PLANE >> 4), a_hi, bk, b_hi, id1, 1u);
+                                }
+                            }
+                            ptx::tc_commit(&b_empty[b]);
+                        }
+                        acc_main = 1;
+                        __syncwarp();
+                        if (++b == NB) { b = 0; bph ^= 1; }
+                    }
+                    if (leader) ptx::tc_commit(&a_empty[a]);
+                    __syncwarp();
+                    if (++a == NA) { a = 0; aph ^= 1; }
                 }
                 if (leader) ptx::tc_commit(&t_full[acc]);
                 __syncwarp();
             }
         }
+    }
     } else {
-        // ===================== epilogue (warps 2..9) =====================
+        // ===================== epilogue (warps 4..11) =====================
+        ptx::reg_inc<REGS_EPILOGUE>();
         auto dec = [&](int wk, int m) {
             TcPix px;
             px.nb = wk % p.n_blocks; int t = wk / p.n_blocks;
             const int tw = t % p.tiles_w; t /= p.tiles_w;
             const int th = t % p.tiles_h; const int n = t / p.tiles_h;
-            const int h = th * TILE_H + m / TILE_W, w = tw * TILE_W + m % TILE_W;
+            const int h = th * C::TH + m / C::TW, w = tw * C::TW + m % C::TW;
             px.valid = (h < p.H) && (w < p.W);
             px.pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
             return px;
         };
-        tc_epilogue_warps<BN, C::NACC>(p, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
+        tc_epilogue_warps<BN, C::NACC>(p, bias_staged ? sbias : p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
     }
 
     ptx::tc_fence_before();
@@ -291,21 +371,18 @@ inline int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
     return st_make_tmap(out, ptr, rank, dims, box, 128, 1);
 }
 
-template <int KS, int BN, int PL>
+template <int KS, int BN, int PL, bool RES>
 int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
            const ConvTcParams& p, cudaStream_t stream) {
-    using C = Cfg<KS, BN, PL>;
+    using C = Cfg<KS, BN, PL, RES>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN, PL, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) { st_set_error("conv_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
-    int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    ConvTcParams q = p;
-    // one K chunk, one channel block, shared weights, and the ring holds all taps: load the weights once
-    q.w_resident = (C::NB == KS * KS && p.Cin == KCH && p.n_blocks == 1 && p.w_img_rows == 0) ? 1 : 0;
-    conv_tc_kernel<KS, BN, PL><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, q);
+    const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
+    conv_tc_kernel<KS, BN, PL, RES><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
 }
@@ -313,9 +390,16 @@ int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, 
 template <int KS, int BN>
 int launch_planes(int planes, const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
                   const ConvTcParams& p, cudaStream_t stream) {
-    if (planes == 3) return launch<KS, BN, 3>(ah, al, wh, wl, p, stream);
-    if (planes == 2) return launch<KS, BN, 2>(ah, al, wh, wl, p, stream);
-    return launch<KS, BN, 1>(ah, al, wh, wl, p, stream);
+    if constexpr (KS == 3 && BN <= 64) {
+        // one K chunk, one channel block, shared weights: the nine weight tiles stay in shared memory
+        if (planes == 2 && p.w_resident) return launch<KS, BN, 2, true>(ah, al, wh, wl, p, stream);
+    }
+    if constexpr (!(KS == 3 && BN == 128)) {
+        if (planes == 3) return launch<KS, BN, 3, false>(ah, al, wh, wl, p, stream);
+    }
+    if (planes == 3) { st_set_error("conv_tc: 3 planes with BN = 128 (3x3) is dispatched as two BN = 64 blocks"); return ST_ERR_UNSUPPORTED; }
+    if (planes == 2) return launch<KS, BN, 2, false>(ah, al, wh, wl, p, stream);
+    return launch<KS, BN, 1, false>(ah, al, wh, wl, p, stream);
 }
 
 }  // namespace
@@ -331,33 +415,36 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo, int add_code,
                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_nchw, int Cnchw,
                 float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, cudaStream_t stream) {
-    const int BN = (Cout % 128 == 0) ? 128 : Cout;
     const int taps = ks * ks;
     ST_CHECK_ARG(!out_nchw || (Cnchw >= 1 && Cnchw <= 4 && !mask && !add_hi), "conv_tc: the NCHW output takes <= 4 channels and no mask / addend");
     ST_CHECK_ARG(pc_f16(x_planes) == pc_f16(w_planes), "conv_tc: activation and weight planes must have the same 16-bit format");
-    ConvTcParams p;
-    p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
-    p.tiles_h = (H + TILE_H - 1) / TILE_H; p.tiles_w = (W + TILE_W - 1) / TILE_W;
-    p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
-    p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
-    p.w_resident = 0;        // set by launch<> when every weight tile of the layer fits the B ring
     // both operands are read at the same plane count (the lower one if they differ)
     const int xp = pc_planes(x_planes), wp = pc_planes(w_planes);
     const int a_planes = x_lo ? (xp >= 3 ? 3 : (xp >= 2 ? 2 : 1)) : 1;
     const int w_planes_ = w_lo ? (wp >= 3 ? 3 : (wp >= 2 ? 2 : 1)) : 1;
     const int planes = a_planes < w_planes_ ? a_planes : w_planes_;
+    // 3x3 with three planes: two A slots of three 23 KB planes leave no room for 128-row weight tiles -> 64-channel blocks
+    const int BN = (Cout % 128 == 0) ? ((ks == 3 && planes == 3) ? 64 : 128) : Cout;
+    const int TH = ks == 3 ? 16 : 8, TW = ks == 3 ? 8 : 16;
+    ConvTcParams p;
+    p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
+    p.tiles_h = (H + TH - 1) / TH; p.tiles_w = (W + TW - 1) / TW;
+    p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
+    p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
+    p.w_resident = (ks == 3 && BN <= 64 && planes == 2 && Cin == KCH && p.n_blocks == 1 && w_img_rows == 0) ? 1 : 0;
     p.fmt_bits = ptx::umma_fmt_bits(pc_f16(x_planes));
     p.out_planes = out_planes; p.add_code = add_code;
     p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = out_nchw; p.nchw_c = Cnchw; p.out_f32 = nullptr;
+    p.dbg = g_conv_debug;
 
     // the third plane follows the second at the same stride: the "lo" map simply spans both
     CUtensorMap ah, al, wh, wl;
     uint64_t ad[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     uint64_t ad2[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)N * (planes == 3 ? 2 : 1)};
-    uint32_t ab[4] = {KCH, TILE_W, (uint32_t)(TILE_H + ks - 1), 1};
+    uint32_t ab[4] = {KCH, (uint32_t)(TW + ks - 1), (uint32_t)(TH + ks - 1), 1};
     uint64_t wd[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total};
     uint64_t wd2[3] = {(uint64_t)Cin, (uint64_t)taps, (uint64_t)w_rows_total * (planes == 3 ? 2 : 1)};
     uint32_t wb[3] = {KCH, 1, (uint32_t)BN};

@@ -8,8 +8,12 @@
 namespace {
 
 constexpr int TILE_H = 8, TILE_W = 16, BLOCK_M = 128;
-constexpr int NUM_THREADS = 320;                 // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
-constexpr int EPI_WARPS = 8;
+// three warpgroups: warp 0 TMA producer, warp 1 MMA issuer (warps 2, 3 idle), warps 4..11 epilogue.  After set-up the
+// first warpgroup hands most of its registers to the two epilogue warpgroups (setmaxnreg): the epilogue keeps a
+// 32-column group of up to three accumulators plus the prefetched mask / addend of the next tile in registers.
+constexpr int NUM_THREADS = 384;
+constexpr int EPI_WARPS = 8, EPI_FIRST_WARP = 4;
+constexpr int REGS_CONTROL = 72, REGS_EPILOGUE = 216;      // 128 * 72 + 256 * 216 = 64512 <= 65536
 
 struct ConvTcParams {
     int N, H, W, Cin, Cout;
@@ -31,6 +35,7 @@ struct ConvTcParams {
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
     float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
     float* out_f32;                 // optional fp32 [pixel][Cout] output (unfused launches only)
+    int dbg;                        // experiments (tools/bench_conv.py --dbg): 1 no global stores, 2 no MMAs, 4 no activation loads
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -72,15 +77,20 @@ __device__ __forceinline__ TcMul tc_muls(const ConvTcParams& p) {
     return m;
 }
 
-template <int BN, int NACC, bool FUSED>
-__device__ __forceinline__ void tc_chunk(const ConvTcParams& p, const TcMul& mul, uint32_t taddr, const TcPix& px, int col,
-                                         const uint32_t* mk, const uint32_t* ah, const uint32_t* al) {
-    uint32_t r[16], rc[16], rd[16];
+// accumulator columns [col, col + 16) of up to three accumulators -> registers (no wait)
+template <int BN, int NACC>
+__device__ __forceinline__ void tc_load_chunk(uint32_t taddr, int col, uint32_t (&r)[16], uint32_t (&rc)[16], uint32_t (&rd)[16]) {
     ptx::tmem_ld16(taddr + col, r);
     if (NACC > 1) ptx::tmem_ld16(taddr + BN + col, rc);
     if (NACC > 2) ptx::tmem_ld16(taddr + 2 * BN + col, rd);
-    ptx::tmem_ld_wait();
-    if (!px.valid) return;
+}
+
+// one 16-channel chunk, accumulators already in registers: bias -> mask -> addend -> stores.
+// bias: [Cout] in shared memory (conv_tc stages it once per CTA) or global, or null.
+template <int BN, int NACC, bool FUSED>
+__device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPix& px, int col,
+                                                 const uint32_t (&r)[16], const uint32_t (&rc)[16], const uint32_t (&rd)[16],
+                                                 const uint32_t* mk, const uint32_t* ah, const uint32_t* al) {
     const int ch = px.nb * BN + col;
     const size_t o = px.pix * p.Cout + ch;
     float v[16];
@@ -90,10 +100,10 @@ __device__ __forceinline__ void tc_chunk(const ConvTcParams& p, const TcMul& mul
         if (NACC == 2) v[i] += __uint_as_float(rc[i]);
         if (NACC == 3) v[i] += __uint_as_float(rc[i]) + __uint_as_float(rd[i]);   // small terms first
     }
-    if (p.bias) {
+    if (bias) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const float4 b = *reinterpret_cast<const float4*>(p.bias + ch + i * 4);
+            const float4 b = *reinterpret_cast<const float4*>(bias + ch + i * 4);
             v[4 * i] = fmaf(v[4 * i], mul.acc, b.x); v[4 * i + 1] = fmaf(v[4 * i + 1], mul.acc, b.y);
             v[4 * i + 2] = fmaf(v[4 * i + 2], mul.acc, b.z); v[4 * i + 3] = fmaf(v[4 * i + 3], mul.acc, b.w);
         }
@@ -151,20 +161,35 @@ __device__ __forceinline__ void tc_chunk(const ConvTcParams& p, const TcMul& mul
     }
 }
 
-template <int BN, int NACC, int GCH>
-__device__ __forceinline__ void tc_process(const ConvTcParams& p, const TcMul& mul, const TcPre& b, uint32_t taddr, const TcPix& px, int col0) {
+// A group of GCH (16 or 32) columns: ALL its accumulator loads are issued before the single wait, and when the group is
+// the last one of the tile the TMEM stage is handed back to the MMA warp right after that wait -- the arithmetic and
+// the global stores of a tile run while the tensor core already fills the stage again.  (The epilogue is latency
+// bound: 8 warps, long dependent chains; per-chunk load -> wait -> store sequences held a stage for the whole epilogue
+// and the tensor pipe idled 40 % of the time, profiles/r02o_conv_tc_ncu_full_summary.csv.)
+template <int BN, int NACC, int GCH, bool FUSED, class EndTile>
+__device__ __forceinline__ void tc_group(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPre* pre, uint32_t taddr,
+                                         const TcPix& px, int col0, bool last, const EndTile& end_tile) {
+    constexpr int NCH = GCH / 16;
+    uint32_t r[NCH][16], rc[NCH][16], rd[NCH][16];
 #pragma unroll
-    for (int j = 0; j < GCH / 16; ++j) tc_chunk<BN, NACC, true>(p, mul, taddr, px, col0 + j * 16, b.mk[j], b.ah[j], b.al[j]);
+    for (int j = 0; j < NCH; ++j) tc_load_chunk<BN, NACC>(taddr, col0 + j * 16, r[j], rc[j], rd[j]);
+    ptx::tmem_ld_wait();
+    if (last) end_tile();
+    if (!px.valid || (p.dbg & 1)) return;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j)
+        tc_chunk_compute<BN, NACC, FUSED>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j],
+                                          FUSED ? pre->mk[j] : nullptr, FUSED ? pre->ah[j] : nullptr, FUSED ? pre->al[j] : nullptr);
 }
 
-// dec(wk, m) -> TcPix of accumulator row m of work item wk
+// dec(wk, m) -> TcPix of accumulator row m of work item wk.  bias: see tc_chunk_compute.
 template <int BN, int NACC, class Decode>
-__device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_t tmem_base, int stage_cols,
+__device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const float* bias, uint32_t tmem_base, int stage_cols,
                                                   uint64_t* t_full, uint64_t* t_empty, int warp, int lane, const Decode& dec) {
     constexpr int CW = BN >= 32 ? BN / 2 : BN;            // columns per warp
     constexpr int GCH = CW < 32 ? CW : 32;                // channels per register buffer
     constexpr int NGRP = CW / GCH;
-    const int q = warp & 3, hf = (warp - 2) >> 2;
+    const int q = warp & 3, hf = (warp - EPI_FIRST_WARP) >> 2;
     const int m = q * 32 + lane;
     const bool active = BN >= 32 || hf == 0;
     const int col_base = BN >= 32 ? hf * CW : 0;
@@ -173,18 +198,20 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
     const int step = gridDim.x;
     auto taddr_of = [&](int it) { return tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (it & 1) * stage_cols; };
     auto begin_tile = [&](int it) { ptx::mbar_wait(&t_full[it & 1], (it >> 1) & 1); ptx::tc_fence_after(); };
-    auto end_tile = [&](int it) { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
 
     if (!fused || !active) {
         int it = 0;
         for (int wk = blockIdx.x; wk < p.work; wk += step, ++it) {
             const TcPix px = dec(wk, m);
             begin_tile(it);
+            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
             if (active) {
-#pragma unroll 1
-                for (int j = 0; j < CW / 16; ++j) tc_chunk<BN, NACC, false>(p, mul, taddr_of(it), px, col_base + j * 16, nullptr, nullptr, nullptr);
+#pragma unroll
+                for (int g = 0; g < NGRP; ++g)
+                    tc_group<BN, NACC, GCH, false>(p, mul, bias, nullptr, taddr_of(it), px, col_base + g * GCH, g == NGRP - 1, end_tile);
+            } else {
+                end_tile();
             }
-            end_tile(it);
         }
         return;
     }
@@ -199,11 +226,11 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             TcPix nx = px;
             if (more) nx = dec(wk + step, m);
             begin_tile(it);
-            tc_process<BN, NACC, GCH>(p, mul, A, taddr_of(it), px, col_base);
+            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
+            tc_group<BN, NACC, GCH, true>(p, mul, bias, &A, taddr_of(it), px, col_base, false, end_tile);
             if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
-            tc_process<BN, NACC, GCH>(p, mul, B, taddr_of(it), px, col_base + GCH);
+            tc_group<BN, NACC, GCH, true>(p, mul, bias, &B, taddr_of(it), px, col_base + GCH, true, end_tile);
             if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
-            end_tile(it);
         }
     } else {
         // buffers alternate between tiles: A holds tile k, B tile k + 1; tile k + 2 is fetched into A after tile k
@@ -211,12 +238,13 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
         if (wk0 < p.work) { const TcPix px = dec(wk0, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
         if (wk1 < p.work) { const TcPix px = dec(wk1, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
         int it = 0;
+        auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
         while (wk0 < p.work) {
             {
                 const TcPix px = dec(wk0, m);
                 begin_tile(it);
-                tc_process<BN, NACC, GCH>(p, mul, A, taddr_of(it), px, col_base);
-                end_tile(it); ++it;
+                tc_group<BN, NACC, GCH, true>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile);
+                ++it;
             }
             const int wk2 = wk0 + 2 * step;
             if (wk2 < p.work) { const TcPix px = dec(wk2, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
@@ -224,8 +252,8 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, uint32_
             {
                 const TcPix px = dec(wk1, m);
                 begin_tile(it);
-                tc_process<BN, NACC, GCH>(p, mul, B, taddr_of(it), px, col_base);
-                end_tile(it); ++it;
+                tc_group<BN, NACC, GCH, true>(p, mul, bias, &B, taddr_of(it), px, col_base, true, end_tile);
+                ++it;
             }
             const int wk3 = wk1 + 2 * step;
             if (wk3 < p.work) { const TcPix px = dec(wk3, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }

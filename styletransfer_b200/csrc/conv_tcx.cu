@@ -6,7 +6,7 @@
 //     no multiplications by the inserted zeros),
 //   * 3x3 stride-1 convs whose K side has 32 channels (backward-data of the 64 -> 32 layer,
 //     network.py:594-599) with 64-byte-swizzled operand rows.
-// Same structure as conv_tc_kernel (warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue,
+// Same structure as conv_tc_kernel (warp 0 TMA producer, warp 1 MMA issuer, warps 4-11 epilogue,
 // A ring / B ring / two TMEM stages, main + correction accumulators); what differs is that the list
 // of A boxes per K chunk, the taps each box feeds (row offset into the box, weight tap index) and
 // the output pixel mapping come from a small table in the kernel parameters:
@@ -102,6 +102,8 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    if (warp < EPI_FIRST_WARP) {
+    ptx::reg_dec<REGS_CONTROL>();          // the whole first warpgroup: producer, MMA issuer and two idle warps
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
@@ -202,8 +204,10 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             if (leader) ptx::tc_commit(&t_full[acc]);
             __syncwarp();
         }
+    }
     } else {
-        // ===================== epilogue (warps 2..9) =====================
+        // ===================== epilogue (warps 4..11) =====================
+        ptx::reg_inc<REGS_EPILOGUE>();
         auto dec = [&](int wk, int m) {
             const XWork w = x_decode(wk, p, geo.per_cls);
             const XClass& g = geo.cls[w.cls];
@@ -214,7 +218,7 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
             px.pix = (static_cast<size_t>(w.n) * geo.OH + oh) * geo.OW + ow;
             return px;
         };
-        tc_epilogue_warps<BN, C::NACC>(p, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
+        tc_epilogue_warps<BN, C::NACC>(p, p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
     }
 
     ptx::tc_fence_before();
@@ -324,7 +328,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
-    p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32;
+    p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32; p.dbg = 0;
 
     CUtensorMap ah, al, wh, wl;
     const int ps = mode == 1 ? 2 : 1;

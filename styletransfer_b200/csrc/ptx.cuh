@@ -76,6 +76,10 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uin
         : "memory");
 }
 
+// ---- register reallocation between warpgroups (4 aligned warps execute it together) ----
+template <int REGS> __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS)); }
+template <int REGS> __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS)); }
+
 // ---- tcgen05 -----------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
@@ -114,6 +118,18 @@ __device__ __forceinline__ void mma_bf16_ss2(uint32_t d_tmem, uint32_t a_lo, uin
         "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// same with a separate hi word per operand (the stride between 8-row groups of A and of B differ)
+__device__ __forceinline__ void mma_ss2h(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                         uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+        "mov.b64 da, {%1, %2};\n\t"
+        "mov.b64 db, {%3, %4};\n\t"
+        "setp.ne.b32 p, %6, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // 32 lanes x 16 consecutive fp32 columns: thread i of the warp gets lane (base_lane + i)
 __device__ __forceinline__ void tmem_ld16(uint32_t addr, uint32_t (&r)[16]) {
@@ -148,6 +164,13 @@ __device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr) {
 }
 __host__ __device__ constexpr uint32_t umma_desc_hi_k_sw128() {
     return static_cast<uint32_t>(1024 >> 4) | (1u << 14) | (2u << 29);
+}
+// the same with a stride of `sbo_bytes` between consecutive 8-row groups.  The swizzle of tcgen05.mma (as of TMA) is a
+// function of the ABSOLUTE shared-memory address (16-byte chunk index ^= address bits [7,10)): an operand may start at
+// any 128-byte row of a TMA-written box and step over its groups with any multiple of 128 bytes, base-offset field 0
+// (measured: profiles/r02k_probe_swizzle_offset.log)
+__host__ __device__ constexpr uint32_t umma_desc_hi_k_sw128_sbo(int sbo_bytes) {
+    return static_cast<uint32_t>(sbo_bytes >> 4) | (1u << 14) | (2u << 29);
 }
 // Instruction descriptor for kind::f16: bf16 A/B (K-major both), fp32 accumulate.
 //   [4,6) c_format=1 (f32)  [7,10) a_format=1 (bf16)  [10,13) b_format=1 (bf16)

@@ -13,10 +13,22 @@ import pytest
 import torch
 
 from oracle import oracle
-from tests.util import nhwc, record, rel_l2, seeded
+from tests.util import nhwc, record, rel_l2, relu_decision_flips, seeded
 
 pytestmark = pytest.mark.gpu
 TOL_FEATURE, TOL_LOSS_GRAD = 1e-2, 1e-3
+# input-gradient bound of the ten-conv loss networks when ReLU decisions of near-zero pre-activations differ from the
+# oracle's (tests.util.relu_decision_flips): each flipped element of an 8x12 ... 16x24 feature map moves a whole receptive
+# field of the gradient.  With no flipped decision the bound is TOL_LOSS_GRAD.
+TOL_GRAD_WITH_FLIPS, FLIP_MARGIN = 5e-3, 1e-4
+
+
+def _deep_grad_tol(tag, x0_cpu, vw_cpu, n_convs):
+    flips, worst = relu_decision_flips(x0_cpu, vw_cpu, n_convs)
+    record(tag + '/relu_decision_flips', flips)
+    record(tag + '/flipped_value_over_layer_max', worst)
+    assert worst < FLIP_MARGIN, 'a ReLU decision differs on an element that is NOT near zero: a forward error, not rounding'
+    return TOL_LOSS_GRAD if flips == 0 else TOL_GRAD_WITH_FLIPS
 
 
 @pytest.fixture(scope='module', params=['f16x3', 'bf16x6'])
@@ -229,7 +241,8 @@ def test_non_default_loss_layers_match_reference_golden(net_mod, golden_dir):
     per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
     assert record('generic_golden/total_rel', abs(float(total) - float(g['total'])) / abs(float(g['total']))) < TOL_LOSS_GRAD
     assert record('generic_golden/losses_rel_l2', rel_l2(per_node, torch.from_numpy(g['losses']))) < TOL_LOSS_GRAD
-    assert record('generic_golden/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < TOL_LOSS_GRAD
+    tol = _deep_grad_tol('generic_golden', x0.cpu(), oracle.make_vgg_weights(1, GENERIC_CONVS), GENERIC_CONVS)
+    assert record('generic_golden/grad_rel_l2', rel_l2(x.grad, torch.from_numpy(g['grad']))) < tol
     # the feature node takes part in the gradient when asked for (static_test's combination)
     xf = x0.clone().requires_grad_(True)
     net(xf, content)
@@ -244,7 +257,7 @@ def test_non_default_loss_layers_match_reference_golden(net_mod, golden_dir):
     ref = 1e5 * sum(oracle.style_loss(outs[n], oracle.gram_matrix(s_out[n])) for n in GL['style']) + \
         1e12 * sum(oracle.feature_loss(outs[n], c_out[n]) for n in GL['feature'])
     ref.backward()
-    assert record('generic_feature/grad_rel_l2', rel_l2(xf.grad, xr.grad)) < TOL_LOSS_GRAD
+    assert record('generic_feature/grad_rel_l2', rel_l2(xf.grad, xr.grad)) < tol
 
 
 def test_non_default_loss_layers_match_oracle_and_all_pieces(net_mod):
@@ -264,7 +277,8 @@ def test_non_default_loss_layers_match_oracle_and_all_pieces(net_mod):
     per_node = torch.stack([n[0].loss for n in net.style_losses + net.content_losses + net.feature_losses]).detach()
     assert record('generic_136x200/total_rel', abs(float(total) - float(o_total)) / abs(float(o_total))) < TOL_LOSS_GRAD
     assert record('generic_136x200/losses_rel_l2', rel_l2(per_node, o_losses)) < TOL_LOSS_GRAD
-    assert record('generic_136x200/grad_rel_l2', rel_l2(x.grad, o_grad)) < TOL_LOSS_GRAD
+    tol = _deep_grad_tol('generic_136x200', x0, vw16, 10)
+    assert record('generic_136x200/grad_rel_l2', rel_l2(x.grad, o_grad)) < tol
     # pieces: all of them (MaxPool2d_16), the piece of a max-pool node, of a ReLU node and of a deep conv node
     names = ['MaxPool2d_16', 'MaxPool2d_4', 'ReLU_7', 'Conv2d_10']
     outs = oracle.vgg_layer_outputs(content, vw16, names)
@@ -278,4 +292,4 @@ def test_non_default_loss_layers_match_oracle_and_all_pieces(net_mod):
     net.compute_feature_loss = False
     closure = net.gatys_closure(xg, content.cuda(), 1e5, 1)
     loss = closure()
-    assert abs(float(loss) - float(o_total)) / abs(float(o_total)) < TOL_LOSS_GRAD and rel_l2(xg.grad, o_grad) < TOL_LOSS_GRAD
+    assert abs(float(loss) - float(o_total)) / abs(float(o_total)) < TOL_LOSS_GRAD and rel_l2(xg.grad, o_grad) < tol

@@ -40,7 +40,11 @@ def time_it(fn, reps, flush):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--reps', type=int, default=20)
+    ap.add_argument('--dbg', type=int, default=0, help='conv_tc experiment switches: 1 no global stores, 2 no MMAs, 4 no activation loads')
+    ap.add_argument('--fwd-only', action='store_true')
     args = ap.parse_args()
+    from styletransfer_b200 import _lib
+    _lib.lib().st_set_conv_path(args.dbg << 8)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
     cases = [('conv1_2', 1, 64, 64, 512), ('conv2_1', 1, 64, 128, 256), ('conv2_2', 1, 128, 128, 256), ('conv3_1', 1, 128, 256, 128),
              ('res', 16, 128, 128, 64)]
@@ -52,6 +56,9 @@ def main():
         gf = 2 * 9 * cin * cout * N * S * S / 1e12      # TFLOP
         t1 = time_it(lambda: ops.conv2d(x, pw, b, want_out=True, want_relu=False), args.reps, flush)
         t2 = time_it(lambda: ops.conv2d(x, pw, b, want_out=True, want_relu=True), args.reps, flush)
+        if args.fwd_only:
+            print(f'{name:8s} N={N} {cin}->{cout} @{S}: fwd out {t1:7.1f} us ({gf / t1 * 1e6:6.1f} TF/s)  fwd out+relu {t2:7.1f} us ({gf / t2 * 1e6:6.1f})', flush=True)
+            continue
         # backward-data with mask + add (2 planes)
         gy = ops.from_nchw(seeded((N, cout, S, S), 4))
         pd = ops.PackedWeight(w, 2, rows_pad=cin, cols_pad=cout)
