@@ -30,6 +30,8 @@ SOURCES = {
 }
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xptxas', '-v']
+if os.environ.get('STRANSFER_CONV_TRACE') == '1':       # per-tile timeline of conv_tc (tools/trace_conv.py), never for product builds
+    NVCC_FLAGS = NVCC_FLAGS + ['-DST_CONV_TRACE']
 LINK_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-cudart', 'shared']
 
 

@@ -18,6 +18,10 @@
 // Pipelines: A ring (halo boxes), B ring (weight tiles), 2 TMEM accumulators.
 #include "common.cuh"
 #include "ptx.cuh"
+#ifdef ST_CONV_TRACE
+__device__ long long g_conv_trace[3 * 64 * 8] = {};
+#define TC_TRACE(role, tile, ev) do { if (blockIdx.x == 0 && (tile) < 64) g_conv_trace[((role) * 64 + (tile)) * 8 + (ev)] = clock64(); } while (0)
+#endif
 #include "conv_tc_epilogue.cuh"
 #include <mutex>
 #include <unordered_map>
@@ -25,6 +29,17 @@
 #include <string.h>
 
 extern int g_conv_debug;
+
+// Per-tile timeline of CTA 0 (tools/trace_conv.py; the library is built with -DST_CONV_TRACE for that run only):
+// g_conv_trace[role][tile][event] = clock64().  roles: 0 producer, 1 MMA issuer, 2 epilogue warp 4.
+#ifdef ST_CONV_TRACE
+#define TRACE(role, tile, ev) do { if (blockIdx.x == 0 && (tile) < 64) g_conv_trace[((role) * 64 + (tile)) * 8 + (ev)] = clock64(); } while (0)
+extern "C" int st_conv_trace_read(long long* out) {
+    return cudaMemcpyFromSymbol(out, g_conv_trace, sizeof(g_conv_trace)) == cudaSuccess ? 0 : -2;
+}
+#else
+#define TRACE(role, tile, ev) do { } while (0)
+#endif
 
 namespace {
 
@@ -144,6 +159,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
 #pragma unroll
                     for (int pl = 0; pl < 2; ++pl) {
                         ptx::mbar_wait(&a_empty[a], aph ^ 1);
+                        TRACE(0, (wk - blockIdx.x) / gridDim.x, pl);
                         if (p.dbg & 4) { ptx::mbar_arrive(&a_full[a]); if (++a == NA) { a = 0; aph ^= 1; } continue; }
                         ptx::mbar_expect_tx(&a_full[a], C::A_TX);
                         ptx::tma_load_4d(sA + a * C::A_SLOT, pl ? &tmA_lo : &tmA_hi, &a_full[a], 0, w0, h0, n);
@@ -183,16 +199,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             constexpr uint32_t a_hi = ptx::umma_desc_hi_k_sw128_sbo(C::A_SBO), b_hi = ptx::umma_desc_hi_k_sw128();
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
             int it = 0;
+            // barriers are polled one step AHEAD (mbar_test before a group of MMAs is issued, see ptx.cuh); the flags
+            // say that the barrier the next step needs has already been seen complete
+            bool t_ready = false, a_ready = false, b_ready = false;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x, ++it) {
                 const int acc = it & 1;
-                ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
+                const bool more = wk + static_cast<int>(gridDim.x) < p.work;
+                if (!t_ready) ptx::mbar_wait(&t_empty[acc], ((it >> 1) & 1) ^ 1);
+                t_ready = false;
                 ptx::tc_fence_after();
                 const uint32_t d_main = tmem_base + acc * C::STAGE_COLS;
                 uint32_t acc_main = 0;
+                TRACE(1, it, 0);
                 if (RES) {
                     // rolled on purpose: a fully unrolled tile is > 1000 SASS instructions of descriptor arithmetic that
-                    // spill uniform registers and miss the instruction cache -- the issue rate of this one warp, not the
-                    // tensor pipe, then bounds the kernel (profiles/r02o: 59 % tensor-pipe activity, epilogue warps idle)
+                    // spill uniform registers and miss the instruction cache
                     if (it == 0) {
 #pragma unroll 1
                         for (int tap = 0; tap < C::TAPS; ++tap) ptx::mbar_wait(&b_full[tap], 0);
@@ -200,45 +221,72 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                     }
 #pragma unroll 1
                     for (int pl = 0; pl < 2; ++pl) {
-                        ptx::mbar_wait(&a_full[a], aph);
+                        if (!a_ready) ptx::mbar_wait(&a_full[a], aph);
+                        a_ready = false;
                         ptx::tc_fence_after();
-                        const uint32_t idesc = ptx::umma_idesc_nofmt(BLOCK_M, pl == 0 ? 2 * BN : BN) | fmt;
+                        TRACE(1, it, 1 + 2 * pl);
+                        const uint32_t idesc = ((p.dbg & 8) ? ptx::umma_idesc_nofmt(BLOCK_M, 16) : ptx::umma_idesc_nofmt(BLOCK_M, pl == 0 ? 2 * BN : BN)) | fmt;
                         const uint32_t d = pl == 0 ? d_main : d_main + BN;
                         uint32_t a_lo = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
                         uint32_t b_lo = ptx::umma_desc_lo(ptx::smem_u32(sB));
+                        const int an = (a + 1 == NA) ? 0 : a + 1;
+                        const uint32_t anph = (a + 1 == NA) ? aph ^ 1 : aph;
 #pragma unroll 1
                         for (int r = 0; r < KS; ++r, a_lo += (C::BOX_W * 128) >> 4, b_lo += (KS * C::B_SLOT) >> 4) {
-                            if (leader && !(p.dbg & 2)) {
-                                // one filter row = 12 MMAs per elected-lane region
-#pragma unroll
-                                for (int sx = 0; sx < KS; ++sx)
-#pragma unroll
-                                    for (int k = 0; k < KCH / 16; ++k)
-                                        ptx::mma_ss2h(d, a_lo + ((sx * 128 + k * 32) >> 4), a_hi, b_lo + ((sx * C::B_SLOT + k * 32) >> 4), b_hi, idesc,
-                                                      (pl == 1 || sx > 0 || k > 0) ? 1u : acc_main);
+                            if (r == KS - 1 && (pl == 0 || more)) {
+                                a_ready = ptx::mbar_test(&a_full[an], anph);
+                                if (pl == 1) t_ready = ptx::mbar_test(&t_empty[acc ^ 1], (((it + 1) >> 1) & 1) ^ 1);
                             }
-                            __syncwarp();
+                            if (leader) {
+                                // one filter row = 12 MMAs per elected-lane region; the commits that follow the last row
+                                // ride in the same region (every instruction between two groups of MMAs is tensor-pipe idle time)
+                                if (!(p.dbg & 2)) {
+#pragma unroll
+                                    for (int sx = 0; sx < KS; ++sx)
+#pragma unroll
+                                        for (int k = 0; k < KCH / 16; ++k)
+                                            ptx::mma_ss2h(d + ((p.dbg & 16) ? (k & 3) * 16 : 0), a_lo + ((sx * 128 + k * 32) >> 4), a_hi, b_lo + ((sx * C::B_SLOT + k * 32) >> 4), b_hi, idesc,
+                                                          (pl == 1 || sx > 0 || k > 0) ? 1u : acc_main);
+                                }
+                                if (r == KS - 1) {
+                                    ptx::tc_commit(&a_empty[a]);
+                                    if (pl == 1) ptx::tc_commit(&t_full[acc]);
+                                }
+                            }
                             acc_main = 1;
                         }
-                        if (leader) ptx::tc_commit(&a_empty[a]);
-                        __syncwarp();
-                        if (++a == NA) { a = 0; aph ^= 1; }
+                        TRACE(1, it, 2 + 2 * pl);
+                        a = an; aph = anph;
                     }
-                    if (leader) ptx::tc_commit(&t_full[acc]);
-                    __syncwarp();
                     continue;
                 }
                 for (int c = 0; c < kchunks; ++c) {
-                    ptx::mbar_wait(&a_full[a], aph);
+                    if (!a_ready) ptx::mbar_wait(&a_full[a], aph);
+                    a_ready = false;
                     ptx::tc_fence_after();
                     const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
+                    const int an = (a + 1 == NA) ? 0 : a + 1;
+                    const uint32_t anph = (a + 1 == NA) ? aph ^ 1 : aph;
 #pragma unroll 1
                     for (int tap = 0; tap < C::TAPS; ++tap) {
-                        ptx::mbar_wait(&b_full[b], bph);
+                        if (!b_ready) ptx::mbar_wait(&b_full[b], bph);
+                        b_ready = false;
                         ptx::tc_fence_after();
                         const uint32_t b_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sB + b * C::B_SLOT));
                         const int r = tap / KS, s = tap - r * KS;
                         const uint32_t a_lo = a_lo0 + (((r * C::BOX_W + s) * 128) >> 4);
+                        // what the NEXT step needs: the next weight tile; after the last tap of a chunk also the next
+                        // activation slot, after the last chunk of a tile also the other accumulator stage
+                        const int bn = (b + 1 == NB) ? 0 : b + 1;
+                        const uint32_t bnph = (b + 1 == NB) ? bph ^ 1 : bph;
+                        const bool last_tap = tap == C::TAPS - 1, last_chunk = c == kchunks - 1;
+                        if (!(last_tap && last_chunk) || more) {
+                            b_ready = ptx::mbar_test(&b_full[bn], bnph);
+                            if (last_tap) {
+                                a_ready = ptx::mbar_test(&a_full[an], anph);
+                                if (last_chunk) t_ready = ptx::mbar_test(&t_empty[acc ^ 1], (((it + 1) >> 1) & 1) ^ 1);
+                            }
+                        }
                         // planes of B are consecutive N rows in shared memory, so one MMA of N = 2*BN / 3*BN
                         // multiplies a plane of A with several planes of B (A is read once, not per pass):
                         //   D0 = a0 w0 | D1 = a0 w1 + a1 w0 | D2 = a0 w2 + a1 w1 + a2 w0   (adjacent TMEM columns)
@@ -267,17 +315,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                                 }
                             }
                             ptx::tc_commit(&b_empty[b]);
+                            if (last_tap) {
+                                ptx::tc_commit(&a_empty[a]);
+                                if (last_chunk) ptx::tc_commit(&t_full[acc]);
+                            }
                         }
                         acc_main = 1;
-                        __syncwarp();
-                        if (++b == NB) { b = 0; bph ^= 1; }
+                        b = bn; bph = bnph;
                     }
-                    if (leader) ptx::tc_commit(&a_empty[a]);
-                    __syncwarp();
-                    if (++a == NA) { a = 0; aph ^= 1; }
+                    a = an; aph = anph;
                 }
-                if (leader) ptx::tc_commit(&t_full[acc]);
-                __syncwarp();
             }
         }
     }

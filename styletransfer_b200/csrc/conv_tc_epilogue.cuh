@@ -5,6 +5,10 @@
 #include "common.cuh"
 #include "ptx.cuh"
 
+#ifndef TC_TRACE
+#define TC_TRACE(role, tile, ev) do { } while (0)
+#endif
+
 namespace {
 
 constexpr int TILE_H = 8, TILE_W = 16, BLOCK_M = 128;
@@ -204,7 +208,9 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
         for (int wk = blockIdx.x; wk < p.work; wk += step, ++it) {
             const TcPix px = dec(wk, m);
             begin_tile(it);
-            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
+            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
+                                    if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
             if (active) {
 #pragma unroll
                 for (int g = 0; g < NGRP; ++g)
@@ -212,6 +218,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             } else {
                 end_tile();
             }
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
         return;
     }

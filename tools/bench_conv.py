@@ -15,6 +15,9 @@ def seeded(shape, seed, scale=1.0):
     return (torch.randn(*shape, generator=torch.Generator().manual_seed(seed)) * scale).cuda()
 
 
+INNER = 8
+
+
 def time_it(fn, reps, flush):
     """median time of one launch, replayed from a CUDA graph (no host overhead inside the events)"""
     side = torch.cuda.Stream()
@@ -24,14 +27,14 @@ def time_it(fn, reps, flush):
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=side):
-            keep = fn()
+            keep = [fn() for _ in range(INNER)]        # event resolution is ~2 us: time several launches per replay
     ts = []
     for _ in range(reps):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); g.replay(); e1.record()
         torch.cuda.synchronize()
-        ts.append(e0.elapsed_time(e1) * 1e3)
+        ts.append(e0.elapsed_time(e1) * 1e3 / INNER)
     ts.sort()
     del keep
     return ts[len(ts) // 2]
@@ -59,10 +62,10 @@ def main():
         if args.fwd_only:
             print(f'{name:8s} N={N} {cin}->{cout} @{S}: fwd out {t1:7.1f} us ({gf / t1 * 1e6:6.1f} TF/s)  fwd out+relu {t2:7.1f} us ({gf / t2 * 1e6:6.1f})', flush=True)
             continue
-        # backward-data with mask + add (2 planes)
-        gy = ops.from_nchw(seeded((N, cout, S, S), 4))
-        pd = ops.PackedWeight(w, 2, rows_pad=cin, cols_pad=cout)
-        tap, add = ops.from_nchw(seeded((N, cin, S, S), 5)), ops.from_nchw(seeded((N, cin, S, S), 6))
+        # backward-data (bf16 gradient planes) plain and with the ReLU mask of the tap + a two-plane addend
+        gy = ops.from_nchw(seeded((N, cout, S, S), 4), planes=2)
+        pd = ops.PackedWeight(w, 2, rows_pad=cin)
+        tap, add = ops.from_nchw(seeded((N, cin, S, S), 5)), ops.from_nchw(seeded((N, cin, S, S), 6), planes=2)
         t3 = time_it(lambda: ops.conv2d(gy, pd), args.reps, flush)
         t4 = time_it(lambda: ops.conv2d(gy, pd, mask=tap, add=add), args.reps, flush)
         print(f'{name:8s} N={N} {cin}->{cout} @{S}: fwd out {t1:7.1f} us ({gf / t1 * 1e6:6.1f} TF/s)  fwd out+relu {t2:7.1f} us ({gf / t2 * 1e6:6.1f})'
