@@ -171,6 +171,14 @@ size_t st_gram_workspace_bytes(int B, int HW, int C);
 int st_set_gram_max_splits(int max_splits);
 int st_gram_fwd(const void* f_hi, const void* f_lo, int f_planes, int B, int HW, int C, float* G,
                 void* workspace, size_t workspace_bytes, void* stream);
+/* StyleLoss.gram_matrix + StyleLoss.forward (network.py:92-123) for one node in TWO launches: the Gram kernel and one
+ * finish launch that reduces the split partials and also writes diff = G - T, loss = mean(diff^2) and max|diff|
+ * (three launches fewer per style node than st_gram_fwd + st_style_mse_fwd).  ticket: a device int that is zero before
+ * the first call; the kernel hands it back at zero (calls that share it must be stream-ordered). */
+size_t st_gram_style_workspace_bytes(int B, int HW, int C);
+int st_gram_style_fwd(const void* f_hi, const void* f_lo, int f_planes, int B, int HW, int C, const float* T,
+                      float* diff, float* loss, float* diff_amax, int* ticket, void* workspace, size_t workspace_bytes,
+                      void* stream);
 /* StyleLoss.forward (network.py:110-123): loss = mean((G - T)^2), T [C][C] broadcast;
  * diff = G - T is kept for the backward; diff_amax (optional) receives max |diff|.  ws: >= 4096 floats */
 int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* diff_amax,
@@ -180,6 +188,10 @@ int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, 
  * that maps max|D| (from diff_amax) to 2^10 and d_slot receives {s, 1/s} (acc_mul_slot of that conv). */
 int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* gw, void* d_hi, void* d_lo,
                           int d_planes, const float* diff_amax, float* d_slot, void* stream);
+/* st_style_mse_bwd_seed for every style node of a loss network in one launch (n <= 16): tables of n entries each */
+int st_style_mse_bwd_seed_multi(int n, const float* const* diff, const int* B, const int* C, const int* HW,
+                                const float* const* gw, void* const* d_hi, void* const* d_lo, const int* d_planes,
+                                const float* const* diff_amax, float* const* d_slot, void* stream);
 /* slot = {s, 1/s}, s the power of two that maps max|x| of a flat fp32 array to 2^target_log2 (the scale under which
  * a gradient image enters fp16 tensor-core operands).  ws: >= 1024 floats */
 int st_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, void* stream);

@@ -51,6 +51,9 @@ SIGNATURES = {
     'st_gram_workspace_bytes': (_Z, [_I, _I, _I]),
     'st_set_gram_max_splits': (_I, [_I]),
     'st_gram_fwd': (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _Z, _P]),
+    'st_gram_style_workspace_bytes': (_Z, [_I, _I, _I]),
+    'st_gram_style_fwd': (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _Z, _P]),
+    'st_style_mse_bwd_seed_multi': (_I, [_I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P]),
     'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P]),
     'st_absmax_slot': (_I, [_P, _Z, _F, _P, _P, _P]),

@@ -33,7 +33,8 @@ int conv_tcx_run(int mode, const bf16*, const bf16*, int, int, int, int, int, co
                  float, const float*, const float*, cudaStream_t);
 bool gram_tc_eligible(int C, bool two_planes);
 size_t gram_tc_workspace_bytes(int B, int HW, int C);
-int gram_tc_run(const bf16*, bool, int, int, int, float, float*, void*, size_t, cudaStream_t);
+int gram_tc_finish_blocks(int B, int HW, int C);
+int gram_tc_run(const bf16*, bool, int, int, int, float, float*, void*, size_t, const float*, float*, float*, float*, float*, int*, cudaStream_t);
 bool wgrad_tc_eligible(int ks, int stride, int pad, int up, int CinPad, int Cdy, bool two_planes);
 size_t wgrad_tc_workspace_bytes(int N, int H, int W, int CinPad, int Cdy, int ks);
 int wgrad_tc_run(const bf16*, const bf16*, bool, const float*, int, int, int, int, int, int, int, int, float*, void*, size_t, cudaStream_t);
@@ -51,6 +52,7 @@ int ew_mse_fwd(const bf16*, const bf16*, int, const bf16*, const bf16*, int, siz
 int ew_mse_bwd(const bf16*, const bf16*, int, const bf16*, const bf16*, int, size_t, int, float, const float*, const float*, int, bf16*, bf16*, cudaStream_t);
 int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, float*, cudaStream_t);
 int ew_style_seed(const float*, int, int, float, const float*, bf16*, bf16*, int, const float*, float*, cudaStream_t);
+int ew_style_seed_multi(const StyleSeedTable&, int, cudaStream_t);
 int ew_absmax_slot(const float*, size_t, float, float*, float*, cudaStream_t);
 int ew_image_u8_to_nchw(const unsigned char*, float*, int, int, int, const float*, const float*, cudaStream_t);
 int ew_image_nchw_to_u8(const float*, unsigned char*, int, int, int, const float*, const float*, cudaStream_t);
@@ -285,10 +287,40 @@ int st_gram_fwd(const void* f_hi, const void* f_lo, int f_planes, int B, int HW,
     // tcgen05 path: 64 / 128 / 256 channels, planes one plane stride apart
     const bool planes_ok = f_lo && pc_planes(f_planes) >= 2 && CBF(f_lo) == CBF(f_hi) + static_cast<size_t>(B) * HW * C;
     if (g_conv_path == 0 && gram_tc_eligible(C, planes_ok))
-        return gram_tc_run(CBF(f_hi), pc_f16(f_planes), B, HW, C, scale, G, workspace, workspace_bytes, STRM(stream));
+        return gram_tc_run(CBF(f_hi), pc_f16(f_planes), B, HW, C, scale, G, workspace, workspace_bytes,
+                           nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, STRM(stream));
     const bf16* lo = pc_planes(f_planes) >= 2 ? CBF(f_lo) : nullptr;
     return contract_run(CBF(f_hi), lo, C, pc_f16(f_planes), nullptr, CBF(f_hi), lo, pc_f16(f_planes), B, HW, 1, C, 0, HW, 1, 1, 1, 0,
                         1, C, C, scale, G, workspace, workspace_bytes, STRM(stream));
+}
+// Gram + StyleLoss.forward in two launches (tcgen05 Gram kernel, then ONE finish launch that also forms diff, the loss
+// and max|diff|); shapes the tensor-core Gram kernel does not take run the separate launches.
+// workspace layout: [Gram split partials | G (B*C*C floats) | style partials (2 * 2048 floats at least)]
+static size_t gram_style_part_floats(int B, int HW, int C) {
+    const int blocks = gram_tc_eligible(C, true) ? gram_tc_finish_blocks(B, HW, C) : 0;
+    return 2 * static_cast<size_t>(blocks > 2048 ? blocks : 2048);
+}
+size_t st_gram_style_workspace_bytes(int B, int HW, int C) {
+    const size_t gram = (st_gram_workspace_bytes(B, HW, C) + 255) & ~static_cast<size_t>(255);
+    return gram + (static_cast<size_t>(B) * C * C + gram_style_part_floats(B, HW, C)) * sizeof(float);
+}
+int st_gram_style_fwd(const void* f_hi, const void* f_lo, int f_planes, int B, int HW, int C, const float* T,
+                      float* diff, float* loss, float* diff_amax, int* ticket, void* workspace, size_t workspace_bytes, void* stream) {
+    ST_CHECK_ARG(f_hi && T && diff && loss && ticket && workspace && B > 0 && HW > 0, "st_gram_style_fwd: null pointer or empty shape");
+    ST_CHECK_ARG(C % 8 == 0 && plane_code_ok(f_planes), "st_gram_style_fwd: C %% 8 != 0 or bad plane code");
+    ST_CHECK_ARG(workspace_bytes >= st_gram_style_workspace_bytes(B, HW, C), "st_gram_style_fwd: workspace too small");
+    const size_t gram_bytes = (st_gram_workspace_bytes(B, HW, C) + 255) & ~static_cast<size_t>(255);
+    float* G = reinterpret_cast<float*>(static_cast<char*>(workspace) + gram_bytes);
+    float* part = G + static_cast<size_t>(B) * C * C;
+    const bool planes_ok = f_lo && pc_planes(f_planes) >= 2 && CBF(f_lo) == CBF(f_hi) + static_cast<size_t>(B) * HW * C;
+    if (g_conv_path == 0 && gram_tc_eligible(C, planes_ok)) {
+        const float scale = 1.0f / (static_cast<float>(C) * static_cast<float>(HW));
+        return gram_tc_run(CBF(f_hi), pc_f16(f_planes), B, HW, C, scale, nullptr, workspace, gram_bytes,
+                           T, diff, loss, diff_amax, part, ticket, STRM(stream));
+    }
+    int rc = st_gram_fwd(f_hi, f_lo, f_planes, B, HW, C, G, workspace, gram_bytes, stream);
+    if (rc) return rc;
+    return ew_style_fwd(G, T, B, C, diff, loss, diff_amax, part, STRM(stream));
 }
 int st_style_mse_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss, float* diff_amax, float* ws, void* stream) {
     ST_CHECK_ARG(G && T && diff && loss && ws, "st_style_mse_fwd: null pointer");
@@ -302,6 +334,26 @@ int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* 
     const double scale = 4.0 / (static_cast<double>(B) * C * C) / (static_cast<double>(C) * HW);
     return ew_style_seed(diff, B, C, static_cast<float>(scale), gw, BF(d_hi), pc_planes(d_planes) >= 2 ? BF(d_lo) : nullptr, d_planes,
                          diff_amax, d_slot, STRM(stream));
+}
+// the seeds of up to ST_MAX_STYLE_NODES style nodes in ONE launch (they depend on the loss gradient only, not on the chain)
+int st_style_mse_bwd_seed_multi(int n, const float* const* diff, const int* B, const int* C, const int* HW, const float* const* gw,
+                                void* const* d_hi, void* const* d_lo, const int* d_planes, const float* const* diff_amax,
+                                float* const* d_slot, void* stream) {
+    ST_CHECK_ARG(n >= 1 && n <= ST_MAX_STYLE_NODES && diff && B && C && HW && gw && d_hi && d_lo && d_planes && diff_amax && d_slot,
+                 "st_style_mse_bwd_seed_multi: 1..%d nodes, no null tables", ST_MAX_STYLE_NODES);
+    StyleSeedTable t;
+    t.n = n;
+    int max_total = 0;
+    for (int i = 0; i < n; ++i) {
+        ST_CHECK_ARG(diff[i] && gw[i] && d_hi[i] && plane_code_ok(d_planes[i]), "st_style_mse_bwd_seed_multi: node %d: null pointer or bad plane code", i);
+        ST_CHECK_ARG(!pc_f16(d_planes[i]) || (diff_amax[i] && d_slot[i]), "st_style_mse_bwd_seed_multi: node %d: fp16 planes need diff_amax and a scale slot", i);
+        t.e[i].diff = diff[i]; t.e[i].total = B[i] * C[i] * C[i];
+        t.e[i].scale = static_cast<float>(4.0 / (static_cast<double>(B[i]) * C[i] * C[i]) / (static_cast<double>(C[i]) * HW[i]));
+        t.e[i].gw = gw[i]; t.e[i].dh = BF(d_hi[i]); t.e[i].dl = pc_planes(d_planes[i]) >= 2 ? BF(d_lo[i]) : nullptr;
+        t.e[i].code = d_planes[i]; t.e[i].amax = diff_amax[i]; t.e[i].slot = d_slot[i];
+        if (t.e[i].total > max_total) max_total = t.e[i].total;
+    }
+    return ew_style_seed_multi(t, max_total, STRM(stream));
 }
 int st_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, void* stream) {
     ST_CHECK_ARG(x && slot && ws && n > 0, "st_absmax_slot: null pointer or empty array");

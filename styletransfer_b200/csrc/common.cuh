@@ -32,6 +32,14 @@ __host__ __device__ __forceinline__ bool pc_f16(int code) { return (code & ST_FM
 #define ST_W_F16_SCALE 256.0f
 #define ST_W_F16_INV_SCALE (1.0f / 256.0f)
 
+// ----- the seeds of several style nodes in one launch (elementwise.cu, api.cu) ----
+#define ST_MAX_STYLE_NODES 16
+struct StyleSeedEntry {
+    const float* diff; int total; float scale; const float* gw;
+    __nv_bfloat16* dh; __nv_bfloat16* dl; int code; const float* amax; float* slot;
+};
+struct StyleSeedTable { int n; StyleSeedEntry e[ST_MAX_STYLE_NODES]; };
+
 // ----- error plumbing (host) -------------------------------------------------
 void st_set_error(const char* fmt, ...);
 #define ST_OK 0

@@ -330,6 +330,26 @@ __global__ void style_seed_kernel(const float* __restrict__ diff, int total, flo
     if (dl) dl[i] = l;
 }
 
+// the same for every style node of a loss network at once: blockIdx.y = node
+__global__ void style_seed_multi_kernel(const StyleSeedTable t) {
+    const StyleSeedEntry& e = t.e[blockIdx.y];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const float coef = e.scale * e.gw[0];
+    if (pc_f16(e.code)) {
+        const float sc = pow2_scale_for(e.amax[0] * fabsf(coef), 10.f);
+        if (i == 0) { e.slot[0] = sc; e.slot[1] = 1.f / sc; }
+        if (i >= e.total) return;
+        uint32_t h2, l2; split2h(e.diff[i] * coef * sc, 0.f, h2, l2);
+        reinterpret_cast<uint16_t*>(e.dh)[i] = static_cast<uint16_t>(h2 & 0xffffu);
+        if (e.dl) reinterpret_cast<uint16_t*>(e.dl)[i] = static_cast<uint16_t>(l2 & 0xffffu);
+        return;
+    }
+    if (i >= e.total) return;
+    bf16 h, l; split_bf16(e.diff[i] * coef, h, l);
+    e.dh[i] = h;
+    if (e.dl) e.dl[i] = l;
+}
+
 // max |x| over a flat fp32 array: per-block partial maxima, then one block -> slot = {s, 1/s} with the power of two s
 // that maps the maximum to 2^target_log2 (the scale under which a gradient image is fed to fp16 tensor-core operands)
 __global__ void absmax_partial_kernel(const float* __restrict__ x, size_t n, float* __restrict__ partial) {
@@ -514,6 +534,10 @@ int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw,
     const int total = B * C * C;
     style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl, code, diff_amax, slot);
     ST_CHECK_LAUNCH("style_seed_kernel"); return ST_OK;
+}
+int ew_style_seed_multi(const StyleSeedTable& t, int max_total, cudaStream_t st) {
+    style_seed_multi_kernel<<<dim3((max_total + 255) / 256, t.n), 256, 0, st>>>(t);
+    ST_CHECK_LAUNCH("style_seed_multi_kernel"); return ST_OK;
 }
 int ew_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
     ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }

@@ -439,6 +439,104 @@ gram_tc_finish_small_kernel(const float* __restrict__ partial, int splits, int n
         make_float4((a0.x + a1.x) * scale, (a0.y + a1.y) * scale, (a0.z + a1.z) * scale, (a0.w + a1.w) * scale);
 }
 
+// ---- Gram finish fused with StyleLoss.forward (network.py:110-123) -------------------------------------------------------
+// diff = G - T (T [C][C] broadcast over images), loss = mean(diff^2), amax = max |diff| -- in the launch that reduces
+// the split partials, instead of three more launches per style node (finish -> diff -> sum).  Every block leaves its
+// sum of squares and its maximum in `part`; the block that draws the last ticket adds them up in a fixed order
+// (deterministic) and hands the ticket counter back at zero.
+struct StyleTail {
+    const float* T; float* diff; float* Gm;          // Gm optional
+    float* part; int* ticket; float* loss; float* amax; float inv_total;
+};
+__device__ __forceinline__ void style_tail_finish(const StyleTail& t, float s, float m, float* sm) {
+    s = block_sum(s, sm);
+    m = block_max(m, sm);
+    __shared__ int last;
+    if (threadIdx.x == 0) {
+        t.part[blockIdx.x] = s; t.part[gridDim.x + blockIdx.x] = m;
+        __threadfence();
+        last = atomicAdd(t.ticket, 1) == static_cast<int>(gridDim.x) - 1;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    float ss = 0.f, mm = 0.f;
+    for (int i = threadIdx.x; i < static_cast<int>(gridDim.x); i += blockDim.x) {
+        ss += __ldcg(t.part + i); mm = fmaxf(mm, __ldcg(t.part + gridDim.x + i));
+    }
+    ss = block_sum(ss, sm);
+    mm = block_max(mm, sm);
+    if (threadIdx.x == 0) { t.loss[0] = ss * t.inv_total; if (t.amax) t.amax[0] = mm; *t.ticket = 0; }
+}
+
+__global__ void __launch_bounds__(256)
+gram_tc_finish_style_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, int total, StyleTail t) {
+    __shared__ float sm[8][33];
+    __shared__ float red[32];
+    const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 32 + ol;
+    float s = 0.f;
+    if (idx < total) {
+        int q = idx; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+        const size_t per = static_cast<size_t>(nacc) * 128 * C;
+        const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
+        float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int sp = sl;
+        for (; sp + 24 < splits; sp += 32) {
+            s += base[static_cast<size_t>(sp) * per];       s1 += base[static_cast<size_t>(sp + 8) * per];
+            s2 += base[static_cast<size_t>(sp + 16) * per]; s3 += base[static_cast<size_t>(sp + 24) * per];
+        }
+        for (; sp < splits; sp += 8) s += base[static_cast<size_t>(sp) * per];
+        s = (s + s1) + (s2 + s3);
+    }
+    sm[sl][ol] = s;
+    __syncthreads();
+    float d2 = 0.f, am = 0.f;
+    if (sl == 0 && idx < total) {
+        float g = 0.f;
+#pragma unroll
+        for (int l = 0; l < 8; ++l) g += sm[l][ol];
+        g *= scale;
+        if (t.Gm) t.Gm[idx] = g;
+        const float d = g - t.T[idx % (C * C)];
+        t.diff[idx] = d;
+        d2 = d * d; am = fabsf(d);
+    }
+    style_tail_finish(t, d2, am, red);
+}
+
+__global__ void __launch_bounds__(256)
+gram_tc_finish_small_style_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, int total4, StyleTail t) {
+    __shared__ float red[32];
+    const int v = blockIdx.x * 256 + threadIdx.x;
+    float d2 = 0.f, am = 0.f;
+    if (v < total4) {
+        int q = v * 4; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+        const size_t per = static_cast<size_t>(nacc) * 128 * C;
+        const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+        int sp = 0;
+        for (; sp + 1 < splits; sp += 2) {
+            const float4 x0 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per);
+            const float4 x1 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp + 1) * per);
+            a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+            a1.x += x1.x; a1.y += x1.y; a1.z += x1.z; a1.w += x1.w;
+        }
+        if (sp < splits) {
+            const float4 x0 = *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per);
+            a0.x += x0.x; a0.y += x0.y; a0.z += x0.z; a0.w += x0.w;
+        }
+        const float4 g = make_float4((a0.x + a1.x) * scale, (a0.y + a1.y) * scale, (a0.z + a1.z) * scale, (a0.w + a1.w) * scale);
+        if (t.Gm) *reinterpret_cast<float4*>(t.Gm + static_cast<size_t>(v) * 4) = g;
+        const float4 tt = *reinterpret_cast<const float4*>(t.T + (static_cast<size_t>(v) * 4) % (static_cast<size_t>(C) * C));
+        const float4 d = make_float4(g.x - tt.x, g.y - tt.y, g.z - tt.z, g.w - tt.w);
+        *reinterpret_cast<float4*>(t.diff + static_cast<size_t>(v) * 4) = d;
+        d2 = (d.x * d.x + d.y * d.y) + (d.z * d.z + d.w * d.w);
+        am = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fmaxf(fabsf(d.z), fabsf(d.w)));
+    }
+    style_tail_finish(t, d2, am, red);
+}
+
 struct GramPlan { int tiles, splits, tiles_per_split, grid, nacc; };
 GramPlan plan_gram(int B, int HW, int C) {
     GramPlan q;
@@ -502,8 +600,17 @@ size_t gram_tc_workspace_bytes(int B, int HW, int C) {
     const GramPlan q = plan_gram(B, HW, C);
     return static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
 }
-// f [planes][B][HW][C] (plane stride B*HW*C elements; f16: the planes are fp16) -> Gm [B][C][C] * scale
-int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes, cudaStream_t stream) {
+// blocks of the finish launch (= entries of each half of the style partials)
+int gram_tc_finish_blocks(int B, int HW, int C) {
+    const GramPlan q = plan_gram(B, HW, C);
+    const int total = B * C * C;
+    return q.splits <= 16 ? (total / 4 + 255) / 256 : (total + 31) / 32;
+}
+// f [planes][B][HW][C] (plane stride B*HW*C elements; f16: the planes are fp16) -> Gm [B][C][C] * scale.
+// With T != null the finish launch also evaluates StyleLoss.forward: diff = G - T, loss = mean(diff^2), amax = max|diff|
+// (Gm then optional; style_part: 2 * gram_tc_finish_blocks floats; ticket: int, zero before the first call).
+int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes,
+                const float* T, float* diff, float* loss, float* amax, float* style_part, int* ticket, cudaStream_t stream) {
     const GramPlan q = plan_gram(B, HW, C);
     const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
     ST_CHECK_ARG(workspace && workspace_bytes >= need, "gram_tc: workspace too small (%zu < %zu)", workspace_bytes, need);
@@ -521,6 +628,19 @@ int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, f
     else rc = launch_gram<256>(tf, p, q.grid, stream);
     if (rc) return rc;
     const int total = B * C * C;
+    if (T) {
+        StyleTail t;
+        t.T = T; t.diff = diff; t.Gm = Gm; t.part = style_part; t.ticket = ticket; t.loss = loss; t.amax = amax;
+        t.inv_total = 1.0f / static_cast<float>(total);
+        if (q.splits <= 16) {
+            gram_tc_finish_small_style_kernel<<<(total / 4 + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, total / 4, t);
+            ST_CHECK_LAUNCH("gram_tc_finish_small_style_kernel");
+        } else {
+            gram_tc_finish_style_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, total, t);
+            ST_CHECK_LAUNCH("gram_tc_finish_style_kernel");
+        }
+        return ST_OK;
+    }
     if (q.splits <= 16) {
         gram_tc_finish_small_kernel<<<(total / 4 + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total / 4);
         ST_CHECK_LAUNCH("gram_tc_finish_small_kernel");

@@ -2,6 +2,7 @@
 format and one function per entry point.  PyTorch is used for memory and streams
 only; every numeric op below is a kernel of libstransfer_b200.so.
 """
+import ctypes
 import os
 
 import torch
@@ -393,6 +394,27 @@ def gram(f):
     return G
 
 
+_tickets = {}
+
+
+def gram_style_fwd(f, T, loss_out):
+    """StyleLoss.gram_matrix + StyleLoss.forward of one node in two launches (network.py:92-123): the loss
+    mean((G - T)^2) goes to the 1-element view ``loss_out``; returns (diff = G - T, max|diff| as a 1-element tensor)."""
+    L = _lib.lib()
+    dev = f.buf.device
+    HW = f.H * f.W
+    ws = workspace(L.st_gram_style_workspace_bytes(f.N, HW, f.C), dev)
+    key = (dev, _stream())
+    ticket = _tickets.get(key)
+    if ticket is None:
+        ticket = _tickets[key] = torch.zeros(1, dtype=torch.int32, device=dev)      # the finish kernel hands it back at zero
+    diff = torch.empty((f.N, f.C, f.C), dtype=torch.float32, device=dev)
+    amax = torch.empty(1, dtype=torch.float32, device=dev)
+    _lib.check(L.st_gram_style_fwd(f.hi, f.lo, f.read_code(2), f.N, HW, f.C, T.data_ptr(), diff.data_ptr(), loss_out.data_ptr(),
+                                   amax.data_ptr(), ticket.data_ptr(), ws.data_ptr(), ws.numel(), _stream()), 'st_gram_style_fwd')
+    return diff, amax
+
+
 def style_mse_fwd(G, T, loss_out):
     """loss_out: 1-element fp32 view that receives mean((G-T)^2); returns (diff, max|diff| as a 1-element tensor)."""
     B, C, _ = G.shape
@@ -415,6 +437,26 @@ def style_seed(diff, amax, HW, gw, fmt):
     _lib.check(_lib.lib().st_style_mse_bwd_seed(diff.data_ptr(), B, C, HW, gw.data_ptr(), hi, lo_p, planes | fmt, amax.data_ptr(),
                                                 _p(slot), _stream()), 'st_style_mse_bwd_seed')
     return (buf, slot), (hi, lo_p, B * C, 1, C, planes | fmt, slot)
+
+
+def style_seed_multi(nodes):
+    """``style_seed`` for every style node of a loss network in ONE launch.  nodes: [(diff, amax, HW, gw, fmt)];
+    returns [(buffers to keep alive, w_ptrs of ops.conv2d)] in the same order."""
+    n = len(nodes)
+    planes = bwd_planes()
+    out, rows = [], []
+    for diff, amax, HW, gw, fmt in nodes:
+        B, C, _ = diff.shape
+        buf = torch.empty((planes, B * C, C), dtype=torch.bfloat16, device=diff.device)
+        hi, lo_p = buf[0].data_ptr(), (buf[1].data_ptr() if planes > 1 else None)
+        slot = torch.empty(2, dtype=torch.float32, device=diff.device) if fmt else None
+        out.append(((buf, slot), (hi, lo_p, B * C, 1, C, planes | fmt, slot)))
+        rows.append((diff.data_ptr(), B, C, HW, gw.data_ptr(), hi, lo_p or 0, planes | fmt, amax.data_ptr(), _p(slot) or 0))
+    VP, IA = ctypes.c_void_p * n, ctypes.c_int * n
+    col = lambda j, T: T(*[r[j] for r in rows])
+    _lib.check(_lib.lib().st_style_mse_bwd_seed_multi(n, col(0, VP), col(1, IA), col(2, IA), col(3, IA), col(4, VP), col(5, VP), col(6, VP),
+                                                      col(7, IA), col(8, VP), col(9, VP), _stream()), 'st_style_mse_bwd_seed_multi')
+    return out
 
 
 def absmax_slot(t, target_log2=10.0):

@@ -222,8 +222,8 @@ class _VGGLossFn(torch.autograd.Function):
         def branch(pt, vals, taps):
             for kind, i in by_point.get(pt, ()):
                 if kind == 'style':
-                    G = ops.gram(vals[pt])
-                    diffs[i] = ops.style_mse_fwd(G, spec.style[i][1], losses[i:i + 1])      # (diff, max |diff|)
+                    # Gram + StyleLoss.forward: the finish launch of the Gram also forms diff, the loss and max |diff|
+                    diffs[i] = ops.gram_style_fwd(vals[pt], spec.style[i][1], losses[i:i + 1])
                 elif kind == 'content':
                     t, relu = mse_operand(pt, vals, taps)
                     ops.mse_fwd(t, spec.content[i][1], losses[n_style + i:n_style + i + 1], relu=relu)
@@ -255,6 +255,11 @@ class _VGGLossFn(torch.autograd.Function):
         gl = gl.contiguous().float()
         K = max(taps)
 
+        # the per-image weights D of every Gram backward (dF = F * D) in one launch: they depend on the loss gradient
+        # only; D takes the plane format of the operand F it multiplies (one format per tensor-core product)
+        seeds = ops.style_seed_multi([(diffs[i][0], diffs[i][1], vals[p].H * vals[p].W, gl[i:i + 1], vals[p].fmt)
+                                      for i, (p, _) in enumerate(spec.style)]) if n_style else []
+
         def node_grads(pt, acc=None):
             """acc + the loss gradients of the nodes at ``pt`` with respect to the value at ``pt`` -- for 'R' points
             with respect to the pre-ReLU tap (relu' applied).  Returns ``acc`` unchanged when no node sits there."""
@@ -274,7 +279,7 @@ class _VGGLossFn(torch.autograd.Function):
                     # dF = F * D  (Gram backward, per-image 1x1 conv on the tensor cores); the per-image weights D take
                     # the plane format of the operand F they multiply (one format per tensor-core product)
                     f = vals[pt]
-                    _keep, wp = ops.style_seed(diffs[i][0], diffs[i][1], f.H * f.W, gl[i:i + 1], f.fmt)
+                    _keep, wp = seeds[i]
                     acc, _, _ = ops.conv2d(f, None, w_ptrs=wp, w_img_rows=f.C, add=acc, mask=taps[pt[1]] if pt[0] == 'R' else None)
             return acc
 

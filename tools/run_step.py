@@ -22,7 +22,7 @@ def seeded(shape, seed):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument('--workload', default='gatys', choices=['gatys', 'fast_st', 'infer', 'lbfgs'])
+    ap.add_argument('--workload', default='gatys', choices=['gatys', 'gatys_graph', 'fast_st', 'fast_st_graph', 'infer', 'lbfgs'])
     ap.add_argument('--size', type=int, default=0)
     ap.add_argument('--batch', type=int, default=0)
     ap.add_argument('--width', type=int, default=0, help='infer: frame width (height = --size)')
@@ -49,6 +49,14 @@ def main():
 
         def step():
             opt.step(evaluate)
+    elif args.workload == 'gatys_graph':
+        # the closure train_gatys replays (loss-vector dot product instead of the getters), as a CUDA graph
+        S = args.size or 512
+        content, style = seeded((1, 3, S, S), 100).to(dev), seeded((1, 3, S, S), 101).to(dev)
+        net = network.StyleNetwork(style, content, vgg_weights=vw)
+        net.compute_feature_loss = False
+        x = content.clone().requires_grad_(True)
+        step = net.gatys_closure(x, content, 1e5, 1.0)
     elif args.workload == 'gatys':
         S = args.size or 512
         content, style = seeded((1, 3, S, S), 100).to(dev), seeded((1, 3, S, S), 101).to(dev)
@@ -77,7 +85,8 @@ def main():
 
             from styletransfer_b200 import dist as st_dist
             bucket = getattr(opt, 'bucket', None) or st_dist.GradBucket(tnet.parameters())
-            closure = tnet.training_closure(batch, loss_net, bucket, graph=False)    # eager: every launch visible to ncu
+            graph = args.workload == 'fast_st_graph'
+            closure = tnet.training_closure(batch, loss_net, bucket, graph=graph, optimizer=opt if graph else None)
 
             def step():
                 opt.step(closure)
