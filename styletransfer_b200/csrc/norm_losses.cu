@@ -272,7 +272,7 @@ in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
 
 // backward apply: dx = gamma*rstd/HW * (HW*dy_eff - s1 - xhat*s2)
 template <int UP>
-__global__ void __launch_bounds__(IN_THREADS)
+__global__ void __launch_bounds__(IN_THREADS, 2)
 in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     const bf16* __restrict__ gh, const bf16* __restrict__ gl,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -518,7 +518,9 @@ __global__ void temporal_warp_bwd_kernel(const float* __restrict__ os, const flo
 
 inline int in_splits(int N, int HW) {
     int splits = (4 * st_num_sms()) / N;              // N * splits = two full waves at 2 CTAs per SM
-    const int maxs = (HW + 255) / 256;
+    // at least 64 pixels per split: a 256-pixel floor left 16 images of 64 x 64 with 256 blocks = 0.43 waves, 21 % of the
+    // warp slots busy and 2.7 TB/s (profiles/r02ac_in_kernels_fast_st.txt)
+    const int maxs = (HW + 63) / 64;
     if (splits > maxs) splits = maxs;
     if (splits > 128) splits = 128;                  // = IN_MAX_SPLITS (workspace sizing below)
     if (splits < 1) splits = 1;
