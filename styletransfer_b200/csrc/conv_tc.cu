@@ -471,8 +471,11 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     const int w_planes_ = w_lo ? (wp >= 3 ? 3 : (wp >= 2 ? 2 : 1)) : 1;
     const int planes = a_planes < w_planes_ ? a_planes : w_planes_;
     // 3x3 with three planes: two A slots of three 23 KB planes leave no room for 128-row weight tiles -> 64-channel blocks
-    const int BN = (Cout % 128 == 0) ? ((ks == 3 && planes == 3) ? 64 : 128) : Cout;
+    int BN = (Cout % 128 == 0) ? ((ks == 3 && planes == 3) ? 64 : 128) : Cout;
     const int TH = ks == 3 ? 16 : 8, TW = ks == 3 ? 8 : 16;
+    // small problems (two images of 64 x 64 per GPU under data parallelism): when 128-channel tiles leave more than half
+    // of the SMs without a work item, 64-channel tiles double the items and halve the weights each CTA has to fetch
+    if (BN == 128 && N * ((H + TH - 1) / TH) * ((W + TW - 1) / TW) * (Cout / 128) * 2 <= st_num_sms()) BN = 64;
     ConvTcParams p;
     p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
     p.tiles_h = (H + TH - 1) / TH; p.tiles_w = (W + TW - 1) / TW;

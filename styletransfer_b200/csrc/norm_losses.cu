@@ -136,10 +136,21 @@ in_finalize_fwd_kernel(const float* __restrict__ partial, int C, int splits, int
     double s = 0.0, q = 0.0;
     if (c < C) {
         const float* base = partial + (static_cast<size_t>(n) * splits) * 2 * C + c;
-        for (int sp = sl; sp < splits; sp += 8) {
+        // four independent load pairs per round: the partials come from L2, a dependent chain of splits / 8 round trips
+        // made this launch cost as much as a statistics pass at small batch (profiles/r02aj_launches_fast_st_b2_f16x3.csv)
+        double s1 = 0.0, q1 = 0.0, s2 = 0.0, q2 = 0.0, s3 = 0.0, q3 = 0.0;
+        int sp = sl;
+        for (; sp + 24 < splits; sp += 32) {
+            const float* b0 = base + static_cast<size_t>(sp) * 2 * C;
+            const size_t st = static_cast<size_t>(8) * 2 * C;
+            const float x0 = b0[0], y0 = b0[C], x1 = b0[st], y1 = b0[st + C], x2 = b0[2 * st], y2 = b0[2 * st + C], x3 = b0[3 * st], y3 = b0[3 * st + C];
+            s += x0; q += y0; s1 += x1; q1 += y1; s2 += x2; q2 += y2; s3 += x3; q3 += y3;
+        }
+        for (; sp < splits; sp += 8) {
             s += base[static_cast<size_t>(sp) * 2 * C];
             q += base[static_cast<size_t>(sp) * 2 * C + C];
         }
+        s = (s + s1) + (s2 + s3); q = (q + q1) + (q2 + q3);
     }
     ss[sl][cl] = s; sq[sl][cl] = q;
     __syncthreads();
@@ -517,7 +528,7 @@ __global__ void temporal_warp_bwd_kernel(const float* __restrict__ os, const flo
 }
 
 inline int in_splits(int N, int HW) {
-    int splits = (4 * st_num_sms()) / N;              // N * splits = two full waves at 2 CTAs per SM
+    int splits = (2 * st_num_sms()) / N;              // N * splits = one full wave at 2 CTAs per SM
     // at least 64 pixels per split: a 256-pixel floor left 16 images of 64 x 64 with 256 blocks = 0.43 waves, 21 % of the
     // warp slots busy and 2.7 TB/s (profiles/r02ac_in_kernels_fast_st.txt)
     const int maxs = (HW + 63) / 64;
