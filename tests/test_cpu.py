@@ -341,3 +341,35 @@ def test_build_stamp_survives_copying_the_tree(tmp_path):
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     assert mod.up_to_date()
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference/stransfer'), reason='needs the reference sources (build container)')
+def test_staged_reference_bytecode_imports_and_matches_the_oracle(tmp_path):
+    """oracle/build_ref.py stages the unmodified reference as sourceless *.refbc files (what travels to the GPU box);
+    imported through the finder of oracle/reference_shim.py it evaluates the Gatys closure like the oracle does."""
+    import subprocess
+    import sys
+    from oracle import build_ref
+    root = build_ref.build()
+    assert root and build_ref.staged()
+    assert not [n for _b, _d, fs in os.walk(root) for n in fs if n.endswith(('.py', '.pyc'))], 'sources or .pyc staged'
+    code = (
+        'import torch\n'
+        'from oracle import oracle, ref_bench, reference_shim\n'
+        'assert reference_shim.REFERENCE_ROOT.endswith("_ref"), reference_shim.REFERENCE_ROOT\n'
+        'ref = ref_bench.load()\n'
+        'assert ref.__file__.endswith("network.refbc"), ref.__file__\n'
+        'g = lambda s, k: torch.randn(*s, generator=torch.Generator().manual_seed(k))\n'
+        'c, st = g((1, 3, 32, 48), 1), g((1, 3, 32, 48), 2)\n'
+        'net = ref.StyleNetwork(st, c)\n'
+        'x = (c + 0.1 * g((1, 3, 32, 48), 3)).requires_grad_(True)\n'
+        'net(x, c)\n'
+        't = net.get_total_current_style_loss(weight=1e5) + net.get_total_current_content_loss(weight=1)\n'
+        'vw = oracle.make_vgg_weights(1)\n'
+        'o, _, _ = oracle.gatys_closure(x.detach(), c, oracle.style_targets(st, vw), vw)\n'
+        'assert abs(float(t) - float(o)) <= 1e-5 * abs(float(o)), (float(t), float(o))\n'
+        'print("ok")\n')
+    env = dict(os.environ, STRANSFER_REFERENCE_ROOT=root, CUDA_VISIBLE_DEVICES='')
+    res = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=600, env=env,
+                         cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert res.returncode == 0 and 'ok' in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]

@@ -14,7 +14,7 @@ def main():
     L = _lib.lib()
     shapes = [(1, 64, 512, 512), (1, 128, 256, 256), (1, 256, 128, 128), (16, 64, 256, 256), (16, 128, 128, 128), (16, 256, 64, 64)]
     for B, C, H, W in shapes:
-        f = ops.from_nchw(torch.randn(B, C, H, W, device='cuda'), planes=3)
+        f = ops.from_nchw(torch.randn(B, C, H, W, device='cuda'))          # the forward format of the current precision mode
         row = []
         for cap in (0, 148, 96, 64, 48, 32, 24, 16, 8):
             L.st_set_gram_max_splits(cap)
