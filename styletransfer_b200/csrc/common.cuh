@@ -54,6 +54,35 @@ extern long long g_st_launches;      // kernels launched by this library (st_lau
          if (e_ != cudaSuccess) { st_set_error("%s: %s", name, cudaGetErrorString(e_)); \
                                   return ST_ERR_CUDA; } } while (0)
 
+// ----- programmatic dependent launch ---------------------------------------------------------------------------------
+// Every kernel of the library can be launched with the programmatic-stream-serialization attribute (st_launch) and starts
+// with pdl_prologue(): it lets the NEXT kernel of the stream be scheduled as soon as every CTA of this one has started
+// (its CTAs become resident as this kernel's CTAs retire, SM by SM, instead of after the whole grid has drained and the
+// dependency has been resolved by the front end), and then waits until the PREVIOUS kernel has completed and its memory
+// is visible before touching global memory.  Inside a captured CUDA graph the launches become programmatic edges.
+// With the attribute off (the default; STRANSFER_PDL=1 turns it on, see api.cu for the measurement) both instructions are no-ops.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() { pdl_trigger(); pdl_wait(); }
+extern int g_st_pdl;
+struct StLaunch {
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr;
+    StLaunch(dim3 grid, dim3 block, size_t smem, cudaStream_t st) {
+        cfg = cudaLaunchConfig_t{};
+        cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+        attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr.val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = &attr; cfg.numAttrs = g_st_pdl ? 1 : 0;
+    }
+    StLaunch(const StLaunch&) = delete;
+    template <class... KArgs, class... Args>
+    void operator()(void (*kernel)(KArgs...), Args&&... args) {
+        cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    }
+};
+#define st_launch StLaunch
+
 // ----- split-bf16 -------------------------------------------------------------
 __device__ __forceinline__ void split_bf16(float v, bf16& hi, bf16& lo) {
     hi = __float2bfloat16_rn(v);

@@ -40,6 +40,7 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 }
 
 __global__ void __launch_bounds__(128) contract_kernel(const ContractParams p) {
+    pdl_prologue();
     __shared__ __align__(16) bf16 Ds[2][TK][LD];
     __shared__ __align__(16) bf16 Xs[2][TK][LD];
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -147,6 +148,7 @@ __global__ void __launch_bounds__(128) contract_kernel(const ContractParams p) {
 // dW[co][ci][r][s] (PyTorch layout, fp32) = sum over splits of partial[split][co][tap*CinPad + ci]
 __global__ void wgrad_finish_kernel(const float* partial, int splits, int Mpad, int Kpad,
                                     int Cout, int Cin, int CinPad, int taps, const float* dy_slot, float* dw) {
+    pdl_prologue();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = Cout * Cin * taps;
     if (idx >= total) return;
@@ -162,6 +164,7 @@ __global__ void wgrad_finish_kernel(const float* partial, int splits, int Mpad, 
 __global__ void __launch_bounds__(256)
 gram_finish_kernel(const float* __restrict__ partial, int splits, int Mpad, int Kpad, int C, float scale,
                    float* __restrict__ G, int total) {
+    pdl_prologue();
     __shared__ float sm[8][33];
     const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int idx = blockIdx.x * 32 + ol;
@@ -223,15 +226,15 @@ int contract_run(const bf16* dy_hi, const bf16* dy_lo, int Cdy, bool dy_f16, con
     const size_t need = static_cast<size_t>(groups) * p.splits * p.Mpad * p.Kpad * sizeof(float);
     ST_CHECK_ARG(workspace && workspace_bytes >= need, "contract: workspace too small (%zu < %zu)", workspace_bytes, need);
     p.partial = static_cast<float*>(workspace);
-    contract_kernel<<<dim3(mt, kt, groups * p.splits), 128, 0, stream>>>(p);
+    st_launch(dim3(mt, kt, groups * p.splits), 128, 0, stream)(contract_kernel, p);
     ST_CHECK_LAUNCH("contract_kernel");
     if (mode == 0) {
         const int total = Cout * Cin * ks * ks;
-        wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cout, Cin, CinPad, ks * ks, dy_slot, out);
+        st_launch((total + 255) / 256, 256, 0, stream)(wgrad_finish_kernel, p.partial, p.splits, p.Mpad, p.Kpad, Cout, Cin, CinPad, ks * ks, dy_slot, out);
         ST_CHECK_LAUNCH("wgrad_finish_kernel");
     } else {
         const int total = N * Cdy * Cdy;
-        gram_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, p.splits, p.Mpad, p.Kpad, Cdy, scale, out, total);
+        st_launch((total + 31) / 32, 256, 0, stream)(gram_finish_kernel, p.partial, p.splits, p.Mpad, p.Kpad, Cdy, scale, out, total);
         ST_CHECK_LAUNCH("gram_finish_kernel");
     }
     return ST_OK;

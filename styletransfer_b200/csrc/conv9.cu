@@ -33,6 +33,7 @@ conv9_expand_kernel(const float* __restrict__ s0, const float* __restrict__ s1, 
                     const float* __restrict__ bias, int flip,
                     bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, int planes,
                     int N, int H, int W, int tiles_h, int tiles_w) {
+    pdl_prologue();
     extern __shared__ float sm[];
     float* sw = sm;                                  // [CS*81][32]
     float* st = sm + CS * 81 * CB;                   // [CS][EX_SH][EX_SW]
@@ -113,6 +114,7 @@ __global__ void __launch_bounds__(RD_THREADS)
 conv9_reduce_kernel(const bf16* __restrict__ x_hi, const bf16* __restrict__ x_lo, int planes,
                     const float* __restrict__ w, const float* __restrict__ bias, float* __restrict__ out,
                     int N, int H, int W, int tiles_h, int tiles_w) {
+    pdl_prologue();
     extern __shared__ float sm[];
     float* sw = sm;                                  // [81][32][4]  (co padded 3 -> 4)
     float* st = sm + 81 * CB * 4;                    // [RD_SH][RD_SW][32]
@@ -204,6 +206,7 @@ namespace {
 // weights [3][32][9][9] fp32 -> split-bf16 [planes][row = co*9 + s (32, 27 used)][tap = r (9)][ci (32)]
 // (plane code with the fp16 bit: fp16 planes of ST_W_F16_SCALE * w)
 __global__ void conv9_pack_vertical_kernel(const float* __restrict__ w, bf16* __restrict__ hi, int code) {
+    pdl_prologue();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = 32 * 9 * CB;
     if (idx >= total) return;
@@ -230,6 +233,7 @@ __global__ void conv9_pack_vertical_kernel(const float* __restrict__ w, bf16* __
 constexpr int GA_PIX = 256, GA_ROWS = GA_PIX + 2 * PAD9, GA_LD = 33;
 __global__ void __launch_bounds__(GA_PIX)
 conv9_gather_kernel(const float* __restrict__ T, const float* __restrict__ bias, float* __restrict__ out, int N, int H, int W) {
+    pdl_prologue();
     __shared__ float sT[GA_ROWS * GA_LD];
     const size_t HW = static_cast<size_t>(H) * W;
     const long long total = static_cast<long long>(N) * HW;
@@ -287,7 +291,7 @@ int conv9_reduce_tc_run(const bf16* x_hi, const bf16* x_lo, int planes, const fl
     const int wplanes = np >= 3 ? 3 : (np == 2 ? 2 : 1);
     const int wcode = wplanes | (f16 ? ST_FMT_F16 : 0);
     const int total = 32 * 9 * CB;
-    conv9_pack_vertical_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, wp, wcode);
+    st_launch((total + 255) / 256, 256, 0, st)(conv9_pack_vertical_kernel, w, wp, wcode);
     ST_CHECK_LAUNCH("conv9_pack_vertical_kernel");
     int rc = conv_tcx_run(3, x_hi, x_lo, planes, N, H, W, CB, wp, wplanes > 1 ? wp + total : nullptr, wcode, 32, 32, H, W,
                           nullptr, nullptr, nullptr, nullptr, 1, nullptr, nullptr, nullptr, nullptr, 1, T,
@@ -296,7 +300,7 @@ int conv9_reduce_tc_run(const bf16* x_hi, const bf16* x_lo, int planes, const fl
     size_t blocks = (static_cast<size_t>(N) * H * W + GA_PIX - 1) / GA_PIX;
     const size_t cap = static_cast<size_t>(st_num_sms()) * 6;
     if (blocks > cap) blocks = cap;
-    conv9_gather_kernel<<<static_cast<unsigned>(blocks), GA_PIX, 0, st>>>(T, bias, out, N, H, W);
+    st_launch(static_cast<unsigned>(blocks), GA_PIX, 0, st)(conv9_gather_kernel, T, bias, out, N, H, W);
     ST_CHECK_LAUNCH("conv9_gather_kernel");
     return ST_OK;
 }

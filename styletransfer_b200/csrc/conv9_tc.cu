@@ -81,6 +81,7 @@ __device__ __forceinline__ void mma2(uint32_t d, uint32_t a_lo, uint32_t a_hi, u
 
 __global__ void __launch_bounds__(THREADS9, 1)
 conv9_correlate_tc_kernel(const __grid_constant__ CUtensorMap tmB, const C9Params p) {
+    pdl_prologue();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + NS9 * STAGE9);
@@ -274,6 +275,7 @@ __host__ __device__ constexpr uint32_t idesc_mn_k(int M, int N) {     // A MN-ma
 template <int CS, int PL>
 __global__ void __launch_bounds__(X_THREADS, 1)
 conv9_expand_tc_kernel(const X9Params p) {
+    pdl_prologue();
     using C = X9Cfg<CS, PL>;
     constexpr int NQ = C::NQ, NSTG = C::NSTG;
     extern __shared__ uint8_t smem_raw[];
@@ -489,7 +491,7 @@ int launch_expand(const X9Params& p, cudaStream_t stream) {
         attr_set = true;
     }
     const int grid = p.tiles < st_num_sms() ? p.tiles : st_num_sms();
-    conv9_expand_tc_kernel<CS, PL><<<grid, X_THREADS, C::SMEM, stream>>>(p);
+    st_launch(grid, X_THREADS, C::SMEM, stream)(conv9_expand_tc_kernel<CS, PL>, p);
     ST_CHECK_LAUNCH("conv9_expand_tc_kernel");
     return ST_OK;
 }
@@ -528,7 +530,7 @@ int conv9_correlate_tc_run(const bf16* b_hi, bool f16, const float* small_slot, 
         attr_set = true;
     }
     const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv9_correlate_tc_kernel<<<grid, THREADS9, SMEM9, stream>>>(tb, p);
+    st_launch(grid, THREADS9, SMEM9, stream)(conv9_correlate_tc_kernel, tb, p);
     ST_CHECK_LAUNCH("conv9_correlate_tc_kernel");
     *nparts = grid;
     return ST_OK;

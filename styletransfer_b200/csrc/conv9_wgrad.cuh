@@ -19,6 +19,7 @@ __global__ void __launch_bounds__(CR_THREADS)
 conv9_correlate_kernel(const bf16* __restrict__ b_hi, const bf16* __restrict__ b_lo, int planes,
                        const float* __restrict__ s0, const float* __restrict__ s1, int sc,
                        float* __restrict__ partial, int N, int H, int W) {
+    pdl_prologue();
     constexpr int ROWS = 6 / CS;                     // 2 rows at a time for 3 channels, 1 for 6
     constexpr int SROWS = ROWS + 2 * PAD9;
     extern __shared__ float sm[];
@@ -106,6 +107,7 @@ conv9_correlate_kernel(const bf16* __restrict__ b_hi, const bf16* __restrict__ b
 // mul_a / mul_b (optional scale slots of the operands): the sum is multiplied by slot[1] of each
 __global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int nparts, int CS, int mode,
                                           const float* __restrict__ mul_a, const float* __restrict__ mul_b, float* __restrict__ dw) {
+    pdl_prologue();
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int total = CB * CS * 81;
     if (idx >= total) return;
@@ -124,6 +126,7 @@ __global__ void conv9_wgrad_finish_kernel(const float* __restrict__ partial, int
 constexpr int CS_PARTS = 128;
 __global__ void __launch_bounds__(256)
 nchw3_channel_sum_kernel(const float* __restrict__ g, int sc, int N, size_t HW, float* __restrict__ part) {
+    pdl_prologue();
     __shared__ float smr[32];
     const int c = blockIdx.y;
     float s = 0.f;
@@ -137,6 +140,7 @@ nchw3_channel_sum_kernel(const float* __restrict__ g, int sc, int N, size_t HW, 
 }
 __global__ void __launch_bounds__(96)
 nchw3_channel_sum_finish_kernel(const float* __restrict__ part, float* __restrict__ out) {
+    pdl_prologue();
     const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float s = 0.f;
     for (int i = lane; i < CS_PARTS; i += 32) s += part[c * CS_PARTS + i];
@@ -165,11 +169,11 @@ int conv9_expand_run(const float* s0, const float* s1, int sc, int CS, const flo
     if (CS == 3) {
         static bool set3 = false;
         if (!set3) { cudaFuncSetAttribute(conv9_expand_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set3 = true; }
-        conv9_expand_kernel<3><<<grid, EX_THREADS, smem, st>>>(s0, s1, sc, w, bias, flip, out_hi, out_lo, planes, N, H, W, th, tw);
+        st_launch(grid, EX_THREADS, smem, st)(conv9_expand_kernel<3>, s0, s1, sc, w, bias, flip, out_hi, out_lo, planes, N, H, W, th, tw);
     } else {
         static bool set6 = false;
         if (!set6) { cudaFuncSetAttribute(conv9_expand_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set6 = true; }
-        conv9_expand_kernel<6><<<grid, EX_THREADS, smem, st>>>(s0, s1, sc, w, bias, flip, out_hi, out_lo, planes, N, H, W, th, tw);
+        st_launch(grid, EX_THREADS, smem, st)(conv9_expand_kernel<6>, s0, s1, sc, w, bias, flip, out_hi, out_lo, planes, N, H, W, th, tw);
     }
     ST_CHECK_LAUNCH("conv9_expand_kernel");
     return ST_OK;
@@ -183,7 +187,7 @@ int conv9_reduce_run(const bf16* x_hi, const bf16* x_lo, int planes, const float
     const size_t smem = (static_cast<size_t>(81) * CB * 4 + RD_SH * RD_SW * CB) * sizeof(float);
     static bool set = false;
     if (!set) { cudaFuncSetAttribute(conv9_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); set = true; }
-    conv9_reduce_kernel<<<grid, RD_THREADS, smem, st>>>(x_hi, x_lo, planes, w, bias, out, N, H, W, th, tw);
+    st_launch(grid, RD_THREADS, smem, st)(conv9_reduce_kernel, x_hi, x_lo, planes, w, bias, out, N, H, W, th, tw);
     ST_CHECK_LAUNCH("conv9_reduce_kernel");
     return ST_OK;
 }
@@ -216,13 +220,13 @@ int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float*
         if ((rc = conv9_correlate_tc_run(b_hi, f16, sslot, s0, sc, CS, 0, ws, N, H, W, &nparts, st))) return rc;
         if (CS == 6 && (rc = conv9_correlate_tc_run(b_hi, f16, sslot, s1, sc, CS, 3, ws, N, H, W, &nparts, st))) return rc;
         const int total = CB * CS * 81;
-        conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, nparts, CS, mode, big_slot, sslot, dw);
+        st_launch((total + 255) / 256, 256, 0, st)(conv9_wgrad_finish_kernel, ws, nparts, CS, mode, big_slot, sslot, dw);
         ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
         if (db) {
             if (mode == 0) return ew_channel_sum(b_hi, b_lo, planes, big_slot, N * H * W, CB, CB, db, ws, st);
-            nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
+            st_launch(dim3(CS_PARTS, 3), 256, 0, st)(nchw3_channel_sum_kernel, s0, sc, N, static_cast<size_t>(H) * W, ws);
             ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
-            nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);
+            st_launch(1, 96, 0, st)(nchw3_channel_sum_finish_kernel, ws, db);
             ST_CHECK_LAUNCH("nchw3_channel_sum_finish_kernel");
         }
         return ST_OK;
@@ -237,17 +241,17 @@ int conv9_wgrad_run(const bf16* b_hi, const bf16* b_lo, int planes, const float*
         cudaFuncSetAttribute(conv9_correlate_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
         set = true;
     }
-    if (CS == 3) conv9_correlate_kernel<3><<<grid, CR_THREADS, smem, st>>>(b_hi, b_lo, planes, s0, s1, sc, ws, N, H, W);
-    else conv9_correlate_kernel<6><<<grid, CR_THREADS, smem, st>>>(b_hi, b_lo, planes, s0, s1, sc, ws, N, H, W);
+    if (CS == 3) st_launch(grid, CR_THREADS, smem, st)(conv9_correlate_kernel<3>, b_hi, b_lo, planes, s0, s1, sc, ws, N, H, W);
+    else st_launch(grid, CR_THREADS, smem, st)(conv9_correlate_kernel<6>, b_hi, b_lo, planes, s0, s1, sc, ws, N, H, W);
     ST_CHECK_LAUNCH("conv9_correlate_kernel");
     const int total = CB * CS * 81;
-    conv9_wgrad_finish_kernel<<<(total + 255) / 256, 256, 0, st>>>(ws, grid * rows, CS, mode, big_slot, nullptr, dw);
+    st_launch((total + 255) / 256, 256, 0, st)(conv9_wgrad_finish_kernel, ws, grid * rows, CS, mode, big_slot, nullptr, dw);
     ST_CHECK_LAUNCH("conv9_wgrad_finish_kernel");
     if (db) {
         if (mode == 0) return ew_channel_sum(b_hi, b_lo, planes, big_slot, N * H * W, CB, CB, db, ws, st);
-        nchw3_channel_sum_kernel<<<dim3(CS_PARTS, 3), 256, 0, st>>>(s0, sc, N, static_cast<size_t>(H) * W, ws);
+        st_launch(dim3(CS_PARTS, 3), 256, 0, st)(nchw3_channel_sum_kernel, s0, sc, N, static_cast<size_t>(H) * W, ws);
         ST_CHECK_LAUNCH("nchw3_channel_sum_kernel");
-        nchw3_channel_sum_finish_kernel<<<1, 96, 0, st>>>(ws, db);
+        st_launch(1, 96, 0, st)(nchw3_channel_sum_finish_kernel, ws, db);
         ST_CHECK_LAUNCH("nchw3_channel_sum_finish_kernel");
     }
     return ST_OK;

@@ -45,6 +45,7 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
 
 template <int BN>
 __global__ void __launch_bounds__(128) conv_gen_kernel(const GenParams p) {
+    pdl_prologue();
     __shared__ __align__(16) bf16 As[3][BM][LDS];
     __shared__ __align__(16) bf16 Bs[3][BN][LDS];
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
@@ -227,13 +228,13 @@ int conv_gen_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H,
     p.M = N * Ho * Wo;
     const int mblocks = (p.M + BM - 1) / BM;
     if (Cout_pad <= 8) {
-        conv_gen_kernel<8><<<dim3(mblocks, 1), 128, 0, stream>>>(p);
+        st_launch(dim3(mblocks, 1), 128, 0, stream)(conv_gen_kernel<8>, p);
     } else if (Cout_pad <= 16) {
-        conv_gen_kernel<16><<<dim3(mblocks, 1), 128, 0, stream>>>(p);
+        st_launch(dim3(mblocks, 1), 128, 0, stream)(conv_gen_kernel<16>, p);
     } else if (Cout_pad <= 32) {
-        conv_gen_kernel<32><<<dim3(mblocks, 1), 128, 0, stream>>>(p);
+        st_launch(dim3(mblocks, 1), 128, 0, stream)(conv_gen_kernel<32>, p);
     } else {
-        conv_gen_kernel<64><<<dim3(mblocks, (Cout_pad + 63) / 64), 128, 0, stream>>>(p);
+        st_launch(dim3(mblocks, (Cout_pad + 63) / 64), 128, 0, stream)(conv_gen_kernel<64>, p);
     }
     ST_CHECK_LAUNCH("conv_gen_kernel");
     return ST_OK;

@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(IMG_THREADS)
 conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                       bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, bf16* __restrict__ relu_hi, bf16* __restrict__ relu_lo,
                       int planes, int N, int H, int W, int tiles_h, int tiles_w) {
+    pdl_prologue();
     __shared__ __align__(16) float sw[27 * 64];                      // [tap = (c*3 + r)*3 + s][perm64(co)]
     __shared__ __align__(16) float st[3 * IM_SH * IM_SW];
     for (int i = threadIdx.x; i < 27 * 64; i += IMG_THREADS) {
@@ -123,6 +124,7 @@ conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, 
 __global__ void __launch_bounds__(IMG_THREADS)
 conv_image_dgrad_kernel(const bf16* __restrict__ g_hi, const bf16* __restrict__ g_lo, int g_planes,
                         const float* __restrict__ w, float* __restrict__ gx, int N, int H, int W, int tiles_h, int tiles_w) {
+    pdl_prologue();
     extern __shared__ __align__(16) float smd[];
     float* sw = smd;                                   // [tap = r*3 + s][c][perm64(co)]
     float* st = smd + 27 * 64;                         // [IM_SH][IM_GW][64]
@@ -216,7 +218,7 @@ int conv_image_fwd(const float* x, const float* w, const float* bias, bf16* out_
                    bf16* relu_hi, bf16* relu_lo, int planes, int N, int H, int W, int Cout, cudaStream_t st) {
     ST_CHECK_ARG(Cout == 64, "conv_image_fwd: Cout must be 64 (got %d)", Cout);
     const int th = (H + IM_TH - 1) / IM_TH, tw = (W + IM_TW - 1) / IM_TW;
-    conv_image_fwd_kernel<<<img_grid(N * th * tw), IMG_THREADS, 0, st>>>(
+    st_launch(img_grid(N * th * tw), IMG_THREADS, 0, st)(conv_image_fwd_kernel, 
         x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, th, tw);
     ST_CHECK_LAUNCH("conv_image_fwd_kernel");
     return ST_OK;
@@ -229,7 +231,7 @@ int conv_image_dgrad(const bf16* g_hi, const bf16* g_lo, int g_planes, const flo
     const int smem = (27 * 64 + IM_SH * IM_GW * 64) * sizeof(float);
     static bool set = false;
     if (!set) { cudaFuncSetAttribute(conv_image_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); set = true; }
-    conv_image_dgrad_kernel<<<img_grid(N * th * tw), IMG_THREADS, smem, st>>>(g_hi, g_lo, g_planes, w, gx, N, H, W, th, tw);
+    st_launch(img_grid(N * th * tw), IMG_THREADS, smem, st)(conv_image_dgrad_kernel, g_hi, g_lo, g_planes, w, gx, N, H, W, th, tw);
     ST_CHECK_LAUNCH("conv_image_dgrad_kernel");
     return ST_OK;
 }

@@ -96,6 +96,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
                const ConvTcParams p) {
+    pdl_trigger();
     using C = Cfg<KS, BN, PL, RES>;
     constexpr int NA = C::NA, NB = C::NB;
     extern __shared__ uint8_t smem_raw[];
@@ -115,11 +116,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int pad = KS / 2;
     const int kchunks = p.Cin / KCH;
-    // the bias of every output channel, read by the epilogue as shared-memory broadcasts
     const bool bias_staged = p.bias && p.Cout <= C::BIAS_MAX;
-    if (bias_staged)
-        for (int i = threadIdx.x; i < p.Cout; i += NUM_THREADS) sbias[i] = p.bias[i];
 
+    // set-up that touches no global memory runs while the previous kernel of the stream drains (pdl_trigger above)
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tmA_hi); ptx::prefetch_tmap(&tmW_hi);
         if (PL > 1) { ptx::prefetch_tmap(&tmA_lo); ptx::prefetch_tmap(&tmW_lo); }
@@ -129,6 +128,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         ptx::fence_barrier_init();
     }
     if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
+    pdl_wait();                              // from here on the previous kernel's results are visible
+    // the bias of every output channel, read by the epilogue as shared-memory broadcasts
+    if (bias_staged)
+        for (int i = threadIdx.x; i < p.Cout; i += NUM_THREADS) sbias[i] = p.bias[i];
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -429,7 +432,7 @@ int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, 
         attr_set = true;
     }
     const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tc_kernel<KS, BN, PL, RES><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p);
+    st_launch(grid, NUM_THREADS, C::SMEM, stream)(conv_tc_kernel<KS, BN, PL, RES>, ah, al, wh, wl, p);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
 }

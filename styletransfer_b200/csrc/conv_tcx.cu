@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                 const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
                 const ConvTcParams p, const __grid_constant__ XGeom geo) {
+    pdl_trigger();
     using C = XCfg<BN, PL, KC, ROWS>;
     constexpr int NA = C::NA, NB = C::NB;
     extern __shared__ uint8_t smem_raw[];
@@ -97,6 +98,7 @@ conv_tcx_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constan
         ptx::fence_barrier_init();
     }
     if (warp == 1) { ptx::tmem_alloc(tmem_slot, C::TMEM_COLS); ptx::tmem_relinquish(); }
+    pdl_wait();                              // from here on the previous kernel's results are visible
     ptx::tc_fence_before();
     __syncthreads();
     ptx::tc_fence_after();
@@ -237,7 +239,7 @@ int xlaunch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh,
         attr_set = true;
     }
     const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    conv_tcx_kernel<BN, PL, KC, ROWS><<<grid, NUM_THREADS, C::SMEM, stream>>>(ah, al, wh, wl, p, g);
+    st_launch(grid, NUM_THREADS, C::SMEM, stream)(conv_tcx_kernel<BN, PL, KC, ROWS>, ah, al, wh, wl, p, g);
     ST_CHECK_LAUNCH("conv_tcx_kernel");
     return ST_OK;
 }

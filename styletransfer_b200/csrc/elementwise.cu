@@ -16,6 +16,7 @@ namespace {
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                     bf16* __restrict__ hi, bf16* __restrict__ lo,
                                     int N, int C1, int C2, int HW, int Cpad, int planes) {
+    pdl_prologue();
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * HW) return;
     const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
@@ -37,6 +38,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ a, const float* __
 __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __restrict__ lo,
                                     float* __restrict__ out, int N, int C, int HW, int Cpad, int planes,
                                     const float* __restrict__ slot) {
+    pdl_prologue();
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * HW) return;
     const int n = idx / HW; const int px = idx - static_cast<size_t>(n) * HW;
@@ -58,6 +60,7 @@ __global__ void nhwc_to_nchw_kernel(const bf16* __restrict__ hi, const bf16* __r
 // ---------------------------------------------------------------------------
 __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict__ hi, bf16* __restrict__ lo,
                                    int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, int planes) {
+    pdl_prologue();
     const int taps = ks * ks;
     const int total = rows_pad * taps * cols_pad;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -89,6 +92,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, bf16* __restrict
 __global__ void relu_maxpool_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                                         bf16* __restrict__ yh, bf16* __restrict__ yl,
                                         int N, int H, int W, int C, int planes) {
+    pdl_prologue();
     const int Ho = H / 2, Wo = W / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
@@ -115,6 +119,7 @@ __global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16*
                                         const bf16* __restrict__ addh, const bf16* __restrict__ addl,
                                         bf16* __restrict__ gxh, bf16* __restrict__ gxl,
                                         int N, int H, int W, int C, int x_planes) {
+    pdl_prologue();
     const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
@@ -165,6 +170,7 @@ __global__ void relu_maxpool_bwd_kernel(const bf16* __restrict__ xh, const bf16*
 __global__ void relu_maxpool_fwd_idx_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                                             bf16* __restrict__ yh, bf16* __restrict__ yl, unsigned char* __restrict__ arg,
                                             int N, int H, int W, int C, int planes) {
+    pdl_prologue();
     const int Ho = H / 2, Wo = W / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
@@ -191,6 +197,7 @@ __global__ void relu_maxpool_bwd_idx_kernel(const unsigned char* __restrict__ ar
                                             const bf16* __restrict__ gyh, const bf16* __restrict__ gyl,
                                             const bf16* __restrict__ addh, const bf16* __restrict__ addl,
                                             bf16* __restrict__ gxh, bf16* __restrict__ gxl, int N, int H, int W, int C) {
+    pdl_prologue();
     const int Ho = H / 2, Wo = W / 2, Hc = (H + 1) / 2, Wc = (W + 1) / 2, Cv = C / 8;
     const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
@@ -232,6 +239,7 @@ __global__ void relu_maxpool_bwd_idx_kernel(const unsigned char* __restrict__ ar
 __global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl, int x_code,
                                    const bf16* __restrict__ th, const bf16* __restrict__ tl, int t_code,
                                    size_t nvec, int relu, float* __restrict__ partial) {
+    pdl_prologue();
     __shared__ float sm[32];
     float s = 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
@@ -252,6 +260,7 @@ __global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __re
 // amax_out (optional): also max(partial[n .. 2n)) -- the second half of the partials holds per-block maxima
 __global__ void sum_partials_kernel(const float* __restrict__ partial, int n, float scale, int square,
                                     float post_scale, float* __restrict__ out, float* __restrict__ amax_out) {
+    pdl_prologue();
     __shared__ float sm[32];
     float s = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
@@ -271,6 +280,7 @@ __global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restri
                                size_t nvec, int relu, float scale, const float* __restrict__ gw,
                                const float* __restrict__ mul, int accumulate,
                                bf16* __restrict__ gh, bf16* __restrict__ gl) {
+    pdl_prologue();
     const float coef = scale * gw[0] * (mul ? mul[0] : 1.f);
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -293,6 +303,7 @@ __global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restri
 // partial[0 .. grid) = per-block sums of diff^2, partial[grid .. 2 grid) = per-block max |diff|
 __global__ void style_diff_kernel(const float* __restrict__ G, const float* __restrict__ T, int CC, int total,
                                   float* __restrict__ diff, float* __restrict__ partial) {
+    pdl_prologue();
     __shared__ float sm[32];
     float s = 0.f, m = 0.f;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -313,6 +324,7 @@ __global__ void style_diff_kernel(const float* __restrict__ G, const float* __re
 __global__ void style_seed_kernel(const float* __restrict__ diff, int total, float scale, const float* __restrict__ gw,
                                   bf16* __restrict__ dh, bf16* __restrict__ dl, int code,
                                   const float* __restrict__ diff_amax, float* __restrict__ slot) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const float coef = scale * gw[0];
     if (pc_f16(code)) {
@@ -332,6 +344,7 @@ __global__ void style_seed_kernel(const float* __restrict__ diff, int total, flo
 
 // the same for every style node of a loss network at once: blockIdx.y = node
 __global__ void style_seed_multi_kernel(const StyleSeedTable t) {
+    pdl_prologue();
     const StyleSeedEntry& e = t.e[blockIdx.y];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const float coef = e.scale * e.gw[0];
@@ -353,6 +366,7 @@ __global__ void style_seed_multi_kernel(const StyleSeedTable t) {
 // max |x| over a flat fp32 array: per-block partial maxima, then one block -> slot = {s, 1/s} with the power of two s
 // that maps the maximum to 2^target_log2 (the scale under which a gradient image is fed to fp16 tensor-core operands)
 __global__ void absmax_partial_kernel(const float* __restrict__ x, size_t n, float* __restrict__ partial) {
+    pdl_prologue();
     __shared__ float sm[32];
     float m = 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += static_cast<size_t>(gridDim.x) * blockDim.x)
@@ -361,6 +375,7 @@ __global__ void absmax_partial_kernel(const float* __restrict__ x, size_t n, flo
     if (threadIdx.x == 0) partial[blockIdx.x] = m;
 }
 __global__ void absmax_finish_kernel(const float* __restrict__ partial, int n, float target_log2, float* __restrict__ slot) {
+    pdl_prologue();
     __shared__ float sm[32];
     float m = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmaxf(m, partial[i]);
@@ -375,6 +390,7 @@ __global__ void absmax_finish_kernel(const float* __restrict__ partial, int n, f
 __global__ void __launch_bounds__(256)
 channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl, int code,
                            int P, int C, float* __restrict__ partial) {
+    pdl_prologue();
     extern __shared__ float sm[];                 // [lanes][C]
     const int Cv = C / 8, lanes = 256 / Cv;
     const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
@@ -402,6 +418,7 @@ channel_sum_partial_kernel(const bf16* __restrict__ xh, const bf16* __restrict__
 __global__ void __launch_bounds__(256)
 channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, int Cout, const float* __restrict__ slot,
                           float* __restrict__ out) {
+    pdl_prologue();
     __shared__ float sm[8][33];
     const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
@@ -435,6 +452,7 @@ channel_sum_finish_kernel(const float* __restrict__ partial, int nblk, int C, in
 // ---------------------------------------------------------------------------
 struct ImgStats { float mean[3], std[3]; };
 __global__ void image_u8_to_nchw_kernel(const unsigned char* __restrict__ in, float* __restrict__ out, size_t pixels, size_t HW, ImgStats st) {
+    pdl_prologue();
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= pixels) return;
     const size_t n = i / HW, px = i - n * HW;
@@ -445,6 +463,7 @@ __global__ void image_u8_to_nchw_kernel(const unsigned char* __restrict__ in, fl
     }
 }
 __global__ void image_nchw_to_u8_kernel(const float* __restrict__ in, unsigned char* __restrict__ out, size_t pixels, size_t HW, ImgStats st) {
+    pdl_prologue();
     const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= pixels) return;
     const size_t n = i / HW, px = i - n * HW;
@@ -466,41 +485,41 @@ inline int grid_for(size_t n, int block, int cap_mult = 8) {
 
 int ew_nchw_to_nhwc(const float* a, const float* b, bf16* hi, bf16* lo, int planes, int N, int C1, int C2, int H, int W, int Cpad, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * H * W;
-    nchw_to_nhwc_kernel<<<(n + 255) / 256, 256, 0, st>>>(a, b, hi, lo, N, C1, C2, H * W, Cpad, planes);
+    st_launch((n + 255) / 256, 256, 0, st)(nchw_to_nhwc_kernel, a, b, hi, lo, N, C1, C2, H * W, Cpad, planes);
     ST_CHECK_LAUNCH("nchw_to_nhwc_kernel"); return ST_OK;
 }
 int ew_nhwc_to_nchw(const bf16* hi, const bf16* lo, int planes, const float* slot, float* out, int N, int C, int H, int W, int Cpad, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * H * W;
-    nhwc_to_nchw_kernel<<<(n + 255) / 256, 256, 0, st>>>(hi, lo, out, N, C, H * W, Cpad, planes, slot);
+    st_launch((n + 255) / 256, 256, 0, st)(nhwc_to_nchw_kernel, hi, lo, out, N, C, H * W, Cpad, planes, slot);
     ST_CHECK_LAUNCH("nhwc_to_nchw_kernel"); return ST_OK;
 }
 int ew_pack_weight(const float* w, bf16* hi, bf16* lo, int planes, int Cout, int Cin, int ks, int rows_pad, int cols_pad, int mode, cudaStream_t st) {
     const int total = rows_pad * ks * ks * cols_pad;
-    pack_weight_kernel<<<(total + 255) / 256, 256, 0, st>>>(w, hi, lo, Cout, Cin, ks, rows_pad, cols_pad, mode, planes);
+    st_launch((total + 255) / 256, 256, 0, st)(pack_weight_kernel, w, hi, lo, Cout, Cin, ks, rows_pad, cols_pad, mode, planes);
     ST_CHECK_LAUNCH("pack_weight_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_fwd(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, int planes, int N, int H, int W, int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * (H / 2) * (W / 2) * (C / 8);
     if (n == 0) return ST_OK;
-    relu_maxpool_fwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, N, H, W, C, planes);
+    st_launch((n + 255) / 256, 256, 0, st)(relu_maxpool_fwd_kernel, xh, xl, yh, yl, N, H, W, C, planes);
     ST_CHECK_LAUNCH("relu_maxpool_fwd_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_fwd_idx(const bf16* xh, const bf16* xl, bf16* yh, bf16* yl, unsigned char* arg, int planes, int N, int H, int W,
                             int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * (H / 2) * (W / 2) * (C / 8);
-    relu_maxpool_fwd_idx_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, yh, yl, arg, N, H, W, C, planes);
+    st_launch((n + 255) / 256, 256, 0, st)(relu_maxpool_fwd_idx_kernel, xh, xl, yh, yl, arg, N, H, W, C, planes);
     ST_CHECK_LAUNCH("relu_maxpool_fwd_idx_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_bwd_idx(const unsigned char* arg, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
                             bf16* gxh, bf16* gxl, int N, int H, int W, int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
-    relu_maxpool_bwd_idx_kernel<<<(n + 255) / 256, 256, 0, st>>>(arg, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C);
+    st_launch((n + 255) / 256, 256, 0, st)(relu_maxpool_bwd_idx_kernel, arg, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C);
     ST_CHECK_LAUNCH("relu_maxpool_bwd_idx_kernel"); return ST_OK;
 }
 int ew_relu_maxpool_bwd(const bf16* xh, const bf16* xl, const bf16* gyh, const bf16* gyl, const bf16* addh, const bf16* addl,
                         bf16* gxh, bf16* gxl, int x_planes, int N, int H, int W, int C, cudaStream_t st) {
     const size_t n = static_cast<size_t>(N) * ((H + 1) / 2) * ((W + 1) / 2) * (C / 8);
-    relu_maxpool_bwd_kernel<<<(n + 255) / 256, 256, 0, st>>>(xh, xl, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C, x_planes);
+    st_launch((n + 255) / 256, 256, 0, st)(relu_maxpool_bwd_kernel, xh, xl, gyh, gyl, addh, addl, gxh, gxl, N, H, W, C, x_planes);
     ST_CHECK_LAUNCH("relu_maxpool_bwd_kernel"); return ST_OK;
 }
 // workspace: >= 4096 floats
@@ -508,55 +527,55 @@ int ew_mse_fwd(const bf16* xh, const bf16* xl, int x_code, const bf16* th, const
                float* loss_out, float* ws, cudaStream_t st) {
     const size_t nvec = n / 8;
     int grid = grid_for(nvec, 256, 4); if (grid > 4096) grid = 4096;
-    mse_partial_kernel<<<grid, 256, 0, st>>>(xh, xl, x_code, th, tl, t_code, nvec, relu, ws);
+    st_launch(grid, 256, 0, st)(mse_partial_kernel, xh, xl, x_code, th, tl, t_code, nvec, relu, ws);
     ST_CHECK_LAUNCH("mse_partial_kernel");
     // feature_form: (mse)^2 / numel   network.py:193-199
-    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(n), feature_form, 1.0f / static_cast<float>(n), loss_out, nullptr);
+    st_launch(1, 256, 0, st)(sum_partials_kernel, ws, grid, 1.0f / static_cast<float>(n), feature_form, 1.0f / static_cast<float>(n), loss_out, nullptr);
     ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
 }
 int ew_mse_bwd(const bf16* xh, const bf16* xl, int x_code, const bf16* th, const bf16* tl, int t_code, size_t n, int relu, float scale,
                const float* gw, const float* mul, int accumulate, bf16* gh, bf16* gl, cudaStream_t st) {
     const size_t nvec = n / 8;
-    mse_bwd_kernel<<<grid_for(nvec, 256), 256, 0, st>>>(xh, xl, x_code, th, tl, t_code, nvec, relu, scale, gw, mul, accumulate, gh, gl);
+    st_launch(grid_for(nvec, 256), 256, 0, st)(mse_bwd_kernel, xh, xl, x_code, th, tl, t_code, nvec, relu, scale, gw, mul, accumulate, gh, gl);
     ST_CHECK_LAUNCH("mse_bwd_kernel"); return ST_OK;
 }
 // ws: >= 4096 floats (2 x 2048 per-block partials); diff_amax (optional): receives max |diff|
 int ew_style_fwd(const float* G, const float* T, int B, int C, float* diff, float* loss_out, float* diff_amax, float* ws, cudaStream_t st) {
     const int total = B * C * C;
     int grid = grid_for(total, 256, 2); if (grid > 2048) grid = 2048;
-    style_diff_kernel<<<grid, 256, 0, st>>>(G, T, C * C, total, diff, ws);
+    st_launch(grid, 256, 0, st)(style_diff_kernel, G, T, C * C, total, diff, ws);
     ST_CHECK_LAUNCH("style_diff_kernel");
-    sum_partials_kernel<<<1, 256, 0, st>>>(ws, grid, 1.0f / static_cast<float>(total), 0, 1.f, loss_out, diff_amax);
+    st_launch(1, 256, 0, st)(sum_partials_kernel, ws, grid, 1.0f / static_cast<float>(total), 0, 1.f, loss_out, diff_amax);
     ST_CHECK_LAUNCH("sum_partials_kernel"); return ST_OK;
 }
 int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw, bf16* dh, bf16* dl, int code,
                   const float* diff_amax, float* slot, cudaStream_t st) {
     const int total = B * C * C;
-    style_seed_kernel<<<(total + 255) / 256, 256, 0, st>>>(diff, total, scale, gw, dh, dl, code, diff_amax, slot);
+    st_launch((total + 255) / 256, 256, 0, st)(style_seed_kernel, diff, total, scale, gw, dh, dl, code, diff_amax, slot);
     ST_CHECK_LAUNCH("style_seed_kernel"); return ST_OK;
 }
 int ew_style_seed_multi(const StyleSeedTable& t, int max_total, cudaStream_t st) {
-    style_seed_multi_kernel<<<dim3((max_total + 255) / 256, t.n), 256, 0, st>>>(t);
+    st_launch(dim3((max_total + 255) / 256, t.n), 256, 0, st)(style_seed_multi_kernel, t);
     ST_CHECK_LAUNCH("style_seed_multi_kernel"); return ST_OK;
 }
 int ew_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
     ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }
     const size_t px = static_cast<size_t>(N) * H * W;
-    image_u8_to_nchw_kernel<<<(px + 255) / 256, 256, 0, st>>>(in, out, px, static_cast<size_t>(H) * W, s);
+    st_launch((px + 255) / 256, 256, 0, st)(image_u8_to_nchw_kernel, in, out, px, static_cast<size_t>(H) * W, s);
     ST_CHECK_LAUNCH("image_u8_to_nchw_kernel"); return ST_OK;
 }
 int ew_image_nchw_to_u8(const float* in, unsigned char* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
     ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }
     const size_t px = static_cast<size_t>(N) * H * W;
-    image_nchw_to_u8_kernel<<<(px + 255) / 256, 256, 0, st>>>(in, out, px, static_cast<size_t>(H) * W, s);
+    st_launch((px + 255) / 256, 256, 0, st)(image_nchw_to_u8_kernel, in, out, px, static_cast<size_t>(H) * W, s);
     ST_CHECK_LAUNCH("image_nchw_to_u8_kernel"); return ST_OK;
 }
 // slot = {s, 1/s}: power of two mapping max|x| to 2^target_log2; ws >= 1024 floats
 int ew_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, cudaStream_t st) {
     int grid = grid_for(n, 1024, 2); if (grid > 1024) grid = 1024;
-    absmax_partial_kernel<<<grid, 256, 0, st>>>(x, n, ws);
+    st_launch(grid, 256, 0, st)(absmax_partial_kernel, x, n, ws);
     ST_CHECK_LAUNCH("absmax_partial_kernel");
-    absmax_finish_kernel<<<1, 256, 0, st>>>(ws, grid, target_log2, slot);
+    st_launch(1, 256, 0, st)(absmax_finish_kernel, ws, grid, target_log2, slot);
     ST_CHECK_LAUNCH("absmax_finish_kernel"); return ST_OK;
 }
 // ws: >= nblk*C floats with nblk = min(1024, ceil(P/64))
@@ -566,8 +585,8 @@ int ew_channel_sum(const bf16* xh, const bf16* xl, int code, const float* slot, 
     const int cap = st_num_sms() * 4 < 1024 ? st_num_sms() * 4 : 1024;   // ws holds >= 1024 * C floats
     if (nblk > cap) nblk = cap;
     if (nblk < 1) nblk = 1;
-    channel_sum_partial_kernel<<<nblk, 256, lanes * C * sizeof(float), st>>>(xh, xl, code, P, C, ws);
+    st_launch(nblk, 256, lanes * C * sizeof(float), st)(channel_sum_partial_kernel, xh, xl, code, P, C, ws);
     ST_CHECK_LAUNCH("channel_sum_partial_kernel");
-    channel_sum_finish_kernel<<<(C + 31) / 32, 256, 0, st>>>(ws, nblk, C, Cout, slot, out);
+    st_launch((C + 31) / 32, 256, 0, st)(channel_sum_finish_kernel, ws, nblk, C, Cout, slot, out);
     ST_CHECK_LAUNCH("channel_sum_finish_kernel"); return ST_OK;
 }

@@ -39,6 +39,7 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                 const float* __restrict__ gamma, const float* __restrict__ beta,
                 int HW, int W, int C, int splits, int chunk, int relu, int x_planes,
                 float* __restrict__ partial /* [N][splits][2][C] */, float* __restrict__ gmax_partial /* [N*splits] or null */) {
+    pdl_prologue();
     extern __shared__ float sm[];                 // [lanes][2][C]
     __shared__ float smx[32];
     float gmax = 0.f;                             // MODE 1: max |dy_eff| of this block (bound of the fp16 scale of dx)
@@ -130,6 +131,7 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
 __global__ void __launch_bounds__(256)
 in_finalize_fwd_kernel(const float* __restrict__ partial, int C, int splits, int HW, float eps,
                        float* __restrict__ mean, float* __restrict__ rstd) {
+    pdl_prologue();
     __shared__ double ss[8][33], sq[8][33];
     const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl, n = blockIdx.y;
@@ -173,6 +175,7 @@ in_finalize_bwd_kernel(const float* __restrict__ partial, int N, int C, int spli
                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                        const float* __restrict__ gmax_partial, int ngmax, const float* __restrict__ gamma,
                        const float* __restrict__ rstd, float inv_hw, float* __restrict__ bound_part) {
+    pdl_prologue();
     __shared__ float sa[32][33], sb[32][33];
     __shared__ float smx[32];
     // bound of |dx| = |gamma rstd| * |dy_eff - (s1 + xhat s2) / HW| for the fp16 scale of dx (when asked for):
@@ -252,6 +255,7 @@ in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     const float* __restrict__ gamma, const float* __restrict__ beta,
                     bf16* __restrict__ yh, bf16* __restrict__ yl,
                     int HW, int W, int C, int chunk, int relu, int planes) {
+    pdl_prologue();
     const int n = blockIdx.y;
     const int Cv = C / 8, lanes = IN_THREADS / Cv;
     const int cv = threadIdx.x % Cv, pl = threadIdx.x / Cv;
@@ -292,6 +296,7 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
                     bf16* __restrict__ dxh, bf16* __restrict__ dxl, int dx_code,
                     const float* __restrict__ bound_part, int nbound, float* __restrict__ dx_slot,
                     int HW, int W, int C, int chunk, int relu, int x_planes, float* __restrict__ dsum_partial) {
+    pdl_prologue();
     extern __shared__ float sm_ds[];                  // [lanes][C], only when dsum_partial != null
     const int n = blockIdx.y;
     // dx_slot: dx is stored multiplied by the power of two that maps its bound to 2^10 (fp16 planes)
@@ -358,6 +363,7 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
 // dependent chain on 1..4 blocks; fixed-order tree over the lanes (deterministic)
 __global__ void __launch_bounds__(1024)
 in_colsum_kernel(const float* __restrict__ partial, int rows, int C, float* __restrict__ out) {
+    pdl_prologue();
     __shared__ float sm[128][9];
     const int cl = threadIdx.x & 7, rl = threadIdx.x >> 3;
     const int c = blockIdx.x * 8 + cl;
@@ -386,6 +392,7 @@ in_colsum_kernel(const float* __restrict__ partial, int rows, int C, float* __re
 // Total variation on an NCHW fp32 image batch: partial sums of |dx| + |dy|
 // ---------------------------------------------------------------------------
 __global__ void tv_partial_kernel(const float* __restrict__ x, size_t total, int H, int W, float* __restrict__ partial) {
+    pdl_prologue();
     __shared__ float sm[32];
     float s = 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -402,6 +409,7 @@ __device__ __forceinline__ float sgn(float v) { return (v > 0.f) ? 1.f : ((v < 0
 // g = coef * d/dx TV,  coef = factor * (*gw)
 __global__ void tv_bwd_kernel(const float* __restrict__ x, size_t total, int H, int W, float factor,
                               const float* __restrict__ gw, float* __restrict__ g) {
+    pdl_prologue();
     const float coef = factor * gw[0];
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -416,6 +424,7 @@ __global__ void tv_bwd_kernel(const float* __restrict__ x, size_t total, int H, 
     }
 }
 __global__ void finish_scalar_kernel(const float* __restrict__ partial, int n, float scale, float* __restrict__ out) {
+    pdl_prologue();
     __shared__ float sm[32];
     float s = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
@@ -429,6 +438,7 @@ __global__ void finish_scalar_kernel(const float* __restrict__ partial, int n, f
 __global__ void temporal_partial_kernel(const float* __restrict__ oc, const float* __restrict__ os,
                                         const float* __restrict__ cc, const float* __restrict__ cs,
                                         size_t total, float* __restrict__ partial /* [grid][2] */) {
+    pdl_prologue();
     __shared__ float sm[32];
     float a = 0.f, b = 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -442,6 +452,7 @@ __global__ void temporal_partial_kernel(const float* __restrict__ oc, const floa
 }
 // out[0] = loss, out[1] = ||ds||, out[2] = ||dc||
 __global__ void temporal_finish_kernel(const float* __restrict__ partial, int n, float tw, float* __restrict__ out) {
+    pdl_prologue();
     __shared__ float sm[32];
     float a = 0.f, b = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) { a += partial[i * 2]; b += partial[i * 2 + 1]; }
@@ -455,6 +466,7 @@ __global__ void temporal_finish_kernel(const float* __restrict__ partial, int n,
 // g = (*gw) * tw / ((nc + 1) * ns) * (cs - os)   (0 when ns == 0, as torch's norm backward)
 __global__ void temporal_bwd_kernel(const float* __restrict__ os, const float* __restrict__ cs, size_t total, float tw,
                                     const float* __restrict__ stats, const float* __restrict__ gw, float* __restrict__ g) {
+    pdl_prologue();
     const float ns = stats[1], nc = stats[2];
     const float coef = ns > 0.f ? gw[0] * tw / ((nc + 1.f) * ns) : 0.f;
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -489,6 +501,7 @@ __global__ void temporal_warp_partial_kernel(const float* __restrict__ oc, const
                                              const float* __restrict__ cc, const float* __restrict__ cs,
                                              const float* __restrict__ flow, int N, int C, int H, int W,
                                              float* __restrict__ partial /* [grid][2] */) {
+    pdl_prologue();
     __shared__ float sm[32];
     const size_t HW = (size_t)H * W, pixels = (size_t)N * HW;
     float a = 0.f, b = 0.f;
@@ -511,6 +524,7 @@ __global__ void temporal_warp_partial_kernel(const float* __restrict__ oc, const
 __global__ void temporal_warp_bwd_kernel(const float* __restrict__ os, const float* __restrict__ cs, const float* __restrict__ flow,
                                          int N, int C, int H, int W, float tw, const float* __restrict__ stats,
                                          const float* __restrict__ gw, float* __restrict__ g) {
+    pdl_prologue();
     const float ns = stats[1], nc = stats[2];
     const float coef = ns > 0.f ? gw[0] * tw / ((nc + 1.f) * ns) : 0.f;
     const size_t HW = (size_t)H * W, pixels = (size_t)N * HW;
@@ -565,14 +579,14 @@ int in_forward(const bf16* xh, const bf16* xl, const float* gamma, const float* 
     const int HW = H * W, splits = in_splits(N, HW);
     const int chunk = (HW + splits - 1) / splits;
     const int lanes = IN_THREADS / (C / 8);
-    in_stats_kernel<0, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+    st_launch(N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st)(in_stats_kernel<0, 0>, 
         xh, xl, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, HW, W, C, splits, chunk, 0, planes, ws, nullptr);
     ST_CHECK_LAUNCH("in_stats_kernel<0>");
-    in_finalize_fwd_kernel<<<dim3((C + 31) / 32, N), 256, 0, st>>>(ws, C, splits, HW, eps, mean, rstd);
+    st_launch(dim3((C + 31) / 32, N), 256, 0, st)(in_finalize_fwd_kernel, ws, C, splits, HW, eps, mean, rstd);
     ST_CHECK_LAUNCH("in_finalize_fwd_kernel");
     const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
-    if (up) in_apply_fwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
-    else in_apply_fwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, 0, st>>>(xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
+    if (up) st_launch(dim3(ablocks, N), IN_THREADS, 0, st)(in_apply_fwd_kernel<1>, xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
+    else st_launch(dim3(ablocks, N), IN_THREADS, 0, st)(in_apply_fwd_kernel<0>, xh, xl, mean, rstd, gamma, beta, yh, yl, HW, W, C, achunk, relu, planes);
     ST_CHECK_LAUNCH("in_apply_fwd_kernel");
     return ST_OK;
 }
@@ -592,24 +606,24 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
     float* boundp = gmaxp + static_cast<size_t>(N) * IN_MAX_SPLITS;
     float* gmax_arg = dx_slot ? gmaxp : nullptr;
     if (up)
-        in_stats_kernel<1, 1><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+        st_launch(N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st)(in_stats_kernel<1, 1>, 
             xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws, gmax_arg);
     else
-        in_stats_kernel<1, 0><<<N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st>>>(
+        st_launch(N * splits, IN_THREADS, lanes * 2 * C * sizeof(float), st)(in_stats_kernel<1, 0>, 
             xh, xl, gh, gl, mean, rstd, gamma, beta, HW, W, C, splits, chunk, relu, x_planes, ws, gmax_arg);
     ST_CHECK_LAUNCH("in_stats_kernel<1>");
     const int nbound = (C + 31) / 32;
-    in_finalize_bwd_kernel<<<nbound, 1024, 0, st>>>(ws, N, C, splits, s1, s2, dgamma, dbeta, gmaxp, N * splits, gamma, rstd,
+    st_launch(nbound, 1024, 0, st)(in_finalize_bwd_kernel, ws, N, C, splits, s1, s2, dgamma, dbeta, gmaxp, N * splits, gamma, rstd,
                                                     1.0f / HW, dx_slot ? boundp : nullptr);
     ST_CHECK_LAUNCH("in_finalize_bwd_kernel");
     const int ablocks = in_apply_blocks(N, HW), achunk = (HW + ablocks - 1) / ablocks;
     float* dpart = dsum ? s2 + static_cast<size_t>(N) * C : nullptr;        // [N * ablocks][C]
     const size_t dsm = dsum ? static_cast<size_t>(IN_THREADS / (C / 8)) * C * sizeof(float) : 0;
-    if (up) in_apply_bwd_kernel<1><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
-    else in_apply_bwd_kernel<0><<<dim3(ablocks, N), IN_THREADS, dsm, st>>>(xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
+    if (up) st_launch(dim3(ablocks, N), IN_THREADS, dsm, st)(in_apply_bwd_kernel<1>, xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
+    else st_launch(dim3(ablocks, N), IN_THREADS, dsm, st)(in_apply_bwd_kernel<0>, xh, xl, gh, gl, mean, rstd, gamma, beta, s1, s2, dxh, dxl, dx_code, boundp, nbound, dx_slot, HW, W, C, achunk, relu, x_planes, dpart);
     ST_CHECK_LAUNCH("in_apply_bwd_kernel");
     if (dsum) {
-        in_colsum_kernel<<<(C + 7) / 8, 1024, 0, st>>>(dpart, N * ablocks, C, dsum);
+        st_launch((C + 7) / 8, 1024, 0, st)(in_colsum_kernel, dpart, N * ablocks, C, dsum);
         ST_CHECK_LAUNCH("in_colsum_kernel");
     }
     return ST_OK;
@@ -617,44 +631,44 @@ int in_backward(const bf16* xh, const bf16* xl, const bf16* gh, const bf16* gl,
 
 int tv_forward(const float* x, size_t total, int H, int W, float factor, float* loss, float* ws, cudaStream_t st) {
     int grid = ew_grid(total, 256); if (grid > 2048) grid = 2048;
-    tv_partial_kernel<<<grid, 256, 0, st>>>(x, total, H, W, ws);
+    st_launch(grid, 256, 0, st)(tv_partial_kernel, x, total, H, W, ws);
     ST_CHECK_LAUNCH("tv_partial_kernel");
-    finish_scalar_kernel<<<1, 256, 0, st>>>(ws, grid, factor, loss);
+    st_launch(1, 256, 0, st)(finish_scalar_kernel, ws, grid, factor, loss);
     ST_CHECK_LAUNCH("finish_scalar_kernel");
     return ST_OK;
 }
 int tv_backward(const float* x, size_t total, int H, int W, float factor, const float* gw, float* g, cudaStream_t st) {
-    tv_bwd_kernel<<<ew_grid(total, 256), 256, 0, st>>>(x, total, H, W, factor, gw, g);
+    st_launch(ew_grid(total, 256), 256, 0, st)(tv_bwd_kernel, x, total, H, W, factor, gw, g);
     ST_CHECK_LAUNCH("tv_bwd_kernel");
     return ST_OK;
 }
 int temporal_forward(const float* oc, const float* os, const float* cc, const float* cs, size_t total, float tw,
                      float* out3, float* ws, cudaStream_t st) {
     int grid = ew_grid(total, 256); if (grid > 1024) grid = 1024;
-    temporal_partial_kernel<<<grid, 256, 0, st>>>(oc, os, cc, cs, total, ws);
+    st_launch(grid, 256, 0, st)(temporal_partial_kernel, oc, os, cc, cs, total, ws);
     ST_CHECK_LAUNCH("temporal_partial_kernel");
-    temporal_finish_kernel<<<1, 256, 0, st>>>(ws, grid, tw, out3);
+    st_launch(1, 256, 0, st)(temporal_finish_kernel, ws, grid, tw, out3);
     ST_CHECK_LAUNCH("temporal_finish_kernel");
     return ST_OK;
 }
 int temporal_warp_forward(const float* oc, const float* os, const float* cc, const float* cs, const float* flow, int N, int C,
                           int H, int W, float tw, float* out3, float* ws, cudaStream_t st) {
     int grid = ew_grid((size_t)N * H * W, 256); if (grid > 1024) grid = 1024;
-    temporal_warp_partial_kernel<<<grid, 256, 0, st>>>(oc, os, cc, cs, flow, N, C, H, W, ws);
+    st_launch(grid, 256, 0, st)(temporal_warp_partial_kernel, oc, os, cc, cs, flow, N, C, H, W, ws);
     ST_CHECK_LAUNCH("temporal_warp_partial_kernel");
-    temporal_finish_kernel<<<1, 256, 0, st>>>(ws, grid, tw, out3);
+    st_launch(1, 256, 0, st)(temporal_finish_kernel, ws, grid, tw, out3);
     ST_CHECK_LAUNCH("temporal_finish_kernel");
     return ST_OK;
 }
 int temporal_warp_backward(const float* os, const float* cs, const float* flow, int N, int C, int H, int W, float tw,
                            const float* stats, const float* gw, float* g, cudaStream_t st) {
-    temporal_warp_bwd_kernel<<<ew_grid((size_t)N * H * W, 256), 256, 0, st>>>(os, cs, flow, N, C, H, W, tw, stats, gw, g);
+    st_launch(ew_grid((size_t)N * H * W, 256), 256, 0, st)(temporal_warp_bwd_kernel, os, cs, flow, N, C, H, W, tw, stats, gw, g);
     ST_CHECK_LAUNCH("temporal_warp_bwd_kernel");
     return ST_OK;
 }
 int temporal_backward(const float* os, const float* cs, size_t total, float tw, const float* stats, const float* gw,
                       float* g, cudaStream_t st) {
-    temporal_bwd_kernel<<<ew_grid(total, 256), 256, 0, st>>>(os, cs, total, tw, stats, gw, g);
+    st_launch(ew_grid(total, 256), 256, 0, st)(temporal_bwd_kernel, os, cs, total, tw, stats, gw, g);
     ST_CHECK_LAUNCH("temporal_bwd_kernel");
     return ST_OK;
 }

@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
                                                    const int* __restrict__ steps, const int* __restrict__ active,
                                                    double lr, double b1d, double b2d, float omb1, float omb2, float eps, float wd,
                                                    float gscale, const AdamPackSeg* __restrict__ packs) {
+    pdl_prologue();
     const AdamChunk c = chunks[blockIdx.x];
     if (!active[c.seg]) return;
     const bool repack = packs && packs[c.seg].ndst > 0;
@@ -98,6 +99,7 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
     }
 }
 __global__ void adam_tick_kernel(int* steps, const int* active, int nseg) {
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nseg && active[i]) steps[i] += 1;
 }
@@ -126,11 +128,11 @@ extern "C" int st_adam_step(float* param, const float* grad, float* exp_avg, flo
     ST_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && chunks && steps && active && nchunks > 0 && nseg > 0,
                  "st_adam_step: null pointer or empty table");
     cudaStream_t st = (cudaStream_t)stream;
-    adam_kernel<<<(unsigned)nchunks, 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, (const AdamChunk*)chunks, steps, active,
+    st_launch((unsigned)nchunks, 256, 0, st)(adam_kernel, param, grad, exp_avg, exp_avg_sq, (const AdamChunk*)chunks, steps, active,
                                                     lr, beta1, beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), (float)eps,
                                                     (float)weight_decay, (float)grad_scale, (const AdamPackSeg*)packs);
     ST_CHECK_LAUNCH("adam_kernel");
-    adam_tick_kernel<<<(nseg + 127) / 128, 128, 0, st>>>(steps, active, nseg);
+    st_launch((nseg + 127) / 128, 128, 0, st)(adam_tick_kernel, steps, active, nseg);
     ST_CHECK_LAUNCH("adam_tick_kernel");
     return ST_OK;
 }
@@ -212,6 +214,7 @@ __global__ void __launch_bounds__(256, PIPE ? 2 : 3) lbfgs_dots_kernel(const flo
                                                          const float* __restrict__ Y, size_t n, size_t ld, int m,
                                                          const double* __restrict__ st, int first, int chunks_per_block,
                                                          double* __restrict__ partials) {
+    pdl_prologue();
     if (!first && st[H_HALT] != 0.0) return;
     const int k = (int)st[H_K];
     const int SL = LB_SL(m);
@@ -285,6 +288,7 @@ __global__ void __launch_bounds__(256, PIPE ? 2 : 3) lbfgs_dots_kernel(const flo
 // ---- solve: history bookkeeping + two-loop recursion on coefficients, one CTA
 __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ st, int m, size_t nblocks, const float* __restrict__ loss_ptr,
                                                            int first) {
+    pdl_prologue();
     extern __shared__ double sm[];
     const LbfgsState L{m};
     const int tid = threadIdx.x, lane = tid & 31;
@@ -477,6 +481,7 @@ __global__ void __launch_bounds__(1024) lbfgs_solve_kernel(double* __restrict__ 
 __global__ void __launch_bounds__(256, 3) lbfgs_update_kernel(float* __restrict__ x, const float* __restrict__ g, float* __restrict__ gp,
                                                            float* __restrict__ d, float* __restrict__ S, float* __restrict__ Y,
                                                            size_t n, size_t ld, int m, double* __restrict__ st) {
+    pdl_prologue();
     if (st[H_RUNB] == 0.0) return;
     const LbfgsState L{m};
     __shared__ double cy[LB_MAX_M], cs[LB_MAX_M];
@@ -538,6 +543,7 @@ __global__ void __launch_bounds__(256, 3) lbfgs_update_kernel(float* __restrict_
 }
 
 __global__ void lbfgs_init_kernel(double* st, int m, double lr, double tolg, double tolc) {
+    pdl_prologue();
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         st[H_LR] = lr; st[H_TOLG] = tolg; st[H_TOLC] = tolc; st[H_M] = (double)m; st[H_HDIAG] = 1.0;
     }
@@ -559,7 +565,7 @@ extern "C" int st_lbfgs_init(void* state, int history, size_t n, double lr, doub
     if (cudaMemsetAsync(state, 0, st_lbfgs_state_bytes(history, n), s) != cudaSuccess) {
         st_set_error("st_lbfgs_init: cudaMemsetAsync failed"); cudaGetLastError(); return ST_ERR_CUDA;
     }
-    lbfgs_init_kernel<<<1, 32, 0, s>>>((double*)state, history, lr, tolerance_grad, tolerance_change);
+    st_launch(1, 32, 0, s)(lbfgs_init_kernel, (double*)state, history, lr, tolerance_grad, tolerance_change);
     ST_CHECK_LAUNCH("lbfgs_init_kernel");
     return ST_OK;
 }
@@ -583,15 +589,15 @@ extern "C" int st_lbfgs_iteration(float* x, const float* grad, const float* loss
         attr = true;
     }
     if (g_lbfgs_variant)
-        lbfgs_dots_kernel<true><<<(unsigned)nb, 256, 0, s>>>(grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
+        st_launch((unsigned)nb, 256, 0, s)(lbfgs_dots_kernel<true>, grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
                                                              st + L.partials());
     else
-        lbfgs_dots_kernel<false><<<(unsigned)nb, 256, 0, s>>>(grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
+        st_launch((unsigned)nb, 256, 0, s)(lbfgs_dots_kernel<false>, grad, g_prev, dir, S, Y, n, ld, history, st, first_of_step, (int)lb_cpb(n),
                                                               st + L.partials());
     ST_CHECK_LAUNCH("lbfgs_dots_kernel");
-    lbfgs_solve_kernel<<<1, 1024, lb_solve_smem(history), s>>>(st, history, nb, loss, first_of_step);
+    st_launch(1, 1024, lb_solve_smem(history), s)(lbfgs_solve_kernel, st, history, nb, loss, first_of_step);
     ST_CHECK_LAUNCH("lbfgs_solve_kernel");
-    lbfgs_update_kernel<<<(unsigned)((n + 1023) / 1024), 256, 0, s>>>(x, grad, g_prev, dir, S, Y, n, ld, history, st);
+    st_launch((unsigned)((n + 1023) / 1024), 256, 0, s)(lbfgs_update_kernel, x, grad, g_prev, dir, S, Y, n, ld, history, st);
     ST_CHECK_LAUNCH("lbfgs_update_kernel");
     return ST_OK;
 }

@@ -89,6 +89,7 @@ __device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint32_t a_lo, uint32_t 
 template <int KH, int CDY>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmD, const WgradParams p) {
+    pdl_prologue();
     using C = WCfg<KH, CDY>;
     constexpr int NS = C::NS;
     extern __shared__ uint8_t smem_raw[];
@@ -220,6 +221,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
 __global__ void __launch_bounds__(256)
 wgrad_tc_finish_kernel(const float* __restrict__ partial, int splits, int KW, int chunks, int nacc, int CDY,
                        int Cout, int Cin, int KH, const float* __restrict__ dy_slot, float* __restrict__ dw) {
+    pdl_prologue();
     __shared__ float tile[8][33];
     const int J = Cin * KH * KW;
     const int co0 = blockIdx.y * 32, j0 = blockIdx.x * 8;
@@ -282,6 +284,7 @@ template <int C_> struct GCfg {
 template <int C_>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
+    pdl_prologue();
     using G = GCfg<C_>;
     constexpr int NS = G::NS;
     extern __shared__ uint8_t smem_raw[];
@@ -386,6 +389,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
 // G[b][i][j] = scale * sum over splits of partial[b][split][i / 128][i % 128][j]
 __global__ void __launch_bounds__(256)
 gram_tc_finish_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, float* __restrict__ Gm, int total) {
+    pdl_prologue();
     __shared__ float sm[8][33];
     const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int idx = blockIdx.x * 32 + ol;
@@ -418,6 +422,7 @@ gram_tc_finish_kernel(const float* __restrict__ partial, int splits, int nacc, i
 // outputs walks the splits itself -- the 8-lane layout above would leave most lanes of its 32768 blocks idle
 __global__ void __launch_bounds__(256)
 gram_tc_finish_small_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, float* __restrict__ Gm, int total4) {
+    pdl_prologue();
     const int v = blockIdx.x * 256 + threadIdx.x;
     if (v >= total4) return;
     int q = v * 4; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
@@ -471,6 +476,7 @@ __device__ __forceinline__ void style_tail_finish(const StyleTail& t, float s, f
 
 __global__ void __launch_bounds__(256)
 gram_tc_finish_style_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, int total, StyleTail t) {
+    pdl_prologue();
     __shared__ float sm[8][33];
     __shared__ float red[32];
     const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
@@ -507,6 +513,7 @@ gram_tc_finish_style_kernel(const float* __restrict__ partial, int splits, int n
 
 __global__ void __launch_bounds__(256)
 gram_tc_finish_small_style_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, int total4, StyleTail t) {
+    pdl_prologue();
     __shared__ float red[32];
     const int v = blockIdx.x * 256 + threadIdx.x;
     float d2 = 0.f, am = 0.f;
@@ -562,7 +569,7 @@ int launch_gram(const CUtensorMap& tf, const GramParams& p, int grid, cudaStream
         if (e != cudaSuccess) { st_set_error("gram_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
-    gram_tc_kernel<C_><<<grid, NUM_THREADS, G::SMEM, stream>>>(tf, p);
+    st_launch(grid, NUM_THREADS, G::SMEM, stream)(gram_tc_kernel<C_>, tf, p);
     ST_CHECK_LAUNCH("gram_tc_kernel");
     return ST_OK;
 }
@@ -576,7 +583,7 @@ int launch_wgrad(const CUtensorMap& tx, const CUtensorMap& td, const WgradParams
         if (e != cudaSuccess) { st_set_error("wgrad_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
-    wgrad_tc_kernel<KH, CDY><<<grid, NUM_THREADS, C::SMEM, stream>>>(tx, td, p);
+    st_launch(grid, NUM_THREADS, C::SMEM, stream)(wgrad_tc_kernel<KH, CDY>, tx, td, p);
     ST_CHECK_LAUNCH("wgrad_tc_kernel");
     return ST_OK;
 }
@@ -633,19 +640,19 @@ int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, f
         t.T = T; t.diff = diff; t.Gm = Gm; t.part = style_part; t.ticket = ticket; t.loss = loss; t.amax = amax;
         t.inv_total = 1.0f / static_cast<float>(total);
         if (q.splits <= 16) {
-            gram_tc_finish_small_style_kernel<<<(total / 4 + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, total / 4, t);
+            st_launch((total / 4 + 255) / 256, 256, 0, stream)(gram_tc_finish_small_style_kernel, p.partial, q.splits, q.nacc, C, scale, total / 4, t);
             ST_CHECK_LAUNCH("gram_tc_finish_small_style_kernel");
         } else {
-            gram_tc_finish_style_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, total, t);
+            st_launch((total + 31) / 32, 256, 0, stream)(gram_tc_finish_style_kernel, p.partial, q.splits, q.nacc, C, scale, total, t);
             ST_CHECK_LAUNCH("gram_tc_finish_style_kernel");
         }
         return ST_OK;
     }
     if (q.splits <= 16) {
-        gram_tc_finish_small_kernel<<<(total / 4 + 255) / 256, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total / 4);
+        st_launch((total / 4 + 255) / 256, 256, 0, stream)(gram_tc_finish_small_kernel, p.partial, q.splits, q.nacc, C, scale, Gm, total / 4);
         ST_CHECK_LAUNCH("gram_tc_finish_small_kernel");
     } else {
-        gram_tc_finish_kernel<<<(total + 31) / 32, 256, 0, stream>>>(p.partial, q.splits, q.nacc, C, scale, Gm, total);
+        st_launch((total + 31) / 32, 256, 0, stream)(gram_tc_finish_kernel, p.partial, q.splits, q.nacc, C, scale, Gm, total);
         ST_CHECK_LAUNCH("gram_tc_finish_kernel");
     }
     return ST_OK;
@@ -685,7 +692,7 @@ int wgrad_tc_run(const bf16* dy_hi, const bf16* x_hi, bool f16, const float* dy_
     else rc = launch_wgrad<3, 32>(tx, td, p, q.grid, stream);
     if (rc) return rc;
     const int J = Cin * ks * ks;
-    wgrad_tc_finish_kernel<<<dim3((J + 7) / 8, (Cout + 31) / 32), 256, 0, stream>>>(p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dy_slot, dw);
+    st_launch(dim3((J + 7) / 8, (Cout + 31) / 32), 256, 0, stream)(wgrad_tc_finish_kernel, p.partial, q.splits, ks, q.chunks, q.nacc, Cdy, Cout, Cin, ks, dy_slot, dw);
     ST_CHECK_LAUNCH("wgrad_tc_finish_kernel");
     return ST_OK;
 }
