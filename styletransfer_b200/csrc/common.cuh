@@ -189,6 +189,40 @@ __device__ __forceinline__ void load8p(const bf16* hi, const bf16* lo, int code,
         for (int i = 0; i < 4; ++i) { v[2 * i] += bf16lo_to_f(lw[i]); v[2 * i + 1] += bf16hi_to_f(lw[i]); }
     }
 }
+// The same in two steps -- raw 16-byte loads of every plane first, arithmetic afterwards -- for loops that want ALL the
+// loads of an iteration in flight before the first use: load8p branches on the plane code between its loads, which
+// makes every load -> convert pair a separate exposed round trip (profiles/r02ac_in_kernels_fast_st.txt).  Absent
+// planes are read from the hi plane (an L1 hit) and replaced by zeros, so the instruction stream has no branches.
+struct Raw8p { uint4 h, l, t; };
+__device__ __forceinline__ void load8p_raw(const bf16* hi, const bf16* lo, int code, size_t off, Raw8p& r) {
+    const int planes = pc_planes(code);
+    const bf16* lp = (planes >= 2 && lo) ? lo : hi;
+    const bf16* tp = third_plane(hi, lo, code);
+    const bf16* tq = tp ? tp : hi;
+    r.h = __ldg(reinterpret_cast<const uint4*>(hi + off));
+    r.l = __ldg(reinterpret_cast<const uint4*>(lp + off));
+    r.t = __ldg(reinterpret_cast<const uint4*>(tq + off));
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    if (lp == hi) r.l = z;
+    if (!tp) r.t = z;
+}
+__device__ __forceinline__ void decode8p(const Raw8p& r, int code, float (&v)[8]) {
+    const uint32_t hw[4] = {r.h.x, r.h.y, r.h.z, r.h.w}, lw[4] = {r.l.x, r.l.y, r.l.z, r.l.w}, tw[4] = {r.t.x, r.t.y, r.t.z, r.t.w};
+    if (pc_f16(code)) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float2 a = unpack_f16x2(hw[i]), b = unpack_f16x2(lw[i]);
+            v[2 * i] = a.x + b.x; v[2 * i + 1] = a.y + b.y;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            // same association as load8p: (hi + lo) + third
+            v[2 * i] = (bf16lo_to_f(hw[i]) + bf16lo_to_f(lw[i])) + bf16lo_to_f(tw[i]);
+            v[2 * i + 1] = (bf16hi_to_f(hw[i]) + bf16hi_to_f(lw[i])) + bf16hi_to_f(tw[i]);
+        }
+    }
+}
 __device__ __forceinline__ void store8p(bf16* hi, bf16* lo, int code, size_t off, const float (&v)[8]) {
     const int planes = pc_planes(code);
     if (pc_f16(code)) { store8h(hi, planes >= 2 ? lo : nullptr, off, v); return; }

@@ -83,14 +83,30 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
             for (int p = p0 + pl; p < p1; p += 2 * lanes) {
                 const bool two = p + lanes < p1;
                 float x0[8], x1[8], g0[8], g1[8];
-                load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x0);
-                in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
-                if (two) {
-                    load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p + lanes) * C + cv * 8, x1);
-                    in_load_grad<UP>(gh, gl, n, HW, W, C, p + lanes, cv, g1);
-                } else {
+                if (UP) {
+                    load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x0);
+                    in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
+                    if (two) {
+                        load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p + lanes) * C + cv * 8, x1);
+                        in_load_grad<UP>(gh, gl, n, HW, W, C, p + lanes, cv, g1);
+                    } else {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) { x1[i] = 0.f; g1[i] = 0.f; }
+                        for (int i = 0; i < 8; ++i) { x1[i] = 0.f; g1[i] = 0.f; }
+                    }
+                } else {
+                    // all ten 16-byte loads of the two pixels are issued before the first conversion (no branch in between);
+                    // a missing second pixel re-reads the first one and its gradient is zeroed
+                    const size_t o0 = (static_cast<size_t>(n) * HW + p) * C + cv * 8;
+                    const size_t o1 = (static_cast<size_t>(n) * HW + (two ? p + lanes : p)) * C + cv * 8;
+                    Raw8p rx0, rx1, rg0, rg1;
+                    load8p_raw(xh, xl, x_planes, o0, rx0); load8p_raw(gh, gl, 2, o0, rg0);
+                    load8p_raw(xh, xl, x_planes, o1, rx1); load8p_raw(gh, gl, 2, o1, rg1);
+                    decode8p(rx0, x_planes, x0); decode8p(rg0, 2, g0);
+                    decode8p(rx1, x_planes, x1); decode8p(rg1, 2, g1);
+                    if (!two) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { x1[i] = 0.f; g1[i] = 0.f; }
+                    }
                 }
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
@@ -323,11 +339,7 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
 #pragma unroll
     for (int i = 0; i < 8; ++i) gr[i] = ga[i] * rs[i];
     const size_t img = static_cast<size_t>(n) * HW;
-#pragma unroll(UP ? 1 : 2)
-    for (int p = p0 + pl; p < p1; p += lanes) {
-        float x0[8], g0[8];                           // (two pixels per iteration measured slower here)
-        load8p(xh, xl, x_planes, (img + p) * C + cv * 8, x0);
-        in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
+    auto finish_pixel = [&](float (&x0)[8], const float (&g0)[8], int p) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float xhat = (x0[i] - mu[i]) * rs[i];
@@ -341,6 +353,28 @@ in_apply_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
             for (int i = 0; i < 8; ++i) x0[i] *= dx_scale;
         }
         store8p(dxh, dxl, dx_code, (img + p) * C + cv * 8, x0);
+    };
+    if (UP) {
+        for (int p = p0 + pl; p < p1; p += lanes) {
+            float x0[8], g0[8];
+            load8p(xh, xl, x_planes, (img + p) * C + cv * 8, x0);
+            in_load_grad<UP>(gh, gl, n, HW, W, C, p, cv, g0);
+            finish_pixel(x0, g0, p);
+        }
+    } else {
+        // two pixels per iteration, all ten 16-byte loads issued before the first conversion
+        for (int p = p0 + pl; p < p1; p += 2 * lanes) {
+            const bool two = p + lanes < p1;
+            const size_t o0 = (img + p) * C + cv * 8, o1 = (img + (two ? p + lanes : p)) * C + cv * 8;
+            Raw8p rx0, rx1, rg0, rg1;
+            load8p_raw(xh, xl, x_planes, o0, rx0); load8p_raw(gh, gl, 2, o0, rg0);
+            load8p_raw(xh, xl, x_planes, o1, rx1); load8p_raw(gh, gl, 2, o1, rg1);
+            float x0[8], g0[8], x1[8], g1[8];
+            decode8p(rx0, x_planes, x0); decode8p(rg0, 2, g0);
+            decode8p(rx1, x_planes, x1); decode8p(rg1, 2, g1);
+            finish_pixel(x0, g0, p);
+            if (two) finish_pixel(x1, g1, p + lanes);
+        }
     }
     }
     // sum of dx per channel over this block's pixels (= bias gradient of the convolution in front)
