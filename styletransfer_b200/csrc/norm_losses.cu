@@ -72,12 +72,24 @@ in_stats_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
     }
     if (pl < lanes) {
         if (MODE == 0) {
-#pragma unroll 2
-            for (int p = p0 + pl; p < p1; p += lanes) {
-                float x[8];
-                load8p(xh, xl, x_planes, (static_cast<size_t>(n) * HW + p) * C + cv * 8, x);
+            // four pixels per iteration, their (up to) twelve 16-byte loads in flight together; a missing pixel re-reads
+            // the first one and contributes nothing
+            for (int p = p0 + pl; p < p1; p += 4 * lanes) {
+                Raw8p r[4];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) { sa[i] += x[i]; sb[i] += x[i] * x[i]; }
+                for (int j = 0; j < 4; ++j) {
+                    const int pj = p + j * lanes < p1 ? p + j * lanes : p;
+                    load8p_raw(xh, xl, x_planes, (static_cast<size_t>(n) * HW + pj) * C + cv * 8, r[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float x[8];
+                    decode8p(r[j], x_planes, x);
+                    if (p + j * lanes < p1) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { sa[i] += x[i]; sb[i] += x[i] * x[i]; }
+                    }
+                }
             }
         } else {
             for (int p = p0 + pl; p < p1; p += 2 * lanes) {
@@ -281,22 +293,31 @@ in_apply_fwd_kernel(const bf16* __restrict__ xh, const bf16* __restrict__ xl,
     load8f(mean + n * C + cv * 8, mu); load8f(rstd + n * C + cv * 8, rs);
     load8f(gamma + cv * 8, ga); load8f(beta + cv * 8, be);
     const size_t img = static_cast<size_t>(n) * HW;
-#pragma unroll 2
-    for (int p = p0 + pl; p < p1; p += lanes) {
-        float x[8];
-        load8p(xh, xl, planes, (img + p) * C + cv * 8, x);
+    // two pixels per iteration, their loads in flight together (load8p_raw: no branch between the loads)
+    for (int p = p0 + pl; p < p1; p += 2 * lanes) {
+        const bool two = p + lanes < p1;
+        Raw8p r0, r1;
+        load8p_raw(xh, xl, planes, (img + p) * C + cv * 8, r0);
+        load8p_raw(xh, xl, planes, (img + (two ? p + lanes : p)) * C + cv * 8, r1);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float y = ga[i] * (x[i] - mu[i]) * rs[i] + be[i];
-            x[i] = relu ? fmaxf(y, 0.f) : y;
-        }
-        if (!UP) {
-            store8p(yh, yl, planes, (img + p) * C + cv * 8, x);
-        } else {
-            const int h = p / W, w = p - h * W;
-            const size_t o = ((img * 4) + static_cast<size_t>(h * 2) * (W * 2) + w * 2) * C + cv * 8;
-            store8p(yh, yl, planes, o, x); store8p(yh, yl, planes, o + C, x);
-            store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C, x); store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C + C, x);
+        for (int j = 0; j < 2; ++j) {
+            if (j == 1 && !two) break;
+            const int q = p + j * lanes;
+            float x[8];
+            decode8p(j ? r1 : r0, planes, x);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float y = ga[i] * (x[i] - mu[i]) * rs[i] + be[i];
+                x[i] = relu ? fmaxf(y, 0.f) : y;
+            }
+            if (!UP) {
+                store8p(yh, yl, planes, (img + q) * C + cv * 8, x);
+            } else {
+                const int h = q / W, w = q - h * W;
+                const size_t o = ((img * 4) + static_cast<size_t>(h * 2) * (W * 2) + w * 2) * C + cv * 8;
+                store8p(yh, yl, planes, o, x); store8p(yh, yl, planes, o + C, x);
+                store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C, x); store8p(yh, yl, planes, o + static_cast<size_t>(W) * 2 * C + C, x);
+            }
         }
     }
 }
