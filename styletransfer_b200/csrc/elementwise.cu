@@ -176,9 +176,14 @@ __global__ void relu_maxpool_fwd_idx_kernel(const bf16* __restrict__ xh, const b
     if (idx >= static_cast<size_t>(N) * Ho * Wo * Cv) return;
     size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wo; q /= Wo; const int oh = q % Ho; const int n = q / Ho;
     float x[4][8];
+    {
+        Raw8p r[4];                                          // every load of the window in flight before the first conversion
 #pragma unroll
-    for (int d = 0; d < 4; ++d)
-        load8p(xh, xl, planes, ((static_cast<size_t>(n) * H + oh * 2 + (d >> 1)) * W + ow * 2 + (d & 1)) * C + cv * 8, x[d]);
+        for (int d = 0; d < 4; ++d)
+            load8p_raw(xh, xl, planes, ((static_cast<size_t>(n) * H + oh * 2 + (d >> 1)) * W + ow * 2 + (d & 1)) * C + cv * 8, r[d]);
+#pragma unroll
+        for (int d = 0; d < 4; ++d) decode8p(r[d], planes, x[d]);
+    }
     float m[8]; uint32_t a_lo = 0, a_hi = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
@@ -203,32 +208,41 @@ __global__ void relu_maxpool_bwd_idx_kernel(const unsigned char* __restrict__ ar
     if (idx >= static_cast<size_t>(N) * Hc * Wc * Cv) return;
     size_t q = idx; const int cv = q % Cv; q /= Cv; const int ow = q % Wc; q /= Wc; const int oh = q % Hc; const int n = q / Hc;
     const bool pooled = oh < Ho && ow < Wo;
-    float g[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) g[i] = 0.f;
-    uint2 a = make_uint2(0x04040404u, 0x04040404u);
-    if (pooled) {
-        const size_t o = ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * C + cv * 8;
-        load8(gyh, gyl, o, g);
-        a = *reinterpret_cast<const uint2*>(arg + o);
-    }
+    // every load of this thread (pooled gradient, routing bytes, the four addends) is issued before the first use
+    const size_t o = ((static_cast<size_t>(n) * Ho + (pooled ? oh : 0)) * Wo + (pooled ? ow : 0)) * C + cv * 8;
+    Raw8p rg, ra[4];
+    load8p_raw(gyh, gyl, 2, o, rg);
+    uint2 a = *reinterpret_cast<const uint2*>(arg + o);
+    size_t off[4]; bool in[4];
 #pragma unroll
     for (int d = 0; d < 4; ++d) {
         const int h = oh * 2 + (d >> 1), w = ow * 2 + (d & 1);
-        if (h >= H || w >= W) continue;
-        const size_t off = ((static_cast<size_t>(n) * H + h) * W + w) * C + cv * 8;
-        float o[8];
+        in[d] = h < H && w < W;
+        off[d] = ((static_cast<size_t>(n) * H + (in[d] ? h : oh * 2)) * W + (in[d] ? w : ow * 2)) * C + cv * 8;
+        if (addh) load8p_raw(addh, addl, 2, off[d], ra[d]);
+    }
+    float g[8];
+    decode8p(rg, 2, g);
+    if (!pooled) {
+        a = make_uint2(0x04040404u, 0x04040404u);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] = 0.f;
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (!in[d]) continue;
+        float ov[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const uint32_t ai = ((i < 4 ? a.x : a.y) >> (8 * (i & 3))) & 0xffu;
-            o[i] = (ai == static_cast<uint32_t>(d)) ? g[i] : 0.f;
+            ov[i] = (ai == static_cast<uint32_t>(d)) ? g[i] : 0.f;
         }
         if (addh) {
-            float ad[8]; load8(addh, addl, off, ad);
+            float ad[8]; decode8p(ra[d], 2, ad);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] += ad[i];
+            for (int i = 0; i < 8; ++i) ov[i] += ad[i];
         }
-        store8(gxh, gxl, off, o);
+        store8(gxh, gxl, off[d], ov);
     }
 }
 
@@ -245,7 +259,9 @@ __global__ void mse_partial_kernel(const bf16* __restrict__ xh, const bf16* __re
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
         float a[8], b[8];
-        load8p(xh, xl, x_code, i * 8, a); load8p(th, tl, t_code, i * 8, b);
+        Raw8p ra, rb;
+        load8p_raw(xh, xl, x_code, i * 8, ra); load8p_raw(th, tl, t_code, i * 8, rb);
+        decode8p(ra, x_code, a); decode8p(rb, t_code, b);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             float d = relu ? (fmaxf(a[k], 0.f) - fmaxf(b[k], 0.f)) : (a[k] - b[k]);
@@ -285,7 +301,9 @@ __global__ void mse_bwd_kernel(const bf16* __restrict__ xh, const bf16* __restri
     for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
          i += static_cast<size_t>(gridDim.x) * blockDim.x) {
         float a[8], b[8], o[8];
-        load8p(xh, xl, x_code, i * 8, a); load8p(th, tl, t_code, i * 8, b);
+        Raw8p ra, rb;
+        load8p_raw(xh, xl, x_code, i * 8, ra); load8p_raw(th, tl, t_code, i * 8, rb);
+        decode8p(ra, x_code, a); decode8p(rb, t_code, b);
         if (accumulate) load8(gh, gl, i * 8, o);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
