@@ -91,7 +91,7 @@ template <int KS, int BN, int PL, bool RES> struct Cfg {
     static_assert(2 * NA + 2 * NB + 4 <= 256 / 8 - 1, "barrier area");
 };
 
-template <int KS, int BN, int PL, bool RES>
+template <int KS, int BN, int PL, bool RES, bool FUSED>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant__ CUtensorMap tmA_lo,
                const __grid_constant__ CUtensorMap tmW_hi, const __grid_constant__ CUtensorMap tmW_lo,
@@ -172,6 +172,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                 }
                 for (int c = 0; c < kchunks; ++c) {
                     ptx::mbar_wait(&a_empty[a], aph ^ 1);
+                    if (c == 0) TRACE(0, (wk - blockIdx.x) / gridDim.x, 0);
                     ptx::mbar_expect_tx(&a_full[a], C::A_TX);
                     uint8_t* dst = sA + a * C::A_SLOT;
                     // planes 1 and 2 of a tensor are equally spaced: the "lo" map spans both
@@ -267,6 +268,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                     if (!a_ready) ptx::mbar_wait(&a_full[a], aph);
                     a_ready = false;
                     ptx::tc_fence_after();
+                    if (c == 0) TRACE(1, it, 1);
                     const uint32_t a_lo0 = ptx::umma_desc_lo(ptx::smem_u32(sA + a * C::A_SLOT));
                     const int an = (a + 1 == NA) ? 0 : a + 1;
                     const uint32_t anph = (a + 1 == NA) ? aph ^ 1 : aph;
@@ -327,6 +329,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
                         b = bn; bph = bnph;
                     }
                     a = an; aph = anph;
+                    if (c == kchunks - 1) TRACE(1, it, 2);
                 }
             }
         }
@@ -344,7 +347,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
             px.pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
             return px;
         };
-        tc_epilogue_warps<BN, C::NACC>(p, bias_staged ? sbias : p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
+        tc_epilogue_warps<BN, C::NACC, FUSED ? 1 : 0>(p, bias_staged ? sbias : p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
     }
 
     ptx::tc_fence_before();
@@ -421,20 +424,27 @@ inline int make_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t*
     return st_make_tmap(out, ptr, rank, dims, box, 128, 1);
 }
 
-template <int KS, int BN, int PL, bool RES>
-int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
-           const ConvTcParams& p, cudaStream_t stream) {
+template <int KS, int BN, int PL, bool RES, bool FUSED>
+int launch_one(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
+               const ConvTcParams& p, cudaStream_t stream) {
     using C = Cfg<KS, BN, PL, RES>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN, PL, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<KS, BN, PL, RES, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) { st_set_error("conv_tc smem attribute: %s", cudaGetErrorString(e)); return ST_ERR_CUDA; }
         attr_set = true;
     }
     const int grid = p.work < st_num_sms() ? p.work : st_num_sms();
-    st_launch(grid, NUM_THREADS, C::SMEM, stream)(conv_tc_kernel<KS, BN, PL, RES>, ah, al, wh, wl, p);
+    st_launch(grid, NUM_THREADS, C::SMEM, stream)(conv_tc_kernel<KS, BN, PL, RES, FUSED>, ah, al, wh, wl, p);
     ST_CHECK_LAUNCH("conv_tc_kernel");
     return ST_OK;
+}
+// the fused epilogue (ReLU mask / addend) and the plain one live in separate kernels
+template <int KS, int BN, int PL, bool RES>
+int launch(const CUtensorMap& ah, const CUtensorMap& al, const CUtensorMap& wh, const CUtensorMap& wl,
+           const ConvTcParams& p, cudaStream_t stream) {
+    if (p.mask || p.add_hi) return launch_one<KS, BN, PL, RES, true>(ah, al, wh, wl, p, stream);
+    return launch_one<KS, BN, PL, RES, false>(ah, al, wh, wl, p, stream);
 }
 
 template <int KS, int BN>

@@ -187,7 +187,7 @@ __device__ __forceinline__ void tc_group(const ConvTcParams& p, const TcMul& mul
 }
 
 // dec(wk, m) -> TcPix of accumulator row m of work item wk.  bias: see tc_chunk_compute.
-template <int BN, int NACC, class Decode>
+template <int BN, int NACC, int FMODE = -1, class Decode>
 __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const float* bias, uint32_t tmem_base, int stage_cols,
                                                   uint64_t* t_full, uint64_t* t_empty, int warp, int lane, const Decode& dec) {
     constexpr int CW = BN >= 32 ? BN / 2 : BN;            // columns per warp
@@ -197,7 +197,9 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
     const int m = q * 32 + lane;
     const bool active = BN >= 32 || hf == 0;
     const int col_base = BN >= 32 ? hf * CW : 0;
-    const bool fused = p.mask || p.add_hi;                // warp-uniform
+    // FMODE >= 0: the launch picked a kernel that holds only one of the two epilogues (half the code: short launches
+    // spent a quarter of their samples on instruction-cache misses, profiles/r02al)
+    const bool fused = FMODE < 0 ? (p.mask || p.add_hi) : (FMODE == 1);                // warp-uniform
     const TcMul mul = tc_muls(p);
     const int step = gridDim.x;
     auto taddr_of = [&](int it) { return tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (it & 1) * stage_cols; };
@@ -233,11 +235,14 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             TcPix nx = px;
             if (more) nx = dec(wk + step, m);
             begin_tile(it);
-            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
+            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
+                                    if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
             tc_group<BN, NACC, GCH, true>(p, mul, bias, &A, taddr_of(it), px, col_base, false, end_tile);
             if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
             tc_group<BN, NACC, GCH, true>(p, mul, bias, &B, taddr_of(it), px, col_base + GCH, true, end_tile);
             if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
     } else {
         // buffers alternate between tiles: A holds tile k, B tile k + 1; tile k + 2 is fetched into A after tile k
