@@ -192,6 +192,11 @@ int st_style_mse_bwd_seed(const float* diff, int B, int C, int HW, const float* 
 int st_style_mse_bwd_seed_multi(int n, const float* const* diff, const int* B, const int* C, const int* HW,
                                 const float* const* gw, void* const* d_hi, void* const* d_lo, const int* d_planes,
                                 const float* const* diff_amax, float* const* d_slot, void* stream);
+/* The value a training closure returns (network.py:704-722, :1020): total = sum_i losses[i] * weights[i]
+ * + extra0 * scale0 + extra1 * scale1 (total-variation and temporal terms; either may be null), one launch instead of
+ * the stack / sum / mul / add chain of the loss getters (network.py:358-364). */
+int st_loss_total(const float* losses, const float* weights, int n, const float* extra0, float scale0,
+                  const float* extra1, float scale1, float* out, void* stream);
 /* slot = {s, 1/s}, s the power of two that maps max|x| of a flat fp32 array to 2^target_log2 (the scale under which
  * a gradient image enters fp16 tensor-core operands).  ws: >= 1024 floats */
 int st_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, void* stream);

@@ -56,6 +56,7 @@ SIGNATURES = {
     'st_style_mse_bwd_seed_multi': (_I, [_I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     'st_style_mse_fwd': (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P]),
     'st_style_mse_bwd_seed': (_I, [_P, _I, _I, _I, _P, _P, _P, _I, _P, _P, _P]),
+    'st_loss_total': (_I, [_P, _P, _I, _P, _F, _P, _F, _P, _P]),
     'st_absmax_slot': (_I, [_P, _Z, _F, _P, _P, _P]),
     'st_mse_fwd': (_I, [_P, _P, _I, _P, _P, _I, _Z, _I, _I, _P, _P, _P]),
     'st_mse_bwd': (_I, [_P, _P, _I, _P, _P, _I, _Z, _I, _F, _P, _P, _I, _P, _P, _P]),

@@ -59,6 +59,7 @@ int ew_style_fwd(const float*, const float*, int, int, float*, float*, float*, f
 int ew_style_seed(const float*, int, int, float, const float*, bf16*, bf16*, int, const float*, float*, cudaStream_t);
 int ew_style_seed_multi(const StyleSeedTable&, int, cudaStream_t);
 int ew_absmax_slot(const float*, size_t, float, float*, float*, cudaStream_t);
+int ew_loss_total(const float*, const float*, int, const float*, float, const float*, float, float*, cudaStream_t);
 int ew_image_u8_to_nchw(const unsigned char*, float*, int, int, int, const float*, const float*, cudaStream_t);
 int ew_image_nchw_to_u8(const float*, unsigned char*, int, int, int, const float*, const float*, cudaStream_t);
 int ew_channel_sum(const bf16*, const bf16*, int, const float*, int, int, int, float*, float*, cudaStream_t);
@@ -359,6 +360,11 @@ int st_style_mse_bwd_seed_multi(int n, const float* const* diff, const int* B, c
         if (t.e[i].total > max_total) max_total = t.e[i].total;
     }
     return ew_style_seed_multi(t, max_total, STRM(stream));
+}
+int st_loss_total(const float* losses, const float* weights, int n, const float* extra0, float scale0,
+                  const float* extra1, float scale1, float* out, void* stream) {
+    ST_CHECK_ARG(losses && weights && out && n > 0, "st_loss_total: null pointer or no loss nodes");
+    return ew_loss_total(losses, weights, n, extra0, scale0, extra1, scale1, out, STRM(stream));
 }
 int st_absmax_slot(const float* x, size_t n, float target_log2, float* slot, float* ws, void* stream) {
     ST_CHECK_ARG(x && slot && ws && n > 0, "st_absmax_slot: null pointer or empty array");

@@ -381,6 +381,18 @@ __global__ void style_seed_multi_kernel(const StyleSeedTable t) {
     if (e.dl) e.dl[i] = l;
 }
 
+// total = sum_i losses[i] * weights[i] + e0 * s0 + e1 * s1: the weighted sum a training closure returns, in one launch
+// (the reference's stack / sum / mul / add chain of the loss getters, network.py:358-364, :704-722)
+__global__ void loss_total_kernel(const float* __restrict__ losses, const float* __restrict__ weights, int n,
+                                  const float* __restrict__ e0, float s0, const float* __restrict__ e1, float s1,
+                                  float* __restrict__ out) {
+    pdl_prologue();
+    float t = 0.f;
+    for (int i = threadIdx.x; i < n; i += 32) t += losses[i] * weights[i];
+    t = warp_sum(t);
+    if (threadIdx.x == 0) out[0] = t + (e0 ? e0[0] * s0 : 0.f) + (e1 ? e1[0] * s1 : 0.f);
+}
+
 // max |x| over a flat fp32 array: per-block partial maxima, then one block -> slot = {s, 1/s} with the power of two s
 // that maps the maximum to 2^target_log2 (the scale under which a gradient image is fed to fp16 tensor-core operands)
 __global__ void absmax_partial_kernel(const float* __restrict__ x, size_t n, float* __restrict__ partial) {
@@ -575,6 +587,10 @@ int ew_style_seed(const float* diff, int B, int C, float scale, const float* gw,
 int ew_style_seed_multi(const StyleSeedTable& t, int max_total, cudaStream_t st) {
     st_launch(dim3((max_total + 255) / 256, t.n), 256, 0, st)(style_seed_multi_kernel, t);
     ST_CHECK_LAUNCH("style_seed_multi_kernel"); return ST_OK;
+}
+int ew_loss_total(const float* losses, const float* weights, int n, const float* e0, float s0, const float* e1, float s1, float* out, cudaStream_t st) {
+    st_launch(1, 32, 0, st)(loss_total_kernel, losses, weights, n, e0, s0, e1, s1, out);
+    ST_CHECK_LAUNCH("loss_total_kernel"); return ST_OK;
 }
 int ew_image_u8_to_nchw(const unsigned char* in, float* out, int N, int H, int W, const float* mean3, const float* std3, cudaStream_t st) {
     ImgStats s; for (int c = 0; c < 3; ++c) { s.mean[c] = mean3[c]; s.std[c] = std3[c]; }

@@ -433,7 +433,7 @@ class StyleNetwork(nn.Module):
             # total = <losses, weights> as one dot product; the weights go into the backward as the gradient of
             # the loss vector itself (no mul / sum nodes for autograd to walk back through)
             losses = self._loss_vector
-            total_loss = torch.dot(losses.detach(), weights)
+            total_loss = ops.loss_total(losses.detach(), weights)
             torch.autograd.backward(losses, grad_tensors=weights)
             return total_loss
         if graph is None:
@@ -752,16 +752,30 @@ class ImageTransformNet(nn.Sequential):
             regularization_loss = regularization_loss * tv_scale
         return style_loss + content_loss + regularization_loss, transformed_image
 
-    def _backward_into_bucket(self, total_loss):
+    def _backward_into_bucket(self, total_loss, grad_tensors=None):
         """backward() with the parameters' (zeroed, bucket-view) ``.grad`` tensors as gradient sinks: the
         backward kernels write dW / db / dgamma / dbeta straight into the flat bucket instead of handing 62
-        tensors to autograd's accumulate kernels (transform._PackCache.grad_sink)."""
+        tensors to autograd's accumulate kernels (transform._PackCache.grad_sink).  ``total_loss`` may be a list of
+        tensors with their ``grad_tensors`` (the loss vector and the extra terms of ``_weighted_total``)."""
         if os.environ.get('STRANSFER_GRAD_SINKS', '1') != '0':
             self._pack_cache.grad_sink = {n: p.grad for n, p in self.named_parameters() if p.grad is not None}
         try:
-            total_loss.backward()
+            if grad_tensors is None:
+                total_loss.backward()
+            else:
+                torch.autograd.backward(total_loss, grad_tensors=grad_tensors)
         finally:
             self._pack_cache.grad_sink = None
+
+    def _weighted_total(self, loss_network, weights, extras):
+        """The training closures' total loss without the getters' stack / sum / mul / add chain (network.py:704-722):
+        ``total = <loss vector, weights> + sum(extra * scale)`` in one launch, and the backward seeded with the weights
+        themselves -- the same arithmetic as style_weight * style + content_weight * content + TV (+ temporal), no ATen
+        launches between the loss kernels and the backward.  extras: [(0-dim loss tensor, scale, device scalar of that
+        scale)].  Returns (total, tensors to differentiate, their gradient seeds)."""
+        losses = loss_network._loss_vector
+        total = ops.loss_total(losses.detach(), weights, [(t.detach(), sc) for t, sc, _ in extras])
+        return total, [losses] + [t for t, _, _ in extras], [weights] + [g for _, _, g in extras]
 
 
     def _step_closure(self, body, bucket, optimizer, graph, loss_network=None):
@@ -851,12 +865,23 @@ class ImageTransformNet(nn.Sequential):
         and the flat gradient bucket."""
         world = st_dist.world_size()
 
+        weights = loss_network.loss_weights(style_weight, content_weight)
+        tv_seed = torch.full((), float(world), dtype=torch.float32, device=batch.device)
+
         def body():
             loss_network._content_key = None             # the content image is the batch: new targets every step
             bucket.rebind()
             bucket.zero()
-            total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight, tv_scale=float(world))
-            self._backward_into_bucket(total_loss)
+            if os.environ.get('STRANSFER_FAST_TOTAL', '1') == '0':
+                total_loss, _ = self.closure_loss(batch, loss_network, style_weight, content_weight, tv_scale=float(world))
+                self._backward_into_bucket(total_loss)
+                return total_loss
+            # closure_loss without the getters: same terms, same weights, one launch for the total
+            transformed_image = self(batch)
+            loss_network(transformed_image, content_image=batch)
+            tv = self.get_total_variation_regularization_loss(transformed_image)
+            total_loss, terms, seeds = self._weighted_total(loss_network, weights, [(tv, float(world), tv_seed)])
+            self._backward_into_bucket(terms, seeds)
             return total_loss
         if graph is None:
             graph = cuda_graphs_enabled()
@@ -1035,15 +1060,29 @@ class VideoTransformNet(ImageTransformNet):
         tensor of optical flow in pixels from the previous frame to this one; the temporal loss then compares against
         the flow-warped previous frames (the loop copies every frame's flow into it)."""
         world = st_dist.world_size()
+        weights = loss_network.loss_weights(style_weight, content_weight)
+        tv_seed = torch.full((), float(world), dtype=torch.float32, device=batch.device)
+        one_seed = torch.ones((), dtype=torch.float32, device=batch.device)
 
         def body():
             loss_network._content_key = None
             bucket.rebind()
             bucket.zero()
-            state = [old_content, old_stylized]
-            total_loss, transformed = self.closure_loss_video(batch, state, loss_network, temporal_weight, style_weight,
-                                                              content_weight, tv_scale=float(world), flow=flow)
-            self._backward_into_bucket(total_loss)
+            if os.environ.get('STRANSFER_FAST_TOTAL', '1') == '0':
+                state = [old_content, old_stylized]
+                total_loss, transformed = self.closure_loss_video(batch, state, loss_network, temporal_weight, style_weight,
+                                                                  content_weight, tv_scale=float(world), flow=flow)
+                self._backward_into_bucket(total_loss)
+            else:
+                # closure_loss_video without the getters (see _weighted_total)
+                transformed = self.forward_pair(batch, old_stylized)
+                loss_network(transformed, content_image=batch)
+                tv = self.get_total_variation_regularization_loss(transformed)
+                temporal = self.get_temporal_loss(old_content, old_stylized, batch, transformed,
+                                                  temporal_weight=temporal_weight, flow=flow)
+                total_loss, terms, seeds = self._weighted_total(loss_network, weights,
+                                                                [(tv, float(world), tv_seed), (temporal, 1.0, one_seed)])
+                self._backward_into_bucket(terms, seeds)
             with torch.no_grad():
                 next_stylized.copy_(transformed)
             return total_loss

@@ -459,6 +459,16 @@ def style_seed_multi(nodes):
     return out
 
 
+def loss_total(losses, weights, extras=()):
+    """sum(losses * weights) + sum(extra * scale) as a 0-dim device tensor, one launch.  extras: up to two
+    (0-dim tensor, float scale) pairs."""
+    out = torch.empty((), dtype=torch.float32, device=losses.device)
+    ex = list(extras) + [(None, 0.0)] * (2 - len(extras))
+    _lib.check(_lib.lib().st_loss_total(losses.data_ptr(), weights.data_ptr(), losses.numel(), _p(ex[0][0]), float(ex[0][1]),
+                                        _p(ex[1][0]), float(ex[1][1]), out.data_ptr(), _stream()), 'st_loss_total')
+    return out
+
+
 def absmax_slot(t, target_log2=10.0):
     """{s, 1/s} with the power of two s that maps max|t| to 2^target_log2 (device tensor, no host sync)."""
     _require_cuda(t, 'absmax_slot')

@@ -458,7 +458,9 @@ def test_bucket_gradient_sinks_match_autograd(network, video):
     else:
         closure = net.training_closure(batch, loss_net, bucket, graph=False)
     total2 = closure()
-    assert float(total2) == float(total)
+    # the closure forms its total as one weighted sum of the loss vector (network._weighted_total): same terms, another
+    # association than weight * stack(...).sum() -- last-bit differences in the value, none in the gradients
+    assert abs(float(total2) - float(total)) <= 1e-6 * abs(float(total))
     got = {n: p.grad for n, p in net.named_parameters() if p.grad is not None}
     assert set(got) == set(want)
     for n in want:
