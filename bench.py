@@ -134,6 +134,15 @@ class KernelTrace:
     def __init__(self, ops, L):
         self.ops, self.L = ops, L
         self.conv, self.norm = [], []
+        # what the bracket itself costs: two event records back to back behind the same spin, no kernel in between
+        # (2.6 us on B200); subtracted from every bracket.  A bracket around a ~2 us kernel reads 6.1 us, so this is a
+        # lower bound of the overhead and the reported launch durations stay on the conservative side.
+        ts = []
+        for _ in range(20):
+            _, e0, e1 = self._bracket(lambda: None, (), {})
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        self.overhead_ms = statistics.median(ts)
 
     def _bracket(self, fn, a, k):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -187,10 +196,14 @@ class KernelTrace:
         per = len(records) // max(steps, 1)
         return [records[i][:t0] + (statistics.median(r[t0].elapsed_time(r[t1]) for r in records[i::per]),) for i in range(per)]
 
+    def _net(self, one):
+        """Subtracts the empty-bracket overhead from the last field (ms) of every record."""
+        return [r[:-1] + (max(r[-1] - self.overhead_ms, 1e-4),) for r in one]
+
     def tensor_roofline(self, precision, step_ms, what):
         """Roofline of the dominant kernel family: the 3x3 conv_tc launches."""
         pk = peaks()
-        one = self._medians(self.conv, self.steps, 3, 4)
+        one = self._net(self._medians(self.conv, self.steps, 3, 4))
         k3 = [r for r in one if r[1] == 3]
         fl, ms = sum(r[2] for r in k3), sum(r[3] for r in k3)
         achieved = fl / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
@@ -204,6 +217,7 @@ class KernelTrace:
                     'peak_source': pk['src'] + ' bf16_tflops_sustained (kernel timed inside a long step)',
                     'avg_launch_ms': ms / max(len(k3), 1), 'algorithmic_gflop_per_launch': fl / max(len(k3), 1) / 1e9,
                     'mma_passes_per_product': passes, 'issued_frac': achieved * passes / pk['tf_sustained'],
+                    'bracket_overhead_us': self.overhead_ms * 1e3,
                     'share_of_step': ms / step_ms if step_ms else None}
         kernels = {k: {'tflops': g[0] / (g[1] * 1e-3) / 1e12, 'ms_per_launch': g[1] / g[2], 'launches_per_step': g[2]}
                    for k, g in sorted(groups.items())}
@@ -215,7 +229,7 @@ class KernelTrace:
         if not self.norm:
             return None
         pk = peaks()
-        one = self._medians(self.norm, self.steps, 2, 3)
+        one = self._net(self._medians(self.norm, self.steps, 2, 3))
         by, ms = sum(r[1] for r in one), sum(r[2] for r in one)
         achieved = by / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         return {'bound': 'hbm', 'kernel': f'InstanceNorm2d forward/backward kernel groups ({len(one)} calls per step)',
