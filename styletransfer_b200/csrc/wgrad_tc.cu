@@ -272,7 +272,7 @@ template <int C_> struct GCfg {
     static constexpr int PLANE = NBOX * BOX;
     static constexpr int STAGE = PL * PLANE;
     static constexpr int NACC = C_ > 128 ? C_ / 128 : 1;
-    static constexpr int TMEM_NEED = NACC * C_;
+    static constexpr int TMEM_NEED = C_;                          // one 128-row half per CTA
     static constexpr int TMEM_COLS = TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
     static constexpr int SLACK = C_ == 64 ? BOX : 0;              // C = 64: the second M group is don't-care data
     static constexpr int NS_FIT = (232448 - 1024 - 256 - SLACK) / STAGE;
@@ -293,7 +293,9 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
     uint64_t* full = bars; uint64_t* empty = full + NS; uint64_t* done = empty + NS;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int split = blockIdx.x % p.splits, b = blockIdx.x / p.splits;
+    // C > 128: blockIdx = ((b * splits) + split) * NACC + g, this CTA accumulates rows [g*128, g*128 + 128) of G only
+    const int gsel = blockIdx.x % G::NACC, cta = blockIdx.x / G::NACC;
+    const int split = cta % p.splits, b = cta / p.splits;
     const int t0 = split * p.tiles_per_split, t1 = min(p.tiles, t0 + p.tiles_per_split);
 
     if (warp == 0 && lane == 0) {
@@ -333,8 +335,8 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
             ptx::mbar_wait(&full[st], ph);
             ptx::tc_fence_after();
             const uint32_t base = ptx::smem_u32(smem + st * G::STAGE);
-#pragma unroll
-            for (int g = 0; g < G::NACC; ++g) {
+            {
+                const int g = gsel;
 #pragma unroll
                 for (int k = 0; k < G::TP / 16; ++k) {
 #pragma unroll
@@ -344,7 +346,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
                             if (pa + pb > 1) continue;
                             const uint32_t a_lo = mn_desc_lo(base + pa * G::PLANE + g * 2 * G::BOX + k * 16 * 128, G::BOX);
                             const uint32_t b_lo = mn_desc_lo(base + pb * G::PLANE + k * 16 * 128, G::BOX);
-                            if (leader) mma_ss(tmem_base + g * C_, a_lo, hi, b_lo, hi, idesc, (k | pa | pb) ? 1u : accumulate);
+                            if (leader) mma_ss(tmem_base, a_lo, hi, b_lo, hi, idesc, (k | pa | pb) ? 1u : accumulate);
                         }
                     }
                 }
@@ -362,16 +364,15 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
         ptx::mbar_wait(done, 0);
         ptx::tc_fence_after();
         const bool any = t1 > t0;
-        float* out = p.partial + (static_cast<size_t>(blockIdx.x) * G::NACC) * 128 * C_;
-#pragma unroll 1
-        for (int g = 0; g < G::NACC; ++g) {
-            if (g * 128 + m >= C_) continue;                         // C = 64: rows 64..127 are don't-care
+        // partial layout [b][split][half][128][C]: blockIdx.x enumerates (b, split, half) in exactly that order
+        float* out = p.partial + static_cast<size_t>(blockIdx.x) * 128 * C_;
+        if (m < C_) {                                                // C = 64: rows 64..127 are don't-care
 #pragma unroll 1
             for (int j = 0; j < C_ / 16; ++j) {
                 uint32_t r[16];
-                ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + g * C_ + j * 16, r);
+                ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + j * 16, r);
                 ptx::tmem_ld_wait();
-                float4* dst = reinterpret_cast<float4*>(out + (static_cast<size_t>(g) * 128 + m) * C_ + j * 16);
+                float4* dst = reinterpret_cast<float4*>(out + static_cast<size_t>(m) * C_ + j * 16);
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
                     dst[i] = any ? make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
@@ -559,14 +560,17 @@ GramPlan plan_gram(int B, int HW, int C) {
     GramPlan q;
     const int tp = C > 128 ? 64 : 128;
     q.tiles = (HW + tp - 1) / tp;
-    int splits = st_num_sms() / B; if (splits < 1) splits = 1; if (splits > q.tiles) splits = q.tiles;
+    // C = 256: a CTA owns ONE 128-row half of G (grid = B x splits x 2), so a 148-SM GPU runs 74 pixel splits x 2 halves:
+    // the fp32 partials (and what the finish launch reads back) halve -- 19 instead of 39 MB for a 128 x 128 tap
+    const int halves = C > 128 ? C / 128 : 1;
+    int splits = st_num_sms() / (B * halves); if (splits < 1) splits = 1; if (splits > q.tiles) splits = q.tiles;
     // Tuning override only.  Measured (tools/bench_gram.py, profiles/r01n_gram_split_sweep.txt): capping the split
     // to cut the C x C partial traffic (39 MB at C = 256) makes every tap SLOWER -- the kernel is bound by the
     // per-CTA tile loop (MMA issue + TMEM epilogue), not by the partials -- so the automatic plan uses every SM.
     if (g_gram_max_splits > 0 && splits > g_gram_max_splits) splits = g_gram_max_splits;
     q.tiles_per_split = (q.tiles + splits - 1) / splits;
     q.splits = (q.tiles + q.tiles_per_split - 1) / q.tiles_per_split;
-    q.grid = B * q.splits; q.nacc = C > 128 ? C / 128 : 1;
+    q.grid = B * q.splits * halves; q.nacc = halves;
     return q;
 }
 
@@ -615,7 +619,7 @@ WgradPlan plan_wgrad(int N, int H, int W, int CinPad, int kh, int kw) {
 bool gram_tc_eligible(int C, bool two_planes) { return (C == 64 || C == 128 || C == 256) && two_planes; }
 size_t gram_tc_workspace_bytes(int B, int HW, int C) {
     const GramPlan q = plan_gram(B, HW, C);
-    return static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
+    return static_cast<size_t>(q.grid) * 128 * C * sizeof(float);          // one 128-row block of partials per CTA
 }
 // blocks of the finish launch (= entries of each half of the style partials)
 int gram_tc_finish_blocks(int B, int HW, int C) {
@@ -629,7 +633,7 @@ int gram_tc_finish_blocks(int B, int HW, int C) {
 int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, float* Gm, void* workspace, size_t workspace_bytes,
                 const float* T, float* diff, float* loss, float* amax, float* style_part, int* ticket, cudaStream_t stream) {
     const GramPlan q = plan_gram(B, HW, C);
-    const size_t need = static_cast<size_t>(q.grid) * q.nacc * 128 * C * sizeof(float);
+    const size_t need = static_cast<size_t>(q.grid) * 128 * C * sizeof(float);
     ST_CHECK_ARG(workspace && workspace_bytes >= need, "gram_tc: workspace too small (%zu < %zu)", workspace_bytes, need);
     GramParams p;
     p.B = B; p.HW = HW; p.tiles = q.tiles; p.splits = q.splits; p.tiles_per_split = q.tiles_per_split;
