@@ -63,12 +63,14 @@ def _source_digest(name, hdr):
     return h.hexdigest()
 
 
+CONV_TC_SOURCES = ('conv_tc.cu', 'conv_tc_epilogue.cuh', 'ptx.cuh', 'common.cuh')
+
+
 def kernel_sources_digest():
-    """Digest of csrc/*.cu + the headers (no flags): ties a committed profile to the kernels it profiled
-    (bench.py reads profiles/conv_tc_traffic.json only when this matches)."""
+    """Digest of the sources of the dominant kernel (conv_tc: kernel, epilogue, PTX wrappers, common helpers): ties a
+    committed ncu capture to the kernel it profiled (bench.py reads profiles/conv_tc_traffic.json only when this matches)."""
     h = hashlib.sha256()
-    h.update(_headers_digest().encode())
-    for name in sorted(SOURCES):
+    for name in CONV_TC_SOURCES:
         with open(os.path.join(CSRC, name), 'rb') as f:
             h.update(name.encode())
             h.update(f.read())

@@ -6,8 +6,8 @@
 
 Reads the raw-page CSV (one row per profiled launch, a units row under the header), averages
 dram__bytes_read.sum + dram__bytes_write.sum over the 3x3 conv_tc launches and writes the entry
-``<workload>/<precision>`` of profiles/conv_tc_traffic.json together with the digest of csrc/ (bench.py reports the
-number only while the digest still matches the sources it runs).  Also writes a compact per-launch summary CSV next
+``<workload>/<precision>`` of profiles/conv_tc_traffic.json together with the digest of the kernel's sources
+(styletransfer_b200.build.CONV_TC_SOURCES; bench.py reports the number only while the digest still matches).  Also writes a compact per-launch summary CSV next
 to the input (kernel, duration, DRAM bytes, tensor-pipe activity, achieved occupancy)."""
 import csv
 import json
