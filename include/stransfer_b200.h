@@ -103,6 +103,20 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
               float* out_nchw, int Cnchw, float acc_mul, const float* acc_mul_slot, const float* add_mul_slot,
               void* stream);
 
+/* st_conv2d (stride 1, pad ks/2, no bias) whose addend is the gradient gy of the OUTPUT of the 2x2 max-pool that
+ * follows this tensor, [N][H/2][W/2][Cout_pad], routed on the fly: out(h, w, c) = conv [* (mask > 0)] +
+ * (route[n][h/2][w/2][c] == (h&1)*2 + (w&1) ? gy[n][h/2][w/2][c] * gy_mul_slot[1] : 0), route = the byte map of
+ * st_relu_maxpool2x2_fwd_idx (4 = window maximum <= 0; rows / columns beyond 2*(H/2), 2*(W/2) receive no gradient).
+ * It replaces st_relu_maxpool2x2_bwd_idx + st_conv2d(add=...) in the backward of a VGG block that ends in a pool and
+ * carries a style node: torch autograd's MaxPool2d / ReLU backward of the pieces reference network.py:257-314 builds,
+ * followed by the Gram backward of StyleLoss (network.py:92-108, :127-168).  Tensor-core path only: returns
+ * ST_ERR_UNSUPPORTED where st_conv2d would have taken another kernel (the caller then runs the two-launch form). */
+int st_conv2d_routed(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin,
+                     const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout_pad,
+                     const void* mask, const void* gy_hi, const void* gy_lo, int gy_planes, const unsigned char* route,
+                     void* out_hi, void* out_lo, int out_planes, float acc_mul, const float* acc_mul_slot, const float* gy_mul_slot,
+                     void* stream);
+
 /* First VGG layer (torchvision vgg19.features[0], 3 -> Cout channels, 3x3, zero padding 1;
  * run by StyleNetwork.run_through_pieces network.py:316-340) in exact fp32 on the CUDA cores:
  * x is the NCHW fp32 image (module boundary format), w [Cout][3][3][3] and bias [Cout] fp32;

@@ -18,9 +18,10 @@ long long g_st_launches = 0;
 
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
+bool conv_tc_outputs_ok(int ks, int Cout, bool relu_out, int out_planes);
 int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                 const float*, const bf16*, const bf16*, const bf16*, int, bf16*, bf16*, bf16*, bf16*, int, float*, int,
-                float, const float*, const float*, cudaStream_t);
+                float, const float*, const float*, const unsigned char*, cudaStream_t);
 int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*, int,
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, float, const float*, const float*, cudaStream_t);
@@ -120,12 +121,12 @@ int st_pack_conv_weight(const float* w, void* hi, void* lo, int planes, int Cout
     return ew_pack_weight(w, BF(hi), BF(lo), one_plane_if_no_lo(planes, lo), Cout, Cin, ks, rows_pad, cols_pad, mode, STRM(stream));
 }
 
-int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
+static int conv2d_impl(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
               const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows,
               int ks, int stride, int pad, int transposed, int Ho, int Wo, int Cout_pad, int Cbias,
               const float* bias, const void* mask, const void* add_hi, const void* add_lo, int add_planes,
               void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes, float* out_nchw, int Cnchw,
-              float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, void* stream) {
+              float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route, void* stream) {
     ST_CHECK_ARG(x_hi && w_hi, "st_conv2d: null input or weight");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0, "st_conv2d: empty shape");
     ST_CHECK_ARG(Cin % 8 == 0 && Cout_pad % 8 == 0, "st_conv2d: channel counts must be multiples of 8 (got %d, %d)", Cin, Cout_pad);
@@ -141,12 +142,18 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
     // an fp32 NCHW output (the image gradient) is taken by the 16-channel tile, unfused launches only
     const bool nchw_ok = !out_nchw || (Cout_pad == 16 && Cnchw <= 4 && !mask && !add_hi);
     const bool tc = g_conv_path == 0 && same_fmt && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && nchw_ok &&
-                    w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad) && (Cout_pad != 16 || out_nchw);
+                    w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad) && (Cout_pad != 16 || out_nchw) &&
+                    conv_tc_outputs_ok(ks, Cout_pad, relu_hi != nullptr, out_planes);
     g_last_conv_kernel = tc ? 1 : 3;
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), add_planes, BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw,
-                           acc_mul, acc_mul_slot, add_mul_slot, STRM(stream));
+                           acc_mul, acc_mul_slot, add_mul_slot, add_route, STRM(stream));
+    if (add_route) {
+        st_set_error("st_conv2d_routed: a routed addend needs the stride-1 tensor-core path (ks %d stride %d Cin %d Cout %d, same 16-bit format %d)",
+                     ks, stride, Cin, Cout_pad, int(same_fmt));
+        return ST_ERR_UNSUPPORTED;
+    }
     // run-time-geometry tcgen05 kernel: stride-2 3x3 (forward / transposed) and 32-channel K chunks
     const int xmode = transposed ? 2 : (stride == 2 ? 1 : 0);
     const bool tcx = g_conv_path == 0 && same_fmt && !up && pad == 1 && stride <= 2 && (!transposed || stride == 2) && !out_nchw && w_img_rows == 0 &&
@@ -181,6 +188,28 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
                         Ho, Wo, Cout_pad, Cout_pad, Cbias, bias, CBF(mask), CBF(add_hi), CBF(add_lo), add_planes,
                         BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw,
                         acc_mul, acc_mul_slot, add_mul_slot, STRM(stream));
+}
+
+int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin, int up,
+              const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows,
+              int ks, int stride, int pad, int transposed, int Ho, int Wo, int Cout_pad, int Cbias,
+              const float* bias, const void* mask, const void* add_hi, const void* add_lo, int add_planes,
+              void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes, float* out_nchw, int Cnchw,
+              float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, void* stream) {
+    return conv2d_impl(x_hi, x_lo, x_planes, N, H, W, Cin, up, w_hi, w_lo, w_planes, w_rows_total, w_img_rows, ks, stride, pad, transposed,
+                       Ho, Wo, Cout_pad, Cbias, bias, mask, add_hi, add_lo, add_planes, out_hi, out_lo, relu_hi, relu_lo, out_planes,
+                       out_nchw, Cnchw, acc_mul, acc_mul_slot, add_mul_slot, nullptr, stream);
+}
+int st_conv2d_routed(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin,
+                     const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout_pad,
+                     const void* mask, const void* gy_hi, const void* gy_lo, int gy_planes, const unsigned char* route,
+                     void* out_hi, void* out_lo, int out_planes, float acc_mul, const float* acc_mul_slot, const float* gy_mul_slot,
+                     void* stream) {
+    ST_CHECK_ARG(gy_hi && route && out_hi, "st_conv2d_routed: null pooled gradient, routing map or output");
+    ST_CHECK_ARG(H >= 2 && W >= 2, "st_conv2d_routed: the 2x2 pool needs H, W >= 2 (got %d x %d)", H, W);
+    return conv2d_impl(x_hi, x_lo, x_planes, N, H, W, Cin, 0, w_hi, w_lo, w_planes, w_rows_total, w_img_rows, ks, 1, ks / 2, 0,
+                       H, W, Cout_pad, 0, nullptr, mask, gy_hi, gy_lo, gy_planes, out_hi, out_lo, nullptr, nullptr, out_planes,
+                       nullptr, 0, acc_mul, acc_mul_slot, gy_mul_slot, route, stream);
 }
 
 int st_conv3x3_image_fwd(const float* x, const float* w, const float* bias, void* out_hi, void* out_lo,

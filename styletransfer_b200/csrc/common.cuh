@@ -121,7 +121,7 @@ __device__ __forceinline__ void split2h(float a, float b, uint32_t& hi, uint32_t
 }
 // sign test of a 16-bit float pair (bf16 or fp16 alike): value > 0  <=>  the bits are a positive non-zero integer
 __device__ __forceinline__ bool pos16_lo(uint32_t w) { return static_cast<int16_t>(w & 0xffffu) > 0; }
-__device__ __forceinline__ bool pos16_hi(uint32_t w) { return static_cast<int32_t>(w & 0xffff0000u) > 0; }
+__device__ __forceinline__ bool pos16_hi(uint32_t w) { return static_cast<int32_t>(w) > 0xffff; }     // one compare, no mask
 // one 16-bit-pair word of plane format f16 / bf16 -> two floats
 __device__ __forceinline__ float2 unpack16x2(uint32_t w, bool f16) {
     return f16 ? unpack_f16x2(w) : make_float2(bf16lo_to_f(w), bf16hi_to_f(w));

@@ -74,12 +74,16 @@ template <int KS, int BN, int PL, bool RES> struct Cfg {
     static constexpr int BAR_BYTES = 256 + BIAS_MAX * 4;    // barriers + TMEM slot, then the bias
     static constexpr int SMEM_MAX = 232448;                 // 227 KB opt-in limit
     static constexpr int TAPS = KS * KS;
-    static constexpr int NA = RES ? 3 : (KS == 1 && PL < 3) ? 4 : 2;
-    static constexpr int NB_FIT = (SMEM_MAX - 1024 - BAR_BYTES - NA * A_SLOT) / B_SLOT;
+    // 1x1 launches (the Gram backward) are bound by their epilogue: their stores go through a shared-memory tile per
+    // epilogue warp (tc_group, TS); the launcher sends outputs that path does not write (ReLU copy, fp32, third plane) elsewhere
+    static constexpr bool TS = KS == 1 && BN >= 64 && PL <= 2;
+    static constexpr int STG_BYTES = TS ? EPI_WARPS * TS_WARP_BYTES : 0;
+    static constexpr int NA = RES ? 3 : (KS == 1 && PL < 3) ? (BN == 128 ? 3 : 4) : 2;
+    static constexpr int NB_FIT = (SMEM_MAX - 1024 - BAR_BYTES - STG_BYTES - NA * A_SLOT) / B_SLOT;
     static constexpr int NB = RES ? TAPS : (NB_FIT > 9 ? 9 : NB_FIT);
     static_assert(NB >= 2 && NB <= NB_FIT, "weight ring does not fit");
     static_assert(!RES || (PL == 2 && KS == 3), "resident schedule: two planes, 3x3");
-    static constexpr int SMEM = 1024 + NA * A_SLOT + NB * B_SLOT + BAR_BYTES;
+    static constexpr int SMEM = 1024 + NA * A_SLOT + NB * B_SLOT + BAR_BYTES + STG_BYTES;
     // PL > 1: the a0*w0 products go to a "main" accumulator, all correction terms to a second
     // one, summed in fp32 by the epilogue.  The tensor core's accumulate truncates; keeping the
     // ~2^-8 smaller corrections out of the main chain divides that error by the pass count.
@@ -112,6 +116,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
     uint64_t* t_empty = t_full + 2;          // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
     float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+    uint8_t* ts_stage = reinterpret_cast<uint8_t*>(bars) + C::BAR_BYTES;       // C::STG_BYTES, 256-byte aligned
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     constexpr int pad = KS / 2;
@@ -144,9 +149,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         if (lane == 0) {
             int a = 0, b = 0; uint32_t aph = 0, bph = 0;
             for (int wk = blockIdx.x; wk < p.work; wk += gridDim.x) {
-                const int nb = wk % p.n_blocks; int t = wk / p.n_blocks;
-                const int tw = t % p.tiles_w; t /= p.tiles_w;
-                const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+                uint32_t t, unb, utw, uth, un;
+                p.fd_nb.divmod(static_cast<uint32_t>(wk), t, unb);
+                p.fd_tw.divmod(t, t, utw);
+                p.fd_th.divmod(t, un, uth);
+                const int nb = static_cast<int>(unb), tw = static_cast<int>(utw), th = static_cast<int>(uth), n = static_cast<int>(un);
                 const int h0 = th * C::TH - pad, w0 = tw * C::TW - pad;
                 const int wrow = n * p.w_img_rows + nb * BN;
                 if (RES) {
@@ -339,15 +346,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_constant
         ptx::reg_inc<REGS_EPILOGUE>();
         auto dec = [&](int wk, int m) {
             TcPix px;
-            px.nb = wk % p.n_blocks; int t = wk / p.n_blocks;
-            const int tw = t % p.tiles_w; t /= p.tiles_w;
-            const int th = t % p.tiles_h; const int n = t / p.tiles_h;
+            uint32_t t, unb, utw, uth, un;
+            p.fd_nb.divmod(static_cast<uint32_t>(wk), t, unb);
+            p.fd_tw.divmod(t, t, utw);
+            p.fd_th.divmod(t, un, uth);
+            px.nb = static_cast<int>(unb);
+            const int tw = static_cast<int>(utw), th = static_cast<int>(uth), n = static_cast<int>(un);
             const int h = th * C::TH + m / C::TW, w = tw * C::TW + m % C::TW;
             px.valid = (h < p.H) && (w < p.W);
             px.pix = (static_cast<size_t>(n) * p.H + h) * p.W + w;
             return px;
         };
-        tc_epilogue_warps<BN, C::NACC, FUSED ? 1 : 0>(p, bias_staged ? sbias : p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec);
+        tc_epilogue_warps<BN, C::NACC, FUSED ? 1 : 0, C::TS>(p, bias_staged ? sbias : p.bias, tmem_base, C::STAGE_COLS, t_full, t_empty, warp, lane, dec, ts_stage);
     }
 
     ptx::tc_fence_before();
@@ -464,6 +474,10 @@ int launch_planes(int planes, const CUtensorMap& ah, const CUtensorMap& al, cons
 
 }  // namespace
 
+// 1x1 launches of the tcgen05 path write `out` (<= 2 planes) only (Cfg::TS)
+bool conv_tc_outputs_ok(int ks, int Cout, bool relu_out, int out_planes) {
+    return ks != 1 || Cout < 64 || (!relu_out && pc_planes(out_planes) <= 2);
+}
 // Eligibility of the tcgen05 path (the generic kernel covers everything else).
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout) {
     return (ks == 3 || ks == 1) && stride == 1 && Cin % 64 == 0 && (Cout % 128 == 0 || Cout == 64 || Cout == 32 || (Cout == 16 && ks == 3));
@@ -474,8 +488,10 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
                 const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout,
                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo, int add_code,
                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_nchw, int Cnchw,
-                float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, cudaStream_t stream) {
+                float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route, cudaStream_t stream) {
     const int taps = ks * ks;
+    ST_CHECK_ARG(!add_route || (add_hi && pc_planes(add_code) <= 2), "conv_tc: a routed addend needs the pooled gradient in add_hi (<= 2 planes)");
+    ST_CHECK_ARG(!add_route || static_cast<long long>(N) * H * W < (1ll << 31), "conv_tc: a routed addend indexes pixels with 32 bits (N*H*W < 2^31)");
     ST_CHECK_ARG(!out_nchw || (Cnchw >= 1 && Cnchw <= 4 && !mask && !add_hi), "conv_tc: the NCHW output takes <= 4 channels and no mask / addend");
     ST_CHECK_ARG(pc_f16(x_planes) == pc_f16(w_planes), "conv_tc: activation and weight planes must have the same 16-bit format");
     // both operands are read at the same plane count (the lower one if they differ)
@@ -493,12 +509,14 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.N = N; p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
     p.tiles_h = (H + TH - 1) / TH; p.tiles_w = (W + TW - 1) / TW;
     p.n_blocks = Cout / BN; p.work = N * p.tiles_h * p.tiles_w * p.n_blocks;
+    p.fd_nb.init(p.n_blocks); p.fd_tw.init(p.tiles_w); p.fd_th.init(p.tiles_h); p.fd_W.init(W); p.fd_H.init(H);
     p.w_img_rows = w_img_rows; p.w_rows_total = w_rows_total;
     p.w_resident = (ks == 3 && BN <= 64 && planes == 2 && Cin == KCH && p.n_blocks == 1 && w_img_rows == 0) ? 1 : 0;
     p.fmt_bits = ptx::umma_fmt_bits(pc_f16(x_planes));
     p.out_planes = out_planes; p.add_code = add_code;
     p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
+    p.add_route = add_route; p.route_Ho = H / 2; p.route_Wo = W / 2;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = out_nchw; p.nchw_c = Cnchw; p.out_f32 = nullptr;
     p.dbg = g_conv_debug;

@@ -19,7 +19,22 @@ constexpr int NUM_THREADS = 384;
 constexpr int EPI_WARPS = 8, EPI_FIRST_WARP = 4;
 constexpr int REGS_CONTROL = 72, REGS_EPILOGUE = 216;      // 128 * 72 + 256 * 216 = 64512 <= 65536
 
+// n / d for 0 <= n < 2^31 and a run-time d >= 1 as a multiply-high, an add and a shift: the work-item decode of every tile
+// sat on the epilogue's critical path with three hardware-less 32-bit divisions (each a dependent chain of I2F / MUFU.RCP /
+// F2I / R2UR, a few hundred cycles of latency that the compiler also rematerialised inside the channel chunks).
+struct FastDiv {
+    uint32_t mul, sh, d;
+    void init(int div) {
+        d = static_cast<uint32_t>(div);
+        sh = 0; while ((1ull << sh) < d) ++sh;
+        mul = static_cast<uint32_t>((((1ull << sh) - d) << 32) / d + 1);
+    }
+    __device__ __forceinline__ uint32_t div(uint32_t n) const { return (__umulhi(n, mul) + n) >> sh; }
+    __device__ __forceinline__ void divmod(uint32_t n, uint32_t& q, uint32_t& r) const { q = div(n); r = n - q * d; }
+};
+
 struct ConvTcParams {
+    FastDiv fd_nb, fd_tw, fd_th, fd_W, fd_H;   // n_blocks, tiles_w, tiles_h, W, H
     int N, H, W, Cin, Cout;
     int tiles_h, tiles_w, n_blocks, work;
     int w_img_rows;                 // weight-row offset per image (0: shared weights)
@@ -35,6 +50,11 @@ struct ConvTcParams {
     const bf16* mask;               // [N,H,W,Cout] or null: acc *= (mask > 0); hi plane, bf16 or fp16 (sign test only)
     const bf16* add_hi;             // [N,H,W,Cout] or null: acc += add
     const bf16* add_lo;
+    // add_route != null: the addend is the gradient of a 2x2 max-pool's OUTPUT, [N,H/2,W/2,Cout], routed on the fly:
+    // pixel (h, w) takes channel c of pooled pixel (h/2, w/2) where the routing byte equals (h&1)*2 + (w&1), else 0
+    // (relu_maxpool_bwd_idx_kernel folded into this epilogue; bytes of 4 mark windows whose maximum was <= 0)
+    const unsigned char* add_route;
+    int route_Ho, route_Wo;
     bf16* out_hi; bf16* out_lo;     // result (pre-activation)
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
     float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
@@ -52,22 +72,42 @@ struct ConvTcParams {
 // per plane.
 // ---------------------------------------------------------------------------------------------
 struct TcPix { int nb; size_t pix; bool valid; };
-struct TcPre { uint32_t mk[2][8], ah[2][8], al[2][8]; };
+struct TcPre { uint32_t mk[2][8], ah[2][8], al[2][8], rt[2][4], pos; };
 
 template <int GCH>
 __device__ __forceinline__ void tc_prefetch(const ConvTcParams& p, TcPre& b, const TcPix& px, int ch0) {
     if (!px.valid) return;
+#ifdef ST_CONV_TRACE
+    if (p.dbg & 64) return;      // experiment: no mask / addend loads (the buffers keep whatever they held)
+#endif
     const size_t off = px.pix * p.Cout + ch0;
     if (p.mask) {
 #pragma unroll
         for (int v = 0; v < GCH / 16; ++v) ldg256(p.mask + off + v * 16, b.mk[v]);
     }
     if (p.add_hi) {
+        size_t aoff = off;
+        if (p.add_route) {
+            // 32-bit arithmetic (the launcher checks N*H*W < 2^31)
+            uint32_t t, w, n, h;
+            p.fd_W.divmod(static_cast<uint32_t>(px.pix), t, w);
+            p.fd_H.divmod(t, n, h);
+            const int oh = static_cast<int>(h >> 1), ow = static_cast<int>(w >> 1);
+            const bool in = oh < p.route_Ho && ow < p.route_Wo;         // odd sizes: the last row / column is not pooled
+            b.pos = ((h & 1) << 1) | (w & 1);
+            aoff = ((static_cast<size_t>(n) * p.route_Ho + (in ? oh : 0)) * p.route_Wo + (in ? ow : 0)) * p.Cout + ch0;
 #pragma unroll
-        for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_hi + off + v * 16, b.ah[v]);
+            for (int v = 0; v < GCH / 16; ++v) {
+                uint4 r = *reinterpret_cast<const uint4*>(p.add_route + aoff + v * 16);
+                if (!in) r = make_uint4(0x04040404u, 0x04040404u, 0x04040404u, 0x04040404u);   // routes nothing
+                b.rt[v][0] = r.x; b.rt[v][1] = r.y; b.rt[v][2] = r.z; b.rt[v][3] = r.w;
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_hi + aoff + v * 16, b.ah[v]);
         if (p.add_lo && pc_planes(p.add_code) >= 2) {
 #pragma unroll
-            for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_lo + off + v * 16, b.al[v]);
+            for (int v = 0; v < GCH / 16; ++v) ldg256(p.add_lo + aoff + v * 16, b.al[v]);
         }
     }
 }
@@ -89,15 +129,29 @@ __device__ __forceinline__ void tc_load_chunk(uint32_t taddr, int col, uint32_t 
     if (NACC > 2) ptx::tmem_ld16(taddr + 2 * BN + col, rd);
 }
 
+// eight 16-bit-pair words per plane -> 16 floats (hi [+ lo])
+template <bool F16, bool LO>
+__device__ __forceinline__ void tc_unpack_add(const uint32_t (&h)[8], const uint32_t (&l)[8], float (&a)[16]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float2 t = F16 ? unpack_f16x2(h[i]) : make_float2(bf16lo_to_f(h[i]), bf16hi_to_f(h[i]));
+        if (LO) {
+            const float2 u = F16 ? unpack_f16x2(l[i]) : make_float2(bf16lo_to_f(l[i]), bf16hi_to_f(l[i]));
+            t.x += u.x; t.y += u.y;
+        }
+        a[2 * i] = t.x; a[2 * i + 1] = t.y;
+    }
+}
+
 // one 16-channel chunk, accumulators already in registers: bias -> mask -> addend -> stores.
 // bias: [Cout] in shared memory (conv_tc stages it once per CTA) or global, or null.
 template <int BN, int NACC, bool FUSED>
-__device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPix& px, int col,
-                                                 const uint32_t (&r)[16], const uint32_t (&rc)[16], const uint32_t (&rd)[16],
-                                                 const uint32_t* mk, const uint32_t* ah, const uint32_t* al) {
+__device__ __forceinline__ void tc_chunk_values(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPix& px, int col,
+                                                const uint32_t (&r)[16], const uint32_t (&rc)[16], const uint32_t (&rd)[16],
+                                                const uint32_t* mk, const uint32_t* ah, const uint32_t* al,
+                                                const uint32_t* rt, uint32_t pos, float (&v)[16]) {
     const int ch = px.nb * BN + col;
     const size_t o = px.pix * p.Cout + ch;
-    float v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         v[i] = __uint_as_float(r[i]);
@@ -125,14 +179,29 @@ __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const Tc
         }
         if (p.add_hi) {
             const bool lo = p.add_lo && pc_planes(p.add_code) >= 2, f16 = pc_f16(p.add_code);
-            float a[16];
+            uint32_t h[8], l[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                float2 t = unpack16x2(ah[i], f16);
-                if (lo) { const float2 u = unpack16x2(al[i], f16); t.x += u.x; t.y += u.y; }
-                a[2 * i] = t.x; a[2 * i + 1] = t.y;
+            for (int i = 0; i < 8; ++i) { h[i] = ah[i]; l[i] = lo ? al[i] : 0u; }
+            if (p.add_route) {
+                // routing bytes are 0..4, pos 0..3: a byte of (rt ^ pos4) is 0 exactly where the gradient goes.  Byte-wise
+                // zero test without carries (bytes <= 7), then PRMT replicates each byte's top bit over a 16-bit lane:
+                // the words of both planes are masked BEFORE they are unpacked (5 + 4 instructions per 4 channels)
+                const uint32_t pos4 = pos * 0x01010101u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t e = ~((rt[j] ^ pos4) + 0x7f7f7f7fu) & 0x80808080u;
+                    const uint32_t m0 = ptx::prmt(e, 0u, 0x9988u), m1 = ptx::prmt(e, 0u, 0xbbaau);    // selector bit 3: replicate the byte's sign
+                    h[2 * j] &= m0; h[2 * j + 1] &= m1; l[2 * j] &= m0; l[2 * j + 1] &= m1;
+                }
             }
-            const bf16* p2 = lo ? third_plane(p.add_hi, p.add_lo, p.add_code) : nullptr;
+            float a[16];
+            // one warp-uniform branch per chunk instead of a predicated copy of both conversions per element
+            if (f16) {
+                if (lo) tc_unpack_add<true, true>(h, l, a); else tc_unpack_add<true, false>(h, l, a);
+            } else {
+                if (lo) tc_unpack_add<false, true>(h, l, a); else tc_unpack_add<false, false>(h, l, a);
+            }
+            const bf16* p2 = (lo && !p.add_route) ? third_plane(p.add_hi, p.add_lo, p.add_code) : nullptr;
             if (p2) {
                 uint32_t w[8];
                 ldg256(p2 + o, w);
@@ -143,6 +212,26 @@ __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const Tc
             for (int i = 0; i < 16; ++i) v[i] = fmaf(a[i], mul.add, v[i]);
         }
     }
+}
+
+template <int BN, int NACC, bool FUSED>
+__device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPix& px, int col,
+                                                 const uint32_t (&r)[16], const uint32_t (&rc)[16], const uint32_t (&rd)[16],
+                                                 const uint32_t* mk, const uint32_t* ah, const uint32_t* al,
+                                                 const uint32_t* rt = nullptr, uint32_t pos = 0) {
+    const int ch = px.nb * BN + col;
+    const size_t o = px.pix * p.Cout + ch;
+    float v[16];
+    tc_chunk_values<BN, NACC, FUSED>(p, mul, bias, px, col, r, rc, rd, mk, ah, al, rt, pos, v);
+#ifdef ST_CONV_TRACE
+    if (p.dbg & 32) {      // experiment: all the arithmetic of the split, (practically) no store
+        uint32_t hw[8], mw[8], x = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { split2h(v[2 * i], v[2 * i + 1], hw[i], mw[i]); x ^= hw[i] ^ mw[i]; }
+        if (x == 0x9e3779b9u) stg256(p.out_hi + o, hw);
+        return;
+    }
+#endif
     if (p.out_hi) store16p(p.out_hi, p.out_lo, p.out_planes, o, v);
     if (!FUSED && p.out_f32) {
         uint32_t w0[8], w1[8];
@@ -170,26 +259,85 @@ __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const Tc
 // the global stores of a tile run while the tensor core already fills the stage again.  (The epilogue is latency
 // bound: 8 warps, long dependent chains; per-chunk load -> wait -> store sequences held a stage for the whole epilogue
 // and the tensor pipe idled 40 % of the time, profiles/r02o_conv_tc_ncu_full_summary.csv.)
-template <int BN, int NACC, int GCH, bool FUSED, class EndTile>
+// TS (transposed stores): the group's 32 channels x 2 planes of the warp's 32 pixels go through a 4 KB shared-memory tile
+// of the warp and leave as 16-byte stores whose lanes run along the CHANNELS of a pixel (4 lanes = 64 contiguous bytes,
+// 8 pixels per instruction) instead of one 32-byte sector per lane in 32 different 128-byte lines: the LSU spends about
+// two cycles per line an instruction touches (tools/probe_store_pattern.cu: 4.6 TB/s for the one-pixel-per-lane pattern
+// with nothing else going on), which made the 1x1 launches store-issue bound.  Rows of the tile are 64 bytes, the
+// 16-byte pieces of a row are XOR-swizzled with bits 1..2 of the row so that writes (8 rows, one piece) and reads
+// (2 rows, 4 pieces) both cover all 32 banks.
+constexpr int TS_WARP_BYTES = 4096;
+template <int BN, int NACC, int GCH, bool FUSED, bool TS, class EndTile>
 __device__ __forceinline__ void tc_group(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPre* pre, uint32_t taddr,
-                                         const TcPix& px, int col0, bool last, const EndTile& end_tile) {
+                                         const TcPix& px, int col0, bool last, const EndTile& end_tile, uint8_t* stage = nullptr) {
     constexpr int NCH = GCH / 16;
     uint32_t r[NCH][16], rc[NCH][16], rd[NCH][16];
 #pragma unroll
     for (int j = 0; j < NCH; ++j) tc_load_chunk<BN, NACC>(taddr, col0 + j * 16, r[j], rc[j], rd[j]);
     ptx::tmem_ld_wait();
     if (last) end_tile();
-    if (!px.valid || (p.dbg & 1)) return;
+    if constexpr (!TS) {
+        if (!px.valid || (p.dbg & 1)) return;
 #pragma unroll
-    for (int j = 0; j < NCH; ++j)
-        tc_chunk_compute<BN, NACC, FUSED>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j],
-                                          FUSED ? pre->mk[j] : nullptr, FUSED ? pre->ah[j] : nullptr, FUSED ? pre->al[j] : nullptr);
+        for (int j = 0; j < NCH; ++j)
+            tc_chunk_compute<BN, NACC, FUSED>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j],
+                                              FUSED ? pre->mk[j] : nullptr, FUSED ? pre->ah[j] : nullptr, FUSED ? pre->al[j] : nullptr,
+                                              FUSED ? pre->rt[j] : nullptr, FUSED ? pre->pos : 0u);
+    } else {
+        static_assert(GCH == 32, "transposed stores: 32-channel groups");
+        const int lane = threadIdx.x & 31;
+        const bool f16 = pc_f16(p.out_planes), two = p.out_lo != nullptr;
+        uint32_t hw[NCH][8], mw[NCH][8];
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { hw[j][i] = 0u; mw[j][i] = 0u; }
+            if (px.valid) {
+                float v[16];
+                tc_chunk_values<BN, NACC, FUSED>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j],
+                                                 FUSED ? pre->mk[j] : nullptr, FUSED ? pre->ah[j] : nullptr, FUSED ? pre->al[j] : nullptr,
+                                                 FUSED ? pre->rt[j] : nullptr, FUSED ? pre->pos : 0u, v);
+                if (f16) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) split2h(v[2 * i], v[2 * i + 1], hw[j][i], mw[j][i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) split2(v[2 * i], v[2 * i + 1], hw[j][i], mw[j][i]);
+                }
+            }
+        }
+        const int wsw = (lane >> 1) & 3;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            uint8_t* dst = stage + lane * 64 + ((c ^ wsw) << 4);
+            *reinterpret_cast<uint4*>(dst) = make_uint4(hw[c >> 1][(c & 1) * 4], hw[c >> 1][(c & 1) * 4 + 1], hw[c >> 1][(c & 1) * 4 + 2], hw[c >> 1][(c & 1) * 4 + 3]);
+            if (two) *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(mw[c >> 1][(c & 1) * 4], mw[c >> 1][(c & 1) * 4 + 1], mw[c >> 1][(c & 1) * 4 + 2], mw[c >> 1][(c & 1) * 4 + 3]);
+        }
+        __syncwarp();
+        const unsigned vm = __ballot_sync(0xffffffffu, px.valid);
+        const unsigned long long obase = static_cast<unsigned long long>(px.pix) * p.Cout + px.nb * BN + col0;
+        const int c = lane & 3;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int prow = 8 * j + (lane >> 2);
+            const unsigned long long o = __shfl_sync(0xffffffffu, obase, prow) + c * 8;
+            const uint8_t* src = stage + prow * 64 + ((c ^ ((prow >> 1) & 3)) << 4);
+            if (((vm >> prow) & 1u) && !(p.dbg & 1)) {
+                *reinterpret_cast<uint4*>(p.out_hi + o) = *reinterpret_cast<const uint4*>(src);
+                if (two) *reinterpret_cast<uint4*>(p.out_lo + o) = *reinterpret_cast<const uint4*>(src + 2048);
+            }
+        }
+        __syncwarp();
+    }
 }
 
 // dec(wk, m) -> TcPix of accumulator row m of work item wk.  bias: see tc_chunk_compute.
-template <int BN, int NACC, int FMODE = -1, class Decode>
+// TS: transposed stores (tc_group); ts_stage: 8 x TS_WARP_BYTES of shared memory, 16-byte aligned
+template <int BN, int NACC, int FMODE = -1, bool TS = false, class Decode>
 __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const float* bias, uint32_t tmem_base, int stage_cols,
-                                                  uint64_t* t_full, uint64_t* t_empty, int warp, int lane, const Decode& dec) {
+                                                  uint64_t* t_full, uint64_t* t_empty, int warp, int lane, const Decode& dec,
+                                                  uint8_t* ts_stage = nullptr) {
+    uint8_t* stage = TS ? ts_stage + (warp - EPI_FIRST_WARP) * TS_WARP_BYTES : nullptr;
     constexpr int CW = BN >= 32 ? BN / 2 : BN;            // columns per warp
     constexpr int GCH = CW < 32 ? CW : 32;                // channels per register buffer
     constexpr int NGRP = CW / GCH;
@@ -216,7 +364,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             if (active) {
 #pragma unroll
                 for (int g = 0; g < NGRP; ++g)
-                    tc_group<BN, NACC, GCH, false>(p, mul, bias, nullptr, taddr_of(it), px, col_base + g * GCH, g == NGRP - 1, end_tile);
+                    tc_group<BN, NACC, GCH, false, TS>(p, mul, bias, nullptr, taddr_of(it), px, col_base + g * GCH, g == NGRP - 1, end_tile, stage);
             } else {
                 end_tile();
             }
@@ -238,9 +386,9 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
             auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
                                     if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
-            tc_group<BN, NACC, GCH, true>(p, mul, bias, &A, taddr_of(it), px, col_base, false, end_tile);
+            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, false, end_tile, stage);
             if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
-            tc_group<BN, NACC, GCH, true>(p, mul, bias, &B, taddr_of(it), px, col_base + GCH, true, end_tile);
+            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &B, taddr_of(it), px, col_base + GCH, true, end_tile, stage);
             if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
             if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
@@ -250,12 +398,16 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
         if (wk0 < p.work) { const TcPix px = dec(wk0, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
         if (wk1 < p.work) { const TcPix px = dec(wk1, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
         int it = 0;
-        auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]); };
+        const bool tracer = warp == EPI_FIRST_WARP && lane == 0;
+        auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
+                                if (tracer) TC_TRACE(2, it, 1); };
         while (wk0 < p.work) {
             {
                 const TcPix px = dec(wk0, m);
                 begin_tile(it);
-                tc_group<BN, NACC, GCH, true>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile);
+                if (tracer) TC_TRACE(2, it, 0);
+                tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile, stage);
+                if (tracer) TC_TRACE(2, it, 2);
                 ++it;
             }
             const int wk2 = wk0 + 2 * step;
@@ -264,7 +416,9 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             {
                 const TcPix px = dec(wk1, m);
                 begin_tile(it);
-                tc_group<BN, NACC, GCH, true>(p, mul, bias, &B, taddr_of(it), px, col_base, true, end_tile);
+                if (tracer) TC_TRACE(2, it, 0);
+                tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &B, taddr_of(it), px, col_base, true, end_tile, stage);
+                if (tracer) TC_TRACE(2, it, 2);
                 ++it;
             }
             const int wk3 = wk1 + 2 * step;

@@ -58,10 +58,13 @@ struct XWork { int cls, nb, tw, th, n; };
 // classes are the slowest index (heaviest first), so every CTA of the persistent grid gets the same mix
 __device__ __forceinline__ XWork x_decode(int wk, const ConvTcParams& p, int per_cls) {
     XWork w;
-    w.cls = wk / per_cls; int t = wk - w.cls * per_cls;
-    w.nb = t % p.n_blocks; t /= p.n_blocks;
-    w.tw = t % p.tiles_w; t /= p.tiles_w;
-    w.th = t % p.tiles_h; w.n = t / p.tiles_h;
+    // cls < 4: compare instead of dividing by the run-time per_cls
+    w.cls = (wk >= per_cls) + (wk >= 2 * per_cls) + (wk >= 3 * per_cls);
+    uint32_t t = static_cast<uint32_t>(wk - w.cls * per_cls), nb, tw, th, n;
+    p.fd_nb.divmod(t, t, nb);
+    p.fd_tw.divmod(t, t, tw);
+    p.fd_th.divmod(t, n, th);
+    w.nb = static_cast<int>(nb); w.tw = static_cast<int>(tw); w.th = static_cast<int>(th); w.n = static_cast<int>(n);
     return w;
 }
 
@@ -319,6 +322,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.tiles_h = (IH + TILE_H - 1) / TILE_H; p.tiles_w = (IW + TILE_W - 1) / TILE_W;
     p.n_blocks = Cout / BN;
     g.per_cls = N * p.tiles_h * p.tiles_w * p.n_blocks; p.work = g.per_cls * g.ncls;
+    p.fd_nb.init(p.n_blocks); p.fd_tw.init(p.tiles_w); p.fd_th.init(p.tiles_h); p.fd_W.init(p.W > 0 ? p.W : 1); p.fd_H.init(p.H > 0 ? p.H : 1);
     p.w_img_rows = 0; p.w_rows_total = w_rows_total;
     const int xp = pc_planes(x_planes), wp = pc_planes(w_planes);
     const int a_planes = x_lo ? (xp >= 3 ? 3 : (xp >= 2 ? 2 : 1)) : 1;
@@ -331,6 +335,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32; p.dbg = 0;
+    p.add_route = nullptr; p.route_Ho = p.route_Wo = 0;
 
     CUtensorMap ah, al, wh, wl;
     const int ps = mode == 1 ? 2 : 1;

@@ -58,6 +58,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 // Non-blocking phase test.  The MMA issuer polls the barrier it will need NEXT before it issues a group of MMAs: an
 // mbarrier operation that sits between two groups costs 200 - 600 cycles under the epilogue's store traffic (same MIO
 // queue) and the tensor pipe drains meanwhile (profiles/r02u_conv_tc_tile_timeline.txt).
+// prmt.b32 with the full selector (bit 3 of a nibble replicates the sign of the selected byte; __byte_perm drops that bit)
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
 __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
     uint32_t done;
     asm volatile(

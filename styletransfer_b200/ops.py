@@ -238,6 +238,31 @@ def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
     return out, relu, nchw
 
 
+def conv2d_routed(x, w_ptrs, w_img_rows, gy, idx, mask=None):
+    """out = x * D (per-image 1x1 weights, the Gram backward) [* (mask > 0)] + the gradient ``gy`` of the OUTPUT of the
+    2x2 max-pool that follows, routed through the byte map ``idx`` of relu_maxpool_fwd(want_idx=True): the MaxPool2d and
+    ReLU backward of torch autograd (reference network.py:257-314 builds the VGG pieces they belong to) folded into the
+    epilogue of the tensor-core launch.  Returns None when this launch cannot take the tensor-core path (the caller then
+    runs relu_maxpool_bwd + conv2d)."""
+    L = _lib.lib()
+    _bf16_grad(gy)
+    w_hi, w_lo, rows_total, ks, cols, w_code, w_slot = w_ptrs
+    assert cols == x.C and ks == 1 and tuple(idx.shape) == (x.N, x.H // 2, x.W // 2, w_img_rows) and gy.shape == tuple(idx.shape)
+    assert not (x.slot is not None and w_slot is not None), 'at most one scaled operand'
+    x_code = x.read_code(bwd_planes())
+    if (x_code & 16) != (w_code & 16):
+        return None
+    acc_slot = x.slot if x.slot is not None else w_slot
+    out = Split(x.N, x.H, x.W, w_img_rows, x.buf.device, planes=bwd_planes(), fmt=0)
+    rc = L.st_conv2d_routed(x.hi, x.lo if (x_code & 15) > 1 else None, x_code, x.N, x.H, x.W, x.C, w_hi, w_lo, w_code, rows_total, w_img_rows, ks,
+                            w_img_rows, mask.hi if mask else None, gy.hi, gy.lo, gy.code, idx.data_ptr(), out.hi, out.lo, bwd_planes(),
+                            1.0, _p(acc_slot), gy.slot_ptr, _stream())
+    if rc == -3:      # ST_ERR_UNSUPPORTED: forced generic path, channel counts outside the tensor-core kernel
+        return None
+    _lib.check(rc, 'st_conv2d_routed')
+    return out
+
+
 def conv_image_fwd(x, w, bias, want_out=True, want_relu=False):
     """VGG conv1_1 on the NCHW fp32 image (exact fp32, CUDA cores) -> (tap Split, relu Split)."""
     _require_cuda(x, 'conv_image_fwd')

@@ -39,6 +39,9 @@ PREFIX = [(3, 64, False), (64, 64, False), (64, 128, True), (128, 128, False), (
 KINDS = {'Conv2d': 'C', 'ReLU': 'R', 'MaxPool2d': 'P'}
 # backward-data of conv1_1: tcgen05 16-channel tile (default) or the exact-fp32 CUDA-core kernel
 IMAGE_GRAD_TC = True
+# MaxPool2d + ReLU backward of a block folded into the epilogue of the block's first Gram-backward launch
+# (ops.conv2d_routed); STRANSFER_FUSE_POOL_ROUTE=0 keeps the separate relu_maxpool_bwd launch
+FUSE_POOL_ROUTE = os.environ.get('STRANSFER_FUSE_POOL_ROUTE', '1') != '0'
 
 
 def parse_layer(name):
@@ -260,9 +263,10 @@ class _VGGLossFn(torch.autograd.Function):
         seeds = ops.style_seed_multi([(diffs[i][0], diffs[i][1], vals[p].H * vals[p].W, gl[i:i + 1], vals[p].fmt)
                                       for i, (p, _) in enumerate(spec.style)]) if n_style else []
 
-        def node_grads(pt, acc=None):
+        def node_grads(pt, acc=None, skip=None):
             """acc + the loss gradients of the nodes at ``pt`` with respect to the value at ``pt`` -- for 'R' points
-            with respect to the pre-ReLU tap (relu' applied).  Returns ``acc`` unchanged when no node sits there."""
+            with respect to the pre-ReLU tap (relu' applied).  Returns ``acc`` unchanged when no node sits there.
+            ``skip``: index of a style node whose gradient ``acc`` already holds."""
             for i, (p, target) in enumerate(spec.content):
                 if p == pt:
                     t, relu = mse_operand(pt, vals, taps)
@@ -275,7 +279,7 @@ class _VGGLossFn(torch.autograd.Function):
                     j = n_style + n_content + i
                     acc = ops.mse_bwd(t, target, gl[j:j + 1], 4.0 / (n * n), out=acc, relu=relu, mul=ctx.feat_mse[i])
             for i, (p, _) in enumerate(spec.style):
-                if p == pt:
+                if p == pt and i != skip:
                     # dF = F * D  (Gram backward, per-image 1x1 conv on the tensor cores); the per-image weights D take
                     # the plane format of the operand F they multiply (one format per tensor-core product)
                     f = vals[pt]
@@ -286,21 +290,37 @@ class _VGGLossFn(torch.autograd.Function):
         def tap_node_grads(k):
             return node_grads(('R', k), node_grads(('C', k)))
 
+        def routed_tap_grads(k, gy, idx):
+            """Gradient of the pre-ReLU tap of a block that ends in a max-pool: the pool's output gradient ``gy`` routed
+            through the pool and the ReLU, + the block's node gradients -- with the routing done by the epilogue of the
+            first Gram-backward launch of the block (one pass over the tap-sized gradient instead of three).  None when
+            the block has no style node or that launch cannot take the tensor-core kernel."""
+            if idx is None or not FUSE_POOL_ROUTE:
+                return None
+            first = next((i for i, (p, _) in enumerate(spec.style) if p in (('C', k), ('R', k))), None)
+            if first is None:
+                return None
+            pt = spec.style[first][0]
+            acc = ops.conv2d_routed(vals[pt], seeds[first][1], vals[pt].C, gy, idx, mask=taps[k] if pt[0] == 'R' else None)
+            if acc is None:
+                return None
+            return node_grads(('R', k), node_grads(('C', k), acc, skip=first), skip=first)
+
         g_out = None          # gradient of the OUTPUT of block k (what conv k + 1 reads), node gradients of MaxPool2d_k included
         g_tap = None          # gradient of the pre-ReLU output of conv k when the launch below has already produced it
         for k in range(K, 0, -1):
             _, _, pool = BLOCKS[k - 1]
             if g_tap is None:
-                add = tap_node_grads(k)
+                gy = None
                 if pool and (g_out is not None or ('P', k) in vals):
                     gy = g_out if g_out is not None else node_grads(('P', k))
-                    if gy is None:
-                        g_tap = add
-                    else:
+                if gy is not None:
+                    g_tap = routed_tap_grads(k, gy, ctx.pool_idx.get(k))
+                    if g_tap is None:
                         # route through the max-pool, relu', + the node gradients of this block, in one kernel
-                        g_tap = ops.relu_maxpool_bwd(taps[k], gy, add=add, idx=ctx.pool_idx.get(k))
+                        g_tap = ops.relu_maxpool_bwd(taps[k], gy, add=tap_node_grads(k), idx=ctx.pool_idx.get(k))
                 else:
-                    g_tap = add                       # top block: the node gradients are the whole gradient
+                    g_tap = tap_node_grads(k)         # top block: the node gradients are the whole gradient
                 if g_tap is None:
                     raise ops._lib.StransferError('internal: no gradient reaches the top of the loss network')
             if k == 1:

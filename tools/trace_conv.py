@@ -25,14 +25,21 @@ def main():
         run = lambda: ops.conv2d(x, pw, b, want_out=True, want_relu=True)
     else:
         # Gram backward dF = F * D of a 128-channel tap at 256x256 with an addend (general schedule, 1x1, fused epilogue)
-        C, S = (128, 256) if case == 'gram128' else (64, 512)
+        # cases gram64 / gram128 / gram256; a trailing 'n' drops the addend (plain epilogue), a trailing 'r' makes it the
+        # routed gradient of the 2x2 max-pool behind the tap (ops.conv2d_routed)
+        C = int(case[4:].rstrip('nr'))
+        S = 512 * 64 // C
         f = ops.from_nchw(g((1, C, S, S), 1))
         diff = g((1, C, C), 2, 1e-3)
         amax = diff.abs().max().reshape(1)
         gw = torch.ones(1, device='cuda')
         keep, wp = ops.style_seed(diff, amax, S * S, gw, f.fmt)
         add = ops.from_nchw(g((1, C, S, S), 3), planes=2)
-        run = lambda: ops.conv2d(f, None, w_ptrs=wp, w_img_rows=C, add=add)
+        run = lambda: ops.conv2d(f, None, w_ptrs=wp, w_img_rows=C, add=None if case.endswith('n') else add)
+        if case.endswith('r'):
+            _, idx = ops.relu_maxpool_fwd(f, want_idx=True)
+            gy = ops.from_nchw(g((1, C, S // 2, S // 2), 4), planes=2, fmt=0)
+            run = lambda: ops.conv2d_routed(f, wp, C, gy, idx)
     for _ in range(3):
         run()
     torch.cuda.synchronize()
