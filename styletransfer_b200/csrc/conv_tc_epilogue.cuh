@@ -94,12 +94,13 @@ __device__ __forceinline__ void tc_prefetch(const ConvTcParams& p, TcPre& b, con
             p.fd_H.divmod(t, n, h);
             const int oh = static_cast<int>(h >> 1), ow = static_cast<int>(w >> 1);
             const bool in = oh < p.route_Ho && ow < p.route_Wo;         // odd sizes: the last row / column is not pooled
-            b.pos = ((h & 1) << 1) | (w & 1);
+            // unpooled border: position 5 matches no routing byte (0..4) -- decided here without touching the loaded bytes,
+            // so nothing in this function waits for a load
+            b.pos = in ? (((h & 1) << 1) | (w & 1)) : 5u;
             aoff = ((static_cast<size_t>(n) * p.route_Ho + (in ? oh : 0)) * p.route_Wo + (in ? ow : 0)) * p.Cout + ch0;
 #pragma unroll
             for (int v = 0; v < GCH / 16; ++v) {
-                uint4 r = *reinterpret_cast<const uint4*>(p.add_route + aoff + v * 16);
-                if (!in) r = make_uint4(0x04040404u, 0x04040404u, 0x04040404u, 0x04040404u);   // routes nothing
+                const uint4 r = *reinterpret_cast<const uint4*>(p.add_route + aoff + v * 16);
                 b.rt[v][0] = r.x; b.rt[v][1] = r.y; b.rt[v][2] = r.z; b.rt[v][3] = r.w;
             }
         }
@@ -177,13 +178,18 @@ __device__ __forceinline__ void tc_chunk_values(const ConvTcParams& p, const TcM
                 v[2 * i + 1] = pos16_hi(mk[i]) ? v[2 * i + 1] : 0.f;
             }
         }
-        if (p.add_hi) {
+#ifdef ST_CONV_TRACE
+        const bool dbg_no_add = p.dbg & 256, dbg_no_route = p.dbg & 128;
+#else
+        constexpr bool dbg_no_add = false, dbg_no_route = false;
+#endif
+        if (p.add_hi && !dbg_no_add) {
             const bool lo = p.add_lo && pc_planes(p.add_code) >= 2, f16 = pc_f16(p.add_code);
             uint32_t h[8], l[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) { h[i] = ah[i]; l[i] = lo ? al[i] : 0u; }
-            if (p.add_route) {
-                // routing bytes are 0..4, pos 0..3: a byte of (rt ^ pos4) is 0 exactly where the gradient goes.  Byte-wise
+            if (p.add_route && !dbg_no_route) {
+                // routing bytes are 0..4, pos 0..3 (5: no gradient): a byte of (rt ^ pos4) is 0 exactly where the gradient goes.  Byte-wise
                 // zero test without carries (bytes <= 7), then PRMT replicates each byte's top bit over a 16-bit lane:
                 // the words of both planes are masked BEFORE they are unpacked (5 + 4 instructions per 4 channels)
                 const uint32_t pos4 = pos * 0x01010101u;
@@ -393,37 +399,24 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
     } else {
-        // buffers alternate between tiles: A holds tile k, B tile k + 1; tile k + 2 is fetched into A after tile k
-        int wk0 = blockIdx.x, wk1 = wk0 + step;
-        if (wk0 < p.work) { const TcPix px = dec(wk0, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
-        if (wk1 < p.work) { const TcPix px = dec(wk1, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
+        // B receives the next tile's mask / addend at the START of a tile (before its arithmetic and stores enter the LSU
+        // queue) and is copied into A when that tile begins -- one rolled loop: the epilogue runs each instruction once
+        // per tile, so its speed is set by instruction fetch, and alternating two buffers over an unrolled pair of tiles
+        // doubled the straight-line code.
         int it = 0;
-        const bool tracer = warp == EPI_FIRST_WARP && lane == 0;
         auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
-                                if (tracer) TC_TRACE(2, it, 1); };
-        while (wk0 < p.work) {
-            {
-                const TcPix px = dec(wk0, m);
-                begin_tile(it);
-                if (tracer) TC_TRACE(2, it, 0);
-                tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile, stage);
-                if (tracer) TC_TRACE(2, it, 2);
-                ++it;
-            }
-            const int wk2 = wk0 + 2 * step;
-            if (wk2 < p.work) { const TcPix px = dec(wk2, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); }
-            if (wk1 >= p.work) break;
-            {
-                const TcPix px = dec(wk1, m);
-                begin_tile(it);
-                if (tracer) TC_TRACE(2, it, 0);
-                tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &B, taddr_of(it), px, col_base, true, end_tile, stage);
-                if (tracer) TC_TRACE(2, it, 2);
-                ++it;
-            }
-            const int wk3 = wk1 + 2 * step;
-            if (wk3 < p.work) { const TcPix px = dec(wk3, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
-            wk0 = wk2; wk1 = wk3;
+                                if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
+        int wk = blockIdx.x;
+        if (wk < p.work) { const TcPix px = dec(wk, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
+#pragma unroll 1
+        for (; wk < p.work; wk += step, ++it) {
+            const TcPix px = dec(wk, m);
+            A = B;
+            if (wk + step < p.work) { const TcPix nx = dec(wk + step, m); tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base); }
+            begin_tile(it);
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
+            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile, stage);
+            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
     }
 }
