@@ -368,7 +368,7 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
             auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
                                     if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
             if (active) {
-#pragma unroll
+#pragma unroll 1
                 for (int g = 0; g < NGRP; ++g)
                     tc_group<BN, NACC, GCH, false, TS>(p, mul, bias, nullptr, taddr_of(it), px, col_base + g * GCH, g == NGRP - 1, end_tile, stage);
             } else {
@@ -378,46 +378,34 @@ __device__ __forceinline__ void tc_epilogue_warps(const ConvTcParams& p, const f
         }
         return;
     }
+    // One rolled loop over (tile, 32-channel group) steps.  B receives the NEXT step's mask / addend at the start of a step
+    // (before this step's arithmetic and stores enter the LSU queue) and is copied into A when that step begins.  The
+    // epilogue runs each instruction once per tile, so its speed is set by instruction fetch: unrolled pairs of tiles /
+    // groups with alternating buffers doubled the straight-line code of the loop and cost more than the copy.
     TcPre A, B;
-    if (NGRP == 2) {
-        // buffer A = first 32 channels, B = second 32 channels; each is refilled for the next tile right after use
-        int wk = blockIdx.x;
-        if (wk < p.work) { const TcPix px = dec(wk, m); tc_prefetch<GCH>(p, A, px, px.nb * BN + col_base); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base + GCH); }
-        for (int it = 0; wk < p.work; wk += step, ++it) {
-            const TcPix px = dec(wk, m);
-            const bool more = wk + step < p.work;
-            TcPix nx = px;
-            if (more) nx = dec(wk + step, m);
-            begin_tile(it);
-            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
-            auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
-                                    if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
-            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, false, end_tile, stage);
-            if (more) tc_prefetch<GCH>(p, A, nx, nx.nb * BN + col_base);
-            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &B, taddr_of(it), px, col_base + GCH, true, end_tile, stage);
-            if (more) tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + GCH);
-            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
-        }
-    } else {
-        // B receives the next tile's mask / addend at the START of a tile (before its arithmetic and stores enter the LSU
-        // queue) and is copied into A when that tile begins -- one rolled loop: the epilogue runs each instruction once
-        // per tile, so its speed is set by instruction fetch, and alternating two buffers over an unrolled pair of tiles
-        // doubled the straight-line code.
-        int it = 0;
-        auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
-                                if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
-        int wk = blockIdx.x;
-        if (wk < p.work) { const TcPix px = dec(wk, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
+    int it = 0, g = 0, wk = blockIdx.x;
+    auto end_tile = [&]() { ptx::tc_fence_before(); __syncwarp(); if (lane == 0) ptx::mbar_arrive(&t_empty[it & 1]);
+                            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 1); };
+    TcPix px;
+    if (wk < p.work) { px = dec(wk, m); tc_prefetch<GCH>(p, B, px, px.nb * BN + col_base); }
 #pragma unroll 1
-        for (; wk < p.work; wk += step, ++it) {
-            const TcPix px = dec(wk, m);
-            A = B;
-            if (wk + step < p.work) { const TcPix nx = dec(wk + step, m); tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base); }
+    while (wk < p.work) {
+        A = B;
+        int ng = g + 1, nwk = wk;
+        if (ng == NGRP) { ng = 0; nwk = wk + step; }
+        TcPix nx = px;
+        if (nwk < p.work) {
+            if (ng == 0) nx = dec(nwk, m);
+            tc_prefetch<GCH>(p, B, nx, nx.nb * BN + col_base + ng * GCH);
+        }
+        if (g == 0) {
             begin_tile(it);
             if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 0);
-            tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base, true, end_tile, stage);
-            if (warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
         }
+        tc_group<BN, NACC, GCH, true, TS>(p, mul, bias, &A, taddr_of(it), px, col_base + g * GCH, g == NGRP - 1, end_tile, stage);
+        if (g == NGRP - 1 && warp == EPI_FIRST_WARP && lane == 0) TC_TRACE(2, it, 2);
+        g = ng; px = nx;
+        if (ng == 0) { wk = nwk; ++it; }
     }
 }
 
