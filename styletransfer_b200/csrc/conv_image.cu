@@ -27,7 +27,7 @@ __device__ __forceinline__ int perm64(int ch) { return ((ch >> 2) & 1) * 32 + (c
 
 // forward: 256 threads = 32 pixel quads (4 along w) x 8 channel groups; 4 px x 8 ch accumulators
 __global__ void __launch_bounds__(IMG_THREADS)
-conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+conv_image_fwd4_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                       bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, bf16* __restrict__ relu_hi, bf16* __restrict__ relu_lo,
                       int planes, int N, int H, int W, int tiles_h, int tiles_w) {
     pdl_prologue();
@@ -111,6 +111,114 @@ conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, 
 #pragma unroll
                     for (int j = 0; j < 8; ++j) acc[p][j] = fmaxf(acc[p][j], 0.f);
                     store8p(relu_hi, relu_lo, planes, o, acc[p]);
+                }
+            }
+        }
+    }
+}
+
+// large batches: 256 threads = 32 pixel blocks (2 rows x 4 pixels) x 8 channel groups; 8 px x 8 ch accumulators per thread.
+// A weight vector fetched from shared memory feeds 8 pixels and an input row both output rows that touch it: 90 LDS.128
+// per 1728 FMAs where the 4-pixel version issues 81 per 864.  Both are bound by instruction issue (ncu: 63 % issue
+// slots busy, fma pipe 43 %): measured, the 8-pixel version wins with many tiles per block (16 x 256 x 256: fast_st step
+// 8.75 -> 8.59 ms) and loses with few (one 512 x 512 image: 41.0 -> 43.6 us), so the launcher picks by tile count.
+constexpr int FW_TH = 8, FW_SH = FW_TH + 2;        // forward tile: 8 x 32 pixels, staged rows
+__global__ void __launch_bounds__(IMG_THREADS, 2)
+conv_image_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                      bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, bf16* __restrict__ relu_hi, bf16* __restrict__ relu_lo,
+                      int planes, int N, int H, int W, int tiles_h, int tiles_w) {
+    pdl_prologue();
+    __shared__ __align__(16) float sw[27 * 64];                      // [tap = (c*3 + r)*3 + s][perm64(co)]
+    __shared__ __align__(16) float st[3 * FW_SH * IM_SW];
+    for (int i = threadIdx.x; i < 27 * 64; i += IMG_THREADS) {
+        const int co = i & 63, tap = i >> 6;                         // w: [64][3][3][3]
+        sw[tap * 64 + perm64(co)] = w[co * 27 + tap];
+    }
+    const int g = threadIdx.x & 7, quad = threadIdx.x >> 3;
+    const int qx = quad & 7, qy = quad >> 3;                         // pixels qx*4 .. +3 of rows 2*qy, 2*qy + 1
+    float b8[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b8[j] = bias ? bias[g * 8 + j] : 0.f;
+    const size_t HW = static_cast<size_t>(H) * W;
+    const int tiles = N * tiles_h * tiles_w;
+    // the staged image tile of the NEXT iteration is fetched into registers while this one is computed
+    constexpr int ST_N = 3 * FW_SH * IM_SW, ST_PER = (ST_N + IMG_THREADS - 1) / IMG_THREADS;
+    float pre[ST_PER];
+    auto fetch = [&](int tile) {
+        int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
+#pragma unroll
+        for (int k = 0; k < ST_PER; ++k) {
+            const int i = threadIdx.x + k * IMG_THREADS;
+            const int xx = i % IM_SW; int r = i / IM_SW; const int y = r % FW_SH; const int c = r / FW_SH;
+            const int ih = th * FW_TH + y - 1, iw = tw * IM_TW + xx - 4;
+            float v = 0.f;
+            if (i < ST_N && ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (static_cast<size_t>(n) * 3 + c) * HW + static_cast<size_t>(ih) * W + iw);
+            pre[k] = v;
+        }
+    };
+    if (blockIdx.x < tiles) fetch(blockIdx.x);
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        int q = tile; const int tw = q % tiles_w; q /= tiles_w; const int th = q % tiles_h; const int n = q / tiles_h;
+        const int h0 = th * FW_TH, w0 = tw * IM_TW;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < ST_PER; ++k) {
+            const int i = threadIdx.x + k * IMG_THREADS;
+            if (i < ST_N) st[i] = pre[k];
+        }
+        __syncthreads();
+        if (tile + gridDim.x < tiles) fetch(tile + gridDim.x);
+        float acc[2][4][8];
+#pragma unroll
+        for (int y = 0; y < 2; ++y)
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[y][p][j] = b8[j];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            // the four staged rows this thread's two output rows read, 12 values each (pixels qx*4 - 1 .. qx*4 + 4 at [3..8])
+            float in[4][12];
+#pragma unroll
+            for (int rr = 0; rr < 4; ++rr) {
+                const float* row = st + (c * FW_SH + 2 * qy + rr) * IM_SW + qx * 4;
+#pragma unroll
+                for (int v = 0; v < 3; ++v) {
+                    const float4 t = *reinterpret_cast<const float4*>(row + v * 4);
+                    in[rr][v * 4] = t.x; in[rr][v * 4 + 1] = t.y; in[rr][v * 4 + 2] = t.z; in[rr][v * 4 + 3] = t.w;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int sx = 0; sx < 3; ++sx) {
+                    const float* wr = sw + ((c * 3 + r) * 3 + sx) * 64 + g * 4;
+                    const float4 wa = *reinterpret_cast<const float4*>(wr);
+                    const float4 wb = *reinterpret_cast<const float4*>(wr + 32);
+                    const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+                    for (int y = 0; y < 2; ++y)
+#pragma unroll
+                        for (int p = 0; p < 4; ++p)
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) acc[y][p][j] = fmaf(in[y + r][p + sx + 3], wv[j], acc[y][p][j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int y = 0; y < 2; ++y) {
+            const int oh = h0 + 2 * qy + y;
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const int ow = w0 + qx * 4 + p;
+                if (oh < H && ow < W) {
+                    const size_t o = ((static_cast<size_t>(n) * H + oh) * W + ow) * 64 + g * 8;
+                    if (out_hi) store8p(out_hi, out_lo, planes, o, acc[y][p]);
+                    if (relu_hi) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[y][p][j] = fmaxf(acc[y][p][j], 0.f);
+                        store8p(relu_hi, relu_lo, planes, o, acc[y][p]);
+                    }
                 }
             }
         }
@@ -217,9 +325,14 @@ inline int img_grid(int tiles) {
 int conv_image_fwd(const float* x, const float* w, const float* bias, bf16* out_hi, bf16* out_lo,
                    bf16* relu_hi, bf16* relu_lo, int planes, int N, int H, int W, int Cout, cudaStream_t st) {
     ST_CHECK_ARG(Cout == 64, "conv_image_fwd: Cout must be 64 (got %d)", Cout);
-    const int th = (H + IM_TH - 1) / IM_TH, tw = (W + IM_TW - 1) / IM_TW;
-    st_launch(img_grid(N * th * tw), IMG_THREADS, 0, st)(conv_image_fwd_kernel, 
-        x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, th, tw);
+    const int th8 = (H + FW_TH - 1) / FW_TH, tw = (W + IM_TW - 1) / IM_TW;
+    const int tiles8 = N * th8 * tw, cap = 2 * st_num_sms();          // two resident blocks per SM (register budget)
+    if (tiles8 >= 4 * cap) {
+        st_launch(cap, IMG_THREADS, 0, st)(conv_image_fwd_kernel, x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, th8, tw);
+    } else {
+        const int th = (H + IM_TH - 1) / IM_TH;
+        st_launch(img_grid(N * th * tw), IMG_THREADS, 0, st)(conv_image_fwd4_kernel, x, w, bias, out_hi, out_lo, relu_hi, relu_lo, planes, N, H, W, th, tw);
+    }
     ST_CHECK_LAUNCH("conv_image_fwd_kernel");
     return ST_OK;
 }

@@ -421,9 +421,10 @@ def test_temporal_flow_warp_extension(ops):
     assert abs(float(loss) - float(tl)) / float(tl) < 1e-5 and rel_l2(cs2.grad, cs.grad) < 1e-5
 
 
-@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64)])
+@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64), (16, 200, 203)])
 def test_conv_image_fwd_and_dgrad(ops, N, H, W):
-    """VGG conv1_1 (3 -> 64) in exact fp32 on the CUDA cores, NCHW fp32 image in, image gradient out."""
+    """VGG conv1_1 (3 -> 64) in exact fp32 on the CUDA cores, NCHW fp32 image in, image gradient out.  The last case has
+    enough tiles for the forward kernel with 8 pixels per thread (conv_image.cu picks by tile count), ragged in both axes."""
     x = seeded((N, 3, H, W), 71, device='cuda').requires_grad_(True)
     w = seeded((64, 3, 3, 3), 72, 0.2, device='cuda')
     b = seeded((64,), 73, 0.1, device='cuda')
