@@ -154,7 +154,7 @@ class KernelTrace:
 
     def run(self, step, steps):
         ops, L = self.ops, self.L
-        real = ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd
+        real = ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed
 
         def conv2d(xs, w, *a, **k):
             out, e0, e1 = self._bracket(real[0], (xs, w) + a, k)
@@ -164,6 +164,14 @@ class KernelTrace:
                 cout = (w.cout if w.mode == 0 else w.cin) if w is not None else k['w_img_rows']
                 self.conv.append((f'conv_tc_kernel<{ks}x{ks}> {xs.C}->{cout} @{xs.H}x{xs.W}x{xs.N}', ks,
                                   2.0 * xs.N * xs.H * xs.W * xs.C * cout * ks * ks, e0, e1))
+            return out
+
+        def conv2d_routed(xs, w_ptrs, w_img_rows, *a, **k):
+            # the Gram-backward launch that also routes the max-pool gradient: a 1x1 conv_tc launch when it returns a tensor
+            out, e0, e1 = self._bracket(real[3], (xs, w_ptrs, w_img_rows) + a, k)
+            if out is not None:
+                self.conv.append((f'conv_tc_kernel<1x1, routed pool gradient> {xs.C}->{w_img_rows} @{xs.H}x{xs.W}x{xs.N}', 1,
+                                  2.0 * xs.N * xs.H * xs.W * xs.C * w_img_rows, e0, e1))
             return out
 
         def instnorm_fwd(x, *a, **k):
@@ -179,14 +187,14 @@ class KernelTrace:
             rd = (x.buf[0].numel() * min(x.planes, ops.bwd_planes()) + gy.buf.numel()) * 2
             self.norm.append(('instnorm_bwd (in_stats + in_finalize_bwd + in_apply_bwd)', 2.0 * rd + dx.buf.numel() * 2, e0, e1))
             return out
-        ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd = conv2d, instnorm_fwd, instnorm_bwd
+        ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed = conv2d, instnorm_fwd, instnorm_bwd, conv2d_routed
         try:
             torch.cuda.synchronize()
             for _ in range(steps):
                 step()
             torch.cuda.synchronize()
         finally:
-            ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd = real
+            ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed = real
         self.steps = steps
 
     @staticmethod

@@ -18,7 +18,7 @@ long long g_st_launches = 0;
 
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
-bool conv_tc_outputs_ok(int ks, int Cout, bool relu_out, int out_planes);
+bool conv_tc_outputs_ok(int ks, int Cout, int x_planes, int w_planes, int out_planes);
 int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                 const float*, const bf16*, const bf16*, const bf16*, int, bf16*, bf16*, bf16*, bf16*, int, float*, int,
                 float, const float*, const float*, const unsigned char*, cudaStream_t);
@@ -143,7 +143,7 @@ static int conv2d_impl(const void* x_hi, const void* x_lo, int x_planes, int N, 
     const bool nchw_ok = !out_nchw || (Cout_pad == 16 && Cnchw <= 4 && !mask && !add_hi);
     const bool tc = g_conv_path == 0 && same_fmt && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && nchw_ok &&
                     w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad) && (Cout_pad != 16 || out_nchw) &&
-                    conv_tc_outputs_ok(ks, Cout_pad, relu_hi != nullptr, out_planes);
+                    conv_tc_outputs_ok(ks, Cout_pad, x_planes, w_planes, out_planes);
     g_last_conv_kernel = tc ? 1 : 3;
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,

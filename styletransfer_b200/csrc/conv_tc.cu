@@ -75,7 +75,9 @@ template <int KS, int BN, int PL, bool RES> struct Cfg {
     static constexpr int SMEM_MAX = 232448;                 // 227 KB opt-in limit
     static constexpr int TAPS = KS * KS;
     // 1x1 launches (the Gram backward) are bound by their epilogue: their stores go through a shared-memory tile per
-    // epilogue warp (tc_group, TS); the launcher sends outputs that path does not write (ReLU copy, fp32, third plane) elsewhere
+    // epilogue warp (tc_group, TS).  Measured on the 3x3 general-schedule launches too (where the tile costs one stage of
+    // the weight ring): slower, Gatys closure 0.674 -> 0.690 ms, fast_st step 8.57 -> 8.98 ms -- they hide their epilogue
+    // under the MMA phase, so 3x3 keeps the direct stores.
     static constexpr bool TS = KS == 1 && BN >= 64 && PL <= 2;
     static constexpr int STG_BYTES = TS ? EPI_WARPS * TS_WARP_BYTES : 0;
     static constexpr int NA = RES ? 3 : (KS == 1 && PL < 3) ? (BN == 128 ? 3 : 4) : 2;
@@ -474,9 +476,11 @@ int launch_planes(int planes, const CUtensorMap& ah, const CUtensorMap& al, cons
 
 }  // namespace
 
-// 1x1 launches of the tcgen05 path write `out` (<= 2 planes) only (Cfg::TS)
-bool conv_tc_outputs_ok(int ks, int Cout, bool relu_out, int out_planes) {
-    return ks != 1 || Cout < 64 || (!relu_out && pc_planes(out_planes) <= 2);
+// 1x1 launches whose operands are read at <= 2 planes store through the per-warp shared-memory tiles (Cfg::TS), which
+// hold two output planes: a three-plane output of such a launch (not produced by the product) goes to the generic kernel.
+bool conv_tc_outputs_ok(int ks, int Cout, int x_planes, int w_planes, int out_planes) {
+    const int p = pc_planes(x_planes) < pc_planes(w_planes) ? pc_planes(x_planes) : pc_planes(w_planes);
+    return ks != 1 || Cout < 64 || p >= 3 || pc_planes(out_planes) <= 2;
 }
 // Eligibility of the tcgen05 path (the generic kernel covers everything else).
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout) {

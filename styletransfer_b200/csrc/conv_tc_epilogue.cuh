@@ -292,48 +292,53 @@ __device__ __forceinline__ void tc_group(const ConvTcParams& p, const TcMul& mul
     } else {
         static_assert(GCH == 32, "transposed stores: 32-channel groups");
         const int lane = threadIdx.x & 31;
-        const bool f16 = pc_f16(p.out_planes), two = p.out_lo != nullptr;
-        uint32_t hw[NCH][8], mw[NCH][8];
+        const bool f16 = pc_f16(p.out_planes);
+        float v[NCH][16];
 #pragma unroll
         for (int j = 0; j < NCH; ++j) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { hw[j][i] = 0u; mw[j][i] = 0u; }
-            if (px.valid) {
-                float v[16];
+            for (int i = 0; i < 16; ++i) v[j][i] = 0.f;
+            if (px.valid)
                 tc_chunk_values<BN, NACC, FUSED>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j],
                                                  FUSED ? pre->mk[j] : nullptr, FUSED ? pre->ah[j] : nullptr, FUSED ? pre->al[j] : nullptr,
-                                                 FUSED ? pre->rt[j] : nullptr, FUSED ? pre->pos : 0u, v);
-                if (f16) {
+                                                 FUSED ? pre->rt[j] : nullptr, FUSED ? pre->pos : 0u, v[j]);
+        }
+        const unsigned vm = (p.dbg & 1) ? 0u : __ballot_sync(0xffffffffu, px.valid);
+        const unsigned long long obase = static_cast<unsigned long long>(px.pix) * p.Cout + px.nb * BN + col0;
+        const int wsw = (lane >> 1) & 3, c = lane & 3;
+        // split the group's values into two 16-bit planes, stage them, store them with lanes along the channels
+        auto flush = [&](bf16* dst_hi, bf16* dst_lo, bool relu) {
+            const bool two = dst_lo != nullptr;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) split2h(v[2 * i], v[2 * i + 1], hw[j][i], mw[j][i]);
-                } else {
+            for (int j = 0; j < NCH; ++j) {
+                uint32_t hw[8], mw[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) split2(v[2 * i], v[2 * i + 1], hw[j][i], mw[j][i]);
+                for (int i = 0; i < 8; ++i) {
+                    const float a = relu ? fmaxf(v[j][2 * i], 0.f) : v[j][2 * i], b = relu ? fmaxf(v[j][2 * i + 1], 0.f) : v[j][2 * i + 1];
+                    if (f16) split2h(a, b, hw[i], mw[i]); else split2(a, b, hw[i], mw[i]);
+                }
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint8_t* dst = stage + lane * 64 + (((2 * j + h) ^ wsw) << 4);
+                    *reinterpret_cast<uint4*>(dst) = make_uint4(hw[4 * h], hw[4 * h + 1], hw[4 * h + 2], hw[4 * h + 3]);
+                    if (two) *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(mw[4 * h], mw[4 * h + 1], mw[4 * h + 2], mw[4 * h + 3]);
                 }
             }
-        }
-        const int wsw = (lane >> 1) & 3;
+            __syncwarp();
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            uint8_t* dst = stage + lane * 64 + ((c ^ wsw) << 4);
-            *reinterpret_cast<uint4*>(dst) = make_uint4(hw[c >> 1][(c & 1) * 4], hw[c >> 1][(c & 1) * 4 + 1], hw[c >> 1][(c & 1) * 4 + 2], hw[c >> 1][(c & 1) * 4 + 3]);
-            if (two) *reinterpret_cast<uint4*>(dst + 2048) = make_uint4(mw[c >> 1][(c & 1) * 4], mw[c >> 1][(c & 1) * 4 + 1], mw[c >> 1][(c & 1) * 4 + 2], mw[c >> 1][(c & 1) * 4 + 3]);
-        }
-        __syncwarp();
-        const unsigned vm = __ballot_sync(0xffffffffu, px.valid);
-        const unsigned long long obase = static_cast<unsigned long long>(px.pix) * p.Cout + px.nb * BN + col0;
-        const int c = lane & 3;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int prow = 8 * j + (lane >> 2);
-            const unsigned long long o = __shfl_sync(0xffffffffu, obase, prow) + c * 8;
-            const uint8_t* src = stage + prow * 64 + ((c ^ ((prow >> 1) & 3)) << 4);
-            if (((vm >> prow) & 1u) && !(p.dbg & 1)) {
-                *reinterpret_cast<uint4*>(p.out_hi + o) = *reinterpret_cast<const uint4*>(src);
-                if (two) *reinterpret_cast<uint4*>(p.out_lo + o) = *reinterpret_cast<const uint4*>(src + 2048);
+            for (int j = 0; j < 4; ++j) {
+                const int prow = 8 * j + (lane >> 2);
+                const unsigned long long o = __shfl_sync(0xffffffffu, obase, prow) + c * 8;
+                const uint8_t* src = stage + prow * 64 + ((c ^ ((prow >> 1) & 3)) << 4);
+                if ((vm >> prow) & 1u) {
+                    *reinterpret_cast<uint4*>(dst_hi + o) = *reinterpret_cast<const uint4*>(src);
+                    if (two) *reinterpret_cast<uint4*>(dst_lo + o) = *reinterpret_cast<const uint4*>(src + 2048);
+                }
             }
-        }
-        __syncwarp();
+            __syncwarp();
+        };
+        if (p.out_hi) flush(p.out_hi, p.out_lo, false);
+        if (p.relu_hi) flush(p.relu_hi, p.relu_lo, true);
     }
 }
 
