@@ -4,6 +4,7 @@
 // HBM-bound kernels: 128-bit accesses, channels-last so a warp reads contiguous
 // memory, per-(n,c) statistics reduced in two deterministic stages.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -597,7 +598,11 @@ __global__ void temporal_warp_bwd_kernel(const float* __restrict__ os, const flo
 }
 
 inline int in_splits(int N, int HW) {
-    int splits = (2 * st_num_sms()) / N;              // N * splits = one full wave at 2 CTAs per SM
+    // STRANSFER_IN_SPLITS_INVARIANT=1: a split that depends on the image size only, so an image's statistics (and with them
+    // every ReLU decision downstream) do not depend on how many images share the launch -- used by tools/check_dp.py to
+    // compare a data-parallel step with the single-GPU step bit for bit in the forward; 4 % slower at batch 16
+    static const bool inv = []() { const char* e = getenv("STRANSFER_IN_SPLITS_INVARIANT"); return e && e[0] == '1'; }();
+    int splits = inv ? 128 : (2 * st_num_sms()) / N;              // N * splits = one full wave at 2 CTAs per SM
     // at least 64 pixels per split: a 256-pixel floor left 16 images of 64 x 64 with 256 blocks = 0.43 waves, 21 % of the
     // warp slots busy and 2.7 TB/s (profiles/r02ac_in_kernels_fast_st.txt)
     const int maxs = (HW + 63) / 64;

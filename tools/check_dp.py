@@ -14,6 +14,12 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+# InstanceNorm statistics with a pixel split that does not depend on the batch size: a shard of 4 images and the global
+# batch of 8 then run bit-identical forwards, and this script compares the data-parallel PLUMBING (sharding, TV scaling,
+# all-reduce, 1/world in Adam).  With the default, batch-size-tuned split the per-image statistics differ in the last
+# bit, a handful of ReLU decisions of near-zero activations flip, and conv weight gradients differ by ~1e-3 relative
+# (tools/diag_batch_split.py) -- the same kind of difference cuDNN's batch-dependent algorithm choice produces.
+os.environ.setdefault('STRANSFER_IN_SPLITS_INVARIANT', '1')
 
 
 def seeded(shape, seed):
