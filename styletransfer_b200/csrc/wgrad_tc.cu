@@ -498,12 +498,30 @@ gram_tc_finish_style_kernel(const float* __restrict__ partial, int splits, int n
         const size_t per = static_cast<size_t>(nacc) * 128 * C;
         const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
         float s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        if (splits <= 160) {
+            // every partial of this lane in flight at once (<= 20 loads), summed in the order of the loop below: the loop is
+            // one L2 round trip per four partials, five in a row for the 147-way split of a single image
+            float v[20];
+#pragma unroll
+            for (int i = 0; i < 20; ++i) {
+                const int sp = sl + 8 * i;
+                v[i] = sp < splits ? __ldcg(base + static_cast<size_t>(sp) * per) : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < 20; i += 4) {
+                // the loop adds four per round only while sp + 24 < splits, the remainder goes to s alone
+                const int sp = sl + 8 * i;
+                if (sp + 24 < splits) { s += v[i]; s1 += v[i + 1]; s2 += v[i + 2]; s3 += v[i + 3]; }
+                else { s += v[i]; s += v[i + 1]; s += v[i + 2]; s += v[i + 3]; }
+            }
+        } else {
         int sp = sl;
         for (; sp + 24 < splits; sp += 32) {
             s += base[static_cast<size_t>(sp) * per];       s1 += base[static_cast<size_t>(sp + 8) * per];
             s2 += base[static_cast<size_t>(sp + 16) * per]; s3 += base[static_cast<size_t>(sp + 24) * per];
         }
         for (; sp < splits; sp += 8) s += base[static_cast<size_t>(sp) * per];
+        }
         s = (s + s1) + (s2 + s3);
     }
     sm[sl][ol] = s;
@@ -518,6 +536,68 @@ gram_tc_finish_style_kernel(const float* __restrict__ partial, int splits, int n
         const float d = g - t.T[idx % (C * C)];
         t.diff[idx] = d;
         d2 = d * d; am = fabsf(d);
+    }
+    style_tail_finish(t, d2, am, red);
+}
+
+// Same reduction with FOUR consecutive outputs per thread (one 16-byte load per split): a quarter of the blocks for the
+// same bytes -- at C = 256 the scalar kernel is 2048 blocks whose per-block tail (two block reductions, a ticket) and
+// 2048-entry last-block reduction cost more than the partials they read.  Used when an image has more than 16 splits
+// and C >= 128; summation order per output as in gram_tc_finish_style_kernel.
+__global__ void __launch_bounds__(256)
+gram_tc_finish_style4_kernel(const float* __restrict__ partial, int splits, int nacc, int C, float scale, int total4, StyleTail t) {
+    pdl_prologue();
+    __shared__ float4 sm[8][33];
+    __shared__ float red[32];
+    const int ol = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int v4 = blockIdx.x * 32 + ol;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto add4 = [](float4& a, const float4& b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; };
+    if (v4 < total4) {
+        int q = v4 * 4; const int j = q % C; q /= C; const int i = q % C; const int b = q / C;
+        const size_t per = static_cast<size_t>(nacc) * 128 * C;
+        const float* base = partial + (static_cast<size_t>(b) * splits) * per + (static_cast<size_t>(i / 128) * 128 + (i % 128)) * C + j;
+        float4 s1 = s, s2 = s, s3 = s;
+        if (splits <= 160) {
+            float4 v[20];
+#pragma unroll
+            for (int k = 0; k < 20; ++k) {
+                const int sp = sl + 8 * k;
+                v[k] = sp < splits ? __ldcg(reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int k = 0; k < 20; k += 4) {
+                const int sp = sl + 8 * k;
+                if (sp + 24 < splits) { add4(s, v[k]); add4(s1, v[k + 1]); add4(s2, v[k + 2]); add4(s3, v[k + 3]); }
+                else { add4(s, v[k]); add4(s, v[k + 1]); add4(s, v[k + 2]); add4(s, v[k + 3]); }
+            }
+        } else {
+            int sp = sl;
+            for (; sp + 24 < splits; sp += 32) {
+                add4(s, *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per));
+                add4(s1, *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp + 8) * per));
+                add4(s2, *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp + 16) * per));
+                add4(s3, *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp + 24) * per));
+            }
+            for (; sp < splits; sp += 8) add4(s, *reinterpret_cast<const float4*>(base + static_cast<size_t>(sp) * per));
+        }
+        s = make_float4((s.x + s1.x) + (s2.x + s3.x), (s.y + s1.y) + (s2.y + s3.y), (s.z + s1.z) + (s2.z + s3.z), (s.w + s1.w) + (s2.w + s3.w));
+    }
+    sm[sl][ol] = s;
+    __syncthreads();
+    float d2 = 0.f, am = 0.f;
+    if (sl == 0 && v4 < total4) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int l = 0; l < 8; ++l) add4(g, sm[l][ol]);
+        g = make_float4(g.x * scale, g.y * scale, g.z * scale, g.w * scale);
+        const size_t idx = static_cast<size_t>(v4) * 4;
+        if (t.Gm) *reinterpret_cast<float4*>(t.Gm + idx) = g;
+        const float4 tt = *reinterpret_cast<const float4*>(t.T + idx % (static_cast<size_t>(C) * C));
+        const float4 d = make_float4(g.x - tt.x, g.y - tt.y, g.z - tt.z, g.w - tt.w);
+        *reinterpret_cast<float4*>(t.diff + idx) = d;
+        d2 = (d.x * d.x + d.y * d.y) + (d.z * d.z + d.w * d.w);
+        am = fmaxf(fmaxf(fabsf(d.x), fabsf(d.y)), fmaxf(fabsf(d.z), fabsf(d.w)));
     }
     style_tail_finish(t, d2, am, red);
 }
@@ -657,8 +737,13 @@ int gram_tc_run(const bf16* f_hi, bool f16, int B, int HW, int C, float scale, f
             st_launch((total / 4 + 255) / 256, 256, 0, stream)(gram_tc_finish_small_style_kernel, p.partial, q.splits, q.nacc, C, scale, total / 4, t);
             ST_CHECK_LAUNCH("gram_tc_finish_small_style_kernel");
         } else {
-            st_launch((total + 31) / 32, 256, 0, stream)(gram_tc_finish_style_kernel, p.partial, q.splits, q.nacc, C, scale, total, t);
-            ST_CHECK_LAUNCH("gram_tc_finish_style_kernel");
+            if (C >= 128) {
+                st_launch((total / 4 + 31) / 32, 256, 0, stream)(gram_tc_finish_style4_kernel, p.partial, q.splits, q.nacc, C, scale, total / 4, t);
+                ST_CHECK_LAUNCH("gram_tc_finish_style4_kernel");
+            } else {
+                st_launch((total + 31) / 32, 256, 0, stream)(gram_tc_finish_style_kernel, p.partial, q.splits, q.nacc, C, scale, total, t);
+                ST_CHECK_LAUNCH("gram_tc_finish_style_kernel");
+            }
         }
         return ST_OK;
     }
