@@ -272,7 +272,12 @@ template <int C_> struct GCfg {
     static constexpr int PLANE = NBOX * BOX;
     static constexpr int STAGE = PL * PLANE;
     static constexpr int NACC = C_ > 128 ? C_ / 128 : 1;
-    static constexpr int TMEM_NEED = C_;                          // one 128-row half per CTA
+    // C <= 128: ONE wide MMA per k-step, hi^T x [hi | lo] (the planes of a stage are adjacent 64-channel boxes, so N = 2C
+    // is one operand with the box stride as leading dimension): accumulators [Hh | X] with X = hi^T lo.  The third product
+    // lo^T hi is X^T and is added by the epilogue -- 8 KB (12 KB at C = 128) of shared-memory operand reads per k-step
+    // instead of 18 (24) KB for three N = C MMAs; the kernel was bound by that, not by HBM.
+    static constexpr bool WIDE = C_ <= 128;
+    static constexpr int TMEM_NEED = WIDE ? 2 * C_ : C_;          // C = 256: one 128-row half per CTA
     static constexpr int TMEM_COLS = TMEM_NEED <= 64 ? 64 : TMEM_NEED <= 128 ? 128 : TMEM_NEED <= 256 ? 256 : 512;
     static constexpr int SLACK = C_ == 64 ? BOX : 0;              // C = 64: the second M group is don't-care data
     static constexpr int NS_FIT = (232448 - 1024 - 256 - SLACK) / STAGE;
@@ -335,7 +340,14 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
             ptx::mbar_wait(&full[st], ph);
             ptx::tc_fence_after();
             const uint32_t base = ptx::smem_u32(smem + st * G::STAGE);
-            {
+            if constexpr (G::WIDE) {
+                constexpr uint32_t idesc_w = idesc_mn(128, 2 * C_);
+#pragma unroll
+                for (int k = 0; k < G::TP / 16; ++k) {
+                    const uint32_t a_lo = mn_desc_lo(base + k * 16 * 128, G::BOX);
+                    if (leader) mma_ss(tmem_base, a_lo, hi, a_lo, hi, idesc_w | p.fmt_bits, k ? 1u : accumulate);
+                }
+            } else {
                 const int g = gsel;
 #pragma unroll
                 for (int k = 0; k < G::TP / 16; ++k) {
@@ -366,7 +378,38 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmF, const GramParams p) {
         const bool any = t1 > t0;
         // partial layout [b][split][half][128][C]: blockIdx.x enumerates (b, split, half) in exactly that order
         float* out = p.partial + static_cast<size_t>(blockIdx.x) * 128 * C_;
-        if (m < C_) {                                                // C = 64: rows 64..127 are don't-care
+        if constexpr (G::WIDE) {
+            // X -> shared memory (the pipeline stages are free now), row stride C + 1 floats; then out = Hh + X + X^T
+            float* xs = reinterpret_cast<float*>(smem);
+            constexpr int LD = C_ + 1;
+            static_assert(LD * C_ * 4 <= NS * G::STAGE, "transpose buffer does not fit the stages");
+            if (m < C_ && any) {
+#pragma unroll 1
+                for (int j = 0; j < C_ / 16; ++j) {
+                    uint32_t r[16];
+                    ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + C_ + j * 16, r);
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) xs[m * LD + j * 16 + i] = __uint_as_float(r[i]);
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (m < C_) {
+#pragma unroll 1
+                for (int j = 0; j < C_ / 16; ++j) {
+                    uint32_t r[16], x[16];
+                    ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + j * 16, r);
+                    ptx::tmem_ld16(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + C_ + j * 16, x);
+                    ptx::tmem_ld_wait();
+                    float4* dst = reinterpret_cast<float4*>(out + static_cast<size_t>(m) * C_ + j * 16);
+                    float v[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = any ? __uint_as_float(r[i]) + (__uint_as_float(x[i]) + xs[(j * 16 + i) * LD + m]) : 0.f;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) dst[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                }
+            }
+        } else if (m < C_) {                                         // C = 256 (half per CTA)
 #pragma unroll 1
             for (int j = 0; j < C_ / 16; ++j) {
                 uint32_t r[16];
