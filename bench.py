@@ -158,7 +158,11 @@ class KernelTrace:
 
         def conv2d(xs, w, *a, **k):
             out, e0, e1 = self._bracket(real[0], (xs, w) + a, k)
-            if L.st_last_conv_kernel() == 1:                      # conv_tc: tcgen05, stride 1
+            kid = L.st_last_conv_kernel()
+            if kid == 4:                                           # conv_imgrad_tc: image gradient, project-then-gather form
+                self.conv.append((f'conv_imgrad_tc_kernel {xs.C}->{k.get("out_nchw_channels", 3)} @{xs.H}x{xs.W}x{xs.N}', 0,
+                                  2.0 * xs.N * xs.H * xs.W * xs.C * k.get('out_nchw_channels', 3) * 9, e0, e1))
+            if kid == 1:                                           # conv_tc: tcgen05, stride 1
                 ks = w.ks if w is not None else k['w_ptrs'][3]
                 # algorithmic output channels (the packed row count is padded, e.g. 3 -> 16 for the image gradient)
                 cout = (w.cout if w.mode == 0 else w.cin) if w is not None else k['w_img_rows']
@@ -745,7 +749,7 @@ def run_ours(args, rank, world, local_rank):
         eager_closure()          # untimed: the eager path's buffers come out of cudaMalloc on first use
     tr = KernelTrace(ops, L)
     tr.run(eager_closure, args.steps)
-    roofline, per_kernel = tr.tensor_roofline(args.precision, ms / args.steps, 'closure: 4 fwd + 5 dgrad')
+    roofline, per_kernel = tr.tensor_roofline(args.precision, ms / args.steps, 'closure: 4 fwd + 4 dgrad')
     roofline['traffic'], roofline['traffic_source'] = ncu_traffic('gatys512', args.precision)
 
     lbfgs = train_e2e = None

@@ -54,10 +54,12 @@ extern "C" {
 /* build info: compute capability the kernels were compiled for (100) */
 int st_arch(void);
 const char* st_last_error(void);
-/* 0 = auto (tcgen05 where eligible), 1 = force the generic mma.sync conv (testing) */
+/* 0 = auto (tcgen05 where eligible), 1 = force the generic mma.sync conv (testing), 2 = auto, but the image gradient of
+ * conv1_1 on the 16-channel tile of conv_tc instead of conv_imgrad_tc (testing) */
 int st_set_conv_path(int path);
 /* test hook: which kernel the last st_conv2d call launched: 1 = conv_tc (tcgen05, stride 1),
- * 2 = conv_tcx (tcgen05, run-time geometry), 3 = conv_gen (mma.sync) */
+ * 2 = conv_tcx (tcgen05, run-time geometry), 3 = conv_gen (mma.sync), 4 = conv_imgrad_tc (tcgen05, the image gradient
+ * of conv1_1 in project-then-gather form) */
 int st_last_conv_kernel(void);
 /* number of kernels this library has launched so far in this process */
 long long st_launch_count(void);

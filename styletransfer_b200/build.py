@@ -24,7 +24,7 @@ OBJ_DIR = os.path.join(HERE, 'build')
 # source -> extra flags
 FAST = ['--use_fast_math']
 SOURCES = {
-    'api.cu': [], 'conv_tc.cu': FAST, 'conv_tcx.cu': FAST, 'conv_generic.cu': FAST, 'conv_image.cu': FAST,
+    'api.cu': [], 'conv_tc.cu': FAST, 'conv_tcx.cu': FAST, 'conv_imgrad_tc.cu': FAST, 'conv_generic.cu': FAST, 'conv_image.cu': FAST,
     'conv9.cu': FAST, 'conv9_tc.cu': FAST, 'contract.cu': FAST, 'wgrad_tc.cu': FAST,
     'elementwise.cu': [], 'norm_losses.cu': [], 'optim.cu': [], 'no_alloc.cu': [],
 }

@@ -18,6 +18,8 @@ long long g_st_launches = 0;
 
 // internal kernels (other translation units)
 bool conv_tc_eligible(int ks, int stride, int Cin, int Cout);
+bool conv_imgrad_tc_eligible(int ks, int Cin, int Cout_pad, int x_planes, int w_planes, int w_rows_total, int Cnchw);
+int conv_imgrad_tc_run(const bf16*, const bf16*, int, int, int, int, const bf16*, const bf16*, int, float*, int, float, const float*, cudaStream_t);
 bool conv_tc_outputs_ok(int ks, int Cout, int x_planes, int w_planes, int out_planes);
 int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                 const float*, const bf16*, const bf16*, const bf16*, int, bf16*, bf16*, bf16*, bf16*, int, float*, int,
@@ -141,10 +143,17 @@ static int conv2d_impl(const void* x_hi, const void* x_lo, int x_planes, int N, 
     const bool same_fmt = pc_f16(x_planes) == pc_f16(w_planes);
     // an fp32 NCHW output (the image gradient) is taken by the 16-channel tile, unfused launches only
     const bool nchw_ok = !out_nchw || (Cout_pad == 16 && Cnchw <= 4 && !mask && !add_hi);
-    const bool tc = g_conv_path == 0 && same_fmt && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && nchw_ok &&
+    const bool tc = (g_conv_path == 0 || g_conv_path == 2) && same_fmt && !up && !transposed && pad == ks / 2 && Ho == H && Wo == W && nchw_ok &&
                     w_rows_total >= Cout_pad && conv_tc_eligible(ks, stride, Cin, Cout_pad) && (Cout_pad != 16 || out_nchw) &&
                     conv_tc_outputs_ok(ks, Cout_pad, x_planes, w_planes, out_planes);
     g_last_conv_kernel = tc ? 1 : 3;
+    // backward-data of conv1_1 to the image: "project, then gather" kernel (conv_imgrad_tc.cu) instead of the 16-channel tile
+    if (tc && g_conv_path == 0 && out_nchw && !out_hi && !relu_hi && !bias && w_img_rows == 0 && x_lo && w_lo &&
+        conv_imgrad_tc_eligible(ks, Cin, Cout_pad, x_planes, w_planes, w_rows_total, Cnchw)) {
+        g_last_conv_kernel = 4;
+        return conv_imgrad_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, CBF(w_hi), CBF(w_lo), w_rows_total, out_nchw, Cnchw,
+                                  acc_mul, acc_mul_slot, STRM(stream));
+    }
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), add_planes, BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw,

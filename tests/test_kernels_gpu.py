@@ -116,9 +116,10 @@ def test_forward_conv_is_fp32_accurate(ops):
     assert rel_l2(nhwc(out, 64), ref) < 2e-5
 
 
-@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64)])
+@pytest.mark.parametrize('N,H,W', [(2, 20, 36), (1, 7, 9), (1, 64, 64), (3, 150, 77)])
 def test_conv_tcgen05_image_gradient(ops, N, H, W):
-    """backward-data of conv1_1 on the 16-channel tcgen05 tile, fp32 NCHW output from the epilogue"""
+    """backward-data of conv1_1: the project-then-gather tcgen05 kernel (conv_imgrad_tc.cu, kernel id 4) and the
+    16-channel tile of conv_tc it replaced (st_set_conv_path(2) selects it), fp32 NCHW output"""
     from styletransfer_b200 import _lib
     x = seeded((N, 3, H, W), 71, device='cuda').requires_grad_(True)
     w = seeded((64, 3, 3, 3), 72, 0.2, device='cuda')
@@ -126,8 +127,15 @@ def test_conv_tcgen05_image_gradient(ops, N, H, W):
     F.conv2d(x, w, None, padding=1).backward(gy)
     pw = ops.PackedWeight(w, 2, rows_pad=16)
     _, _, gx = ops.conv2d(_bf16_grad(ops, gy), pw, want_out=False, out_nchw_channels=3)
-    assert _lib.lib().st_last_conv_kernel() == 1
+    assert _lib.lib().st_last_conv_kernel() == 4
     assert rel_l2(gx, x.grad) < TOL
+    _lib.lib().st_set_conv_path(2)
+    try:
+        _, _, gx16 = ops.conv2d(_bf16_grad(ops, gy), pw, want_out=False, out_nchw_channels=3)
+        assert _lib.lib().st_last_conv_kernel() == 1
+    finally:
+        _lib.lib().st_set_conv_path(0)
+    assert rel_l2(gx16, x.grad) < TOL and rel_l2(gx, gx16) < 1e-5
 
 
 @pytest.mark.parametrize('cin,cout,H,W', [(32, 64, 20, 28), (64, 128, 16, 32), (32, 64, 33, 47), (64, 128, 9, 19)])
