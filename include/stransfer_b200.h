@@ -119,6 +119,18 @@ int st_conv2d_routed(const void* x_hi, const void* x_lo, int x_planes, int N, in
                      void* out_hi, void* out_lo, int out_planes, float acc_mul, const float* acc_mul_slot, const float* gy_mul_slot,
                      void* stream);
 
+/* st_conv2d (3x3, stride 1, pad 1, shared weights) that also writes the output of the ReLU + MaxPool2d(2, 2) behind it:
+ * pool = relu(maxpool2x2(conv + bias)) [N][H/2][W/2][Cout_pad] in the planes of `out`, and one routing byte per pooled
+ * element (window position 0..3 of the first maximum in PyTorch's scan order, 4 = maximum <= 0) for
+ * st_relu_maxpool2x2_bwd_idx / st_conv2d_routed.  `out` (the pre-ReLU tap) is optional.  Replaces st_conv2d +
+ * st_relu_maxpool2x2_fwd_idx for the convs in front of VGG pieces 2 and 5 (nn.Conv2d -> nn.ReLU -> nn.MaxPool2d of the
+ * pieces reference network.py:257-314 builds): the pool no longer re-reads the full-resolution tap.  Tensor-core path
+ * only: ST_ERR_UNSUPPORTED where st_conv2d would take another kernel (the caller then runs the two launches). */
+int st_conv2d_pool(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin,
+                   const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int ks, int Cout_pad, int Cbias, const float* bias,
+                   void* out_hi, void* out_lo, int out_planes, void* pool_hi, void* pool_lo, unsigned char* pool_idx,
+                   float acc_mul, const float* acc_mul_slot, void* stream);
+
 /* First VGG layer (torchvision vgg19.features[0], 3 -> Cout channels, 3x3, zero padding 1;
  * run by StyleNetwork.run_through_pieces network.py:316-340) in exact fp32 on the CUDA cores:
  * x is the NCHW fp32 image (module boundary format), w [Cout][3][3][3] and bias [Cout] fp32;

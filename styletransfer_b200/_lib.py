@@ -38,6 +38,10 @@ SIGNATURES = {
                               _P, _P, _I, _I, _I, _I, _I,   # w, planes, rows_total, img_rows, ks, Cout_pad
                               _P, _P, _P, _I, _P,           # mask gy_hi gy_lo gy_planes route
                               _P, _P, _I, _F, _P, _P, _P]), # out_hi out_lo out_planes acc_mul acc_mul_slot gy_mul_slot stream
+    'st_conv2d_pool': (_I, [_P, _P, _I, _I, _I, _I, _I,     # x, planes, N H W Cin
+                            _P, _P, _I, _I, _I, _I, _I, _P, # w, planes, rows_total, ks, Cout_pad, Cbias, bias
+                            _P, _P, _I, _P, _P, _P,         # out_hi out_lo out_planes pool_hi pool_lo pool_idx
+                            _F, _P, _P]),                   # acc_mul acc_mul_slot stream
     'st_conv3x3_image_fwd': (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     'st_conv3x3_image_dgrad': (_I, [_P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),
     'st_conv9_expand': (_I, [_P, _P, _I, _I, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P]),

@@ -23,7 +23,7 @@ int conv_imgrad_tc_run(const bf16*, const bf16*, int, int, int, int, const bf16*
 bool conv_tc_outputs_ok(int ks, int Cout, int x_planes, int w_planes, int out_planes);
 int conv_tc_run(const bf16*, const bf16*, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                 const float*, const bf16*, const bf16*, const bf16*, int, bf16*, bf16*, bf16*, bf16*, int, float*, int,
-                float, const float*, const float*, const unsigned char*, cudaStream_t);
+                float, const float*, const float*, const unsigned char*, bf16*, bf16*, unsigned char*, cudaStream_t);
 int conv_gen_run(const bf16*, const bf16*, int, int, int, int, int, int, const bf16*, const bf16*, int, int, int, int, int,
                  int, int, int, int, int, const float*, const bf16*, const bf16*, const bf16*, int,
                  bf16*, bf16*, bf16*, bf16*, int, float*, int, float, const float*, const float*, cudaStream_t);
@@ -128,12 +128,13 @@ static int conv2d_impl(const void* x_hi, const void* x_lo, int x_planes, int N, 
               int ks, int stride, int pad, int transposed, int Ho, int Wo, int Cout_pad, int Cbias,
               const float* bias, const void* mask, const void* add_hi, const void* add_lo, int add_planes,
               void* out_hi, void* out_lo, void* relu_hi, void* relu_lo, int out_planes, float* out_nchw, int Cnchw,
-              float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route, void* stream) {
+              float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route,
+              void* pool_hi, void* pool_lo, unsigned char* pool_idx, void* stream) {
     ST_CHECK_ARG(x_hi && w_hi, "st_conv2d: null input or weight");
     ST_CHECK_ARG(N > 0 && H > 0 && W > 0 && Ho > 0 && Wo > 0, "st_conv2d: empty shape");
     ST_CHECK_ARG(Cin % 8 == 0 && Cout_pad % 8 == 0, "st_conv2d: channel counts must be multiples of 8 (got %d, %d)", Cin, Cout_pad);
     ST_CHECK_ARG(ks >= 1 && ks <= 11 && (ks & 1) && stride >= 1, "st_conv2d: unsupported kernel size/stride");
-    ST_CHECK_ARG(out_hi || relu_hi || out_nchw, "st_conv2d: no output requested");
+    ST_CHECK_ARG(out_hi || relu_hi || out_nchw || pool_idx, "st_conv2d: no output requested");
     ST_CHECK_ARG(!(add_lo && !add_hi), "st_conv2d: add_lo without add_hi");
     ST_CHECK_ARG(plane_code_ok(x_planes) && plane_code_ok(w_planes) && plane_code_ok(out_planes) && (!add_hi || plane_code_ok(add_planes)),
                  "st_conv2d: bad plane code (x %d, w %d, out %d, add %d)", x_planes, w_planes, out_planes, add_planes);
@@ -157,7 +158,12 @@ static int conv2d_impl(const void* x_hi, const void* x_lo, int x_planes, int N, 
     if (tc)
         return conv_tc_run(CBF(x_hi), CBF(x_lo), x_planes, N, H, W, Cin, CBF(w_hi), CBF(w_lo), w_planes, w_rows_total, w_img_rows, ks, Cout_pad,
                            bias, CBF(mask), CBF(add_hi), CBF(add_lo), add_planes, BF(out_hi), BF(out_lo), BF(relu_hi), BF(relu_lo), out_planes, out_nchw, Cnchw,
-                           acc_mul, acc_mul_slot, add_mul_slot, add_route, STRM(stream));
+                           acc_mul, acc_mul_slot, add_mul_slot, add_route, BF(pool_hi), BF(pool_lo), pool_idx, STRM(stream));
+    if (pool_idx) {
+        st_set_error("st_conv2d_pool: the fused relu + max-pool output needs the stride-1 3x3 tensor-core path (ks %d stride %d Cin %d Cout %d)",
+                     ks, stride, Cin, Cout_pad);
+        return ST_ERR_UNSUPPORTED;
+    }
     if (add_route) {
         st_set_error("st_conv2d_routed: a routed addend needs the stride-1 tensor-core path (ks %d stride %d Cin %d Cout %d, same 16-bit format %d)",
                      ks, stride, Cin, Cout_pad, int(same_fmt));
@@ -207,7 +213,7 @@ int st_conv2d(const void* x_hi, const void* x_lo, int x_planes, int N, int H, in
               float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, void* stream) {
     return conv2d_impl(x_hi, x_lo, x_planes, N, H, W, Cin, up, w_hi, w_lo, w_planes, w_rows_total, w_img_rows, ks, stride, pad, transposed,
                        Ho, Wo, Cout_pad, Cbias, bias, mask, add_hi, add_lo, add_planes, out_hi, out_lo, relu_hi, relu_lo, out_planes,
-                       out_nchw, Cnchw, acc_mul, acc_mul_slot, add_mul_slot, nullptr, stream);
+                       out_nchw, Cnchw, acc_mul, acc_mul_slot, add_mul_slot, nullptr, nullptr, nullptr, nullptr, stream);
 }
 int st_conv2d_routed(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin,
                      const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout_pad,
@@ -218,7 +224,19 @@ int st_conv2d_routed(const void* x_hi, const void* x_lo, int x_planes, int N, in
     ST_CHECK_ARG(H >= 2 && W >= 2, "st_conv2d_routed: the 2x2 pool needs H, W >= 2 (got %d x %d)", H, W);
     return conv2d_impl(x_hi, x_lo, x_planes, N, H, W, Cin, 0, w_hi, w_lo, w_planes, w_rows_total, w_img_rows, ks, 1, ks / 2, 0,
                        H, W, Cout_pad, 0, nullptr, mask, gy_hi, gy_lo, gy_planes, out_hi, out_lo, nullptr, nullptr, out_planes,
-                       nullptr, 0, acc_mul, acc_mul_slot, gy_mul_slot, route, stream);
+                       nullptr, 0, acc_mul, acc_mul_slot, gy_mul_slot, route, nullptr, nullptr, nullptr, stream);
+}
+
+int st_conv2d_pool(const void* x_hi, const void* x_lo, int x_planes, int N, int H, int W, int Cin,
+                   const void* w_hi, const void* w_lo, int w_planes, int w_rows_total, int ks, int Cout_pad, int Cbias, const float* bias,
+                   void* out_hi, void* out_lo, int out_planes, void* pool_hi, void* pool_lo, unsigned char* pool_idx,
+                   float acc_mul, const float* acc_mul_slot, void* stream) {
+    ST_CHECK_ARG(pool_hi && pool_idx, "st_conv2d_pool: null pooled output or routing map");
+    ST_CHECK_ARG(pc_planes(out_planes) < 2 || pool_lo, "st_conv2d_pool: the pooled output needs its lo plane");
+    ST_CHECK_ARG(H >= 2 && W >= 2, "st_conv2d_pool: the 2x2 pool needs H, W >= 2 (got %d x %d)", H, W);
+    return conv2d_impl(x_hi, x_lo, x_planes, N, H, W, Cin, 0, w_hi, w_lo, w_planes, w_rows_total, 0, ks, 1, ks / 2, 0,
+                       H, W, Cout_pad, Cbias, bias, nullptr, nullptr, nullptr, 1, out_hi, out_lo, nullptr, nullptr, out_planes,
+                       nullptr, 0, acc_mul, acc_mul_slot, nullptr, nullptr, pool_hi, pool_lo, pool_idx, stream);
 }
 
 int st_conv3x3_image_fwd(const float* x, const float* w, const float* bias, void* out_hi, void* out_lo,

@@ -492,8 +492,11 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
                 const bf16* w_hi, const bf16* w_lo, int w_planes, int w_rows_total, int w_img_rows, int ks, int Cout,
                 const float* bias, const bf16* mask, const bf16* add_hi, const bf16* add_lo, int add_code,
                 bf16* out_hi, bf16* out_lo, bf16* relu_hi, bf16* relu_lo, int out_planes, float* out_nchw, int Cnchw,
-                float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route, cudaStream_t stream) {
+                float acc_mul, const float* acc_mul_slot, const float* add_mul_slot, const unsigned char* add_route,
+                bf16* pool_hi, bf16* pool_lo, unsigned char* pool_idx, cudaStream_t stream) {
     const int taps = ks * ks;
+    ST_CHECK_ARG(!pool_idx || (ks == 3 && pool_hi && !mask && !add_hi && H >= 2 && W >= 2 && static_cast<long long>(N) * H * W < (1ll << 31)),
+                 "conv_tc: the fused relu + max-pool output needs an unfused 3x3 launch");
     ST_CHECK_ARG(!add_route || (add_hi && pc_planes(add_code) <= 2), "conv_tc: a routed addend needs the pooled gradient in add_hi (<= 2 planes)");
     ST_CHECK_ARG(!add_route || static_cast<long long>(N) * H * W < (1ll << 31), "conv_tc: a routed addend indexes pixels with 32 bits (N*H*W < 2^31)");
     ST_CHECK_ARG(!out_nchw || (Cnchw >= 1 && Cnchw <= 4 && !mask && !add_hi), "conv_tc: the NCHW output takes <= 4 channels and no mask / addend");
@@ -521,6 +524,7 @@ int conv_tc_run(const bf16* x_hi, const bf16* x_lo, int x_planes, int N, int H, 
     p.acc_mul = acc_mul; p.acc_mul_slot = acc_mul_slot; p.add_mul_slot = add_mul_slot;
     p.bias = bias; p.mask = mask; p.add_hi = add_hi; p.add_lo = add_lo;
     p.add_route = add_route; p.route_Ho = H / 2; p.route_Wo = W / 2;
+    p.pool_hi = pool_hi; p.pool_lo = pool_lo; p.pool_idx = pool_idx; p.pool_lane_h = TW; p.pool_Ho = H / 2; p.pool_Wo = W / 2;
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = out_nchw; p.nchw_c = Cnchw; p.out_f32 = nullptr;
     p.dbg = g_conv_debug;

@@ -55,6 +55,11 @@ struct ConvTcParams {
     // (relu_maxpool_bwd_idx_kernel folded into this epilogue; bytes of 4 mark windows whose maximum was <= 0)
     const unsigned char* add_route;
     int route_Ho, route_Wo;
+    // pool_idx != null (unfused 3x3 launches): the epilogue also writes relu(maxpool2x2(result)) [N][H/2][W/2][Cout] in the
+    // planes of `out` and the routing byte of every pooled element (relu_maxpool_fwd_idx_kernel folded into the conv that
+    // produces its input); pool_lane_h = lane distance of the pixel one row down in the accumulator tile (its width)
+    bf16* pool_hi; bf16* pool_lo; unsigned char* pool_idx;
+    int pool_lane_h, pool_Ho, pool_Wo;
     bf16* out_hi; bf16* out_lo;     // result (pre-activation)
     bf16* relu_hi; bf16* relu_lo;   // optional second output relu(result)
     float* out_nchw; int nchw_c;    // optional fp32 NCHW output of the first nchw_c channels (unfused launches only)
@@ -220,6 +225,9 @@ __device__ __forceinline__ void tc_chunk_values(const ConvTcParams& p, const TcM
     }
 }
 
+template <int BN, bool FUSED>
+__device__ __forceinline__ void tc_chunk_store(const ConvTcParams& p, const TcPix& px, int col, float (&v)[16]);
+
 template <int BN, int NACC, bool FUSED>
 __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const TcMul& mul, const float* bias, const TcPix& px, int col,
                                                  const uint32_t (&r)[16], const uint32_t (&rc)[16], const uint32_t (&rd)[16],
@@ -229,6 +237,14 @@ __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const Tc
     const size_t o = px.pix * p.Cout + ch;
     float v[16];
     tc_chunk_values<BN, NACC, FUSED>(p, mul, bias, px, col, r, rc, rd, mk, ah, al, rt, pos, v);
+    tc_chunk_store<BN, FUSED>(p, px, col, v);
+}
+
+// the stores of one 16-channel chunk of a valid pixel
+template <int BN, bool FUSED>
+__device__ __forceinline__ void tc_chunk_store(const ConvTcParams& p, const TcPix& px, int col, float (&v)[16]) {
+    const int ch = px.nb * BN + col;
+    const size_t o = px.pix * p.Cout + ch;
 #ifdef ST_CONV_TRACE
     if (p.dbg & 32) {      // experiment: all the arithmetic of the split, (practically) no store
         uint32_t hw[8], mw[8], x = 0;
@@ -260,6 +276,39 @@ __device__ __forceinline__ void tc_chunk_compute(const ConvTcParams& p, const Tc
     }
 }
 
+// relu + 2x2 max-pool of one 16-channel chunk inside the accumulator tile: the four pixels of a window are lanes l, l^1,
+// l^W, l^(W|1) of one warp (tile rows are W = pool_lane_h pixels wide, a warp holds whole row pairs); ALL lanes call this.
+// First maximum in PyTorch's scan order wins, byte 4 = the window maximum is <= 0 (relu' = 0 everywhere).
+template <int BN>
+__device__ __forceinline__ void tc_pool_chunk(const ConvTcParams& p, const TcPix& px, int col, const float (&v)[16]) {
+    const int lane = threadIdx.x & 31, dh = p.pool_lane_h;
+    float best[16];
+    uint32_t idx[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        const float a = v[i];
+        const float b = __shfl_xor_sync(0xffffffffu, a, 1), c = __shfl_xor_sync(0xffffffffu, a, dh), d = __shfl_xor_sync(0xffffffffu, a, dh | 1);
+        float m = a; uint32_t k = 0u;
+        if (b > m) { m = b; k = 1u; }
+        if (c > m) { m = c; k = 2u; }
+        if (d > m) { m = d; k = 3u; }
+        if (!(m > 0.f)) { m = 0.f; k = 4u; }
+        best[i] = m;
+        idx[i >> 2] |= k << (8 * (i & 3));
+    }
+    if (!(lane & 1) && !(lane & dh) && px.valid) {
+        uint32_t t, w, n, h;
+        p.fd_W.divmod(static_cast<uint32_t>(px.pix), t, w);
+        p.fd_H.divmod(t, n, h);
+        const int oh = static_cast<int>(h >> 1), ow = static_cast<int>(w >> 1);
+        if (oh < p.pool_Ho && ow < p.pool_Wo) {
+            const size_t o = ((static_cast<size_t>(n) * p.pool_Ho + oh) * p.pool_Wo + ow) * p.Cout + px.nb * BN + col;
+            store16p(p.pool_hi, p.pool_lo, p.out_planes, o, best);
+            *reinterpret_cast<uint4*>(p.pool_idx + o) = make_uint4(idx[0], idx[1], idx[2], idx[3]);
+        }
+    }
+}
+
 // A group of GCH (16 or 32) columns: ALL its accumulator loads are issued before the single wait, and when the group is
 // the last one of the tile the TMEM stage is handed back to the MMA warp right after that wait -- the arithmetic and
 // the global stores of a tile run while the tensor core already fills the stage again.  (The epilogue is latency
@@ -283,6 +332,17 @@ __device__ __forceinline__ void tc_group(const ConvTcParams& p, const TcMul& mul
     ptx::tmem_ld_wait();
     if (last) end_tile();
     if constexpr (!TS) {
+        if (!FUSED && p.pool_idx) {
+            // every lane computes its values (the pool exchanges them between lanes), valid pixels store
+#pragma unroll
+            for (int j = 0; j < NCH; ++j) {
+                float v[16];
+                tc_chunk_values<BN, NACC, false>(p, mul, bias, px, col0 + j * 16, r[j], rc[j], rd[j], nullptr, nullptr, nullptr, nullptr, 0u, v);
+                tc_pool_chunk<BN>(p, px, col0 + j * 16, v);
+                if (px.valid && (p.out_hi || p.relu_hi)) tc_chunk_store<BN, false>(p, px, col0 + j * 16, v);
+            }
+            return;
+        }
         if (!px.valid || (p.dbg & 1)) return;
 #pragma unroll
         for (int j = 0; j < NCH; ++j)

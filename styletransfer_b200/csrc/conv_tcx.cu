@@ -336,6 +336,7 @@ int conv_tcx_run(int mode, const bf16* x_hi, const bf16* x_lo, int x_planes, int
     p.out_hi = out_hi; p.out_lo = out_lo; p.relu_hi = relu_hi; p.relu_lo = relu_lo;
     p.out_nchw = nullptr; p.nchw_c = 0; p.out_f32 = out_f32; p.dbg = 0;
     p.add_route = nullptr; p.route_Ho = p.route_Wo = 0;
+    p.pool_hi = p.pool_lo = nullptr; p.pool_idx = nullptr; p.pool_lane_h = 0; p.pool_Ho = p.pool_Wo = 0;
 
     CUtensorMap ah, al, wh, wl;
     const int ps = mode == 1 ? 2 : 1;

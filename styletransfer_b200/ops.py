@@ -238,6 +238,29 @@ def conv2d(x, w, bias=None, stride=1, pad=None, up=0, transposed=0, out_hw=None,
     return out, relu, nchw
 
 
+def conv2d_pool(x, w, bias, want_out=True):
+    """Forward 3x3 conv whose epilogue also applies the ReLU + MaxPool2d(2, 2) that follows it in the VGG pieces
+    (reference network.py:257-314): returns (tap Split | None, pooled Split, routing byte map) -- what ``conv2d`` +
+    ``relu_maxpool_fwd(want_idx=True)`` return -- or None when the launch cannot take the tensor-core kernel."""
+    assert w.mode == 0 and w.ks == 3 and w.cols == x.C
+    L = _lib.lib()
+    dev = x.buf.device
+    out_planes, out_fmt = fwd_planes(), fwd_fmt()
+    if (x.code & 16) != (w.code & 16) or x.H < 2 or x.W < 2:
+        return None
+    out = Split(x.N, x.H, x.W, w.rows, dev, planes=out_planes, fmt=out_fmt) if want_out else None
+    pooled = Split(x.N, x.H // 2, x.W // 2, w.rows, dev, planes=out_planes, fmt=out_fmt)
+    idx = torch.empty((x.N, x.H // 2, x.W // 2, w.rows), dtype=torch.uint8, device=dev)
+    cbias = 0 if bias is None else bias.numel()
+    rc = L.st_conv2d_pool(x.hi, x.lo if (x.code & 15) > 1 else None, x.code, x.N, x.H, x.W, x.C, w.hi, w.lo, w.code, w.rows, w.ks, w.rows, cbias,
+                          _p(bias), out.hi if out else None, out.lo if out else None, out_planes | out_fmt, pooled.hi, pooled.lo, idx.data_ptr(),
+                          float(w.acc_mul), _p(x.slot), _stream())
+    if rc == -3:      # ST_ERR_UNSUPPORTED
+        return None
+    _lib.check(rc, 'st_conv2d_pool')
+    return out, pooled, idx
+
+
 def conv2d_routed(x, w_ptrs, w_img_rows, gy, idx, mask=None):
     """out = x * D (per-image 1x1 weights, the Gram backward) [* (mask > 0)] + the gradient ``gy`` of the OUTPUT of the
     2x2 max-pool that follows, routed through the byte map ``idx`` of relu_maxpool_fwd(want_idx=True): the MaxPool2d and

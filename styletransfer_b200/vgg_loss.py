@@ -42,6 +42,8 @@ IMAGE_GRAD_TC = True
 # MaxPool2d + ReLU backward of a block folded into the epilogue of the block's first Gram-backward launch
 # (ops.conv2d_routed); STRANSFER_FUSE_POOL_ROUTE=0 keeps the separate relu_maxpool_bwd launch
 FUSE_POOL_ROUTE = os.environ.get('STRANSFER_FUSE_POOL_ROUTE', '1') != '0'
+# ReLU + MaxPool2d forward folded into the epilogue of the conv in front of it (ops.conv2d_pool); =0 keeps the pool launch
+FUSE_POOL_FWD = os.environ.get('STRANSFER_FUSE_POOL_FWD', '1') != '0'
 
 
 def parse_layer(name):
@@ -127,10 +129,17 @@ class VGGPrefix:
             # loss node wants the ReLU output as a tensor-core operand (style node on ReLU_k)
             want_relu = (need_next and not pool) or ('R!', k) in points
             want_tap = keep_taps or ('C', k) in points or ('R', k) in points or need_pool or not want_relu
+            pooled = None
             if k == 1:
                 tap, relu = ops.conv_image_fwd(x.contiguous().float(), self.w0, self.bias[0], want_out=want_tap, want_relu=want_relu)
             else:
-                tap, relu, _ = ops.conv2d(h, self.fwd[k - 1], self.bias[k - 1], want_out=want_tap, want_relu=want_relu)
+                if need_pool and not want_relu and FUSE_POOL_FWD:
+                    # ReLU + MaxPool2d_k ride on the epilogue of conv k (the pool does not re-read the tap)
+                    pooled = ops.conv2d_pool(h, self.fwd[k - 1], self.bias[k - 1], want_out=want_tap)
+                if pooled is not None:
+                    tap, relu = pooled[0], None
+                else:
+                    tap, relu, _ = ops.conv2d(h, self.fwd[k - 1], self.bias[k - 1], want_out=want_tap, want_relu=want_relu)
             taps[k] = tap
             if tap is not None:
                 vals[('C', k)] = tap
@@ -140,7 +149,11 @@ class VGGPrefix:
                 if pt in points and on_point is not None:
                     on_point(pt, vals, taps)
             if need_pool:
-                if pool_idx is not None:
+                if pooled is not None:
+                    h = pooled[1]
+                    if pool_idx is not None:
+                        pool_idx[k] = pooled[2]
+                elif pool_idx is not None:
                     h, pool_idx[k] = ops.relu_maxpool_fwd(tap, want_idx=True)
                 else:
                     h = ops.relu_maxpool_fwd(tap)

@@ -330,6 +330,35 @@ def test_gram_backward_with_routed_pool_gradient(ops, B, C, H, W, masked):
         _lib.lib().st_set_conv_path(0)
 
 
+@pytest.mark.parametrize('N,Cin,Cout,H,W', [(1, 64, 64, 32, 48), (2, 64, 128, 21, 19), (1, 128, 128, 40, 24), (1, 64, 64, 130, 70)])
+def test_conv_with_fused_relu_maxpool(ops, N, Cin, Cout, H, W):
+    """st_conv2d_pool = st_conv2d + st_relu_maxpool2x2_fwd_idx in one launch (nn.Conv2d -> nn.ReLU -> nn.MaxPool2d of the
+    VGG pieces): the tap is bit-identical and the pooled values are identical to the two-launch form (rounding to the planes
+    is monotone), the routing bytes agree except where two window values round to the same stored number."""
+    x = seeded((N, Cin, H, W), 81, device='cuda')
+    w = seeded((Cout, Cin, 3, 3), 82, 0.05, device='cuda')
+    b = seeded((Cout,), 83, 0.1, device='cuda')
+    xs = ops.from_nchw(F.relu(x))
+    pw = ops.PackedWeight(w, 0, cols_pad=Cin)
+    got = ops.conv2d_pool(xs, pw, b)
+    assert got is not None, 'these shapes take the tensor-core kernel'
+    tap, pooled, idx = got
+    tap2, _, _ = ops.conv2d(xs, pw, b)
+    pooled2, idx2 = ops.relu_maxpool_fwd(tap2, want_idx=True)
+    assert torch.equal(tap.buf, tap2.buf)
+    # same VALUES (hi + lo); the split of a value into planes is not unique when lo is exactly half an ulp of hi
+    assert torch.equal(nhwc(pooled), nhwc(pooled2))
+    assert idx.shape == idx2.shape and float((idx != idx2).float().mean()) < 1e-4
+    ref = F.max_pool2d(F.relu(F.conv2d(F.relu(x), w, b, padding=1)), 2)
+    assert rel_l2(nhwc(pooled), ref) < 1e-4
+    # the routing bytes point at a window element whose stored value is the pooled value (4: nothing positive)
+    t = nhwc(tap2)[:, :, :2 * (H // 2), :2 * (W // 2)]
+    win = torch.stack([t[:, :, 0::2, 0::2], t[:, :, 0::2, 1::2], t[:, :, 1::2, 0::2], t[:, :, 1::2, 1::2]], 0)
+    sel = idx.permute(0, 3, 1, 2).long()
+    picked = torch.gather(torch.cat([win, torch.zeros_like(win[:1])], 0), 0, sel.unsqueeze(0)).squeeze(0)
+    assert torch.equal(picked.clamp(min=0), nhwc(pooled))
+
+
 def test_mse(ops):
     x = seeded((2, 128, 10, 12), 41, device='cuda').requires_grad_(True)
     t = seeded((2, 128, 10, 12), 42, device='cuda')
