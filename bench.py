@@ -154,7 +154,7 @@ class KernelTrace:
 
     def run(self, step, steps):
         ops, L = self.ops, self.L
-        real = ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed
+        real = ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed, ops.conv2d_pool
 
         def conv2d(xs, w, *a, **k):
             out, e0, e1 = self._bracket(real[0], (xs, w) + a, k)
@@ -178,6 +178,14 @@ class KernelTrace:
                                   2.0 * xs.N * xs.H * xs.W * xs.C * w_img_rows, e0, e1))
             return out
 
+        def conv2d_pool(xs, w, *a, **k):
+            # forward 3x3 conv_tc launch whose epilogue also writes the ReLU + max-pool output
+            out, e0, e1 = self._bracket(real[4], (xs, w) + a, k)
+            if out is not None:
+                self.conv.append((f'conv_tc_kernel<3x3, fused relu + max-pool> {xs.C}->{w.cout} @{xs.H}x{xs.W}x{xs.N}', 3,
+                                  2.0 * xs.N * xs.H * xs.W * xs.C * w.cout * 9, e0, e1))
+            return out
+
         def instnorm_fwd(x, *a, **k):
             out, e0, e1 = self._bracket(real[1], (x,) + a, k)
             y = out[0]
@@ -191,14 +199,14 @@ class KernelTrace:
             rd = (x.buf[0].numel() * min(x.planes, ops.bwd_planes()) + gy.buf.numel()) * 2
             self.norm.append(('instnorm_bwd (in_stats + in_finalize_bwd + in_apply_bwd)', 2.0 * rd + dx.buf.numel() * 2, e0, e1))
             return out
-        ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed = conv2d, instnorm_fwd, instnorm_bwd, conv2d_routed
+        ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed, ops.conv2d_pool = conv2d, instnorm_fwd, instnorm_bwd, conv2d_routed, conv2d_pool
         try:
             torch.cuda.synchronize()
             for _ in range(steps):
                 step()
             torch.cuda.synchronize()
         finally:
-            ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed = real
+            ops.conv2d, ops.instnorm_fwd, ops.instnorm_bwd, ops.conv2d_routed, ops.conv2d_pool = real
         self.steps = steps
 
     @staticmethod
