@@ -12,7 +12,8 @@
 // quarter: warps 2..5 own M block 0 = box pixels 0..127, warps 6..9 M block 1 = box pixels 128..255, of which 128..179
 // exist).  Operand split as everywhere else: hi x [w_hi | w_lo] as ONE N = 64 MMA (main | correction accumulators), then
 // lo x w_hi (N = 32) into the correction accumulator.  The epilogue writes (main + correction) * acc_mul of its box pixel
-// to a shared-memory table P[256][27], then the first 128 epilogue threads gather the nine taps of their output pixel.
+// to a shared-memory table P[256][27] (two tables, alternating between tiles: one barrier per tile), then the 256 epilogue
+// threads gather the nine taps of their output pixel and channel(s).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tmap.cuh"
@@ -26,7 +27,7 @@ constexpr int A_PLANE = (A_BYTES + 1023) & ~1023;            // 23552
 constexpr int A_SLOT = 2 * A_PLANE, NA = 3;
 constexpr int A_TAIL = 256 * 128 - A_PLANE;                  // M block 1 of the lo plane of the last slot reads this far past it
 constexpr int W_ROWS = 27, W_PLANE = 32 * 128, W_BYTES = 2 * W_PLANE;     // [w_hi rows 0..31 | w_lo rows 32..63]
-constexpr int P_LD = 27, P_BYTES = 256 * P_LD * 4;
+constexpr int P_LD = 27, P_TABLE = 256 * P_LD, P_BYTES = 2 * P_TABLE * 4;      // two tables: tiles alternate
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM = 1024 + NA * A_SLOT + A_TAIL + W_BYTES + P_BYTES + BAR_BYTES;
 constexpr int THREADS = 320, EPI_FIRST = 2;
@@ -143,35 +144,39 @@ conv_imgrad_tc_kernel(const __grid_constant__ CUtensorMap tmA_hi, const __grid_c
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&t_empty[acc]);
-            // the table of the previous tile has been gathered by everyone (second barrier of that tile) before it is overwritten
+            // tables alternate between tiles: the one written now was last read two tiles ago, and every thread has passed the
+            // barrier of the tile in between since then (one barrier per tile)
+            float* tab = sP + acc * P_TABLE;
             if (row < BOX_PIX) {
-                float* dst = sP + row * P_LD;
+                float* dst = tab + row * P_LD;
 #pragma unroll
                 for (int i = 0; i < 16; ++i) dst[i] = (__uint_as_float(m0[i]) + __uint_as_float(c0[i])) * mul;
 #pragma unroll
                 for (int i = 0; i < W_ROWS - 16; ++i) dst[16 + i] = (__uint_as_float(m1[i]) + __uint_as_float(c1[i])) * mul;
             }
             asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (et < TH * TW) {
+            {
+                // all 256 threads gather: threads 0..127 channels 0 and 1 of their pixel, threads 128..255 channel 2
                 const int n = wk / tiles_per_img, t = wk - n * tiles_per_img;
                 const int th = t / p.tiles_w, tw = t - th * p.tiles_w;
-                const int hl = et / TW, wl = et - hl * TW;
+                const int m = et & (TH * TW - 1), part = et >> 7;
+                const int hl = m / TW, wl = m - hl * TW;
                 const int h = th * TH + hl, w = tw * TW + wl;
                 if (h < p.H && w < p.W) {
 #pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        if (c < p.nchw_c) {
+                    for (int cc = 0; cc < 2; ++cc) {
+                        const int c = part ? 2 : cc;
+                        if ((part == 0 || cc == 0) && c < p.nchw_c) {
                             float s = 0.f;
 #pragma unroll
                             for (int r = 0; r < 3; ++r)
 #pragma unroll
-                                for (int sx = 0; sx < 3; ++sx) s += sP[((hl + r) * BOX_W + wl + sx) * P_LD + c * 9 + r * 3 + sx];
+                                for (int sx = 0; sx < 3; ++sx) s += tab[((hl + r) * BOX_W + wl + sx) * P_LD + c * 9 + r * 3 + sx];
                             p.out[(static_cast<size_t>(n) * p.nchw_c + c) * HW + static_cast<size_t>(h) * p.W + w] = s;
                         }
                     }
                 }
             }
-            asm volatile("bar.sync 2, 256;" ::: "memory");
         }
     }
     ptx::tc_fence_before();
